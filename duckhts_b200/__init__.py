@@ -1,0 +1,9 @@
+"""duckhts_b200 — B200-native read_bam / bgunzip hot path of DuckHTS.
+
+The product is native: `lib/libduckhts_cuda.so` (C-ABI in include/duckhts_cuda.h, sm_100a kernels) and
+`lib/duckhts_b200.duckdb_extension.so` (DuckDB C-API table functions).  This Python package is a thin
+ctypes mirror of the C-ABI used by tests and bench.py.  There is no CPU fallback: importing works
+anywhere, but every compute entry point raises if the CUDA library or a GPU is missing.
+"""
+from ._lib import DuckhtsError, lib, lib_path  # noqa: F401
+from .bgzf import BgzfDevice, Context, bgzf_inflate, bgzf_walk  # noqa: F401

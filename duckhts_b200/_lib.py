@@ -1,0 +1,76 @@
+"""ctypes binding of libduckhts_cuda.so (include/duckhts_cuda.h).  Fails loudly if the library is absent."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+lib_path = os.path.join(_HERE, "lib", "libduckhts_cuda.so")
+
+
+class DuckhtsError(RuntimeError):
+    pass
+
+
+class BgzfBlock(C.Structure):
+    _fields_ = [("coffset", C.c_uint64), ("csize", C.c_uint32), ("isize", C.c_uint32), ("crc", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+
+class InflateStats(C.Structure):
+    _fields_ = [("n_blocks", C.c_uint64), ("comp_bytes", C.c_uint64), ("out_bytes", C.c_uint64),
+                ("bad_block", C.c_int64), ("bad_code", C.c_int32), ("eof_marker", C.c_int32),
+                ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
+
+
+_lib = None
+
+# name -> (restype, argtypes); tests/test_abi.py checks every symbol declared in include/*.h is here and exported
+SIGNATURES = {
+    "dh_version": (C.c_char_p, []),
+    "dh_last_error": (C.c_char_p, []),
+    "dh_device_count": (C.c_int, []),
+    "dh_ctx_create": (C.c_void_p, [C.c_int]),
+    "dh_ctx_destroy": (None, [C.c_void_p]),
+    "dh_ctx_sm_count": (C.c_int, [C.c_void_p]),
+    "dh_host_alloc": (C.c_void_p, [C.c_size_t]),
+    "dh_host_free": (None, [C.c_void_p]),
+    "dh_bgzf_walk": (C.c_int64, [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(BgzfBlock), C.c_int64,
+                                 C.POINTER(C.c_uint64), C.c_int]),
+    "dh_bgzf_inflate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                       C.POINTER(C.c_uint64), C.POINTER(InflateStats)]),
+    "dh_bgzf_dev_load": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "dh_bgzf_dev_free": (None, [C.c_void_p]),
+    "dh_bgzf_dev_nblocks": (C.c_uint64, [C.c_void_p]),
+    "dh_bgzf_dev_comp_bytes": (C.c_uint64, [C.c_void_p]),
+    "dh_bgzf_dev_out_bytes": (C.c_uint64, [C.c_void_p]),
+    "dh_bgzf_dev_inflate": (C.c_int, [C.c_void_p]),
+    "dh_bgzf_dev_check": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
+    "dh_bgzf_dev_read": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
+    "dh_ctx_sync": (C.c_int, [C.c_void_p]),
+    "dh_timer_start": (C.c_int, [C.c_void_p]),
+    "dh_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "dh_flush_l2": (C.c_int, [C.c_void_p]),
+    "dh_measure_pcie": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "dh_ctx_launch_count": (C.c_uint64, [C.c_void_p]),
+}
+
+
+def lib():
+    """Load libduckhts_cuda.so once.  No fallback: a missing library is an error, not a slow path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(lib_path):
+            raise DuckhtsError(f"{lib_path} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(duckhts_b200 has no CPU fallback)")
+        _lib = C.CDLL(lib_path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(_lib, name)
+            fn.restype = res
+            fn.argtypes = args
+    return _lib
+
+
+def check(rc, what=""):
+    if rc is None or (isinstance(rc, int) and rc < 0):
+        msg = lib().dh_last_error().decode(errors="replace")
+        raise DuckhtsError(f"{what}: rc={rc}: {msg}")
+    return rc

@@ -1,0 +1,499 @@
+// dh_api.cu — C-ABI of libduckhts_cuda.so: contexts, BGZF framing (A1), inflate entry points (A2/A3).
+// Declarations and the reference interfaces each one replaces: include/duckhts_cuda.h.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "dh_internal.h"
+#include "inflate_core.cuh"
+
+namespace dh {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+int cuda_fail(cudaError_t e, const char *what) {
+    set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return DH_ECUDA;
+}
+
+int DevBuf::reserve(size_t n) {
+    if (n <= cap) return DH_OK;
+    release();
+    size_t want = std::max(n, (size_t)1 << 20);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMalloc"); }
+    cap = want;
+    return DH_OK;
+}
+void DevBuf::release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+}
+int PinBuf::reserve(size_t n) {
+    if (n <= cap) return DH_OK;
+    release();
+    size_t want = std::max(n, (size_t)1 << 16);
+    cudaError_t e = cudaMallocHost(&p, want);
+    if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMallocHost"); }
+    cap = want;
+    return DH_OK;
+}
+void PinBuf::release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+}
+
+// ---- A1: framing -------------------------------------------------------------------------------------
+// htslib/bgzf.c:896-903 check_header: ID1=31 ID2=139 CM=8, FLG&4, XLEN=6, SI1='B' SI2='C', SLEN=2.
+// A plain-gzip header (check_header == -1) is not BGZF: the reference switches to a streaming gzip
+// reader (bgzf.c:1168-1195), which is outside this path — we report DH_EFORMAT.
+static inline bool bgzf_header_ok(const uint8_t *h) {
+    return h[0] == 31 && h[1] == 139 && h[2] == 8 && (h[3] & 4) && (h[10] | (h[11] << 8)) == 6 && h[12] == 'B' &&
+           h[13] == 'C' && (h[14] | (h[15] << 8)) == 2;
+}
+static inline uint32_t le32(const uint8_t *p) {
+    return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+}
+
+int walk_blocks(const uint8_t *data, uint64_t size, uint64_t start, BlockTable &bt, uint64_t *bad_off) {
+    uint64_t off = start, u = bt.uoff.empty() ? 0 : bt.uoff.back();
+    if (bt.uoff.empty()) bt.uoff.push_back(0);
+    bt.eof_marker = false;
+    while (off < size) {
+        if (size - off < 18 || !bgzf_header_ok(data + off)) { if (bad_off) *bad_off = off; return DH_EFORMAT; }
+        uint32_t bsize = (uint32_t)(data[off + 16] | (data[off + 17] << 8)) + 1;
+        // bgzf.c:1198-1204: block_length < BLOCK_HEADER_LENGTH is an error; we also need room for the footer
+        if (bsize < 18 + 8 || size - off < bsize) { if (bad_off) *bad_off = off; return DH_EFORMAT; }
+        dh_bgzf_block b;
+        b.coffset = off;
+        b.csize = bsize;
+        b.crc = le32(data + off + bsize - 8);
+        b.isize = le32(data + off + bsize - 4);
+        b.reserved = 0;
+        if (b.isize > BGZF_MAX_OUT) { if (bad_off) *bad_off = off; return DH_EFORMAT; }
+        bt.blocks.push_back(b);
+        u += b.isize;
+        bt.uoff.push_back(u);
+        bt.eof_marker = (bsize == 28 && b.isize == 0);
+        off += bsize;
+    }
+    bt.end_off = off;
+    return DH_OK;
+}
+
+// Build device block descriptors for blocks [b0,b1) whose compressed bytes were uploaded starting at
+// file offset `comp_base` (16-byte aligned) and whose output buffer starts at inflated offset `out_base`.
+static void fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_base, uint64_t out_base,
+                       BlockDesc *d) {
+    for (size_t i = b0; i < b1; ++i) {
+        const dh_bgzf_block &b = bt.blocks[i];
+        BlockDesc &o = d[i - b0];
+        o.in_off = (uint32_t)(b.coffset + 18 - comp_base);
+        o.in_len = b.csize - 26;
+        o.isize = b.isize;
+        o.crc = b.crc;
+        o.out_off = bt.uoff[i] - out_base;
+    }
+}
+
+}  // namespace dh
+
+using namespace dh;
+
+extern "C" {
+
+const char *dh_version(void) { return "duckhts_b200 0.1 (sm_100a)"; }
+const char *dh_last_error(void) { return g_err; }
+
+int dh_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+dh_ctx *dh_ctx_create(int device) {
+    int n = dh_device_count();
+    if (n <= 0) { set_error("no CUDA device available: duckhts_b200 has no CPU fallback"); return nullptr; }
+    if (device < 0 || device >= n) { set_error("device %d out of range (have %d)", device, n); return nullptr; }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) { cuda_fail(e, "cudaSetDevice"); return nullptr; }
+    dh_ctx *c = new dh_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) { cuda_fail(e, "cudaGetDeviceProperties"); delete c; return nullptr; }
+    if (prop.major < 10) {
+        set_error("device %d is sm_%d%d; this library ships sm_100a code only", device, prop.major, prop.minor);
+        delete c;
+        return nullptr;
+    }
+    c->sm_count = prop.multiProcessorCount;
+    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; i < 3 && ok; ++i) {
+        ok = cudaStreamCreateWithFlags(&c->copy_streams[i], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreate(&c->slots[i].ev_k0) == cudaSuccess && cudaEventCreate(&c->slots[i].ev_k1) == cudaSuccess &&
+             cudaEventCreate(&c->slots[i].ev_done) == cudaSuccess;
+    }
+    ok = ok && cudaEventCreate(&c->ev_timer[0]) == cudaSuccess && cudaEventCreate(&c->ev_timer[1]) == cudaSuccess;
+    ok = ok && c->counter.reserve(64 * sizeof(unsigned int)) == DH_OK;
+    if (!ok) {
+        if (!g_err[0]) set_error("failed to create CUDA streams/events");
+        dh_ctx_destroy(c);
+        return nullptr;
+    }
+    return c;
+}
+
+void dh_ctx_destroy(dh_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < 3; ++i) {
+        auto &s = c->slots[i];
+        s.comp.release(); s.out.release(); s.desc.release(); s.status.release();
+        s.h_desc.release(); s.h_status.release();
+        if (s.ev_k0) cudaEventDestroy(s.ev_k0);
+        if (s.ev_k1) cudaEventDestroy(s.ev_k1);
+        if (s.ev_done) cudaEventDestroy(s.ev_done);
+        if (c->copy_streams[i]) cudaStreamDestroy(c->copy_streams[i]);
+    }
+    c->l2_scratch.release();
+    c->counter.release();
+    if (c->ev_timer[0]) cudaEventDestroy(c->ev_timer[0]);
+    if (c->ev_timer[1]) cudaEventDestroy(c->ev_timer[1]);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int dh_ctx_sm_count(const dh_ctx *c) { return c ? c->sm_count : 0; }
+uint64_t dh_ctx_launch_count(const dh_ctx *c) { return c ? c->launches : 0; }
+
+void *dh_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 1);
+    if (e != cudaSuccess) { cuda_fail(e, "cudaMallocHost"); return nullptr; }
+    return p;
+}
+void dh_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
+int64_t dh_bgzf_walk(const uint8_t *data, uint64_t size, uint64_t start, dh_bgzf_block *out, int64_t cap,
+                     uint64_t *end_off, int strict) {
+    if (!data || start > size) { set_error("dh_bgzf_walk: bad arguments"); return DH_EINVAL; }
+    BlockTable bt;
+    uint64_t bad = 0;
+    int rc = walk_blocks(data, size, start, bt, &bad);
+    if (rc != DH_OK) {
+        // blocks before the bad offset are still reported; a short tail is only an error when strict
+        bool truncated_tail = bad + 18 > size || (bgzf_header_ok(data + bad) && size - bad < (uint64_t)(data[bad + 16] | (data[bad + 17] << 8)) + 1);
+        if (strict || !truncated_tail) {
+            set_error("invalid BGZF header at offset %llu", (unsigned long long)bad);
+            return DH_EFORMAT;
+        }
+        bt.end_off = bad;
+    }
+    int64_t n = (int64_t)bt.blocks.size();
+    if (out) {
+        if (n > cap) n = cap;
+        memcpy(out, bt.blocks.data(), (size_t)n * sizeof(dh_bgzf_block));
+        if (n < (int64_t)bt.blocks.size()) bt.end_off = bt.blocks[n].coffset;
+    }
+    if (end_off) *end_off = bt.end_off;
+    return n;
+}
+
+// ---- A2/A3 host -> host, pipelined over segments -------------------------------------------------------
+static const uint64_t SEG_COMP = 384ull << 20;   // compressed bytes per segment
+static const uint64_t SEG_OUT = 1536ull << 20;   // inflated bytes per segment
+static const size_t SEG_BLOCKS = 1u << 17;
+
+int dh_bgzf_inflate_host(dh_ctx *c, const uint8_t *comp, uint64_t comp_size, uint8_t *out, uint64_t out_cap,
+                         uint64_t *out_size, dh_inflate_stats *st) {
+    if (!c || (!comp && comp_size)) { set_error("dh_bgzf_inflate_host: bad arguments"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(c->device));
+    dh_inflate_stats local;
+    if (!st) st = &local;
+    memset(st, 0, sizeof *st);
+    st->bad_block = -1;
+
+    BlockTable bt;
+    uint64_t bad_off = 0;
+    int wrc = walk_blocks(comp, comp_size, 0, bt, &bad_off);
+    if (wrc != DH_OK) {
+        st->bad_block = (int64_t)bt.blocks.size();
+        st->bad_code = INF_ERR_HEADER;
+        set_error("invalid BGZF header at offset %llu", (unsigned long long)bad_off);
+        return DH_EFORMAT;
+    }
+    const size_t nb = bt.blocks.size();
+    st->n_blocks = nb;
+    st->comp_bytes = bt.end_off;
+    st->out_bytes = bt.uoff.back();
+    st->eof_marker = bt.eof_marker;
+    if (out_size) *out_size = bt.uoff.back();
+    if (out && out_cap < bt.uoff.back()) { set_error("output buffer too small: need %llu", (unsigned long long)bt.uoff.back()); return DH_EINVAL; }
+
+    cudaEvent_t ev_begin, ev_end;
+    DH_CUDA(cudaEventCreate(&ev_begin));
+    DH_CUDA(cudaEventCreate(&ev_end));
+    DH_CUDA(cudaEventRecord(ev_begin, c->copy_streams[0]));
+
+    struct Pending { size_t b0, b1; int slot; bool live; };
+    Pending pend[3] = {};
+    float kernel_ms = 0.f;
+    int rc = DH_OK;
+    auto retire = [&](Pending &p) -> int {
+        if (!p.live) return DH_OK;
+        auto &s = c->slots[p.slot];
+        DH_CUDA(cudaEventSynchronize(s.ev_done));
+        float ms = 0.f;
+        DH_CUDA(cudaEventElapsedTime(&ms, s.ev_k0, s.ev_k1));
+        kernel_ms += ms;
+        const int *hs = (const int *)s.h_status.p;
+        for (size_t i = p.b0; i < p.b1; ++i)
+            if (hs[i - p.b0] != 0 && st->bad_block < 0) { st->bad_block = (int64_t)i; st->bad_code = hs[i - p.b0]; }
+        p.live = false;
+        return DH_OK;
+    };
+
+    size_t b = 0;
+    int seg = 0;
+    while (b < nb && rc == DH_OK) {
+        // cut a segment on block boundaries
+        size_t e = b;
+        uint64_t cbase = bt.blocks[b].coffset & ~15ull;
+        while (e < nb && e - b < SEG_BLOCKS && bt.blocks[e].coffset + bt.blocks[e].csize - cbase <= SEG_COMP &&
+               bt.uoff[e + 1] - bt.uoff[b] <= SEG_OUT)
+            ++e;
+        if (e == b) e = b + 1;
+        const int slot = seg % 3;
+        auto &s = c->slots[slot];
+        cudaStream_t strm = c->copy_streams[slot];
+        if ((rc = retire(pend[slot])) != DH_OK) break;
+        const uint64_t cend = bt.blocks[e - 1].coffset + bt.blocks[e - 1].csize;
+        const uint64_t cbytes = cend - cbase, obytes = bt.uoff[e] - bt.uoff[b];
+        if ((rc = s.comp.reserve(cbytes + DH_COMP_PAD)) != DH_OK) break;
+        if ((rc = s.out.reserve(obytes + BGZF_MAX_OUT)) != DH_OK) break;
+        if ((rc = s.desc.reserve((e - b) * sizeof(BlockDesc))) != DH_OK) break;
+        if ((rc = s.status.reserve((e - b) * sizeof(int))) != DH_OK) break;
+        if ((rc = s.h_desc.reserve((e - b) * sizeof(BlockDesc))) != DH_OK) break;
+        if ((rc = s.h_status.reserve((e - b) * sizeof(int))) != DH_OK) break;
+        fill_descs(bt, b, e, cbase, bt.uoff[b], (BlockDesc *)s.h_desc.p);
+        DH_CUDA(cudaMemcpyAsync(s.comp.p, comp + cbase, cbytes, cudaMemcpyHostToDevice, strm));
+        DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + cbytes, 0, DH_COMP_PAD, strm));
+        DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, (e - b) * sizeof(BlockDesc), cudaMemcpyHostToDevice, strm));
+        DH_CUDA(cudaEventRecord(s.ev_k0, strm));
+        DH_CUDA(launch_bgzf_inflate((const uint8_t *)s.comp.p, (const BlockDesc *)s.desc.p, (uint32_t)(e - b),
+                                    (uint8_t *)s.out.p, (int *)s.status.p, (unsigned int *)c->counter.p + 1 + slot,
+                                    c->sm_count, strm));
+        c->launches++;
+        DH_CUDA(cudaEventRecord(s.ev_k1, strm));
+        if (out && obytes) DH_CUDA(cudaMemcpyAsync(out + bt.uoff[b], s.out.p, obytes, cudaMemcpyDeviceToHost, strm));
+        DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, (e - b) * sizeof(int), cudaMemcpyDeviceToHost, strm));
+        DH_CUDA(cudaEventRecord(s.ev_done, strm));
+        pend[slot] = Pending{b, e, slot, true};
+        b = e;
+        ++seg;
+    }
+    for (int i = 0; i < 3; ++i) {
+        // retire in issue order so that bad_block is the FIRST failing block
+        int slot = (seg + i) % 3;
+        int r2 = retire(pend[slot]);
+        if (rc == DH_OK) rc = r2;
+    }
+    // all slots done: stamp the end on every stream's tail by waiting for them explicitly
+    for (int i = 0; i < 3; ++i) cudaStreamSynchronize(c->copy_streams[i]);
+    cudaEventRecord(ev_end, c->copy_streams[0]);
+    cudaEventSynchronize(ev_end);
+    cudaEventElapsedTime(&st->total_ms, ev_begin, ev_end);
+    cudaEventDestroy(ev_begin);
+    cudaEventDestroy(ev_end);
+    st->kernel_ms = kernel_ms;
+    if (rc != DH_OK) return rc;
+    if (st->bad_block >= 0) {
+        set_error("BGZF block %lld failed inflate/CRC check (code %d)", (long long)st->bad_block, st->bad_code);
+        return DH_EDATA;
+    }
+    return DH_OK;
+}
+
+// ---- device-resident variant -----------------------------------------------------------------------------
+struct dh_bgzf_dev {
+    dh_ctx *ctx;
+    BlockTable bt;
+    DevBuf comp, out, desc, status;
+    struct Seg { size_t b0, b1; uint64_t cbase; };
+    std::vector<Seg> segs;
+};
+
+dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size) {
+    if (!c || !comp) { set_error("dh_bgzf_dev_load: bad arguments"); return nullptr; }
+    if (cudaSetDevice(c->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return nullptr; }
+    dh_bgzf_dev *d = new dh_bgzf_dev();
+    d->ctx = c;
+    uint64_t bad = 0;
+    if (walk_blocks(comp, comp_size, 0, d->bt, &bad) != DH_OK) {
+        set_error("invalid BGZF header at offset %llu", (unsigned long long)bad);
+        delete d;
+        return nullptr;
+    }
+    const size_t nb = d->bt.blocks.size();
+    const uint64_t cbytes = d->bt.end_off;
+    bool ok = d->comp.reserve(cbytes + DH_COMP_PAD) == DH_OK && d->out.reserve(d->bt.uoff.back() + BGZF_MAX_OUT) == DH_OK &&
+              d->desc.reserve((nb + 1) * sizeof(BlockDesc)) == DH_OK && d->status.reserve((nb + 1) * sizeof(int)) == DH_OK;
+    if (!ok) { dh_bgzf_dev_free(d); return nullptr; }
+    // segments: in_off is 32-bit, so a launch covers at most 2 GiB of compressed bytes
+    std::vector<BlockDesc> descs(nb);
+    size_t b = 0;
+    while (b < nb) {
+        size_t e = b;
+        uint64_t cbase = d->bt.blocks[b].coffset & ~15ull;
+        while (e < nb && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
+        fill_descs(d->bt, b, e, cbase, 0, descs.data() + b);
+        d->segs.push_back({b, e, cbase});
+        b = e;
+    }
+    cudaError_t e1 = cudaMemcpy(d->comp.p, comp, cbytes, cudaMemcpyHostToDevice);
+    cudaError_t e2 = cudaMemset((uint8_t *)d->comp.p + cbytes, 0, DH_COMP_PAD);
+    cudaError_t e3 = nb ? cudaMemcpy(d->desc.p, descs.data(), nb * sizeof(BlockDesc), cudaMemcpyHostToDevice) : cudaSuccess;
+    if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
+        cuda_fail(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3), "dh_bgzf_dev_load upload");
+        dh_bgzf_dev_free(d);
+        return nullptr;
+    }
+    return d;
+}
+
+void dh_bgzf_dev_free(dh_bgzf_dev *d) {
+    if (!d) return;
+    cudaSetDevice(d->ctx->device);
+    cudaStreamSynchronize(d->ctx->stream);
+    d->comp.release(); d->out.release(); d->desc.release(); d->status.release();
+    delete d;
+}
+uint64_t dh_bgzf_dev_nblocks(const dh_bgzf_dev *d) { return d ? d->bt.blocks.size() : 0; }
+uint64_t dh_bgzf_dev_comp_bytes(const dh_bgzf_dev *d) { return d ? d->bt.end_off : 0; }
+uint64_t dh_bgzf_dev_out_bytes(const dh_bgzf_dev *d) { return d ? d->bt.uoff.back() : 0; }
+
+int dh_bgzf_dev_inflate(dh_bgzf_dev *d) {
+    if (!d) { set_error("dh_bgzf_dev_inflate: null handle"); return DH_EINVAL; }
+    dh_ctx *c = d->ctx;
+    DH_CUDA(cudaSetDevice(c->device));
+    for (auto &s : d->segs) {
+        DH_CUDA(launch_bgzf_inflate((const uint8_t *)d->comp.p + s.cbase, (const BlockDesc *)d->desc.p + s.b0,
+                                    (uint32_t)(s.b1 - s.b0), (uint8_t *)d->out.p, (int *)d->status.p + s.b0,
+                                    (unsigned int *)c->counter.p, c->sm_count, c->stream));
+        c->launches++;
+    }
+    return DH_OK;
+}
+
+int dh_bgzf_dev_check(dh_bgzf_dev *d, int64_t *bad_block, int32_t *bad_code) {
+    if (!d) { set_error("dh_bgzf_dev_check: null handle"); return DH_EINVAL; }
+    dh_ctx *c = d->ctx;
+    DH_CUDA(cudaSetDevice(c->device));
+    const size_t nb = d->bt.blocks.size();
+    std::vector<int> hs(nb);
+    DH_CUDA(cudaStreamSynchronize(c->stream));
+    if (nb) DH_CUDA(cudaMemcpy(hs.data(), d->status.p, nb * sizeof(int), cudaMemcpyDeviceToHost));
+    if (bad_block) *bad_block = -1;
+    if (bad_code) *bad_code = 0;
+    for (size_t i = 0; i < nb; ++i)
+        if (hs[i]) {
+            if (bad_block) *bad_block = (int64_t)i;
+            if (bad_code) *bad_code = hs[i];
+            set_error("BGZF block %zu failed inflate/CRC check (code %d)", i, hs[i]);
+            return DH_EDATA;
+        }
+    return DH_OK;
+}
+
+int dh_bgzf_dev_read(dh_bgzf_dev *d, uint64_t offset, uint8_t *dst, uint64_t n) {
+    if (!d || !dst || offset + n > d->bt.uoff.back()) { set_error("dh_bgzf_dev_read: bad range"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(d->ctx->device));
+    DH_CUDA(cudaStreamSynchronize(d->ctx->stream));
+    if (n) DH_CUDA(cudaMemcpy(dst, (const uint8_t *)d->out.p + offset, n, cudaMemcpyDeviceToHost));
+    return DH_OK;
+}
+
+// ---- timing / measurement helpers -----------------------------------------------------------------------
+int dh_ctx_sync(dh_ctx *c) {
+    if (!c) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(c->device));
+    DH_CUDA(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(c->copy_streams[i]));
+    return DH_OK;
+}
+int dh_timer_start(dh_ctx *c) {
+    if (!c) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(c->device));
+    DH_CUDA(cudaEventRecord(c->ev_timer[0], c->stream));
+    return DH_OK;
+}
+int dh_timer_stop(dh_ctx *c, float *ms) {
+    if (!c || !ms) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(c->device));
+    DH_CUDA(cudaEventRecord(c->ev_timer[1], c->stream));
+    DH_CUDA(cudaEventSynchronize(c->ev_timer[1]));
+    DH_CUDA(cudaEventElapsedTime(ms, c->ev_timer[0], c->ev_timer[1]));
+    return DH_OK;
+}
+int dh_flush_l2(dh_ctx *c) {
+    if (!c) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(c->device));
+    const size_t n = 256u << 20;  // 2x the 126 MB L2
+    int rc = c->l2_scratch.reserve(n);
+    if (rc != DH_OK) return rc;
+    DH_CUDA(cudaMemsetAsync(c->l2_scratch.p, 0x5a, n, c->stream));
+    return DH_OK;
+}
+int dh_measure_pcie(dh_ctx *c, uint64_t bytes, float *h2d_gbs, float *d2h_gbs) {
+    if (!c || !bytes) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(c->device));
+    void *h = nullptr, *d = nullptr;
+    DH_CUDA(cudaMallocHost(&h, bytes));
+    cudaError_t e = cudaMalloc(&d, bytes);
+    if (e != cudaSuccess) { cudaFreeHost(h); return cuda_fail(e, "cudaMalloc"); }
+    memset(h, 1, bytes);
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    float best_h2d = 0.f, best_d2h = 0.f;
+    for (int it = 0; it < 4; ++it) {
+        float ms;
+        cudaEventRecord(a, c->stream);
+        cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, c->stream);
+        cudaEventRecord(b, c->stream);
+        cudaEventSynchronize(b);
+        cudaEventElapsedTime(&ms, a, b);
+        best_h2d = std::max(best_h2d, (float)(bytes / 1e6 / ms));
+        cudaEventRecord(a, c->stream);
+        cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, c->stream);
+        cudaEventRecord(b, c->stream);
+        cudaEventSynchronize(b);
+        cudaEventElapsedTime(&ms, a, b);
+        best_d2h = std::max(best_d2h, (float)(bytes / 1e6 / ms));
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    cudaFree(d);
+    cudaFreeHost(h);
+    if (h2d_gbs) *h2d_gbs = best_h2d;
+    if (d2h_gbs) *d2h_gbs = best_d2h;
+    cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) return cuda_fail(le, "dh_measure_pcie");
+    return DH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,64 @@
+// dh_internal.h — internals shared by the translation units of libduckhts_cuda.so (not part of the C-ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/duckhts_cuda.h"
+#include "bgzf_inflate.cuh"
+
+namespace dh {
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);  // records the message, returns DH_ECUDA
+
+#define DH_CUDA(call)                                             \
+    do {                                                          \
+        cudaError_t e__ = (call);                                 \
+        if (e__ != cudaSuccess) return ::dh::cuda_fail(e__, #call); \
+    } while (0)
+
+// growable device / pinned-host buffers (never shrink; reused across calls)
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t n);
+    void release();
+};
+struct PinBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t n);
+    void release();
+};
+
+// host-side block table for a BGZF image (A1)
+struct BlockTable {
+    std::vector<dh_bgzf_block> blocks;
+    std::vector<uint64_t> uoff;  // inflated offset of each block; size nblocks+1
+    uint64_t end_off = 0;
+    bool eof_marker = false;
+};
+// walk data[start..size); returns DH_OK / DH_EFORMAT (bad header at *bad_off)
+int walk_blocks(const uint8_t *data, uint64_t size, uint64_t start, BlockTable &bt, uint64_t *bad_off);
+
+}  // namespace dh
+
+struct dh_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;        // the stream every kernel is launched on
+    cudaStream_t copy_streams[3] = {};    // pipeline slots for the *_host entry points
+    cudaEvent_t ev_timer[2] = {};
+    dh::DevBuf l2_scratch;
+    dh::DevBuf counter;                   // inflate ticket counters (one word per pipeline slot + main)
+    uint64_t launches = 0;
+    // pipeline slots of dh_bgzf_inflate_host
+    struct Slot {
+        dh::DevBuf comp, out, desc, status;
+        dh::PinBuf h_desc, h_status;
+        cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
+    } slots[3];
+};

@@ -22,9 +22,11 @@
 #if defined(__CUDACC__)
 #define DH_HD __host__ __device__ __forceinline__
 #define DH_HDM __host__ __device__ __forceinline__
+#define DH_HD_NOINLINE static __host__ __device__ __noinline__
 #else
 #define DH_HD static inline
 #define DH_HDM inline
+#define DH_HD_NOINLINE static __attribute__((noinline))
 #endif
 
 namespace dh {
@@ -107,9 +109,10 @@ DH_HD void dist_sym(uint32_t s, uint32_t &base, uint32_t &extra) {
 // Returns 0 on success, 1 on over-subscribed / disallowed-incomplete code.
 // Serial version (one lane does all the work; every lane of the group calls it with identical
 // arguments on the device, where `leader` gates the shared-memory stores).
-template <typename LensPtr>
-DH_HD int build_table(LensPtr lens, int n, int root, uint32_t *table, int enough, uint16_t *sorted, int mode,
-                      bool leader) {
+// Out of line on purpose: five call sites, cold relative to the symbol loop, and it only touches the
+// group's shared-memory tables (no decoder registers escape).
+DH_HD_NOINLINE int build_table(bool leader, const uint8_t *lens, int n, int root, uint32_t *table, int enough,
+                               uint16_t *sorted, int mode) {
     uint32_t count[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) count[i] = 0;
@@ -159,10 +162,7 @@ DH_HD int build_table(LensPtr lens, int n, int root, uint32_t *table, int enough
         if (left > 0)
             for (uint32_t i = 0; i < nroot; ++i) table[i] = mk_entry(0, KIND_BAD, 0, 1);
     }
-#if defined(__CUDA_ARCH__)
-    __syncwarp(__activemask());
-#endif
-    if (!leader) return 0;
+    if (!leader) return 0;  // the group meets again at the caller's io.sync()
 
     uint32_t code = 0;        // next canonical code (MSB-first value) at the current length
     uint32_t idx = 0;         // index into sorted[]
@@ -208,11 +208,16 @@ DH_HD int build_table(LensPtr lens, int n, int root, uint32_t *table, int enough
                     sub_bits = curr;
                     sub_start = next_free;
                     next_free += 1u << sub_bits;
-                    if ((int)next_free > enough) return 1;  // cannot happen for valid deflate codes
+                    if ((int)next_free > enough) {  // cannot happen (see "enough" bounds); never write out of range
+                        next_free = sub_start;
+                        sub_start = nroot;
+                        sub_bits = 0;
+                    }
                     table[prefix] = mk_entry(sub_start, KIND_SUB, sub_bits, root);
                 }
                 uint32_t hi = rev >> root;
-                for (uint32_t i = hi; i < (1u << sub_bits); i += (1u << (len - root))) table[sub_start + i] = ent;
+                for (uint32_t i = hi; i < (1u << sub_bits); i += (1u << (len - root)))
+                    if ((int)(sub_start + i) < enough) table[sub_start + i] = ent;
             }
         }
         code <<= 1;
@@ -287,7 +292,7 @@ struct Inflater {
         // the precode table borrows the (not yet built) distance table area; its sort scratch sits behind it
         uint32_t *pre = t.dist;
         uint16_t *scratch = reinterpret_cast<uint16_t *>(t.dist + (1 << PRE_ROOT));
-        if (build_table(t.lens, 19, PRE_ROOT, pre, 1 << PRE_ROOT, scratch, 2, io.leader())) return INF_ERR_PRECODE;
+        if (build_table(io.leader(), t.lens, 19, PRE_ROOT, pre, 1 << PRE_ROOT, scratch, 2)) return INF_ERR_PRECODE;
         io.sync();
         // litlen + distance code lengths
         uint32_t n = hlit + hdist, i = 0, prev = 0;
@@ -332,12 +337,11 @@ struct Inflater {
             for (uint32_t k = hlit; k < 288; ++k) t.lens[k] = 0;
         }
         io.sync();
-        if (build_table(t.lens, 288, LIT_ROOT, t.lit, LIT_ENOUGH, reinterpret_cast<uint16_t *>(t.dist), 0,
-                        io.leader()))
+        if (build_table(io.leader(), t.lens, 288, LIT_ROOT, t.lit, LIT_ENOUGH, reinterpret_cast<uint16_t *>(t.dist), 0))
             return INF_ERR_LITLEN_SET;
         io.sync();
         uint16_t dscratch[32];
-        if (build_table(t.lens + 288, 32, DIST_ROOT, t.dist, DIST_ENOUGH, dscratch, 1, io.leader()))
+        if (build_table(io.leader(), t.lens + 288, 32, DIST_ROOT, t.dist, DIST_ENOUGH, dscratch, 1))
             return INF_ERR_DIST_SET;
         io.sync();
         return INF_OK;
@@ -352,12 +356,11 @@ struct Inflater {
             for (int i = 288; i < 320; ++i) t.lens[i] = 5;
         }
         io.sync();
-        if (build_table(t.lens, 288, LIT_ROOT, t.lit, LIT_ENOUGH, reinterpret_cast<uint16_t *>(t.dist), 0,
-                        io.leader()))
+        if (build_table(io.leader(), t.lens, 288, LIT_ROOT, t.lit, LIT_ENOUGH, reinterpret_cast<uint16_t *>(t.dist), 0))
             return INF_ERR_LITLEN_SET;
         io.sync();
         uint16_t dscratch[32];
-        if (build_table(t.lens + 288, 32, DIST_ROOT, t.dist, DIST_ENOUGH, dscratch, 1, io.leader()))
+        if (build_table(io.leader(), t.lens + 288, 32, DIST_ROOT, t.dist, DIST_ENOUGH, dscratch, 1))
             return INF_ERR_DIST_SET;
         io.sync();
         return INF_OK;
@@ -367,8 +370,10 @@ struct Inflater {
     DH_HDM int decode_block() {
         const uint32_t *lit = t.lit;
         const uint32_t *dist = t.dist;
+        const uint32_t in_limit = in_len + 8;
         for (;;) {
-            refill();  // >= 33 bits: enough for litlen code (15) + length extra (5) ...
+            if (inpos > in_limit) return INF_ERR_IN_OVERRUN;  // bounds how far a corrupt stream can read ahead
+            refill();  // >= 32 bits: enough for litlen code (15) + length extra (5) ...
             uint32_t e = lit[peek(LIT_ROOT)];
             if (e_kind(e) == KIND_SUB) e = lit[e_payload(e) + (((uint32_t)(bitbuf >> LIT_ROOT)) & ((1u << e_extra(e)) - 1u))];
             drop(e_len(e));
@@ -387,7 +392,6 @@ struct Inflater {
                 drop(e_len(d));
                 uint32_t dd = e_payload(d) + take(e_extra(d));
                 if (!io.match(len, dd)) return (dd > io.produced()) ? INF_ERR_DIST_TOO_FAR : INF_ERR_OUT_OVERFLOW;
-                if (inpos > in_len + 8) return INF_ERR_IN_OVERRUN;
                 continue;
             }
             if (kind == KIND_EOB) return INF_OK;
