@@ -21,6 +21,26 @@ class InflateStats(C.Structure):
                 ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
 
 
+DH_BAM_CORE_COLS = 13
+DH_BAM_MAX_COLS = 13 + 63
+
+
+class TagReq(C.Structure):
+    _fields_ = [("tag", C.c_char * 2), ("type", C.c_char), ("pad", C.c_char)]
+
+
+class BamBatch(C.Structure):
+    _fields_ = [("n_rows", C.c_uint64), ("row0", C.c_uint64), ("status", C.c_int32), ("n_cols", C.c_int32),
+                ("data", C.c_void_p * DH_BAM_MAX_COLS), ("validity", C.c_void_p * DH_BAM_MAX_COLS),
+                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64)]
+
+
+class BamScanStats(C.Structure):
+    _fields_ = [("rows", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("inflated_bytes", C.c_uint64),
+                ("n_blocks", C.c_uint64), ("rewalk_rounds", C.c_uint64), ("status", C.c_int32), ("pad", C.c_int32),
+                ("end_voffset", C.c_uint64), ("inflate_ms", C.c_float), ("walk_ms", C.c_float), ("decode_ms", C.c_float)]
+
+
 _lib = None
 
 # name -> (restype, argtypes); tests/test_abi.py checks every symbol declared in include/*.h is here and exported
@@ -45,6 +65,20 @@ SIGNATURES = {
     "dh_bgzf_dev_inflate": (C.c_int, [C.c_void_p]),
     "dh_bgzf_dev_check": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "dh_bgzf_dev_read": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
+    "dh_bam_open": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "dh_bam_close": (None, [C.c_void_p]),
+    "dh_bam_n_ref": (C.c_int32, [C.c_void_p]),
+    "dh_bam_ref_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "dh_bam_ref_len": (C.c_uint32, [C.c_void_p, C.c_int32]),
+    "dh_bam_header_text": (C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint32)]),
+    "dh_bam_first_voffset": (C.c_uint64, [C.c_void_p]),
+    "dh_bam_n_blocks": (C.c_uint64, [C.c_void_p]),
+    "dh_bam_set_projection": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(TagReq), C.c_int]),
+    "dh_bam_configure": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64]),
+    "dh_bam_scan_begin": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64]),
+    "dh_bam_next_batch": (C.c_int, [C.c_void_p, C.POINTER(BamBatch)]),
+    "dh_bam_scan_stats_get": (C.c_int, [C.c_void_p, C.POINTER(BamScanStats)]),
+    "dh_bam_split": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]),
     "dh_ctx_sync": (C.c_int, [C.c_void_p]),
     "dh_timer_start": (C.c_int, [C.c_void_p]),
     "dh_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),

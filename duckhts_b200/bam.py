@@ -1,0 +1,197 @@
+"""Host-side mirror of the read_bam part of the C-ABI (rows A4-A15 of SURVEY.md §8; reference src/bam_reader.c).
+
+Column names, order and NULL rules are the reference's (bam_reader.c:189-204, 509-549)."""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import DH_BAM_CORE_COLS, BamBatch, BamScanStats, DuckhtsError, TagReq, check, lib
+from .bgzf import _as_u8
+
+VOFF_MAX = 0xFFFFFFFFFFFFFFFF
+CORE_NAMES = ("qname", "flag", "rname", "pos", "mapq", "cigar", "rnext", "pnext", "tlen", "seq", "qual", "rg", "sample")
+CORE_DTYPES = {"flag": np.uint16, "pos": np.int64, "mapq": np.int32, "pnext": np.int64, "tlen": np.int64}
+# the reference's standard_tags table (bam_reader.c:54-70): tag -> column type
+STD_TAGS = {"AM": "i", "AS": "i", "BC": "Z", "BQ": "Z", "BZ": "Z", "CB": "Z", "CC": "Z", "CM": "i", "CO": "Z", "CP": "i",
+            "CQ": "Z", "CR": "Z", "CS": "Z", "CT": "Z", "CY": "Z", "E2": "Z", "FI": "i", "FS": "Z", "H0": "i", "H1": "i",
+            "H2": "i", "HI": "i", "IH": "i", "LB": "Z", "MC": "Z", "MD": "Z", "MI": "Z", "MM": "Z", "MN": "i", "MQ": "i",
+            "NH": "i", "NM": "i", "OA": "Z", "OC": "Z", "OP": "i", "OQ": "Z", "OX": "Z", "PG": "Z", "PQ": "i", "PT": "Z",
+            "PU": "Z", "Q2": "Z", "QT": "Z", "QX": "Z", "R2": "Z", "RG": "Z", "RX": "Z", "SA": "Z", "SM": "i", "TC": "i",
+            "TS": "A", "U2": "Z", "UQ": "i"}
+
+
+def cells_to_list(ptr, n, validity=None):
+    """duckdb_string_t[n] at host address ptr -> [bytes | None]; follows the pointers exactly as DuckDB would."""
+    if n == 0:
+        return []
+    raw = C.string_at(ptr, 16 * n)
+    a = np.frombuffer(raw, dtype=np.uint8).reshape(n, 16)
+    lens = a[:, :4].copy().view(np.uint32).ravel()
+    ptrs = a[:, 8:].copy().view(np.uint64).ravel()
+    out = [None] * n
+    for i in range(n):
+        if validity is not None and not validity[i]:
+            continue
+        ln = int(lens[i])
+        out[i] = raw[16 * i + 4:16 * i + 4 + ln] if ln <= 12 else C.string_at(int(ptrs[i]), ln)
+    return out
+
+
+def validity_to_bool(ptr, n):
+    if not ptr:
+        return None
+    words = np.frombuffer(C.string_at(ptr, ((n + 63) // 64) * 8), dtype=np.uint64)
+    return np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
+
+
+class BamFile:
+    """One BAM image bound to a Context (dh_bam)."""
+
+    def __init__(self, ctx, data):
+        self.a = _as_u8(data)  # keep alive
+        self.ctx = ctx
+        self.h = lib().dh_bam_open(ctx.h, self.a.ctypes.data, self.a.size)
+        if not self.h:
+            raise DuckhtsError("dh_bam_open failed: " + lib().dh_last_error().decode())
+        self.tags = []
+
+    def close(self):
+        if self.h:
+            lib().dh_bam_close(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def ref_names(self):
+        return [lib().dh_bam_ref_name(self.h, i) for i in range(lib().dh_bam_n_ref(self.h))]
+
+    @property
+    def ref_lens(self):
+        return [lib().dh_bam_ref_len(self.h, i) for i in range(lib().dh_bam_n_ref(self.h))]
+
+    @property
+    def header_text(self):
+        n = C.c_uint32(0)
+        p = lib().dh_bam_header_text(self.h, C.byref(n))
+        return C.string_at(p, n.value)
+
+    @property
+    def first_voffset(self):
+        return lib().dh_bam_first_voffset(self.h)
+
+    def set_projection(self, col_mask=None, tags=()):
+        self.tags = [(t if isinstance(t, bytes) else t.encode(), ty) for t, ty in tags]
+        reqs = (TagReq * max(len(self.tags), 1))()
+        for k, (tg, ty) in enumerate(self.tags):
+            reqs[k].tag = tg
+            reqs[k].type = ty.encode()
+        if col_mask is None:
+            col_mask = (1 << (DH_BAM_CORE_COLS + len(self.tags))) - 1
+        self.col_mask = col_mask
+        check(lib().dh_bam_set_projection(self.h, col_mask, reqs, len(self.tags)), "dh_bam_set_projection")
+
+    def configure(self, seg_comp=0, batch_rows=0, carry=0):
+        check(lib().dh_bam_configure(self.h, seg_comp, batch_rows, carry), "dh_bam_configure")
+
+    def split(self, n_parts):
+        v = (C.c_uint64 * (n_parts + 1))()
+        check(lib().dh_bam_split(self.h, n_parts, v), "dh_bam_split")
+        return list(v)
+
+    def scan_begin(self, voff_beg=0, voff_end=VOFF_MAX):
+        check(lib().dh_bam_scan_begin(self.h, voff_beg, voff_end), "dh_bam_scan_begin")
+
+    def next_batch(self):
+        b = BamBatch()
+        rc = check(lib().dh_bam_next_batch(self.h, C.byref(b)), "dh_bam_next_batch")
+        return b if rc == 1 else None
+
+    def stats(self):
+        st = BamScanStats()
+        check(lib().dh_bam_scan_stats_get(self.h, C.byref(st)), "dh_bam_scan_stats_get")
+        return st
+
+    def drain(self):
+        """Run the scan to the end without looking at the rows (timing)."""
+        rows = 0
+        while True:
+            b = self.next_batch()
+            if b is None:
+                return rows
+            rows += b.n_rows
+
+
+def batch_to_columns(bf, b):
+    """One dh_bam_batch -> dict of numpy arrays / lists of bytes (None = NULL)."""
+    n = int(b.n_rows)
+    out = {"n": n}
+    for c, name in enumerate(CORE_NAMES):
+        if not (bf.col_mask >> c) & 1:
+            continue
+        if name in CORE_DTYPES:
+            dt = np.dtype(CORE_DTYPES[name])
+            out[name] = np.frombuffer(C.string_at(b.data[c], n * dt.itemsize), dtype=dt).copy() if n else np.zeros(0, dt)
+        else:
+            out[name] = cells_to_list(b.data[c], n, validity_to_bool(b.validity[c], n))
+    tags = []
+    for k, (tg, ty) in enumerate(bf.tags):
+        c = DH_BAM_CORE_COLS + k
+        if not (bf.col_mask >> c) & 1:
+            tags.append(None)
+            continue
+        valid = validity_to_bool(b.validity[c], n)
+        d = {"valid": valid if valid is not None else np.zeros(0, bool)}
+        if ty == "i":
+            d["i"] = np.frombuffer(C.string_at(b.data[c], n * 8), dtype=np.int64).copy() if n else np.zeros(0, np.int64)
+        elif ty == "f":
+            d["f"] = np.frombuffer(C.string_at(b.data[c], n * 8), dtype=np.float64).copy() if n else np.zeros(0, np.float64)
+        else:
+            d["s"] = cells_to_list(b.data[c], n, valid)
+        tags.append(d)
+    out["tags"] = tags
+    return out
+
+
+def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, batch_rows=0, carry=0):
+    """Whole scan -> one dict of columns in row order (test/inspection helper; the product API is batch-wise)."""
+    with BamFile(ctx, data) as bf:
+        bf.set_projection(col_mask, tags)
+        bf.configure(seg_comp, batch_rows, carry)
+        bf.scan_begin(*voff)
+        parts = []
+        status = 0
+        while True:
+            b = bf.next_batch()
+            if b is None:
+                break
+            parts.append(batch_to_columns(bf, b))
+            status = b.status
+        st = bf.stats()
+        res = {"n": sum(p["n"] for p in parts), "status": st.status, "ref_names": bf.ref_names, "ref_lens": bf.ref_lens,
+               "text": bf.header_text, "n_batches": len(parts), "stats": st, "last_batch_status": status}
+        names = [nm for c, nm in enumerate(CORE_NAMES) if (bf.col_mask >> c) & 1]
+        for nm in names:
+            if nm in CORE_DTYPES:
+                res[nm] = np.concatenate([p[nm] for p in parts]) if parts else np.zeros(0, CORE_DTYPES[nm])
+            else:
+                res[nm] = [x for p in parts for x in p[nm]]
+        res["tags"] = []
+        for k, (tg, ty) in enumerate(bf.tags):
+            if not (bf.col_mask >> (DH_BAM_CORE_COLS + k)) & 1:
+                res["tags"].append(None)
+                continue
+            d = {"valid": np.concatenate([p["tags"][k]["valid"] for p in parts]) if parts else np.zeros(0, bool)}
+            for key in ("i", "f"):
+                if parts and key in parts[0]["tags"][k]:
+                    d[key] = np.concatenate([p["tags"][k][key] for p in parts])
+                elif not parts and ty == key:
+                    d[key] = np.zeros(0, np.int64 if key == "i" else np.float64)
+            if ty not in ("i", "f"):
+                d["s"] = [x for p in parts for x in p["tags"][k]["s"]]
+            res["tags"].append(d)
+        return res

@@ -1,0 +1,84 @@
+// bam_decode.cuh — device-side types + launchers of the BAM record-boundary (A5-A7) and columnar decode
+// (A9-A15) kernels.  See bam_decode.cu for the reference functions each kernel replaces.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dh {
+
+// DuckDB VARCHAR cell (duckdb_string_t, reference duckdb_capi/duckdb.h:376-391): <= 12 bytes inlined
+// (zero padded), else 4-byte prefix + pointer.  The pointer the kernel stores is a HOST address inside
+// the pinned heap the batch is copied into, so the cells are valid DuckDB cells after the D2H copy.
+struct alignas(16) StrCell {
+    uint32_t len;
+    uint32_t w[3];  // inlined bytes 0..11 | prefix, ptr_lo, ptr_hi
+};
+
+struct TagReq {
+    uint8_t t0, t1;
+    uint8_t type;  // 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (Z or H), 'A' VARCHAR(1)
+    uint8_t pad;
+};
+
+// @RG dictionary entry: ID bytes live in a side heap; sample = prebuilt cell (SM value) or absent
+struct alignas(16) RgEntry {
+    StrCell sample;
+    uint32_t id_off, id_len, has_sample, pad;
+};
+
+constexpr int BAM_CORE_COLS = 13;  // QNAME FLAG RNAME POS MAPQ CIGAR RNEXT PNEXT TLEN SEQ QUAL READ_GROUP_ID SAMPLE_ID
+constexpr int BAM_MAX_TAGS = 63;   // + 1 internal RG request = 64 = two per lane
+constexpr int BAM_MAX_COLS = BAM_CORE_COLS + BAM_MAX_TAGS;
+enum { COL_QNAME = 0, COL_FLAG, COL_RNAME, COL_POS, COL_MAPQ, COL_CIGAR, COL_RNEXT, COL_PNEXT, COL_TLEN, COL_SEQ,
+       COL_QUAL, COL_RG, COL_SAMPLE };
+
+// what both kernels need to know about the file and the projection
+struct ScanTables {
+    const StrCell *ref_cells;  // n_ref + 1 cells; [n_ref] = "*"
+    const RgEntry *rg;
+    const uint8_t *rg_ids;
+    const TagReq *tags;        // n_tags user requests
+    int32_t n_ref;
+    uint32_t n_rg;
+    uint32_t n_tags;
+    uint32_t pad;
+    uint64_t col_mask;         // bit c set = column c projected (core columns 0..12, tag k at 13+k)
+};
+
+// per BGZF block result of the boundary walk (device -> host)
+struct BlockWalk {
+    int64_t entry;        // offset (relative to the segment's inflated base) of the first record starting in the block
+    int64_t exit_off;     // offset of the first record NOT consumed by this block's walk
+    uint64_t heap_bytes;  // heap bytes the block's records need (4-byte aligned slots)
+    uint32_t count;       // records that start in this block and were accepted
+    int32_t stop;         // 0; 1 = record at exit_off needs bytes beyond the segment; <0 = bam_read1 error code there
+};
+
+struct WalkParams {
+    const uint8_t *u;          // segment inflated base (offset 0); bytes [-carry, seg_end) are valid
+    const int64_t *blk_start;  // n+1 block start offsets (blk_start[0] may be negative: carry pseudo-block)
+    const int64_t *entry_in;   // per block: fixed entry, or INT64_MIN = speculate
+    const uint8_t *todo;       // per block: 1 = walk it in this round (nullptr = all)
+    BlockWalk *out;
+    uint32_t n;
+    int32_t is_final;          // 1: the data ends at seg_end (EOF): an incomplete record is an error, not a carry
+    int64_t seg_end;
+    int64_t limit_end;         // records starting at or after this offset are outside the scan range
+};
+
+struct DecodeParams {
+    const uint8_t *u;
+    const BlockWalk *walk;        // entry + count per block
+    const uint32_t *row_base;     // per block, relative to the batch
+    const uint64_t *heap_base;    // per block, relative to the batch heap
+    uint32_t b_lo, b_hi;          // blocks of this batch
+    uint8_t *col[BAM_MAX_COLS];   // device column data (nullptr = not projected)
+    unsigned long long *valid[BAM_MAX_COLS];  // validity words (bit = 1 valid); nullptr = column has no NULLs
+    uint8_t *heap;                // device heap
+    uint64_t heap_host;           // host address the heap will be copied to
+};
+
+cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream);
+cudaError_t launch_bam_decode(const DecodeParams &p, const ScanTables &t, cudaStream_t stream);
+
+}  // namespace dh

@@ -1,0 +1,800 @@
+// dh_bam.cu — host pipeline of the read_bam scan behind the C-ABI (include/duckhts_cuda.h, dh_bam_*).
+//
+// Per segment of BGZF blocks:   H2D (pinned, copy stream)  ->  bgzf_inflate_kernel  ->  bam_walk_kernel
+//   -> host validates the boundary chain (entry[i] == exit[i-1]) and cuts the segment into row batches
+// per batch:                    bam_decode_kernel -> one D2H copy of the batch arena (columns + validity + heap)
+// Two segments and three batches are in flight so that H2D, the kernels and D2H overlap.  Everything the host
+// does per segment is O(#BGZF blocks) bookkeeping; no record or byte of payload is touched on the CPU.
+#include <string.h>
+
+#include <algorithm>
+#include <deque>
+#include <string>
+#include <vector>
+
+#include "bam_decode.cuh"
+#include "dh_internal.h"
+#include "inflate_core.cuh"
+
+using namespace dh;
+
+namespace {
+
+constexpr int NSEG = 2, NBATCH = 3;
+constexpr uint64_t A256 = 255;
+
+struct Batch {           // one output batch of the current segment
+    uint32_t b_lo, b_hi; // walk-block index range
+    uint64_t rows, heap, row0;
+};
+
+struct SegSlot {
+    DevBuf comp, out, desc, status, blk_start, entry, todo, walk, row_base, heap_base;
+    PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base;
+    cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_walk0 = nullptr, ev_walk1 = nullptr;
+    size_t b0 = 0, b1 = 0;  // file block range
+    uint64_t cbase = 0, obytes = 0;
+    int issued_for = -1;    // segment index whose inflate was issued into this slot
+};
+
+struct BatchSlot {
+    DevBuf arena;
+    PinBuf h_arena;
+    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
+    dh_bam_batch desc;
+    bool timed = false;
+};
+
+struct Seg { size_t b0, b1; };
+
+}  // namespace
+
+struct dh_bam {
+    dh_ctx *ctx = nullptr;
+    const uint8_t *data = nullptr;
+    uint64_t size = 0;
+    BlockTable bt;
+    // header
+    std::string text;
+    std::vector<std::string> ref_names;
+    std::vector<uint32_t> ref_lens;
+    size_t first_blk = 0;
+    uint32_t first_off = 0;
+    // dictionaries (host strings must keep stable addresses: cells point at them)
+    std::deque<std::string> dict;
+    std::vector<StrCell> ref_cells;
+    std::vector<RgEntry> rg;
+    std::string rg_ids;
+    DevBuf d_ref_cells, d_rg, d_rg_ids, d_tags;
+    // projection
+    uint64_t col_mask = (1ull << BAM_CORE_COLS) - 1;
+    std::vector<TagReq> tags;
+    ScanTables tabs;
+    // knobs
+    uint64_t seg_comp = 256ull << 20;
+    uint32_t batch_rows = 1u << 20;
+    uint64_t carry_cap = 8ull << 20;
+    // scan state
+    std::vector<Seg> segs;
+    SegSlot ss[NSEG];
+    BatchSlot bs[NBATCH];
+    bool scanning = false;
+    int cur_seg = -1;              // segment whose batches are being issued
+    std::vector<Batch> batches;    // of cur_seg
+    size_t next_batch_i = 0;
+    uint64_t issued = 0, returned = 0;  // batch counters (slot = counter % NBATCH)
+    std::deque<uint64_t> inflight;
+    uint64_t rows_total = 0;
+    int64_t carry = 0;             // bytes of the incomplete record at the end of the previous segment
+    int final_status = 0;
+    bool chain_done = false;       // range end / error / EOF reached: no further segments
+    size_t end_blk = 0;            // first block NOT inflated for this scan
+    size_t limit_blk = 0;          // block index of voff_end (records starting at/after (limit_blk, limit_off) are excluded)
+    uint32_t limit_off = 0;
+    bool to_eof = true;
+    int64_t first_entry = 0;       // in-block offset of the first record of the scan
+    dh_bam_scan_stats st;
+    std::vector<cudaEvent_t> inf_events;
+};
+
+namespace {
+
+uint32_t col_width(const dh_bam *b, int c) {
+    switch (c) {
+    case COL_FLAG: return 2;
+    case COL_MAPQ: return 4;
+    case COL_POS: case COL_PNEXT: case COL_TLEN: return 8;
+    default: break;
+    }
+    if (c < BAM_CORE_COLS) return 16;
+    char t = (char)b->tags[c - BAM_CORE_COLS].type;
+    return (t == 'i' || t == 'f') ? 8 : 16;
+}
+bool col_nullable(int c) { return c == COL_RG || c == COL_SAMPLE || c >= BAM_CORE_COLS; }
+
+StrCell make_cell(dh_bam *b, const std::string &s) {
+    StrCell c;
+    memset(&c, 0, sizeof c);
+    c.len = (uint32_t)s.size();
+    if (s.size() <= 12) memcpy(c.w, s.data(), s.size());
+    else {
+        b->dict.push_back(s);
+        const char *p = b->dict.back().data();
+        memcpy(&c.w[0], p, 4);
+        uint64_t a = (uint64_t)(uintptr_t)p;
+        c.w[1] = (uint32_t)a;
+        c.w[2] = (uint32_t)(a >> 32);
+    }
+    return c;
+}
+
+size_t block_of(const dh_bam *b, uint64_t coffset) {
+    size_t lo = 0, hi = b->bt.blocks.size();
+    while (lo < hi) {
+        size_t mid = (lo + hi) / 2;
+        if (b->bt.blocks[mid].coffset < coffset) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// ---- header (bam_hdr_read, htslib/sam.c:229-342) on the host, from GPU-inflated bytes ----
+int parse_header(dh_bam *b) {
+    const size_t nb = b->bt.blocks.size();
+    size_t take = std::min<size_t>(nb, 4);
+    std::vector<uint8_t> u;
+    for (;;) {
+        uint64_t cend = take ? b->bt.blocks[take - 1].coffset + b->bt.blocks[take - 1].csize : 0;
+        u.resize((size_t)b->bt.uoff[take] + 8);
+        uint64_t n = 0;
+        int rc = dh_bgzf_inflate_host(b->ctx, b->data, cend, u.data(), u.size(), &n, nullptr);
+        if (rc != DH_OK) return rc;
+        const uint64_t have = n;
+        auto need_more = [&](uint64_t want) { return want > have && take < nb; };
+        auto le32 = [&](uint64_t p) { return (uint32_t)u[p] | ((uint32_t)u[p + 1] << 8) | ((uint32_t)u[p + 2] << 16) | ((uint32_t)u[p + 3] << 24); };
+        bool again = false, bad = false;
+        uint64_t p = 0;
+        do {
+            if (need_more(12)) { again = true; break; }
+            if (have < 12 || memcmp(u.data(), "BAM\1", 4)) { bad = true; break; }
+            uint32_t l_text = le32(4);
+            p = 8;
+            if (need_more(p + l_text + 4)) { again = true; break; }
+            if (p + l_text + 4 > have) { bad = true; break; }
+            b->text.assign((const char *)u.data() + p, l_text);
+            p += l_text;
+            int32_t n_ref = (int32_t)le32(p);
+            p += 4;
+            if (n_ref < 0) { bad = true; break; }
+            b->ref_names.clear();
+            b->ref_lens.clear();
+            for (int32_t i = 0; i < n_ref && !again && !bad; ++i) {
+                if (need_more(p + 4)) { again = true; break; }
+                if (p + 4 > have) { bad = true; break; }
+                int32_t l = (int32_t)le32(p);
+                p += 4;
+                if (l <= 0) { bad = true; break; }
+                if (need_more(p + (uint64_t)l + 4)) { again = true; break; }
+                if (p + (uint64_t)l + 4 > have) { bad = true; break; }
+                std::string name((const char *)u.data() + p, (size_t)l);
+                name = std::string(name.c_str());  // C-string semantics (tid2name), incl. the missing-NUL fix-up
+                b->ref_names.push_back(name);
+                p += (uint64_t)l;
+                b->ref_lens.push_back(le32(p));
+                p += 4;
+            }
+        } while (0);
+        if (bad) { set_error("invalid BAM binary header"); return DH_EFORMAT; }
+        if (again) { take = std::min(nb, take * 4); continue; }
+        // first alignment record: inflated offset p -> (block, in-block offset); skip to the next non-empty block
+        size_t blk = std::upper_bound(b->bt.uoff.begin(), b->bt.uoff.end(), p) - b->bt.uoff.begin() - 1;
+        if (blk >= nb) { blk = nb; b->first_off = 0; }
+        else b->first_off = (uint32_t)(p - b->bt.uoff[blk]);
+        b->first_blk = blk;
+        return DH_OK;
+    }
+}
+
+// @RG ID -> SM dictionary in header order (first line with an ID wins in the kernel's lookup)
+void build_dictionaries(dh_bam *b) {
+    b->ref_cells.clear();
+    for (auto &n : b->ref_names) b->ref_cells.push_back(make_cell(b, n));
+    b->ref_cells.push_back(make_cell(b, "*"));
+    b->rg.clear();
+    b->rg_ids.clear();
+    const std::string &t = b->text;
+    size_t p = 0;
+    while (p < t.size()) {
+        size_t eol = t.find('\n', p);
+        if (eol == std::string::npos) eol = t.size();
+        if (eol - p >= 4 && !t.compare(p, 4, "@RG\t")) {
+            std::string id, sm;
+            bool has_id = false, has_sm = false;
+            size_t f = p + 4;
+            while (f < eol) {
+                size_t fe = t.find('\t', f);
+                if (fe == std::string::npos || fe > eol) fe = eol;
+                if (fe - f >= 3 && t[f + 2] == ':') {
+                    if (t[f] == 'I' && t[f + 1] == 'D' && !has_id) { id = t.substr(f + 3, fe - f - 3); has_id = true; }
+                    if (t[f] == 'S' && t[f + 1] == 'M' && !has_sm) { sm = t.substr(f + 3, fe - f - 3); has_sm = true; }
+                }
+                f = fe + 1;
+            }
+            if (has_id) {
+                RgEntry e;
+                memset(&e, 0, sizeof e);
+                e.id_off = (uint32_t)b->rg_ids.size();
+                e.id_len = (uint32_t)id.size();
+                b->rg_ids += id;
+                sm = std::string(sm.c_str());
+                e.has_sample = has_sm && !sm.empty();
+                if (e.has_sample) e.sample = make_cell(b, sm);
+                b->rg.push_back(e);
+            }
+        }
+        p = eol + 1;
+    }
+}
+
+int upload_tables(dh_bam *b) {
+    int rc;
+    if ((rc = b->d_ref_cells.reserve(b->ref_cells.size() * sizeof(StrCell))) != DH_OK) return rc;
+    DH_CUDA(cudaMemcpy(b->d_ref_cells.p, b->ref_cells.data(), b->ref_cells.size() * sizeof(StrCell), cudaMemcpyHostToDevice));
+    if ((rc = b->d_rg.reserve(std::max<size_t>(1, b->rg.size()) * sizeof(RgEntry))) != DH_OK) return rc;
+    if (!b->rg.empty()) DH_CUDA(cudaMemcpy(b->d_rg.p, b->rg.data(), b->rg.size() * sizeof(RgEntry), cudaMemcpyHostToDevice));
+    if ((rc = b->d_rg_ids.reserve(std::max<size_t>(1, b->rg_ids.size()))) != DH_OK) return rc;
+    if (!b->rg_ids.empty()) DH_CUDA(cudaMemcpy(b->d_rg_ids.p, b->rg_ids.data(), b->rg_ids.size(), cudaMemcpyHostToDevice));
+    if ((rc = b->d_tags.reserve(std::max<size_t>(1, b->tags.size()) * sizeof(TagReq))) != DH_OK) return rc;
+    if (!b->tags.empty()) DH_CUDA(cudaMemcpy(b->d_tags.p, b->tags.data(), b->tags.size() * sizeof(TagReq), cudaMemcpyHostToDevice));
+    ScanTables &t = b->tabs;
+    t.ref_cells = (const StrCell *)b->d_ref_cells.p;
+    t.rg = (const RgEntry *)b->d_rg.p;
+    t.rg_ids = (const uint8_t *)b->d_rg_ids.p;
+    t.tags = (const TagReq *)b->d_tags.p;
+    t.n_ref = (int32_t)b->ref_names.size();
+    t.n_rg = (uint32_t)b->rg.size();
+    t.n_tags = (uint32_t)b->tags.size();
+    t.pad = 0;
+    t.col_mask = b->col_mask;
+    return DH_OK;
+}
+
+cudaStream_t s_comp(dh_bam *b) { return b->ctx->stream; }
+cudaStream_t s_copy(dh_bam *b) { return b->ctx->copy_streams[0]; }
+cudaStream_t s_d2h(dh_bam *b) { return b->ctx->copy_streams[1]; }
+
+int ensure_events(dh_bam *b) {
+    for (auto &s : b->ss)
+        if (!s.ev_h2d) {
+            DH_CUDA(cudaEventCreate(&s.ev_h2d));
+            DH_CUDA(cudaEventCreate(&s.ev_inf0));
+            DH_CUDA(cudaEventCreate(&s.ev_inf1));
+            DH_CUDA(cudaEventCreate(&s.ev_walk0));
+            DH_CUDA(cudaEventCreate(&s.ev_walk1));
+        }
+    for (auto &s : b->bs)
+        if (!s.ev_done) {
+            DH_CUDA(cudaEventCreate(&s.ev_k0));
+            DH_CUDA(cudaEventCreate(&s.ev_k1));
+            DH_CUDA(cudaEventCreate(&s.ev_done));
+        }
+    return DH_OK;
+}
+
+// H2D + inflate of segment k into slot k % NSEG (asynchronous)
+int issue_inflate(dh_bam *b, int k) {
+    SegSlot &s = b->ss[k % NSEG];
+    if (s.issued_for == k) return DH_OK;
+    const Seg &sg = b->segs[k];
+    const BlockTable &bt = b->bt;
+    s.b0 = sg.b0;
+    s.b1 = sg.b1;
+    const size_t nblk = sg.b1 - sg.b0;
+    s.cbase = bt.blocks[sg.b0].coffset & ~15ull;
+    const uint64_t cend = bt.blocks[sg.b1 - 1].coffset + bt.blocks[sg.b1 - 1].csize;
+    const uint64_t cbytes = cend - s.cbase;
+    s.obytes = bt.uoff[sg.b1] - bt.uoff[sg.b0];
+    int rc;
+    // the slot's previous tenant (segment k - NSEG) has finished on the compute stream before anything here runs:
+    // its kernels were all enqueued on s_comp earlier, and the copy stream waits for its last inflate below.
+    if ((rc = s.comp.reserve(cbytes + DH_COMP_PAD)) != DH_OK) return rc;
+    if ((rc = s.out.reserve(b->carry_cap + s.obytes + 2 * BGZF_MAX_OUT)) != DH_OK) return rc;
+    if ((rc = s.desc.reserve(nblk * sizeof(BlockDesc))) != DH_OK) return rc;
+    if ((rc = s.status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
+    if ((rc = s.h_desc.reserve(nblk * sizeof(BlockDesc))) != DH_OK) return rc;
+    if ((rc = s.h_status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
+    BlockDesc *d = (BlockDesc *)s.h_desc.p;
+    for (size_t i = sg.b0; i < sg.b1; ++i) {
+        const dh_bgzf_block &bl = bt.blocks[i];
+        BlockDesc &o = d[i - sg.b0];
+        o.in_off = (uint32_t)(bl.coffset + 18 - s.cbase);
+        o.in_len = bl.csize - 26;
+        o.isize = bl.isize;
+        o.crc = bl.crc;
+        o.out_off = b->carry_cap + (bt.uoff[i] - bt.uoff[sg.b0]);
+    }
+    cudaStream_t sc = s_copy(b), sk = s_comp(b);
+    DH_CUDA(cudaStreamWaitEvent(sc, s.ev_inf1, 0));  // previous inflate from this comp buffer is done (no-op if never recorded)
+    DH_CUDA(cudaMemcpyAsync(s.comp.p, b->data + s.cbase, cbytes, cudaMemcpyHostToDevice, sc));
+    DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + cbytes, 0, DH_COMP_PAD, sc));
+    DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, nblk * sizeof(BlockDesc), cudaMemcpyHostToDevice, sc));
+    DH_CUDA(cudaEventRecord(s.ev_h2d, sc));
+    DH_CUDA(cudaStreamWaitEvent(sk, s.ev_h2d, 0));
+    DH_CUDA(cudaEventRecord(s.ev_inf0, sk));
+    DH_CUDA(launch_bgzf_inflate((const uint8_t *)s.comp.p, (const BlockDesc *)s.desc.p, (uint32_t)nblk, (uint8_t *)s.out.p,
+                                (int *)s.status.p, (unsigned int *)b->ctx->counter.p + 8 + (k % NSEG), b->ctx->sm_count, sk));
+    b->ctx->launches++;
+    DH_CUDA(cudaEventRecord(s.ev_inf1, sk));
+    DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, nblk * sizeof(int), cudaMemcpyDeviceToHost, sk));
+    s.issued_for = k;
+    b->st.h2d_bytes += cbytes + nblk * sizeof(BlockDesc);
+    b->st.inflated_bytes += s.obytes;
+    b->st.n_blocks += nblk;
+    return DH_OK;
+}
+
+// Boundary walk of segment k + host validation; fills b->batches.  Synchronises with the walk results only.
+int walk_segment(dh_bam *b, int k) {
+    SegSlot &s = b->ss[k % NSEG];
+    const BlockTable &bt = b->bt;
+    const size_t nblk = s.b1 - s.b0;
+    const uint32_t n = (uint32_t)nblk + 1;  // + pseudo-block 0 = the carried-over partial record
+    cudaStream_t sk = s_comp(b);
+    int rc;
+    if ((rc = s.blk_start.reserve((n + 1) * 8)) != DH_OK || (rc = s.entry.reserve(n * 8)) != DH_OK ||
+        (rc = s.todo.reserve(n)) != DH_OK || (rc = s.walk.reserve(n * sizeof(BlockWalk))) != DH_OK ||
+        (rc = s.row_base.reserve(n * 4)) != DH_OK || (rc = s.heap_base.reserve(n * 8)) != DH_OK ||
+        (rc = s.h_blk_start.reserve((n + 1) * 8)) != DH_OK || (rc = s.h_entry.reserve(n * 8)) != DH_OK ||
+        (rc = s.h_todo.reserve(n)) != DH_OK || (rc = s.h_walk.reserve(n * sizeof(BlockWalk))) != DH_OK ||
+        (rc = s.h_row_base.reserve(n * 4)) != DH_OK || (rc = s.h_heap_base.reserve(n * 8)) != DH_OK)
+        return rc;
+    uint8_t *ubase = (uint8_t *)s.out.p + b->carry_cap;
+    // carry: the incomplete record at the end of the previous segment goes in front of this segment's bytes
+    if (b->carry > 0) {
+        SegSlot &ps = b->ss[(k - 1) % NSEG];
+        const uint8_t *src = (const uint8_t *)ps.out.p + b->carry_cap + ps.obytes - b->carry;
+        DH_CUDA(cudaMemcpyAsync(ubase - b->carry, src, (size_t)b->carry, cudaMemcpyDeviceToDevice, sk));
+    }
+    int64_t *hs = (int64_t *)s.h_blk_start.p, *he = (int64_t *)s.h_entry.p;
+    uint8_t *ht = (uint8_t *)s.h_todo.p;
+    hs[0] = -b->carry;
+    for (size_t i = 0; i < nblk; ++i) hs[i + 1] = (int64_t)(bt.uoff[s.b0 + i] - bt.uoff[s.b0]);
+    hs[n] = (int64_t)s.obytes;
+    const bool first_seg = k == 0;
+    for (uint32_t i = 0; i < n; ++i) { he[i] = INT64_MIN; ht[i] = 1; }
+    he[0] = -b->carry;                       // the carried record starts exactly there
+    if (first_seg) { he[0] = b->first_entry; he[1] = b->first_entry; }   // scan start is a known record boundary
+    else if (b->carry == 0) he[1] = 0;       // previous segment ended exactly on a record boundary
+    const bool is_final = b->to_eof && s.b1 == bt.blocks.size();
+    int64_t limit_end = INT64_MAX;
+    if (!b->to_eof && b->limit_blk < s.b1) {
+        limit_end = b->limit_blk >= s.b0 ? (int64_t)(bt.uoff[b->limit_blk] - bt.uoff[s.b0]) + b->limit_off : 0;
+    }
+    WalkParams wp;
+    wp.u = ubase;
+    wp.blk_start = (const int64_t *)s.blk_start.p;
+    wp.entry_in = (const int64_t *)s.entry.p;
+    wp.todo = (const uint8_t *)s.todo.p;
+    wp.out = (BlockWalk *)s.walk.p;
+    wp.n = n;
+    wp.is_final = is_final ? 1 : 0;
+    wp.seg_end = (int64_t)s.obytes;
+    wp.limit_end = limit_end;
+    DH_CUDA(cudaMemcpyAsync(s.blk_start.p, hs, (n + 1) * 8, cudaMemcpyHostToDevice, sk));
+    BlockWalk *hw = (BlockWalk *)s.h_walk.p;
+    uint32_t validated = 0;  // blocks [0, validated) have entry == predecessor's exit
+    bool stopped = false;
+    uint32_t stop_blk = 0;
+    bool first_round = true;
+    for (;;) {
+        DH_CUDA(cudaMemcpyAsync(s.entry.p, he, n * 8, cudaMemcpyHostToDevice, sk));
+        DH_CUDA(cudaMemcpyAsync(s.todo.p, ht, n, cudaMemcpyHostToDevice, sk));
+        if (first_round) DH_CUDA(cudaEventRecord(s.ev_walk0, sk));
+        DH_CUDA(launch_bam_walk(wp, b->tabs, sk));
+        b->ctx->launches++;
+        if (first_round) DH_CUDA(cudaEventRecord(s.ev_walk1, sk));
+        if (first_round) DH_CUDA(cudaMemcpyAsync(hw, s.walk.p, n * sizeof(BlockWalk), cudaMemcpyDeviceToHost, sk));
+        else {
+            // only the re-walked block changed
+            uint32_t j = validated;
+            DH_CUDA(cudaMemcpyAsync(hw + j, (BlockWalk *)s.walk.p + j, sizeof(BlockWalk), cudaMemcpyDeviceToHost, sk));
+        }
+        DH_CUDA(cudaStreamSynchronize(sk));
+        if (first_round) {
+            // verdicts of the inflate kernel (fused CRC32/ISIZE): stop at the first bad block like bgzf_read does
+            const int *hst = (const int *)s.h_status.p;
+            for (size_t i = 0; i < nblk; ++i)
+                if (hst[i] != 0) {
+                    set_error("BGZF block %zu failed inflate/CRC check (code %d)", s.b0 + i, hst[i]);
+                    return DH_EDATA;
+                }
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, s.ev_inf0, s.ev_inf1) == cudaSuccess) b->st.inflate_ms += ms;
+            if (cudaEventElapsedTime(&ms, s.ev_walk0, s.ev_walk1) == cudaSuccess) b->st.walk_ms += ms;
+        }
+        first_round = false;
+        memset(ht, 0, n);
+        // pointer-jumping check: entry[i] must equal exit[i-1]
+        if (validated == 0) validated = 1;  // block 0's entry is given
+        bool need_round = false;
+        while (validated < n) {
+            const BlockWalk &pw = hw[validated - 1];
+            if (pw.stop != 0) { stopped = true; stop_blk = validated - 1; break; }
+            if (pw.exit_off >= limit_end) { stopped = true; stop_blk = validated - 1; break; }
+            int64_t expect = pw.exit_off;
+            BlockWalk &w = hw[validated];
+            if (w.entry != expect) {
+                if (expect >= hs[validated + 1]) {
+                    // a long record spans this whole block: nothing starts here (no GPU work needed)
+                    w.entry = w.exit_off = expect;
+                    w.count = 0;
+                    w.heap_bytes = 0;
+                    w.stop = 0;
+                    DH_CUDA(cudaMemcpyAsync((BlockWalk *)s.walk.p + validated, &w, sizeof(BlockWalk), cudaMemcpyHostToDevice, sk));
+                } else {
+                    he[validated] = expect;
+                    ht[validated] = 1;
+                    need_round = true;
+                    b->st.rewalk_rounds++;
+                    break;
+                }
+            }
+            ++validated;
+        }
+        if (!need_round) {
+            if (!stopped && hw[n - 1].stop != 0) { stopped = true; stop_blk = n - 1; }
+            if (!stopped && hw[n - 1].exit_off >= limit_end) { stopped = true; stop_blk = n - 1; }
+            break;
+        }
+    }
+    // rows / heap prefix sums, batches
+    const uint32_t last = stopped ? stop_blk : n - 1;
+    b->batches.clear();
+    b->next_batch_i = 0;
+    uint32_t *hrb = (uint32_t *)s.h_row_base.p;
+    uint64_t *hhb = (uint64_t *)s.h_heap_base.p;
+    Batch cur{0, 0, 0, 0, b->rows_total};
+    for (uint32_t i = 0; i <= last; ++i) {
+        const BlockWalk &w = hw[i];
+        if (cur.rows > 0 && cur.rows + w.count > b->batch_rows) {
+            cur.b_hi = i;
+            b->batches.push_back(cur);
+            cur = Batch{i, i, 0, 0, cur.row0 + cur.rows};
+        }
+        hrb[i] = (uint32_t)cur.rows;
+        hhb[i] = cur.heap;
+        cur.rows += w.count;
+        cur.heap += w.heap_bytes;
+    }
+    cur.b_hi = last + 1;
+    if (cur.rows > 0) b->batches.push_back(cur);
+    for (auto &bb : b->batches) b->rows_total += bb.rows;
+    DH_CUDA(cudaMemcpyAsync(s.row_base.p, hrb, n * 4, cudaMemcpyHostToDevice, sk));
+    DH_CUDA(cudaMemcpyAsync(s.heap_base.p, hhb, n * 8, cudaMemcpyHostToDevice, sk));
+    // how the chain continues
+    const BlockWalk &lw = hw[last];
+    b->carry = 0;
+    auto voff_of = [&](int64_t off) -> uint64_t {  // segment-relative inflated offset -> virtual offset
+        if (off < 0) return 0;
+        uint64_t abs_u = bt.uoff[s.b0] + (uint64_t)off;
+        size_t blk = std::upper_bound(bt.uoff.begin() + s.b0, bt.uoff.end(), abs_u) - bt.uoff.begin() - 1;
+        if (blk >= bt.blocks.size()) return ((bt.end_off) << 16);
+        return (bt.blocks[blk].coffset << 16) | (abs_u - bt.uoff[blk]);
+    };
+    if (stopped && lw.stop < 0) {
+        b->final_status = lw.stop;   // bam_read1 / sam_read1_bam error: the reference ends the scan silently here
+        b->chain_done = true;
+        b->st.end_voffset = voff_of(lw.exit_off);
+    } else if (stopped && lw.stop == 0) {
+        b->chain_done = true;        // reached voff_end
+        b->st.end_voffset = voff_of(lw.exit_off);
+    } else if (stopped && lw.stop == 1) {
+        b->carry = (int64_t)s.obytes - lw.exit_off;
+        if ((uint64_t)b->carry > b->carry_cap) {
+            set_error("BAM record of more than %llu bytes straddles a segment: raise the carry buffer (dh_bam_configure)",
+                      (unsigned long long)b->carry_cap);
+            return DH_EFORMAT;
+        }
+        if ((size_t)k + 1 >= b->segs.size()) {
+            // range scan whose last record runs past the inflated look-ahead
+            set_error("record at the end of the scan range extends beyond the look-ahead blocks");
+            return DH_EFORMAT;
+        }
+    } else {
+        b->st.end_voffset = voff_of(lw.exit_off);
+        if ((size_t)k + 1 >= b->segs.size()) b->chain_done = true;
+    }
+    return DH_OK;
+}
+
+int issue_batch(dh_bam *b) {
+    const Batch &bb = b->batches[b->next_batch_i++];
+    SegSlot &s = b->ss[b->cur_seg % NSEG];
+    BatchSlot &o = b->bs[b->issued % NBATCH];
+    // arena layout: [col data | validity]* aligned to 256, heap last
+    uint64_t off = 0, coff[BAM_MAX_COLS], voff[BAM_MAX_COLS];
+    const int ncols = BAM_CORE_COLS + (int)b->tags.size();
+    for (int c = 0; c < ncols; ++c) {
+        coff[c] = voff[c] = UINT64_MAX;
+        if (!((b->col_mask >> c) & 1ull)) continue;
+        coff[c] = off;
+        off = (off + (uint64_t)col_width(b, c) * bb.rows + A256) & ~A256;
+        if (col_nullable(c)) {
+            voff[c] = off;
+            off = (off + ((bb.rows + 63) / 64) * 8 + A256) & ~A256;
+        }
+    }
+    const uint64_t heap_off = off, total = off + bb.heap;
+    int rc;
+    if ((rc = o.arena.reserve(total + 256)) != DH_OK) return rc;
+    if ((rc = o.h_arena.reserve(total + 256)) != DH_OK) return rc;
+    cudaStream_t sk = s_comp(b), sd = s_d2h(b);
+    DecodeParams dp;
+    memset(&dp, 0, sizeof dp);
+    dp.u = (const uint8_t *)s.out.p + b->carry_cap;
+    dp.walk = (const BlockWalk *)s.walk.p;
+    dp.row_base = (const uint32_t *)s.row_base.p;
+    dp.heap_base = (const uint64_t *)s.heap_base.p;
+    dp.b_lo = bb.b_lo;
+    dp.b_hi = bb.b_hi;
+    dp.heap = (uint8_t *)o.arena.p + heap_off;
+    dp.heap_host = (uint64_t)(uintptr_t)((uint8_t *)o.h_arena.p + heap_off);
+    memset(&o.desc, 0, sizeof o.desc);
+    for (int c = 0; c < ncols; ++c) {
+        if (coff[c] == UINT64_MAX) continue;
+        dp.col[c] = (uint8_t *)o.arena.p + coff[c];
+        o.desc.data[c] = (uint8_t *)o.h_arena.p + coff[c];
+        if (voff[c] != UINT64_MAX) {
+            dp.valid[c] = (unsigned long long *)((uint8_t *)o.arena.p + voff[c]);
+            o.desc.validity[c] = (const uint64_t *)((uint8_t *)o.h_arena.p + voff[c]);
+            DH_CUDA(cudaMemsetAsync(dp.valid[c], 0, ((bb.rows + 63) / 64) * 8, sk));
+        }
+    }
+    DH_CUDA(cudaEventRecord(o.ev_k0, sk));
+    DH_CUDA(launch_bam_decode(dp, b->tabs, sk));
+    b->ctx->launches++;
+    DH_CUDA(cudaEventRecord(o.ev_k1, sk));
+    DH_CUDA(cudaStreamWaitEvent(sd, o.ev_k1, 0));
+    if (total) DH_CUDA(cudaMemcpyAsync(o.h_arena.p, o.arena.p, total, cudaMemcpyDeviceToHost, sd));
+    DH_CUDA(cudaEventRecord(o.ev_done, sd));
+    o.timed = true;
+    o.desc.n_rows = bb.rows;
+    o.desc.row0 = bb.row0;
+    o.desc.status = 0;
+    o.desc.n_cols = ncols;
+    o.desc.heap = (const uint8_t *)o.h_arena.p + heap_off;
+    o.desc.heap_bytes = bb.heap;
+    o.desc.bytes = total;
+    b->st.d2h_bytes += total;
+    b->inflight.push_back(b->issued);
+    b->issued++;
+    return DH_OK;
+}
+
+// make sure there is a next batch to issue: advance through segments.  Returns 1 if a batch is available,
+// 0 if the scan is exhausted, < 0 on error.
+int have_work(dh_bam *b) {
+    for (;;) {
+        if (b->cur_seg >= 0 && b->next_batch_i < b->batches.size()) return 1;
+        if (b->chain_done) return 0;
+        int k = b->cur_seg + 1;
+        if ((size_t)k >= b->segs.size()) { b->chain_done = true; return 0; }
+        int rc = issue_inflate(b, k);  // no-op when prefetched
+        if (rc != DH_OK) return rc;
+        b->cur_seg = k;
+        if ((rc = walk_segment(b, k)) != DH_OK) return rc;
+        // prefetch: H2D + inflate of the next segment overlap this segment's decode batches and D2H.  Its slot
+        // still holds segment k-1, whose decode kernels and carry copy were all enqueued on s_comp before this.
+        if (!b->chain_done && (size_t)k + 1 < b->segs.size() && (rc = issue_inflate(b, k + 1)) != DH_OK) return rc;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+dh_bam *dh_bam_open(dh_ctx *ctx, const uint8_t *data, uint64_t size) {
+    if (!ctx || !data) { set_error("dh_bam_open: bad arguments"); return nullptr; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return nullptr; }
+    dh_bam *b = new dh_bam();
+    b->ctx = ctx;
+    b->data = data;
+    b->size = size;
+    memset(&b->st, 0, sizeof b->st);
+    uint64_t bad = 0;
+    if (walk_blocks(data, size, 0, b->bt, &bad) != DH_OK) {
+        set_error("invalid BGZF header at offset %llu", (unsigned long long)bad);
+        delete b;
+        return nullptr;
+    }
+    if (b->bt.blocks.empty()) { set_error("empty file"); delete b; return nullptr; }
+    if (parse_header(b) != DH_OK) { delete b; return nullptr; }
+    build_dictionaries(b);
+    if (ensure_events(b) != DH_OK || upload_tables(b) != DH_OK) { dh_bam_close(b); return nullptr; }
+    return b;
+}
+
+void dh_bam_close(dh_bam *b) {
+    if (!b) return;
+    cudaSetDevice(b->ctx->device);
+    cudaDeviceSynchronize();
+    for (auto &s : b->ss) {
+        s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.blk_start.release(); s.entry.release();
+        s.todo.release(); s.walk.release(); s.row_base.release(); s.heap_base.release();
+        s.h_desc.release(); s.h_status.release(); s.h_blk_start.release(); s.h_entry.release(); s.h_todo.release();
+        s.h_walk.release(); s.h_row_base.release(); s.h_heap_base.release();
+        for (cudaEvent_t e : {s.ev_h2d, s.ev_inf0, s.ev_inf1, s.ev_walk0, s.ev_walk1}) if (e) cudaEventDestroy(e);
+    }
+    for (auto &s : b->bs) {
+        s.arena.release(); s.h_arena.release();
+        for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_done}) if (e) cudaEventDestroy(e);
+    }
+    b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release();
+    delete b;
+}
+
+int32_t dh_bam_n_ref(const dh_bam *b) { return b ? (int32_t)b->ref_names.size() : 0; }
+const char *dh_bam_ref_name(const dh_bam *b, int32_t tid) {
+    return (b && tid >= 0 && (size_t)tid < b->ref_names.size()) ? b->ref_names[tid].c_str() : nullptr;
+}
+uint32_t dh_bam_ref_len(const dh_bam *b, int32_t tid) {
+    return (b && tid >= 0 && (size_t)tid < b->ref_lens.size()) ? b->ref_lens[tid] : 0;
+}
+const char *dh_bam_header_text(const dh_bam *b, uint32_t *len) {
+    if (!b) return nullptr;
+    if (len) *len = (uint32_t)b->text.size();
+    return b->text.c_str();
+}
+uint64_t dh_bam_first_voffset(const dh_bam *b) {
+    if (!b) return 0;
+    if (b->first_blk >= b->bt.blocks.size()) return b->bt.end_off << 16;
+    return (b->bt.blocks[b->first_blk].coffset << 16) | b->first_off;
+}
+uint64_t dh_bam_n_blocks(const dh_bam *b) { return b ? b->bt.blocks.size() : 0; }
+
+int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, int n_tags) {
+    if (!b || n_tags < 0 || n_tags > BAM_MAX_TAGS || (n_tags && !tags)) { set_error("dh_bam_set_projection: bad arguments"); return DH_EINVAL; }
+    if (b->scanning && !b->inflight.empty()) { set_error("dh_bam_set_projection: scan in progress"); return DH_EINVAL; }
+    b->tags.clear();
+    for (int i = 0; i < n_tags; ++i) {
+        TagReq r;
+        r.t0 = (uint8_t)tags[i].tag[0];
+        r.t1 = (uint8_t)tags[i].tag[1];
+        char ty = tags[i].type == 'H' ? 'Z' : tags[i].type;
+        if (ty != 'i' && ty != 'f' && ty != 'Z' && ty != 'A') { set_error("unsupported tag column type '%c'", tags[i].type); return DH_EINVAL; }
+        r.type = (uint8_t)ty;
+        r.pad = 0;
+        b->tags.push_back(r);
+    }
+    const int ncols = BAM_CORE_COLS + n_tags;
+    b->col_mask = ncols >= 64 ? col_mask : (col_mask & ((1ull << ncols) - 1));
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    return upload_tables(b);
+}
+
+int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, uint64_t carry_bytes) {
+    if (!b) return DH_EINVAL;
+    if (seg_comp_bytes) b->seg_comp = std::min<uint64_t>(std::max<uint64_t>(seg_comp_bytes, 1 << 16), 2ull << 30);
+    if (batch_rows) b->batch_rows = batch_rows;
+    if (carry_bytes) {
+        b->carry_cap = (carry_bytes + 255) & ~255ull;
+        for (auto &s : b->ss) { s.out.release(); s.issued_for = -1; }
+    }
+    return DH_OK;
+}
+
+int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
+    if (!b) { set_error("dh_bam_scan_begin: null handle"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    DH_CUDA(cudaDeviceSynchronize());  // drop whatever an abandoned scan left in flight
+    const BlockTable &bt = b->bt;
+    const size_t nb = bt.blocks.size();
+    size_t b_first = b->first_blk;
+    uint32_t off_first = b->first_off;
+    if (voff_beg != 0) {
+        b_first = block_of(b, voff_beg >> 16);
+        off_first = (uint32_t)(voff_beg & 0xffff);
+        if (b_first < nb && bt.blocks[b_first].coffset != (voff_beg >> 16)) { set_error("voff_beg is not a BGZF block address"); return DH_EINVAL; }
+    }
+    b->to_eof = voff_end == UINT64_MAX || (voff_end >> 16) >= bt.end_off;
+    size_t b_stop = nb;
+    if (!b->to_eof) {
+        b->limit_blk = block_of(b, voff_end >> 16);
+        b->limit_off = (uint32_t)(voff_end & 0xffff);
+        if (b->limit_blk < nb && bt.blocks[b->limit_blk].coffset != (voff_end >> 16)) { set_error("voff_end is not a BGZF block address"); return DH_EINVAL; }
+        // inflate up to the limit block plus look-ahead for a record that straddles the range end
+        b_stop = std::min(nb, b->limit_blk + (b->limit_off ? 1 : 0) + 2);
+        if (b_stop >= nb) { b_stop = nb; }
+    }
+    b->end_blk = b_stop;
+    b->segs.clear();
+    size_t s0 = std::min(b_first, b_stop);
+    while (s0 < b_stop) {
+        size_t e = s0;
+        const uint64_t cbase = bt.blocks[s0].coffset & ~15ull;
+        while (e < b_stop && e - s0 < (1u << 17) && bt.blocks[e].coffset + bt.blocks[e].csize - cbase <= b->seg_comp &&
+               bt.uoff[e + 1] - bt.uoff[s0] <= (3ull << 30))
+            ++e;
+        if (e == s0) e = s0 + 1;
+        b->segs.push_back(Seg{s0, e});
+        s0 = e;
+    }
+    for (auto &s : b->ss) s.issued_for = -1;
+    b->first_entry = off_first;
+    b->cur_seg = -1;
+    b->batches.clear();
+    b->next_batch_i = 0;
+    b->inflight.clear();
+    b->issued = b->returned = 0;
+    b->rows_total = 0;
+    b->carry = 0;
+    b->final_status = 0;
+    b->chain_done = b->segs.empty();
+    memset(&b->st, 0, sizeof b->st);
+    b->st.end_voffset = voff_beg ? voff_beg : dh_bam_first_voffset(b);
+    b->scanning = true;
+    return DH_OK;
+}
+
+int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
+    if (!b || !out || !b->scanning) { set_error("dh_bam_next_batch: no scan in progress"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    auto top_up = [&]() -> int {
+        while (b->inflight.size() < 2) {
+            int w = have_work(b);
+            if (w < 0) return w;
+            if (w == 0) break;
+            int rc = issue_batch(b);
+            if (rc != DH_OK) return rc;
+        }
+        return DH_OK;
+    };
+    int rc = top_up();
+    if (rc != DH_OK) { b->scanning = false; return rc; }
+    if (b->inflight.empty()) {
+        b->st.rows = b->rows_total;
+        b->st.status = b->final_status;
+        return 0;
+    }
+    BatchSlot &o = b->bs[b->inflight.front() % NBATCH];
+    b->inflight.pop_front();
+    DH_CUDA(cudaEventSynchronize(o.ev_done));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, o.ev_k0, o.ev_k1) == cudaSuccess) b->st.decode_ms += ms;
+    rc = top_up();  // keep two batches in flight while the caller consumes this one
+    if (rc != DH_OK) { b->scanning = false; return rc; }
+    *out = o.desc;
+    if (b->inflight.empty() && b->chain_done) out->status = b->final_status;
+    b->returned++;
+    b->st.rows = b->rows_total;
+    b->st.status = b->final_status;
+    return 1;
+}
+
+int dh_bam_scan_stats_get(const dh_bam *b, dh_bam_scan_stats *out) {
+    if (!b || !out) return DH_EINVAL;
+    *out = b->st;
+    out->rows = b->rows_total;
+    out->status = b->final_status;
+    return DH_OK;
+}
+
+int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs) {
+    if (!b || n_parts < 1 || !voffs) { set_error("dh_bam_split: bad arguments"); return DH_EINVAL; }
+    const BlockTable &bt = b->bt;
+    const size_t nb = bt.blocks.size();
+    voffs[0] = dh_bam_first_voffset(b);
+    // the block holding the first record stays whole in part 0; cut the rest by compressed bytes
+    size_t lo = std::min(nb, b->first_blk + (b->first_off ? 1 : 0));
+    const uint64_t c0 = lo < nb ? bt.blocks[lo].coffset : bt.end_off, c1 = bt.end_off;
+    size_t prev = lo;
+    for (int p = 1; p < n_parts; ++p) {
+        uint64_t target = c0 + (c1 - c0) * (uint64_t)p / (uint64_t)n_parts;
+        size_t blk = std::max(block_of(b, target), prev);
+        voffs[p] = blk < nb ? (bt.blocks[blk].coffset << 16) : UINT64_MAX;
+        prev = blk;
+    }
+    voffs[n_parts] = UINT64_MAX;
+    return DH_OK;
+}
+
+}  // extern "C"

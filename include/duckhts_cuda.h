@@ -96,6 +96,89 @@ int dh_bgzf_dev_inflate(dh_bgzf_dev *d);
 int dh_bgzf_dev_check(dh_bgzf_dev *d, int64_t *bad_block, int32_t *bad_code);
 int dh_bgzf_dev_read(dh_bgzf_dev *d, uint64_t offset, uint8_t *dst, uint64_t n);
 
+/* ---- A4-A15: read_bam scan -----------------------------------------------------------------------------
+ * Replaces, for one BAM image in host memory, what bam_read_bind/local_init/bam_read_function get from htslib
+ * (src/bam_reader.c:410-1038): sam_open + sam_hdr_read (bam_hdr_read, htslib/sam.c:229-342), then per record
+ * sam_read1 -> bam_read1 (sam.c:779-855, 4124-4134) and the per-row column conversions (bam_reader.c:779-966),
+ * here done by batches on the GPU: BGZF inflate -> record-boundary walk -> columnar decode straight into
+ * DuckDB vector layouts.  Rows come back in file order, exactly the rows the reference's sequential scan
+ * returns; an invalid record ends the scan silently after the rows before it (bam_reader.c:754-765) with the
+ * htslib error code reported in dh_bam_batch.status / dh_bam_scan_status. */
+typedef struct dh_bam dh_bam;
+
+/* Frames the image (A1), inflates the header blocks on the GPU and parses the BAM header on the host.
+ * `data` must stay valid (and should be pinned, dh_host_alloc) until dh_bam_close.  NULL on error. */
+dh_bam *dh_bam_open(dh_ctx *ctx, const uint8_t *data, uint64_t size);
+void dh_bam_close(dh_bam *b);
+int32_t dh_bam_n_ref(const dh_bam *b);                       /* sam_hdr_nref */
+const char *dh_bam_ref_name(const dh_bam *b, int32_t tid);   /* sam_hdr_tid2name */
+uint32_t dh_bam_ref_len(const dh_bam *b, int32_t tid);
+const char *dh_bam_header_text(const dh_bam *b, uint32_t *len);
+uint64_t dh_bam_first_voffset(const dh_bam *b);              /* virtual offset of the first alignment record */
+uint64_t dh_bam_n_blocks(const dh_bam *b);
+
+/* Column schema = the reference's (bam_reader.c:189-204): 0 QNAME 1 FLAG 2 RNAME 3 POS 4 MAPQ 5 CIGAR 6 RNEXT
+ * 7 PNEXT 8 TLEN 9 SEQ 10 QUAL 11 READ_GROUP_ID 12 SAMPLE_ID, then one column per requested typed tag
+ * (standard_tags, bam_reader.c:54-70).  col_mask bit c = column c is projected (projection pushdown,
+ * bam_reader.c:676-679); tag k is column 13+k.  Tag types: 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (SAM Z or H),
+ * 'A' VARCHAR. */
+#define DH_BAM_CORE_COLS 13
+#define DH_BAM_MAX_TAGS 63
+#define DH_BAM_MAX_COLS (DH_BAM_CORE_COLS + DH_BAM_MAX_TAGS)
+typedef struct {
+    char tag[2];
+    char type;
+    char pad;
+} dh_tag_req;
+int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, int n_tags);
+
+/* Pipeline knobs (0 = keep): compressed bytes per inflate segment, rows per output batch, carry buffer for
+ * records that straddle segments.  Small values exercise the multi-segment paths in tests. */
+int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, uint64_t carry_bytes);
+
+/* Start a scan over the records that START at virtual offsets in [voff_beg, voff_end) (bgzf virtual offset =
+ * coffset << 16 | uoffset, htslib/bgzf.h:261).  voff_beg = 0 means "first record"; voff_end = UINT64_MAX means
+ * "to EOF".  voff_beg must be a record boundary (first record, a BAI chunk start, or a dh_bam_split boundary).
+ * This is the unit of multi-GPU sharding: each GPU scans one contiguous range with its own dh_ctx/dh_bam. */
+int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end);
+
+/* VARCHAR cells are DuckDB duckdb_string_t (16 bytes): <= 12 bytes inlined, else prefix + pointer into `heap`
+ * (or, for RNAME/RNEXT/SAMPLE_ID, into a dictionary owned by the dh_bam handle).  Fixed-width columns are plain
+ * arrays: FLAG uint16, POS/PNEXT/TLEN int64, MAPQ int32, 'i' tags int64, 'f' tags double.  validity[c] is a
+ * DuckDB validity mask (bit r = row r valid) or NULL when the column cannot be NULL. */
+typedef struct {
+    uint64_t n_rows;
+    uint64_t row0;        /* scan-relative index of the first row of this batch */
+    int32_t status;       /* 0, or the htslib error code that ended the scan right after this batch */
+    int32_t n_cols;
+    const void *data[DH_BAM_MAX_COLS];
+    const uint64_t *validity[DH_BAM_MAX_COLS];
+    const uint8_t *heap;
+    uint64_t heap_bytes;
+    uint64_t bytes;       /* bytes copied device -> host for this batch */
+} dh_bam_batch;
+/* Returns 1 and fills *out (buffers stay valid until the next call on this handle), 0 at end of scan, < 0 on
+ * error. */
+int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out);
+
+typedef struct {
+    uint64_t rows;
+    uint64_t h2d_bytes, d2h_bytes;
+    uint64_t inflated_bytes;
+    uint64_t n_blocks;
+    uint64_t rewalk_rounds;   /* boundary speculation misses that needed a re-walk */
+    int32_t status;           /* final scan status (0 = clean EOF / range end) */
+    int32_t pad;
+    uint64_t end_voffset;     /* virtual offset of the first record NOT returned (for range merging) */
+    float inflate_ms, walk_ms, decode_ms;  /* sums of CUDA-event kernel times */
+} dh_bam_scan_stats;
+int dh_bam_scan_stats_get(const dh_bam *b, dh_bam_scan_stats *out);
+
+/* n_parts + 1 virtual offsets cutting the alignment section into contiguous ranges of about equal compressed
+ * size on BGZF block boundaries (htslib-written BAM starts every block on a record boundary, htslib/sam.c:883).
+ * voffs[0] = first record, voffs[n_parts] = UINT64_MAX. */
+int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs);
+
 /* CUDA-event timer on the context's stream (the stream every kernel of this library is launched on). */
 int dh_ctx_sync(dh_ctx *ctx);
 int dh_timer_start(dh_ctx *ctx);

@@ -1,0 +1,30 @@
+#!/bin/bash
+# Regenerates tests/golden/ from the REFERENCE (run in the build container, where /root/reference exists):
+#   * small binary fixtures of the reference's own test suites (test/data, third_party/htslib/test), the .sam ones
+#     converted to BAM by the reference's htslib (harness/_bin/ref_dump sam2bam);
+#   * for each, the cells the reference scan stores (harness/_bin/ref_dump dump = htslib calls of
+#     src/bam_reader.c:779-966), and the raw bgzf_read() stream sha256.
+# The outputs are committed; the GPU box never needs /root/reference.
+set -e
+cd "$(dirname "$0")"
+REF=/root/reference
+HT=$REF/third_party/htslib/test
+D=../../harness/_bin/ref_dump
+TAGS="NM:i MD:Z AS:i XS:i XA:A XZ:Z Xf:f F0:f I1:i ZA:A H0:Z"
+cp $REF/test/data/range.bam range.bam
+cp $HT/bgzf_boundaries/bgzf_boundaries1.bam $HT/bgzf_boundaries/bgzf_boundaries2.bam $HT/bgzf_boundaries/bgzf_boundaries3.bam .
+cp $HT/colons.bam colons.bam
+cp $HT/bgziptest.txt.gz bgziptest.txt.gz
+for s in 'auxf#values' 'ce#unmap' 'ce#unmap1' 'ce#unmap2' 'c1#noseq' 'ce#large_seq' 'ce#5b' 'c1#clip' 'ce#1' 'ce#supp' 'c1#bounds' 'xx#rg'; do
+  o=$(echo "$s" | tr '#' '_')
+  $D sam2bam "$HT/$s.sam" "$o.bam"
+done
+zcat $REF/test/data/rg.sam.gz > /tmp/rg.sam && $D sam2bam /tmp/rg.sam rg.bam
+zcat $REF/test/data/aux_tags.sam.gz > /tmp/aux_tags.sam && $D sam2bam /tmp/aux_tags.sam aux_tags.bam
+chmod u+w *.bam *.gz
+for f in *.bam; do
+  $D dump "$f" $TAGS > "${f%.bam}.tsv"
+  $D bgunzip "$f" | sha256sum | cut -d' ' -f1 > "${f%.bam}.sha256"
+done
+$D bgunzip bgziptest.txt.gz | sha256sum | cut -d' ' -f1 > bgziptest.txt.sha256
+ls -la

@@ -1,0 +1,253 @@
+"""Parity of the read_bam scan (BGZF inflate -> boundary walk -> columnar decode, through the C-ABI) against the
+oracle's restatement of bam_read1 + bam_read_function.  Bit-exact: values, row order, NULLs, stop-on-error."""
+import struct
+
+import numpy as np
+import pytest
+
+import duckhts_b200 as dh
+from oracle import dh_oracle_py as orc
+from tests import util
+from tests.util import aux_tag, bam_header, bam_record
+
+pytestmark = pytest.mark.gpu
+
+TAGS = [(b"NM", "i"), (b"MD", "Z"), (b"AS", "i")]
+
+
+def both(ctx, img, tags=TAGS, **kw):
+    rc, infl, bad = orc.bgzf_inflate(img)
+    assert rc == 0
+    exp = orc.bam_decode(infl, tags)
+    got = dh.bam_scan(ctx, img, tags=tags, **kw)
+    util.assert_bam_equal(got, exp)
+    assert got["ref_names"] == exp["ref_names"] and got["ref_lens"] == exp["ref_lens"] and got["text"] == exp["text"]
+    return got, exp
+
+
+def test_synthetic_single_end(ctx):
+    got, exp = both(ctx, util.synth_bam_bytes(n_records=20000, seed=11))
+    assert got["n"] == 20000 and got["status"] == 0
+
+
+def test_synthetic_paired_small_segments_and_batches(ctx):
+    img = util.synth_bam_bytes(n_records=60000, seed=12, paired=True)
+    got, _ = both(ctx, img, seg_comp=1 << 16, batch_rows=777)
+    assert got["n_batches"] > 50
+    both(ctx, img, seg_comp=1 << 20, batch_rows=5000)
+    both(ctx, img)
+
+
+def test_records_straddling_blocks_and_segments(ctx):
+    """gen_synth bgzf: the BAM byte stream cut into BGZF blocks at arbitrary byte positions (foreign-writer case,
+    htslib/test/bgzf_boundaries): exercises speculative entries, the exit/entry chain check and the carry."""
+    img = np.fromfile(util.synth_path("bgzf", n_records=30000, seed=13, paired=True), dtype=np.uint8)
+    got, _ = both(ctx, img, seg_comp=1 << 16, batch_rows=4096)
+    both(ctx, img)
+
+
+def test_unplaced_reads_are_returned_in_sequential_mode(ctx):
+    img = util.synth_bam_bytes(n_records=3000, seed=14, paired=True, extra=("--unplaced", "50"))
+    got, exp = both(ctx, img)
+    assert got["rname"][-1] == b"*" and got["n"] == 3050
+
+
+def test_projection_subsets(ctx):
+    img = util.synth_bam_bytes(n_records=5000, seed=15, paired=True)
+    rc, infl, _ = orc.bgzf_inflate(img)
+    exp = orc.bam_decode(infl, TAGS)
+    for mask in (0, 1 << 1, (1 << 3) | (1 << 9), (1 << 12), (1 << 11) | (1 << 14), 0xffff & ~(1 << 10)):
+        got = dh.bam_scan(ctx, img, tags=TAGS, col_mask=mask)
+        assert got["n"] == exp["n"]
+        for c, name in enumerate(dh.bam.CORE_NAMES):
+            if (mask >> c) & 1:
+                if name in util.FIX_COLS:
+                    assert np.array_equal(got[name], exp[name])
+                else:
+                    assert got[name] == orc.strcol_list(exp[name]), name
+        for k in range(3):
+            if (mask >> (13 + k)) & 1:
+                assert np.array_equal(got["tags"][k]["valid"], exp["tags"][k]["valid"])
+
+
+REFS = [(b"chr1", 1000000), (b"a_contig_name_longer_than_12", 5000), (b"c", 10)]
+TEXT = (b"@HD\tVN:1.6\tSO:unsorted\n@SQ\tSN:chr1\tLN:1000000\n@SQ\tSN:a_contig_name_longer_than_12\tLN:5000\n@SQ\tSN:c\tLN:10\n"
+        b"@RG\tID:g1\tSM:s1\n@RG\tID:nosm\tPL:x\n@RG\tID:a_long_read_group_identifier\tSM:a_sample_name_longer_than_12_bytes\n"
+        b"@RG\tID:g1\tSM:shadowed\n@CO\tx\n")
+
+
+def edge_records():
+    r = []
+    seq = "ACGTNACGTMRSVWYHKDB=" * 3
+    r.append(bam_record(b"plain", 0, 0, 99, 60, [(60, "M")], seq=seq, qual=range(60), aux=aux_tag("RG", "Z", "g1") + aux_tag("NM", "C", 3)))
+    r.append(bam_record(b"unmapped", 4, -1, -1, 0, [], seq="ACGT", qual=[1, 2, 3, 4]))
+    r.append(bam_record(b"noseq", 0, 0, 5, 1, [], seq=""))
+    r.append(bam_record(b"noqual", 0, 1, 5, 1, [(13, "M")], seq="ACGTACGTACGTA", aux=aux_tag("RG", "Z", "nosm")))
+    r.append(bam_record(b"short12chars", 16, 2, 0, 7, [(12, "M")], mtid=1, mpos=41, tlen=-77, seq="ACGTACGTACGT", qual=[40] * 12,
+                        aux=aux_tag("RG", "Z", "a_long_read_group_identifier")))
+    r.append(bam_record(b"q" * 13, 0, 0, 1, 1, [(5, "S"), (1000, "M"), (3, "I"), (20, "D"), (992, "M")], seq="A" * 2000, qual=[30] * 2000,
+                        aux=aux_tag("MD", "Z", "1000^" + "A" * 20 + "992") + aux_tag("AS", "s", -5) + aux_tag("RG", "Z", "unknown_rg")))
+    r.append(bam_record(b"n" * 254, 0, 0, 1, 1, [(1, "M")], seq="C", qual=[0]))
+    ops = [(1 + (i % 3), "MID"[i % 3]) for i in range(100)]
+    qlen = sum(l for l, o in ops if o in "MI")
+    r.append(bam_record(b"manyops", 0, 0, 1, 1, ops, seq="G" * qlen, qual=[2] * qlen, aux=aux_tag("NM", "i", -7) + aux_tag("NM", "i", 9)))
+    r.append(bam_record(b"alltypes", 0, 0, 1, 1, [(4, "M")], seq="ACGT", qual=[9] * 4,
+                        aux=aux_tag("XA", "A", "Q") + aux_tag("Xc", "c", -128) + aux_tag("XC", "C", 255) + aux_tag("Xs", "s", -32768) +
+                        aux_tag("XS", "S", 65535) + aux_tag("Xi", "i", -2147483648) + aux_tag("XI", "I", 4294967295) + aux_tag("Xf", "f", 3.25) +
+                        aux_tag("Xd", "d", -1e300) + aux_tag("XZ", "Z", "") + aux_tag("XH", "H", "DEADBEEF") + aux_tag("XB", "B", ("S", [1, 2, 3])) +
+                        aux_tag("Xb", "B", ("f", [1.5])) + aux_tag("TS", "A", "+") + aux_tag("AS", "f", 2.5) + aux_tag("NM", "Z", "notint") +
+                        aux_tag("MD", "i", 5) + aux_tag("RG", "Z", "g1")))
+    r.append(bam_record(b"qual223", 0, 0, 1, 1, [(20, "M")], seq="A" * 20, qual=[30] * 15 + [223] + [30] * 4))
+    r.append(bam_record(b"qual223early", 0, 0, 1, 1, [(20, "M")], seq="A" * 20, qual=[30] * 3 + [223] + [30] * 16))
+    r.append(bam_record(b"qual223first", 0, 0, 1, 1, [(20, "M")], seq="A" * 20, qual=[223] + [30] * 19))
+    r.append(bam_record(b"nul\0inside", 0, 0, 1, 1, [(1, "M")], seq="T", qual=[5]))
+    r.append(bam_record(raw_qname=b"nonul", flag=0, tid=0, pos=1, mapq=1, cigar=[(1, "M")], seq="T", qual=[5]))
+    # CG:B,I long-CIGAR convention (bam_tag2cigar, sam.c:675-730): placeholder kS mN + real CIGAR in the tag
+    real = [(10, "M"), (2, "I"), (8, "M")]
+    cg = aux_tag("CG", "B", ("I", [(l << 4) | util.CIG_OPS.index(o) for l, o in real]))
+    r.append(bam_record(b"cgtag", 0, 0, 100, 1, [(20, "S"), (18, "N")], seq="A" * 20, qual=[1] * 20, aux=aux_tag("NM", "C", 1) + cg + aux_tag("RG", "Z", "g1")))
+    r.append(bam_record(b"hugeread", 0, 0, 1, 1, [(150000, "M")], seq="ACGT" * 37500, qual=[20] * 150000, aux=aux_tag("MD", "Z", "150000")))
+    r.append(bam_record(b"after_huge", 0, 0, 2, 2, [(3, "M")], seq="AAA", qual=[1, 2, 3], aux=aux_tag("RG", "H", "AB")))
+    r.append(bam_record(b"badaux", 0, 0, 2, 2, [(3, "M")], seq="AAA", qual=[1, 2, 3], aux=aux_tag("NM", "C", 1) + b"ZZ?" + aux_tag("AS", "C", 9)))
+    r.append(bam_record(b"unterminatedZ", 0, 0, 2, 2, [(3, "M")], seq="AAA", qual=[1, 2, 3], aux=aux_tag("NM", "C", 1) + b"MDZabc"))
+    return r
+
+
+EDGE_TAGS = [(b"NM", "i"), (b"MD", "Z"), (b"AS", "i"), (b"AS", "f"), (b"TS", "A"), (b"XA", "A"), (b"Xf", "f"), (b"Xd", "f"), (b"XZ", "Z"),
+             (b"XH", "Z"), (b"XI", "i"), (b"Xi", "i"), (b"Xs", "i"), (b"XS", "i"), (b"Xc", "i"), (b"XC", "i"), (b"XB", "Z"), (b"XB", "i"),
+             (b"XA", "i"), (b"ZZ", "Z"), (b"Xf", "i")]
+
+
+def test_edge_case_records(ctx):
+    stream = bam_header(REFS, TEXT) + b"".join(edge_records())
+    for block in (0xff00, 4096, 333):
+        img = util.make_bgzf(stream, block=block)
+        got, exp = both(ctx, img, tags=EDGE_TAGS, seg_comp=1 << 16, batch_rows=5)
+        assert got["n"] == len(edge_records()) and got["status"] == 0
+    assert got["rname"][4] == b"c" and got["rnext"][4] == b"a_contig_name_longer_than_12"
+    assert got["sample"][0] == b"s1" and got["sample"][3] is None and got["sample"][4] == b"a_sample_name_longer_than_12_bytes"
+    assert got["cigar"][14] == b"10M2I8M" and got["qual"][9] == b"?" * 15 and got["qual"][11] == b""
+
+
+@pytest.mark.parametrize("case", ["block_len_small", "cigar_qlen", "tid_range", "mtid_range", "l_qname0", "sizes", "trunc_core",
+                                  "trunc_body", "trunc_len", "neg_lseq"])
+def test_invalid_record_ends_scan_silently_with_same_rows_and_code(ctx, case):
+    good = [bam_record(b"g%d" % i, 0, 0, i, 1, [(4, "M")], seq="ACGT", qual=[1] * 4) for i in range(300)]
+    bad = bam_record(b"bad", 0, 0, 5, 1, [(4, "M")], seq="ACGT", qual=[1] * 4)
+    tail = good[:7]
+    if case == "block_len_small":
+        bad = struct.pack("<I", 31) + bad[4:]
+    elif case == "cigar_qlen":
+        bad = bam_record(b"bad", 0, 0, 5, 1, [(5, "M")], seq="ACGT", qual=[1] * 4)
+    elif case == "tid_range":
+        bad = bam_record(b"bad", 0, 3, 5, 1, [(4, "M")], seq="ACGT", qual=[1] * 4)
+    elif case == "mtid_range":
+        bad = bam_record(b"bad", 0, 0, 5, 1, [(4, "M")], mtid=-2, seq="ACGT", qual=[1] * 4)
+    elif case == "l_qname0":
+        bad = bytearray(bad); bad[12] = 0; bad = bytes(bad)
+    elif case == "sizes":
+        bad = bytearray(bad); bad[20:24] = struct.pack("<i", 1000); bad = bytes(bad)
+    elif case == "neg_lseq":
+        bad = bytearray(bad); bad[20:24] = struct.pack("<i", -1); bad = bytes(bad)
+    elif case == "trunc_core":
+        bad, tail = bad[:20], []
+    elif case == "trunc_body":
+        bad, tail = bad[:-3], []
+    elif case == "trunc_len":
+        bad, tail = bad[:2], []
+    stream = bam_header(REFS, TEXT) + b"".join(good) + bad + b"".join(tail)
+    for block in (0xff00, 700):
+        got, exp = both(ctx, util.make_bgzf(stream, block=block), seg_comp=1 << 16, batch_rows=64)
+        assert got["n"] == 300 and got["status"] == exp["status"] < 0
+
+
+def test_header_only_and_tiny_files(ctx):
+    got, _ = both(ctx, util.make_bgzf(bam_header(REFS, TEXT)))
+    assert got["n"] == 0 and got["status"] == 0
+    got, _ = both(ctx, util.make_bgzf(bam_header([], b"")))
+    assert got["n"] == 0
+    got, _ = both(ctx, util.make_bgzf(bam_header(REFS, TEXT) + edge_records()[0]))
+    assert got["n"] == 1
+    # a header larger than several BGZF blocks
+    refs = [(b"contig_%05d" % i, 1000 + i) for i in range(20000)]
+    got, _ = both(ctx, util.make_bgzf(bam_header(refs, b"@CO\t" + b"x" * 200000 + b"\n") + bam_record(b"r", 0, 19999, 1, 1, [(1, "M")], seq="A", qual=[1])))
+    assert got["n"] == 1 and got["rname"][0] == b"contig_19999"
+    with pytest.raises(dh.DuckhtsError):
+        dh.bam_scan(ctx, util.make_bgzf(b"NOTBAM" * 10))
+
+
+def test_range_scans_concatenate_to_the_sequential_scan(ctx):
+    """Offset-range sharding (the multi-GPU unit): ranges from dh_bam_split scanned independently and merged in
+    order give exactly the sequential scan; each range's end_voffset is the next range's start."""
+    img = util.synth_bam_bytes(n_records=80000, seed=16, paired=True)
+    rc, infl, _ = orc.bgzf_inflate(img)
+    exp = orc.bam_decode(infl, TAGS)
+    for parts in (2, 3, 8):
+        with dh.BamFile(ctx, img) as bf:
+            voffs = bf.split(parts)
+        assert voffs[0] == dh.BamFile(ctx, img).first_voffset and voffs[-1] == dh.VOFF_MAX
+        qn, pos, total = [], [], 0
+        for p in range(parts):
+            if voffs[p] == dh.VOFF_MAX:
+                continue
+            got = dh.bam_scan(ctx, img, tags=TAGS, voff=(voffs[p], voffs[p + 1]), seg_comp=1 << 18)
+            assert got["status"] == 0
+            if voffs[p + 1] != dh.VOFF_MAX:
+                assert got["stats"].end_voffset == voffs[p + 1]
+            qn += got["qname"]
+            pos.append(got["pos"])
+            total += got["n"]
+        assert total == exp["n"] and qn == orc.strcol_list(exp["qname"]) and np.array_equal(np.concatenate(pos), exp["pos"])
+
+
+def test_large_scan_properties(ctx):
+    """1M records: row count, per-column checksums vs the oracle, monotone row0, heap pointers inside the heap."""
+    img = util.synth_bam_bytes(n_records=1000000, seed=6, paired=True)
+    rc, infl, _ = orc.bgzf_inflate(img)
+    exp = orc.bam_decode(infl, TAGS)
+    with dh.BamFile(ctx, img) as bf:
+        bf.set_projection(None, TAGS)
+        bf.scan_begin()
+        rows, sums = 0, {k: 0 for k in util.FIX_COLS}
+        seq_heap_bytes = 0
+        while True:
+            b = bf.next_batch()
+            if b is None:
+                break
+            assert b.row0 == rows
+            cols = dh.batch_to_columns(bf, b) if rows == 0 else None
+            n = int(b.n_rows)
+            import ctypes as C
+            for c, name in enumerate(dh.bam.CORE_NAMES):
+                if name in util.FIX_COLS:
+                    dt = np.dtype(dh.bam.CORE_DTYPES[name])
+                    sums[name] += int(np.frombuffer(C.string_at(b.data[c], n * dt.itemsize), dtype=dt).astype(np.int64).sum())
+            cells = np.frombuffer(C.string_at(b.data[9], 16 * n), dtype=np.uint8).reshape(n, 16)
+            ptr = cells[:, 8:].copy().view(np.uint64).ravel()
+            ln = cells[:, :4].copy().view(np.uint32).ravel()
+            assert (ln == 150).all() and (ptr >= b.heap).all() and (ptr + 150 <= b.heap + b.heap_bytes).all()
+            if cols is not None:
+                k = min(n, 2000)
+                assert cols["seq"][:k] == orc.strcol_list(exp["seq"])[:k]
+            rows += n
+        assert rows == exp["n"] == 1000000
+        for k in util.FIX_COLS:
+            assert sums[k] == int(exp[k].astype(np.int64).sum()), k
+        assert bf.stats().status == 0
+
+
+@pytest.mark.parametrize("name", util.golden_names())
+def test_reference_golden_vectors(ctx, name):
+    """The reference's own fixtures (test/data/range.bam, htslib/test/bgzf_boundaries*, auxf#values, ce#unmap*, c1#noseq,
+    ce#large_seq ...): GPU scan vs the cells the reference's htslib produced (tests/golden/*.tsv)."""
+    import hashlib
+    import os
+    img = np.fromfile(os.path.join(util.GOLDEN, name + ".bam"), dtype=np.uint8)
+    out, st = dh.bgzf_inflate(ctx, img)
+    assert hashlib.sha256(out.tobytes()).hexdigest() == open(os.path.join(util.GOLDEN, name + ".sha256")).read().strip()
+    got = dh.bam_scan(ctx, img, tags=util.GOLDEN_TAGS, seg_comp=1 << 16, batch_rows=50)
+    lines = util.dump_lines(got, util.GOLDEN_TAGS, False)
+    exp = open(os.path.join(util.GOLDEN, name + ".tsv")).read().split("\n")[:-1]
+    assert len(lines) == len(exp)
+    for i, (a, b) in enumerate(zip(lines, exp)):
+        assert a == b, f"{name} line {i}"

@@ -106,3 +106,91 @@ def assert_bam_equal(got, exp, tags=True):
                 assert np.array_equal(gt["f"][et["valid"]].view(np.uint64), et["f"][et["valid"]].view(np.uint64)), f"tag {k} f"
             else:
                 assert gt["s"] == orc.strcol_list(et["s"]), f"tag {k} strings"
+
+
+# ---- hand-made BAM streams for edge cases ---------------------------------------------------------------
+def bam_header(refs, text=b"@HD\tVN:1.6\n"):
+    out = [b"BAM\x01", struct.pack("<I", len(text)), text, struct.pack("<I", len(refs))]
+    for name, ln in refs:
+        nb = name + b"\0"
+        out += [struct.pack("<I", len(nb)), nb, struct.pack("<I", ln)]
+    return b"".join(out)
+
+
+CIG_OPS = "MIDNSHP=XB"
+NT16 = "=ACMGRSVTWYHKDBN"
+
+
+def bam_record(qname=b"r", flag=0, tid=0, pos=0, mapq=0, cigar=(), mtid=-1, mpos=-1, tlen=0, seq="", qual=None, aux=b"",
+               raw_qname=None, bin_=0):
+    """cigar: iterable of (len, opchar).  qual: bytes of phred values, None -> 0xff * len.  raw_qname overrides the
+    NUL-terminated name bytes."""
+    qn = raw_qname if raw_qname is not None else qname + b"\0"
+    cig = b"".join(struct.pack("<I", (l << 4) | CIG_OPS.index(o)) for l, o in cigar)
+    l_seq = len(seq)
+    packed = bytearray((l_seq + 1) // 2)
+    for i, ch in enumerate(seq):
+        packed[i >> 1] |= NT16.index(ch) << (4 if i % 2 == 0 else 0)
+    q = bytes([0xff] * l_seq) if qual is None else bytes(qual)
+    assert len(q) == l_seq
+    body = struct.pack("<iiBBHHHiiii", tid, pos, len(qn), mapq, bin_, len(cigar), flag, l_seq, mtid, mpos, tlen) + qn + cig + bytes(packed) + q + aux
+    return struct.pack("<I", len(body)) + body
+
+
+def aux_tag(tag, ty, val):
+    t = tag if isinstance(tag, bytes) else tag.encode()
+    fmt = {"c": "<b", "C": "<B", "s": "<h", "S": "<H", "i": "<i", "I": "<I", "f": "<f", "d": "<d"}
+    if ty in fmt:
+        return t + ty.encode() + struct.pack(fmt[ty], val)
+    if ty == "A":
+        return t + b"A" + (val if isinstance(val, bytes) else val.encode())
+    if ty in ("Z", "H"):
+        return t + ty.encode() + (val if isinstance(val, bytes) else val.encode()) + b"\0"
+    if ty == "B":
+        sub, vals = val
+        return t + b"B" + sub.encode() + struct.pack("<I", len(vals)) + b"".join(struct.pack(fmt[sub], v) for v in vals)
+    raise ValueError(ty)
+
+
+# ---- canonical text form shared with harness/ref_dump.c (the reference-generated golden vectors) -------------
+GOLDEN_TAGS = [(b"NM", "i"), (b"MD", "Z"), (b"AS", "i"), (b"XS", "i"), (b"XA", "A"), (b"XZ", "Z"), (b"Xf", "f"), (b"F0", "f"),
+               (b"I1", "i"), (b"ZA", "A"), (b"H0", "Z")]
+
+
+def _esc(b):
+    return "".join(chr(c) if 0x21 <= c <= 0x7e and c != 0x5c else "\\x%02x" % c for c in b)
+
+
+def dump_lines(res, tags, from_oracle):
+    """Rows of a scan result (oracle dict or duckhts_b200.bam_scan dict) in ref_dump's text form."""
+    from oracle import dh_oracle_py as orc
+
+    def strs(name):
+        return orc.strcol_list(res[name]) if from_oracle else res[name]
+
+    S = {n: strs(n) for n in STR_COLS}
+    tag_cols = []
+    for k, (tg, ty) in enumerate(tags):
+        t = res["tags"][k]
+        if ty == "i":
+            tag_cols.append([str(int(v)) if ok else "\\N" for v, ok in zip(t["i"], t["valid"])])
+        elif ty == "f":
+            tag_cols.append(["%016x" % int(np.float64(v).view(np.uint64)) if ok else "\\N" for v, ok in zip(t["f"], t["valid"])])
+        else:
+            s = orc.strcol_list(t["s"]) if from_oracle else t["s"]
+            tag_cols.append([("\\N" if x is None else (_esc(x) if x else "\\e")) for x in s])
+    lines = ["#n_ref %d" % len(res["ref_names"])]
+    for nm, ln in zip(res["ref_names"], res["ref_lens"]):
+        lines.append("#ref %s %d" % (_esc(nm), ln))
+    for r in range(res["n"]):
+        f = [_esc(S["qname"][r]), str(int(res["flag"][r])), _esc(S["rname"][r]), str(int(res["pos"][r])), str(int(res["mapq"][r])),
+             _esc(S["cigar"][r]), _esc(S["rnext"][r]), str(int(res["pnext"][r])), str(int(res["tlen"][r])), _esc(S["seq"][r]),
+             _esc(S["qual"][r]), "\\N" if S["rg"][r] is None else _esc(S["rg"][r]), "\\N" if S["sample"][r] is None else _esc(S["sample"][r])]
+        f += [tc[r] for tc in tag_cols]
+        lines.append("\t".join(f))
+    lines.append("#status %d %d" % (res["status"], res["n"]))
+    return lines
+
+
+def golden_names():
+    return sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith(".bam"))
