@@ -58,7 +58,10 @@ struct Rec {
     uint32_t cigar_text_len; // exact length of the CIGAR text (0 if cig_n == 0)
 };
 
-// scalar skip_aux (sam.c:4785-4809): s = offset of the type byte.  Returns next offset, or -1 if corrupt.
+// Offsets may be negative (bytes carried over from the previous segment), so "none/corrupt" is NONE, never -1.
+constexpr int64_t NONE = INT64_MIN;
+
+// scalar skip_aux (sam.c:4785-4809): s = offset of the type byte.  Returns next offset, or NONE if corrupt.
 // *complete: for Z/H, whether a NUL terminator was found.
 __device__ __forceinline__ int64_t skip_aux_scalar(const uint8_t *u, int64_t s, int64_t end, bool *complete) {
     *complete = true;
@@ -72,33 +75,33 @@ __device__ __forceinline__ int64_t skip_aux_scalar(const uint8_t *u, int64_t s, 
         return end;
     }
     if (size == 'B') {
-        if (end - s < 5) return -1;
+        if (end - s < 5) return NONE;
         size = aux_type2size(ld8(u, s));
         ++s;
         uint32_t n = ld32u(u, s);
         s += 4;
-        if (size == 0 || (uint64_t)(end - s) < (uint64_t)size * n) return -1;
+        if (size == 0 || (uint64_t)(end - s) < (uint64_t)size * n) return NONE;
         return s + (int64_t)((uint64_t)size * n);
     }
-    if (size == 0) return -1;
-    if (end - s < size) return -1;
+    if (size == 0) return NONE;
+    if (end - s < size) return NONE;
     return s + size;
 }
 
 // scalar bam_aux_get (sam.c:4832-4855) over aux bytes [a0, end): returns offset of the type byte or -1
 __device__ __forceinline__ int64_t aux_get_scalar(const uint8_t *u, int64_t a0, int64_t end, uint32_t t0, uint32_t t1) {
-    if (end - a0 <= 2) return -1;
+    if (end - a0 <= 2) return NONE;
     int64_t s = a0 + 2;
     for (;;) {
         bool complete;
         int64_t nx = skip_aux_scalar(u, s, end, &complete);
         if (ld8(u, s - 2) == t0 && ld8(u, s - 1) == t1) {
-            if (nx < 0) return -1;
+            if (nx == NONE) return NONE;
             uint32_t ty = ld8(u, s);
-            if ((ty == 'Z' || ty == 'H') && !complete) return -1;
+            if ((ty == 'Z' || ty == 'H') && !complete) return NONE;
             return s;
         }
-        if (nx < 0 || end - nx <= 2) return -1;
+        if (nx == NONE || end - nx <= 2) return NONE;
         s = nx + 2;
     }
 }
@@ -147,11 +150,11 @@ __device__ __forceinline__ int parse_record(const uint8_t *u, int64_t off, int64
     r.qual = r.seq + (((int64_t)r.l_qseq + 1) >> 1);
     r.aux = r.qual + r.l_qseq;
     r.cig_n = r.n_cigar;
-    r.cg_lo = r.cg_hi = INT64_MIN;
+    r.cg_lo = r.cg_hi = NONE;
     // bam_tag2cigar (sam.c:675-730): fast-path test first
     if (r.n_cigar && ld32u(u, r.cigar) == (4u | ((uint32_t)r.l_qseq << 4)) && r.tid >= 0 && r.pos >= 0) {
         int64_t CG = aux_get_scalar(u, r.aux, r.end, 'C', 'G');
-        if (CG >= 0 && ld8(u, CG) == 'B' && (ld8(u, CG + 1) == 'I' || ld8(u, CG + 1) == 'i')) {
+        if (CG != NONE && ld8(u, CG) == 'B' && (ld8(u, CG + 1) == 'I' || ld8(u, CG + 1) == 'i')) {
             uint32_t CG_len = ld32u(u, CG + 2);
             if (CG_len >= r.n_cigar && CG_len < (1u << 29)) {
                 r.cig_n = CG_len;
@@ -253,7 +256,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
                 bool complete;
                 int64_t nx = skip_aux_scalar(u, s, r.end, &complete);
                 uint32_t ty = ld8(u, s);
-                if (nx >= 0 && complete && (ty == 'Z' || ty == 'H')) {
+                if (nx != NONE && complete && (ty == 'Z' || ty == 'H')) {
                     uint32_t len = (uint32_t)(nx - 1 - (s + 1));
                     if (len > 12u) {
                         uint32_t t0 = ld8(u, s - 2), t1 = ld8(u, s - 1);
@@ -264,7 +267,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
                         if (wanted) need += align4(len);
                     }
                 }
-                if (nx < 0 || r.end - nx <= 2) break;
+                if (nx == NONE || r.end - nx <= 2) break;
                 s = nx + 2;
             }
         }
@@ -349,7 +352,7 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
     for (uint32_t rec_i = 0; rec_i < bw.count; ++rec_i, ++row) {
         Rec r;
         // counts/entries come from the validated walk, so this cannot fail; is_final=false keeps it cheap
-        parse_record(u, off, INT64_MAX, false, t.n_ref, r);
+        parse_record(u, off, INT64_MAX / 2, false, t.n_ref, r);  // (off may be negative: carried bytes)
         // ---- fixed-width columns (bam_reader.c:790-855): one lane each ----
         if (lane == 0 && ((mask >> COL_FLAG) & 1)) reinterpret_cast<uint16_t *>(p.col[COL_FLAG])[row] = (uint16_t)r.flag;
         if (lane == 1 && ((mask >> COL_POS) & 1)) reinterpret_cast<int64_t *>(p.col[COL_POS])[row] = (int64_t)r.pos + 1;
@@ -486,10 +489,10 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
                         nx = complete ? z + 1 : r.end;
                     } else nx = skip_aux_scalar(u, s, r.end, &complete);
                     uint32_t tg = ld8(u, s - 2) | (ld8(u, s - 1) << 8);
-                    const int32_t hv = (nx < 0 || !complete) ? -1 : (int32_t)(s - r.off);
+                    const int32_t hv = (nx == NONE || !complete) ? -1 : (int32_t)(s - r.off);
                     if (hit0 == 0 && rq_tag[0] == tg) hit0 = hv;
                     if (hit1 == 0 && rq_tag[1] == tg) hit1 = hv;
-                    if (nx < 0 || r.end - nx <= 2) break;
+                    if (nx == NONE || r.end - nx <= 2) break;
                     s = nx + 2;
                 }
             }
