@@ -186,14 +186,27 @@ def cpu_baseline_inflate(unit_path, threads, out_limit):
 
 
 # ---------------------------------------------------------------------------------------------------------
+WORKLOAD = ("read_bam full-column scan (13 core columns + typed tags NM, MD, AS) of a synthetic 100M-record 2x150 bp paired "
+            "WGS-like BAM (BASELINE configs[2]); BGZF inflate GB/s of the same bytes reported alongside (configs[1])")
+TAGS = [(b"NM", "i"), (b"MD", "Z"), (b"AS", "i")]
+
+
+def cpu_baseline_read_bam(unit_path, threads, max_records):
+    """The reference's htslib path (sam_read1 + the column conversions of src/bam_reader.c:779-966 through the same
+    htslib calls) with hts_set_threads(threads), on a bounded sample."""
+    r = run_ref_bench("sam_read1", unit_path, threads, max_records)
+    return {"value": r["records"] / 1e6 / r["seconds"], "unit": "Mrecords/s", "cores": threads, "kind": "reference",
+            "sample": f"first {r['records']} records of the seeded unit BAM; htslib 1.23 (zlib) sam_read1 + bam_reader.c conversions, "
+                      f"hts_set_threads({threads})"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="inflate", choices=["inflate"])
-    ap.add_argument("--target-gb", type=float, default=10.0, help="compressed GB per GPU (BASELINE config 2: 10 GB)")
+    ap.add_argument("--records", type=float, default=100e6, help="records per GPU (BASELINE configs[2]: 100M)")
     ap.add_argument("--unit-records", type=int, default=4000000)
     ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x9E3779B97F4A7C15)
     args = ap.parse_args()
@@ -202,29 +215,28 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     ncpu = os.cpu_count() or 1
+    config = {"workload": WORKLOAD, "records_per_gpu_target": int(args.records),
+              "input": f"seeded unit ({args.unit_records} paired 2x150 records, 22 contigs, written by the reference htslib at BGZF level 6) "
+                       "with its record blocks tiled to the target size", "sharding": "contiguous virtual-offset range per GPU, no collective"}
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        unit_path = gen_unit("bgzf", args.unit_records, args.seed, True, ncpu)
-        unit_out = 0
-        res = []
-        limit = int(3e9)
-        for _ in range(args.warmup):
-            run_ref_bench("bgunzip", unit_path, ncpu, int(2e8))
-        for _ in range(args.steps):
-            res.append(run_ref_bench("bgunzip", unit_path, ncpu, limit))
+        unit_path = gen_unit("bam", args.unit_records, args.seed, True, ncpu)
+        limit = 2000000
+        for _ in range(min(args.warmup, 1)):
+            run_ref_bench("sam_read1", unit_path, ncpu, 200000)
+        res = [run_ref_bench("sam_read1", unit_path, ncpu, limit) for _ in range(args.steps)]
         secs = sum(r["seconds"] for r in res)
-        outb = sum(r["bytes_out"] for r in res)
-        v = outb / 1e9 / secs
-        sample = f"first {res[0]['bytes_out'] / 1e9:.2f} GB (inflated) of the seeded unit per step; htslib 1.23 (zlib) bgzf_mt({ncpu})"
-        line = {"impl": "reference", "metric": "bgzf_inflate_decompressed_GBps", "value": v, "unit": "GB/s", "n_gpus": args.gpus,
+        recs = sum(r["records"] for r in res)
+        v = recs / 1e6 / secs
+        cb = {"value": v, "unit": "Mrecords/s", "cores": ncpu, "kind": "reference",
+              "sample": f"first {res[0]['records']} records of the seeded unit BAM per step; htslib 1.23 (zlib) sam_read1 + "
+                        f"src/bam_reader.c column conversions, hts_set_threads({ncpu})"}
+        line = {"impl": "reference", "metric": "read_bam_Mrecords_per_s", "value": v, "unit": "Mrecords/s", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "bgunzip-equivalent raw BGZF inflate, 10 GB synthetic BGZF (BASELINE configs[1]); bounded sample",
-                           "compressed_gb_per_gpu": args.target_gb},
-                "cpu_baseline": {"value": v, "unit": "GB/s decompressed", "cores": ncpu, "kind": "reference", "sample": sample},
-                "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config, "cpu_baseline": cb,
+                "e2e": {"value": v, "unit": "Mrecords/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
         print(json.dumps(line), flush=True)
         return 0
 
@@ -232,6 +244,7 @@ def main():
     import torch.distributed as dist
 
     import duckhts_b200 as dh
+    from duckhts_b200.bgzf import PinnedBuffer  # noqa: F401
 
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -243,95 +256,125 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(local_rank)
 
-    def max_over_ranks(x):
+    def reduce(x, op):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=op)
         return float(t.item())
 
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    rmax = lambda x: reduce(x, dist.ReduceOp.MAX) if world > 1 else x  # noqa: E731
+    rsum = lambda x: reduce(x, dist.ReduceOp.SUM) if world > 1 else x  # noqa: E731
 
     torch.cuda.set_device(local_rank)
     if rank == 0:
-        unit_path = gen_unit("bgzf", args.unit_records, args.seed, True, ncpu)
+        gen_unit("bam", args.unit_records, args.seed, True, ncpu)
     barrier()
-    unit_path = gen_unit("bgzf", args.unit_records, args.seed, True, ncpu)
+    unit_path = gen_unit("bam", args.unit_records, args.seed, True, ncpu)
     unit = np.fromfile(unit_path, dtype=np.uint8)
 
     ctx = dh.Context(local_rank)
-    # weak scaling: every rank owns its own contiguous offset range of target_gb compressed bytes
-    pin, reps = tile_image(dh, unit, int(args.target_gb * 1e9))
-    img = pin.array
+    with dh.BamFile(ctx, unit) as ub:   # where do the alignment blocks start, how many records does the unit hold
+        first_voff = ub.first_voffset
+        ub.set_projection(0, ())
+        ub.scan_begin()
+        unit_rows = ub.drain()
+    blocks, _ = dh.bgzf_walk(unit)
+    header_blocks = next(i for i, b in enumerate(blocks) if b[0] == first_voff >> 16)
+    assert first_voff & 0xffff == 0, "htslib flushes after the header: first record starts a block"
+    body_bytes = blocks[-1][0] - blocks[header_blocks][0]
+    reps = max(1, int(round(args.records / unit_rows)))
+    pin, reps = tile_image(dh, unit, reps * body_bytes, header_blocks=header_blocks)
     h2d_gbs, d2h_gbs = ctx.measure_pcie(1 << 30)
+    bf = dh.BamFile(ctx, pin)
+    bf.set_projection(None, TAGS)
 
-    # ---- device-resident: `value` and the roofline of the inflate kernel -------------------------------------
-    dev = dh.BgzfDevice(ctx, pin)
-    comp_bytes, out_bytes, nblocks = dev.comp_bytes, dev.out_bytes, dev.nblocks
+    def scan_once():
+        bf.scan_begin()
+        rows = bf.drain()
+        return rows, bf.stats()
+
+    # ---- value: compressed image resident in HBM, columns left in HBM; CUDA events on the kernels' stream --------
+    bf.set_mode(device_input=True, device_output=True)
     for _ in range(args.warmup):
-        dev.inflate()
-    ctx.sync()
-    rcw, bb, bc = dev.check()
-    assert rcw == 0, f"inflate verdict failed at block {bb} code {bc}"
+        rows, st = scan_once()
+    assert st.status == 0 and rows == reps * unit_rows, (st.status, rows, reps * unit_rows)
     barrier()
     with ClockSampler(local_rank) as clk:
         launches0 = ctx.launches
         ctx.timer_start()
+        kms = [0.0, 0.0, 0.0]
         for _ in range(args.steps):
-            dev.inflate()
+            rows, st = scan_once()
+            kms = [kms[0] + st.inflate_ms, kms[1] + st.walk_ms, kms[2] + st.decode_ms]
         ms = ctx.timer_stop()
+        launches = ctx.launches - launches0
         barrier()
-    k_launches = ctx.launches - launches0        # kernels launched inside the timed region
-    ms = max_over_ranks(ms)
+    ms = rmax(ms)
     ms_per_step = ms / args.steps
-    total_out = sum_over_ranks(float(out_bytes))
-    value = total_out / 1e9 / (ms_per_step / 1e3)
-    kernel_ms = ms / max(k_launches, 1)          # per-launch average (the step is nothing but this kernel)
-    alg_bytes = (comp_bytes + out_bytes) / max(k_launches // args.steps, 1)
-    peak, peak_src = measured_peaks()
-    achieved = alg_bytes / 1e9 / (kernel_ms / 1e3)
-    dev.free()
+    total_rows = rsum(float(rows))
+    value = total_rows / 1e6 / (ms_per_step / 1e3)
+    comp_bytes, out_bytes, nblocks = st.h2d_bytes, st.inflated_bytes, st.n_blocks
+    comp_bytes = pin.nbytes
 
-    # ---- e2e: host (pinned) -> host (pinned) through dh_bgzf_inflate_host --------------------------------------
-    from duckhts_b200.bgzf import PinnedBuffer
-
-    outpin = PinnedBuffer(out_bytes)
-    e2e_ms = []
-    for it in range(min(args.warmup, 1) + args.steps):
+    # ---- e2e: pinned host image in, DuckDB-layout column batches in pinned host memory out -------------------------
+    bf.set_mode(device_input=False, device_output=False)
+    e2e_ms, d2h_bytes, h2d_bytes = [], 0, 0
+    for it in range(1 + args.steps):
         barrier()
         t0 = time.perf_counter()
-        _, st = dh.bgzf_inflate(ctx, pin, out=outpin)
+        rows, st = scan_once()
         wall = (time.perf_counter() - t0) * 1e3
-        if it >= min(args.warmup, 1):
-            e2e_ms.append(max_over_ranks(max(wall, st.total_ms)))
+        if it >= 1:
+            e2e_ms.append(rmax(wall))
+            d2h_bytes, h2d_bytes = st.d2h_bytes, st.h2d_bytes
     e2e_step = float(np.mean(e2e_ms))
-    e2e_val = total_out / 1e9 / (e2e_step / 1e3)
+    e2e_val = total_rows / 1e6 / (e2e_step / 1e3)
+    bf.close()
 
-    line = None
+    # ---- the dominant kernel alone (BGZF inflate of the same bytes, device-resident): roofline + inflate GB/s -------
+    dev = dh.BgzfDevice(ctx, pin)
+    ib_comp, ib_out = dev.comp_bytes, dev.out_bytes
+    for _ in range(args.warmup):
+        dev.inflate()
+    ctx.sync()
+    assert dev.check()[0] == 0
+    barrier()
+    l0 = ctx.launches
+    ctx.timer_start()
+    for _ in range(args.steps):
+        dev.inflate()
+    ims = rmax(ctx.timer_stop())
+    k_inf = ctx.launches - l0
+    dev.free()
+    inflate_gbs = rsum(float(ib_out)) / 1e9 / (ims / args.steps / 1e3)
+    peak, peak_src = measured_peaks()
+    alg_bytes = (ib_comp + ib_out) * args.steps / max(k_inf, 1)
+    kernel_ms = ims / max(k_inf, 1)
+    achieved = alg_bytes / 1e9 / (kernel_ms / 1e3)
+
     if rank == 0:
-        cpu = cpu_baseline_inflate(unit_path, ncpu, int(3e9)) if world == 1 else None
-        clocks = clk.summary()
-        line = {"metric": "bgzf_inflate_decompressed_GBps", "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "bgunzip-equivalent raw BGZF inflate, 10 GB synthetic BGZF (BASELINE configs[1])",
-                           "compressed_gb_per_gpu": comp_bytes / 1e9, "inflated_gb_per_gpu": out_bytes / 1e9,
-                           "bgzf_blocks_per_gpu": nblocks,
-                           "input": f"seeded unit ({args.unit_records} paired 2x150 records' BAM stream via bgzf_write, htslib level 6) tiled x{reps}",
-                           "l2": "inputs (>=10 GB) far exceed the 126 MB L2; no flush needed", "sharding": "offset-range per GPU, no collective"},
+        cpu = cpu_baseline_read_bam(unit_path, ncpu, 2000000) if world == 1 else None
+        rec_c = comp_bytes / rows
+        config.update({"records_per_gpu": int(rows), "compressed_gb_per_gpu": comp_bytes / 1e9, "inflated_gb_per_gpu": ib_out / 1e9,
+                       "bgzf_blocks_per_gpu": int(nblocks), "tiles": reps, "compressed_bytes_per_record": rec_c,
+                       "l2": "inputs (>= 10 GB per GPU) far exceed the 126 MB L2; no flush needed"})
+        line = {"metric": "read_bam_Mrecords_per_s", "value": value, "unit": "Mrecords/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u8", "data": "synthetic", "config": config,
+                "kernel_ms_per_step": {"bgzf_inflate": kms[0] / args.steps, "bam_walk": kms[1] / args.steps, "bam_decode": kms[2] / args.steps},
+                "inflate": {"metric": "bgzf_inflate_decompressed_GBps", "value": inflate_gbs, "unit": "GB/s",
+                            "ms_per_step": ims / args.steps, "compressed_gb": ib_comp / 1e9, "inflated_gb": ib_out / 1e9,
+                            "pcie_ingest_bound_GBps": h2d_gbs * ib_out / ib_comp},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "kernel": "bgzf_inflate_kernel", "algorithmic_bytes_per_launch": alg_bytes,
                              "peak_source": peak_src, "kernel_ms": kernel_ms},
-                "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": comp_bytes, "d2h_bytes_per_step": out_bytes,
+                "e2e": {"value": e2e_val, "unit": "Mrecords/s", "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
                         "ms_per_step": e2e_step, "pcie_h2d_gbs": h2d_gbs, "pcie_d2h_gbs": d2h_gbs,
-                        "pcie_ingest_roofline_frac": (comp_bytes / 1e9 / (e2e_step / 1e3)) / h2d_gbs,
-                        "pcie_return_roofline_frac": (out_bytes / 1e9 / (e2e_step / 1e3)) / d2h_gbs},
-                "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": k_launches, "host_cores": ncpu}
+                        "pcie_ingest_roofline_Mrec_s": h2d_gbs * 1e3 / rec_c,
+                        "pcie_ingest_roofline_frac": e2e_val / (h2d_gbs * 1e3 / rec_c),
+                        "pcie_return_roofline_frac": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / d2h_gbs},
+                "cpu_baseline": cpu, "clocks": clk.summary(), "gpu_launches": int(launches), "host_cores": ncpu}
         print(json.dumps(line), flush=True)
     barrier()
     ctx.close()

@@ -75,6 +75,7 @@ SIGNATURES = {
     "dh_bam_n_blocks": (C.c_uint64, [C.c_void_p]),
     "dh_bam_set_projection": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(TagReq), C.c_int]),
     "dh_bam_configure": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64]),
+    "dh_bam_set_mode": (C.c_int, [C.c_void_p, C.c_uint32]),
     "dh_bam_scan_begin": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64]),
     "dh_bam_next_batch": (C.c_int, [C.c_void_p, C.POINTER(BamBatch)]),
     "dh_bam_scan_stats_get": (C.c_int, [C.c_void_p, C.POINTER(BamScanStats)]),

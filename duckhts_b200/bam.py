@@ -98,6 +98,9 @@ class BamFile:
     def configure(self, seg_comp=0, batch_rows=0, carry=0):
         check(lib().dh_bam_configure(self.h, seg_comp, batch_rows, carry), "dh_bam_configure")
 
+    def set_mode(self, device_input=False, device_output=False):
+        check(lib().dh_bam_set_mode(self.h, (1 if device_input else 0) | (2 if device_output else 0)), "dh_bam_set_mode")
+
     def split(self, n_parts):
         v = (C.c_uint64 * (n_parts + 1))()
         check(lib().dh_bam_split(self.h, n_parts, v), "dh_bam_split")

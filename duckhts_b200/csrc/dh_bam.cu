@@ -66,6 +66,8 @@ struct dh_bam {
     std::vector<RgEntry> rg;
     std::string rg_ids;
     DevBuf d_ref_cells, d_rg, d_rg_ids, d_tags;
+    DevBuf d_image;                // whole compressed image staged in HBM (DH_BAM_DEVICE_INPUT)
+    uint32_t mode = 0;
     // projection
     uint64_t col_mask = (1ull << BAM_CORE_COLS) - 1;
     std::vector<TagReq> tags;
@@ -296,7 +298,8 @@ int issue_inflate(dh_bam *b, int k) {
     int rc;
     // the slot's previous tenant (segment k - NSEG) has finished on the compute stream before anything here runs:
     // its kernels were all enqueued on s_comp earlier, and the copy stream waits for its last inflate below.
-    if ((rc = s.comp.reserve(cbytes + DH_COMP_PAD)) != DH_OK) return rc;
+    const bool staged = (b->mode & DH_BAM_DEVICE_INPUT) && b->d_image.p;
+    if (!staged && (rc = s.comp.reserve(cbytes + DH_COMP_PAD)) != DH_OK) return rc;
     if ((rc = s.out.reserve(b->carry_cap + s.obytes + 2 * BGZF_MAX_OUT)) != DH_OK) return rc;
     if ((rc = s.desc.reserve(nblk * sizeof(BlockDesc))) != DH_OK) return rc;
     if ((rc = s.status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
@@ -314,19 +317,22 @@ int issue_inflate(dh_bam *b, int k) {
     }
     cudaStream_t sc = s_copy(b), sk = s_comp(b);
     DH_CUDA(cudaStreamWaitEvent(sc, s.ev_inf1, 0));  // previous inflate from this comp buffer is done (no-op if never recorded)
-    DH_CUDA(cudaMemcpyAsync(s.comp.p, b->data + s.cbase, cbytes, cudaMemcpyHostToDevice, sc));
-    DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + cbytes, 0, DH_COMP_PAD, sc));
+    if (!staged) {
+        DH_CUDA(cudaMemcpyAsync(s.comp.p, b->data + s.cbase, cbytes, cudaMemcpyHostToDevice, sc));
+        DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + cbytes, 0, DH_COMP_PAD, sc));
+    }
     DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, nblk * sizeof(BlockDesc), cudaMemcpyHostToDevice, sc));
     DH_CUDA(cudaEventRecord(s.ev_h2d, sc));
     DH_CUDA(cudaStreamWaitEvent(sk, s.ev_h2d, 0));
     DH_CUDA(cudaEventRecord(s.ev_inf0, sk));
-    DH_CUDA(launch_bgzf_inflate((const uint8_t *)s.comp.p, (const BlockDesc *)s.desc.p, (uint32_t)nblk, (uint8_t *)s.out.p,
+    const uint8_t *comp_ptr = staged ? (const uint8_t *)b->d_image.p + s.cbase : (const uint8_t *)s.comp.p;
+    DH_CUDA(launch_bgzf_inflate(comp_ptr, (const BlockDesc *)s.desc.p, (uint32_t)nblk, (uint8_t *)s.out.p,
                                 (int *)s.status.p, (unsigned int *)b->ctx->counter.p + 8 + (k % NSEG), b->ctx->sm_count, sk));
     b->ctx->launches++;
     DH_CUDA(cudaEventRecord(s.ev_inf1, sk));
     DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, nblk * sizeof(int), cudaMemcpyDeviceToHost, sk));
     s.issued_for = k;
-    b->st.h2d_bytes += cbytes + nblk * sizeof(BlockDesc);
+    b->st.h2d_bytes += (staged ? 0 : cbytes) + nblk * sizeof(BlockDesc);
     b->st.inflated_bytes += s.obytes;
     b->st.n_blocks += nblk;
     return DH_OK;
@@ -554,7 +560,8 @@ int issue_batch(dh_bam *b) {
     b->ctx->launches++;
     DH_CUDA(cudaEventRecord(o.ev_k1, sk));
     DH_CUDA(cudaStreamWaitEvent(sd, o.ev_k1, 0));
-    if (total) DH_CUDA(cudaMemcpyAsync(o.h_arena.p, o.arena.p, total, cudaMemcpyDeviceToHost, sd));
+    const bool keep = (b->mode & DH_BAM_DEVICE_OUTPUT) != 0;
+    if (total && !keep) DH_CUDA(cudaMemcpyAsync(o.h_arena.p, o.arena.p, total, cudaMemcpyDeviceToHost, sd));
     DH_CUDA(cudaEventRecord(o.ev_done, sd));
     o.timed = true;
     o.desc.n_rows = bb.rows;
@@ -564,7 +571,7 @@ int issue_batch(dh_bam *b) {
     o.desc.heap = (const uint8_t *)o.h_arena.p + heap_off;
     o.desc.heap_bytes = bb.heap;
     o.desc.bytes = total;
-    b->st.d2h_bytes += total;
+    b->st.d2h_bytes += keep ? 0 : total;
     b->inflight.push_back(b->issued);
     b->issued++;
     return DH_OK;
@@ -628,7 +635,7 @@ void dh_bam_close(dh_bam *b) {
         s.arena.release(); s.h_arena.release();
         for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_done}) if (e) cudaEventDestroy(e);
     }
-    b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release();
+    b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release(); b->d_image.release();
     delete b;
 }
 
@@ -679,6 +686,20 @@ int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, ui
         b->carry_cap = (carry_bytes + 255) & ~255ull;
         for (auto &s : b->ss) { s.out.release(); s.issued_for = -1; }
     }
+    return DH_OK;
+}
+
+int dh_bam_set_mode(dh_bam *b, uint32_t flags) {
+    if (!b) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    if ((flags & DH_BAM_DEVICE_INPUT) && !b->d_image.p) {
+        int rc = b->d_image.reserve(b->bt.end_off + DH_COMP_PAD + 16);
+        if (rc != DH_OK) return rc;
+        DH_CUDA(cudaMemcpy(b->d_image.p, b->data, b->bt.end_off, cudaMemcpyHostToDevice));
+        DH_CUDA(cudaMemset((uint8_t *)b->d_image.p + b->bt.end_off, 0, DH_COMP_PAD));
+    }
+    if (!(flags & DH_BAM_DEVICE_INPUT)) b->d_image.release();
+    b->mode = flags;
     return DH_OK;
 }
 

@@ -136,6 +136,14 @@ int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, 
  * records that straddle segments.  Small values exercise the multi-segment paths in tests. */
 int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, uint64_t carry_bytes);
 
+/* Measurement modes (bench.py `value`): DH_BAM_DEVICE_INPUT stages the whole compressed image in HBM once, so
+ * scans read it from there instead of copying segments host->device; DH_BAM_DEVICE_OUTPUT leaves each batch in
+ * the device arena (no device->host copy; the batch's host pointers are then NOT filled).  Default 0: host in,
+ * host out. */
+#define DH_BAM_DEVICE_INPUT 1u
+#define DH_BAM_DEVICE_OUTPUT 2u
+int dh_bam_set_mode(dh_bam *b, uint32_t flags);
+
 /* Start a scan over the records that START at virtual offsets in [voff_beg, voff_end) (bgzf virtual offset =
  * coffset << 16 | uoffset, htslib/bgzf.h:261).  voff_beg = 0 means "first record"; voff_end = UINT64_MAX means
  * "to EOF".  voff_beg must be a record boundary (first record, a BAI chunk start, or a dh_bam_split boundary).
