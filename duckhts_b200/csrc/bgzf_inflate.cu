@@ -243,7 +243,7 @@ __device__ __forceinline__ uint32_t group_crc32(const CtaSmem *cs, const uint8_t
 
 __global__ void __launch_bounds__(CTA_THREADS, 1)
 bgzf_inflate_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, uint32_t nblocks,
-                    uint8_t *__restrict__ outbuf, int *__restrict__ status, unsigned int *__restrict__ counter) {
+                    uint8_t *__restrict__ outbuf, int *__restrict__ status, unsigned int *__restrict__ counter, int only_flagged) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     CtaSmem *cs = reinterpret_cast<CtaSmem *>(smem_raw);
 
@@ -277,6 +277,7 @@ bgzf_inflate_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
         if (lane == 0) b = atomicAdd(counter, 1u);
         b = __shfl_sync(gmask, b, 0, G);
         if (b >= nblocks) break;
+        if (only_flagged && status[b] != INF_NEEDS_V1) continue;  // filter mode: redo what the lockstep kernel passed on
         const BlockDesc d = blocks[b];
 
         io.payload = comp + d.in_off;
@@ -304,7 +305,7 @@ bgzf_inflate_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
 }
 
 cudaError_t launch_bgzf_inflate(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out,
-                                int *status, unsigned int *counter, int sm_count, cudaStream_t stream) {
+                                int *status, unsigned int *counter, int sm_count, cudaStream_t stream, bool only_flagged) {
     static bool configured = false;
     const size_t smem = sizeof(CtaSmem);
     if (!configured) {
@@ -319,7 +320,7 @@ cudaError_t launch_bgzf_inflate(const uint8_t *comp, const BlockDesc *blocks, ui
     // persistent: one CTA per SM; fewer if there is not enough work for every lane-group
     uint32_t ctas = (nblocks + GROUPS - 1) / GROUPS;
     if (ctas > (uint32_t)sm_count) ctas = (uint32_t)sm_count;
-    bgzf_inflate_kernel<<<ctas, CTA_THREADS, smem, stream>>>(comp, blocks, nblocks, out, status, counter);
+    bgzf_inflate_kernel<<<ctas, CTA_THREADS, smem, stream>>>(comp, blocks, nblocks, out, status, counter, only_flagged ? 1 : 0);
     return cudaGetLastError();
 }
 

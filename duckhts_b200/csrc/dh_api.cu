@@ -2,6 +2,7 @@
 // Declarations and the reference interfaces each one replaces: include/duckhts_cuda.h.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -91,10 +92,9 @@ int walk_blocks(const uint8_t *data, uint64_t size, uint64_t start, BlockTable &
     return DH_OK;
 }
 
-// Build device block descriptors for blocks [b0,b1) whose compressed bytes were uploaded starting at
-// file offset `comp_base` (16-byte aligned) and whose output buffer starts at inflated offset `out_base`.
-static void fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_base, uint64_t out_base,
-                       BlockDesc *d) {
+uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_base, size_t out_b0, uint64_t out_bias,
+                    BlockDesc *d) {
+    uint64_t words = 0;
     for (size_t i = b0; i < b1; ++i) {
         const dh_bgzf_block &b = bt.blocks[i];
         BlockDesc &o = d[i - b0];
@@ -102,8 +102,27 @@ static void fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp
         o.in_len = b.csize - 26;
         o.isize = b.isize;
         o.crc = b.crc;
-        o.out_off = bt.uoff[i] - out_base;
+        o.out_off = out_bias + (bt.uoff[i] - bt.uoff[out_b0]);
+        o.cmd_off = words;
+        words += cmd_words_for(b.isize);
     }
+    return words;
+}
+
+int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
+                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream) {
+    static const bool force_v1 = getenv("DH_INFLATE_V1") != nullptr;
+    if (force_v1) {
+        DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter, c->sm_count, stream, false));
+        c->launches += 1;
+        return DH_OK;
+    }
+    int rc = work.reserve(inflate_work_bytes(n, cmd_words));
+    if (rc != DH_OK) return rc;
+    DH_CUDA(launch_bgzf_inflate_v2(comp, descs, n, out, status, (uint32_t *)work.p, counter, c->sm_count, stream));
+    DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, stream, true));
+    c->launches += 3;
+    return DH_OK;
 }
 
 }  // namespace dh
@@ -160,7 +179,7 @@ void dh_ctx_destroy(dh_ctx *c) {
     cudaDeviceSynchronize();
     for (int i = 0; i < 3; ++i) {
         auto &s = c->slots[i];
-        s.comp.release(); s.out.release(); s.desc.release(); s.status.release();
+        s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release();
         s.h_desc.release(); s.h_status.release();
         if (s.ev_k0) cudaEventDestroy(s.ev_k0);
         if (s.ev_k1) cudaEventDestroy(s.ev_k1);
@@ -289,15 +308,14 @@ int dh_bgzf_inflate_host(dh_ctx *c, const uint8_t *comp, uint64_t comp_size, uin
         if ((rc = s.status.reserve((e - b) * sizeof(int))) != DH_OK) break;
         if ((rc = s.h_desc.reserve((e - b) * sizeof(BlockDesc))) != DH_OK) break;
         if ((rc = s.h_status.reserve((e - b) * sizeof(int))) != DH_OK) break;
-        fill_descs(bt, b, e, cbase, bt.uoff[b], (BlockDesc *)s.h_desc.p);
+        const uint64_t cw = fill_descs(bt, b, e, cbase, b, 0, (BlockDesc *)s.h_desc.p);
         DH_CUDA(cudaMemcpyAsync(s.comp.p, comp + cbase, cbytes, cudaMemcpyHostToDevice, strm));
         DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + cbytes, 0, DH_COMP_PAD, strm));
         DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, (e - b) * sizeof(BlockDesc), cudaMemcpyHostToDevice, strm));
         DH_CUDA(cudaEventRecord(s.ev_k0, strm));
-        DH_CUDA(launch_bgzf_inflate((const uint8_t *)s.comp.p, (const BlockDesc *)s.desc.p, (uint32_t)(e - b),
-                                    (uint8_t *)s.out.p, (int *)s.status.p, (unsigned int *)c->counter.p + 1 + slot,
-                                    c->sm_count, strm));
-        c->launches++;
+        if ((rc = inflate_blocks(c, (const uint8_t *)s.comp.p, (const BlockDesc *)s.desc.p, (uint32_t)(e - b), cw, (uint8_t *)s.out.p,
+                                 (int *)s.status.p, s.work, (unsigned int *)c->counter.p + 2 + 2 * slot, strm)) != DH_OK)
+            break;
         DH_CUDA(cudaEventRecord(s.ev_k1, strm));
         if (out && obytes) DH_CUDA(cudaMemcpyAsync(out + bt.uoff[b], s.out.p, obytes, cudaMemcpyDeviceToHost, strm));
         DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, (e - b) * sizeof(int), cudaMemcpyDeviceToHost, strm));
@@ -332,8 +350,8 @@ int dh_bgzf_inflate_host(dh_ctx *c, const uint8_t *comp, uint64_t comp_size, uin
 struct dh_bgzf_dev {
     dh_ctx *ctx;
     BlockTable bt;
-    DevBuf comp, out, desc, status;
-    struct Seg { size_t b0, b1; uint64_t cbase; };
+    DevBuf comp, out, desc, status, work;
+    struct Seg { size_t b0, b1; uint64_t cbase, cmd_words; };
     std::vector<Seg> segs;
 };
 
@@ -359,9 +377,10 @@ dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size
     while (b < nb) {
         size_t e = b;
         uint64_t cbase = d->bt.blocks[b].coffset & ~15ull;
-        while (e < nb && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
-        fill_descs(d->bt, b, e, cbase, 0, descs.data() + b);
-        d->segs.push_back({b, e, cbase});
+        // a launch covers at most 2 GiB of compressed bytes (32-bit in_off) and 2^17 blocks (bounded work buffer)
+        while (e < nb && e - b < (1u << 17) && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
+        const uint64_t cw = fill_descs(d->bt, b, e, cbase, 0, 0, descs.data() + b);
+        d->segs.push_back({b, e, cbase, cw});
         b = e;
     }
     cudaError_t e1 = cudaMemcpy(d->comp.p, comp, cbytes, cudaMemcpyHostToDevice);
@@ -379,7 +398,7 @@ void dh_bgzf_dev_free(dh_bgzf_dev *d) {
     if (!d) return;
     cudaSetDevice(d->ctx->device);
     cudaStreamSynchronize(d->ctx->stream);
-    d->comp.release(); d->out.release(); d->desc.release(); d->status.release();
+    d->comp.release(); d->out.release(); d->desc.release(); d->status.release(); d->work.release();
     delete d;
 }
 uint64_t dh_bgzf_dev_nblocks(const dh_bgzf_dev *d) { return d ? d->bt.blocks.size() : 0; }
@@ -391,10 +410,10 @@ int dh_bgzf_dev_inflate(dh_bgzf_dev *d) {
     dh_ctx *c = d->ctx;
     DH_CUDA(cudaSetDevice(c->device));
     for (auto &s : d->segs) {
-        DH_CUDA(launch_bgzf_inflate((const uint8_t *)d->comp.p + s.cbase, (const BlockDesc *)d->desc.p + s.b0,
-                                    (uint32_t)(s.b1 - s.b0), (uint8_t *)d->out.p, (int *)d->status.p + s.b0,
-                                    (unsigned int *)c->counter.p, c->sm_count, c->stream));
-        c->launches++;
+        int rc = inflate_blocks(c, (const uint8_t *)d->comp.p + s.cbase, (const BlockDesc *)d->desc.p + s.b0, (uint32_t)(s.b1 - s.b0),
+                                s.cmd_words, (uint8_t *)d->out.p, (int *)d->status.p + s.b0, d->work, (unsigned int *)c->counter.p,
+                                c->stream);
+        if (rc != DH_OK) return rc;
     }
     return DH_OK;
 }

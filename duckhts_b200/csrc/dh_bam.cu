@@ -29,7 +29,7 @@ struct Batch {           // one output batch of the current segment
 };
 
 struct SegSlot {
-    DevBuf comp, out, desc, status, blk_start, entry, todo, walk, row_base, heap_base;
+    DevBuf comp, out, desc, status, work, blk_start, entry, todo, walk, row_base, heap_base;
     PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base;
     cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_walk0 = nullptr, ev_walk1 = nullptr;
     size_t b0 = 0, b1 = 0;  // file block range
@@ -73,7 +73,7 @@ struct dh_bam {
     std::vector<TagReq> tags;
     ScanTables tabs;
     // knobs
-    uint64_t seg_comp = 256ull << 20;
+    uint64_t seg_comp = 1024ull << 20;
     uint32_t batch_rows = 1u << 20;
     uint64_t carry_cap = 8ull << 20;
     // scan state
@@ -305,16 +305,7 @@ int issue_inflate(dh_bam *b, int k) {
     if ((rc = s.status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
     if ((rc = s.h_desc.reserve(nblk * sizeof(BlockDesc))) != DH_OK) return rc;
     if ((rc = s.h_status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
-    BlockDesc *d = (BlockDesc *)s.h_desc.p;
-    for (size_t i = sg.b0; i < sg.b1; ++i) {
-        const dh_bgzf_block &bl = bt.blocks[i];
-        BlockDesc &o = d[i - sg.b0];
-        o.in_off = (uint32_t)(bl.coffset + 18 - s.cbase);
-        o.in_len = bl.csize - 26;
-        o.isize = bl.isize;
-        o.crc = bl.crc;
-        o.out_off = b->carry_cap + (bt.uoff[i] - bt.uoff[sg.b0]);
-    }
+    const uint64_t cw = fill_descs(bt, sg.b0, sg.b1, s.cbase, sg.b0, b->carry_cap, (BlockDesc *)s.h_desc.p);
     cudaStream_t sc = s_copy(b), sk = s_comp(b);
     DH_CUDA(cudaStreamWaitEvent(sc, s.ev_inf1, 0));  // previous inflate from this comp buffer is done (no-op if never recorded)
     if (!staged) {
@@ -326,9 +317,9 @@ int issue_inflate(dh_bam *b, int k) {
     DH_CUDA(cudaStreamWaitEvent(sk, s.ev_h2d, 0));
     DH_CUDA(cudaEventRecord(s.ev_inf0, sk));
     const uint8_t *comp_ptr = staged ? (const uint8_t *)b->d_image.p + s.cbase : (const uint8_t *)s.comp.p;
-    DH_CUDA(launch_bgzf_inflate(comp_ptr, (const BlockDesc *)s.desc.p, (uint32_t)nblk, (uint8_t *)s.out.p,
-                                (int *)s.status.p, (unsigned int *)b->ctx->counter.p + 8 + (k % NSEG), b->ctx->sm_count, sk));
-    b->ctx->launches++;
+    if ((rc = inflate_blocks(b->ctx, comp_ptr, (const BlockDesc *)s.desc.p, (uint32_t)nblk, cw, (uint8_t *)s.out.p, (int *)s.status.p,
+                             s.work, (unsigned int *)b->ctx->counter.p + 16 + 2 * (k % NSEG), sk)) != DH_OK)
+        return rc;
     DH_CUDA(cudaEventRecord(s.ev_inf1, sk));
     DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, nblk * sizeof(int), cudaMemcpyDeviceToHost, sk));
     s.issued_for = k;
@@ -625,7 +616,7 @@ void dh_bam_close(dh_bam *b) {
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
     for (auto &s : b->ss) {
-        s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.blk_start.release(); s.entry.release();
+        s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release(); s.blk_start.release(); s.entry.release();
         s.todo.release(); s.walk.release(); s.row_base.release(); s.heap_base.release();
         s.h_desc.release(); s.h_status.release(); s.h_blk_start.release(); s.h_entry.release(); s.h_todo.release();
         s.h_walk.release(); s.h_row_base.release(); s.h_heap_base.release();

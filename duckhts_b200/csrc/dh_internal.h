@@ -44,6 +44,16 @@ struct BlockTable {
 // walk data[start..size); returns DH_OK / DH_EFORMAT (bad header at *bad_off)
 int walk_blocks(const uint8_t *data, uint64_t size, uint64_t start, BlockTable &bt, uint64_t *bad_off);
 
+// Device block descriptors for blocks [b0,b1): compressed bytes were uploaded starting at file offset `comp_base`
+// (16-byte aligned); block i's bytes go to out + out_bias + (uoff[i] - uoff[out_b0]).  Returns the command words the
+// lockstep kernel's work buffer needs for these blocks.
+uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_base, size_t out_b0, uint64_t out_bias,
+                    BlockDesc *d);
+// Inflate `n` described blocks on `stream`: lockstep kernels (phase 1 + 2), then the lane-group kernel in filter mode
+// for blocks the compact tables could not hold.  `work` is grown as needed.  counter: >= 2 device words.
+int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
+                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream);
+
 }  // namespace dh
 
 struct dh_ctx {
@@ -57,7 +67,7 @@ struct dh_ctx {
     uint64_t launches = 0;
     // pipeline slots of dh_bgzf_inflate_host
     struct Slot {
-        dh::DevBuf comp, out, desc, status;
+        dh::DevBuf comp, out, desc, status, work;
         dh::PinBuf h_desc, h_status;
         cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
     } slots[3];

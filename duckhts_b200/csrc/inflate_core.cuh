@@ -75,7 +75,8 @@ enum : int {
     INF_ERR_IN_OVERRUN = 13,    // stream runs past the compressed payload (zlib: Z_BUF_ERROR)
     INF_ERR_ISIZE = 14,         // inflated length != ISIZE footer (stricter than the reference)
     INF_ERR_CRC = 15,           // CRC-32 of output != footer (htslib BGZF_ERR_CRC)
-    INF_ERR_HEADER = 16         // bad BGZF header (htslib BGZF_ERR_HEADER); set by host framing
+    INF_ERR_HEADER = 16,        // bad BGZF header (htslib BGZF_ERR_HEADER); set by host framing
+    INF_NEEDS_V1 = 100          // internal: lockstep kernel's compact tables too small; redone by the lane-group kernel
 };
 
 // ---- small helpers ---------------------------------------------------------------------------
