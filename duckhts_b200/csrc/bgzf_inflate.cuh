@@ -16,14 +16,20 @@ struct BlockDesc {
     uint32_t isize;    // ISIZE footer: expected inflated length
     uint32_t crc;      // CRC-32 footer
     uint64_t out_off;  // where the block's bytes go in the inflated buffer (prefix sum of ISIZE)
-    uint64_t cmd_off;  // lockstep kernel: first word of the block's match-command area inside the work buffer
+    uint64_t cmd_off;  // lockstep kernels: byte offset of the block's literal/command area inside the work buffer
 };
 
-// match-command words a block of `isize` inflated bytes can need: one per match (>= 3 bytes each) + one skip word per
-// literal run longer than 255 bytes
-inline uint64_t cmd_words_for(uint32_t isize) { return (uint64_t)isize / 3u + (uint64_t)isize / 256u + 4u; }
-// work-buffer bytes for a launch over `nblocks` blocks whose command areas total `cmd_words`
-inline size_t inflate_work_bytes(uint32_t nblocks, uint64_t cmd_words) { return ((size_t)((nblocks + 63u) & ~63u) + cmd_words) * 4u; }
+// Lockstep kernels, work area of one block of `isize` inflated bytes: the literal stream grows upwards from the start,
+// the command stream (one 32-bit word per match, one per 255-literal run) downwards from the end.  With L literal
+// bytes and M matches, L + 3M <= isize, so L + 4M + 4(L/255 + 1) <= 4/3 isize + 4; 64 bytes of slack, 16-byte aligned.
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline uint32_t inflate_work_cap(uint32_t isize) { return (isize + isize / 3u + 64u + 15u) & ~15u; }
+// the per-block command counts sit in front of the areas
+inline size_t inflate_work_header(uint32_t nblocks) { return (size_t)((nblocks + 63u) & ~63u) * 4u; }
+// work-buffer bytes for a launch over `nblocks` blocks whose areas total `area_bytes`
+inline size_t inflate_work_bytes(uint32_t nblocks, uint64_t area_bytes) { return inflate_work_header(nblocks) + (size_t)area_bytes + 256u; }
 
 // Launch the persistent inflate kernel over `nblocks` blocks.
 //   comp     device buffer holding the compressed bytes; must be 16-byte aligned and padded with
@@ -36,11 +42,12 @@ cudaError_t launch_bgzf_inflate(const uint8_t *comp, const BlockDesc *blocks, ui
                                 int *status, unsigned int *counter, int sm_count, cudaStream_t stream,
                                 bool only_flagged = false);
 
-// Second-generation ("lockstep") kernels: phase 1 decodes one stream per lane into literals + match commands,
-// phase 2 replays the matches and checks CRC-32/ISIZE.  `work` = inflate_work_bytes(nblocks, sum of cmd areas).
-// Blocks flagged INF_NEEDS_V1 must then be redone with launch_bgzf_inflate(..., only_flagged = true).
-cudaError_t launch_bgzf_inflate_v2(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
-                                   uint32_t *work, unsigned int *counter, int sm_count, cudaStream_t stream);
+// Third-generation ("lockstep") kernels (bgzf_inflate3.cu): phase 1 decodes one stream per lane into a literal stream +
+// match commands, phase 2 (a warp per block) places literals, replays the matches and checks CRC-32/ISIZE.
+// `work` = inflate_work_bytes(nblocks, sum of inflate_work_cap).  Blocks flagged INF_NEEDS_V1 must then be redone with
+// launch_bgzf_inflate(..., only_flagged = true).
+cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
+                                   uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream);
 
 constexpr uint32_t DH_COMP_PAD = 8192;
 

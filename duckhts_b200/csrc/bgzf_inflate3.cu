@@ -1,0 +1,689 @@
+// bgzf_inflate3.cu — "lockstep" BGZF inflate for sm_100a, third generation.
+//
+// Replaces bgzf_uncompress / inflate_block / bgzf_decode_func (htslib/bgzf.c:762-804, 808-824, 1373-1384):
+// raw DEFLATE inflate of every BGZF block + CRC-32 and ISIZE footer checks.
+//
+// What ncu said about generation 2 (profiles/r1c_*): phase 1 ran 3 warps per SM at 233 warp-instructions and
+// ~1000 cycles per symbol step (one warp per scheduler, every dependent instruction exposed, 13 % of the samples
+// waiting on the next compressed word from L2); phase 2 (one THREAD per block) read 8x the bytes it produced
+// from DRAM because 300k threads with 64 KB working sets thrash L2.  Generation 3:
+//
+//   phase 1  bgzf_decode3_kernel — still ONE DEFLATE STREAM PER LANE (Huffman decoding is bit-serial), but
+//     * 4 warps per SM (one per scheduler): litlen root 8 (worst case 660 entries, enumerated in DESIGN.md) +
+//       distance root 7 capped at 232 entries = 892 u16 entries per stream, lane-interleaved; exactly 227 KB/SM;
+//     * compressed bytes reach each lane through a private 2 x 16-byte shared-memory ring filled by cp.async
+//       (one 16-byte chunk in flight while the other is consumed), so the symbol loop never waits on L2/DRAM;
+//     * the bit reader is a 64-bit window (w0,w1) + one funnel shift per lookup, no 64-bit shifts;
+//     * table entries carry length base/extra and distance mantissa/extra, so no RFC-1951 arithmetic in the loop;
+//     * the loop is straight-line (both lookups always issued, literal path predicated, one vote per step);
+//     * output = a LITERAL STREAM (bytes, 4 per store) + a COMMAND STREAM (one word per match), not final bytes.
+//   phase 2  bgzf_resolve3_kernel — ONE WARP PER BLOCK: 32 commands per step, warp scans give every lane its
+//     destination, literals are copied from the literal stream, matches are copied in dependency rounds (a lane
+//     waits only for earlier lanes of the same step whose destination it reads), then the warp computes the CRC-32
+//     of the finished block with coalesced loads (lane-interleaved Horner form: H = H*x^1024 + w through four
+//     256-entry tables) and compares CRC and ISIZE with the BGZF footer.
+// Streams whose distance code needs more than 232 table entries (worst case 400; never seen from zlib/libdeflate)
+// are flagged INF_NEEDS_V1 and redone by the lane-group kernel (bgzf_inflate.cu) in filter mode.
+#include "bgzf_inflate.cuh"
+#include "crc32_core.cuh"
+#include "inflate_core.cuh"
+
+namespace dh {
+namespace v3 {
+
+constexpr int WARPS = 4;
+constexpr int THREADS = WARPS * 32;
+constexpr int LROOT = 8, DROOT = 7;
+constexpr int LIT_N = 660;          // worst case for 286 symbols, root 8, max length 15
+constexpr int DIST_N = 232;         // capacity; worst case for 30 symbols, root 7 is 400 -> fallback above DIST_N
+constexpr int TAB_N = LIT_N + DIST_N;
+constexpr int SCR_LENS = LIT_N;           // litlen build: code lengths, two per entry, in the distance region [0,158)
+constexpr int SCR_NC = LIT_N + 160;       // litlen build: next_code[16] in the distance region [160,176)
+constexpr unsigned FULL = 0xffffffffu;
+
+// per warp: tables [TAB_N][32] u16, then the input ring [2 chunks][32 lanes][16 bytes]
+constexpr int WARP_SMEM = TAB_N * 64 + 2 * 512;
+static_assert(WARP_SMEM * WARPS == 232448, "phase 1 is sized to fill the 227 KB of one SM exactly");
+
+// ---- table entries (u16) ---------------------------------------------------------------------------------
+// litlen:  bit15 = 1: length code   [14:12] extra bits  [11:4] base-3  [3:0] code length
+//          bit15 = 0: [14:13] 0 literal / 1 end-of-block / 2 link / 3 invalid   [12:4] value  [3:0] code length
+//          (link: value = sub-table offset behind the root, code-length field = sub-table index bits)
+// dist:    [15:14] 0 distance code / 2 link / 3 invalid
+//          code: [13:10] extra bits  [9:8] mantissa m (distance = 1 + (m << extra) + extra value)  [3:0] code length
+//          link: [12:4] sub-table offset behind the root  [3:0] sub-table index bits
+__device__ __forceinline__ uint32_t lit_entry(uint32_t sym, uint32_t l) {
+    if (sym < 256u) return (sym << 4) | l;
+    if (sym == 256u) return (1u << 13) | l;
+    if (sym < 286u) { uint32_t b, x; len_sym(sym, b, x); return 0x8000u | (x << 12) | ((b - 3u) << 4) | l; }
+    return (3u << 13) | l;
+}
+__device__ __forceinline__ uint32_t dist_entry(uint32_t sym, uint32_t l) {
+    if (sym >= 30u) return (3u << 14) | l;
+    uint32_t x = sym < 4u ? 0u : (sym >> 1) - 1u, m = sym < 4u ? sym : 2u + (sym & 1u);
+    return (x << 10) | (m << 8) | l;
+}
+constexpr uint32_t LIT_BAD = (3u << 13) | 1u, DIST_BAD = (3u << 14) | 1u;
+
+// ---- shared-memory access by 32-bit shared address ----------------------------------------------------------
+__device__ __forceinline__ uint32_t lds16(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v)); }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// ---- bit reader: 64-bit window (w0,w1) over the stream, w2 = next word, fed from the lane's cp.async ring -------
+struct Bits {
+    uint32_t w0, w1, w2;
+    uint32_t bitpos;      // bits of w0 already consumed; < 32 after normalize()
+    uint32_t wi;          // stream word (relative to the 16-byte aligned base) that the next advance() loads into w2
+    uint32_t ring;        // shared address of this lane's 16 bytes in ring chunk 0 (chunk 1 is 512 bytes further)
+    const uint8_t *g;     // 16-byte aligned global address of stream word 0
+
+    __device__ __forceinline__ void advance() {
+        w0 = w1;
+        w1 = w2;
+        bitpos -= 32u;
+        const uint32_t c = wi >> 2, k = wi & 3u;
+        if (k == 0u) cp_async_wait1();                       // chunk c has landed (chunk c+1 may still be in flight)
+        w2 = lds32(ring + ((c & 1u) << 9) + (k << 2));
+        if (k == 3u) { cp_async16(ring + ((c & 1u) << 9), g + ((size_t)(c + 2u) << 4)); cp_async_commit(); }
+        ++wi;
+    }
+    __device__ __forceinline__ void open(const uint8_t *payload, uint32_t ring_addr) {
+        ring = ring_addr;
+        g = reinterpret_cast<const uint8_t *>((uintptr_t)payload & ~(uintptr_t)15);
+        cp_async_wait0();                                    // nothing of the previous stream may still be landing
+        cp_async16(ring, g);
+        cp_async_commit();
+        cp_async16(ring + 512u, g + 16);
+        cp_async_commit();
+        cp_async_wait1();
+        w0 = lds32(ring);
+        w1 = lds32(ring + 4u);
+        w2 = lds32(ring + 8u);
+        wi = 3u;
+        bitpos = (uint32_t)((uintptr_t)payload & 15u) * 8u;
+        while (bitpos >= 32u) advance();
+    }
+    __device__ __forceinline__ void normalize() { if (bitpos >= 32u) advance(); }
+    __device__ __forceinline__ uint32_t window() const { return __funnelshift_r(w0, w1, bitpos); }  // next 32 bits
+    // header-path helpers (n <= 25)
+    __device__ __forceinline__ uint32_t take(uint32_t n) {
+        normalize();
+        uint32_t v = window() & ((1u << n) - 1u);
+        bitpos += n;
+        return v;
+    }
+    // bits consumed since the 16-byte aligned base
+    __device__ __forceinline__ uint32_t consumed() const { return (wi - 3u) * 32u + bitpos; }
+};
+
+// per-lane decoder state
+struct Lane {
+    Bits in;
+    uint32_t tab;         // shared address of this lane's column: entry i at tab + i * 64
+    uint8_t *lit;         // literal stream (grows upwards, 4 bytes per store)
+    uint32_t *cmd_top;    // command k is stored at cmd_top[-k]
+    uint32_t lit_acc, nlit, ncmd, lit_run, pos, isize;
+    uint32_t end_bits;    // consumed() value at the end of the payload
+    uint32_t wi_limit;    // a corrupt stream may not fetch words beyond this
+    int status;
+};
+
+__device__ __forceinline__ uint32_t tget(const Lane &s, uint32_t i) { return lds16(s.tab + (i << 6)); }
+__device__ __forceinline__ void tput(const Lane &s, uint32_t i, uint32_t v) { sts16(s.tab + (i << 6), v); }
+
+// cold-path literal (stored blocks): same stream format as the hot loop
+__device__ __forceinline__ void put_literal(Lane &s, uint32_t byte) {
+    s.lit_acc |= byte << (8u * (s.nlit & 3u));
+    ++s.nlit;
+    if ((s.nlit & 3u) == 0u) { *reinterpret_cast<uint32_t *>(s.lit + s.nlit - 4u) = s.lit_acc; s.lit_acc = 0u; }
+    ++s.pos;
+    if (++s.lit_run == 255u) { s.cmd_top[-(int)s.ncmd] = 0x80000000u | 255u; ++s.ncmd; s.lit_run = 0u; }
+}
+
+// ---- canonical Huffman table build, one lane's private column -------------------------------------------------
+// counts of code lengths 0..15 in 16-bit fields of four 64-bit registers (no dynamically indexed local array)
+struct Counts {
+    uint64_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    __device__ __forceinline__ void add(uint32_t l) {
+        const uint64_t one = 1ull << ((l & 3u) * 16u);
+        const uint32_t q = l >> 2;
+        c0 += q == 0 ? one : 0ull;
+        c1 += q == 1 ? one : 0ull;
+        c2 += q == 2 ? one : 0ull;
+        c3 += q == 3 ? one : 0ull;
+    }
+    __device__ __forceinline__ uint32_t get(int l) const {
+        const int q = l >> 2;
+        const uint64_t w = q == 0 ? c0 : q == 1 ? c1 : q == 2 ? c2 : c3;
+        return (uint32_t)(w >> ((l & 3) * 16)) & 0xffffu;
+    }
+};
+
+// Kraft check shared by both builds: returns INF_OK / err; sets maxlen and left (unused code space at length 15)
+__device__ __forceinline__ int check_lengths(const Counts &c, int err, int &maxlen, int &left) {
+    left = 1;
+    maxlen = 0;
+#pragma unroll
+    for (int l = 1; l <= 15; ++l) {
+        const uint32_t cl = c.get(l);
+        left = (left << 1) - (int)cl;
+        if (left < 0) return err;                   // over-subscribed
+        if (cl) maxlen = l;
+    }
+    if (left > 0 && maxlen > 1) return err;         // incomplete set: zlib allows it only for a single 1-bit code
+    return INF_OK;
+}
+
+// Root prefixes that carry codes longer than `root` bits get a sub-table sized by the longest code under them.
+// Canonical codes grow with length, so these prefixes are the top end [p_first, nroot) of the prefix space.
+// mark(p, bits) / finish(p) -> stores; shared by both builds through lambdas on the code ranges.
+template <typename FirstFn>
+__device__ __forceinline__ int layout_subtables(const Lane &s, const Counts &c, const int base, const int root, const int cap,
+                                                const int maxlen, const uint32_t link_kind, FirstFn first_code) {
+    const int nroot = 1 << root;
+    int p_first = nroot;
+    for (int l = root + 1; l <= maxlen; ++l) {
+        const uint32_t cl = c.get(l);
+        if (!cl) continue;
+        const uint32_t first = first_code(l);
+        const int p0 = (int)(first >> (l - root)), p1 = (int)((first + cl - 1u) >> (l - root));
+        if (p0 < p_first) p_first = p0;
+        for (int p = p0; p <= p1; ++p) tput(s, base + (__brev((uint32_t)p) >> (32 - root)), (uint32_t)(l - root));
+    }
+    int next_free = nroot;
+    for (int p = p_first; p < nroot; ++p) {
+        const uint32_t ri = base + (__brev((uint32_t)p) >> (32 - root));
+        const uint32_t bits = tget(s, ri);
+        const int off = next_free;
+        next_free += 1 << bits;
+        if (next_free > cap) return INF_NEEDS_V1;
+        tput(s, ri, link_kind | ((uint32_t)(off - nroot) << 4) | bits);
+    }
+    return INF_OK;
+}
+
+// store entry `ent` for the code `cd` (MSB-first value) of length l
+__device__ __forceinline__ void place_code(const Lane &s, const int base, const int root, const uint32_t cd, const uint32_t l,
+                                           const uint32_t ent) {
+    const uint32_t rev = __brev(cd) >> (32u - l);
+    const uint32_t nroot = 1u << root;
+    if ((int)l <= root) {
+        for (uint32_t k = rev; k < nroot; k += 1u << l) tput(s, base + k, ent);
+    } else {
+        const uint32_t link = tget(s, base + (rev & (nroot - 1u)));
+        const uint32_t sub = base + nroot + ((link >> 4) & 511u), bits = link & 15u;
+        for (uint32_t k = rev >> root; k < (1u << bits); k += 1u << (l - (uint32_t)root)) tput(s, sub + k, ent);
+    }
+}
+
+// literal/length table from the n code lengths parked (two per entry) at SCR_LENS
+__device__ __forceinline__ uint32_t parked_len(const Lane &s, uint32_t j) { return (tget(s, SCR_LENS + (j >> 1)) >> (8u * (j & 1u))) & 255u; }
+
+__device__ __forceinline__ int build_litlen(const Lane &s, const int n) {
+    Counts c;
+    for (int j = 0; j < n; ++j) c.add(parked_len(s, (uint32_t)j));
+    c.c0 &= ~0xffffull;  // length 0 = unused symbol
+    int maxlen, left;
+    int rc = check_lengths(c, INF_ERR_LITLEN_SET, maxlen, left);
+    if (rc != INF_OK) return rc;
+    uint32_t code = 0;
+#pragma unroll
+    for (int l = 1; l <= 15; ++l) {                 // next_code[l]: first canonical code of length l
+        tput(s, SCR_NC + l, code);
+        code = (code + c.get(l)) << 1;
+    }
+    if (left > 0 || maxlen == 0)
+        for (int k = 0; k < (1 << LROOT); ++k) tput(s, k, LIT_BAD);
+    if (maxlen > LROOT) {
+        rc = layout_subtables(s, c, 0, LROOT, LIT_N, maxlen, 2u << 13, [&](int l) -> uint32_t { return tget(s, SCR_NC + l); });
+        if (rc != INF_OK) return rc;
+    }
+    for (int j = 0; j < n; ++j) {
+        const uint32_t l = parked_len(s, (uint32_t)j);
+        if (!l) continue;
+        const uint32_t cd = tget(s, SCR_NC + l);
+        tput(s, SCR_NC + l, cd + 1u);
+        place_code(s, 0, LROOT, cd, l, lit_entry((uint32_t)j, l));
+    }
+    return INF_OK;
+}
+
+// distance table from n <= 32 code lengths held as nibbles in four registers; needs no scratch
+__device__ __forceinline__ int build_dist(const Lane &s, const int n, const uint32_t d0, const uint32_t d1, const uint32_t d2,
+                                       const uint32_t d3) {
+    auto nib = [&](int j) -> uint32_t { const uint32_t w = j < 8 ? d0 : j < 16 ? d1 : j < 24 ? d2 : d3; return (w >> (4 * (j & 7))) & 15u; };
+    Counts c;
+    for (int j = 0; j < n; ++j) c.add(nib(j));
+    c.c0 &= ~0xffffull;
+    int maxlen, left;
+    int rc = check_lengths(c, INF_ERR_DIST_SET, maxlen, left);
+    if (rc != INF_OK) return rc;
+    if (left > 0 || maxlen == 0)
+        for (int k = 0; k < (1 << DROOT); ++k) tput(s, LIT_N + k, DIST_BAD);
+    if (maxlen > DROOT) {
+        rc = layout_subtables(s, c, LIT_N, DROOT, DIST_N, maxlen, 2u << 14, [&](int l) -> uint32_t {
+            uint32_t code = 0;
+            for (int q = 1; q < l; ++q) code = (code + c.get(q)) << 1;
+            return code;
+        });
+        if (rc != INF_OK) return rc;
+    }
+    uint32_t code = 0;
+    for (int l = 1; l <= maxlen; ++l) {
+        if (c.get(l))
+            for (int j = 0; j < n; ++j)
+                if (nib(j) == (uint32_t)l) place_code(s, LIT_N, DROOT, code++, (uint32_t)l, dist_entry((uint32_t)j, (uint32_t)l));
+        code <<= 1;
+    }
+    return INF_OK;
+}
+
+// ---- deflate block header (RFC 1951 3.2.3-3.2.7): returns INF_OK with tables built, or an error / INF_NEEDS_V1 -----
+// stored blocks are copied through the literal path here and return with *stored = true
+__device__ __forceinline__ int read_block_header(Lane &s, uint32_t &bfinal, bool &stored) {
+    stored = false;
+    bfinal = s.in.take(1);
+    const uint32_t btype = s.in.take(2);
+    if (btype == 3u) return INF_ERR_BTYPE;
+    if (btype == 0u) {
+        stored = true;
+        s.in.bitpos = (s.in.bitpos + 7u) & ~7u;        // LEN/NLEN start at the next byte boundary
+        const uint32_t len = s.in.take(16), nlen = s.in.take(16);
+        if ((len ^ 0xffffu) != nlen) return INF_ERR_STORED_LEN;
+        if (s.pos + len > s.isize) return INF_ERR_ISIZE;
+        if (s.in.consumed() + 8u * len > s.end_bits) return INF_ERR_IN_OVERRUN;
+        for (uint32_t i = 0; i < len; ++i) put_literal(s, s.in.take(8));
+        return INF_OK;
+    }
+    uint32_t hlit = 288u, hdist = 32u;
+    uint32_t d0 = 0x55555555u, d1 = 0x55555555u, d2 = 0x55555555u, d3 = 0x55555555u;  // fixed code: 32 distance codes of 5 bits
+    if (btype == 1u) {
+        // fixed Huffman code (RFC 1951 3.2.6): lengths parked where the dynamic path would put them
+        for (uint32_t j = 0; j < 288u; j += 2u) {
+            const uint32_t l = j < 144u ? 8u : j < 256u ? 9u : j < 280u ? 7u : 8u;
+            tput(s, SCR_LENS + (j >> 1), l | (l << 8));
+        }
+    } else {
+        hlit = s.in.take(5) + 257u;
+        hdist = s.in.take(5) + 1u;
+        const uint32_t hclen = s.in.take(4) + 4u;
+        if (hlit > 286u || hdist > 30u) return INF_ERR_TOO_MANY_SYMS;
+        // code-length code: 19 x 3 bits, kept in one register
+        uint64_t pl = 0;
+        for (uint32_t i = 0; i < hclen; ++i) pl |= (uint64_t)s.in.take(3) << (3u * precode_order(i));
+        {
+            Counts c;
+            for (int sym = 0; sym < 19; ++sym) c.add((uint32_t)(pl >> (3 * sym)) & 7u);
+            c.c0 &= ~0xffffull;
+            int left = 1;
+#pragma unroll
+            for (int q = 1; q < 8; ++q) { left = (left << 1) - (int)c.get(q); if (left < 0) return INF_ERR_PRECODE; }
+            if (left > 0) return INF_ERR_PRECODE;   // an incomplete code-length code is never allowed (zlib CODES rule)
+        }
+        // 7-bit direct table in litlen-region slots [0,128): entry = sym << 4 | len
+        uint32_t code = 0;
+        for (uint32_t l = 1; l < 8u; ++l) {
+            for (uint32_t sym = 0; sym < 19u; ++sym) {
+                if (((uint32_t)(pl >> (3u * sym)) & 7u) != l) continue;
+                const uint32_t rev = __brev(code) >> (32u - l);
+                for (uint32_t k = rev; k < 128u; k += 1u << l) tput(s, k, (sym << 4) | l);
+                ++code;
+            }
+            code <<= 1;
+        }
+        // litlen + distance code lengths, parked two per entry
+        const uint32_t n = hlit + hdist;
+        uint32_t i = 0, prev = 0, pend = 0;
+        auto put_len = [&](uint32_t idx, uint32_t v) { if (idx & 1u) tput(s, SCR_LENS + (idx >> 1), pend | (v << 8)); else pend = v; };
+        while (i < n) {
+            s.in.normalize();
+            const uint32_t e = tget(s, s.in.window() & 127u);
+            s.in.bitpos += e & 15u;
+            const uint32_t sym = e >> 4;
+            if (sym < 16u) { put_len(i, sym); prev = sym; ++i; continue; }
+            uint32_t rep, val;
+            if (sym == 16u) { if (i == 0u) return INF_ERR_LENS_REPEAT; rep = 3u + s.in.take(2); val = prev; }
+            else if (sym == 17u) { rep = 3u + s.in.take(3); val = 0u; }
+            else { rep = 11u + s.in.take(7); val = 0u; }
+            if (i + rep > n) return INF_ERR_LENS_REPEAT;
+            for (uint32_t k = 0; k < rep; ++k) put_len(i + k, val);
+            i += rep;
+            prev = val;
+        }
+        if (n & 1u) tput(s, SCR_LENS + (n >> 1), pend);
+        if (s.in.consumed() > s.end_bits) return INF_ERR_IN_OVERRUN;
+        if (parked_len(s, 256u) == 0u) return INF_ERR_NO_EOB;
+        d0 = d1 = d2 = d3 = 0u;
+        for (uint32_t k = 0; k < hdist; ++k) {
+            const uint32_t v = parked_len(s, hlit + k) << (4u * (k & 7u)), q = k >> 3;
+            d0 |= q == 0u ? v : 0u; d1 |= q == 1u ? v : 0u; d2 |= q == 2u ? v : 0u; d3 |= q == 3u ? v : 0u;
+        }
+    }
+    int rc = build_litlen(s, (int)hlit);
+    if (rc != INF_OK) return rc;
+    return build_dist(s, (int)hdist, d0, d1, d2, d3);
+}
+
+}  // namespace v3
+
+using namespace v3;
+
+// =========================================================================================================
+// phase 1: Huffman decode, one stream per lane -> literal stream + command stream
+// =========================================================================================================
+// commands (32 bits):  [31]=0 match:   [30:23] literals since the previous command (0..254)  [22:15] length-3  [14:0] distance-1
+//                      [31]=1 literals: [30:0] run of literals with no match behind it (255 inside a run, or the tail)
+__global__ void __launch_bounds__(THREADS, 1)
+bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, uint32_t nblocks,
+                    int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
+                    unsigned int *__restrict__ counter) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t warp_base = (uint32_t)__cvta_generic_to_shared(smem_raw) + warp * (uint32_t)WARP_SMEM;
+    enum { ST_HEADER = 0, ST_RUN = 1, ST_DONE = 2 };
+
+    for (;;) {
+        // ---- a generation: 32 consecutive blocks, one per lane ----
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(counter, 32u);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= nblocks) break;
+        const uint32_t b = base + lane;
+        Lane s;
+        s.tab = warp_base + lane * 2u;
+        s.status = INF_OK;
+        s.lit_acc = s.nlit = s.ncmd = s.lit_run = s.pos = s.isize = 0u;
+        s.end_bits = 0u;
+        s.wi_limit = 0u;
+        s.lit = work;
+        s.cmd_top = reinterpret_cast<uint32_t *>(work);
+        int st = ST_DONE;
+        uint32_t bfinal = 0;
+        if (b < nblocks) {
+            const BlockDesc d = blocks[b];
+            s.isize = d.isize;
+            s.lit = work + d.cmd_off;
+            s.cmd_top = reinterpret_cast<uint32_t *>(work + d.cmd_off + inflate_work_cap(d.isize)) - 1;
+            s.in.open(comp + d.in_off, warp_base + (uint32_t)TAB_N * 64u + lane * 16u);
+            const uint32_t mis = (uint32_t)((uintptr_t)(comp + d.in_off) & 15u);
+            s.end_bits = (mis + d.in_len) * 8u;
+            s.wi_limit = ((mis + d.in_len + 3u) >> 2) + 8u;
+            st = ST_HEADER;
+        }
+        auto fail = [&](int code) { s.status = code; st = ST_DONE; };
+        // end of the final deflate block: flush the literal word, announce the trailing literals
+        auto finish = [&]() {
+            if (s.nlit & 3u) *reinterpret_cast<uint32_t *>(s.lit + (s.nlit & ~3u)) = s.lit_acc;
+            if (s.lit_run) { s.cmd_top[-(int)s.ncmd] = 0x80000000u | s.lit_run; ++s.ncmd; s.lit_run = 0u; }
+            if (s.in.consumed() > s.end_bits) s.status = INF_ERR_IN_OVERRUN;
+            else if (s.pos != s.isize) s.status = INF_ERR_ISIZE;
+            st = ST_DONE;
+        };
+
+        while (__any_sync(FULL, st != ST_DONE)) {
+            // ---------------- deflate block headers (in lock-step for zlib-made streams) ----------------
+            if (st == ST_HEADER) {
+                bool stored;
+                const int rc = read_block_header(s, bfinal, stored);
+                if (rc != INF_OK) fail(rc);
+                else if (!stored) st = ST_RUN;
+                else if (bfinal) finish();
+            }
+            // ---------------- symbols: one per lane per step, until every running lane has hit something rare ----------------
+            while (__any_sync(FULL, st == ST_RUN)) {
+                uint32_t rare;
+                uint32_t e = 0;
+                do {
+                    rare = 0u;
+                    if (st == ST_RUN) {
+                        s.in.normalize();
+                        uint32_t bits = s.in.window();
+                        e = tget(s, bits & 255u);
+                        {   // second level: always issued, so that the step is straight-line code
+                            const bool link = (e >> 13) == 2u;
+                            const uint32_t sub = 256u + ((e >> 4) & 511u) + ((bits >> 8) & ((1u << (e & 15u)) - 1u));
+                            const uint32_t e2 = tget(s, link ? sub : 0u);
+                            e = link ? e2 : e;
+                        }
+                        const uint32_t cl = e & 15u;
+                        bits >>= cl;
+                        s.in.bitpos += cl;
+                        if ((e >> 13) == 0u) {                      // literal
+                            s.lit_acc |= ((e >> 4) & 255u) << (8u * (s.nlit & 3u));
+                            ++s.nlit;
+                            ++s.lit_run;
+                            ++s.pos;
+                            if ((s.nlit & 3u) == 0u) { *reinterpret_cast<uint32_t *>(s.lit + s.nlit - 4u) = s.lit_acc; s.lit_acc = 0u; }
+                            rare = (s.lit_run == 255u) | (s.pos > s.isize);
+                        } else if (e >> 15) {                       // length + distance
+                            const uint32_t xb = (e >> 12) & 7u;
+                            const uint32_t len = 3u + ((e >> 4) & 255u) + (bits & ((1u << xb) - 1u));
+                            s.in.bitpos += xb;
+                            s.in.normalize();
+                            bits = s.in.window();
+                            uint32_t d = tget(s, LIT_N + (bits & 127u));
+                            {
+                                const bool link = (d >> 14) == 2u;
+                                const uint32_t sub = LIT_N + 128u + ((d >> 4) & 511u) + ((bits >> 7) & ((1u << (d & 15u)) - 1u));
+                                const uint32_t d2 = tget(s, link ? sub : LIT_N);
+                                d = link ? d2 : d;
+                            }
+                            const uint32_t dl = d & 15u, dx = (d >> 10) & 15u;
+                            bits >>= dl;
+                            const uint32_t dist = 1u + (((d >> 8) & 3u) << dx) + (bits & ((1u << dx) - 1u));
+                            s.in.bitpos += dl + dx;
+                            s.cmd_top[-(int)s.ncmd] = (s.lit_run << 23) | ((len - 3u) << 15) | (dist - 1u);
+                            ++s.ncmd;
+                            s.lit_run = 0u;
+                            rare = ((d >> 14) != 0u) | (dist > s.pos);
+                            s.pos += len;
+                            rare |= s.pos > s.isize;
+                            e = 0x8000u | (d & 0xc000u) >> 2;       // keep the distance verdict for the slow path
+                        } else {
+                            rare = 1u;                              // end of block / invalid code
+                        }
+                        rare |= s.in.wi > s.wi_limit;
+                    }
+                } while (!__any_sync(FULL, rare));
+                // ---------------- rare events ----------------
+                if (rare) {
+                    if (s.in.wi > s.wi_limit) fail(INF_ERR_IN_OVERRUN);
+                    else if ((e >> 13) == 0u) {                     // literal
+                        if (s.pos > s.isize) fail(INF_ERR_ISIZE);
+                        else { s.cmd_top[-(int)s.ncmd] = 0x80000000u | 255u; ++s.ncmd; s.lit_run = 0u; }
+                    } else if (e >> 15) {                           // match
+                        if (e & 0x3000u) fail(INF_ERR_BAD_DIST);
+                        else if (s.pos > s.isize) fail(INF_ERR_ISIZE);
+                        else fail(INF_ERR_DIST_TOO_FAR);
+                    } else if ((e >> 13) == 1u) {                   // end of block
+                        if (s.in.consumed() > s.end_bits) fail(INF_ERR_IN_OVERRUN);
+                        else if (bfinal) finish();
+                        else st = ST_HEADER;
+                    } else fail(INF_ERR_BAD_LITLEN);
+                }
+            }
+        }
+        if (b < nblocks) {
+            status[b] = s.status;
+            ncmd_out[b] = s.ncmd;
+        }
+    }
+    cp_async_wait0();
+}
+
+// =========================================================================================================
+// phase 2: one warp per block — place literals, replay matches in dependency rounds, CRC-32 + footer check
+// =========================================================================================================
+// CRC tables (host-built, uploaded once per device): [k*256 + i], k = 0..3: byte i at byte position k of a 32-bit
+// register advanced by 128 bytes (multiplication by x^1024 mod P, split by byte); k = 4: the classic byte table;
+// [1280 + l]: x^(8 * (128 - 4l)) for lane l.
+constexpr int CRC3_WORDS = 5 * 256 + 32;
+__device__ uint32_t g_crc3[CRC3_WORDS];
+
+constexpr uint32_t LONG_COPY = 64;   // copies of at least this many bytes are done by the whole warp
+
+__global__ void __launch_bounds__(256, 4)
+bgzf_resolve3_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uint8_t *__restrict__ outbuf,
+                     int *__restrict__ status, const uint32_t *__restrict__ ncmd_in, const uint8_t *__restrict__ work) {
+    __shared__ uint32_t tabs[CRC3_WORDS];
+    for (int i = threadIdx.x; i < CRC3_WORDS; i += 256) tabs[i] = g_crc3[i];
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t b = blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (b >= nblocks) return;
+    if (status[b] != INF_OK) return;
+    const BlockDesc d = blocks[b];
+    uint8_t *o = outbuf + d.out_off;
+    const uint8_t *lit = work + d.cmd_off;
+    const uint32_t *cmd_top = reinterpret_cast<const uint32_t *>(work + d.cmd_off + inflate_work_cap(d.isize)) - 1;
+    const uint32_t n = ncmd_in[b];
+    uint32_t pos = 0, lpos = 0;
+
+    for (uint32_t k0 = 0; k0 < n; k0 += 32u) {
+        const uint32_t k = k0 + lane;
+        const uint32_t c = k < n ? cmd_top[-(int)k] : 0x80000000u;
+        const bool isrun = (c >> 31) != 0u;
+        const uint32_t lr = isrun ? (c & 0x7fffffffu) : (c >> 23);
+        const uint32_t len = isrun ? 0u : ((c >> 15) & 255u) + 3u;
+        const uint32_t dist = (c & 0x7fffu) + 1u;
+        // inclusive warp scans: output bytes and literal bytes up to and including this command
+        uint32_t ae = lr + len, le = lr;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const uint32_t va = __shfl_up_sync(FULL, ae, sft), vl = __shfl_up_sync(FULL, le, sft);
+            if (lane >= (uint32_t)sft) { ae += va; le += vl; }
+        }
+        const uint32_t dl = pos + ae - lr - len;     // where this command's literals go
+        const uint32_t dm = dl + lr;                 // where its match goes
+        const uint32_t ls = lpos + le - lr;          // its literals in the literal stream
+        // ---- literals ----
+        {
+            const uint32_t small = lr < LONG_COPY ? lr : 0u;
+            const uint32_t mx = __reduce_max_sync(FULL, small);
+            for (uint32_t i = 0; i < mx; ++i)
+                if (i < small) o[dl + i] = lit[ls + i];
+            uint32_t big = __ballot_sync(FULL, lr >= LONG_COPY);
+            while (big) {
+                const int L = __ffs(big) - 1;
+                big &= big - 1u;
+                const uint32_t d_ = __shfl_sync(FULL, dl, L), s_ = __shfl_sync(FULL, ls, L), n_ = __shfl_sync(FULL, lr, L);
+                for (uint32_t i = lane; i < n_; i += 32u) o[d_ + i] = lit[s_ + i];
+            }
+        }
+        // ---- matches: which earlier lanes of this step write bytes that this lane reads? ----
+        uint32_t pend = __ballot_sync(FULL, len > 0u);
+        if (pend) {
+            const uint32_t src = dm - dist;
+            const uint32_t src_end = dist < len ? dm : src + len;    // source bytes outside the lane's own destination
+            const uint32_t me = dm + len;
+            uint32_t lo = 0, hi = 0;                                 // lo = #lanes with me <= src, hi = #lanes with dm < src_end
+#pragma unroll
+            for (int step = 16; step; step >>= 1) {
+                const uint32_t vme = __shfl_sync(FULL, me, (int)lo + step - 1), vms = __shfl_sync(FULL, dm, (int)hi + step - 1);
+                if (vme <= src) lo += (uint32_t)step;
+                if (vms < src_end) hi += (uint32_t)step;
+            }
+            const uint32_t depmask = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+            __syncwarp();                                            // literals of this step are in place
+            while (pend) {
+                const bool ready = ((pend >> lane) & 1u) && !(depmask & pend);
+                uint32_t big = __ballot_sync(FULL, ready && len >= LONG_COPY);
+                while (big) {
+                    const int L = __ffs(big) - 1;
+                    big &= big - 1u;
+                    const uint32_t d_ = __shfl_sync(FULL, dm, L), s_ = __shfl_sync(FULL, src, L), n_ = __shfl_sync(FULL, len, L),
+                                   p_ = __shfl_sync(FULL, dist, L);
+                    for (uint32_t i = lane; i < n_; i += 32u) o[d_ + i] = o[s_ + (p_ < n_ ? i % p_ : i)];
+                }
+                const uint32_t nb = (ready && len < LONG_COPY) ? len : 0u;
+                const uint32_t mx = __reduce_max_sync(FULL, nb);
+                for (uint32_t i = 0; i < mx; ++i)
+                    if (i < nb) o[dm + i] = o[src + i];
+                __syncwarp();
+                pend &= ~__ballot_sync(FULL, ready);
+            }
+        }
+        pos += __shfl_sync(FULL, ae, 31);
+        lpos += __shfl_sync(FULL, le, 31);
+        __syncwarp();
+    }
+
+    // ---- CRC-32 (htslib/bgzf.c:793) of the finished block ----
+    const uint32_t *T0 = tabs + 4 * 256;
+    const uint8_t *p = o, *end = o + d.isize;
+    const uint8_t *a0 = reinterpret_cast<const uint8_t *>(((uintptr_t)o + 127u) & ~(uintptr_t)127);
+    if (a0 > end) a0 = end;
+    uint32_t r = 0xffffffffu;
+    if (lane == 0)
+        for (; p < a0; ++p) r = T0[(r ^ *p) & 0xffu] ^ (r >> 8);
+    r = __shfl_sync(FULL, r, 0);
+    const uint32_t rows = (uint32_t)(end - a0) >> 7;
+    if (rows) {
+        const uint32_t *wp = reinterpret_cast<const uint32_t *>(a0) + lane;
+        uint32_t H = 0;
+        for (uint32_t row = 0; row < rows; ++row) {
+            uint32_t w = wp[(size_t)row * 32u];
+            if (row == 0 && lane == 0) w ^= r;
+            H = tabs[H & 0xffu] ^ tabs[256 + ((H >> 8) & 0xffu)] ^ tabs[512 + ((H >> 16) & 0xffu)] ^ tabs[768 + (H >> 24)] ^ w;
+        }
+        uint32_t v = crc_mulmod(tabs[5 * 256 + lane], H);
+#pragma unroll
+        for (int sft = 16; sft; sft >>= 1) v ^= __shfl_xor_sync(FULL, v, sft);
+        r = v;
+    }
+    if (lane == 0) {
+        for (p = a0 + ((size_t)rows << 7); p < end; ++p) r = T0[(r ^ *p) & 0xffu] ^ (r >> 8);
+        if ((r ^ 0xffffffffu) != d.crc) status[b] = INF_ERR_CRC;
+        else if (pos != d.isize) status[b] = INF_ERR_ISIZE;
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+static void build_crc3_tables(uint32_t *t) {
+    uint32_t slice[8 * 256], x2n[32];
+    for (int i = 0; i < 256; ++i) crc_table_column(slice, i);
+    crc_x2n_init(x2n);
+    for (int k = 0; k < 4; ++k)
+        for (int i = 0; i < 256; ++i) t[k * 256 + i] = crc_shift(x2n, slice[i], 127u - (uint32_t)k);
+    for (int i = 0; i < 256; ++i) t[4 * 256 + i] = slice[i];
+    for (int l = 0; l < 32; ++l) t[5 * 256 + l] = crc_shift(x2n, 0x80000000u, 128u - 4u * (uint32_t)l);
+}
+
+cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
+                                   uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream) {
+    static bool ready[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!ready[dev]) {
+        static uint32_t host_tabs[CRC3_WORDS];
+        build_crc3_tables(host_tabs);
+        e = cudaMemcpyToSymbol(g_crc3, host_tabs, sizeof host_tabs);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(bgzf_decode3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WARP_SMEM * WARPS);
+        if (e != cudaSuccess) return e;
+        ready[dev] = true;
+    }
+    e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if (nblocks == 0) return cudaSuccess;
+    uint32_t *ncmd = reinterpret_cast<uint32_t *>(work);
+    uint8_t *areas = work + inflate_work_header(nblocks);
+    uint32_t ctas = (nblocks + THREADS - 1) / THREADS;
+    if (ctas > (uint32_t)sm_count) ctas = (uint32_t)sm_count;
+    bgzf_decode3_kernel<<<ctas, THREADS, WARP_SMEM * WARPS, stream>>>(comp, blocks, nblocks, status, ncmd, areas, counter);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    bgzf_resolve3_kernel<<<(nblocks + 7u) / 8u, 256, 0, stream>>>(blocks, nblocks, out, status, ncmd, areas);
+    return cudaGetLastError();
+}
+
+}  // namespace dh

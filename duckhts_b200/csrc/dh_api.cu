@@ -94,7 +94,7 @@ int walk_blocks(const uint8_t *data, uint64_t size, uint64_t start, BlockTable &
 
 uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_base, size_t out_b0, uint64_t out_bias,
                     BlockDesc *d) {
-    uint64_t words = 0;
+    uint64_t area = 0;
     for (size_t i = b0; i < b1; ++i) {
         const dh_bgzf_block &b = bt.blocks[i];
         BlockDesc &o = d[i - b0];
@@ -103,10 +103,10 @@ uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_ba
         o.isize = b.isize;
         o.crc = b.crc;
         o.out_off = out_bias + (bt.uoff[i] - bt.uoff[out_b0]);
-        o.cmd_off = words;
-        words += cmd_words_for(b.isize);
+        o.cmd_off = area;
+        area += inflate_work_cap(b.isize);
     }
-    return words;
+    return area;
 }
 
 int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
@@ -119,7 +119,7 @@ int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint3
     }
     int rc = work.reserve(inflate_work_bytes(n, cmd_words));
     if (rc != DH_OK) return rc;
-    DH_CUDA(launch_bgzf_inflate_v2(comp, descs, n, out, status, (uint32_t *)work.p, counter, c->sm_count, stream));
+    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, c->sm_count, stream));
     DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, stream, true));
     c->launches += 3;
     return DH_OK;

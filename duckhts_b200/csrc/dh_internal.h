@@ -45,7 +45,7 @@ struct BlockTable {
 int walk_blocks(const uint8_t *data, uint64_t size, uint64_t start, BlockTable &bt, uint64_t *bad_off);
 
 // Device block descriptors for blocks [b0,b1): compressed bytes were uploaded starting at file offset `comp_base`
-// (16-byte aligned); block i's bytes go to out + out_bias + (uoff[i] - uoff[out_b0]).  Returns the command words the
+// (16-byte aligned); block i's bytes go to out + out_bias + (uoff[i] - uoff[out_b0]).  Returns the work-area bytes the
 // lockstep kernel's work buffer needs for these blocks.
 uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_base, size_t out_b0, uint64_t out_bias,
                     BlockDesc *d);

@@ -1,7 +1,9 @@
 #!/bin/bash
-# tests + read_bam bench (inflate v2) + reference arm
+# tests + read_bam bench + reference arm
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
-tail -5 gpurun_out/pytest_gpu.log
-timeout 900 python bench.py --steps 2 --warmup 3 > gpurun_out/bench_v2.json 2> gpurun_out/bench_v2.err; echo "bench exit $?"
-cat gpurun_out/bench_v2.json; tail -5 gpurun_out/bench_v2.err
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+tail -15 gpurun_out/pytest_gpu.log
+if grep -q "pytest exit 0" gpurun_out/pytest_gpu.log; then
+timeout 900 python bench.py --steps 2 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
+cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
+fi
