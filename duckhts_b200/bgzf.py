@@ -95,6 +95,11 @@ class Context:
         check(lib().dh_measure_pcie(self.h, nbytes, C.byref(a), C.byref(b)), "dh_measure_pcie")
         return a.value, b.value
 
+    def measure_pcie_bidir(self, nbytes=1 << 30):
+        a, b = C.c_float(0), C.c_float(0)
+        check(lib().dh_measure_pcie_bidir(self.h, nbytes, C.byref(a), C.byref(b)), "dh_measure_pcie_bidir")
+        return a.value, b.value
+
 
 def bgzf_inflate(ctx, data, out=None, want_output=True):
     """A2/A3: inflate a whole BGZF image host->host (src/bgzip.c:154-200 equivalent).  Returns (bytes-like, stats)."""

@@ -227,6 +227,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
             off = s;  // == bend if nothing starts here (a long record spans the block)
         }
     }
+    uint16_t *rec = p.rec + ((start - p.rec_bias) / 36 + (int64_t)i);
     BlockWalk w;
     w.entry = off;
     w.count = 0;
@@ -272,6 +273,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
             }
         }
         w.heap_bytes += need;
+        rec[w.count] = (uint16_t)(off - start);   // where the decode kernel finds this record (relative to the block start)
         w.count++;
         off = r.end;
     }
@@ -280,306 +282,380 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
 }
 
 // =======================================================================================================
-// columnar decode: one warp per BGZF block
+// columnar decode: one warp per BGZF block, 32 records per step
 // =======================================================================================================
+// Step layout (ncu on the first version, which walked ONE record per warp step, showed ~6.5k cycles per record):
+//   A  every lane parses ITS OWN record (offsets come from the walk: rec[] is read coalesced) and stores the
+//      fixed-width columns -> 32 consecutive rows per store instruction;
+//   B  a warp scan of the per-record heap needs gives every record its string slots;
+//   C  the long strings (QNAME, SEQ nibbles -> ASCII, QUAL+33, long CIGAR text) are produced record by record
+//      by the whole warp: 8 output bytes per lane, contiguous stores into the heap;
+//   D  every lane builds the 16-byte duckdb_string_t cells of its own row and the typed tag values ->
+//      512 contiguous bytes per column per store instruction; validity bits go out as one word per 32 rows.
 constexpr unsigned FULL = 0xffffffffu;
 
-__device__ __forceinline__ void set_valid(unsigned long long *v, uint32_t row) {
-    atomicOr(&v[row >> 6], 1ull << (row & 63u));
-}
 __device__ __forceinline__ void store_cell(uint8_t *col, uint32_t row, uint32_t len, uint32_t w0, uint32_t w1, uint32_t w2) {
     reinterpret_cast<uint4 *>(col)[row] = make_uint4(len, w0, w1, w2);
 }
-
-// Warp-cooperative VARCHAR cell from `len` bytes at u[src..]; `bound` is the slot size rule shared with the walk.
-__device__ __forceinline__ void emit_str(const DecodeParams &p, int c, uint32_t row, const uint8_t *u, int64_t src,
-                                         uint32_t len, uint32_t bound, uint64_t &hp, uint32_t lane) {
-    uint64_t slot = hp;
-    hp += slot_bytes(bound);
-    if (len <= 12u) {
-        if (lane == 0) {
-            uint32_t w0 = len > 0 ? mask_bytes(ld32u(u, src), len) : 0u;
-            uint32_t w1 = len > 4 ? mask_bytes(ld32u(u, src + 4), len - 4u) : 0u;
-            uint32_t w2 = len > 8 ? mask_bytes(ld32u(u, src + 8), len - 8u) : 0u;
-            store_cell(p.col[c], row, len, w0, w1, w2);
-        }
-        return;
-    }
-    uint32_t *dst = reinterpret_cast<uint32_t *>(p.heap + slot);
-    uint32_t words = (len + 3u) >> 2;
-    for (uint32_t k = lane; k < words; k += 32u) dst[k] = mask_bytes(ld32u(u, src + 4ll * k), len - 4u * k);
-    if (lane == 0) {
-        uint64_t hptr = p.heap_host + slot;
-        store_cell(p.col[c], row, len, ld32u(u, src), (uint32_t)hptr, (uint32_t)(hptr >> 32));
+// validity bits of the 32 rows [row0, row0 + 32): two 32-bit atomics per warp instead of one per row
+__device__ __forceinline__ void set_valid_group(unsigned long long *v, uint32_t row0, uint32_t mask, uint32_t lane) {
+    if (lane == 0 && mask) {
+        unsigned int *v32 = reinterpret_cast<unsigned int *>(v);
+        const uint32_t sh = row0 & 31u;
+        atomicOr(&v32[row0 >> 5], mask << sh);
+        if (sh && (mask >> (32u - sh))) atomicOr(&v32[(row0 >> 5) + 1u], mask >> (32u - sh));
     }
 }
-
-// lane-parallel strlen bounded by [s, end): returns offset of the NUL or `end`
-__device__ __forceinline__ int64_t find_nul(const uint8_t *u, int64_t s, int64_t end, uint32_t lane) {
-    for (int64_t b = s; b < end; b += 32) {
-        int64_t q = b + lane;
-        bool z = q < end && ld8(u, q) == 0;
-        unsigned m = __ballot_sync(FULL, z);
-        if (m) return b + (__ffs(m) - 1);
+// <= 12 bytes at u[src..src+len) as the three payload words of an inlined cell
+__device__ __forceinline__ void inline_words(const uint8_t *u, int64_t src, uint32_t len, uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    w0 = len > 0 ? mask_bytes(ld32u(u, src), len) : 0u;
+    w1 = len > 4 ? mask_bytes(ld32u(u, src + 4), len - 4u) : 0u;
+    w2 = len > 8 ? mask_bytes(ld32u(u, src + 8), len - 8u) : 0u;
+}
+__device__ __forceinline__ void store_str_cell(uint8_t *col, uint32_t row, const uint8_t *u, int64_t src, uint32_t len, uint64_t hptr) {
+    if (len <= 12u) {
+        uint32_t w0, w1, w2;
+        inline_words(u, src, len, w0, w1, w2);
+        store_cell(col, row, len, w0, w1, w2);
+    } else store_cell(col, row, len, ld32u(u, src), (uint32_t)hptr, (uint32_t)(hptr >> 32));
+}
+// two packed bytes (b0 | b1 << 8) of 4-bit bases, first base in the high nibble (bam_seqi, htslib/sam.h:325) ->
+// four characters of "=ACMGRSVTWYHKDBN" (seq_nt16_str, htslib/hts.c:260) by byte permutes
+__device__ __forceinline__ uint32_t seq4(uint32_t h) {
+    const uint32_t s = ((h & 0x0f0fu) << 4) | ((h >> 4) & 0x0f0fu);   // nibbles in base order
+    const uint32_t s7 = s & 0x7777u;
+    const uint32_t a = __byte_perm(0x4d43413du, 0x56535247u, s7);     // "=ACM" "GRSV"
+    const uint32_t b = __byte_perm(0x48595754u, 0x4e42444bu, s7);     // "TWYH" "KDBN"
+    return __byte_perm(a, b, 0x3210u | ((s & 0x8888u) >> 1));
+}
+// per-byte +33 mod 256 (qual_to_string, bam_reader.c:400-404)
+__device__ __forceinline__ uint32_t qual4(uint32_t w) { return ((w & 0x7f7f7f7fu) + 0x21212121u) ^ (w & 0x80808080u); }
+// index of the first zero byte of w (0..3), 4 if none
+__device__ __forceinline__ uint32_t first_zero_byte(uint32_t w) {
+    const uint32_t z = (w - 0x01010101u) & ~w & 0x80808080u;
+    return z ? (uint32_t)(__ffs(z) - 1) >> 3 : 4u;
+}
+// bam_aux_get (sam.c:4832-4855) for one lane's record, skipping a CG tag consumed by bam_tag2cigar:
+// offset of the type byte of the first entry with this tag, or NONE (absent, or present but malformed)
+__device__ __forceinline__ int64_t aux_find(const uint8_t *u, const Rec &r, uint32_t tg) {
+    if (r.end - r.aux <= 2) return NONE;
+    int64_t s = r.aux + 2;
+    for (;;) {
+        if (s - 2 == r.cg_lo) {
+            if (r.end - r.cg_hi <= 2) return NONE;
+            s = r.cg_hi + 2;
+            continue;
+        }
+        bool complete;
+        const int64_t nx = skip_aux_scalar(u, s, r.end, &complete);
+        if ((ld8(u, s - 2) | (ld8(u, s - 1) << 8)) == tg) return (nx == NONE || !complete) ? NONE : s;
+        if (nx == NONE || r.end - nx <= 2) return NONE;
+        s = nx + 2;
     }
-    return end;
+}
+// bam_aux2Z view of a hit: length of the NUL-terminated value, or -1 if the entry is not Z/H (-> NULL)
+__device__ __forceinline__ int32_t aux_zlen(const uint8_t *u, const Rec &r, int64_t h) {
+    if (h == NONE) return -1;
+    const uint32_t ty = ld8(u, h);
+    if (ty != 'Z' && ty != 'H') return -1;
+    int64_t z = h + 1;
+    while (z < r.end && ld8(u, z) != 0) ++z;
+    return (int32_t)(z - (h + 1));
+}
+// per-lane copy of a long aux string into its heap slot (rare: Z values longer than 12 bytes)
+__device__ __forceinline__ void copy_bytes(uint8_t *dst, const uint8_t *u, int64_t src, uint32_t len) {
+    uint32_t *d = reinterpret_cast<uint32_t *>(dst);
+    for (uint32_t k = 0; 4u * k < len; ++k) d[k] = mask_bytes(ld32u(u, src + 4ll * k), len - 4u * k);
+}
+// <= 12 characters of CIGAR text in three words (cigar_to_kstring, bam_reader.c:375-383)
+__device__ __forceinline__ void cigar_inline(const uint8_t *u, const Rec &r, uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    w0 = w1 = w2 = 0u;
+    uint32_t pos = 0;
+    for (uint32_t i = 0; i < r.cig_n; ++i) {
+        const uint32_t c = ld32u(u, r.cigar + 4ll * i);
+        uint32_t v = c >> 4;
+        const uint32_t nd = dec_digits(v);
+        for (uint32_t j = nd + 1u; j-- > 0;) {                       // op char last, digits right to left
+            uint32_t ch;
+            if (j == nd) ch = (uint32_t)"MIDNSHP=XB??????"[c & 15u];   // BAM_CIGAR_STR, sam.h:112-130
+            else { ch = '0' + v % 10u; v /= 10u; }
+            const uint32_t q = pos + j, sh = 8u * (q & 3u);
+            w0 |= (q >> 2) == 0u ? ch << sh : 0u;
+            w1 |= (q >> 2) == 1u ? ch << sh : 0u;
+            w2 |= (q >> 2) == 2u ? ch << sh : 0u;
+        }
+        pos += nd + 1u;
+    }
 }
 
 __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__ DecodeParams p, const ScanTables t) {
-    __shared__ uint32_t stage_all[4][4];  // per warp: first 16 chars of the CIGAR text
-    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
-    const uint32_t bi = p.b_lo + blockIdx.x * 4u + wib;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t bi = p.b_lo + blockIdx.x * 4u + (threadIdx.x >> 5);
     if (bi >= p.b_hi) return;
-    uint8_t *stage = reinterpret_cast<uint8_t *>(stage_all[wib]);
+    const uint32_t count = p.walk[bi].count;
+    if (!count) return;
     const uint8_t *u = p.u;
-    const BlockWalk bw = p.walk[bi];
-    int64_t off = bw.entry;
-    uint32_t row = p.row_base[bi];
-    uint64_t hp = p.heap_base[bi];
+    const int64_t bstart = p.blk_start[bi];
+    const uint16_t *rec = p.rec + ((bstart - p.rec_bias) / 36 + (int64_t)bi);
     const uint64_t mask = t.col_mask;
-    // tag requests owned by this lane: k0 = lane, k1 = lane + 32; request n_tags is the internal RG lookup
-    const uint32_t n_req = t.n_tags + 1u;
-    uint32_t rq_tag[2], rq_type[2];
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        uint32_t k = lane + 32u * j;
-        if (k < t.n_tags) { rq_tag[j] = t.tags[k].t0 | (t.tags[k].t1 << 8); rq_type[j] = t.tags[k].type; }
-        else if (k == t.n_tags) { rq_tag[j] = 'R' | ('G' << 8); rq_type[j] = 'Z'; }
-        else { rq_tag[j] = 0xffffffffu; rq_type[j] = 0; }
-    }
-    const bool any_tag_cols = (mask >> COL_RG) != 0;  // RG, SAMPLE or any tag column
+    const bool cQ = (mask >> COL_QNAME) & 1, cC = (mask >> COL_CIGAR) & 1, cS = (mask >> COL_SEQ) & 1, cU = (mask >> COL_QUAL) & 1,
+               cRG = (mask >> COL_RG) & 1, cSM = (mask >> COL_SAMPLE) & 1;
+    const bool any_tag_cols = (mask >> BAM_CORE_COLS) != 0;
+    uint32_t row0 = p.row_base[bi];
+    uint64_t hp = p.heap_base[bi];
 
-    for (uint32_t rec_i = 0; rec_i < bw.count; ++rec_i, ++row) {
+    for (uint32_t g = 0; g < count; g += 32u, row0 += 32u) {
+        const uint32_t cnt = count - g < 32u ? count - g : 32u;
+        const bool act = lane < cnt;
+        const uint32_t row = row0 + lane;
+        // ---------------- A: own record ----------------
         Rec r;
-        // counts/entries come from the validated walk, so this cannot fail; is_final=false keeps it cheap
-        parse_record(u, off, INT64_MAX / 2, false, t.n_ref, r);  // (off may be negative: carried bytes)
-        // ---- fixed-width columns (bam_reader.c:790-855): one lane each ----
-        if (lane == 0 && ((mask >> COL_FLAG) & 1)) reinterpret_cast<uint16_t *>(p.col[COL_FLAG])[row] = (uint16_t)r.flag;
-        if (lane == 1 && ((mask >> COL_POS) & 1)) reinterpret_cast<int64_t *>(p.col[COL_POS])[row] = (int64_t)r.pos + 1;
-        if (lane == 2 && ((mask >> COL_MAPQ) & 1)) reinterpret_cast<int32_t *>(p.col[COL_MAPQ])[row] = (int32_t)r.mapq;
-        if (lane == 3 && ((mask >> COL_PNEXT) & 1)) reinterpret_cast<int64_t *>(p.col[COL_PNEXT])[row] = (int64_t)r.mpos + 1;
-        if (lane == 4 && ((mask >> COL_TLEN) & 1)) reinterpret_cast<int64_t *>(p.col[COL_TLEN])[row] = (int64_t)r.isize;
-        if (lane == 5 && ((mask >> COL_RNAME) & 1))
-            reinterpret_cast<uint4 *>(p.col[COL_RNAME])[row] = reinterpret_cast<const uint4 *>(t.ref_cells)[r.tid >= 0 ? r.tid : t.n_ref];
-        if (lane == 6 && ((mask >> COL_RNEXT) & 1))
-            reinterpret_cast<uint4 *>(p.col[COL_RNEXT])[row] = reinterpret_cast<const uint4 *>(t.ref_cells)[r.mtid >= 0 ? r.mtid : t.n_ref];
-        // ---- QNAME: C string, at most l_qname bytes (missing-NUL fix-up, sam.c:828-832) ----
-        if ((mask >> COL_QNAME) & 1) {
-            int64_t z = find_nul(u, r.qname, r.qname + r.l_qname, lane);
-            emit_str(p, COL_QNAME, row, u, r.qname, (uint32_t)(z - r.qname), r.l_qname, hp, lane);
+        r.off = r.end = r.qname = r.cigar = r.seq = r.qual = r.aux = 0;
+        r.cg_lo = r.cg_hi = NONE;
+        r.block_len = r.n_cigar = r.cig_n = r.flag = r.mapq = r.cigar_text_len = 0u;
+        r.l_qname = 1u;
+        r.tid = r.pos = r.mtid = r.mpos = r.isize = -1;
+        r.l_qseq = 0;
+        uint32_t roff = 0;
+        if (act) {
+            roff = rec[g + lane];
+            // entries and counts come from the validated walk, so this cannot fail; is_final = false keeps it cheap
+            parse_record(u, bstart + roff, INT64_MAX / 2, false, t.n_ref, r);
+            if ((mask >> COL_FLAG) & 1) reinterpret_cast<uint16_t *>(p.col[COL_FLAG])[row] = (uint16_t)r.flag;
+            if ((mask >> COL_POS) & 1) reinterpret_cast<int64_t *>(p.col[COL_POS])[row] = (int64_t)r.pos + 1;
+            if ((mask >> COL_MAPQ) & 1) reinterpret_cast<int32_t *>(p.col[COL_MAPQ])[row] = (int32_t)r.mapq;
+            if ((mask >> COL_PNEXT) & 1) reinterpret_cast<int64_t *>(p.col[COL_PNEXT])[row] = (int64_t)r.mpos + 1;
+            if ((mask >> COL_TLEN) & 1) reinterpret_cast<int64_t *>(p.col[COL_TLEN])[row] = (int64_t)r.isize;
+            if ((mask >> COL_RNAME) & 1)
+                reinterpret_cast<uint4 *>(p.col[COL_RNAME])[row] = reinterpret_cast<const uint4 *>(t.ref_cells)[r.tid >= 0 ? r.tid : t.n_ref];
+            if ((mask >> COL_RNEXT) & 1)
+                reinterpret_cast<uint4 *>(p.col[COL_RNEXT])[row] = reinterpret_cast<const uint4 *>(t.ref_cells)[r.mtid >= 0 ? r.mtid : t.n_ref];
         }
-        // ---- CIGAR text (cigar_to_kstring, bam_reader.c:375-383; "*" when n_cigar == 0, :819-834) ----
-        if ((mask >> COL_CIGAR) & 1) {
-            const uint32_t L = r.cigar_text_len;
-            if (r.cig_n == 0) {
-                if (lane == 0) store_cell(p.col[COL_CIGAR], row, 1, '*', 0, 0);
-            } else {
-                uint64_t slot = hp;
-                hp += slot_bytes(L);
-                uint8_t *dst = L > 12u ? p.heap + slot : nullptr;
-                if (lane < 4) reinterpret_cast<uint32_t *>(stage)[lane] = 0;
-                __syncwarp();
+        const uint32_t L = (uint32_t)r.l_qseq;
+        const bool absent = !act || qual_absent(u, r);
+        // QNAME is a C string of at most l_qname bytes (missing-NUL fix-up, sam.c:828-832)
+        uint32_t qn = r.l_qname;
+        if (act && cQ) {
+            for (uint32_t k = 0; k < r.l_qname; k += 4u) {
+                const uint32_t z = first_zero_byte(ld32u(u, r.qname + k));
+                if (z < 4u) { if (k + z < qn) qn = k + z; break; }
+            }
+        }
+        // ---------------- B: heap slots (the same rules as the walk; 4-byte aligned, in this order) ----------------
+        uint32_t need = 0;
+        if (act) {
+            if (cQ) need += slot_bytes(r.l_qname);
+            if (cC) need += slot_bytes(r.cigar_text_len);
+            if (cS) need += slot_bytes(L);
+            if (cU && !absent) need += slot_bytes(L);
+        }
+        const uint32_t aux_slot0 = need;   // long Z values follow, in request order (tags, then RG)
+        int64_t h_rg = NONE;
+        int32_t z_rg = -1;
+        if (act && (cRG || cSM)) {
+            h_rg = aux_find(u, r, 'R' | ('G' << 8));
+            z_rg = aux_zlen(u, r, h_rg);
+        }
+        if (act && any_tag_cols)
+            for (uint32_t k = 0; k < t.n_tags; ++k) {
+                if (t.tags[k].type != 'Z' || !((mask >> (BAM_CORE_COLS + k)) & 1ull)) continue;
+                const int32_t zl = aux_zlen(u, r, aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8)));
+                if (zl > 12) need += align4((uint32_t)zl);
+            }
+        if (act && cRG && z_rg > 12) need += align4((uint32_t)z_rg);
+        uint32_t incl = need;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, sft); if (lane >= (uint32_t)sft) incl += v; }
+        const uint32_t rel = incl - need;                       // this record's first slot, relative to hp
+        const uint32_t total = __shfl_sync(FULL, incl, 31);
+        // ---------------- C: long strings, record by record, whole warp ----------------
+        uint32_t qcut = L;                                      // QUAL is strlen-truncated: first produced NUL
+        const uint32_t lqnc = r.l_qname | (r.n_cigar << 8), lab = L | (absent ? 0x80000000u : 0u);
+        for (uint32_t q = 0; q < cnt; ++q) {
+            const uint32_t o_ = __shfl_sync(FULL, roff, q), lq_ = __shfl_sync(FULL, lqnc, q), la_ = __shfl_sync(FULL, lab, q),
+                           ct_ = __shfl_sync(FULL, r.cigar_text_len, q), rel_ = __shfl_sync(FULL, rel, q);
+            const uint32_t lqn = lq_ & 0xffu, ncg = lq_ >> 8, Lq = la_ & 0x7fffffffu;
+            const int64_t qname = bstart + o_ + 36, seq = qname + lqn + 4ll * ncg, qual = seq + (((int64_t)Lq + 1) >> 1);
+            uint8_t *slot = p.heap + hp + rel_;
+            if (cQ && lqn > 12u) {
+                uint32_t *d = reinterpret_cast<uint32_t *>(slot);
+                for (uint32_t k = lane; 4u * k < lqn; k += 32u) d[k] = mask_bytes(ld32u(u, qname + 4ll * k), lqn - 4u * k);
+                slot += align4(lqn);
+            }
+            if (cC && ct_ > 12u) {
+                // long CIGAR text: lanes take operations, a warp scan of the text widths places them
+                const int64_t cig = bstart + __shfl_sync(FULL, (int32_t)(r.cigar - bstart), q);
+                const uint32_t cn = __shfl_sync(FULL, r.cig_n, q);
                 uint32_t base = 0;
-                for (uint32_t k0 = 0; k0 < r.cig_n; k0 += 32u) {
-                    uint32_t k = k0 + lane, c = 0, d = 0;
-                    if (k < r.cig_n) { c = ld32u(u, r.cigar + 4ll * k); d = dec_digits(c >> 4) + 1u; }
-                    uint32_t incl = d;  // inclusive warp scan of d
+                for (uint32_t k0 = 0; k0 < cn; k0 += 32u) {
+                    const uint32_t k = k0 + lane;
+                    uint32_t c = 0, dgt = 0;
+                    if (k < cn) { c = ld32u(u, cig + 4ll * k); dgt = dec_digits(c >> 4) + 1u; }
+                    uint32_t inc = dgt;
 #pragma unroll
-                    for (int s = 1; s < 32; s <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, s); if (lane >= (uint32_t)s) incl += v; }
-                    uint32_t o = base + incl - d;
-                    if (k < r.cig_n) {
-                        uint32_t v = c >> 4, q = o + d - 1;
-                        const char opc = "MIDNSHP=XB??????"[c & 15u];  // BAM_CIGAR_STR, sam.h:112-130
-                        if (dst) dst[q] = (uint8_t)opc;
-                        if (q < 16u) stage[q] = (uint8_t)opc;
-                        for (uint32_t j = d - 1; j-- > 0;) {
-                            uint32_t dg = '0' + v % 10u;
-                            v /= 10u;
-                            if (dst) dst[o + j] = (uint8_t)dg;
-                            if (o + j < 16u) stage[o + j] = (uint8_t)dg;
+                    for (int sft = 1; sft < 32; sft <<= 1) { const uint32_t v = __shfl_up_sync(FULL, inc, sft); if (lane >= (uint32_t)sft) inc += v; }
+                    if (k < cn) {
+                        uint32_t v = c >> 4, at = base + inc - 1u;
+                        slot[at] = (uint8_t)"MIDNSHP=XB??????"[c & 15u];
+                        for (uint32_t j = dgt - 1u; j-- > 0;) { slot[--at] = (uint8_t)('0' + v % 10u); v /= 10u; }
+                    }
+                    base += __shfl_sync(FULL, inc, 31);
+                }
+                slot += align4(ct_);
+            }
+            if (cS && Lq > 12u) {
+                uint32_t *d = reinterpret_cast<uint32_t *>(slot);
+                for (uint32_t k = lane; 8u * k < Lq; k += 32u) {             // 4 packed bytes -> 8 characters per lane
+                    const uint32_t pk = ld32u(u, seq + 4ll * k);
+                    d[2u * k] = mask_bytes(seq4(pk & 0xffffu), Lq - 8u * k);
+                    if (8u * k + 4u < Lq) d[2u * k + 1u] = mask_bytes(seq4(pk >> 16), Lq - 8u * k - 4u);
+                }
+                slot += align4(Lq);
+            }
+            if (cU && !(la_ >> 31) && Lq > 12u) {
+                uint32_t *d = reinterpret_cast<uint32_t *>(slot);
+                uint32_t zpos = 0xffffffffu;
+                for (uint32_t k = lane; 8u * k < Lq; k += 32u) {
+                    const uint32_t a = mask_bytes(qual4(ld32u(u, qual + 8ll * k)), Lq - 8u * k) | (Lq - 8u * k < 4u ? 0xffffffffu << (8u * (Lq - 8u * k)) : 0u);
+                    d[2u * k] = mask_bytes(a, Lq - 8u * k);
+                    uint32_t z = first_zero_byte(a);
+                    if (z < 4u && zpos == 0xffffffffu) zpos = 8u * k + z;
+                    if (8u * k + 4u < Lq) {
+                        const uint32_t rem = Lq - 8u * k - 4u;
+                        const uint32_t b = mask_bytes(qual4(ld32u(u, qual + 8ll * k + 4)), rem) | (rem < 4u ? 0xffffffffu << (8u * rem) : 0u);
+                        d[2u * k + 1u] = mask_bytes(b, rem);
+                        z = first_zero_byte(b);
+                        if (z < 4u && zpos == 0xffffffffu) zpos = 8u * k + 4u + z;
+                    }
+                }
+                zpos = __reduce_min_sync(FULL, zpos);
+                if (lane == q && zpos < qcut) qcut = zpos;
+            }
+        }
+        __syncwarp();   // the heap of this step is complete (cells below read CIGAR prefixes back)
+        // ---------------- D: cells and tag values of the lane's own row ----------------
+        const uint64_t hbase = p.heap_host + hp + rel;          // host address of this record's first slot
+        if (act) {
+            uint64_t hs = hbase;
+            if (cQ) { store_str_cell(p.col[COL_QNAME], row, u, r.qname, qn, hs); hs += slot_bytes(r.l_qname); }
+            if (cC) {
+                // cigar_to_kstring (bam_reader.c:375-383); "*" when n_cigar == 0 (:819-834)
+                const uint32_t ctl = r.cigar_text_len;
+                if (r.cig_n == 0u) store_cell(p.col[COL_CIGAR], row, 1, '*', 0, 0);
+                else if (ctl <= 12u) { uint32_t w0, w1, w2; cigar_inline(u, r, w0, w1, w2); store_cell(p.col[COL_CIGAR], row, ctl, w0, w1, w2); }
+                else store_cell(p.col[COL_CIGAR], row, ctl, *reinterpret_cast<const uint32_t *>(p.heap + (hs - p.heap_host)), (uint32_t)hs, (uint32_t)(hs >> 32));
+                hs += slot_bytes(ctl);
+            }
+            if (cS) {
+                // seq_to_string (bam_reader.c:390-394); "*" when l_qseq == 0 (:857-866)
+                if (L == 0u) store_cell(p.col[COL_SEQ], row, 1, '*', 0, 0);
+                else if (L <= 12u) {
+                    const uint32_t p0 = ld32u(u, r.seq), p1 = L > 8u ? ld32u(u, r.seq + 4) : 0u;
+                    store_cell(p.col[COL_SEQ], row, L, mask_bytes(seq4(p0 & 0xffffu), L), L > 4u ? mask_bytes(seq4(p0 >> 16), L - 4u) : 0u,
+                               L > 8u ? mask_bytes(seq4(p1 & 0xffffu), L - 8u) : 0u);
+                } else store_cell(p.col[COL_SEQ], row, L, seq4(ld32u(u, r.seq) & 0xffffu), (uint32_t)hs, (uint32_t)(hs >> 32));
+                hs += slot_bytes(L);
+            }
+            if (cU) {
+                // qual_to_string (bam_reader.c:400-404); "*" if absent (:868-877); strlen semantics
+                if (absent) store_cell(p.col[COL_QUAL], row, 1, '*', 0, 0);
+                else {
+                    uint32_t w0 = mask_bytes(qual4(ld32u(u, r.qual)), L), w1 = L > 4u ? mask_bytes(qual4(ld32u(u, r.qual + 4)), L - 4u) : 0u,
+                             w2 = L > 8u ? mask_bytes(qual4(ld32u(u, r.qual + 8)), L - 8u) : 0u;
+                    uint32_t cut = qcut;
+                    if (L <= 12u) {                               // short reads never went through step C
+                        uint32_t z = first_zero_byte(w0 | (L < 4u ? 0xffffffffu << (8u * L) : 0u));
+                        if (z < 4u) cut = z;
+                        else if (L > 4u && (z = first_zero_byte(w1 | (L < 8u ? 0xffffffffu << (8u * (L - 4u)) : 0u))) < 4u) cut = 4u + z;
+                        else if (L > 8u && (z = first_zero_byte(w2 | (L < 12u ? 0xffffffffu << (8u * (L - 8u)) : 0u))) < 4u) cut = 8u + z;
+                    }
+                    if (cut <= 12u) store_cell(p.col[COL_QUAL], row, cut, mask_bytes(w0, cut), cut > 4u ? mask_bytes(w1, cut - 4u) : 0u,
+                                               cut > 8u ? mask_bytes(w2, cut - 8u) : 0u);
+                    else store_cell(p.col[COL_QUAL], row, cut, w0, (uint32_t)hs, (uint32_t)(hs >> 32));
+                    hs += slot_bytes(L);
+                }
+            }
+        }
+        // typed standard tags (bam_reader.c:920-966): 'i' bam_aux2i, 'f' bam_aux2f, 'A' bam_aux2A, 'Z' bam_aux2Z
+        uint64_t hz = hbase + aux_slot0;                        // long Z values, in request order
+        if (any_tag_cols)
+            for (uint32_t k = 0; k < t.n_tags; ++k) {
+                const int c = BAM_CORE_COLS + (int)k;
+                if (!((mask >> c) & 1ull)) continue;
+                const uint32_t ty_req = t.tags[k].type;
+                bool valid = false;
+                if (act) {
+                    const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
+                    if (ty_req == 'Z') {
+                        const int32_t zl = aux_zlen(u, r, a);        // NULL for any non-Z/H type (bam_aux2Z)
+                        if (zl >= 0) {
+                            valid = true;
+                            if (zl > 12) copy_bytes(p.heap + (hz - p.heap_host), u, a + 1, (uint32_t)zl);
+                            store_str_cell(p.col[c], row, u, a + 1, (uint32_t)zl, hz);
+                            if (zl > 12) hz += align4((uint32_t)zl);
+                        } else store_cell(p.col[c], row, 0, 0, 0, 0);
+                    } else if (a == NONE) {
+                        if (ty_req == 'A') store_cell(p.col[c], row, 0, 0, 0, 0);
+                    } else {
+                        valid = true;
+                        const uint32_t ty = ld8(u, a);
+                        int64_t iv = 0;
+                        bool is_int = true;
+                        switch (ty) {
+                        case 'c': iv = (int8_t)ld8(u, a + 1); break;
+                        case 'C': iv = ld8(u, a + 1); break;
+                        case 's': iv = (int16_t)(ld8(u, a + 1) | (ld8(u, a + 2) << 8)); break;
+                        case 'S': iv = ld8(u, a + 1) | (ld8(u, a + 2) << 8); break;
+                        case 'i': iv = (int32_t)ld32u(u, a + 1); break;
+                        case 'I': iv = ld32u(u, a + 1); break;
+                        default: is_int = false; break;
+                        }
+                        if (ty_req == 'i') reinterpret_cast<int64_t *>(p.col[c])[row] = iv;   // non-integer type -> 0
+                        else if (ty_req == 'f') {
+                            double dv;
+                            if (ty == 'd') dv = __longlong_as_double(((long long)ld32u(u, a + 5) << 32) | ld32u(u, a + 1));
+                            else if (ty == 'f') dv = (double)__uint_as_float(ld32u(u, a + 1));
+                            else dv = is_int ? (double)iv : 0.0;
+                            reinterpret_cast<double *>(p.col[c])[row] = dv;
+                        } else {  // 'A': one character, or "" on a type mismatch (bam_aux2A returns 0)
+                            const uint32_t ch = ty == 'A' ? ld8(u, a + 1) : 0u;
+                            store_cell(p.col[c], row, ch ? 1u : 0u, ch, 0, 0);
                         }
                     }
-                    base += __shfl_sync(FULL, incl, 31);
                 }
-                __syncwarp();
-                if (lane == 0) {
-                    const uint32_t *sw = reinterpret_cast<const uint32_t *>(stage);
-                    if (L <= 12u) store_cell(p.col[COL_CIGAR], row, L, sw[0], sw[1], sw[2]);
-                    else { uint64_t hptr = p.heap_host + slot; store_cell(p.col[COL_CIGAR], row, L, sw[0], (uint32_t)hptr, (uint32_t)(hptr >> 32)); }
-                }
-                __syncwarp();
+                set_valid_group(p.valid[c], row0, __ballot_sync(FULL, valid), lane);
             }
+        // READ_GROUP_ID / SAMPLE_ID (bam_reader.c:879-918): RG:Z value; SM of the first @RG line with that ID
+        if (cRG) {
+            if (act) {
+                if (z_rg >= 0) {
+                    if (z_rg > 12) copy_bytes(p.heap + (hz - p.heap_host), u, h_rg + 1, (uint32_t)z_rg);
+                    store_str_cell(p.col[COL_RG], row, u, h_rg + 1, (uint32_t)z_rg, hz);
+                } else store_cell(p.col[COL_RG], row, 0, 0, 0, 0);
+            }
+            set_valid_group(p.valid[COL_RG], row0, __ballot_sync(FULL, act && z_rg >= 0), lane);
         }
-        // ---- SEQ: 4-bit nibbles -> ASCII (seq_to_string, bam_reader.c:390-394; "*" when l_qseq == 0) ----
-        if ((mask >> COL_SEQ) & 1) {
-            const uint32_t L = (uint32_t)r.l_qseq;
-            const uint64_t LUT_LO = 0x565352474d43413dull, LUT_HI = 0x4e42444b48595754ull;  // "=ACMGRSV" "TWYHKDBN"
-            auto nt = [&](uint32_t c) -> uint32_t { return (uint32_t)(((c & 8u) ? LUT_HI : LUT_LO) >> (8u * (c & 7u))) & 0xffu; };
-            auto word = [&](uint32_t k) -> uint32_t {  // chars 4k..4k+3
-                uint32_t b0 = ld8(u, r.seq + 2ll * k), b1 = (4u * k + 2u < L) ? ld8(u, r.seq + 2ll * k + 1) : 0u;
-                uint32_t v = nt(b0 >> 4) | (nt(b0 & 15u) << 8) | (nt(b1 >> 4) << 16) | (nt(b1 & 15u) << 24);
-                return mask_bytes(v, L - 4u * k);
-            };
-            if (L == 0) { if (lane == 0) store_cell(p.col[COL_SEQ], row, 1, '*', 0, 0); }
-            else if (L <= 12u) {
-                if (lane == 0) store_cell(p.col[COL_SEQ], row, L, word(0), L > 4 ? word(1) : 0u, L > 8 ? word(2) : 0u);
-            } else {
-                uint64_t slot = hp;
-                hp += align4(L);
-                uint32_t *dst = reinterpret_cast<uint32_t *>(p.heap + slot);
-                uint32_t words = (L + 3u) >> 2;
-                for (uint32_t k = lane; k < words; k += 32u) dst[k] = word(k);
-                if (lane == 0) { uint64_t hptr = p.heap_host + slot; store_cell(p.col[COL_SEQ], row, L, word(0), (uint32_t)hptr, (uint32_t)(hptr >> 32)); }
+        if (cSM) {
+            int found = -1;
+            if (act && z_rg >= 0)
+                for (uint32_t e = 0; e < t.n_rg && found < 0; ++e) {
+                    if (t.rg[e].id_len != (uint32_t)z_rg) continue;
+                    const uint8_t *id = t.rg_ids + t.rg[e].id_off;
+                    bool m = true;
+                    for (int32_t q = 0; q < z_rg && m; ++q) m = id[q] == ld8(u, h_rg + 1 + q);
+                    if (m) found = (int)e;
+                }
+            const bool ok = found >= 0 && t.rg[found].has_sample;
+            if (act) {
+                if (ok) reinterpret_cast<uint4 *>(p.col[COL_SAMPLE])[row] = *reinterpret_cast<const uint4 *>(&t.rg[found].sample);
+                else store_cell(p.col[COL_SAMPLE], row, 0, 0, 0, 0);
             }
+            set_valid_group(p.valid[COL_SAMPLE], row0, __ballot_sync(FULL, ok), lane);
         }
-        // ---- QUAL + 33 (qual_to_string, bam_reader.c:400-404; "*" if absent; strlen-truncated) ----
-        if ((mask >> COL_QUAL) & 1) {
-            if (qual_absent(u, r)) { if (lane == 0) store_cell(p.col[COL_QUAL], row, 1, '*', 0, 0); }
-            else {
-                const uint32_t L = (uint32_t)r.l_qseq;
-                uint64_t slot = hp;
-                hp += slot_bytes(L);
-                auto word = [&](uint32_t k) -> uint32_t {
-                    uint32_t w = mask_bytes(ld32u(u, r.qual + 4ll * k), L - 4u * k);
-                    uint32_t s = ((w & 0x7f7f7f7fu) + 0x21212121u) ^ (w & 0x80808080u);  // per-byte +33 mod 256
-                    return mask_bytes(s, L - 4u * k);
-                };
-                uint32_t words = (L + 3u) >> 2, cut = L;  // cut = position of the first produced NUL (q == 223)
-                uint32_t *dst = L > 12u ? reinterpret_cast<uint32_t *>(p.heap + slot) : nullptr;
-                for (uint32_t k0 = 0; k0 < words; k0 += 32u) {
-                    uint32_t k = k0 + lane, w = 0x01010101u, zpos = 0xffffffffu;
-                    if (k < words) {
-                        w = word(k);
-                        if (dst) dst[k] = w;
-                        uint32_t nv = L - 4u * k < 4u ? L - 4u * k : 4u;
-                        for (uint32_t j = 0; j < nv; ++j)
-                            if (((w >> (8u * j)) & 0xffu) == 0u) { zpos = 4u * k + j; break; }
-                    }
-#pragma unroll
-                    for (int s = 16; s > 0; s >>= 1) { uint32_t o = __shfl_xor_sync(FULL, zpos, s); zpos = o < zpos ? o : zpos; }
-                    if (zpos < cut) cut = zpos;
-                }
-                if (lane == 0) {
-                    if (cut <= 12u) store_cell(p.col[COL_QUAL], row, cut, cut > 0 ? mask_bytes(word(0), cut) : 0u,
-                                               cut > 4 ? mask_bytes(word(1), cut - 4u) : 0u, cut > 8 ? mask_bytes(word(2), cut - 8u) : 0u);
-                    else { uint64_t hptr = p.heap_host + slot; store_cell(p.col[COL_QUAL], row, cut, word(0), (uint32_t)hptr, (uint32_t)(hptr >> 32)); }
-                }
-            }
-        }
-        // ---- aux tags: READ_GROUP_ID, SAMPLE_ID, typed standard tags ----
-        if (any_tag_cols) {
-            // hit*: 0 = absent, -1 = decided NULL (matched but invalid), else offset of the type byte relative to the record
-            int32_t hit0 = 0, hit1 = 0;
-            if (r.end - r.aux > 2) {
-                int64_t s = r.aux + 2;
-                for (;;) {
-                    if (s - 2 == r.cg_lo) {
-                        if (r.end - r.cg_hi <= 2) break;
-                        s = r.cg_hi + 2;
-                        continue;
-                    }
-                    // skip_aux, with the Z/H scan done lane-parallel
-                    uint32_t ty = ld8(u, s);
-                    int size = aux_type2size(ty);
-                    int64_t nx;
-                    bool complete = true;
-                    if (size == 'Z' || size == 'H') {
-                        int64_t z = find_nul(u, s + 1, r.end, lane);
-                        complete = z < r.end;
-                        nx = complete ? z + 1 : r.end;
-                    } else nx = skip_aux_scalar(u, s, r.end, &complete);
-                    uint32_t tg = ld8(u, s - 2) | (ld8(u, s - 1) << 8);
-                    const int32_t hv = (nx == NONE || !complete) ? -1 : (int32_t)(s - r.off);
-                    if (hit0 == 0 && rq_tag[0] == tg) hit0 = hv;
-                    if (hit1 == 0 && rq_tag[1] == tg) hit1 = hv;
-                    if (nx == NONE || r.end - nx <= 2) break;
-                    s = nx + 2;
-                }
-            }
-            // numeric / char columns: the owning lane converts (bam_aux2i / bam_aux2f / bam_aux2A, sam.c:5093-5141)
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                uint32_t k = lane + 32u * j;
-                if (k >= t.n_tags || !((mask >> (BAM_CORE_COLS + k)) & 1ull)) continue;
-                int c = BAM_CORE_COLS + (int)k;
-                if (rq_type[j] == 'Z') continue;
-                const int32_t hj = j ? hit1 : hit0;
-                if (hj <= 0) { if (rq_type[j] == 'A') store_cell(p.col[c], row, 0, 0, 0, 0); continue; }
-                int64_t a = r.off + hj;
-                uint32_t ty = ld8(u, a);
-                int64_t iv = 0;
-                bool is_int = true;
-                switch (ty) {
-                case 'c': iv = (int8_t)ld8(u, a + 1); break;
-                case 'C': iv = ld8(u, a + 1); break;
-                case 's': iv = (int16_t)(ld8(u, a + 1) | (ld8(u, a + 2) << 8)); break;
-                case 'S': iv = ld8(u, a + 1) | (ld8(u, a + 2) << 8); break;
-                case 'i': iv = (int32_t)ld32u(u, a + 1); break;
-                case 'I': iv = ld32u(u, a + 1); break;
-                default: is_int = false; break;
-                }
-                if (rq_type[j] == 'i') reinterpret_cast<int64_t *>(p.col[c])[row] = iv;  // non-integer type -> 0
-                else if (rq_type[j] == 'f') {
-                    double dv;
-                    if (ty == 'd') dv = __longlong_as_double(((long long)ld32u(u, a + 5) << 32) | ld32u(u, a + 1));
-                    else if (ty == 'f') dv = (double)__uint_as_float(ld32u(u, a + 1));
-                    else dv = is_int ? (double)iv : 0.0;
-                    reinterpret_cast<double *>(p.col[c])[row] = dv;
-                } else {  // 'A': one character, or "" on a type mismatch (bam_aux2A returns 0)
-                    uint32_t ch = ty == 'A' ? ld8(u, a + 1) : 0u;
-                    store_cell(p.col[c], row, ch ? 1u : 0u, ch, 0, 0);
-                }
-                set_valid(p.valid[c], row);
-            }
-            // string columns, one request at a time (warp-cooperative emit)
-            for (uint32_t k = 0; k < n_req; ++k) {
-                const bool is_rg = k == t.n_tags;
-                uint32_t ktype = __shfl_sync(FULL, (k >> 5) ? rq_type[1] : rq_type[0], k & 31u);
-                if (ktype != 'Z') continue;
-                int c = is_rg ? COL_RG : BAM_CORE_COLS + (int)k;
-                bool want_cell = is_rg ? ((mask >> COL_RG) & 1ull) : ((mask >> c) & 1ull);
-                bool want_sample = is_rg && ((mask >> COL_SAMPLE) & 1ull);
-                if (!want_cell && !want_sample) continue;
-                int32_t hrel = __shfl_sync(FULL, (k >> 5) ? hit1 : hit0, k & 31u);
-                int64_t h = r.off + hrel;
-                uint32_t ty = hrel > 0 ? ld8(u, h) : 0u;
-                bool ok = hrel > 0 && (ty == 'Z' || ty == 'H');   // bam_aux2Z: NULL for any other type
-                int64_t z = 0;
-                if (ok) z = find_nul(u, h + 1, r.end, lane);
-                uint32_t len = ok ? (uint32_t)(z - (h + 1)) : 0u;
-                if (want_cell) {
-                    if (ok) { emit_str(p, c, row, u, h + 1, len, len, hp, lane); if (lane == 0) set_valid(p.valid[c], row); }
-                    else if (lane == 0) store_cell(p.col[c], row, 0, 0, 0, 0);
-                }
-                if (want_sample) {
-                    // @RG ID -> SM dictionary (sam_hdr_find_tag_id, bam_reader.c:892-918): first @RG line with this ID
-                    int found = -1;
-                    if (ok) {
-                        for (uint32_t e0 = 0; e0 < t.n_rg && found < 0; e0 += 32u) {
-                            uint32_t e = e0 + lane;
-                            bool m = false;
-                            if (e < t.n_rg && t.rg[e].id_len == len) {
-                                m = true;
-                                const uint8_t *id = t.rg_ids + t.rg[e].id_off;
-                                for (uint32_t q = 0; q < len; ++q)
-                                    if (id[q] != ld8(u, h + 1 + q)) { m = false; break; }
-                            }
-                            unsigned bm = __ballot_sync(FULL, m);
-                            if (bm) found = (int)(e0 + __ffs(bm) - 1);
-                        }
-                    }
-                    if (lane == 0) {
-                        if (found >= 0 && t.rg[found].has_sample) {
-                            reinterpret_cast<uint4 *>(p.col[COL_SAMPLE])[row] = *reinterpret_cast<const uint4 *>(&t.rg[found].sample);
-                            set_valid(p.valid[COL_SAMPLE], row);
-                        } else store_cell(p.col[COL_SAMPLE], row, 0, 0, 0, 0);
-                    }
-                }
-            }
-        }
-        off = r.end;
+        hp += total;
     }
 }
+
 
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream) {
     if (p.n == 0) return cudaSuccess;

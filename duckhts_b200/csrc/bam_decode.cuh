@@ -64,11 +64,18 @@ struct WalkParams {
     int32_t is_final;          // 1: the data ends at seg_end (EOF): an incomplete record is an error, not a carry
     int64_t seg_end;
     int64_t limit_end;         // records starting at or after this offset are outside the scan range
+    // in-block offset of every record the walk accepts: block i's records sit at rec[(blk_start[i] - rec_bias) / 36 + i ...]
+    // (a record is at least 36 bytes, so the ranges of consecutive blocks cannot overlap)
+    uint16_t *rec;
+    int64_t rec_bias;          // = blk_start[0]
 };
 
 struct DecodeParams {
     const uint8_t *u;
-    const BlockWalk *walk;        // entry + count per block
+    const BlockWalk *walk;        // count per block
+    const int64_t *blk_start;     // block start offsets (as given to the walk)
+    const uint16_t *rec;          // record offsets written by the walk
+    int64_t rec_bias;
     const uint32_t *row_base;     // per block, relative to the batch
     const uint64_t *heap_base;    // per block, relative to the batch heap
     uint32_t b_lo, b_hi;          // blocks of this batch

@@ -686,4 +686,26 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     return cudaGetLastError();
 }
 
+
+// first failing block of a launch, written straight to (pinned host) memory: the scan pipeline learns the verdict
+// without a device-to-host copy that would queue behind the column batches on the copy engine
+__global__ void __launch_bounds__(256) status_first_bad_kernel(const int *__restrict__ status, uint32_t nblocks, int *__restrict__ out) {
+    __shared__ unsigned int first;
+    if (threadIdx.x == 0) first = 0xffffffffu;
+    __syncthreads();
+    unsigned int mine = 0xffffffffu;
+    for (uint32_t i = threadIdx.x; i < nblocks; i += 256u)
+        if (status[i] != 0) { mine = i; break; }
+    if (mine != 0xffffffffu) atomicMin(&first, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        out[1] = first == 0xffffffffu ? 0 : status[first];
+        out[0] = first == 0xffffffffu ? -1 : (int)first;
+    }
+}
+cudaError_t launch_status_first_bad(const int *status, uint32_t nblocks, int *out, cudaStream_t stream) {
+    status_first_bad_kernel<<<1, 256, 0, stream>>>(status, nblocks, out);
+    return cudaGetLastError();
+}
+
 }  // namespace dh

@@ -110,7 +110,8 @@ uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_ba
 }
 
 int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
-                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream) {
+                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream, int sm_limit) {
+    const int sms = sm_limit > 0 && sm_limit < c->sm_count ? sm_limit : c->sm_count;
     static const bool force_v1 = getenv("DH_INFLATE_V1") != nullptr;
     if (force_v1) {
         DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter, c->sm_count, stream, false));
@@ -119,7 +120,7 @@ int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint3
     }
     int rc = work.reserve(inflate_work_bytes(n, cmd_words));
     if (rc != DH_OK) return rc;
-    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, c->sm_count, stream));
+    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, sms, stream));
     DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, stream, true));
     c->launches += 3;
     return DH_OK;
@@ -379,6 +380,8 @@ dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size
         uint64_t cbase = d->bt.blocks[b].coffset & ~15ull;
         // a launch covers at most 2 GiB of compressed bytes (32-bit in_off) and 2^17 blocks (bounded work buffer)
         while (e < nb && e - b < (1u << 17) && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
+        const size_t quantum = (size_t)c->sm_count * 128u;   // streams phase 1 decodes at a time: launch whole rounds
+        if (e < nb && e - b > quantum) e = b + (e - b) / quantum * quantum;
         const uint64_t cw = fill_descs(d->bt, b, e, cbase, 0, 0, descs.data() + b);
         d->segs.push_back({b, e, cbase, cw});
         b = e;
@@ -512,6 +515,48 @@ int dh_measure_pcie(dh_ctx *c, uint64_t bytes, float *h2d_gbs, float *d2h_gbs) {
     if (d2h_gbs) *d2h_gbs = best_d2h;
     cudaError_t le = cudaGetLastError();
     if (le != cudaSuccess) return cuda_fail(le, "dh_measure_pcie");
+    return DH_OK;
+}
+
+// both directions at once on two streams: what the read_bam pipeline sees (compressed bytes in, columns out)
+int dh_measure_pcie_bidir(dh_ctx *c, uint64_t bytes, float *h2d_gbs, float *d2h_gbs) {
+    if (!c || !bytes) return DH_EINVAL;
+    DH_CUDA(cudaSetDevice(c->device));
+    void *h1 = nullptr, *h2 = nullptr, *d1 = nullptr, *d2 = nullptr;
+    DH_CUDA(cudaMallocHost(&h1, bytes));
+    DH_CUDA(cudaMallocHost(&h2, bytes));
+    if (cudaMalloc(&d1, bytes) != cudaSuccess || cudaMalloc(&d2, bytes) != cudaSuccess) {
+        cudaFreeHost(h1); cudaFreeHost(h2); cudaFree(d1);
+        return cuda_fail(cudaGetLastError(), "cudaMalloc");
+    }
+    memset(h1, 1, bytes);
+    memset(h2, 2, bytes);
+    cudaEvent_t a0, a1, b0, b1;
+    cudaEventCreate(&a0); cudaEventCreate(&a1); cudaEventCreate(&b0); cudaEventCreate(&b1);
+    float best_a = 0.f, best_b = 0.f;
+    for (int it = 0; it < 3; ++it) {
+        cudaEventRecord(a0, c->copy_streams[0]);
+        cudaEventRecord(b0, c->copy_streams[1]);
+        for (int r = 0; r < 4; ++r) {
+            cudaMemcpyAsync(d1, h1, bytes, cudaMemcpyHostToDevice, c->copy_streams[0]);
+            cudaMemcpyAsync(h2, d2, bytes, cudaMemcpyDeviceToHost, c->copy_streams[1]);
+        }
+        cudaEventRecord(a1, c->copy_streams[0]);
+        cudaEventRecord(b1, c->copy_streams[1]);
+        cudaEventSynchronize(a1);
+        cudaEventSynchronize(b1);
+        float ma, mb;
+        cudaEventElapsedTime(&ma, a0, a1);
+        cudaEventElapsedTime(&mb, b0, b1);
+        best_a = std::max(best_a, (float)(4.0 * bytes / 1e6 / ma));
+        best_b = std::max(best_b, (float)(4.0 * bytes / 1e6 / mb));
+    }
+    cudaEventDestroy(a0); cudaEventDestroy(a1); cudaEventDestroy(b0); cudaEventDestroy(b1);
+    cudaFree(d1); cudaFree(d2); cudaFreeHost(h1); cudaFreeHost(h2);
+    if (h2d_gbs) *h2d_gbs = best_a;
+    if (d2h_gbs) *d2h_gbs = best_b;
+    cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) return cuda_fail(le, "dh_measure_pcie_bidir");
     return DH_OK;
 }
 

@@ -3,8 +3,12 @@
 // Per segment of BGZF blocks:   H2D (pinned, copy stream)  ->  bgzf_inflate_kernel  ->  bam_walk_kernel
 //   -> host validates the boundary chain (entry[i] == exit[i-1]) and cuts the segment into row batches
 // per batch:                    bam_decode_kernel -> one D2H copy of the batch arena (columns + validity + heap)
-// Two segments and three batches are in flight so that H2D, the kernels and D2H overlap.  Everything the host
+// Four streams: H2D copies, inflate kernels, walk + decode kernels, D2H copies.  Three segments (the one being
+// decoded and two being uploaded/inflated ahead) and up to five batches are in flight, so the D2H copy engine --
+// the binding resource when every column returns to the host -- never waits for a kernel.  Everything the host
 // does per segment is O(#BGZF blocks) bookkeeping; no record or byte of payload is touched on the CPU.
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -20,7 +24,7 @@ using namespace dh;
 
 namespace {
 
-constexpr int NSEG = 2, NBATCH = 3;
+constexpr int NSEG = 3, NBATCH = 6;
 constexpr uint64_t A256 = 255;
 
 struct Batch {           // one output batch of the current segment
@@ -29,9 +33,11 @@ struct Batch {           // one output batch of the current segment
 };
 
 struct SegSlot {
-    DevBuf comp, out, desc, status, work, blk_start, entry, todo, walk, row_base, heap_base;
+    DevBuf comp, out, desc, status, work, rec;
+    int64_t rec_bias = 0;
     PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base;
-    cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_walk0 = nullptr, ev_walk1 = nullptr;
+    cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_inf_done = nullptr, ev_free = nullptr, ev_walk0 = nullptr,
+                ev_walk1 = nullptr, ev_walk2 = nullptr;
     size_t b0 = 0, b1 = 0;  // file block range
     uint64_t cbase = 0, obytes = 0;
     int issued_for = -1;    // segment index whose inflate was issued into this slot
@@ -40,7 +46,7 @@ struct SegSlot {
 struct BatchSlot {
     DevBuf arena;
     PinBuf h_arena;
-    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
+    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c0 = nullptr, ev_done = nullptr;
     dh_bam_batch desc;
     bool timed = false;
 };
@@ -96,7 +102,7 @@ struct dh_bam {
     bool to_eof = true;
     int64_t first_entry = 0;       // in-block offset of the first record of the scan
     dh_bam_scan_stats st;
-    std::vector<cudaEvent_t> inf_events;
+    cudaEvent_t ev_scan0 = nullptr;
 };
 
 namespace {
@@ -263,6 +269,10 @@ int upload_tables(dh_bam *b) {
 cudaStream_t s_comp(dh_bam *b) { return b->ctx->stream; }
 cudaStream_t s_copy(dh_bam *b) { return b->ctx->copy_streams[0]; }
 cudaStream_t s_d2h(dh_bam *b) { return b->ctx->copy_streams[1]; }
+cudaStream_t s_inf(dh_bam *b) { return b->ctx->copy_streams[2]; }
+// Phase 1 of the inflate is a persistent kernel that takes whole SMs (227 KB of shared memory each).  When batches go
+// back to the host, a few SMs stay free so that the decode kernels feeding the D2H copy engine are never locked out.
+int inflate_sms(const dh_bam *b) { return (b->mode & DH_BAM_DEVICE_OUTPUT) ? b->ctx->sm_count : b->ctx->sm_count - 8; }
 
 int ensure_events(dh_bam *b) {
     for (auto &s : b->ss)
@@ -270,13 +280,17 @@ int ensure_events(dh_bam *b) {
             DH_CUDA(cudaEventCreate(&s.ev_h2d));
             DH_CUDA(cudaEventCreate(&s.ev_inf0));
             DH_CUDA(cudaEventCreate(&s.ev_inf1));
+            DH_CUDA(cudaEventCreate(&s.ev_inf_done));
+            DH_CUDA(cudaEventCreate(&s.ev_free));
             DH_CUDA(cudaEventCreate(&s.ev_walk0));
             DH_CUDA(cudaEventCreate(&s.ev_walk1));
+            DH_CUDA(cudaEventCreate(&s.ev_walk2));
         }
     for (auto &s : b->bs)
         if (!s.ev_done) {
             DH_CUDA(cudaEventCreate(&s.ev_k0));
             DH_CUDA(cudaEventCreate(&s.ev_k1));
+            DH_CUDA(cudaEventCreate(&s.ev_c0));
             DH_CUDA(cudaEventCreate(&s.ev_done));
         }
     return DH_OK;
@@ -304,9 +318,9 @@ int issue_inflate(dh_bam *b, int k) {
     if ((rc = s.desc.reserve(nblk * sizeof(BlockDesc))) != DH_OK) return rc;
     if ((rc = s.status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
     if ((rc = s.h_desc.reserve(nblk * sizeof(BlockDesc))) != DH_OK) return rc;
-    if ((rc = s.h_status.reserve(nblk * sizeof(int))) != DH_OK) return rc;
+    if ((rc = s.h_status.reserve(64)) != DH_OK) return rc;
     const uint64_t cw = fill_descs(bt, sg.b0, sg.b1, s.cbase, sg.b0, b->carry_cap, (BlockDesc *)s.h_desc.p);
-    cudaStream_t sc = s_copy(b), sk = s_comp(b);
+    cudaStream_t sc = s_copy(b), si = s_inf(b);
     DH_CUDA(cudaStreamWaitEvent(sc, s.ev_inf1, 0));  // previous inflate from this comp buffer is done (no-op if never recorded)
     if (!staged) {
         DH_CUDA(cudaMemcpyAsync(s.comp.p, b->data + s.cbase, cbytes, cudaMemcpyHostToDevice, sc));
@@ -314,14 +328,17 @@ int issue_inflate(dh_bam *b, int k) {
     }
     DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, nblk * sizeof(BlockDesc), cudaMemcpyHostToDevice, sc));
     DH_CUDA(cudaEventRecord(s.ev_h2d, sc));
-    DH_CUDA(cudaStreamWaitEvent(sk, s.ev_h2d, 0));
-    DH_CUDA(cudaEventRecord(s.ev_inf0, sk));
+    DH_CUDA(cudaStreamWaitEvent(si, s.ev_h2d, 0));
+    DH_CUDA(cudaStreamWaitEvent(si, s.ev_free, 0));  // the slot's previous tenant has been decoded (and its tail carried over)
+    DH_CUDA(cudaEventRecord(s.ev_inf0, si));
     const uint8_t *comp_ptr = staged ? (const uint8_t *)b->d_image.p + s.cbase : (const uint8_t *)s.comp.p;
     if ((rc = inflate_blocks(b->ctx, comp_ptr, (const BlockDesc *)s.desc.p, (uint32_t)nblk, cw, (uint8_t *)s.out.p, (int *)s.status.p,
-                             s.work, (unsigned int *)b->ctx->counter.p + 16 + 2 * (k % NSEG), sk)) != DH_OK)
+                             s.work, (unsigned int *)b->ctx->counter.p + 16 + 2 * (k % NSEG), si, inflate_sms(b))) != DH_OK)
         return rc;
-    DH_CUDA(cudaEventRecord(s.ev_inf1, sk));
-    DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, nblk * sizeof(int), cudaMemcpyDeviceToHost, sk));
+    DH_CUDA(cudaEventRecord(s.ev_inf1, si));
+    DH_CUDA(launch_status_first_bad((const int *)s.status.p, (uint32_t)nblk, (int *)s.h_status.p, si));
+    b->ctx->launches++;
+    DH_CUDA(cudaEventRecord(s.ev_inf_done, si));
     s.issued_for = k;
     b->st.h2d_bytes += (staged ? 0 : cbytes) + nblk * sizeof(BlockDesc);
     b->st.inflated_bytes += s.obytes;
@@ -337,13 +354,14 @@ int walk_segment(dh_bam *b, int k) {
     const uint32_t n = (uint32_t)nblk + 1;  // + pseudo-block 0 = the carried-over partial record
     cudaStream_t sk = s_comp(b);
     int rc;
-    if ((rc = s.blk_start.reserve((n + 1) * 8)) != DH_OK || (rc = s.entry.reserve(n * 8)) != DH_OK ||
-        (rc = s.todo.reserve(n)) != DH_OK || (rc = s.walk.reserve(n * sizeof(BlockWalk))) != DH_OK ||
-        (rc = s.row_base.reserve(n * 4)) != DH_OK || (rc = s.heap_base.reserve(n * 8)) != DH_OK ||
+    // control arrays (block starts, entries, walk results, row/heap bases) live in pinned host memory that the
+    // kernels read and write directly: a few bytes per BGZF block, and they never queue behind the bulk copies
+    if ((rc = s.rec.reserve(((s.obytes + b->carry_cap) / 36 + n + 8) * 2)) != DH_OK ||
         (rc = s.h_blk_start.reserve((n + 1) * 8)) != DH_OK || (rc = s.h_entry.reserve(n * 8)) != DH_OK ||
         (rc = s.h_todo.reserve(n)) != DH_OK || (rc = s.h_walk.reserve(n * sizeof(BlockWalk))) != DH_OK ||
         (rc = s.h_row_base.reserve(n * 4)) != DH_OK || (rc = s.h_heap_base.reserve(n * 8)) != DH_OK)
         return rc;
+    DH_CUDA(cudaStreamWaitEvent(sk, s.ev_inf_done, 0));
     uint8_t *ubase = (uint8_t *)s.out.p + b->carry_cap;
     // carry: the incomplete record at the end of the previous segment goes in front of this segment's bytes
     if (b->carry > 0) {
@@ -368,42 +386,34 @@ int walk_segment(dh_bam *b, int k) {
     }
     WalkParams wp;
     wp.u = ubase;
-    wp.blk_start = (const int64_t *)s.blk_start.p;
-    wp.entry_in = (const int64_t *)s.entry.p;
-    wp.todo = (const uint8_t *)s.todo.p;
-    wp.out = (BlockWalk *)s.walk.p;
+    wp.blk_start = hs;
+    wp.entry_in = he;
+    wp.todo = ht;
+    wp.out = (BlockWalk *)s.h_walk.p;
     wp.n = n;
     wp.is_final = is_final ? 1 : 0;
     wp.seg_end = (int64_t)s.obytes;
     wp.limit_end = limit_end;
-    DH_CUDA(cudaMemcpyAsync(s.blk_start.p, hs, (n + 1) * 8, cudaMemcpyHostToDevice, sk));
+    wp.rec = (uint16_t *)s.rec.p;
+    wp.rec_bias = s.rec_bias = -b->carry;
     BlockWalk *hw = (BlockWalk *)s.h_walk.p;
     uint32_t validated = 0;  // blocks [0, validated) have entry == predecessor's exit
     bool stopped = false;
     uint32_t stop_blk = 0;
     bool first_round = true;
     for (;;) {
-        DH_CUDA(cudaMemcpyAsync(s.entry.p, he, n * 8, cudaMemcpyHostToDevice, sk));
-        DH_CUDA(cudaMemcpyAsync(s.todo.p, ht, n, cudaMemcpyHostToDevice, sk));
         if (first_round) DH_CUDA(cudaEventRecord(s.ev_walk0, sk));
         DH_CUDA(launch_bam_walk(wp, b->tabs, sk));
         b->ctx->launches++;
-        if (first_round) DH_CUDA(cudaEventRecord(s.ev_walk1, sk));
-        if (first_round) DH_CUDA(cudaMemcpyAsync(hw, s.walk.p, n * sizeof(BlockWalk), cudaMemcpyDeviceToHost, sk));
-        else {
-            // only the re-walked block changed
-            uint32_t j = validated;
-            DH_CUDA(cudaMemcpyAsync(hw + j, (BlockWalk *)s.walk.p + j, sizeof(BlockWalk), cudaMemcpyDeviceToHost, sk));
-        }
-        DH_CUDA(cudaStreamSynchronize(sk));
+        DH_CUDA(cudaEventRecord(first_round ? s.ev_walk1 : s.ev_walk2, sk));
+        DH_CUDA(cudaEventSynchronize(first_round ? s.ev_walk1 : s.ev_walk2));
         if (first_round) {
             // verdicts of the inflate kernel (fused CRC32/ISIZE): stop at the first bad block like bgzf_read does
-            const int *hst = (const int *)s.h_status.p;
-            for (size_t i = 0; i < nblk; ++i)
-                if (hst[i] != 0) {
-                    set_error("BGZF block %zu failed inflate/CRC check (code %d)", s.b0 + i, hst[i]);
-                    return DH_EDATA;
-                }
+            const int *hst = (const int *)s.h_status.p;   // {first failing block or -1, its code}
+            if (hst[0] >= 0) {
+                set_error("BGZF block %zu failed inflate/CRC check (code %d)", s.b0 + (size_t)hst[0], hst[1]);
+                return DH_EDATA;
+            }
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, s.ev_inf0, s.ev_inf1) == cudaSuccess) b->st.inflate_ms += ms;
             if (cudaEventElapsedTime(&ms, s.ev_walk0, s.ev_walk1) == cudaSuccess) b->st.walk_ms += ms;
@@ -426,7 +436,6 @@ int walk_segment(dh_bam *b, int k) {
                     w.count = 0;
                     w.heap_bytes = 0;
                     w.stop = 0;
-                    DH_CUDA(cudaMemcpyAsync((BlockWalk *)s.walk.p + validated, &w, sizeof(BlockWalk), cudaMemcpyHostToDevice, sk));
                 } else {
                     he[validated] = expect;
                     ht[validated] = 1;
@@ -465,8 +474,6 @@ int walk_segment(dh_bam *b, int k) {
     cur.b_hi = last + 1;
     if (cur.rows > 0) b->batches.push_back(cur);
     for (auto &bb : b->batches) b->rows_total += bb.rows;
-    DH_CUDA(cudaMemcpyAsync(s.row_base.p, hrb, n * 4, cudaMemcpyHostToDevice, sk));
-    DH_CUDA(cudaMemcpyAsync(s.heap_base.p, hhb, n * 8, cudaMemcpyHostToDevice, sk));
     // how the chain continues
     const BlockWalk &lw = hw[last];
     b->carry = 0;
@@ -528,9 +535,12 @@ int issue_batch(dh_bam *b) {
     DecodeParams dp;
     memset(&dp, 0, sizeof dp);
     dp.u = (const uint8_t *)s.out.p + b->carry_cap;
-    dp.walk = (const BlockWalk *)s.walk.p;
-    dp.row_base = (const uint32_t *)s.row_base.p;
-    dp.heap_base = (const uint64_t *)s.heap_base.p;
+    dp.walk = (const BlockWalk *)s.h_walk.p;
+    dp.blk_start = (const int64_t *)s.h_blk_start.p;
+    dp.rec = (const uint16_t *)s.rec.p;
+    dp.rec_bias = s.rec_bias;
+    dp.row_base = (const uint32_t *)s.h_row_base.p;
+    dp.heap_base = (const uint64_t *)s.h_heap_base.p;
     dp.b_lo = bb.b_lo;
     dp.b_hi = bb.b_hi;
     dp.heap = (uint8_t *)o.arena.p + heap_off;
@@ -551,6 +561,7 @@ int issue_batch(dh_bam *b) {
     b->ctx->launches++;
     DH_CUDA(cudaEventRecord(o.ev_k1, sk));
     DH_CUDA(cudaStreamWaitEvent(sd, o.ev_k1, 0));
+    DH_CUDA(cudaEventRecord(o.ev_c0, sd));
     const bool keep = (b->mode & DH_BAM_DEVICE_OUTPUT) != 0;
     if (total && !keep) DH_CUDA(cudaMemcpyAsync(o.h_arena.p, o.arena.p, total, cudaMemcpyDeviceToHost, sd));
     DH_CUDA(cudaEventRecord(o.ev_done, sd));
@@ -580,9 +591,12 @@ int have_work(dh_bam *b) {
         if (rc != DH_OK) return rc;
         b->cur_seg = k;
         if ((rc = walk_segment(b, k)) != DH_OK) return rc;
-        // prefetch: H2D + inflate of the next segment overlap this segment's decode batches and D2H.  Its slot
-        // still holds segment k-1, whose decode kernels and carry copy were all enqueued on s_comp before this.
-        if (!b->chain_done && (size_t)k + 1 < b->segs.size() && (rc = issue_inflate(b, k + 1)) != DH_OK) return rc;
+        // Segment k-1 is no longer needed: its decode kernels and the carry copy out of its tail are all enqueued on
+        // the decode stream.  Its slot is the one segment k+2 will be inflated into.
+        if (k >= 1) DH_CUDA(cudaEventRecord(b->ss[(k - 1) % NSEG].ev_free, s_comp(b)));
+        // prefetch: H2D + inflate of the next two segments overlap this segment's decode batches and their D2H copies
+        for (int a = 1; a < NSEG && !b->chain_done; ++a)
+            if ((size_t)(k + a) < b->segs.size() && (rc = issue_inflate(b, k + a)) != DH_OK) return rc;
     }
 }
 
@@ -616,15 +630,14 @@ void dh_bam_close(dh_bam *b) {
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
     for (auto &s : b->ss) {
-        s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release(); s.blk_start.release(); s.entry.release();
-        s.todo.release(); s.walk.release(); s.row_base.release(); s.heap_base.release();
+        s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release(); s.rec.release();
         s.h_desc.release(); s.h_status.release(); s.h_blk_start.release(); s.h_entry.release(); s.h_todo.release();
         s.h_walk.release(); s.h_row_base.release(); s.h_heap_base.release();
-        for (cudaEvent_t e : {s.ev_h2d, s.ev_inf0, s.ev_inf1, s.ev_walk0, s.ev_walk1}) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : {s.ev_h2d, s.ev_inf0, s.ev_inf1, s.ev_inf_done, s.ev_free, s.ev_walk0, s.ev_walk1, s.ev_walk2}) if (e) cudaEventDestroy(e);
     }
     for (auto &s : b->bs) {
         s.arena.release(); s.h_arena.release();
-        for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_done}) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_c0, s.ev_done}) if (e) cudaEventDestroy(e);
     }
     b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release(); b->d_image.release();
     delete b;
@@ -726,6 +739,9 @@ int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
         while (e < b_stop && e - s0 < (1u << 17) && bt.blocks[e].coffset + bt.blocks[e].csize - cbase <= b->seg_comp &&
                bt.uoff[e + 1] - bt.uoff[s0] <= (3ull << 30))
             ++e;
+        // phase 1 of the inflate runs sm_count * 128 streams at a time: cut on a whole number of such rounds
+        const size_t quantum = (size_t)inflate_sms(b) * 128u;
+        if (e < b_stop && e - s0 > quantum) e = s0 + (e - s0) / quantum * quantum;
         if (e == s0) e = s0 + 1;
         b->segs.push_back(Seg{s0, e});
         s0 = e;
@@ -743,6 +759,8 @@ int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
     b->chain_done = b->segs.empty();
     memset(&b->st, 0, sizeof b->st);
     b->st.end_voffset = voff_beg ? voff_beg : dh_bam_first_voffset(b);
+    if (!b->ev_scan0) DH_CUDA(cudaEventCreate(&b->ev_scan0));
+    DH_CUDA(cudaEventRecord(b->ev_scan0, s_comp(b)));
     b->scanning = true;
     return DH_OK;
 }
@@ -751,7 +769,7 @@ int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
     if (!b || !out || !b->scanning) { set_error("dh_bam_next_batch: no scan in progress"); return DH_EINVAL; }
     DH_CUDA(cudaSetDevice(b->ctx->device));
     auto top_up = [&]() -> int {
-        while (b->inflight.size() < 2) {
+        while (b->inflight.size() < NBATCH - 1) {
             int w = have_work(b);
             if (w < 0) return w;
             if (w == 0) break;
@@ -772,7 +790,17 @@ int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
     DH_CUDA(cudaEventSynchronize(o.ev_done));
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, o.ev_k0, o.ev_k1) == cudaSuccess) b->st.decode_ms += ms;
-    rc = top_up();  // keep two batches in flight while the caller consumes this one
+    static const bool trace = getenv("DH_TRACE") != nullptr;
+    if (trace && b->ev_scan0) {   // per-batch timeline relative to scan_begin: decode start/end, D2H start/end (ms)
+        float t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+        cudaEventElapsedTime(&t0, b->ev_scan0, o.ev_k0);
+        cudaEventElapsedTime(&t1, b->ev_scan0, o.ev_k1);
+        cudaEventElapsedTime(&t2, b->ev_scan0, o.ev_c0);
+        cudaEventElapsedTime(&t3, b->ev_scan0, o.ev_done);
+        fprintf(stderr, "[dh_trace] batch %llu rows %llu decode %.1f-%.1f d2h %.1f-%.1f (%.1f GB/s)\n", (unsigned long long)b->returned,
+                (unsigned long long)o.desc.n_rows, t0, t1, t2, t3, o.desc.bytes / 1e6 / (t3 - t2 > 0 ? t3 - t2 : 1));
+    }
+    rc = top_up();  // keep the pipeline full while the caller consumes this one
     if (rc != DH_OK) { b->scanning = false; return rc; }
     *out = o.desc;
     if (b->inflight.empty() && b->chain_done) out->status = b->final_status;

@@ -52,7 +52,7 @@ uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_ba
 // Inflate `n` described blocks on `stream`: lockstep kernels (phase 1 + 2), then the lane-group kernel in filter mode
 // for blocks the compact tables could not hold.  `work` is grown as needed.  counter: >= 2 device words.
 int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
-                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream);
+                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream, int sm_limit = 0);
 
 }  // namespace dh
 

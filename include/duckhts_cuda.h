@@ -195,6 +195,8 @@ int dh_timer_stop(dh_ctx *ctx, float *ms);
 int dh_flush_l2(dh_ctx *ctx);
 /* Host<->device copy bandwidth probe (pinned, `bytes` per direction); GB/s. */
 int dh_measure_pcie(dh_ctx *ctx, uint64_t bytes, float *h2d_gbs, float *d2h_gbs);
+/* Same, both directions running at the same time (what the read_bam pipeline sees). */
+int dh_measure_pcie_bidir(dh_ctx *ctx, uint64_t bytes, float *h2d_gbs, float *d2h_gbs);
 /* Number of kernels this library has launched on this context so far (for bench.py's gpu_launches). */
 uint64_t dh_ctx_launch_count(const dh_ctx *ctx);
 
