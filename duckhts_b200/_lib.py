@@ -85,6 +85,7 @@ SIGNATURES = {
     "dh_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "dh_flush_l2": (C.c_int, [C.c_void_p]),
     "dh_measure_pcie": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "dh_bgzf_dev_inflate_timed": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "dh_measure_pcie_bidir": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "dh_ctx_launch_count": (C.c_uint64, [C.c_void_p]),
 }

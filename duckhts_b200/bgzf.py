@@ -138,6 +138,12 @@ class BgzfDevice:
     def inflate(self):
         check(lib().dh_bgzf_dev_inflate(self.h), "dh_bgzf_dev_inflate")
 
+    def inflate_timed(self):
+        """One pass with CUDA events between the kernels -> (phase1_ms, phase2_ms, fallback_ms)."""
+        ms = (C.c_float * 3)()
+        check(lib().dh_bgzf_dev_inflate_timed(self.h, ms), "dh_bgzf_dev_inflate_timed")
+        return ms[0], ms[1], ms[2]
+
     def check(self):
         bb, bc = C.c_int64(-1), C.c_int32(0)
         rc = lib().dh_bgzf_dev_check(self.h, C.byref(bb), C.byref(bc))

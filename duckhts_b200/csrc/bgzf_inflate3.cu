@@ -657,7 +657,7 @@ static void build_crc3_tables(uint32_t *t) {
 }
 
 cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
-                                   uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream) {
+                                   uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream, cudaEvent_t between_phases) {
     static bool ready[64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -682,6 +682,7 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     bgzf_decode3_kernel<<<ctas, THREADS, WARP_SMEM * WARPS, stream>>>(comp, blocks, nblocks, status, ncmd, areas, counter);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    if (between_phases && (e = cudaEventRecord(between_phases, stream)) != cudaSuccess) return e;
     bgzf_resolve3_kernel<<<(nblocks + 7u) / 8u, 256, 0, stream>>>(blocks, nblocks, out, status, ncmd, areas);
     return cudaGetLastError();
 }

@@ -120,8 +120,12 @@ int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint3
     }
     int rc = work.reserve(inflate_work_bytes(n, cmd_words));
     if (rc != DH_OK) return rc;
-    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, sms, stream));
+    const bool tp = c->time_phases;
+    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[0], stream));
+    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, sms, stream, tp ? c->ev_ph[1] : nullptr));
+    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[2], stream));
     DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, stream, true));
+    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[3], stream));
     c->launches += 3;
     return DH_OK;
 }
@@ -189,6 +193,7 @@ void dh_ctx_destroy(dh_ctx *c) {
     }
     c->l2_scratch.release();
     c->counter.release();
+    for (int i = 0; i < 4; ++i) if (c->ev_ph[i]) cudaEventDestroy(c->ev_ph[i]);
     if (c->ev_timer[0]) cudaEventDestroy(c->ev_timer[0]);
     if (c->ev_timer[1]) cudaEventDestroy(c->ev_timer[1]);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -419,6 +424,30 @@ int dh_bgzf_dev_inflate(dh_bgzf_dev *d) {
         if (rc != DH_OK) return rc;
     }
     return DH_OK;
+}
+
+int dh_bgzf_dev_inflate_timed(dh_bgzf_dev *d, float *ms) {
+    if (!d || !ms) { set_error("dh_bgzf_dev_inflate_timed: bad arguments"); return DH_EINVAL; }
+    dh_ctx *c = d->ctx;
+    DH_CUDA(cudaSetDevice(c->device));
+    for (int i = 0; i < 4; ++i)
+        if (!c->ev_ph[i]) DH_CUDA(cudaEventCreate(&c->ev_ph[i]));
+    ms[0] = ms[1] = ms[2] = 0.f;
+    c->time_phases = true;
+    int rc = DH_OK;
+    for (auto &s : d->segs) {
+        rc = inflate_blocks(c, (const uint8_t *)d->comp.p + s.cbase, (const BlockDesc *)d->desc.p + s.b0, (uint32_t)(s.b1 - s.b0),
+                            s.cmd_words, (uint8_t *)d->out.p, (int *)d->status.p + s.b0, d->work, (unsigned int *)c->counter.p, c->stream);
+        if (rc != DH_OK) break;
+        if (cudaEventSynchronize(c->ev_ph[3]) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "cudaEventSynchronize"); break; }
+        for (int i = 0; i < 3; ++i) {
+            float t = 0.f;
+            cudaEventElapsedTime(&t, c->ev_ph[i], c->ev_ph[i + 1]);
+            ms[i] += t;
+        }
+    }
+    c->time_phases = false;
+    return rc;
 }
 
 int dh_bgzf_dev_check(dh_bgzf_dev *d, int64_t *bad_block, int32_t *bad_code) {

@@ -739,9 +739,6 @@ int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
         while (e < b_stop && e - s0 < (1u << 17) && bt.blocks[e].coffset + bt.blocks[e].csize - cbase <= b->seg_comp &&
                bt.uoff[e + 1] - bt.uoff[s0] <= (3ull << 30))
             ++e;
-        // phase 1 of the inflate runs sm_count * 128 streams at a time: cut on a whole number of such rounds
-        const size_t quantum = (size_t)inflate_sms(b) * 128u;
-        if (e < b_stop && e - s0 > quantum) e = s0 + (e - s0) / quantum * quantum;
         if (e == s0) e = s0 + 1;
         b->segs.push_back(Seg{s0, e});
         s0 = e;

@@ -65,6 +65,10 @@ struct dh_ctx {
     dh::DevBuf l2_scratch;
     dh::DevBuf counter;                   // inflate ticket counters (one word per pipeline slot + main)
     uint64_t launches = 0;
+    // per-phase timing of the inflate (dh_bgzf_dev_inflate_timed): events before phase 1, between the phases, after
+    // phase 2, after the fallback filter
+    bool time_phases = false;
+    cudaEvent_t ev_ph[4] = {};
     // pipeline slots of dh_bgzf_inflate_host
     struct Slot {
         dh::DevBuf comp, out, desc, status, work;

@@ -93,6 +93,9 @@ uint64_t dh_bgzf_dev_nblocks(const dh_bgzf_dev *d);
 uint64_t dh_bgzf_dev_comp_bytes(const dh_bgzf_dev *d);
 uint64_t dh_bgzf_dev_out_bytes(const dh_bgzf_dev *d);
 int dh_bgzf_dev_inflate(dh_bgzf_dev *d);
+/* One inflate pass with CUDA events between the kernels (synchronises after every launch group): ms[0] = phase 1
+ * (Huffman decode, one stream per lane), ms[1] = phase 2 (literal/match placement + CRC-32), ms[2] = fallback filter. */
+int dh_bgzf_dev_inflate_timed(dh_bgzf_dev *d, float *ms);
 int dh_bgzf_dev_check(dh_bgzf_dev *d, int64_t *bad_block, int32_t *bad_code);
 int dh_bgzf_dev_read(dh_bgzf_dev *d, uint64_t offset, uint8_t *dst, uint64_t n);
 
