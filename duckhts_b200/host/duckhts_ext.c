@@ -1,0 +1,429 @@
+/* duckhts_ext.c — the DuckDB side of duckhts_b200: a C extension that registers `read_bam` and `bgunzip` with the
+ * same names, parameters, column schemas and error behaviour as the reference (src/bam_reader.c:1044-1068,
+ * src/bgzip.c:359-380) and serves them from the GPU through the C-ABI of libduckhts_cuda.so
+ * (include/duckhts_cuda.h).  Host code in C, as the reference's; no htslib, no CPU decode path.
+ *
+ * Entry point: duckhts_init_c_api (reference duckdb_capi/duckdb_extension.h:1179-1195) — the extension is a
+ * drop-in for the reference's shared object as far as these two table functions go.
+ *
+ * How a scan maps onto the reference's callbacks (src/bam_reader.c:410-1038):
+ *   bind        reads the file into pinned memory, dh_bam_open (BGZF framing on the host, header inflated on the GPU),
+ *               declares the schema (13 SAM columns [+ 56 SAMtags columns] — same order and types)
+ *   global init max_threads = 1: the GPU is the parallelism; rows come back in file order (the reference's sequential
+ *               order; in its contig-parallel mode DuckDB interleaves threads nondeterministically)
+ *   local init  projection pushdown -> dh_bam_set_projection, dh_bam_scan_begin
+ *   scan        copies up to duckdb_vector_size() rows of the current dh_bam_batch into the output chunk: fixed-width
+ *               columns by memcpy, VARCHAR cells of <= 12 bytes by a 16-byte store (the kernel wrote duckdb_string_t),
+ *               longer strings through duckdb_vector_assign_string_element_len, NULLs through the validity mask.
+ */
+#define _GNU_SOURCE
+#include <errno.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include "duckdb_ext_abi.h"
+#include "duckhts_cuda.h"
+
+static duckdb_ext_api_v1 api;   /* the host's function table, copied by value like DUCKDB_EXTENSION_API_INIT does */
+
+/* ---- one GPU context per process (device from DUCKHTS_DEVICE, default 0) ------------------------------------------ */
+static pthread_mutex_t g_lock = PTHREAD_MUTEX_INITIALIZER;
+static dh_ctx *g_ctx;
+static dh_ctx *shared_ctx(void) {
+    pthread_mutex_lock(&g_lock);
+    if (!g_ctx) {
+        const char *d = getenv("DUCKHTS_DEVICE");
+        g_ctx = dh_ctx_create(d ? atoi(d) : 0);
+    }
+    dh_ctx *c = g_ctx;
+    pthread_mutex_unlock(&g_lock);
+    return c;
+}
+
+/* whole file -> pinned host memory (the C-ABI copies from it at full PCIe rate) */
+static uint8_t *slurp_pinned(const char *path, uint64_t *size_out) {
+    FILE *f = fopen(path, "rb");
+    if (!f) return NULL;
+    struct stat st;
+    if (fstat(fileno(f), &st) != 0 || !S_ISREG(st.st_mode)) { fclose(f); return NULL; }
+    uint64_t n = (uint64_t)st.st_size;
+    uint8_t *p = (uint8_t *)dh_host_alloc(n ? n : 1);
+    if (!p) { fclose(f); return NULL; }
+    uint64_t got = 0;
+    while (got < n) {
+        size_t k = fread(p + got, 1, (size_t)((n - got) < (64u << 20) ? (n - got) : (64u << 20)), f);
+        if (k == 0) break;
+        got += k;
+    }
+    fclose(f);
+    if (got != n) { dh_host_free(p); return NULL; }
+    *size_out = n;
+    return p;
+}
+
+static char *named_varchar(duckdb_bind_info info, const char *name) {
+    duckdb_value v = api.duckdb_bind_get_named_parameter(info, name);
+    char *s = NULL;
+    if (v && !api.duckdb_is_null_value(v)) s = api.duckdb_get_varchar(v);
+    if (v) api.duckdb_destroy_value(&v);
+    return s;
+}
+static int named_bool(duckdb_bind_info info, const char *name, int dflt) {
+    duckdb_value v = api.duckdb_bind_get_named_parameter(info, name);
+    int r = dflt;
+    if (v && !api.duckdb_is_null_value(v)) r = api.duckdb_get_bool(v) ? 1 : 0;
+    if (v) api.duckdb_destroy_value(&v);
+    return r;
+}
+static int file_exists(const char *p) { struct stat st; return p && stat(p, &st) == 0; }
+
+/* ================================================================================================================
+ * read_bam
+ * ================================================================================================================ */
+/* SAMtags columns of standard_tags := true, in the reference's order (src/bam_reader.c:54-70); type letters as there:
+ * i BIGINT, Z VARCHAR, A VARCHAR, B LIST (sub-type in the next letter) */
+static const char STD_TAGS[] =
+    "AMi ASi BCZ BQZ BZZ CBZ CCZ CGBICMi COZ CPi CQZ CRZ CSZ CTZ CYZ E2Z FIi FSZ FZBSH0i H1i H2i HIi IHi LBZ MCZ MDZ MIZ MLBCMMZ MNi "
+    "MQi NHi NMi OAZ OCZ OPi OQZ OXZ PGZ PQi PTZ PUZ Q2Z QTZ QXZ R2Z RGZ RXZ SAZ SMi TCi TSA U2Z UQi ";
+#define N_STD_TAGS 56
+#define N_CORE 13
+
+typedef struct {
+    char *path;
+    uint8_t *image;
+    uint64_t size;
+    dh_bam *bam;
+    int standard_tags, has_index, n_contigs;
+    int n_cols;
+} bam_bind_t;
+
+typedef struct {
+    idx_t n_proj;
+    idx_t *col_ids;          /* schema column of output vector i */
+    int *abi_col;            /* its column in dh_bam_batch, or -1 for a column this build always returns NULL for */
+    dh_bam_batch batch;
+    uint64_t cursor;         /* next row of `batch` to hand out */
+    int have_batch, done;
+} bam_local_t;
+
+static void bam_bind_free(void *p) {
+    bam_bind_t *b = (bam_bind_t *)p;
+    if (!b) return;
+    if (b->bam) dh_bam_close(b->bam);
+    if (b->image) dh_host_free(b->image);
+    free(b->path);
+    api.duckdb_free(b);
+}
+static void bam_local_free(void *p) {
+    bam_local_t *l = (bam_local_t *)p;
+    if (!l) return;
+    free(l->col_ids);
+    free(l->abi_col);
+    api.duckdb_free(l);
+}
+
+static void read_bam_bind(duckdb_bind_info info) {
+    duckdb_value pv = api.duckdb_bind_get_parameter(info, 0);
+    char *path = api.duckdb_get_varchar(pv);
+    api.duckdb_destroy_value(&pv);
+    if (!path || !path[0]) {
+        api.duckdb_bind_set_error(info, "read_bam requires a file path");
+        if (path) api.duckdb_free(path);
+        return;
+    }
+    char *region = named_varchar(info, "region"), *index_path = named_varchar(info, "index_path"), *reference = named_varchar(info, "reference");
+    const int standard_tags = named_bool(info, "standard_tags", 0), auxiliary_tags = named_bool(info, "auxiliary_tags", 0);
+    char err[768];
+    err[0] = 0;
+    bam_bind_t *b = NULL;
+    dh_ctx *ctx = shared_ctx();
+    if (!ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
+    else if (region && region[0]) snprintf(err, sizeof err, "read_bam: region queries are not available in this build (BAI/CSI support is the next row of the scope table)");
+    else if (auxiliary_tags) snprintf(err, sizeof err, "read_bam: auxiliary_tags := true is not available in this build");
+    else {
+        b = (bam_bind_t *)api.duckdb_malloc(sizeof *b);
+        memset(b, 0, sizeof *b);
+        b->image = slurp_pinned(path, &b->size);
+        if (!b->image) snprintf(err, sizeof err, "Failed to open SAM/BAM/CRAM file: %s", path);
+        else if (!(b->bam = dh_bam_open(ctx, b->image, b->size))) snprintf(err, sizeof err, "Failed to read SAM/BAM/CRAM header");
+    }
+    if (err[0]) {
+        api.duckdb_bind_set_error(info, err);
+        bam_bind_free(b);
+        api.duckdb_free(path);
+        if (region) api.duckdb_free(region);
+        if (index_path) api.duckdb_free(index_path);
+        if (reference) api.duckdb_free(reference);
+        return;
+    }
+    b->path = strdup(path);
+    b->standard_tags = standard_tags;
+    b->n_contigs = dh_bam_n_ref(b->bam);
+    /* index probe like sam_index_load3: explicit path, else PATH.bai / PATH.csi / PATH with .bam -> .bai */
+    {
+        char cand[3][1024];
+        snprintf(cand[0], sizeof cand[0], "%s.bai", path);
+        snprintf(cand[1], sizeof cand[1], "%s.csi", path);
+        snprintf(cand[2], sizeof cand[2], "%s", path);
+        size_t n = strlen(cand[2]);
+        if (n > 4 && !strcmp(cand[2] + n - 4, ".bam")) strcpy(cand[2] + n - 4, ".bai"); else cand[2][0] = 0;
+        b->has_index = index_path ? file_exists(index_path) : (file_exists(cand[0]) || file_exists(cand[1]) || (cand[2][0] && file_exists(cand[2])));
+    }
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER),
+                        t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT), t_usmall = api.duckdb_create_logical_type(DUCKDB_TYPE_USMALLINT),
+                        t_double = api.duckdb_create_logical_type(DUCKDB_TYPE_DOUBLE);
+    static const struct { const char *name; int kind; } core[N_CORE] = {
+        {"QNAME", 0}, {"FLAG", 3}, {"RNAME", 0}, {"POS", 2}, {"MAPQ", 1}, {"CIGAR", 0}, {"RNEXT", 0}, {"PNEXT", 2}, {"TLEN", 2},
+        {"SEQ", 0}, {"QUAL", 0}, {"READ_GROUP_ID", 0}, {"SAMPLE_ID", 0}};
+    for (int c = 0; c < N_CORE; ++c)
+        api.duckdb_bind_add_result_column(info, core[c].name, core[c].kind == 0 ? t_varchar : core[c].kind == 1 ? t_int : core[c].kind == 2 ? t_bigint : t_usmall);
+    b->n_cols = N_CORE;
+    if (standard_tags) {
+        for (int k = 0; k < N_STD_TAGS; ++k) {
+            const char *e = STD_TAGS + 4 * k;
+            char name[3] = {e[0], e[1], 0};
+            if (e[2] == 'B') {
+                duckdb_logical_type lt = api.duckdb_create_list_type(e[3] == 'f' ? t_double : t_bigint);
+                api.duckdb_bind_add_result_column(info, name, lt);
+                api.duckdb_destroy_logical_type(&lt);
+            } else api.duckdb_bind_add_result_column(info, name, e[2] == 'i' ? t_bigint : e[2] == 'f' ? t_double : t_varchar);
+        }
+        b->n_cols += N_STD_TAGS;
+    }
+    api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_int); api.duckdb_destroy_logical_type(&t_bigint);
+    api.duckdb_destroy_logical_type(&t_usmall); api.duckdb_destroy_logical_type(&t_double);
+    api.duckdb_bind_set_bind_data(info, b, bam_bind_free);
+    api.duckdb_free(path);
+    if (region) api.duckdb_free(region);
+    if (index_path) api.duckdb_free(index_path);
+    if (reference) api.duckdb_free(reference);
+}
+
+static void read_bam_init(duckdb_init_info info) {
+    api.duckdb_init_set_max_threads(info, 1);
+    api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free);
+}
+
+static void read_bam_local_init(duckdb_init_info info) {
+    bam_bind_t *b = (bam_bind_t *)api.duckdb_init_get_bind_data(info);
+    bam_local_t *l = (bam_local_t *)api.duckdb_malloc(sizeof *l);
+    memset(l, 0, sizeof *l);
+    l->n_proj = api.duckdb_init_get_column_count(info);
+    l->col_ids = (idx_t *)calloc(l->n_proj ? l->n_proj : 1, sizeof(idx_t));
+    l->abi_col = (int *)calloc(l->n_proj ? l->n_proj : 1, sizeof(int));
+    /* projection pushdown (src/bam_reader.c:676-679): only projected columns are decoded on the GPU.  Tag columns are
+     * requested from the C-ABI in projection order; tag k of the request is column 13 + k of every batch. */
+    uint64_t mask = 0;
+    dh_tag_req tags[DH_BAM_MAX_TAGS];
+    int n_tags = 0;
+    for (idx_t i = 0; i < l->n_proj; ++i) {
+        const idx_t c = api.duckdb_init_get_column_index(info, i);
+        l->col_ids[i] = c;
+        if (c < N_CORE) { l->abi_col[i] = (int)c; mask |= 1ull << c; continue; }
+        const char *e = STD_TAGS + 4 * (c - N_CORE);
+        if (c - N_CORE >= N_STD_TAGS || e[2] == 'B' || n_tags >= DH_BAM_MAX_TAGS) { l->abi_col[i] = -1; continue; }   /* LIST tags: NULL for now */
+        tags[n_tags].tag[0] = e[0]; tags[n_tags].tag[1] = e[1]; tags[n_tags].type = e[2]; tags[n_tags].pad = 0;
+        l->abi_col[i] = N_CORE + n_tags;
+        mask |= 1ull << (N_CORE + n_tags);
+        ++n_tags;
+    }
+    if (dh_bam_set_projection(b->bam, mask, tags, n_tags) != DH_OK || dh_bam_scan_begin(b->bam, 0, UINT64_MAX) != DH_OK) {
+        api.duckdb_init_set_error(info, dh_last_error());
+        bam_local_free(l);
+        return;
+    }
+    api.duckdb_init_set_init_data(info, l, bam_local_free);
+}
+
+static size_t core_width(idx_t c) { return c == 1 ? 2 : c == 4 ? 4 : (c == 3 || c == 7 || c == 8) ? 8 : 16; }
+
+static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
+    bam_bind_t *b = (bam_bind_t *)api.duckdb_function_get_bind_data(info);
+    bam_local_t *l = (bam_local_t *)api.duckdb_function_get_local_init_data(info);
+    if (!l || l->done) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    while (!l->have_batch || l->cursor >= l->batch.n_rows) {
+        const int rc = dh_bam_next_batch(b->bam, &l->batch);
+        if (rc == 1) { l->have_batch = 1; l->cursor = 0; continue; }
+        l->done = 1;
+        /* rc == 0: end of file, or an invalid record ended the scan: the reference stops silently there too
+         * (src/bam_reader.c:754-765).  A failed BGZF block (DH_EDATA) is a read error to htslib = the same silent end.
+         * Anything else is a CUDA/runtime failure and is reported. */
+        if (rc < 0 && rc != DH_EDATA && rc != DH_EFORMAT) api.duckdb_function_set_error(info, dh_last_error());
+        api.duckdb_data_chunk_set_size(output, 0);
+        return;
+    }
+    const idx_t vs = api.duckdb_vector_size();
+    const uint64_t r0 = l->cursor;
+    const idx_t n = l->batch.n_rows - r0 < vs ? (idx_t)(l->batch.n_rows - r0) : vs;
+    for (idx_t i = 0; i < l->n_proj; ++i) {
+        duckdb_vector vec = api.duckdb_data_chunk_get_vector(output, i);
+        const int ac = l->abi_col[i];
+        if (ac < 0) {   /* column not served: all NULL */
+            api.duckdb_vector_ensure_validity_writable(vec);
+            uint64_t *val = api.duckdb_vector_get_validity(vec);
+            for (idx_t r = 0; r < n; ++r) api.duckdb_validity_set_row_invalid(val, r);
+            if (STD_TAGS[4 * (l->col_ids[i] - N_CORE) + 2] == 'B') {
+                duckdb_list_entry *le = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
+                for (idx_t r = 0; r < n; ++r) { le[r].offset = 0; le[r].length = 0; }
+            }
+            continue;
+        }
+        const idx_t c = l->col_ids[i];
+        size_t w = c < N_CORE ? core_width(c) : (STD_TAGS[4 * (c - N_CORE) + 2] == 'i' || STD_TAGS[4 * (c - N_CORE) + 2] == 'f') ? 8 : 16;
+        const uint8_t *src = (const uint8_t *)l->batch.data[ac] + r0 * w;
+        void *dst = api.duckdb_vector_get_data(vec);
+        const uint64_t *valid = l->batch.validity[ac];
+        if (w != 16) memcpy(dst, src, n * w);
+        else {
+            const duckdb_string_t *cells = (const duckdb_string_t *)src;
+            duckdb_string_t *out = (duckdb_string_t *)dst;
+            for (idx_t r = 0; r < n; ++r) {
+                if (valid && !((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) continue;
+                if (cells[r].value.inlined.length <= 12) out[r] = cells[r];
+                else api.duckdb_vector_assign_string_element_len(vec, r, cells[r].value.pointer.ptr, cells[r].value.inlined.length);
+            }
+        }
+        if (valid) {
+            uint64_t *val = NULL;
+            for (idx_t r = 0; r < n; ++r)
+                if (!((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) {
+                    if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
+                    api.duckdb_validity_set_row_invalid(val, r);
+                }
+        }
+    }
+    l->cursor += n;
+    api.duckdb_data_chunk_set_size(output, n);
+}
+
+static void register_read_bam(duckdb_connection con) {
+    duckdb_table_function tf = api.duckdb_create_table_function();
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN);
+    api.duckdb_table_function_set_name(tf, "read_bam");
+    api.duckdb_table_function_add_parameter(tf, t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "region", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "index_path", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "reference", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "standard_tags", t_bool);
+    api.duckdb_table_function_add_named_parameter(tf, "auxiliary_tags", t_bool);
+    api.duckdb_table_function_set_bind(tf, read_bam_bind);
+    api.duckdb_table_function_set_init(tf, read_bam_init);
+    api.duckdb_table_function_set_local_init(tf, read_bam_local_init);
+    api.duckdb_table_function_set_function(tf, read_bam_scan);
+    api.duckdb_table_function_supports_projection_pushdown(tf, true);
+    api.duckdb_register_table_function(con, tf);
+    api.duckdb_destroy_table_function(&tf);
+    api.duckdb_destroy_logical_type(&t_varchar);
+    api.duckdb_destroy_logical_type(&t_bool);
+}
+
+/* ================================================================================================================
+ * bgunzip — like the reference, the work happens in bind and the scan returns one row (src/bgzip.c:86-200, 300-330)
+ * ================================================================================================================ */
+typedef struct { char *out_path; int64_t bytes_in, bytes_out; int emitted; } gz_bind_t;
+static void gz_bind_free(void *p) { gz_bind_t *g = (gz_bind_t *)p; if (g) { free(g->out_path); api.duckdb_free(g); } }
+
+static void bgunzip_bind(duckdb_bind_info info) {
+    duckdb_value pv = api.duckdb_bind_get_parameter(info, 0);
+    char *in = api.duckdb_get_varchar(pv);
+    api.duckdb_destroy_value(&pv);
+    if (!in || !in[0]) { api.duckdb_bind_set_error(info, "bgunzip requires a file path"); if (in) api.duckdb_free(in); return; }
+    char *outp = named_varchar(info, "output_path");
+    const int keep = named_bool(info, "keep", 1), overwrite = named_bool(info, "overwrite", 0);
+    char out_path[4096], err[4608];
+    err[0] = 0;
+    if (outp) snprintf(out_path, sizeof out_path, "%s", outp);
+    else {
+        const size_t n = strlen(in);
+        if (n > 3 && !strcmp(in + n - 3, ".gz")) snprintf(out_path, sizeof out_path, "%.*s", (int)(n - 3), in);
+        else snprintf(out_path, sizeof out_path, "%s.out", in);
+    }
+    uint8_t *comp = NULL, *plain = NULL;
+    uint64_t csize = 0, usize = 0;
+    dh_ctx *ctx = NULL;
+    if (!overwrite && file_exists(out_path)) snprintf(err, sizeof err, "bgunzip: output '%s' already exists (use overwrite := TRUE to replace)", out_path);
+    else if (!(ctx = shared_ctx())) snprintf(err, sizeof err, "bgunzip: no usable CUDA device (%s)", dh_last_error());
+    else if (!(comp = slurp_pinned(in, &csize))) snprintf(err, sizeof err, "bgunzip: cannot open input %s", in);
+    else {
+        dh_inflate_stats st;
+        int rc = dh_bgzf_inflate_host(ctx, comp, csize, NULL, 0, &usize, &st);      /* framing + verdicts, size of the output */
+        if (rc == DH_OK) {
+            plain = (uint8_t *)dh_host_alloc(usize ? usize : 1);
+            if (!plain) rc = DH_ENOMEM;
+            else rc = dh_bgzf_inflate_host(ctx, comp, csize, plain, usize, &usize, &st);
+        }
+        if (rc != DH_OK) snprintf(err, sizeof err, "bgunzip: read error");
+        else {
+            FILE *f = fopen(out_path, "wb");
+            if (!f) snprintf(err, sizeof err, "bgunzip: cannot open output %s: %s", out_path, strerror(errno));
+            else {
+                if (fwrite(plain, 1, usize, f) != usize) snprintf(err, sizeof err, "bgunzip: write error");
+                if (fclose(f) != 0 && !err[0]) snprintf(err, sizeof err, "bgunzip: close error");
+            }
+        }
+    }
+    if (comp) dh_host_free(comp);
+    if (plain) dh_host_free(plain);
+    if (err[0]) api.duckdb_bind_set_error(info, err);
+    else {
+        if (!keep) unlink(in);
+        duckdb_logical_type t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN), t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR),
+                            t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT);
+        api.duckdb_bind_add_result_column(info, "success", t_bool);
+        api.duckdb_bind_add_result_column(info, "output_path", t_varchar);
+        api.duckdb_bind_add_result_column(info, "bytes_in", t_bigint);
+        api.duckdb_bind_add_result_column(info, "bytes_out", t_bigint);
+        api.duckdb_destroy_logical_type(&t_bool); api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_bigint);
+        gz_bind_t *g = (gz_bind_t *)api.duckdb_malloc(sizeof *g);
+        g->out_path = strdup(out_path); g->bytes_in = (int64_t)csize; g->bytes_out = (int64_t)usize; g->emitted = 0;
+        api.duckdb_bind_set_bind_data(info, g, gz_bind_free);
+    }
+    api.duckdb_free(in);
+    if (outp) api.duckdb_free(outp);
+}
+static void bgunzip_init(duckdb_init_info info) { ((gz_bind_t *)api.duckdb_init_get_bind_data(info))->emitted = 0; }
+static void bgunzip_scan(duckdb_function_info info, duckdb_data_chunk output) {
+    gz_bind_t *g = (gz_bind_t *)api.duckdb_function_get_bind_data(info);
+    if (g->emitted) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    ((bool *)api.duckdb_vector_get_data(api.duckdb_data_chunk_get_vector(output, 0)))[0] = true;
+    api.duckdb_vector_assign_string_element(api.duckdb_data_chunk_get_vector(output, 1), 0, g->out_path ? g->out_path : "");
+    ((int64_t *)api.duckdb_vector_get_data(api.duckdb_data_chunk_get_vector(output, 2)))[0] = g->bytes_in;
+    ((int64_t *)api.duckdb_vector_get_data(api.duckdb_data_chunk_get_vector(output, 3)))[0] = g->bytes_out;
+    g->emitted = 1;
+    api.duckdb_data_chunk_set_size(output, 1);
+}
+static void register_bgunzip(duckdb_connection con) {
+    duckdb_table_function tf = api.duckdb_create_table_function();
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER),
+                        t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN);
+    api.duckdb_table_function_set_name(tf, "bgunzip");
+    api.duckdb_table_function_add_parameter(tf, t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "output_path", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "threads", t_int);      /* accepted for compatibility: the GPU does the inflating */
+    api.duckdb_table_function_add_named_parameter(tf, "keep", t_bool);
+    api.duckdb_table_function_add_named_parameter(tf, "overwrite", t_bool);
+    api.duckdb_table_function_set_bind(tf, bgunzip_bind);
+    api.duckdb_table_function_set_init(tf, bgunzip_init);
+    api.duckdb_table_function_set_function(tf, bgunzip_scan);
+    api.duckdb_register_table_function(con, tf);
+    api.duckdb_destroy_table_function(&tf);
+    api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_int); api.duckdb_destroy_logical_type(&t_bool);
+}
+
+/* ---- entry point (reference duckdb_capi/duckdb_extension.h:1179-1195) ------------------------------------------------ */
+__attribute__((visibility("default"))) bool duckhts_init_c_api(duckdb_extension_info info, struct duckdb_extension_access *access) {
+    const duckdb_ext_api_v1 *host = (const duckdb_ext_api_v1 *)access->get_api(info, DUCKDB_EXT_ABI_VERSION);
+    if (!host) return false;
+    api = *host;
+    duckdb_database *db = access->get_database(info);
+    duckdb_connection con;
+    if (api.duckdb_connect(*db, &con) == DuckDBError) { access->set_error(info, "Failed to open connection to database"); return false; }
+    register_read_bam(con);
+    register_bgunzip(con);
+    api.duckdb_disconnect(&con);
+    return true;
+}

@@ -74,3 +74,15 @@ def test_host_framing_matches_oracle():
     except dh.DuckhtsError:
         pass
     assert orc.bgzf_walk(bytes(bad))[0] is None
+
+
+def test_duckdb_extension_exports_only_the_entry_point():
+    """Like the reference's build (CMAKE_C_VISIBILITY_PRESET hidden): one default-visibility symbol, duckhts_init_c_api."""
+    import subprocess
+
+    ext = os.path.join(ROOT, "duckhts_b200", "lib", "duckhts.duckdb_extension.so")
+    assert os.path.exists(ext), "run __graft_entry__.build()"
+    out = subprocess.check_output(["nm", "-D", "--defined-only", ext], text=True)
+    names = [ln.split()[-1] for ln in out.splitlines() if ln.strip() and ln.split()[-2] in ("T", "t") or " T " in ln]
+    assert "duckhts_init_c_api" in names
+    assert [n for n in names if not n.startswith("_")] == ["duckhts_init_c_api"], names
