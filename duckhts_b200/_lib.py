@@ -80,6 +80,14 @@ SIGNATURES = {
     "dh_bam_next_batch": (C.c_int, [C.c_void_p, C.POINTER(BamBatch)]),
     "dh_bam_scan_stats_get": (C.c_int, [C.c_void_p, C.POINTER(BamScanStats)]),
     "dh_bam_split": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]),
+    "dh_index_load": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "dh_index_free": (None, [C.c_void_p]),
+    "dh_index_n_ref": (C.c_int32, [C.c_void_p]),
+    "dh_index_is_csi": (C.c_int, [C.c_void_p]),
+    "dh_index_n_no_coor": (C.c_uint64, [C.c_void_p]),
+    "dh_bam_scan_regions": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_char_p), C.c_int]),
+    "dh_bam_scan_contigs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
+    "dh_bam_split_contigs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int32)]),
     "dh_ctx_sync": (C.c_int, [C.c_void_p]),
     "dh_timer_start": (C.c_int, [C.c_void_p]),
     "dh_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),

@@ -44,6 +44,38 @@ def validity_to_bool(ptr, n):
     return np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
 
 
+DH_ENOREGION = -7
+
+
+class Index:
+    """A BAI or CSI index image (dh_index; reference hts_idx_load3).  CSI is BGZF: the GPU inflates it."""
+
+    def __init__(self, ctx, data):
+        self.a = _as_u8(data)
+        self.h = lib().dh_index_load(ctx.h, self.a.ctypes.data, self.a.size)
+        if not self.h:
+            raise DuckhtsError("dh_index_load failed: " + lib().dh_last_error().decode())
+
+    @property
+    def n_ref(self):
+        return lib().dh_index_n_ref(self.h)
+
+    @property
+    def is_csi(self):
+        return bool(lib().dh_index_is_csi(self.h))
+
+    def close(self):
+        if self.h:
+            lib().dh_index_free(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
 class BamFile:
     """One BAM image bound to a Context (dh_bam)."""
 
@@ -109,6 +141,24 @@ class BamFile:
     def scan_begin(self, voff_beg=0, voff_end=VOFF_MAX):
         check(lib().dh_bam_scan_begin(self.h, voff_beg, voff_end), "dh_bam_scan_begin")
 
+    def scan_regions(self, index, regions):
+        """read_bam(region := ...): `regions` = the parameter split at commas (src/bam_reader.c:318-348).
+        Returns False when no region names a known contig (the reference's "No reads found for region(s)")."""
+        arr = (C.c_char_p * max(len(regions), 1))(*[r.encode() if isinstance(r, str) else r for r in regions])
+        rc = lib().dh_bam_scan_regions(self.h, index.h, arr, len(regions))
+        if rc == DH_ENOREGION:
+            return False
+        check(rc, "dh_bam_scan_regions")
+        return True
+
+    def scan_contigs(self, index, tid_lo=0, tid_hi=1 << 30):
+        check(lib().dh_bam_scan_contigs(self.h, index.h, tid_lo, min(tid_hi, 1 << 30)), "dh_bam_scan_contigs")
+
+    def split_contigs(self, index, n_parts):
+        v = (C.c_int32 * (n_parts + 1))()
+        check(lib().dh_bam_split_contigs(self.h, index.h, n_parts, v), "dh_bam_split_contigs")
+        return list(v)
+
     def next_batch(self):
         b = BamBatch()
         rc = check(lib().dh_bam_next_batch(self.h, C.byref(b)), "dh_bam_next_batch")
@@ -160,12 +210,22 @@ def batch_to_columns(bf, b):
     return out
 
 
-def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, batch_rows=0, carry=0):
-    """Whole scan -> one dict of columns in row order (test/inspection helper; the product API is batch-wise)."""
+def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, batch_rows=0, carry=0, index=None,
+             regions=None, contigs=None):
+    """Whole scan -> one dict of columns in row order (test/inspection helper; the product API is batch-wise).
+    index = index file bytes; with it, regions = list of region strings, or contigs = (tid_lo, tid_hi) / True."""
     with BamFile(ctx, data) as bf:
         bf.set_projection(col_mask, tags)
         bf.configure(seg_comp, batch_rows, carry)
-        bf.scan_begin(*voff)
+        if index is not None:
+            with Index(ctx, index) as ix:
+                if regions is not None:
+                    if not bf.scan_regions(ix, regions):
+                        return None
+                else:
+                    bf.scan_contigs(ix, *(contigs if isinstance(contigs, tuple) else ()))
+        else:
+            bf.scan_begin(*voff)
         parts = []
         status = 0
         while True:

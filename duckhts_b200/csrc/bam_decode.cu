@@ -56,6 +56,7 @@ struct Rec {
     uint32_t block_len, l_qname, n_cigar, cig_n, flag, mapq;
     int32_t tid, pos, l_qseq, mtid, mpos, isize;
     uint32_t cigar_text_len; // exact length of the CIGAR text (0 if cig_n == 0)
+    int64_t rlen;            // bam_cigar2rlen: reference bases the CIGAR consumes (0 if cig_n == 0)
 };
 
 // Offsets may be negative (bytes carried over from the previous segment), so "none/corrupt" is NONE, never -1.
@@ -165,15 +166,18 @@ __device__ __forceinline__ int parse_record(const uint8_t *u, int64_t off, int64
         }
     }
     r.cigar_text_len = 0;
+    r.rlen = 0;
     if (r.cig_n) {                                           // :841-852
-        int64_t qlen = 0;
+        int64_t qlen = 0, rlen = 0;
         uint32_t tl = 0;
         for (uint32_t i = 0; i < r.cig_n; ++i) {
             uint32_t c = ld32u(u, r.cigar + 4ll * i);
             if ((0x3C1A7u >> ((c & 15u) << 1)) & 1u) qlen += c >> 4;  // bam_cigar_type bit 0: consumes query
+            if ((0x3C1A7u >> ((c & 15u) << 1)) & 2u) rlen += c >> 4;  // bit 1: consumes reference (bam_cigar2rlen)
             tl += dec_digits(c >> 4) + 1u;
         }
         r.cigar_text_len = tl;
+        r.rlen = rlen;
         if (r.l_qseq > 0 && !(r.flag & 4u) && qlen != r.l_qseq) return -4;
     }
     if (r.tid >= n_ref || r.tid < -1 || r.mtid >= n_ref || r.mtid < -1) return -3;  // sam.c:4127-4131
@@ -201,6 +205,28 @@ __device__ __forceinline__ bool plausible_header(const uint8_t *u, int64_t off, 
 // string-heap slots (4-byte aligned) a record needs for the projected columns; both kernels use these rules
 __device__ __forceinline__ uint32_t slot_bytes(uint32_t bound) { return bound > 12u ? align4(bound) : 0u; }
 __device__ __forceinline__ bool qual_absent(const uint8_t *u, const Rec &r) { return r.l_qseq <= 0 || ld8(u, r.qual) == 0xffu; }
+
+// Region filter of indexed scans (A8).  htslib reads the records of the index's chunks and keeps those with
+// `end > beg_q && end_q > beg` on the queried contig (hts_itr_next, htslib/hts.c:4301-4311; multi-region form
+// hts_itr_multi_next :4565-4597), end = bam_endpos (sam.c:519-524: pos + rlen, rlen = 1 for unmapped reads or a CIGAR
+// that consumes no reference).  Here the host turns the chunk list into one virtual-offset range and the overlap
+// test runs in the walk, so rejected records never cost a row, a heap byte or a PCIe byte.
+__device__ __forceinline__ bool region_pass(const WalkParams &p, const Rec &r) {
+    if (r.tid < 0) return false;
+    int64_t rl = (r.flag & 4u) ? 0 : r.rlen;
+    if (rl == 0) rl = 1;
+    const int64_t beg = r.pos, end = (int64_t)r.pos + rl;
+    if (p.filt_mode == 1) return end > 0;          // one whole-contig query per contig: [0, HTS_POS_MAX)
+    uint32_t lo = 0, hi = p.filt_n;                // first interval (sorted by tid, beg; disjoint) with (tid, end) > (r.tid, beg)
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        const RegIntv v = p.filt[mid];
+        if (v.tid < r.tid || (v.tid == r.tid && v.end <= beg)) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= p.filt_n) return false;
+    const RegIntv v = p.filt[lo];
+    return v.tid == r.tid && end > v.beg;
+}
 
 // =======================================================================================================
 // boundary walk: one thread per BGZF block
@@ -240,6 +266,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
         Rec r;
         int rc = parse_record(u, off, p.seg_end, p.is_final != 0, t.n_ref, r);
         if (rc != 0) { w.stop = rc; break; }
+        if (p.filt_mode && !region_pass(p, r)) { off = r.end; continue; }   // hts_itr_next / hts_itr_multi_next overlap test
         uint64_t need = 0;
         if ((t.col_mask >> COL_QNAME) & 1ull) need += slot_bytes(r.l_qname);
         if ((t.col_mask >> COL_CIGAR) & 1ull) need += slot_bytes(r.cigar_text_len);

@@ -54,6 +54,12 @@ struct BlockWalk {
     int32_t stop;         // 0; 1 = record at exit_off needs bytes beyond the segment; <0 = bam_read1 error code there
 };
 
+// one interval of a region query: [beg, end) 0-based on contig tid (hts_reglist_t intervals after reg_compact)
+struct RegIntv {
+    int64_t beg, end;
+    int32_t tid, pad;
+};
+
 struct WalkParams {
     const uint8_t *u;          // segment inflated base (offset 0); bytes [-carry, seg_end) are valid
     const int64_t *blk_start;  // n+1 block start offsets (blk_start[0] may be negative: carry pseudo-block)
@@ -68,6 +74,11 @@ struct WalkParams {
     // (a record is at least 36 bytes, so the ranges of consecutive blocks cannot overlap)
     uint16_t *rec;
     int64_t rec_bias;          // = blk_start[0]
+    // region filter: 0 none; 1 = every placed record (tid >= 0, end > 0: the reference's per-contig index scan);
+    // 2 = records overlapping one of the filt_n intervals (device array, sorted by tid then beg, disjoint)
+    int32_t filt_mode;
+    uint32_t filt_n;
+    const RegIntv *filt;
 };
 
 struct DecodeParams {

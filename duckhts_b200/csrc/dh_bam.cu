@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "bam_decode.cuh"
+#include "dh_index.h"
 #include "dh_internal.h"
 #include "inflate_core.cuh"
 
@@ -103,6 +104,11 @@ struct dh_bam {
     int64_t first_entry = 0;       // in-block offset of the first record of the scan
     dh_bam_scan_stats st;
     cudaEvent_t ev_scan0 = nullptr;
+    // indexed scans (A8): overlap filter applied by the walk kernel + the virtual-offset ranges still to scan
+    int filt_mode = 0;
+    std::vector<RegIntv> filt;
+    DevBuf d_filt;
+    std::deque<IdxChunk> pending;
 };
 
 namespace {
@@ -396,6 +402,9 @@ int walk_segment(dh_bam *b, int k) {
     wp.limit_end = limit_end;
     wp.rec = (uint16_t *)s.rec.p;
     wp.rec_bias = s.rec_bias = -b->carry;
+    wp.filt_mode = b->filt_mode;
+    wp.filt_n = (uint32_t)b->filt.size();
+    wp.filt = (const RegIntv *)b->d_filt.p;
     BlockWalk *hw = (BlockWalk *)s.h_walk.p;
     uint32_t validated = 0;  // blocks [0, validated) have entry == predecessor's exit
     bool stopped = false;
@@ -639,7 +648,7 @@ void dh_bam_close(dh_bam *b) {
         s.arena.release(); s.h_arena.release();
         for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_c0, s.ev_done}) if (e) cudaEventDestroy(e);
     }
-    b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release(); b->d_image.release();
+    b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release(); b->d_image.release(); b->d_filt.release();
     delete b;
 }
 
@@ -707,28 +716,39 @@ int dh_bam_set_mode(dh_bam *b, uint32_t flags) {
     return DH_OK;
 }
 
-int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
-    if (!b) { set_error("dh_bam_scan_begin: null handle"); return DH_EINVAL; }
+// (block, in-block offset) of a virtual offset.  htslib's bgzf_tell reports "end of block k" as (k, isize) while the next
+// record really starts at (k + 1, 0); empty blocks are skipped the same way (htslib/bgzf.c:1145-1228).
+static int locate_voff(const dh_bam *b, uint64_t voff, const char *what, size_t &blk, uint32_t &off) {
+    const BlockTable &bt = b->bt;
+    const size_t nb = bt.blocks.size();
+    blk = block_of(b, voff >> 16);
+    off = (uint32_t)(voff & 0xffff);
+    if (blk < nb && bt.blocks[blk].coffset != (voff >> 16)) { set_error("%s is not a BGZF block address", what); return DH_EINVAL; }
+    while (blk < nb && off >= bt.blocks[blk].isize) {
+        if (off > bt.blocks[blk].isize) { set_error("%s points beyond the end of its BGZF block", what); return DH_EINVAL; }
+        ++blk;
+        off = 0;
+    }
+    return DH_OK;
+}
+
+// Start scanning one virtual-offset range.  `fresh` = first range of a scan: counters and statistics restart.
+static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh) {
     DH_CUDA(cudaSetDevice(b->ctx->device));
     DH_CUDA(cudaDeviceSynchronize());  // drop whatever an abandoned scan left in flight
     const BlockTable &bt = b->bt;
     const size_t nb = bt.blocks.size();
     size_t b_first = b->first_blk;
     uint32_t off_first = b->first_off;
-    if (voff_beg != 0) {
-        b_first = block_of(b, voff_beg >> 16);
-        off_first = (uint32_t)(voff_beg & 0xffff);
-        if (b_first < nb && bt.blocks[b_first].coffset != (voff_beg >> 16)) { set_error("voff_beg is not a BGZF block address"); return DH_EINVAL; }
-    }
+    int rc;
+    if (voff_beg != 0 && (rc = locate_voff(b, voff_beg, "voff_beg", b_first, off_first)) != DH_OK) return rc;
     b->to_eof = voff_end == UINT64_MAX || (voff_end >> 16) >= bt.end_off;
     size_t b_stop = nb;
     if (!b->to_eof) {
-        b->limit_blk = block_of(b, voff_end >> 16);
-        b->limit_off = (uint32_t)(voff_end & 0xffff);
-        if (b->limit_blk < nb && bt.blocks[b->limit_blk].coffset != (voff_end >> 16)) { set_error("voff_end is not a BGZF block address"); return DH_EINVAL; }
+        if ((rc = locate_voff(b, voff_end, "voff_end", b->limit_blk, b->limit_off)) != DH_OK) return rc;
+        if (b->limit_blk >= nb) b->to_eof = true;
         // inflate up to the limit block plus look-ahead for a record that straddles the range end
-        b_stop = std::min(nb, b->limit_blk + (b->limit_off ? 1 : 0) + 2);
-        if (b_stop >= nb) { b_stop = nb; }
+        else b_stop = std::min(nb, b->limit_blk + (b->limit_off ? 1 : 0) + 2);
     }
     b->end_blk = b_stop;
     b->segs.clear();
@@ -750,15 +770,113 @@ int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
     b->next_batch_i = 0;
     b->inflight.clear();
     b->issued = b->returned = 0;
-    b->rows_total = 0;
     b->carry = 0;
-    b->final_status = 0;
     b->chain_done = b->segs.empty();
-    memset(&b->st, 0, sizeof b->st);
-    b->st.end_voffset = voff_beg ? voff_beg : dh_bam_first_voffset(b);
-    if (!b->ev_scan0) DH_CUDA(cudaEventCreate(&b->ev_scan0));
-    DH_CUDA(cudaEventRecord(b->ev_scan0, s_comp(b)));
+    if (fresh) {
+        b->rows_total = 0;
+        b->final_status = 0;
+        memset(&b->st, 0, sizeof b->st);
+        b->st.end_voffset = voff_beg ? voff_beg : dh_bam_first_voffset(b);
+        if (!b->ev_scan0) DH_CUDA(cudaEventCreate(&b->ev_scan0));
+        DH_CUDA(cudaEventRecord(b->ev_scan0, s_comp(b)));
+    }
     b->scanning = true;
+    return DH_OK;
+}
+
+int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
+    if (!b) { set_error("dh_bam_scan_begin: null handle"); return DH_EINVAL; }
+    b->filt_mode = 0;
+    b->filt.clear();
+    b->pending.clear();
+    return begin_range(b, voff_beg, voff_end, true);
+}
+
+// ---- A8: indexed scans ------------------------------------------------------------------------------------
+dh_index *dh_index_load(dh_ctx *ctx, const uint8_t *data, uint64_t size) {
+    if (!data || size < 8) { set_error("dh_index_load: bad arguments"); return nullptr; }
+    std::vector<uint8_t> plain;
+    if (data[0] == 0x1f && data[1] == 0x8b) {   // CSI files are BGZF-compressed: inflate on the GPU like any other BGZF stream
+        if (!ctx) { set_error("dh_index_load: a context is needed to inflate a BGZF-compressed index"); return nullptr; }
+        uint64_t n = 0;
+        if (dh_bgzf_inflate_host(ctx, data, size, nullptr, 0, &n, nullptr) != DH_OK) return nullptr;
+        plain.resize((size_t)n + 8);
+        if (dh_bgzf_inflate_host(ctx, data, size, plain.data(), plain.size(), &n, nullptr) != DH_OK) return nullptr;
+        data = plain.data();
+        size = n;
+    }
+    dh_index *ix = new dh_index();
+    std::string err;
+    if (!index_parse(data, size, ix->ix, err)) { set_error("%s", err.c_str()); delete ix; return nullptr; }
+    return ix;
+}
+void dh_index_free(dh_index *ix) { delete ix; }
+int32_t dh_index_n_ref(const dh_index *ix) { return ix ? (int32_t)ix->ix.refs.size() : 0; }
+int dh_index_is_csi(const dh_index *ix) { return ix && ix->ix.csi; }
+uint64_t dh_index_n_no_coor(const dh_index *ix) { return ix ? ix->ix.n_no_coor : 0; }
+
+static int start_filtered(dh_bam *b, const dh_index *idx, int mode) {
+    std::vector<IdxChunk> ranges;
+    plan_ranges(idx->ix, b->filt, ranges);
+    b->pending.assign(ranges.begin(), ranges.end());
+    b->filt_mode = mode;
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    int rc = b->d_filt.reserve(std::max<size_t>(1, b->filt.size()) * sizeof(RegIntv));
+    if (rc != DH_OK) return rc;
+    if (!b->filt.empty()) DH_CUDA(cudaMemcpy(b->d_filt.p, b->filt.data(), b->filt.size() * sizeof(RegIntv), cudaMemcpyHostToDevice));
+    if (b->pending.empty()) {
+        // nothing indexed under the query: an iterator that is already finished (hts_itr_query :3467-3470, :3533-3537)
+        rc = begin_range(b, 0, UINT64_MAX, true);
+        b->segs.clear();
+        b->chain_done = true;
+        return rc;
+    }
+    const IdxChunk c = b->pending.front();
+    b->pending.pop_front();
+    return begin_range(b, c.u, c.v, true);
+}
+
+int dh_bam_scan_regions(dh_bam *b, const dh_index *idx, const char *const *regions, int n_regions) {
+    if (!b || !idx || (n_regions > 0 && !regions)) { set_error("dh_bam_scan_regions: bad arguments"); return DH_EINVAL; }
+    std::string err;
+    const int n = regions_to_intervals(regions, n_regions, b->ref_names, b->filt, err);
+    if (n < 0) { set_error("%s", err.c_str()); return DH_EINVAL; }
+    if (n == 0) { set_error("no region names a reference sequence of this file"); return DH_ENOREGION; }
+    return start_filtered(b, idx, 2);
+}
+
+int dh_bam_scan_contigs(dh_bam *b, const dh_index *idx, int32_t tid_lo, int32_t tid_hi) {
+    if (!b || !idx) { set_error("dh_bam_scan_contigs: bad arguments"); return DH_EINVAL; }
+    const int32_t n_ref = (int32_t)b->ref_names.size();
+    tid_lo = std::max(tid_lo, 0);
+    tid_hi = std::min(tid_hi, n_ref);
+    b->filt.clear();
+    for (int32_t t = tid_lo; t < tid_hi; ++t) {
+        RegIntv v;
+        v.tid = t; v.beg = 0; v.end = INT64_MAX; v.pad = 0;
+        b->filt.push_back(v);
+    }
+    return start_filtered(b, idx, (tid_lo == 0 && tid_hi == n_ref) ? 1 : 2);
+}
+
+int dh_bam_split_contigs(const dh_bam *b, const dh_index *idx, int n_parts, int32_t *tid_bounds) {
+    if (!b || !idx || n_parts < 1 || !tid_bounds) { set_error("dh_bam_split_contigs: bad arguments"); return DH_EINVAL; }
+    const int32_t n_ref = (int32_t)b->ref_names.size();
+    std::vector<uint64_t> pre((size_t)n_ref + 1, 0);   // compressed bytes of contigs [0, t)
+    for (int32_t t = 0; t < n_ref; ++t) {
+        uint64_t u, v, w = 0;
+        if (contig_span(idx->ix, t, u, v) && (v >> 16) >= (u >> 16)) w = (v >> 16) - (u >> 16) + 1;
+        pre[(size_t)t + 1] = pre[(size_t)t] + w;
+    }
+    tid_bounds[0] = 0;
+    for (int p = 1; p < n_parts; ++p) {
+        const uint64_t target = pre[(size_t)n_ref] / (uint64_t)n_parts * (uint64_t)p;
+        int32_t t = (int32_t)(std::lower_bound(pre.begin(), pre.end(), target) - pre.begin());
+        // cut at the contig boundary nearest to the target
+        if (t > 0 && target - pre[(size_t)t - 1] < pre[(size_t)std::min(t, n_ref)] - target) --t;
+        tid_bounds[p] = std::min(std::max(t, tid_bounds[p - 1]), n_ref);
+    }
+    tid_bounds[n_parts] = n_ref;
     return DH_OK;
 }
 
@@ -777,6 +895,12 @@ int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
     };
     int rc = top_up();
     if (rc != DH_OK) { b->scanning = false; return rc; }
+    while (b->inflight.empty() && !b->pending.empty() && b->final_status == 0) {
+        // this range is exhausted: go on with the next one of the query (rows keep counting)
+        const IdxChunk c = b->pending.front();
+        b->pending.pop_front();
+        if ((rc = begin_range(b, c.u, c.v, false)) != DH_OK || (rc = top_up()) != DH_OK) { b->scanning = false; return rc; }
+    }
     if (b->inflight.empty()) {
         b->st.rows = b->rows_total;
         b->st.status = b->final_status;

@@ -7,6 +7,12 @@
  *                                         [0x21,0x7e] and '\' as \xHH; last line "#status <code> <n>"
  *   ref_dump sam2bam IN OUT               convert (for turning htslib's .sam fixtures into BAM)
  *   ref_dump bgunzip FILE                 raw bgzf_read() stream to stdout
+ *   ref_dump dumpregion FILE REGIONS [TAG:type ...]   like dump, but through sam_index_load3 + sam_itr_regarray +
+ *                                         sam_itr_next exactly as src/bam_reader.c:642-671,749-752 (REGIONS = the
+ *                                         `region` parameter: comma separated); "#no-iterator" if regarray fails
+ *   ref_dump dumpcontigs FILE [TAG:type ...]          the index-driven scan without a region: sam_itr_queryi per
+ *                                         contig in order (bam_reader.c:689-716), empty contigs skipped
+ *   ref_dump index FILE MIN_SHIFT         sam_index_build (0 = BAI, 14 = CSI)
  */
 #include <inttypes.h>
 #include <stdio.h>
@@ -51,6 +57,9 @@ int main(int argc, char **argv) {
         sam_close(in);
         return sam_close(out) < 0 || r < -1;
     }
+    if (!strcmp(argv[1], "index")) return sam_index_build(argv[2], argc > 3 ? atoi(argv[3]) : 0) < 0;
+    const int by_region = !strcmp(argv[1], "dumpregion"), by_contig = !strcmp(argv[1], "dumpcontigs");
+    const int tag0 = by_region ? 4 : 3;
     samFile *fp = sam_open(argv[2], "r");
     if (!fp) { fprintf(stderr, "cannot open %s\n", argv[2]); return 1; }
     sam_hdr_t *hdr = sam_hdr_read(fp);
@@ -63,7 +72,31 @@ int main(int argc, char **argv) {
     int ret;
     printf("#n_ref %d\n", sam_hdr_nref(hdr));
     for (int i = 0; i < sam_hdr_nref(hdr); ++i) { printf("#ref "); put_cstr(sam_hdr_tid2name(hdr, i)); printf(" %" PRId64 "\n", (int64_t)sam_hdr_tid2len(hdr, i)); }
-    while ((ret = sam_read1(fp, hdr, b)) >= 0) {
+    hts_idx_t *idx = NULL;
+    hts_itr_t *itr = NULL;
+    int contig = -1;
+    if (by_region || by_contig) {
+        idx = sam_index_load3(fp, argv[2], NULL, HTS_IDX_SILENT_FAIL);
+        if (!idx) { printf("#no-index\n"); return 0; }
+    }
+    if (by_region) {
+        char *dup = strdup(argv[3]), *regs[256];
+        unsigned nreg = 0;
+        for (char *tok = strtok(dup, ","); tok && nreg < 256; tok = strtok(NULL, ",")) regs[nreg++] = tok;   /* parse_regions, bam_reader.c:318-348 */
+        itr = sam_itr_regarray(idx, hdr, regs, nreg);
+        if (!itr) { printf("#no-iterator\n"); return 0; }
+    }
+    for (;;) {
+        if (by_contig && !itr) {
+            if (++contig >= sam_hdr_nref(hdr)) { ret = -1; break; }
+            itr = sam_itr_queryi(idx, contig, 0, HTS_POS_MAX);
+            if (!itr) continue;
+        }
+        ret = itr ? sam_itr_next(fp, itr, b) : sam_read1(fp, hdr, b);
+        if (ret < 0) {
+            if (by_contig && ret == -1) { hts_itr_destroy(itr); itr = NULL; continue; }
+            break;
+        }
         int l = b->core.l_qseq;
         if ((size_t)l + 1 > cap) { cap = (size_t)l + 1; buf = realloc(buf, cap); }
         put_cstr(bam_get_qname(b));
@@ -89,7 +122,7 @@ int main(int argc, char **argv) {
         putchar('\t');
         sm.l = 0;
         if (rg && sam_hdr_find_tag_id(hdr, "RG", "ID", rg, "SM", &sm) == 0 && sm.s && sm.l > 0) put_cstr(sm.s); else printf("\\N");
-        for (int t = 3; t < argc; ++t) {
+        for (int t = tag0; t < argc; ++t) {
             const char *tag = argv[t];
             char type = tag[3];
             putchar('\t');

@@ -26,6 +26,7 @@ extern "C" {
 #define DH_EDATA (-4)   /* a block failed inflate / CRC / ISIZE (htslib BGZF_ERR_ZLIB / BGZF_ERR_CRC) */
 #define DH_ENOMEM (-5)
 #define DH_EIO (-6)
+#define DH_ENOREGION (-7) /* no requested region names a reference sequence (sam_itr_regarray returned NULL) */
 
 typedef struct dh_ctx dh_ctx;
 
@@ -189,6 +190,33 @@ int dh_bam_scan_stats_get(const dh_bam *b, dh_bam_scan_stats *out);
  * size on BGZF block boundaries (htslib-written BAM starts every block on a record boundary, htslib/sam.c:883).
  * voffs[0] = first record, voffs[n_parts] = UINT64_MAX. */
 int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs);
+
+/* ---- A8: BAI/CSI index, region queries, contig-parallel scans -----------------------------------------------
+ * Replaces hts_idx_load3 -> idx_read / idx_read_core (htslib/hts.c:2920-3055) and, per query, sam_itr_regarray /
+ * sam_itr_queryi -> hts_itr_query / hts_itr_multi_bam (hts.c:3421-3745) plus the record filter of hts_itr_next /
+ * hts_itr_multi_next (hts.c:4266-4604) that src/bam_reader.c:642-671,689-716,749-752 drives.  The index is parsed on
+ * the host (a CSI file is BGZF: it is inflated by the GPU kernel first); a query becomes a few virtual-offset ranges
+ * and an overlap filter evaluated inside the record-boundary kernel, so only matching records produce rows.  Rows:
+ * the records, in file order, that overlap any requested interval (each once) — the iterator's result on a
+ * coordinate-sorted file.  `data` is the index file image (BAI: "BAI\1"; CSI: BGZF-wrapped "CSI\1"). */
+typedef struct dh_index dh_index;
+dh_index *dh_index_load(dh_ctx *ctx, const uint8_t *data, uint64_t size);
+void dh_index_free(dh_index *ix);
+int32_t dh_index_n_ref(const dh_index *ix);
+int dh_index_is_csi(const dh_index *ix);
+uint64_t dh_index_n_no_coor(const dh_index *ix);
+/* Region strings as read_bam's `region` parameter carries them after splitting at commas (src/bam_reader.c:318-348):
+ * "chr", "chr:beg-end", "chr:beg", "chr:-end", "{chr}:beg-end"; 1-based inclusive; thousands separators allowed.
+ * Unknown names are skipped like htslib does; if none is left the call returns DH_ENOREGION (the reference reports
+ * "No reads found for region(s): ..." at init).  Starts the scan: follow with dh_bam_next_batch. */
+int dh_bam_scan_regions(dh_bam *b, const dh_index *idx, const char *const *regions, int n_regions);
+/* The reference's index-driven scan without a region (src/bam_reader.c:577-585,689-716): contigs tid_lo..tid_hi-1, one
+ * whole-contig query each, in contig order.  Reads without a contig (tid = -1) are not returned.  This is
+ * also the unit of region-sharded multi-GPU scans: rank r scans the contig group dh_bam_split_contigs gives it. */
+int dh_bam_scan_contigs(dh_bam *b, const dh_index *idx, int32_t tid_lo, int32_t tid_hi);
+/* n_parts + 1 contig bounds cutting [0, n_ref) into contiguous groups of about equal compressed size (from the
+ * index's chunk offsets). */
+int dh_bam_split_contigs(const dh_bam *b, const dh_index *idx, int n_parts, int32_t *tid_bounds);
 
 /* CUDA-event timer on the context's stream (the stream every kernel of this library is launched on). */
 int dh_ctx_sync(dh_ctx *ctx);

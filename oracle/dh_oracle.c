@@ -86,3 +86,4 @@ int dho_bgzf_inflate(const uint8_t *data, uint64_t size, uint8_t *out, uint64_t 
 }
 
 #include "dh_oracle_bam.inc"
+#include "dh_oracle_idx.inc"

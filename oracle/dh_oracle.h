@@ -86,6 +86,7 @@ typedef struct {
     /* 0 = clean EOF; <0 = the bam_read1/sam_read1_bam error code that ended the scan after n records
      * (the reference stops silently) */
     int status;
+    int64_t *endpos;       /* bam_endpos (htslib/sam.c:519-524) of every record: what index iterators compare */
 } dho_bam_columns;
 
 /* htslib/sam.c:229-342 (bam_hdr_read), :779-855 (bam_read1), :4124-4134 (sam_read1_bam range check),
@@ -94,6 +95,21 @@ typedef struct {
  * Returns 0, or -1 if the header itself is invalid (the reference fails in bind). */
 int dho_bam_decode(const uint8_t *u, uint64_t n, const dho_tag_req *tags, int n_tags, dho_bam_columns *out);
 void dho_bam_free(dho_bam_columns *c);
+
+/* ---- A8: BAI/CSI index + iterators (dh_oracle_idx.inc) ------------------------------------------------
+ * idx_read_core / update_loff (htslib/hts.c:2920-2983, 2426-2455); hts_itr_query + hts_itr_next (:3421-3595,
+ * 4266-4318) = sam_itr_queryi; hts_itr_multi_bam + hts_itr_multi_next (:3597-3745, 4320-4604) = sam_itr_regarray.
+ * Records are described by arrays: virtual offset of each record and of the record after it (bgzf_tell before /
+ * after the read), tid, pos, bam_endpos.  The functions write the indices of the records the iterator returns. */
+typedef struct dho_index dho_index;
+dho_index *dho_index_parse(const uint8_t *data, uint64_t size);   /* uncompressed BAI / CSI image */
+void dho_index_free(dho_index *ix);
+int32_t dho_index_n_ref(const dho_index *ix);
+int64_t dho_itr_query_rows(const dho_index *ix, uint64_t n_rec, const uint64_t *voff, const uint64_t *voff_next, const int32_t *rtid,
+                           const int64_t *rbeg, const int64_t *rend, int tid, int64_t beg, int64_t end, uint64_t *out);
+int64_t dho_itr_regions_rows(const dho_index *ix, uint64_t n_rec, const uint64_t *voff, const uint64_t *voff_next, const int32_t *rtid,
+                             const int64_t *rbeg, const int64_t *rend, int n_iv, const int32_t *iv_tid, const int64_t *iv_beg,
+                             const int64_t *iv_end, uint64_t *out);
 
 #ifdef __cplusplus
 }

@@ -28,3 +28,21 @@ for f in *.bam; do
 done
 $D bgunzip bgziptest.txt.gz | sha256sum | cut -d' ' -f1 > bgziptest.txt.sha256
 ls -la
+# ---- A8: index-driven scans of range.bam (.bai from the reference's test/data) through sam_itr_regarray / sam_itr_queryi
+cp $REF/test/data/range.bam.bai range.bam.bai; chmod u+w range.bam.bai
+k=0
+while IFS= read -r reg; do
+  $D dumpregion range.bam "$reg" $TAGS > "range.region$k.tsv"; echo "$reg" > "range.region$k.txt"; k=$((k+1))
+done <<'REGIONS'
+CHROMOSOME_I
+CHROMOSOME_I:1-1000
+CHROMOSOME_I:1-1000,CHROMOSOME_I:1-1000
+CHROMOSOME_II:2000-2500,CHROMOSOME_IV:1000-1100,CHROMOSOME_II:1-1200
+CHROMOSOME_III:2,900-
+CHROMOSOME_V
+nosuchcontig,CHROMOSOME_IV:-1500
+nosuchcontig
+CHROMOSOME_II:1136-1136
+{CHROMOSOME_X}:1-10,CHROMOSOME_III:1k-1.1k
+REGIONS
+$D dumpcontigs range.bam $TAGS > range.contigs.tsv
