@@ -97,6 +97,8 @@ typedef struct {
     uint8_t *image;
     uint64_t size;
     dh_bam *bam;
+    dh_index *index;         /* BAI/CSI next to the file (or index_path), NULL if none: sam_index_load3, bam_reader.c:499 */
+    char *region;            /* the `region` parameter as given (comma separated), NULL if absent or empty */
     int standard_tags, has_index, n_contigs;
     int n_cols;
 } bam_bind_t;
@@ -114,8 +116,10 @@ static void bam_bind_free(void *p) {
     bam_bind_t *b = (bam_bind_t *)p;
     if (!b) return;
     if (b->bam) dh_bam_close(b->bam);
+    if (b->index) dh_index_free(b->index);
     if (b->image) dh_host_free(b->image);
     free(b->path);
+    free(b->region);
     api.duckdb_free(b);
 }
 static void bam_local_free(void *p) {
@@ -142,7 +146,6 @@ static void read_bam_bind(duckdb_bind_info info) {
     bam_bind_t *b = NULL;
     dh_ctx *ctx = shared_ctx();
     if (!ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
-    else if (region && region[0]) snprintf(err, sizeof err, "read_bam: region queries are not available in this build (BAI/CSI support is the next row of the scope table)");
     else if (auxiliary_tags) snprintf(err, sizeof err, "read_bam: auxiliary_tags := true is not available in this build");
     else {
         b = (bam_bind_t *)api.duckdb_malloc(sizeof *b);
@@ -163,15 +166,29 @@ static void read_bam_bind(duckdb_bind_info info) {
     b->path = strdup(path);
     b->standard_tags = standard_tags;
     b->n_contigs = dh_bam_n_ref(b->bam);
-    /* index probe like sam_index_load3: explicit path, else PATH.bai / PATH.csi / PATH with .bam -> .bai */
+    if (region && region[0]) b->region = strdup(region);
+    /* index lookup like sam_index_load3(fp, path, index_path, HTS_IDX_SILENT_FAIL) (htslib/hts.c idx_find_and_load):
+     * explicit path, else PATH.csi, PATH with its suffix replaced by .csi, PATH.bai, PATH with .bai */
     {
-        char cand[3][1024];
-        snprintf(cand[0], sizeof cand[0], "%s.bai", path);
-        snprintf(cand[1], sizeof cand[1], "%s.csi", path);
-        snprintf(cand[2], sizeof cand[2], "%s", path);
-        size_t n = strlen(cand[2]);
-        if (n > 4 && !strcmp(cand[2] + n - 4, ".bam")) strcpy(cand[2] + n - 4, ".bai"); else cand[2][0] = 0;
-        b->has_index = index_path ? file_exists(index_path) : (file_exists(cand[0]) || file_exists(cand[1]) || (cand[2][0] && file_exists(cand[2])));
+        char cand[5][1100];
+        int nc = 0;
+        if (index_path) snprintf(cand[nc++], sizeof cand[0], "%s", index_path);
+        else {
+            static const char *const EXT[2] = {".csi", ".bai"};
+            const char *dot = strrchr(path, '.'), *slash = strrchr(path, '/');
+            for (int e = 0; e < 2; ++e) {
+                snprintf(cand[nc++], sizeof cand[0], "%s%s", path, EXT[e]);
+                if (dot && (!slash || dot > slash)) snprintf(cand[nc++], sizeof cand[0], "%.*s%s", (int)(dot - path), path, EXT[e]);
+            }
+        }
+        for (int i = 0; i < nc && !b->index; ++i) {
+            if (!file_exists(cand[i])) continue;
+            uint64_t isz = 0;
+            uint8_t *ibuf = slurp_pinned(cand[i], &isz);
+            if (ibuf) { b->index = dh_index_load(ctx, ibuf, isz); dh_host_free(ibuf); }
+            if (!index_path) break;        /* the first file that exists is the one htslib reads */
+        }
+        b->has_index = b->index != NULL;
     }
     duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER),
                         t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT), t_usmall = api.duckdb_create_logical_type(DUCKDB_TYPE_USMALLINT),
@@ -231,8 +248,29 @@ static void read_bam_local_init(duckdb_init_info info) {
         mask |= 1ull << (N_CORE + n_tags);
         ++n_tags;
     }
-    if (dh_bam_set_projection(b->bam, mask, tags, n_tags) != DH_OK || dh_bam_scan_begin(b->bam, 0, UINT64_MAX) != DH_OK) {
-        api.duckdb_init_set_error(info, dh_last_error());
+    /* which rows (src/bam_reader.c:601-671): region(s) through the index; else, with an index and more than one contig,
+     * contig by contig (reads without a contig are then never returned); else the whole file in order */
+    int rc = dh_bam_set_projection(b->bam, mask, tags, n_tags);
+    char err[1200];
+    err[0] = 0;
+    if (rc != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+    else if (b->region) {
+        if (!b->index) snprintf(err, sizeof err, "Region query requires an index (.bai/.csi/.crai)");
+        else {
+            char *dup = strdup(b->region), *save = NULL;
+            const char *regs[1024];
+            int nreg = 0;
+            for (char *tok = strtok_r(dup, ",", &save); tok && nreg < 1024; tok = strtok_r(NULL, ",", &save)) regs[nreg++] = tok;
+            rc = dh_bam_scan_regions(b->bam, b->index, regs, nreg);
+            if (rc == DH_ENOREGION) snprintf(err, sizeof err, "No reads found for region(s): %s", b->region);
+            else if (rc != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+            free(dup);
+        }
+    } else if (b->index && b->n_contigs > 1) {
+        if (dh_bam_scan_contigs(b->bam, b->index, 0, b->n_contigs) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+    } else if (dh_bam_scan_begin(b->bam, 0, UINT64_MAX) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+    if (err[0]) {
+        api.duckdb_init_set_error(info, err);
         bam_local_free(l);
         return;
     }

@@ -97,3 +97,39 @@ def test_bgunzip_writes_identical_bytes(tmp_path):
         assert rc == 1
         msgs.append(text.replace(tag + ".bin", "X.bin"))
     assert msgs[0] == msgs[1]
+
+
+# ---- A8: region queries and the index-driven contig scan, cell for cell against the reference extension -------------
+@pytest.mark.parametrize("region", ["CHROMOSOME_I", "CHROMOSOME_I:1-1000", "CHROMOSOME_I:1-1000,CHROMOSOME_I:1-1000",
+                                    "CHROMOSOME_II:2000-2500,CHROMOSOME_IV:1000-1100,CHROMOSOME_II:1-1200", "CHROMOSOME_V",
+                                    "nosuchcontig,CHROMOSOME_IV:-1500", "CHROMOSOME_II:1136-1136"])
+def test_region_queries_match_reference_extension(region):
+    path = os.path.join(GOLD, "range.bam")       # range.bam.bai sits next to it (reference test/data)
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "region=" + region)
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r
+
+
+def test_region_errors_read_like_the_reference():
+    # no region names a known contig -> init error; region on a file without index -> init error
+    for path, region in ((os.path.join(GOLD, "range.bam"), "nosuchcontig"), (os.path.join(GOLD, "rg.bam"), "xx:1-10")):
+        (rc_r, out_r, _), (rc_o, out_o, _) = both("read_bam", path, "region=" + region)
+        assert rc_r == 1 and rc_o == 1
+        assert out_o == out_r
+
+
+def test_indexed_synthetic_file_regions_and_contig_mode():
+    path = util.synth_path("bam", n_records=30000, seed=31, paired=True, extra=("--unplaced", "25"), index=True)
+    cols = ",".join(str(c) for c in range(13 + 56) if c not in B_COLS)
+    for args in ((), ("region=chr3:10,000,000-20,000,000",), ("region=chr2:1-5000000,chr2:4000000-9000000,chr7:49000000-",),
+                 ("region=chr22:-1000000,chr5:25m-26m",)):
+        (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "standard_tags=true", "--cols", cols, "--hash", *args)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r, args
+    # explicit index_path (a copy under another name)
+    import shutil
+    alt = path + ".alt_index"
+    shutil.copyfile(path + ".bai", alt)
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "index_path=" + alt, "region=chr9", "--hash")
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r
