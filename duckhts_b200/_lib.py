@@ -41,6 +41,18 @@ class BamScanStats(C.Structure):
                 ("end_voffset", C.c_uint64), ("inflate_ms", C.c_float), ("walk_ms", C.c_float), ("decode_ms", C.c_float)]
 
 
+class BcfField(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("type", C.c_int32), ("is_list", C.c_int32)]
+
+
+class BcfBatch(C.Structure):
+    _fields_ = [("n_records", C.c_uint64), ("n_samples", C.c_uint64), ("rec0", C.c_uint64), ("status", C.c_int32), ("pad", C.c_int32),
+                ("core", C.c_void_p * 7), ("core_validity", C.c_void_p * 7),
+                ("info", C.POINTER(C.c_void_p)), ("info_validity", C.POINTER(C.c_void_p)),
+                ("format", C.POINTER(C.c_void_p)), ("format_validity", C.POINTER(C.c_void_p)),
+                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64)]
+
+
 _lib = None
 
 # name -> (restype, argtypes); tests/test_abi.py checks every symbol declared in include/*.h is here and exported
@@ -88,6 +100,24 @@ SIGNATURES = {
     "dh_bam_scan_regions": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_char_p), C.c_int]),
     "dh_bam_scan_contigs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
     "dh_bam_split_contigs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int32)]),
+    "dh_bcf_open": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "dh_bcf_close": (None, [C.c_void_p]),
+    "dh_bcf_n_samples": (C.c_int32, [C.c_void_p]),
+    "dh_bcf_sample_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "dh_bcf_n_contigs": (C.c_int32, [C.c_void_p]),
+    "dh_bcf_contig_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "dh_bcf_n_info": (C.c_int32, [C.c_void_p]),
+    "dh_bcf_n_format": (C.c_int32, [C.c_void_p]),
+    "dh_bcf_info_field": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(BcfField)]),
+    "dh_bcf_format_field": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(BcfField)]),
+    "dh_bcf_has_vep": (C.c_int, [C.c_void_p]),
+    "dh_bcf_header_text": (C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint32)]),
+    "dh_bcf_set_projection": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "dh_bcf_configure": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64]),
+    "dh_bcf_set_mode": (C.c_int, [C.c_void_p, C.c_uint32]),
+    "dh_bcf_scan_begin": (C.c_int, [C.c_void_p]),
+    "dh_bcf_next_batch": (C.c_int, [C.c_void_p, C.POINTER(BcfBatch)]),
+    "dh_bcf_scan_stats_get": (C.c_int, [C.c_void_p, C.POINTER(BamScanStats)]),
     "dh_ctx_sync": (C.c_int, [C.c_void_p]),
     "dh_timer_start": (C.c_int, [C.c_void_p]),
     "dh_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),

@@ -16,100 +16,10 @@
 #include <string>
 #include <vector>
 
-#include "bam_decode.cuh"
-#include "dh_index.h"
-#include "dh_internal.h"
+#include "dh_scan.h"
 #include "inflate_core.cuh"
 
 using namespace dh;
-
-namespace {
-
-constexpr int NSEG = 3, NBATCH = 6;
-constexpr uint64_t A256 = 255;
-
-struct Batch {           // one output batch of the current segment
-    uint32_t b_lo, b_hi; // walk-block index range
-    uint64_t rows, heap, row0;
-};
-
-struct SegSlot {
-    DevBuf comp, out, desc, status, work, rec;
-    int64_t rec_bias = 0;
-    PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base;
-    cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_inf_done = nullptr, ev_free = nullptr, ev_walk0 = nullptr,
-                ev_walk1 = nullptr, ev_walk2 = nullptr;
-    size_t b0 = 0, b1 = 0;  // file block range
-    uint64_t cbase = 0, obytes = 0;
-    int issued_for = -1;    // segment index whose inflate was issued into this slot
-};
-
-struct BatchSlot {
-    DevBuf arena;
-    PinBuf h_arena;
-    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c0 = nullptr, ev_done = nullptr;
-    dh_bam_batch desc;
-    bool timed = false;
-};
-
-struct Seg { size_t b0, b1; };
-
-}  // namespace
-
-struct dh_bam {
-    dh_ctx *ctx = nullptr;
-    const uint8_t *data = nullptr;
-    uint64_t size = 0;
-    BlockTable bt;
-    // header
-    std::string text;
-    std::vector<std::string> ref_names;
-    std::vector<uint32_t> ref_lens;
-    size_t first_blk = 0;
-    uint32_t first_off = 0;
-    // dictionaries (host strings must keep stable addresses: cells point at them)
-    std::deque<std::string> dict;
-    std::vector<StrCell> ref_cells;
-    std::vector<RgEntry> rg;
-    std::string rg_ids;
-    DevBuf d_ref_cells, d_rg, d_rg_ids, d_tags;
-    DevBuf d_image;                // whole compressed image staged in HBM (DH_BAM_DEVICE_INPUT)
-    uint32_t mode = 0;
-    // projection
-    uint64_t col_mask = (1ull << BAM_CORE_COLS) - 1;
-    std::vector<TagReq> tags;
-    ScanTables tabs;
-    // knobs
-    uint64_t seg_comp = 1024ull << 20;
-    uint32_t batch_rows = 1u << 20;
-    uint64_t carry_cap = 8ull << 20;
-    // scan state
-    std::vector<Seg> segs;
-    SegSlot ss[NSEG];
-    BatchSlot bs[NBATCH];
-    bool scanning = false;
-    int cur_seg = -1;              // segment whose batches are being issued
-    std::vector<Batch> batches;    // of cur_seg
-    size_t next_batch_i = 0;
-    uint64_t issued = 0, returned = 0;  // batch counters (slot = counter % NBATCH)
-    std::deque<uint64_t> inflight;
-    uint64_t rows_total = 0;
-    int64_t carry = 0;             // bytes of the incomplete record at the end of the previous segment
-    int final_status = 0;
-    bool chain_done = false;       // range end / error / EOF reached: no further segments
-    size_t end_blk = 0;            // first block NOT inflated for this scan
-    size_t limit_blk = 0;          // block index of voff_end (records starting at/after (limit_blk, limit_off) are excluded)
-    uint32_t limit_off = 0;
-    bool to_eof = true;
-    int64_t first_entry = 0;       // in-block offset of the first record of the scan
-    dh_bam_scan_stats st;
-    cudaEvent_t ev_scan0 = nullptr;
-    // indexed scans (A8): overlap filter applied by the walk kernel + the virtual-offset ranges still to scan
-    int filt_mode = 0;
-    std::vector<RegIntv> filt;
-    DevBuf d_filt;
-    std::deque<IdxChunk> pending;
-};
 
 namespace {
 
@@ -362,7 +272,8 @@ int walk_segment(dh_bam *b, int k) {
     int rc;
     // control arrays (block starts, entries, walk results, row/heap bases) live in pinned host memory that the
     // kernels read and write directly: a few bytes per BGZF block, and they never queue behind the bulk copies
-    if ((rc = s.rec.reserve(((s.obytes + b->carry_cap) / 36 + n + 8) * 2)) != DH_OK ||
+    const uint64_t min_rec = b->kind == 1 ? 32 : 36;   // smallest record: bounds the number of record offsets a block can hold
+    if ((rc = s.rec.reserve(((s.obytes + b->carry_cap) / min_rec + n + 8) * 2)) != DH_OK ||
         (rc = s.h_blk_start.reserve((n + 1) * 8)) != DH_OK || (rc = s.h_entry.reserve(n * 8)) != DH_OK ||
         (rc = s.h_todo.reserve(n)) != DH_OK || (rc = s.h_walk.reserve(n * sizeof(BlockWalk))) != DH_OK ||
         (rc = s.h_row_base.reserve(n * 4)) != DH_OK || (rc = s.h_heap_base.reserve(n * 8)) != DH_OK)
@@ -412,7 +323,8 @@ int walk_segment(dh_bam *b, int k) {
     bool first_round = true;
     for (;;) {
         if (first_round) DH_CUDA(cudaEventRecord(s.ev_walk0, sk));
-        DH_CUDA(launch_bam_walk(wp, b->tabs, sk));
+        if (b->kind == 1) DH_CUDA(bcf_launch_walk(b, wp, sk));
+        else DH_CUDA(launch_bam_walk(wp, b->tabs, sk));
         b->ctx->launches++;
         DH_CUDA(cudaEventRecord(first_round ? s.ev_walk1 : s.ev_walk2, sk));
         DH_CUDA(cudaEventSynchronize(first_round ? s.ev_walk1 : s.ev_walk2));
@@ -649,6 +561,7 @@ void dh_bam_close(dh_bam *b) {
         for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_c0, s.ev_done}) if (e) cudaEventDestroy(e);
     }
     b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release(); b->d_image.release(); b->d_filt.release();
+    if (b->bcf) bcf_state_free(b->bcf);
     delete b;
 }
 
@@ -959,3 +872,22 @@ int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs) {
 }
 
 }  // extern "C"
+
+// ---- pipeline steps shared with dh_bcf.cu ----------------------------------------------------------------------
+namespace dh {
+int scan_ensure_events(dh_bam *b) { return ensure_events(b); }
+int scan_begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh) { return begin_range(b, voff_beg, voff_end, fresh); }
+int scan_have_work(dh_bam *b) { return have_work(b); }
+int scan_inflate_head(dh_bam *b, uint64_t want, std::vector<uint8_t> &u) {
+    const size_t nb = b->bt.blocks.size();
+    size_t take = 0;
+    while (take < nb && b->bt.uoff[take] < want) ++take;
+    const uint64_t cend = take ? b->bt.blocks[take - 1].coffset + b->bt.blocks[take - 1].csize : 0;
+    u.resize((size_t)b->bt.uoff[take] + 8);
+    uint64_t n = 0;
+    int rc = take ? dh_bgzf_inflate_host(b->ctx, b->data, cend, u.data(), u.size(), &n, nullptr) : DH_OK;
+    if (rc != DH_OK) return rc;
+    u.resize((size_t)n);
+    return DH_OK;
+}
+}  // namespace dh

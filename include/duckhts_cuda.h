@@ -218,6 +218,70 @@ int dh_bam_scan_contigs(dh_bam *b, const dh_index *idx, int32_t tid_lo, int32_t 
  * index's chunk offsets). */
 int dh_bam_split_contigs(const dh_bam *b, const dh_index *idx, int n_parts, int32_t *tid_bounds);
 
+/* ---- B1-B10: read_bcf scan --------------------------------------------------------------------------------------
+ * Replaces, for one BCF image in host memory, what bcf_read_bind / bcf_read_local_init / bcf_read_function get from
+ * htslib (src/bcf_reader.c:451-2053): bcf_hdr_read (htslib/vcf.c:1710+) -> dictionaries and column schema; per record
+ * bcf_read -> bcf_read1_core + bcf_record_check (vcf.c:1874-1911, 2040-2212), bcf_unpack (vcf.c:4178-4302),
+ * bcf_get_info_* / bcf_get_format_* / bcf_get_genotypes (vcf.c:6056-6248) and the column writers incl. the GT string
+ * builder (bcf_reader.c:1381-1462, 1542-1733, 1738-1998) — done by batches on the GPU.  Records come back in file
+ * order; an invalid record ends the scan silently after the records before it (bcf_reader.c:1311-1338) with htslib's
+ * code (-2) in the batch / scan status.
+ *
+ * Layout of a batch: site-level columns (CHROM POS ID REF ALT QUAL FILTER, INFO_*) hold ONE cell per record; FORMAT
+ * columns hold one cell per (record, sample), sample fastest — exactly the row order of tidy_format := true, where the
+ * site-level cell of row r is cell r / n_samples (the reference repeats it per sample row, bcf_reader.c:1283-1290);
+ * in wide mode column FORMAT_<f>_<sample s> is cell r * n_samples + s of FORMAT column f.  Cell types: VARCHAR =
+ * duckdb_string_t (long strings point into `heap`), BOOLEAN uint8, INTEGER int32, FLOAT float (bit copies), POS int64,
+ * QUAL double, LIST = duckdb_list_entry {offset, length} with the children at `heap` + offset * child size (4 for
+ * INTEGER / FLOAT children, 16 for VARCHAR children).  validity = DuckDB mask (bit = 1 valid) or NULL when the column
+ * cannot be NULL; the cells of NULL rows are unspecified. */
+typedef struct dh_bcf dh_bcf;
+typedef struct {
+    const char *name;      /* header ID */
+    int32_t type;          /* 0 Flag -> BOOLEAN, 1 Integer -> INTEGER, 2 Float -> FLOAT, 3 String -> VARCHAR (create_bcf_field_type) */
+    int32_t is_list;       /* LIST column (Number, corrected by the VCF-spec table of src/include/vcf_types.h, is not fixed) */
+} dh_bcf_field;
+dh_bcf *dh_bcf_open(dh_ctx *ctx, const uint8_t *data, uint64_t size);
+void dh_bcf_close(dh_bcf *b);
+int32_t dh_bcf_n_samples(const dh_bcf *b);
+const char *dh_bcf_sample_name(const dh_bcf *b, int32_t i);
+int32_t dh_bcf_n_contigs(const dh_bcf *b);
+const char *dh_bcf_contig_name(const dh_bcf *b, int32_t rid);
+int32_t dh_bcf_n_info(const dh_bcf *b);              /* INFO_<id> columns, in header-dictionary order */
+int32_t dh_bcf_n_format(const dh_bcf *b);            /* FORMAT_<id> columns, in header-dictionary order */
+int dh_bcf_info_field(const dh_bcf *b, int32_t i, dh_bcf_field *out);
+int dh_bcf_format_field(const dh_bcf *b, int32_t i, dh_bcf_field *out);
+int dh_bcf_has_vep(const dh_bcf *b);                 /* header declares CSQ / BCSQ / ANN (VEP_* columns: not served) */
+const char *dh_bcf_header_text(const dh_bcf *b, uint32_t *len);
+/* Projection pushdown: bit c of core_mask = core column c (0 CHROM .. 6 FILTER); info_want[i] / format_want[i] != 0 =
+ * INFO / FORMAT column i.  NULL arrays = all. */
+#define DH_BCF_CORE_COLS 7
+int dh_bcf_set_projection(dh_bcf *b, uint32_t core_mask, const uint8_t *info_want, const uint8_t *format_want);
+/* Pipeline knobs (0 = keep): compressed bytes per inflate segment, records per batch, bytes of the per-batch region
+ * for strings longer than 12 bytes and string-list cells. */
+int dh_bcf_configure(dh_bcf *b, uint64_t seg_comp_bytes, uint32_t batch_records, uint64_t string_bytes);
+int dh_bcf_set_mode(dh_bcf *b, uint32_t flags);      /* DH_BAM_DEVICE_INPUT / DH_BAM_DEVICE_OUTPUT, as for dh_bam */
+int dh_bcf_scan_begin(dh_bcf *b);
+typedef struct {
+    uint64_t n_records;
+    uint64_t n_samples;
+    uint64_t rec0;         /* scan-relative index of the first record of this batch */
+    int32_t status;        /* 0, or -2 when an invalid record ended the scan right after this batch */
+    int32_t pad;
+    const void *core[DH_BCF_CORE_COLS];
+    const uint64_t *core_validity[DH_BCF_CORE_COLS];
+    const void *const *info;                 /* dh_bcf_n_info entries; NULL where not projected */
+    const uint64_t *const *info_validity;
+    const void *const *format;               /* dh_bcf_n_format entries */
+    const uint64_t *const *format_validity;
+    const uint8_t *heap;
+    uint64_t heap_bytes;
+    uint64_t bytes;        /* bytes copied device -> host for this batch */
+} dh_bcf_batch;
+/* Returns 1 and fills *out (buffers stay valid until the next call on this handle), 0 at end of scan, < 0 on error. */
+int dh_bcf_next_batch(dh_bcf *b, dh_bcf_batch *out);
+int dh_bcf_scan_stats_get(const dh_bcf *b, dh_bam_scan_stats *out);
+
 /* CUDA-event timer on the context's stream (the stream every kernel of this library is launched on). */
 int dh_ctx_sync(dh_ctx *ctx);
 int dh_timer_start(dh_ctx *ctx);

@@ -46,3 +46,13 @@ CHROMOSOME_II:1136-1136
 {CHROMOSOME_X}:1-10,CHROMOSOME_III:1k-1.1k
 REGIONS
 $D dumpcontigs range.bam $TAGS > range.contigs.tsv
+# ---- B1-B10: read_bcf.  The reference EXTENSION itself (oracle/_ref/libduckhts_ref.so, unchanged sources) under the
+# fake DuckDB host prints every cell; the files are the reference's own fixture and a small seeded --edge file.
+H=../../harness/_bin/fake_duckdb; RX=../../oracle/_ref/libduckhts_ref.so
+cp $REF/test/data/vcf_file.bcf vcf_file.bcf; chmod u+w vcf_file.bcf
+../../harness/_bin/gen_bcf edge_small.bcf 60 5 0x51 --edge --contigs 3
+../../harness/_bin/gen_bcf plain_small.bcf 40 9 0x52 --contigs 2
+for f in vcf_file edge_small plain_small; do
+  $H $RX read_bcf $f.bcf tidy_format=true --dump > $f.bcf.tidy.txt 2>/dev/null
+  $H $RX read_bcf $f.bcf --dump > $f.bcf.wide.txt 2>/dev/null
+done

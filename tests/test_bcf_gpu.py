@@ -1,0 +1,76 @@
+"""B1-B10 — read_bcf on the GPU against the REFERENCE: golden dumps the reference extension produced under the fake
+DuckDB host (tests/golden/*.bcf.{tidy,wide}.txt, make_golden.sh), and — where the prebuilt reference extension is
+present — live runs of it on seeded synthetic files (harness/_bin/gen_bcf), cell for cell."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from tests import util
+
+ROOT = util.ROOT
+HOST = os.path.join(ROOT, "harness", "_bin", "fake_duckdb")
+REF_EXT = os.path.join(ROOT, "oracle", "_ref", "libduckhts_ref.so")
+GEN = os.path.join(ROOT, "harness", "_bin", "gen_bcf")
+GOLD = util.GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import duckhts_b200 as dh
+    with dh.Context(0) as c:
+        yield c
+
+
+def first_diff(a, b):
+    for i, (x, y) in enumerate(zip(a, b)):
+        if x != y:
+            return "line %d:\n  got %s\n  exp %s" % (i, x[:600], y[:600])
+    return "length %d vs %d" % (len(a), len(b))
+
+
+@pytest.mark.parametrize("name", ["vcf_file", "edge_small", "plain_small"])
+@pytest.mark.parametrize("tidy", [True, False])
+def test_read_bcf_matches_reference_golden(ctx, name, tidy):
+    from duckhts_b200 import bcf
+    img = np.fromfile(os.path.join(GOLD, name + ".bcf"), dtype=np.uint8)
+    exp = open(os.path.join(GOLD, "%s.bcf.%s.txt" % (name, "tidy" if tidy else "wide"))).read().split("\n")[:-1]
+    got, status, _ = bcf.rows_text(ctx, img, tidy=tidy)
+    assert status == 0
+    assert got == exp, first_diff(got, exp)
+
+
+def ref_dump(path, *args):
+    p = subprocess.run([HOST, REF_EXT, "read_bcf", path, *args, "--dump"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, timeout=900)
+    assert p.returncode == 0
+    return p.stdout.decode("utf-8", "replace").split("\n")[:-1]
+
+
+def synth_bcf(n_sites, n_samples, seed, edge, contigs=22):
+    os.makedirs(util.CACHE, exist_ok=True)
+    path = os.path.join(util.CACHE, "bcf_%d_%d_%d_%d_%d.bcf" % (n_sites, n_samples, seed, int(edge), contigs))
+    if not os.path.exists(path):
+        subprocess.check_call([GEN, path + ".tmp", str(n_sites), str(n_samples), hex(seed), "--contigs", str(contigs)] + (["--edge"] if edge else []))
+        os.replace(path + ".tmp", path)
+    return path
+
+
+@pytest.mark.skipif(not (os.path.exists(HOST) and os.path.exists(REF_EXT) and os.path.exists(GEN)), reason="prebuilt reference extension / generator absent")
+@pytest.mark.parametrize("n_sites,n_samples,seed,edge,kw", [
+    (1500, 40, 0x61, True, {}),                                   # every record shape, records straddling BGZF blocks
+    (400, 300, 0x62, True, dict(batch_records=37, seg_comp=1 << 17)),   # many small segments and batches, carries between segments
+    (300, 2504, 0x63, False, dict(batch_records=64)),             # the config-5 shape: 2,504 samples
+    (200, 0, 0x64, True, {}),                                     # sites only
+])
+def test_read_bcf_matches_live_reference_on_synthetic(ctx, n_sites, n_samples, seed, edge, kw):
+    from duckhts_b200 import bcf
+    path = synth_bcf(n_sites, n_samples, seed, edge)
+    img = np.fromfile(path, dtype=np.uint8)
+    exp = ref_dump(path, "tidy_format=true")
+    got, status, _ = bcf.rows_text(ctx, img, tidy=True, **kw)
+    assert status == 0
+    assert len(got) == len(exp) == 1 + n_sites * max(n_samples, 1)
+    assert got == exp, first_diff(got, exp)
