@@ -360,6 +360,278 @@ static void register_read_bam(duckdb_connection con) {
 }
 
 /* ================================================================================================================
+ * read_bcf — same parameters, schema and NULL rules as the reference (src/bcf_reader.c:451-830, 2055-2081); rows come
+ * from dh_bcf batches: site-level cells once per record, FORMAT cells once per (record, sample).  tidy_format := true
+ * repeats the site-level cell for each sample row here, on the host, 16 bytes at a time.
+ * ================================================================================================================ */
+typedef struct {
+    uint8_t *image;
+    uint64_t size;
+    dh_bcf *bcf;
+    int tidy, n_samples, n_info, n_fmt, default_gt;
+    int info_start, sample_id_col, fmt_start, n_cols;
+    dh_bcf_field *info, *fmt;
+} bcf_bind_t;
+
+typedef struct {
+    idx_t n_proj;
+    idx_t *col_ids;
+    dh_bcf_batch batch;
+    uint64_t cursor;        /* next row of the batch: records (wide) or records x samples (tidy) */
+    int have_batch, done;
+} bcf_local_t;
+
+static void bcf_bind_free(void *p) {
+    bcf_bind_t *b = (bcf_bind_t *)p;
+    if (!b) return;
+    if (b->bcf) dh_bcf_close(b->bcf);
+    if (b->image) dh_host_free(b->image);
+    free(b->info);
+    free(b->fmt);
+    api.duckdb_free(b);
+}
+static void bcf_local_free(void *p) {
+    bcf_local_t *l = (bcf_local_t *)p;
+    if (!l) return;
+    free(l->col_ids);
+    api.duckdb_free(l);
+}
+
+static duckdb_logical_type bcf_field_type(int type, int is_list) {   /* create_bcf_field_type, bcf_reader.c:391-417 */
+    duckdb_logical_type e = api.duckdb_create_logical_type(type == 0 ? DUCKDB_TYPE_BOOLEAN : type == 1 ? DUCKDB_TYPE_INTEGER : type == 2 ? DUCKDB_TYPE_FLOAT : DUCKDB_TYPE_VARCHAR);
+    if (!is_list) return e;
+    duckdb_logical_type l = api.duckdb_create_list_type(e);
+    api.duckdb_destroy_logical_type(&e);
+    return l;
+}
+
+static void read_bcf_bind(duckdb_bind_info info) {
+    duckdb_value pv = api.duckdb_bind_get_parameter(info, 0);
+    char *path = api.duckdb_get_varchar(pv);
+    api.duckdb_destroy_value(&pv);
+    if (!path || !path[0]) {
+        api.duckdb_bind_set_error(info, "read_bcf requires a file path");
+        if (path) api.duckdb_free(path);
+        return;
+    }
+    char *region = named_varchar(info, "region"), *index_path = named_varchar(info, "index_path");
+    const int tidy = named_bool(info, "tidy_format", 0);
+    char err[768];
+    err[0] = 0;
+    bcf_bind_t *b = NULL;
+    dh_ctx *ctx = shared_ctx();
+    if (!ctx) snprintf(err, sizeof err, "read_bcf: no usable CUDA device (%s)", dh_last_error());
+    else if (region && region[0]) snprintf(err, sizeof err, "read_bcf: region queries are not available in this build");
+    else {
+        b = (bcf_bind_t *)api.duckdb_malloc(sizeof *b);
+        memset(b, 0, sizeof *b);
+        b->image = slurp_pinned(path, &b->size);
+        if (!b->image) snprintf(err, sizeof err, "Failed to open BCF/VCF file: %s", path);
+        else if (!(b->bcf = dh_bcf_open(ctx, b->image, b->size))) snprintf(err, sizeof err, "Failed to read BCF/VCF header");
+        else if (dh_bcf_has_vep(b->bcf)) snprintf(err, sizeof err, "read_bcf: VEP_* columns (CSQ/BCSQ/ANN) are not available in this build");
+    }
+    if (err[0]) {
+        api.duckdb_bind_set_error(info, err);
+        bcf_bind_free(b);
+    } else {
+        b->tidy = tidy;
+        b->n_samples = dh_bcf_n_samples(b->bcf);
+        b->n_info = dh_bcf_n_info(b->bcf);
+        b->n_fmt = dh_bcf_n_format(b->bcf);
+        b->info = (dh_bcf_field *)calloc((size_t)b->n_info + 1, sizeof *b->info);
+        b->fmt = (dh_bcf_field *)calloc((size_t)b->n_fmt + 1, sizeof *b->fmt);
+        for (int i = 0; i < b->n_info; ++i) dh_bcf_info_field(b->bcf, i, &b->info[i]);
+        for (int i = 0; i < b->n_fmt; ++i) dh_bcf_format_field(b->bcf, i, &b->fmt[i]);
+        if (b->n_samples > 0 && b->n_fmt == 0) {      /* "Add GT as default" (bcf_reader.c:669-678): a VARCHAR column that is always NULL */
+            b->default_gt = 1;
+            b->n_fmt = 1;
+            b->fmt[0].name = "GT"; b->fmt[0].type = 3; b->fmt[0].is_list = 0;
+        }
+        duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT),
+                            t_double = api.duckdb_create_logical_type(DUCKDB_TYPE_DOUBLE);
+        duckdb_logical_type t_vlist = api.duckdb_create_list_type(t_varchar);
+        api.duckdb_bind_add_result_column(info, "CHROM", t_varchar);
+        api.duckdb_bind_add_result_column(info, "POS", t_bigint);
+        api.duckdb_bind_add_result_column(info, "ID", t_varchar);
+        api.duckdb_bind_add_result_column(info, "REF", t_varchar);
+        api.duckdb_bind_add_result_column(info, "ALT", t_vlist);
+        api.duckdb_bind_add_result_column(info, "QUAL", t_double);
+        api.duckdb_bind_add_result_column(info, "FILTER", t_vlist);
+        int col = 7;
+        char name[600];
+        b->info_start = col;
+        for (int i = 0; i < b->n_info; ++i, ++col) {
+            snprintf(name, sizeof name, "INFO_%s", b->info[i].name);
+            duckdb_logical_type t = bcf_field_type(b->info[i].type, b->info[i].is_list);
+            api.duckdb_bind_add_result_column(info, name, t);
+            api.duckdb_destroy_logical_type(&t);
+        }
+        b->sample_id_col = -1;
+        b->fmt_start = col;
+        if (b->n_samples > 0) {
+            if (tidy) {
+                b->sample_id_col = col++;
+                api.duckdb_bind_add_result_column(info, "SAMPLE_ID", t_varchar);
+                b->fmt_start = col;
+                for (int f = 0; f < b->n_fmt; ++f, ++col) {
+                    snprintf(name, sizeof name, "FORMAT_%s", b->fmt[f].name);
+                    duckdb_logical_type t = bcf_field_type(b->fmt[f].type, b->fmt[f].is_list);
+                    api.duckdb_bind_add_result_column(info, name, t);
+                    api.duckdb_destroy_logical_type(&t);
+                }
+            } else {
+                for (int sidx = 0; sidx < b->n_samples; ++sidx)
+                    for (int f = 0; f < b->n_fmt; ++f, ++col) {
+                        snprintf(name, sizeof name, "FORMAT_%s_%s", b->fmt[f].name, dh_bcf_sample_name(b->bcf, sidx));
+                        duckdb_logical_type t = bcf_field_type(b->fmt[f].type, b->fmt[f].is_list);
+                        api.duckdb_bind_add_result_column(info, name, t);
+                        api.duckdb_destroy_logical_type(&t);
+                    }
+            }
+        }
+        b->n_cols = col;
+        api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_bigint); api.duckdb_destroy_logical_type(&t_double);
+        api.duckdb_destroy_logical_type(&t_vlist);
+        api.duckdb_bind_set_bind_data(info, b, bcf_bind_free);
+    }
+    api.duckdb_free(path);
+    if (region) api.duckdb_free(region);
+    if (index_path) api.duckdb_free(index_path);
+}
+
+static void read_bcf_init(duckdb_init_info info) {
+    api.duckdb_init_set_max_threads(info, 1);
+    api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free);
+}
+
+static void read_bcf_local_init(duckdb_init_info info) {
+    bcf_bind_t *b = (bcf_bind_t *)api.duckdb_init_get_bind_data(info);
+    bcf_local_t *l = (bcf_local_t *)api.duckdb_malloc(sizeof *l);
+    memset(l, 0, sizeof *l);
+    l->n_proj = api.duckdb_init_get_column_count(info);
+    l->col_ids = (idx_t *)calloc(l->n_proj ? l->n_proj : 1, sizeof(idx_t));
+    uint32_t core_mask = 0;
+    uint8_t *iw = (uint8_t *)calloc((size_t)b->n_info + 1, 1), *fw = (uint8_t *)calloc((size_t)b->n_fmt + 1, 1);
+    for (idx_t i = 0; i < l->n_proj; ++i) {
+        const idx_t c = api.duckdb_init_get_column_index(info, i);
+        l->col_ids[i] = c;
+        if (c < 7) core_mask |= 1u << c;
+        else if ((int)c < b->info_start + b->n_info) iw[c - (idx_t)b->info_start] = 1;
+        else if ((int)c >= b->fmt_start && (int)c != b->sample_id_col) fw[(c - (idx_t)b->fmt_start) % (idx_t)b->n_fmt] = 1;
+    }
+    const int rc = dh_bcf_set_projection(b->bcf, core_mask, iw, b->default_gt ? NULL : fw);
+    free(iw);
+    free(fw);
+    if (rc != DH_OK || dh_bcf_scan_begin(b->bcf) != DH_OK) {
+        api.duckdb_init_set_error(info, dh_last_error());
+        bcf_local_free(l);
+        return;
+    }
+    api.duckdb_init_set_init_data(info, l, bcf_local_free);
+}
+
+static int cell_valid(const uint64_t *v, uint64_t i) { return !v || ((v[i >> 6] >> (i & 63)) & 1); }
+static void set_null(duckdb_vector vec, idx_t row) {
+    api.duckdb_vector_ensure_validity_writable(vec);
+    api.duckdb_validity_set_row_invalid(api.duckdb_vector_get_validity(vec), row);
+}
+static void put_varchar(duckdb_vector vec, idx_t row, const duckdb_string_t *cell) {
+    if (cell->value.inlined.length <= 12) ((duckdb_string_t *)api.duckdb_vector_get_data(vec))[row] = *cell;
+    else api.duckdb_vector_assign_string_element_len(vec, row, cell->value.pointer.ptr, cell->value.inlined.length);
+}
+/* one cell of a batch column -> row `row` of `vec`.  type: 0 BOOLEAN 1 INTEGER 2 FLOAT 3 VARCHAR 4 BIGINT 5 DOUBLE */
+static void emit_cell(duckdb_vector vec, idx_t row, int type, int is_list, const void *col, const uint64_t *validity, uint64_t i, const uint8_t *heap) {
+    const int ok = col && cell_valid(validity, i);
+    if (is_list) {
+        duckdb_list_entry *out = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
+        duckdb_list_entry e;
+        e.offset = api.duckdb_list_vector_get_size(vec);
+        e.length = 0;
+        if (ok) {
+            const duckdb_list_entry src = ((const duckdb_list_entry *)col)[i];
+            e.length = src.length;
+            if (e.length) {
+                api.duckdb_list_vector_reserve(vec, e.offset + e.length);
+                api.duckdb_list_vector_set_size(vec, e.offset + e.length);
+                duckdb_vector child = api.duckdb_list_vector_get_child(vec);
+                if (type == 3) {
+                    const duckdb_string_t *cells = (const duckdb_string_t *)(heap + 16 * src.offset);
+                    for (uint64_t k = 0; k < src.length; ++k) put_varchar(child, e.offset + k, &cells[k]);
+                } else memcpy((uint8_t *)api.duckdb_vector_get_data(child) + 4 * e.offset, heap + 4 * src.offset, 4 * src.length);
+            }
+        } else set_null(vec, row);
+        out[row] = e;
+        return;
+    }
+    if (!ok) { set_null(vec, row); return; }
+    void *dst = api.duckdb_vector_get_data(vec);
+    switch (type) {
+    case 0: ((uint8_t *)dst)[row] = ((const uint8_t *)col)[i]; break;
+    case 1: case 2: ((uint32_t *)dst)[row] = ((const uint32_t *)col)[i]; break;
+    case 3: put_varchar(vec, row, &((const duckdb_string_t *)col)[i]); break;
+    default: ((uint64_t *)dst)[row] = ((const uint64_t *)col)[i]; break;
+    }
+}
+
+static void read_bcf_scan(duckdb_function_info info, duckdb_data_chunk output) {
+    bcf_bind_t *b = (bcf_bind_t *)api.duckdb_function_get_bind_data(info);
+    bcf_local_t *l = (bcf_local_t *)api.duckdb_function_get_local_init_data(info);
+    if (!l || l->done) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    const uint64_t ns = (uint64_t)b->n_samples, per_rec = (b->tidy && ns) ? ns : 1;
+    while (!l->have_batch || l->cursor >= l->batch.n_records * per_rec) {
+        const int rc = dh_bcf_next_batch(b->bcf, &l->batch);
+        if (rc == 1) { l->have_batch = 1; l->cursor = 0; continue; }
+        l->done = 1;
+        if (rc < 0 && rc != DH_EDATA && rc != DH_EFORMAT) api.duckdb_function_set_error(info, dh_last_error());   /* a bad record / block ends the scan silently (bcf_reader.c:1311-1338) */
+        api.duckdb_data_chunk_set_size(output, 0);
+        return;
+    }
+    const idx_t vs = api.duckdb_vector_size();
+    const uint64_t r0 = l->cursor, left = l->batch.n_records * per_rec - r0;
+    const idx_t n = left < vs ? (idx_t)left : vs;
+    static const int CORE_TYPE[7] = {3, 4, 3, 3, 3, 5, 3};
+    const dh_bcf_batch *bt = &l->batch;
+    for (idx_t i = 0; i < l->n_proj; ++i) {
+        duckdb_vector vec = api.duckdb_data_chunk_get_vector(output, i);
+        const idx_t c = l->col_ids[i];
+        for (idx_t r = 0; r < n; ++r) {
+            const uint64_t row = r0 + r, rec = row / per_rec, smp = row % per_rec;
+            if (c < 7) emit_cell(vec, r, CORE_TYPE[c], c == 4 || c == 6, bt->core[c], bt->core_validity[c], rec, bt->heap);
+            else if ((int)c < b->info_start + b->n_info) {
+                const int k = (int)c - b->info_start;
+                emit_cell(vec, r, b->info[k].type, b->info[k].is_list, bt->info[k], bt->info_validity[k], rec, bt->heap);
+            } else if ((int)c == b->sample_id_col) api.duckdb_vector_assign_string_element(vec, r, dh_bcf_sample_name(b->bcf, (int32_t)smp));
+            else {
+                const uint64_t k = c - (idx_t)b->fmt_start, f = k % (uint64_t)b->n_fmt, s_idx = b->tidy ? smp : k / (uint64_t)b->n_fmt;
+                if (b->default_gt) set_null(vec, r);
+                else emit_cell(vec, r, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], rec * ns + s_idx, bt->heap);
+            }
+        }
+    }
+    l->cursor += n;
+    api.duckdb_data_chunk_set_size(output, n);
+}
+
+static void register_read_bcf(duckdb_connection con) {
+    duckdb_table_function tf = api.duckdb_create_table_function();
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN);
+    api.duckdb_table_function_set_name(tf, "read_bcf");
+    api.duckdb_table_function_add_parameter(tf, t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "region", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "index_path", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "tidy_format", t_bool);
+    api.duckdb_table_function_set_bind(tf, read_bcf_bind);
+    api.duckdb_table_function_set_init(tf, read_bcf_init);
+    api.duckdb_table_function_set_local_init(tf, read_bcf_local_init);
+    api.duckdb_table_function_set_function(tf, read_bcf_scan);
+    api.duckdb_table_function_supports_projection_pushdown(tf, true);
+    api.duckdb_register_table_function(con, tf);
+    api.duckdb_destroy_table_function(&tf);
+    api.duckdb_destroy_logical_type(&t_varchar);
+    api.duckdb_destroy_logical_type(&t_bool);
+}
+
+/* ================================================================================================================
  * bgunzip — like the reference, the work happens in bind and the scan returns one row (src/bgzip.c:86-200, 300-330)
  * ================================================================================================================ */
 typedef struct { char *out_path; int64_t bytes_in, bytes_out; int emitted; } gz_bind_t;
@@ -461,6 +733,7 @@ __attribute__((visibility("default"))) bool duckhts_init_c_api(duckdb_extension_
     duckdb_connection con;
     if (api.duckdb_connect(*db, &con) == DuckDBError) { access->set_error(info, "Failed to open connection to database"); return false; }
     register_read_bam(con);
+    register_read_bcf(con);
     register_bgunzip(con);
     api.duckdb_disconnect(&con);
     return true;

@@ -219,7 +219,9 @@ static void api_assign_string_len(duckdb_vector vv, idx_t index, const char *str
 static void api_assign_string(duckdb_vector v, idx_t index, const char *str) { api_assign_string_len(v, index, str, strlen(str)); }
 static duckdb_vector api_list_get_child(duckdb_vector v) { return (duckdb_vector)((Vec *)v)->child; }
 static idx_t api_list_get_size(duckdb_vector v) { return ((Vec *)v)->list_size; }
-static duckdb_state api_list_set_size(duckdb_vector v, idx_t n) { ((Vec *)v)->list_size = n; return DuckDBSuccess; }
+/* set_size also grows the child: the reference's FILTER writer calls it without duckdb_list_vector_reserve
+ * (src/bcf_reader.c:1446,1451), which only works in DuckDB while the child fits its initial capacity */
+static duckdb_state api_list_set_size(duckdb_vector v, idx_t n) { vec_reserve(((Vec *)v)->child, n); ((Vec *)v)->list_size = n; return DuckDBSuccess; }
 static duckdb_state api_list_reserve(duckdb_vector v, idx_t n) { vec_reserve(((Vec *)v)->child, n); return DuckDBSuccess; }
 static duckdb_vector api_struct_get_child(duckdb_vector v, idx_t i) { return (duckdb_vector)((Vec *)v)->members[i]; }
 static uint32_t api_string_t_length(duckdb_string_t s) { return s.value.inlined.length; }

@@ -74,3 +74,68 @@ def test_read_bcf_matches_live_reference_on_synthetic(ctx, n_sites, n_samples, s
     assert status == 0
     assert len(got) == len(exp) == 1 + n_sites * max(n_samples, 1)
     assert got == exp, first_diff(got, exp)
+
+
+# ---- against the oracle (oracle/bcf_oracle.py), incl. inputs the reference stops on ---------------------------------
+def oracle_lines(img, tidy):
+    from oracle import bcf_oracle
+    from oracle import dh_oracle_py as orc
+    rc, infl, _ = orc.bgzf_inflate(img)
+    assert rc == 0
+    return bcf_oracle.scan(infl.tobytes(), tidy), infl
+
+
+@pytest.mark.parametrize("name", ["vcf_file", "edge_small", "plain_small"])
+def test_read_bcf_matches_oracle(ctx, name):
+    from duckhts_b200 import bcf
+    img = np.fromfile(os.path.join(GOLD, name + ".bcf"), dtype=np.uint8)
+    (exp, est), _ = oracle_lines(img, True)
+    got, status, _ = bcf.rows_text(ctx, img, tidy=True, batch_records=7)
+    assert status == est == 0 and got == exp, first_diff(got, exp)
+
+
+@pytest.mark.parametrize("what", ["rid", "fmt_type", "truncated", "l_shared", "info_key"])
+def test_invalid_records_end_the_scan_like_the_reference(ctx, what):
+    """bcf_read returns -2 (bcf_read1_core / bcf_record_check); the rows before the bad record are returned."""
+    import struct
+    from oracle import bcf_oracle
+    from duckhts_b200 import bcf
+    img = np.fromfile(os.path.join(GOLD, "edge_small.bcf"), dtype=np.uint8)
+    (_, _), infl = oracle_lines(img, True)
+    u = bytearray(infl.tobytes())
+    l_text = struct.unpack_from("<I", u, 5)[0]
+    p = 9 + l_text
+    for _ in range(23):
+        l_shared, l_indiv = struct.unpack_from("<II", u, p)
+        p += 8 + l_shared + l_indiv
+    l_shared, l_indiv = struct.unpack_from("<II", u, p)
+    if what == "rid":
+        struct.pack_into("<i", u, p + 8, 77)
+    elif what == "fmt_type":
+        u[p + 8 + l_shared + 2] = (u[p + 8 + l_shared + 2] & 0xf0) | 6      # an undefined value type in the first FORMAT field
+    elif what == "truncated":
+        u = u[:p + 8 + l_shared + 5]
+    elif what == "l_shared":
+        struct.pack_into("<I", u, p, 20)
+    elif what == "info_key":
+        u[p + 32] = 0x13                                                       # the ID descriptor becomes an int vector
+    bad = np.frombuffer(util.make_bgzf(bytes(u), block=30000), dtype=np.uint8)
+    exp, est = bcf_oracle.scan(bytes(u), True)
+    got, status, last = bcf.rows_text(ctx, bad, tidy=True, batch_records=5)
+    assert est == -2 and status == -2 and last == -2
+    assert len(exp) == 1 + 23 * 5
+    assert got == exp, first_diff(got, exp)
+
+
+def test_projection_returns_only_requested_columns(ctx):
+    import duckhts_b200 as dh
+    img = np.fromfile(os.path.join(GOLD, "edge_small.bcf"), dtype=np.uint8)
+    with dh.BcfFile(ctx, img) as bf:
+        bf.set_projection(core_mask=0b0000010, info_want=[False] * len(bf.info), format_want=[f[0] == "GT" for f in bf.format])
+        bf.scan_begin()
+        b = bf.next_batch()
+        assert b.n_records == 60 and b.core[1] and not b.core[0] and not b.core[4]
+        gt = [i for i, f in enumerate(bf.format) if f[0] == "GT"][0]
+        assert all((b.format[i] is not None) == (i == gt) for i in range(len(bf.format)))
+        assert all(b.info[i] is None for i in range(len(bf.info)))
+        assert bf.next_batch() is None

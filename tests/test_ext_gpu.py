@@ -133,3 +133,44 @@ def test_indexed_synthetic_file_regions_and_contig_mode():
     (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "index_path=" + alt, "region=chr9", "--hash")
     assert rc_r == 0 and rc_o == 0, err_o
     assert out_o == out_r
+
+
+# ---- B1-B10: read_bcf, the two extensions under the same host ------------------------------------------------------
+GEN_BCF = os.path.join(ROOT, "harness", "_bin", "gen_bcf")
+
+
+@pytest.mark.parametrize("name", ["vcf_file", "edge_small", "plain_small"])
+@pytest.mark.parametrize("args", [(), ("tidy_format=true",)])
+def test_read_bcf_matches_reference_extension(name, args):
+    path = os.path.join(GOLD, name + ".bcf")
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bcf", path, *args)
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r
+
+
+@pytest.mark.parametrize("cols", ["0,1", "16,17", "4,6,2", "18,20,22", "7,9,11,13", "19"])
+def test_read_bcf_projection_pushdown(cols):
+    path = os.path.join(GOLD, "edge_small.bcf")
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bcf", path, "tidy_format=true", "--cols", cols)
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r
+
+
+@pytest.mark.skipif(not os.path.exists(GEN_BCF), reason="generator absent")
+def test_read_bcf_synthetic_2504_samples_hashes():
+    os.makedirs(util.CACHE, exist_ok=True)
+    path = os.path.join(util.CACHE, "ext_bcf_500x2504.bcf")
+    if not os.path.exists(path):
+        subprocess.check_call([GEN_BCF, path + ".tmp", "500", "2504", "0x71"])
+        os.replace(path + ".tmp", path)
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bcf", path, "tidy_format=true", "--hash")
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_r.splitlines()[0].startswith("rows\t1252000")
+    assert out_o == out_r
+
+
+def test_read_bcf_bind_errors(tmp_path):
+    for args in (("read_bcf", str(tmp_path / "missing.bcf")), ("read_bcf", "")):
+        (rc_r, out_r, _), (rc_o, out_o, _) = both(*args)
+        assert rc_r == 1 and rc_o == 1
+        assert out_o == out_r

@@ -1,0 +1,66 @@
+"""Pins oracle/bcf_oracle.py (CPU restatement of rows B1-B10) against the REFERENCE: dumps the reference extension
+produced under the fake DuckDB host (tests/golden/*.bcf.*.txt) and live runs on seeded synthetic files."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import bcf_oracle
+from oracle import dh_oracle_py as orc
+from tests import util
+
+HOST = os.path.join(util.ROOT, "harness", "_bin", "fake_duckdb")
+REF_EXT = os.path.join(util.ROOT, "oracle", "_ref", "libduckhts_ref.so")
+GEN = os.path.join(util.ROOT, "harness", "_bin", "gen_bcf")
+
+
+def inflated(path):
+    rc, infl, bad = orc.bgzf_inflate(np.fromfile(path, dtype=np.uint8))
+    assert rc == 0, (rc, bad)
+    return infl.tobytes()
+
+
+@pytest.mark.parametrize("name", ["vcf_file", "edge_small", "plain_small"])
+@pytest.mark.parametrize("tidy", [True, False])
+def test_bcf_oracle_matches_reference_golden(name, tidy):
+    exp = open(os.path.join(util.GOLDEN, "%s.bcf.%s.txt" % (name, "tidy" if tidy else "wide"))).read().split("\n")[:-1]
+    got, status = bcf_oracle.scan(inflated(os.path.join(util.GOLDEN, name + ".bcf")), tidy)
+    assert status == 0
+    assert len(got) == len(exp)
+    for i, (a, b) in enumerate(zip(got, exp)):
+        assert a == b, "line %d" % i
+
+
+def test_known_answers_of_duckhts_sqllogictest_bcf():
+    """test/sql/duckhts.test:15-40: vcf_file.bcf has 15 records; the first is 1:3000150 C>T."""
+    got, _ = bcf_oracle.scan(inflated(os.path.join(util.GOLDEN, "vcf_file.bcf")), False)
+    assert len(got) == 16
+    assert got[1].split("\t")[:5] == ["1", "3000150", "\\N", "C", "[T]"]
+
+
+@pytest.mark.skipif(not (os.path.exists(HOST) and os.path.exists(REF_EXT) and os.path.exists(GEN)), reason="prebuilt reference extension / generator absent")
+@pytest.mark.parametrize("n_sites,n_samples,seed", [(400, 12, 0x81), (150, 0, 0x82), (60, 120, 0x83)])
+def test_bcf_oracle_matches_live_reference_on_synthetic(n_sites, n_samples, seed, tmp_path):
+    path = str(tmp_path / "s.bcf")
+    subprocess.check_call([GEN, path, str(n_sites), str(n_samples), hex(seed), "--edge", "--contigs", "5"])
+    u = inflated(path)
+    for tidy in (True, False):
+        args = ["tidy_format=true"] if tidy else []
+        ref = subprocess.run([HOST, REF_EXT, "read_bcf", path, *args, "--dump"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL).stdout.decode("utf-8", "replace").split("\n")[:-1]
+        got, status = bcf_oracle.scan(u, tidy)
+        assert status == 0 and got == ref, tidy
+
+
+def test_bcf_oracle_stops_at_a_bad_record():
+    u = bytearray(inflated(os.path.join(util.GOLDEN, "plain_small.bcf")))
+    full, _ = bcf_oracle.scan(bytes(u), False)
+    import struct
+    l_text = struct.unpack_from("<I", u, 5)[0]
+    p = 9 + l_text
+    for _ in range(7):                                              # corrupt the 8th record's contig id
+        l_shared, l_indiv = struct.unpack_from("<II", u, p)
+        p += 8 + l_shared + l_indiv
+    struct.pack_into("<i", u, p + 8, 9999)
+    got, status = bcf_oracle.scan(bytes(u), False)
+    assert status == -2 and got == full[:8]
