@@ -200,6 +200,114 @@ def cpu_baseline_read_bam(unit_path, threads, max_records):
                       f"hts_set_threads({threads})"}
 
 
+def gen_bcf(n_sites, n_samples, seed):
+    os.makedirs(CACHE, exist_ok=True)
+    path = os.path.join(CACHE, f"bench_bcf_{n_sites}_{n_samples}_{seed}.bcf")
+    if not os.path.exists(path):
+        gen = os.path.join(HARNESS, "gen_bcf")
+        t0 = time.time()
+        subprocess.check_call([gen, path + ".tmp", str(n_sites), str(n_samples), hex(seed)])
+        os.replace(path + ".tmp", path)
+        log(f"[bench] generated {path}: {os.path.getsize(path) / 1e6:.1f} MB in {time.time() - t0:.1f}s")
+    return path
+
+
+def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
+    """BASELINE configs[4] shape (tidy FORMAT/GT + INFO decode, 2,504 samples), every column: sites/s and tidy rows/s."""
+    ns = 2504
+    if rank == 0:
+        gen_bcf(args.bcf_sites, ns, 0x5eed)
+    barrier()
+    path = gen_bcf(args.bcf_sites, ns, 0x5eed)
+    from duckhts_b200.bgzf import PinnedBuffer
+
+    raw = np.fromfile(path, dtype=np.uint8)
+    pin = PinnedBuffer(raw.size)
+    pin.array[:] = raw
+    bf = dh.BcfFile(ctx, pin)
+    out = {"workload": f"read_bcf tidy_format scan, all columns (7 core + {len(bf.info)} INFO + SAMPLE_ID + {len(bf.format)} FORMAT), "
+                       f"{args.bcf_sites} biallelic sites x {ns} samples (BASELINE configs[4] shape), BGZF level 6 via the reference htslib",
+           "compressed_mb": raw.size / 1e6}
+
+    def once():
+        bf.scan_begin()
+        n = bf.drain()
+        return n, bf.stats()
+
+    bf.set_mode(device_input=True, device_output=True)
+    for _ in range(args.warmup):
+        n, st = once()
+    assert st.status == 0 and n == args.bcf_sites, (st.status, n)
+    barrier()
+    ctx.timer_start()
+    k = [0.0, 0.0, 0.0]
+    for _ in range(args.steps):
+        n, st = once()
+        k = [k[0] + st.inflate_ms, k[1] + st.walk_ms, k[2] + st.decode_ms]
+    ms = rmax(ctx.timer_stop()) / args.steps
+    sites = rsum(float(n))
+    out.update({"value": sites / (ms / 1e3), "unit": "sites/s", "rows_per_s": sites * ns / (ms / 1e3), "ms_per_step": ms,
+                "inflated_mb": st.inflated_bytes / 1e6,
+                "kernel_ms_per_step": {"bgzf_inflate": k[0] / args.steps, "bcf_walk": k[1] / args.steps, "bcf_decode": k[2] / args.steps}})
+    bf.set_mode(device_input=False, device_output=False)
+    walls = []
+    for it in range(1 + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        n, st = once()
+        if it:
+            walls.append(rmax((time.perf_counter() - t0) * 1e3))
+    w = float(np.mean(walls))
+    out["e2e"] = {"value": sites / (w / 1e3), "unit": "sites/s", "rows_per_s": sites * ns / (w / 1e3), "ms_per_step": w,
+                  "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes),
+                  "d2h_gbs": st.d2h_bytes / 1e9 / (w / 1e3)}
+    bf.close()
+    host, ref = os.path.join(HARNESS, "fake_duckdb"), os.path.join(ROOT, "oracle", "_ref", "libduckhts_ref.so")
+    if rank == 0 and os.path.exists(host) and os.path.exists(ref):
+        sample = gen_bcf(min(args.bcf_sites, 3000), ns, 0x5eed)
+        r = json.loads(subprocess.check_output([host, ref, "read_bcf", sample, "tidy_format=true", "--time"], stderr=subprocess.DEVNULL, text=True).strip().splitlines()[-1])
+        out["cpu_baseline"] = {"value": r["rows"] / ns / r["seconds"], "unit": "sites/s", "rows_per_s": r["rows"] / r["seconds"], "cores": 1, "kind": "reference",
+                               "sample": f"{r['rows'] // ns} sites x {ns} samples; the unchanged reference extension (read_bcf, tidy_format) under harness/fake_duckdb, "
+                                         "1 scan thread (no index => the reference scans sequentially)"}
+    return out
+
+
+def bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rsum):
+    """BASELINE configs[3]: BAI-driven scan, contig groups balanced by compressed bytes, one group per GPU (no collective)."""
+    exe = os.path.join(HARNESS, "ref_dump")
+    if rank == 0 and not os.path.exists(unit_path + ".bai") and os.path.exists(exe):
+        subprocess.check_call([exe, "index", unit_path, "0"])
+    barrier()
+    if not os.path.exists(unit_path + ".bai"):
+        return None
+    from duckhts_b200.bgzf import PinnedBuffer
+
+    raw = np.fromfile(unit_path, dtype=np.uint8)
+    pin = PinnedBuffer(raw.size)
+    pin.array[:] = raw
+    bai = np.fromfile(unit_path + ".bai", dtype=np.uint8)
+    bf = dh.BamFile(ctx, pin)
+    bf.set_projection(None, TAGS)
+    ix = dh.Index(ctx, bai)
+    bounds = bf.split_contigs(ix, world)
+    walls, rows = [], 0
+    for it in range(1 + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        bf.scan_contigs(ix, bounds[rank], bounds[rank + 1])
+        rows = bf.drain()
+        if it:
+            walls.append(rmax((time.perf_counter() - t0) * 1e3))
+    st = bf.stats()
+    total = rsum(float(rows))
+    w = float(np.mean(walls))
+    bf.close()
+    ix.close()
+    return {"workload": "read_bam over contig groups from the BAI index (chr1-chr22), host buffers in and out; the file is split over the GPUs "
+                        "(strong scaling on one 4M-record file)", "value": total / 1e6 / (w / 1e3), "unit": "Mrecords/s", "ms_per_step": w,
+            "records": int(total), "contig_bounds": bounds, "status": int(st.status)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -209,6 +317,7 @@ def main():
     ap.add_argument("--records", type=float, default=100e6, help="records per GPU (BASELINE configs[2]: 100M)")
     ap.add_argument("--unit-records", type=int, default=4000000)
     ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x9E3779B97F4A7C15)
+    ap.add_argument("--bcf-sites", type=int, default=20000, help="sites of the 2,504-sample BCF sub-benchmark (0 = skip)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -363,6 +472,9 @@ def main():
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))["dram_bytes_per_inflated_byte"] * ib_out * args.steps / groups
 
+    bcf_res = bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum) if args.bcf_sites > 0 and os.path.exists(os.path.join(HARNESS, "gen_bcf")) else None
+    shard_res = bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rsum)
+
     if rank == 0:
         cpu = cpu_baseline_read_bam(unit_path, ncpu, 2000000) if world == 1 else None
         rec_c = comp_bytes / rows
@@ -388,6 +500,7 @@ def main():
                         "pcie_return_roofline_frac": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / d2h_gbs,
                         "pcie_bidir_h2d_gbs": bi_h2d, "pcie_bidir_d2h_gbs": bi_d2h,
                         "pcie_return_roofline_frac_bidir": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / bi_d2h},
+                "read_bcf": bcf_res, "contig_sharded": shard_res,
                 "cpu_baseline": cpu, "clocks": clk.summary(), "gpu_launches": int(launches), "host_cores": ncpu}
         print(json.dumps(line), flush=True)
     barrier()
