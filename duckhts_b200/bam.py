@@ -121,11 +121,12 @@ class BamFile:
         reqs = (TagReq * max(len(self.tags), 1))()
         for k, (tg, ty) in enumerate(self.tags):
             reqs[k].tag = tg
-            reqs[k].type = ty.encode()
+            reqs[k].type = ty[:1].encode()          # "Bi" / "Bf": LIST column with BIGINT / DOUBLE children
+            reqs[k].pad = ty[1:2].encode() if len(ty) > 1 else b"\0"
         if col_mask is None:
             col_mask = (1 << (DH_BAM_CORE_COLS + len(self.tags))) - 1
         self.col_mask = col_mask
-        check(lib().dh_bam_set_projection(self.h, col_mask, reqs, len(self.tags)), "dh_bam_set_projection")
+        check(lib().dh_bam_set_projection(self.h, col_mask & 0xFFFFFFFFFFFFFFFF, reqs, len(self.tags)), "dh_bam_set_projection")
 
     def configure(self, seg_comp=0, batch_rows=0, carry=0):
         check(lib().dh_bam_configure(self.h, seg_comp, batch_rows, carry), "dh_bam_configure")
@@ -194,7 +195,7 @@ def batch_to_columns(bf, b):
     tags = []
     for k, (tg, ty) in enumerate(bf.tags):
         c = DH_BAM_CORE_COLS + k
-        if not (bf.col_mask >> c) & 1:
+        if c < 64 and not (bf.col_mask >> c) & 1:
             tags.append(None)
             continue
         valid = validity_to_bool(b.validity[c], n)
@@ -203,6 +204,18 @@ def batch_to_columns(bf, b):
             d["i"] = np.frombuffer(C.string_at(b.data[c], n * 8), dtype=np.int64).copy() if n else np.zeros(0, np.int64)
         elif ty == "f":
             d["f"] = np.frombuffer(C.string_at(b.data[c], n * 8), dtype=np.float64).copy() if n else np.zeros(0, np.float64)
+        elif ty[0] == "B":
+            # duckdb_list_entry cells; children = 8-byte words at heap + 8 * offset (raw bits: int64, or double bits)
+            ent = np.frombuffer(C.string_at(b.data[c], n * 16), dtype=np.uint64).reshape(n, 2) if n else np.zeros((0, 2), np.uint64)
+            heap = np.frombuffer(C.string_at(b.heap, int(b.heap_bytes)), dtype=np.uint8) if b.heap_bytes else np.zeros(0, np.uint8)
+            lists = []
+            for r in range(n):
+                if valid is not None and not valid[r]:
+                    lists.append(None)
+                    continue
+                o, ln = int(ent[r, 0]) * 8, int(ent[r, 1])
+                lists.append(heap[o:o + 8 * ln].view(np.int64).copy())
+            d["b"] = lists
         else:
             d["s"] = cells_to_list(b.data[c], n, valid)
         tags.append(d)
@@ -245,7 +258,7 @@ def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, 
                 res[nm] = [x for p in parts for x in p[nm]]
         res["tags"] = []
         for k, (tg, ty) in enumerate(bf.tags):
-            if not (bf.col_mask >> (DH_BAM_CORE_COLS + k)) & 1:
+            if DH_BAM_CORE_COLS + k < 64 and not (bf.col_mask >> (DH_BAM_CORE_COLS + k)) & 1:
                 res["tags"].append(None)
                 continue
             d = {"valid": np.concatenate([p["tags"][k]["valid"] for p in parts]) if parts else np.zeros(0, bool)}
@@ -254,7 +267,9 @@ def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, 
                     d[key] = np.concatenate([p["tags"][k][key] for p in parts])
                 elif not parts and ty == key:
                     d[key] = np.zeros(0, np.int64 if key == "i" else np.float64)
-            if ty not in ("i", "f"):
+            if ty[0] == "B":
+                d["b"] = [x for p in parts for x in p["tags"][k]["b"]]
+            elif ty not in ("i", "f"):
                 d["s"] = [x for p in parts for x in p["tags"][k]["s"]]
             res["tags"].append(d)
         return res

@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
     w.stop = 0;
     bool want_aux_strings = ((t.col_mask >> COL_RG) & 1ull) != 0;
     for (uint32_t k = 0; k < t.n_tags; ++k)
-        want_aux_strings |= t.tags[k].type == 'Z' && ((t.col_mask >> (BAM_CORE_COLS + k)) & 1ull);
+        want_aux_strings |= (t.tags[k].type == 'Z' || t.tags[k].type == 'B') && t.tags[k].want;
     while (off < lim) {
         Rec r;
         int rc = parse_record(u, off, p.seg_end, p.is_final != 0, t.n_ref, r);
@@ -291,9 +291,17 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
                         bool wanted = (t0 == 'R' && t1 == 'G' && ((t.col_mask >> COL_RG) & 1ull));
                         for (uint32_t k = 0; k < t.n_tags && !wanted; ++k)
                             wanted = t.tags[k].t0 == t0 && t.tags[k].t1 == t1 && t.tags[k].type == 'Z' &&
-                                     ((t.col_mask >> (BAM_CORE_COLS + k)) & 1ull);
+                                     t.tags[k].want;
                         if (wanted) need += align4(len);
                     }
+                }
+                if (nx != NONE && ty == 'B') {   // children of a projected B-array LIST column: 8 bytes each (+4 to reach 8-byte alignment)
+                    const uint32_t t0 = ld8(u, s - 2), t1 = ld8(u, s - 1);
+                    for (uint32_t k = 0; k < t.n_tags; ++k)
+                        if (t.tags[k].t0 == t0 && t.tags[k].t1 == t1 && t.tags[k].type == 'B' && t.tags[k].want) {
+                            need += 4ull + 8ull * ld32u(u, s + 2);
+                            break;
+                        }
                 }
                 if (nx == NONE || r.end - nx <= 2) break;
                 s = nx + 2;
@@ -427,7 +435,7 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
     const uint64_t mask = t.col_mask;
     const bool cQ = (mask >> COL_QNAME) & 1, cC = (mask >> COL_CIGAR) & 1, cS = (mask >> COL_SEQ) & 1, cU = (mask >> COL_QUAL) & 1,
                cRG = (mask >> COL_RG) & 1, cSM = (mask >> COL_SAMPLE) & 1;
-    const bool any_tag_cols = (mask >> BAM_CORE_COLS) != 0;
+    const bool any_tag_cols = t.any_tag_cols != 0;
     uint32_t row0 = p.row_base[bi];
     uint64_t hp = p.heap_base[bi];
 
@@ -485,8 +493,13 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
         }
         if (act && any_tag_cols)
             for (uint32_t k = 0; k < t.n_tags; ++k) {
-                if (t.tags[k].type != 'Z' || !((mask >> (BAM_CORE_COLS + k)) & 1ull)) continue;
-                const int32_t zl = aux_zlen(u, r, aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8)));
+                if ((t.tags[k].type != 'Z' && t.tags[k].type != 'B') || !t.tags[k].want) continue;
+                const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
+                if (t.tags[k].type == 'B') {
+                    if (a != NONE && ld8(u, a) == 'B') need += 4u + 8u * ld32u(u, a + 2);
+                    continue;
+                }
+                const int32_t zl = aux_zlen(u, r, a);
                 if (zl > 12) need += align4((uint32_t)zl);
             }
         if (act && cRG && z_rg > 12) need += align4((uint32_t)z_rg);
@@ -608,12 +621,42 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
         if (any_tag_cols)
             for (uint32_t k = 0; k < t.n_tags; ++k) {
                 const int c = BAM_CORE_COLS + (int)k;
-                if (!((mask >> c) & 1ull)) continue;
+                if (!t.tags[k].want) continue;
                 const uint32_t ty_req = t.tags[k].type;
                 bool valid = false;
                 if (act) {
                     const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
-                    if (ty_req == 'Z') {
+                    if (ty_req == 'B') {
+                        // bam_assign_list_int / _double (bam_reader.c:106-138): the writer follows the value's RUNTIME subtype
+                        // (f, d -> bam_auxB2f, else bam_auxB2i), 8 bytes per element whatever the column's child type
+                        uint64_t off8 = 0, len = 0;
+                        if (a != NONE && ld8(u, a) == 'B') {
+                            valid = true;
+                            const uint32_t sub = ld8(u, a + 1);
+                            len = ld32u(u, a + 2);
+                            const uint64_t h8 = (hz + 7ull) & ~7ull;
+                            off8 = (h8 - p.heap_host) >> 3;
+                            unsigned long long *dst = reinterpret_cast<unsigned long long *>(p.heap + (h8 - p.heap_host));
+                            for (uint32_t e = 0; e < len; ++e) {
+                                long long iv = 0;
+                                bool is_int = true;
+                                switch (sub) {
+                                case 'c': iv = (int8_t)ld8(u, a + 6 + e); break;
+                                case 'C': iv = ld8(u, a + 6 + e); break;
+                                case 's': iv = (int16_t)(ld8(u, a + 6 + 2ll * e) | (ld8(u, a + 7 + 2ll * e) << 8)); break;
+                                case 'S': iv = ld8(u, a + 6 + 2ll * e) | (ld8(u, a + 7 + 2ll * e) << 8); break;
+                                case 'i': iv = (int32_t)ld32u(u, a + 6 + 4ll * e); break;
+                                case 'I': iv = ld32u(u, a + 6 + 4ll * e); break;
+                                default: is_int = false; break;
+                                }
+                                if (sub == 'f') dst[e] = (unsigned long long)__double_as_longlong((double)__uint_as_float(ld32u(u, a + 6 + 4ll * e)));
+                                else if (sub == 'd') dst[e] = 0ull;                   // bam_auxB2f: not 'f' -> integer getter -> EINVAL, 0
+                                else dst[e] = is_int ? (unsigned long long)iv : 0ull;
+                            }
+                            hz += 4ull + 8ull * len;
+                        }
+                        reinterpret_cast<ulonglong2 *>(p.col[c])[row] = make_ulonglong2(off8, len);
+                    } else if (ty_req == 'Z') {
                         const int32_t zl = aux_zlen(u, r, a);        // NULL for any non-Z/H type (bam_aux2Z)
                         if (zl >= 0) {
                             valid = true;

@@ -16,8 +16,8 @@ struct alignas(16) StrCell {
 
 struct TagReq {
     uint8_t t0, t1;
-    uint8_t type;  // 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (Z or H), 'A' VARCHAR(1)
-    uint8_t pad;
+    uint8_t type;  // 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (Z or H), 'A' VARCHAR(1), 'B' LIST (duckdb_list_entry + 8-byte children in the heap)
+    uint8_t want;  // column projected
 };
 
 // @RG dictionary entry: ID bytes live in a side heap; sample = prebuilt cell (SM value) or absent
@@ -41,8 +41,8 @@ struct ScanTables {
     int32_t n_ref;
     uint32_t n_rg;
     uint32_t n_tags;
-    uint32_t pad;
-    uint64_t col_mask;         // bit c set = column c projected (core columns 0..12, tag k at 13+k)
+    uint32_t any_tag_cols;     // any tag column projected
+    uint64_t col_mask;         // bit c set = core column c projected (tag columns: TagReq.want)
 };
 
 // per BGZF block result of the boundary walk (device -> host)

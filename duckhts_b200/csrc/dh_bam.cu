@@ -159,6 +159,9 @@ void build_dictionaries(dh_bam *b) {
     }
 }
 
+// bit c of col_mask = column c projected; tag columns past bit 63 (more than 51 tag requests) are always materialised
+static inline bool col_on(const dh_bam *b, int c) { return c >= 64 || ((b->col_mask >> c) & 1ull); }
+
 int upload_tables(dh_bam *b) {
     int rc;
     if ((rc = b->d_ref_cells.reserve(b->ref_cells.size() * sizeof(StrCell))) != DH_OK) return rc;
@@ -167,6 +170,8 @@ int upload_tables(dh_bam *b) {
     if (!b->rg.empty()) DH_CUDA(cudaMemcpy(b->d_rg.p, b->rg.data(), b->rg.size() * sizeof(RgEntry), cudaMemcpyHostToDevice));
     if ((rc = b->d_rg_ids.reserve(std::max<size_t>(1, b->rg_ids.size()))) != DH_OK) return rc;
     if (!b->rg_ids.empty()) DH_CUDA(cudaMemcpy(b->d_rg_ids.p, b->rg_ids.data(), b->rg_ids.size(), cudaMemcpyHostToDevice));
+    uint32_t any_tag = 0;
+    for (size_t k = 0; k < b->tags.size(); ++k) any_tag |= (b->tags[k].want = col_on(b, BAM_CORE_COLS + (int)k));
     if ((rc = b->d_tags.reserve(std::max<size_t>(1, b->tags.size()) * sizeof(TagReq))) != DH_OK) return rc;
     if (!b->tags.empty()) DH_CUDA(cudaMemcpy(b->d_tags.p, b->tags.data(), b->tags.size() * sizeof(TagReq), cudaMemcpyHostToDevice));
     ScanTables &t = b->tabs;
@@ -177,7 +182,7 @@ int upload_tables(dh_bam *b) {
     t.n_ref = (int32_t)b->ref_names.size();
     t.n_rg = (uint32_t)b->rg.size();
     t.n_tags = (uint32_t)b->tags.size();
-    t.pad = 0;
+    t.any_tag_cols = any_tag;
     t.col_mask = b->col_mask;
     return DH_OK;
 }
@@ -440,7 +445,7 @@ int issue_batch(dh_bam *b) {
     const int ncols = BAM_CORE_COLS + (int)b->tags.size();
     for (int c = 0; c < ncols; ++c) {
         coff[c] = voff[c] = UINT64_MAX;
-        if (!((b->col_mask >> c) & 1ull)) continue;
+        if (!col_on(b, c)) continue;
         coff[c] = off;
         off = (off + (uint64_t)col_width(b, c) * bb.rows + A256) & ~A256;
         if (col_nullable(c)) {
@@ -593,9 +598,9 @@ int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, 
         r.t0 = (uint8_t)tags[i].tag[0];
         r.t1 = (uint8_t)tags[i].tag[1];
         char ty = tags[i].type == 'H' ? 'Z' : tags[i].type;
-        if (ty != 'i' && ty != 'f' && ty != 'Z' && ty != 'A') { set_error("unsupported tag column type '%c'", tags[i].type); return DH_EINVAL; }
+        if (ty != 'i' && ty != 'f' && ty != 'Z' && ty != 'A' && ty != 'B') { set_error("unsupported tag column type '%c'", tags[i].type); return DH_EINVAL; }
         r.type = (uint8_t)ty;
-        r.pad = 0;
+        r.want = 1;
         b->tags.push_back(r);
     }
     const int ncols = BAM_CORE_COLS + n_tags;

@@ -242,10 +242,10 @@ static void read_bam_local_init(duckdb_init_info info) {
         l->col_ids[i] = c;
         if (c < N_CORE) { l->abi_col[i] = (int)c; mask |= 1ull << c; continue; }
         const char *e = STD_TAGS + 4 * (c - N_CORE);
-        if (c - N_CORE >= N_STD_TAGS || e[2] == 'B' || n_tags >= DH_BAM_MAX_TAGS) { l->abi_col[i] = -1; continue; }   /* LIST tags: NULL for now */
-        tags[n_tags].tag[0] = e[0]; tags[n_tags].tag[1] = e[1]; tags[n_tags].type = e[2]; tags[n_tags].pad = 0;
+        if (c - N_CORE >= N_STD_TAGS || n_tags >= DH_BAM_MAX_TAGS) { l->abi_col[i] = -1; continue; }
+        tags[n_tags].tag[0] = e[0]; tags[n_tags].tag[1] = e[1]; tags[n_tags].type = e[2]; tags[n_tags].pad = e[2] == 'B' ? e[3] : 0;
         l->abi_col[i] = N_CORE + n_tags;
-        mask |= 1ull << (N_CORE + n_tags);
+        if (N_CORE + n_tags < 64) mask |= 1ull << (N_CORE + n_tags);   /* tag columns past bit 63 are always projected */
         ++n_tags;
     }
     /* which rows (src/bam_reader.c:601-671): region(s) through the index; else, with an index and more than one contig,
@@ -315,7 +315,24 @@ static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
         const uint8_t *src = (const uint8_t *)l->batch.data[ac] + r0 * w;
         void *dst = api.duckdb_vector_get_data(vec);
         const uint64_t *valid = l->batch.validity[ac];
-        if (w != 16) memcpy(dst, src, n * w);
+        if (c >= N_CORE && STD_TAGS[4 * (c - N_CORE) + 2] == 'B') {
+            /* LIST cells (bam_assign_list_int/_double, src/bam_reader.c:106-138): children are appended to the list child */
+            const duckdb_list_entry *cells = (const duckdb_list_entry *)src;
+            duckdb_list_entry *out = (duckdb_list_entry *)dst;
+            idx_t total = api.duckdb_list_vector_get_size(vec), need = total;
+            for (idx_t r = 0; r < n; ++r)
+                if (!valid || ((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) need += cells[r].length;
+            api.duckdb_list_vector_reserve(vec, need);
+            api.duckdb_list_vector_set_size(vec, need);
+            uint64_t *child = (uint64_t *)api.duckdb_vector_get_data(api.duckdb_list_vector_get_child(vec));
+            for (idx_t r = 0; r < n; ++r) {
+                if (valid && !((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) continue;
+                memcpy(child + total, (const uint64_t *)l->batch.heap + cells[r].offset, 8 * cells[r].length);
+                out[r].offset = total;
+                out[r].length = cells[r].length;
+                total += cells[r].length;
+            }
+        } else if (w != 16) memcpy(dst, src, n * w);
         else {
             const duckdb_string_t *cells = (const duckdb_string_t *)src;
             duckdb_string_t *out = (duckdb_string_t *)dst;

@@ -6,7 +6,7 @@
  * defines the record mix.
  *
  *   gen_synth bam  OUT N SEED [--paired] [--contigs C] [--part P/K] [--no-header] [--no-eof] [--index]
- *                       [--unplaced M] [--threads T]
+ *                       [--unplaced M] [--threads T] [--btags]
  *       coordinate-sorted BAM, C contigs chr1..chrC of 50 Mb, N records in total (split evenly over
  *       contigs; every contig gets >= 1 read).  --part P/K writes only the contigs of part P
  *       of K (contig c belongs to part c*K/C), so K processes can write in parallel; the caller
@@ -71,6 +71,72 @@ static sam_hdr_t *make_header(int n_contigs) {
 }
 
 /* fill one record.  unmapped: FUNMAP set, placed at mate's coordinates, no CIGAR, no NM/MD/AS */
+static int g_btags = 0;   /* --btags: B-array tags (CG, FZ, ML of the SAMtags table and others) + tags of every other aux type */
+
+/* B arrays of every sub-type under the three LIST columns of standard_tags (CG, FZ, ML), their declared sub-type or not
+ * (a float array under an integer LIST column), empty arrays, and non-standard tags for auxiliary_tags */
+static void add_btags(bam1_t *b, rng_t *r) {
+    uint8_t buf[4 * 64];
+    const uint32_t k = rng_below(r, 16);
+    if (k < 9) {   /* ML: base-modification likelihoods, B:C, 0..40 values */
+        const uint32_t n = rng_below(r, 8) == 0 ? 0 : 1 + rng_below(r, 40);
+        for (uint32_t i = 0; i < n; ++i) buf[i] = (uint8_t)rng_below(r, 256);
+        bam_aux_update_array(b, "ML", 'C', n, buf);
+    } else if (k == 9) {   /* ML as floats: the writer then stores doubles in the BIGINT child */
+        float f[5];
+        const uint32_t n = 1 + rng_below(r, 5);
+        for (uint32_t i = 0; i < n; ++i) f[i] = (float)rng_below(r, 1000) / 8.0f - 20.0f;
+        bam_aux_update_array(b, "ML", 'f', n, f);
+    } else if (k == 10) {   /* ML as signed bytes / shorts */
+        int16_t h[6];
+        int8_t c[6];
+        const uint32_t n = 1 + rng_below(r, 6);
+        for (uint32_t i = 0; i < n; ++i) { h[i] = (int16_t)(rng_below(r, 65536) - 32768); c[i] = (int8_t)(rng_below(r, 256) - 128); }
+        if (rng_below(r, 2)) bam_aux_update_array(b, "ML", 's', n, h); else bam_aux_update_array(b, "ML", 'c', n, c);
+    }
+    if (rng_below(r, 4) == 0) {   /* CG: BAM-only long CIGAR, B:I */
+        uint32_t cg[12];
+        const uint32_t n = 1 + rng_below(r, 12);
+        for (uint32_t i = 0; i < n; ++i) cg[i] = (uint32_t)rng_next(r);
+        bam_aux_update_array(b, "CG", 'I', n, cg);
+    }
+    if (rng_below(r, 5) == 0) {   /* FZ: flow signal intensities, B:S; sometimes B:i with negative values */
+        uint16_t fz[20];
+        int32_t fi[4];
+        const uint32_t n = 1 + rng_below(r, 20);
+        for (uint32_t i = 0; i < n; ++i) fz[i] = (uint16_t)rng_below(r, 65536);
+        for (uint32_t i = 0; i < 4; ++i) fi[i] = (int32_t)rng_next(r);
+        if (rng_below(r, 6)) bam_aux_update_array(b, "FZ", 'S', n, fz); else bam_aux_update_array(b, "FZ", 'i', 4, fi);
+    }
+    /* non-standard tags of every aux type (for the auxiliary_tags MAP): XA:A XC:c XS:s XI:I Xf:f XZ:Z XH:H XB:B:i XD:B:f */
+    const uint32_t m = rng_below(r, 64);
+    if (m & 1) { char a = (char)('!' + rng_below(r, 90)); bam_aux_append(b, "XA", 'A', 1, (uint8_t *)&a); }
+    if (m & 2) bam_aux_update_int(b, "XC", (int64_t)rng_below(r, 200) - 100);
+    if (m & 4) bam_aux_update_int(b, "XS", (int64_t)rng_below(r, 60000) - 30000);
+    if (m & 8) bam_aux_update_int(b, "XI", (int64_t)(uint32_t)rng_next(r));
+    if (m & 16) {
+        static const float FV[] = {0.0f, 1.0f, -1.5f, 3.14159274f, 1e-5f, 1e-4f, 123456.0f, 1234567.0f, 1e20f, -2.5e-10f, 0.1f, 100000.0f, 999999.5f, 0.000123456f};
+        const uint32_t pick = rng_below(r, 20);
+        bam_aux_update_float(b, "Xf", pick < 14 ? FV[pick] : (float)rng_below(r, 1000000) / 997.0f);
+    }
+    if (m & 32) {
+        char z[40];
+        const uint32_t n = rng_below(r, 30);
+        for (uint32_t i = 0; i < n; ++i) z[i] = (char)('a' + rng_below(r, 26));
+        z[n] = 0;
+        bam_aux_update_str(b, "XZ", -1, z);
+    }
+    if (rng_below(r, 8) == 0) { const char *hx = "1AE301"; bam_aux_append(b, "XH", 'H', 7, (const uint8_t *)hx); }
+    if (rng_below(r, 8) == 0) {
+        int32_t v[3] = {(int32_t)rng_next(r), -1, 7};
+        bam_aux_update_array(b, "XB", 'i', 1 + rng_below(r, 3), v);
+    }
+    if (rng_below(r, 8) == 0) {
+        float v[3] = {(float)rng_below(r, 100000) / 64.0f, 1e-7f, -3.0e9f};
+        bam_aux_update_array(b, "XD", 'f', 1 + rng_below(r, 3), v);
+    }
+}
+
 static void fill_record(bam1_t *b, rng_t *r, int tid, int64_t pos, uint16_t flag, int mtid, int64_t mpos,
                         int32_t isize, uint64_t id, int rg, int ctg_label) {
     char qname[64];
@@ -115,6 +181,7 @@ static void fill_record(bam1_t *b, rng_t *r, int tid, int64_t pos, uint16_t flag
         bam_aux_update_int(b, "AS", (int)(READ_LEN - 5 * nm - rng_below(r, 10) + (rng_below(r, 50) == 0 ? 200 : 0)));
     }
     bam_aux_update_str(b, "RG", -1, RG_ID[rg]);
+    if (g_btags) add_btags(b, r);
 }
 
 typedef int (*emit_fn)(void *ctx, bam1_t *b);
@@ -222,7 +289,7 @@ static int emit_raw(void *ctx, bam1_t *b) {
 int main(int argc, char **argv) {
     if (argc < 5) {
         fprintf(stderr, "usage: gen_synth bam|bgzf OUT N SEED [--paired] [--contigs C] [--part P/K] [--no-header] "
-                        "[--no-eof] [--index] [--unplaced M] [--threads T]\n");
+                        "[--no-eof] [--index] [--unplaced M] [--threads T] [--btags]\n");
         return 2;
     }
     const char *mode = argv[1], *out = argv[2];
@@ -238,6 +305,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--index")) do_index = 1;
         else if (!strcmp(argv[i], "--unplaced") && i + 1 < argc) unplaced = strtoull(argv[++i], NULL, 10);
         else if (!strcmp(argv[i], "--threads") && i + 1 < argc) threads = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--btags")) g_btags = 1;
         else { fprintf(stderr, "unknown option %s\n", argv[i]); return 2; }
     }
     sam_hdr_t *hdr = make_header(n_contigs);

@@ -124,8 +124,9 @@ uint64_t dh_bam_n_blocks(const dh_bam *b);
 /* Column schema = the reference's (bam_reader.c:189-204): 0 QNAME 1 FLAG 2 RNAME 3 POS 4 MAPQ 5 CIGAR 6 RNEXT
  * 7 PNEXT 8 TLEN 9 SEQ 10 QUAL 11 READ_GROUP_ID 12 SAMPLE_ID, then one column per requested typed tag
  * (standard_tags, bam_reader.c:54-70).  col_mask bit c = column c is projected (projection pushdown,
- * bam_reader.c:676-679); tag k is column 13+k.  Tag types: 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (SAM Z or H),
- * 'A' VARCHAR. */
+ * bam_reader.c:676-679); tag k is column 13+k (tag columns past bit 63, i.e. k >= 51, are always projected).  Tag types: 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (SAM Z or H),
+ * 'A' VARCHAR, 'B' LIST of 8-byte children (BIGINT or DOUBLE by the column's declared sub-type; the cell writer
+ * follows the value's RUNTIME sub-type as bam_assign_list_int/_double do, bam_reader.c:106-138, 954-962). */
 #define DH_BAM_CORE_COLS 13
 #define DH_BAM_MAX_TAGS 63
 #define DH_BAM_MAX_COLS (DH_BAM_CORE_COLS + DH_BAM_MAX_TAGS)
@@ -156,7 +157,9 @@ int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end);
 
 /* VARCHAR cells are DuckDB duckdb_string_t (16 bytes): <= 12 bytes inlined, else prefix + pointer into `heap`
  * (or, for RNAME/RNEXT/SAMPLE_ID, into a dictionary owned by the dh_bam handle).  Fixed-width columns are plain
- * arrays: FLAG uint16, POS/PNEXT/TLEN int64, MAPQ int32, 'i' tags int64, 'f' tags double.  validity[c] is a
+ * arrays: FLAG uint16, POS/PNEXT/TLEN int64, MAPQ int32, 'i' tags int64, 'f' tags double.  'B' tag cells are
+ * duckdb_list_entry {offset, length} with the children at ((const uint64_t *)heap)[offset .. offset+length)
+ * (int64 or double bit patterns; the host appends them to the DuckDB list child vector).  validity[c] is a
  * DuckDB validity mask (bit r = row r valid) or NULL when the column cannot be NULL. */
 typedef struct {
     uint64_t n_rows;

@@ -52,7 +52,8 @@ typedef struct {
 
 typedef struct {
     char tag[2];
-    char type; /* 'i' BIGINT (bam_aux2i), 'f' DOUBLE (bam_aux2f), 'Z'/'H' VARCHAR (bam_aux2Z), 'A' VARCHAR(1) */
+    char type; /* 'i' BIGINT (bam_aux2i), 'f' DOUBLE (bam_aux2f), 'Z'/'H' VARCHAR (bam_aux2Z), 'A' VARCHAR(1),
+                  'B' LIST (children as 8-byte words in the string column, 8*len bytes per row) */
 } dho_tag_req;
 
 typedef struct {

@@ -123,7 +123,7 @@ def bam_decode(inflated, tags=()):
     reqs = (TagReq * max(len(tags), 1))()
     for k, (tg, ty) in enumerate(tags):
         reqs[k].tag = tg if isinstance(tg, bytes) else tg.encode()
-        reqs[k].type = ty.encode()
+        reqs[k].type = ty[:1].encode()
     cols = BamColumns()
     rc = lib().dho_bam_decode(a.ctypes.data, a.size, reqs, len(tags), C.byref(cols))
     if rc != 0:
@@ -151,6 +151,8 @@ def bam_decode(inflated, tags=()):
             d["i"] = np.ctypeslib.as_array(tc.i, shape=(max(n, 1),))[:n].copy()
         elif ty == "f":
             d["f"] = np.ctypeslib.as_array(tc.f, shape=(max(n, 1),))[:n].copy()
+        elif ty[0] == "B":
+            d["b"] = [None if x is None else np.frombuffer(x, dtype=np.int64) for x in strcol_list(_strcol(tc.s, n))]
         else:
             d["s"] = _strcol(tc.s, n)
         out["tags"].append(d)

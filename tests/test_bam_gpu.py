@@ -46,6 +46,27 @@ def test_records_straddling_blocks_and_segments(ctx):
     both(ctx, img)
 
 
+def test_b_array_list_tags(ctx):
+    """A15: CG / FZ / ML LIST columns (bam_reader.c:106-138, 954-962): every B sub-type, float arrays under a BIGINT list,
+    empty arrays; children cross batch and segment boundaries; mixed with long-string tag slots in the same heap."""
+    img = util.synth_bam_bytes(n_records=30000, seed=79, paired=True, extra=("--btags",))
+    tags = [(b"ML", "Bi"), (b"MD", "Z"), (b"CG", "Bi"), (b"XZ", "Z"), (b"FZ", "Bi"), (b"NM", "i"), (b"XD", "Bf"), (b"XB", "Bi")]
+    got, exp = both(ctx, img, tags=tags)
+    assert sum(x is not None for x in got["tags"][0]["b"]) > 10000
+    both(ctx, img, tags=tags, seg_comp=1 << 16, batch_rows=333)
+    # projection: only list columns / a list column whose tag never occurs
+    sub = dh.bam_scan(ctx, img, tags=[(b"ML", "Bi"), (b"ZZ", "Bf")], col_mask=(1 << 13) | (1 << 14) | 1)
+    assert sub["n"] == exp["n"] and sub["qname"] == orc.strcol_list(exp["qname"]) and all(x is None for x in sub["tags"][1]["b"])
+    assert all((g is None) == (e is None) and (e is None or np.array_equal(g, e)) for g, e in zip(sub["tags"][0]["b"], exp["tags"][0]["b"]))
+    # hand-made: sub-type 'd' is no B sub-type (skip_aux accepts it, the getter returns 0), first of two equal tags wins
+    recs = [util.bam_record(qname=b"q1", aux=b"MLBd" + struct.pack("<I", 2) + struct.pack("<dd", 1.5, -2.0) + b"MLBC" + struct.pack("<I", 1) + b"\x07"),
+            util.bam_record(qname=b"q2", aux=b"XXZ" + b"y" * 30 + b"\0" + b"MLBs" + struct.pack("<Ihh", 2, -5, 300)),
+            util.bam_record(qname=b"q3", aux=b"MLBI" + struct.pack("<I", 0))]
+    img2 = np.frombuffer(util.make_bgzf(util.bam_header([(b"c1", 1000)]) + b"".join(recs)), dtype=np.uint8)
+    got, exp = both(ctx, img2, tags=[(b"ML", "Bi"), (b"XX", "Z")])
+    assert [None if x is None else x.tolist() for x in got["tags"][0]["b"]] == [[0, 0], [-5, 300], []]
+
+
 def test_unplaced_reads_are_returned_in_sequential_mode(ctx):
     img = util.synth_bam_bytes(n_records=3000, seed=14, paired=True, extra=("--unplaced", "50"))
     got, exp = both(ctx, img)

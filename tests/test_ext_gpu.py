@@ -16,8 +16,8 @@ GOLD = os.path.join(ROOT, "tests", "golden")
 
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not (os.path.exists(HOST) and os.path.exists(REF_EXT)), reason="prebuilt fake host / reference extension absent")]
 
-# SAMtags LIST columns (CG, FZ, ML) are not served yet: compared columns exclude them (their schema is checked separately)
-B_COLS = {13 + 7, 13 + 19, 13 + 29}
+# SAMtags LIST columns (CG, FZ, ML; B-array tags, A15)
+B_COLS = (13 + 7, 13 + 19, 13 + 29)
 
 
 def run(ext, func, path, *args):
@@ -42,13 +42,25 @@ def test_read_bam_matches_reference_extension_on_reference_fixtures(name):
 @pytest.mark.parametrize("name", ["aux_tags", "auxf_values", "range", "rg", "ce_unmap2"])
 def test_standard_tags_columns(name):
     path = os.path.join(GOLD, name + ".bam")
-    cols = ",".join(str(c) for c in range(13 + 56) if c not in B_COLS)
+    cols = ",".join(str(c) for c in range(13 + 56))
     (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "standard_tags=true", "--cols", cols)
     assert rc_r == 0 and rc_o == 0, err_o
     assert out_o == out_r
     # schema (header line) with every column, LIST columns included
     (_, full_r, _), (_, full_o, _) = both("read_bam", path, "standard_tags=true")
     assert full_o.splitlines()[0] == full_r.splitlines()[0]
+
+
+def test_b_array_list_columns(tmp_path):
+    # B arrays of every sub-type under CG / FZ / ML, float arrays under the BIGINT lists, empty arrays; small batches
+    # so that list children cross batch and vector boundaries
+    path = util.synth_path("bam", n_records=20000, seed=77, paired=True, extra=("--btags",))
+    allc = ",".join(str(c) for c in range(13 + 56))
+    for cols in (",".join(str(c) for c in B_COLS), "42,0,20", allc):
+        (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "standard_tags=true", "--cols", cols)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r, cols
+    assert "[" in out_r
 
 
 @pytest.mark.parametrize("cols", ["0", "1,3,4", "9,10", "12,11,2", "5,0,8,6", "3"])
@@ -61,7 +73,7 @@ def test_projection_pushdown(cols):
 
 def test_synthetic_paired_file_hashes(tmp_path):
     path = util.synth_path("bam", n_records=60000, seed=31, paired=True)
-    cols = ",".join(str(c) for c in range(13 + 56) if c not in B_COLS)
+    cols = ",".join(str(c) for c in range(13 + 56))
     (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "standard_tags=true", "--cols", cols, "--hash")
     assert rc_r == 0 and rc_o == 0, err_o
     assert out_r.splitlines()[0].startswith("rows\t")
@@ -120,7 +132,7 @@ def test_region_errors_read_like_the_reference():
 
 def test_indexed_synthetic_file_regions_and_contig_mode():
     path = util.synth_path("bam", n_records=30000, seed=31, paired=True, extra=("--unplaced", "25"), index=True)
-    cols = ",".join(str(c) for c in range(13 + 56) if c not in B_COLS)
+    cols = ",".join(str(c) for c in range(13 + 56))
     for args in ((), ("region=chr3:10,000,000-20,000,000",), ("region=chr2:1-5000000,chr2:4000000-9000000,chr7:49000000-",),
                  ("region=chr22:-1000000,chr5:25m-26m",)):
         (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "standard_tags=true", "--cols", cols, "--hash", *args)

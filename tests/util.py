@@ -104,6 +104,10 @@ def assert_bam_equal(got, exp, tags=True):
                 assert np.array_equal(gt["i"][et["valid"]], et["i"][et["valid"]]), f"tag {k} int values"
             elif "f" in et:
                 assert np.array_equal(gt["f"][et["valid"]].view(np.uint64), et["f"][et["valid"]].view(np.uint64)), f"tag {k} f"
+            elif "b" in et:
+                assert len(gt["b"]) == len(et["b"])
+                for r, (g, e) in enumerate(zip(gt["b"], et["b"])):
+                    assert (g is None) == (e is None) and (e is None or np.array_equal(g, e)), f"tag {k} list, row {r}: {g} != {e}"
             else:
                 assert gt["s"] == orc.strcol_list(et["s"]), f"tag {k} strings"
 
