@@ -32,7 +32,9 @@ class TagReq(C.Structure):
 class BamBatch(C.Structure):
     _fields_ = [("n_rows", C.c_uint64), ("row0", C.c_uint64), ("status", C.c_int32), ("n_cols", C.c_int32),
                 ("data", C.c_void_p * DH_BAM_MAX_COLS), ("validity", C.c_void_p * DH_BAM_MAX_COLS),
-                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64)]
+                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64),
+                ("aux_map", C.c_void_p), ("aux_map_validity", C.c_void_p), ("aux_keys", C.c_void_p), ("aux_values", C.c_void_p),
+                ("n_aux", C.c_uint64)]
 
 
 class BamScanStats(C.Structure):
@@ -50,7 +52,9 @@ class BcfBatch(C.Structure):
                 ("core", C.c_void_p * 7), ("core_validity", C.c_void_p * 7),
                 ("info", C.POINTER(C.c_void_p)), ("info_validity", C.POINTER(C.c_void_p)),
                 ("format", C.POINTER(C.c_void_p)), ("format_validity", C.POINTER(C.c_void_p)),
-                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64)]
+                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64),
+                ("aux_map", C.c_void_p), ("aux_map_validity", C.c_void_p), ("aux_keys", C.c_void_p), ("aux_values", C.c_void_p),
+                ("n_aux", C.c_uint64)]
 
 
 _lib = None
@@ -86,6 +90,7 @@ SIGNATURES = {
     "dh_bam_first_voffset": (C.c_uint64, [C.c_void_p]),
     "dh_bam_n_blocks": (C.c_uint64, [C.c_void_p]),
     "dh_bam_set_projection": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(TagReq), C.c_int]),
+    "dh_bam_set_aux_map": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_int]),
     "dh_bam_configure": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64]),
     "dh_bam_set_mode": (C.c_int, [C.c_void_p, C.c_uint32]),
     "dh_bam_scan_begin": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64]),

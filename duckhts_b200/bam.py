@@ -128,6 +128,12 @@ class BamFile:
         self.col_mask = col_mask
         check(lib().dh_bam_set_projection(self.h, col_mask & 0xFFFFFFFFFFFFFFFF, reqs, len(self.tags)), "dh_bam_set_projection")
 
+    def set_aux_map(self, enable=True, exclude=()):
+        """AUXILIARY_TAGS MAP column; exclude = two-byte tags left out (the typed standard_tags columns)."""
+        ex = b"".join(t if isinstance(t, bytes) else t.encode() for t in exclude)
+        self.aux_map = bool(enable)
+        check(lib().dh_bam_set_aux_map(self.h, 1 if enable else 0, ex, len(ex) // 2), "dh_bam_set_aux_map")
+
     def configure(self, seg_comp=0, batch_rows=0, carry=0):
         check(lib().dh_bam_configure(self.h, seg_comp, batch_rows, carry), "dh_bam_configure")
 
@@ -220,15 +226,25 @@ def batch_to_columns(bf, b):
             d["s"] = cells_to_list(b.data[c], n, valid)
         tags.append(d)
     out["tags"] = tags
+    if b.aux_map:
+        # MAP(VARCHAR, VARCHAR): per row None or [(key, value), ...]
+        na = int(b.n_aux)
+        keys, vals = cells_to_list(b.aux_keys, na), cells_to_list(b.aux_values, na)
+        ent = np.frombuffer(C.string_at(b.aux_map, n * 16), dtype=np.uint64).reshape(n, 2) if n else np.zeros((0, 2), np.uint64)
+        valid = validity_to_bool(b.aux_map_validity, n)
+        out["aux_map"] = [None if not valid[r] else [(keys[i], vals[i]) for i in range(int(ent[r, 0]), int(ent[r, 0] + ent[r, 1]))]
+                          for r in range(n)]
     return out
 
 
 def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, batch_rows=0, carry=0, index=None,
-             regions=None, contigs=None):
+             regions=None, contigs=None, aux_map=None):
     """Whole scan -> one dict of columns in row order (test/inspection helper; the product API is batch-wise).
     index = index file bytes; with it, regions = list of region strings, or contigs = (tid_lo, tid_hi) / True."""
     with BamFile(ctx, data) as bf:
         bf.set_projection(col_mask, tags)
+        if aux_map is not None:          # aux_map = iterable of excluded tags (may be empty)
+            bf.set_aux_map(True, aux_map)
         bf.configure(seg_comp, batch_rows, carry)
         if index is not None:
             with Index(ctx, index) as ix:
@@ -256,6 +272,8 @@ def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, 
                 res[nm] = np.concatenate([p[nm] for p in parts]) if parts else np.zeros(0, CORE_DTYPES[nm])
             else:
                 res[nm] = [x for p in parts for x in p[nm]]
+        if aux_map is not None:
+            res["aux_map"] = [x for p in parts for x in p["aux_map"]]
         res["tags"] = []
         for k, (tg, ty) in enumerate(bf.tags):
             if DH_BAM_CORE_COLS + k < 64 and not (bf.col_mask >> (DH_BAM_CORE_COLS + k)) & 1:

@@ -206,6 +206,47 @@ __device__ __forceinline__ bool plausible_header(const uint8_t *u, int64_t off, 
 __device__ __forceinline__ uint32_t slot_bytes(uint32_t bound) { return bound > 12u ? align4(bound) : 0u; }
 __device__ __forceinline__ bool qual_absent(const uint8_t *u, const Rec &r) { return r.l_qseq <= 0 || ld8(u, r.qual) == 0xffu; }
 
+// ---- AUXILIARY_TAGS (A16) ---------------------------------------------------------------------------------------------
+// Upper bound of the text bam_aux_to_string (bam_reader.c:140-183) writes for the value whose type byte is at s; exact for
+// A / Z / H.  Bounds above 12 reserve a heap slot (slot_bytes); both kernels use this rule.
+__device__ __forceinline__ uint32_t aux_text_bound(const uint8_t *u, int64_t s, int64_t nx, int64_t end) {
+    switch (ld8(u, s)) {
+    case 'A': return 1u;
+    case 'c': case 'C': case 's': case 'S': case 'i': case 'I': return 11u;   // "-2147483648"
+    case 'f': case 'd': return 13u;                                           // "-1.79769e+308"
+    case 'Z': case 'H': return (uint32_t)((nx == end && ld8(u, end - 1) != 0 ? end : nx - 1) - (s + 1));
+    case 'B': {
+        const uint32_t sub = ld8(u, s + 1), n = ld32u(u, s + 2);
+        const uint32_t per = sub == 'c' ? 5u : sub == 'C' ? 4u : sub == 's' ? 7u : sub == 'S' ? 6u : sub == 'i' ? 12u : sub == 'I' ? 11u : sub == 'f' ? 14u : 2u;
+        return 1u + per * n;
+    }
+    default: return 0u;
+    }
+}
+__device__ __forceinline__ bool aux_excluded(const ScanTables &t, uint32_t key) { return t.aux_excl && ((t.aux_excl[key >> 5] >> (key & 31u)) & 1u); }
+// pairs and heap bytes of one record's MAP cell: the bam_aux_first / bam_aux_next walk of bam_reader.c:969-980.  An entry
+// whose value does not fit the record (skip_aux fails) is still returned by bam_aux_next and counted; the walk ends after it.
+__device__ __forceinline__ void aux_map_need(const uint8_t *u, const Rec &r, const ScanTables &t, uint32_t &cnt, uint32_t &heap) {
+    cnt = heap = 0;
+    if (r.end - r.aux <= 2) return;
+    int64_t s = r.aux + 2;
+    for (;;) {
+        if (s - 2 == r.cg_lo) {   // tag consumed by bam_tag2cigar
+            if (r.end - r.cg_hi <= 2) return;
+            s = r.cg_hi + 2;
+            continue;
+        }
+        bool complete;
+        const int64_t nx = skip_aux_scalar(u, s, r.end, &complete);
+        if (!aux_excluded(t, ld8(u, s - 2) | (ld8(u, s - 1) << 8))) {
+            ++cnt;
+            if (nx != NONE) heap += slot_bytes(aux_text_bound(u, s, nx, r.end));
+        }
+        if (nx == NONE || r.end - nx <= 2) return;
+        s = nx + 2;
+    }
+}
+
 // Region filter of indexed scans (A8).  htslib reads the records of the index's chunks and keeps those with
 // `end > beg_q && end_q > beg` on the queried contig (hts_itr_next, htslib/hts.c:4301-4311; multi-region form
 // hts_itr_multi_next :4565-4597), end = bam_endpos (sam.c:519-524: pos + rlen, rlen = 1 for unmapped reads or a CIGAR
@@ -257,6 +298,7 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
     BlockWalk w;
     w.entry = off;
     w.count = 0;
+    w.map_entries = w.map_heap = 0;
     w.heap_bytes = 0;
     w.stop = 0;
     bool want_aux_strings = ((t.col_mask >> COL_RG) & 1ull) != 0;
@@ -306,6 +348,13 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
                 if (nx == NONE || r.end - nx <= 2) break;
                 s = nx + 2;
             }
+        }
+        if (t.aux_map) {
+            uint32_t mc, mh;
+            aux_map_need(u, r, t, mc, mh);
+            w.map_entries += mc;
+            w.map_heap += mh;
+            need += mh;
         }
         w.heap_bytes += need;
         rec[w.count] = (uint16_t)(off - start);   // where the decode kernel finds this record (relative to the block start)
@@ -727,9 +776,274 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
 }
 
 
+// =======================================================================================================
+// AUXILIARY_TAGS MAP column (A16)
+// =======================================================================================================
+// printf("%g") of a double, exactly as glibc rounds it (correct rounding of the exact binary value, ties to even): the six
+// significant digits come from an exact big-integer division R / S (the "fixed format" branch of Steele & White's dragon4).
+// 36 words cover the largest cases (2^1024 numerators, 10^324 * 2^53 for subnormals).  Values are rare in the aux area
+// (types f / d and B:f only), so the routine is kept out of line.
+struct Big {
+    uint32_t w[36];
+    int n;   // words in use
+};
+__device__ __forceinline__ void big_set(Big &a, uint64_t v) {
+    a.w[0] = (uint32_t)v;
+    a.w[1] = (uint32_t)(v >> 32);
+    a.n = a.w[1] ? 2 : 1;
+}
+__device__ __forceinline__ void big_mul(Big &a, uint32_t m) {
+    uint64_t c = 0;
+    for (int i = 0; i < a.n; ++i) {
+        c += (uint64_t)a.w[i] * m;
+        a.w[i] = (uint32_t)c;
+        c >>= 32;
+    }
+    if (c && a.n < 36) a.w[a.n++] = (uint32_t)c;
+}
+__device__ __forceinline__ void big_shl(Big &a, int bits) {
+    const int ws = bits >> 5, bs = bits & 31;
+    int n = a.n + ws + 1;
+    if (n > 36) n = 36;
+    for (int i = n - 1; i >= 0; --i) {
+        const int j = i - ws;
+        uint32_t v = 0;
+        if (j >= 0 && j < a.n) v = a.w[j] << bs;
+        if (bs && j - 1 >= 0 && j - 1 < a.n) v |= a.w[j - 1] >> (32 - bs);
+        a.w[i] = v;
+    }
+    a.n = n;
+    while (a.n > 1 && a.w[a.n - 1] == 0) --a.n;
+}
+__device__ __forceinline__ int big_cmp(const Big &a, const Big &b) {
+    if (a.n != b.n) return a.n > b.n ? 1 : -1;
+    for (int i = a.n - 1; i >= 0; --i)
+        if (a.w[i] != b.w[i]) return a.w[i] > b.w[i] ? 1 : -1;
+    return 0;
+}
+__device__ __forceinline__ void big_sub(Big &a, const Big &b) {   // a -= b, a >= b
+    uint32_t borrow = 0;
+    for (int i = 0; i < a.n; ++i) {
+        const uint64_t d = (uint64_t)a.w[i] - (i < b.n ? b.w[i] : 0u) - borrow;
+        a.w[i] = (uint32_t)d;
+        borrow = (uint32_t)(d >> 63);
+    }
+    while (a.n > 1 && a.w[a.n - 1] == 0) --a.n;
+}
+__device__ __forceinline__ void big_pow10(Big &a, int e) {   // a *= 10^e
+    for (; e >= 9; e -= 9) big_mul(a, 1000000000u);
+    uint32_t m = 1;
+    for (; e > 0; --e) m *= 10u;
+    if (m > 1) big_mul(a, m);
+}
+// six significant decimal digits of |x| (finite, non-zero): digits in [100000, 999999], x ~ digits * 10^(exp10 - 5)
+__device__ __noinline__ void g6_digits(double ax, uint32_t &digits, int &exp10) {
+    const uint64_t bits = (uint64_t)__double_as_longlong(ax);
+    int be = (int)((bits >> 52) & 0x7ffu);
+    uint64_t m = bits & 0xfffffffffffffull;
+    if (be) m |= 1ull << 52; else be = 1;
+    const int k = be - 1075;   // ax = m * 2^k
+    Big R, S;
+    big_set(R, m);
+    big_set(S, 1);
+    if (k >= 0) big_shl(R, k); else big_shl(S, -k);
+    int e = (int)floor(log10(ax));
+    if (e >= 0) big_pow10(S, e); else big_pow10(R, -e);
+    while (big_cmp(R, S) < 0) { big_mul(R, 10u); --e; }          // the estimate may be one off either way
+    for (;;) {
+        Big T = S;
+        big_mul(T, 10u);
+        if (big_cmp(R, T) < 0) break;
+        S = T;
+        ++e;
+    }
+    uint32_t d6 = 0;
+    for (int i = 0; i < 6; ++i) {
+        uint32_t d = 0;
+        while (big_cmp(R, S) >= 0) { big_sub(R, S); ++d; }
+        d6 = d6 * 10u + d;
+        if (i < 5) big_mul(R, 10u);
+    }
+    big_shl(R, 1);                                               // remainder against one half: ties go to the even digit
+    const int c = big_cmp(R, S);
+    if (c > 0 || (c == 0 && (d6 & 1u))) ++d6;
+    if (d6 == 1000000u) { d6 = 100000u; ++e; }
+    digits = d6;
+    exp10 = e;
+}
+
+// text sink of one MAP value: a heap slot when the bound needs one, else 16 bytes of local memory
+struct Sink {
+    uint8_t *dst;
+    uint32_t len;
+};
+__device__ __forceinline__ void put(Sink &k, uint32_t c) { k.dst[k.len++] = (uint8_t)c; }
+__device__ __forceinline__ void put_i64(Sink &k, long long v) {   // "%" PRId64
+    unsigned long long a = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+    if (v < 0) put(k, '-');
+    char tmp[20];
+    int n = 0;
+    do { tmp[n++] = (char)('0' + a % 10ull); a /= 10ull; } while (a);
+    while (n) put(k, tmp[--n]);
+}
+__device__ __noinline__ void put_g(Sink &k, double x) {   // "%g"
+    const uint64_t bits = (uint64_t)__double_as_longlong(x);
+    if (bits >> 63) put(k, '-');
+    const uint64_t mag = bits & 0x7fffffffffffffffull;
+    if (mag > 0x7ff0000000000000ull) { put(k, 'n'); put(k, 'a'); put(k, 'n'); return; }
+    if (mag == 0x7ff0000000000000ull) { put(k, 'i'); put(k, 'n'); put(k, 'f'); return; }
+    if (mag == 0) { put(k, '0'); return; }
+    uint32_t d6;
+    int X;
+    g6_digits(__longlong_as_double((long long)mag), d6, X);
+    int nd = 6;
+    while (nd > 1 && d6 % 10u == 0u) { d6 /= 10u; --nd; }   // %g drops trailing zeros
+    char ds[6];
+    for (int i = nd - 1; i >= 0; --i) { ds[i] = (char)('0' + d6 % 10u); d6 /= 10u; }
+    if (X < -4 || X >= 6) {                                  // exponent form, at least two exponent digits
+        put(k, ds[0]);
+        if (nd > 1) { put(k, '.'); for (int i = 1; i < nd; ++i) put(k, ds[i]); }
+        put(k, 'e');
+        put(k, X < 0 ? '-' : '+');
+        const uint32_t ax = (uint32_t)(X < 0 ? -X : X);
+        if (ax >= 100u) put(k, '0' + ax / 100u);
+        put(k, '0' + (ax / 10u) % 10u);
+        put(k, '0' + ax % 10u);
+    } else if (X >= 0) {
+        for (int i = 0; i <= X; ++i) put(k, i < nd ? ds[i] : '0');
+        if (nd > X + 1) { put(k, '.'); for (int i = X + 1; i < nd; ++i) put(k, ds[i]); }
+    } else {
+        put(k, '0');
+        put(k, '.');
+        for (int i = -1; i > X; --i) put(k, '0');
+        for (int i = 0; i < nd; ++i) put(k, ds[i]);
+    }
+}
+__device__ __forceinline__ long long aux_int_at(const uint8_t *u, uint32_t ty, int64_t o) {   // get_int_aux_val, sam.c:5126-5141
+    switch (ty) {
+    case 'c': return (int8_t)ld8(u, o);
+    case 'C': return ld8(u, o);
+    case 's': return (int16_t)(ld8(u, o) | (ld8(u, o + 1) << 8));
+    case 'S': return ld8(u, o) | (ld8(u, o + 1) << 8);
+    case 'i': return (int32_t)ld32u(u, o);
+    case 'I': return ld32u(u, o);
+    default: return 0;
+    }
+}
+// bam_aux_to_string (bam_reader.c:140-183) of the complete entry whose type byte is at s
+__device__ __forceinline__ void aux_value_text(Sink &k, const uint8_t *u, int64_t s, uint32_t zlen) {
+    const uint32_t ty = ld8(u, s);
+    switch (ty) {
+    case 'A': { const uint32_t c = ld8(u, s + 1); if (c) put(k, c); break; }      // the cell is assigned with strlen semantics
+    case 'c': case 'C': case 's': case 'S': case 'i': case 'I': put_i64(k, aux_int_at(u, ty, s + 1)); break;
+    case 'f': put_g(k, (double)__uint_as_float(ld32u(u, s + 1))); break;
+    case 'd': put_g(k, __longlong_as_double((long long)(ld32u(u, s + 1) | ((uint64_t)ld32u(u, s + 5) << 32)))); break;
+    case 'Z': case 'H': for (uint32_t i = 0; i < zlen; ++i) put(k, ld8(u, s + 1 + i)); break;
+    case 'B': {
+        const uint32_t sub = ld8(u, s + 1), n = ld32u(u, s + 2);
+        const uint32_t esz = (sub == 'c' || sub == 'C') ? 1u : (sub == 's' || sub == 'S') ? 2u : 4u;
+        put(k, sub);
+        for (uint32_t e = 0; e < n; ++e) {
+            put(k, ',');
+            if (sub == 'f') put_g(k, (double)__uint_as_float(ld32u(u, s + 6 + 4ll * e)));
+            else if (sub == 'd') put(k, '0');                                     // bam_auxB2f of a non-float sub-type: 0
+            else put_i64(k, aux_int_at(u, sub, s + 6 + (int64_t)esz * e));
+        }
+        break;
+    }
+    default: break;
+    }
+}
+
+// One warp per BGZF block, one lane per record (as the decode kernel): the pairs of a row sit at consecutive child indices,
+// rows in order, so the host appends keys / values to the DuckDB child vectors with two copies per vector chunk.
+__global__ void __launch_bounds__(128) bam_auxmap_kernel(const __grid_constant__ AuxMapParams p, const ScanTables t) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t bi = p.b_lo + blockIdx.x * 4u + (threadIdx.x >> 5);
+    if (bi >= p.b_hi) return;
+    const BlockWalk bw = p.walk[bi];
+    if (!bw.count) return;
+    const uint8_t *u = p.u;
+    const int64_t bstart = p.blk_start[bi];
+    const uint16_t *rec = p.rec + ((bstart - p.rec_bias) / 36 + (int64_t)bi);
+    uint32_t row0 = p.row_base[bi];
+    uint32_t child = p.map_base[bi];
+    uint64_t hp = p.heap_base[bi] + bw.heap_bytes - bw.map_heap;   // the MAP's slots are the tail of the block's heap range
+    for (uint32_t g = 0; g < bw.count; g += 32u, row0 += 32u) {
+        const bool act = lane < bw.count - g;
+        Rec r;
+        uint32_t cnt = 0, need = 0;
+        if (act) {
+            parse_record(u, bstart + rec[g + lane], INT64_MAX / 2, false, t.n_ref, r);
+            aux_map_need(u, r, t, cnt, need);
+        }
+        uint32_t ci = cnt, hi = need;   // inclusive warp scans
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const uint32_t a = __shfl_up_sync(FULL, ci, sft), b = __shfl_up_sync(FULL, hi, sft);
+            if (lane >= (uint32_t)sft) { ci += a; hi += b; }
+        }
+        uint32_t at = child + ci - cnt;
+        uint64_t hs = hp + hi - need;
+        if (act) {
+            reinterpret_cast<ulonglong2 *>(p.entries)[row0 + lane] = make_ulonglong2(at, cnt);
+            if (cnt) {
+                int64_t s = r.aux + 2;
+                for (;;) {
+                    if (s - 2 == r.cg_lo) {
+                        if (r.end - r.cg_hi <= 2) break;
+                        s = r.cg_hi + 2;
+                        continue;
+                    }
+                    bool complete;
+                    const int64_t nx = skip_aux_scalar(u, s, r.end, &complete);
+                    const uint32_t t0 = ld8(u, s - 2), t1 = ld8(u, s - 1);
+                    if (!aux_excluded(t, t0 | (t1 << 8))) {
+                        // key: tagbuf[3] assigned with strlen semantics
+                        const uint32_t kl = t0 == 0 ? 0u : t1 == 0 ? 1u : 2u;
+                        store_cell(p.keys, at, kl, kl == 2 ? (t0 | (t1 << 8)) : kl == 1 ? t0 : 0u, 0u, 0u);
+                        uint8_t local[16];
+                        Sink k;
+                        k.len = 0;
+                        k.dst = local;
+                        uint32_t bound = 0;
+                        if (nx != NONE) {
+                            bound = aux_text_bound(u, s, nx, r.end);
+                            if (bound > 12u) k.dst = p.heap + hs;
+                            const uint32_t ty = ld8(u, s);
+                            aux_value_text(k, u, s, (ty == 'Z' || ty == 'H') ? bound : 0u);
+                        }
+                        if (k.len <= 12u) {
+                            uint32_t w[3] = {0u, 0u, 0u};
+                            for (uint32_t i = 0; i < k.len; ++i) w[i >> 2] |= (uint32_t)k.dst[i] << (8u * (i & 3u));
+                            store_cell(p.values, at, k.len, w[0], w[1], w[2]);
+                        } else {
+                            const uint64_t hptr = p.heap_host + hs;
+                            store_cell(p.values, at, k.len, k.dst[0] | (k.dst[1] << 8) | (k.dst[2] << 16) | ((uint32_t)k.dst[3] << 24),
+                                       (uint32_t)hptr, (uint32_t)(hptr >> 32));
+                        }
+                        hs += slot_bytes(bound);
+                        ++at;
+                    }
+                    if (nx == NONE || r.end - nx <= 2) break;
+                    s = nx + 2;
+                }
+            }
+        }
+        set_valid_group(p.valid, row0, __ballot_sync(FULL, act && cnt > 0), lane);
+        child += __shfl_sync(FULL, ci, 31);
+        hp += __shfl_sync(FULL, hi, 31);
+    }
+}
+
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream) {
     if (p.n == 0) return cudaSuccess;
     bam_walk_kernel<<<(p.n + 127u) / 128u, 128, 0, stream>>>(p, t);
+    return cudaGetLastError();
+}
+cudaError_t launch_bam_auxmap(const AuxMapParams &p, const ScanTables &t, cudaStream_t stream) {
+    if (p.b_hi <= p.b_lo) return cudaSuccess;
+    bam_auxmap_kernel<<<(p.b_hi - p.b_lo + 3u) / 4u, 128, 0, stream>>>(p, t);
     return cudaGetLastError();
 }
 cudaError_t launch_bam_decode(const DecodeParams &p, const ScanTables &t, cudaStream_t stream) {

@@ -42,6 +42,9 @@ struct ScanTables {
     uint32_t n_rg;
     uint32_t n_tags;
     uint32_t any_tag_cols;     // any tag column projected
+    uint32_t aux_map;          // the AUXILIARY_TAGS MAP column is projected (A16)
+    uint32_t pad;
+    const uint32_t *aux_excl;  // 65,536-bit set of tags (t0 | t1 << 8) left out of the MAP (the standard_tags columns), or nullptr
     uint64_t col_mask;         // bit c set = core column c projected (tag columns: TagReq.want)
 };
 
@@ -52,6 +55,8 @@ struct BlockWalk {
     uint64_t heap_bytes;  // heap bytes the block's records need (4-byte aligned slots)
     uint32_t count;       // records that start in this block and were accepted
     int32_t stop;         // 0; 1 = record at exit_off needs bytes beyond the segment; <0 = bam_read1 error code there
+    uint32_t map_entries; // AUXILIARY_TAGS: key/value pairs of the block's records
+    uint32_t map_heap;    // AUXILIARY_TAGS: heap bytes of their long values (the tail of the block's heap_bytes)
 };
 
 // one interval of a region query: [beg, end) 0-based on contig tid (hts_reglist_t intervals after reg_compact)
@@ -96,6 +101,25 @@ struct DecodeParams {
     uint64_t heap_host;           // host address the heap will be copied to
 };
 
+// AUXILIARY_TAGS MAP(VARCHAR, VARCHAR) column (bam_reader.c:967-1031): one list entry per row, key / value cells per pair
+struct AuxMapParams {
+    const uint8_t *u;
+    const BlockWalk *walk;
+    const int64_t *blk_start;
+    const uint16_t *rec;
+    int64_t rec_bias;
+    const uint32_t *row_base;
+    const uint64_t *heap_base;
+    const uint32_t *map_base;     // per block: pairs of the batch before this block
+    uint32_t b_lo, b_hi;
+    uint8_t *entries;             // duckdb_list_entry per row
+    unsigned long long *valid;    // row validity (NULL row = no pair)
+    uint8_t *keys, *values;       // duckdb_string_t cells, one per pair
+    uint8_t *heap;
+    uint64_t heap_host;
+};
+
+cudaError_t launch_bam_auxmap(const AuxMapParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_decode(const DecodeParams &p, const ScanTables &t, cudaStream_t stream);
 

@@ -255,6 +255,7 @@ __global__ void __launch_bounds__(128) bcf_walk_kernel(const WalkParams p, const
     BlockWalk w;
     w.entry = off;
     w.count = 0;
+    w.map_entries = w.map_heap = 0;
     w.heap_bytes = 0;
     w.stop = 0;
     while (off < lim) {

@@ -183,6 +183,14 @@ int upload_tables(dh_bam *b) {
     t.n_rg = (uint32_t)b->rg.size();
     t.n_tags = (uint32_t)b->tags.size();
     t.any_tag_cols = any_tag;
+    t.aux_map = b->aux_map ? 1u : 0u;
+    t.pad = 0;
+    t.aux_excl = nullptr;
+    if (b->aux_map && !b->aux_excl.empty()) {
+        if ((rc = b->d_aux_excl.reserve(b->aux_excl.size() * 4)) != DH_OK) return rc;
+        DH_CUDA(cudaMemcpy(b->d_aux_excl.p, b->aux_excl.data(), b->aux_excl.size() * 4, cudaMemcpyHostToDevice));
+        t.aux_excl = (const uint32_t *)b->d_aux_excl.p;
+    }
     t.col_mask = b->col_mask;
     return DH_OK;
 }
@@ -281,7 +289,8 @@ int walk_segment(dh_bam *b, int k) {
     if ((rc = s.rec.reserve(((s.obytes + b->carry_cap) / min_rec + n + 8) * 2)) != DH_OK ||
         (rc = s.h_blk_start.reserve((n + 1) * 8)) != DH_OK || (rc = s.h_entry.reserve(n * 8)) != DH_OK ||
         (rc = s.h_todo.reserve(n)) != DH_OK || (rc = s.h_walk.reserve(n * sizeof(BlockWalk))) != DH_OK ||
-        (rc = s.h_row_base.reserve(n * 4)) != DH_OK || (rc = s.h_heap_base.reserve(n * 8)) != DH_OK)
+        (rc = s.h_row_base.reserve(n * 4)) != DH_OK || (rc = s.h_heap_base.reserve(n * 8)) != DH_OK ||
+        (rc = s.h_map_base.reserve(n * 4)) != DH_OK)
         return rc;
     DH_CUDA(cudaStreamWaitEvent(sk, s.ev_inf_done, 0));
     uint8_t *ubase = (uint8_t *)s.out.p + b->carry_cap;
@@ -361,6 +370,7 @@ int walk_segment(dh_bam *b, int k) {
                     w.entry = w.exit_off = expect;
                     w.count = 0;
                     w.heap_bytes = 0;
+                    w.map_entries = w.map_heap = 0;
                     w.stop = 0;
                 } else {
                     he[validated] = expect;
@@ -384,6 +394,7 @@ int walk_segment(dh_bam *b, int k) {
     b->next_batch_i = 0;
     uint32_t *hrb = (uint32_t *)s.h_row_base.p;
     uint64_t *hhb = (uint64_t *)s.h_heap_base.p;
+    uint32_t *hmb = (uint32_t *)s.h_map_base.p;
     Batch cur{0, 0, 0, 0, b->rows_total};
     for (uint32_t i = 0; i <= last; ++i) {
         const BlockWalk &w = hw[i];
@@ -394,8 +405,10 @@ int walk_segment(dh_bam *b, int k) {
         }
         hrb[i] = (uint32_t)cur.rows;
         hhb[i] = cur.heap;
+        hmb[i] = (uint32_t)cur.map;
         cur.rows += w.count;
         cur.heap += w.heap_bytes;
+        cur.map += w.map_entries;
     }
     cur.b_hi = last + 1;
     if (cur.rows > 0) b->batches.push_back(cur);
@@ -453,6 +466,11 @@ int issue_batch(dh_bam *b) {
             off = (off + ((bb.rows + 63) / 64) * 8 + A256) & ~A256;
         }
     }
+    uint64_t map_off[4] = {0, 0, 0, 0};   // list entries, validity, key cells, value cells
+    if (b->aux_map) {
+        const uint64_t sz[4] = {16 * bb.rows, ((bb.rows + 63) / 64) * 8, 16 * bb.map, 16 * bb.map};
+        for (int q = 0; q < 4; ++q) { map_off[q] = off; off = (off + sz[q] + A256) & ~A256; }
+    }
     const uint64_t heap_off = off, total = off + bb.heap;
     int rc;
     if ((rc = o.arena.reserve(total + 256)) != DH_OK) return rc;
@@ -485,6 +503,28 @@ int issue_batch(dh_bam *b) {
     DH_CUDA(cudaEventRecord(o.ev_k0, sk));
     DH_CUDA(launch_bam_decode(dp, b->tabs, sk));
     b->ctx->launches++;
+    if (b->aux_map) {
+        AuxMapParams mp;
+        memset(&mp, 0, sizeof mp);
+        mp.u = dp.u; mp.walk = dp.walk; mp.blk_start = dp.blk_start; mp.rec = dp.rec; mp.rec_bias = dp.rec_bias;
+        mp.row_base = dp.row_base; mp.heap_base = dp.heap_base; mp.map_base = (const uint32_t *)s.h_map_base.p;
+        mp.b_lo = bb.b_lo; mp.b_hi = bb.b_hi;
+        uint8_t *da = (uint8_t *)o.arena.p, *ha = (uint8_t *)o.h_arena.p;
+        mp.entries = da + map_off[0];
+        mp.valid = (unsigned long long *)(da + map_off[1]);
+        mp.keys = da + map_off[2];
+        mp.values = da + map_off[3];
+        mp.heap = dp.heap;
+        mp.heap_host = dp.heap_host;
+        DH_CUDA(cudaMemsetAsync(mp.valid, 0, ((bb.rows + 63) / 64) * 8, sk));
+        DH_CUDA(launch_bam_auxmap(mp, b->tabs, sk));
+        b->ctx->launches++;
+        o.desc.aux_map = ha + map_off[0];
+        o.desc.aux_map_validity = (const uint64_t *)(ha + map_off[1]);
+        o.desc.aux_keys = ha + map_off[2];
+        o.desc.aux_values = ha + map_off[3];
+        o.desc.n_aux = bb.map;
+    }
     DH_CUDA(cudaEventRecord(o.ev_k1, sk));
     DH_CUDA(cudaStreamWaitEvent(sd, o.ev_k1, 0));
     DH_CUDA(cudaEventRecord(o.ev_c0, sd));
@@ -558,7 +598,7 @@ void dh_bam_close(dh_bam *b) {
     for (auto &s : b->ss) {
         s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release(); s.rec.release();
         s.h_desc.release(); s.h_status.release(); s.h_blk_start.release(); s.h_entry.release(); s.h_todo.release();
-        s.h_walk.release(); s.h_row_base.release(); s.h_heap_base.release();
+        s.h_walk.release(); s.h_row_base.release(); s.h_heap_base.release(); s.h_map_base.release();
         for (cudaEvent_t e : {s.ev_h2d, s.ev_inf0, s.ev_inf1, s.ev_inf_done, s.ev_free, s.ev_walk0, s.ev_walk1, s.ev_walk2}) if (e) cudaEventDestroy(e);
     }
     for (auto &s : b->bs) {
@@ -605,6 +645,22 @@ int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, 
     }
     const int ncols = BAM_CORE_COLS + n_tags;
     b->col_mask = ncols >= 64 ? col_mask : (col_mask & ((1ull << ncols) - 1));
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    return upload_tables(b);
+}
+
+int dh_bam_set_aux_map(dh_bam *b, int enable, const char *exclude, int n_exclude) {
+    if (!b || n_exclude < 0 || (n_exclude && !exclude)) { set_error("dh_bam_set_aux_map: bad arguments"); return DH_EINVAL; }
+    if (b->scanning && !b->inflight.empty()) { set_error("dh_bam_set_aux_map: scan in progress"); return DH_EINVAL; }
+    b->aux_map = enable != 0;
+    b->aux_excl.clear();
+    if (enable && n_exclude) {
+        b->aux_excl.assign(2048, 0u);
+        for (int i = 0; i < n_exclude; ++i) {
+            const uint32_t key = (uint8_t)exclude[2 * i] | ((uint32_t)(uint8_t)exclude[2 * i + 1] << 8);
+            b->aux_excl[key >> 5] |= 1u << (key & 31u);
+        }
+    }
     DH_CUDA(cudaSetDevice(b->ctx->device));
     return upload_tables(b);
 }

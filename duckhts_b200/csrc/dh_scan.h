@@ -17,12 +17,13 @@ constexpr uint64_t A256 = 255;
 struct Batch {           // one output batch of the current segment
     uint32_t b_lo, b_hi; // walk-block index range
     uint64_t rows, heap, row0;
+    uint64_t map = 0;    // AUXILIARY_TAGS key/value pairs
 };
 
 struct SegSlot {
     DevBuf comp, out, desc, status, work, rec;
     int64_t rec_bias = 0;
-    PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base;
+    PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base, h_map_base;
     cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_inf_done = nullptr, ev_free = nullptr, ev_walk0 = nullptr,
                 ev_walk1 = nullptr, ev_walk2 = nullptr;
     size_t b0 = 0, b1 = 0;  // file block range
@@ -70,6 +71,9 @@ struct dh_bam {
     uint64_t col_mask = (1ull << BAM_CORE_COLS) - 1;
     std::vector<TagReq> tags;
     ScanTables tabs;
+    bool aux_map = false;          // AUXILIARY_TAGS MAP column requested (A16)
+    std::vector<uint32_t> aux_excl; // tags left out of it (bit set over t0 | t1 << 8), empty = none
+    DevBuf d_aux_excl;
     // knobs
     uint64_t seg_comp = 1024ull << 20;
     uint32_t batch_rows = 1u << 20;

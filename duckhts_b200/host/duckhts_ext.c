@@ -101,6 +101,7 @@ typedef struct {
     char *region;            /* the `region` parameter as given (comma separated), NULL if absent or empty */
     int standard_tags, has_index, n_contigs;
     int n_cols;
+    int aux_col;             /* schema index of AUXILIARY_TAGS (auxiliary_tags := true), else -1 */
 } bam_bind_t;
 
 typedef struct {
@@ -146,7 +147,6 @@ static void read_bam_bind(duckdb_bind_info info) {
     bam_bind_t *b = NULL;
     dh_ctx *ctx = shared_ctx();
     if (!ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
-    else if (auxiliary_tags) snprintf(err, sizeof err, "read_bam: auxiliary_tags := true is not available in this build");
     else {
         b = (bam_bind_t *)api.duckdb_malloc(sizeof *b);
         memset(b, 0, sizeof *b);
@@ -211,6 +211,13 @@ static void read_bam_bind(duckdb_bind_info info) {
         }
         b->n_cols += N_STD_TAGS;
     }
+    b->aux_col = -1;
+    if (auxiliary_tags) {   /* MAP(VARCHAR, VARCHAR) after the typed tag columns (src/bam_reader.c:539-549) */
+        duckdb_logical_type mt = api.duckdb_create_map_type(t_varchar, t_varchar);
+        b->aux_col = b->n_cols++;
+        api.duckdb_bind_add_result_column(info, "AUXILIARY_TAGS", mt);
+        api.duckdb_destroy_logical_type(&mt);
+    }
     api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_int); api.duckdb_destroy_logical_type(&t_bigint);
     api.duckdb_destroy_logical_type(&t_usmall); api.duckdb_destroy_logical_type(&t_double);
     api.duckdb_bind_set_bind_data(info, b, bam_bind_free);
@@ -236,11 +243,12 @@ static void read_bam_local_init(duckdb_init_info info) {
      * requested from the C-ABI in projection order; tag k of the request is column 13 + k of every batch. */
     uint64_t mask = 0;
     dh_tag_req tags[DH_BAM_MAX_TAGS];
-    int n_tags = 0;
+    int n_tags = 0, want_map = 0;
     for (idx_t i = 0; i < l->n_proj; ++i) {
         const idx_t c = api.duckdb_init_get_column_index(info, i);
         l->col_ids[i] = c;
         if (c < N_CORE) { l->abi_col[i] = (int)c; mask |= 1ull << c; continue; }
+        if ((int)c == b->aux_col) { l->abi_col[i] = -2; want_map = 1; continue; }
         const char *e = STD_TAGS + 4 * (c - N_CORE);
         if (c - N_CORE >= N_STD_TAGS || n_tags >= DH_BAM_MAX_TAGS) { l->abi_col[i] = -1; continue; }
         tags[n_tags].tag[0] = e[0]; tags[n_tags].tag[1] = e[1]; tags[n_tags].type = e[2]; tags[n_tags].pad = e[2] == 'B' ? e[3] : 0;
@@ -251,6 +259,11 @@ static void read_bam_local_init(duckdb_init_info info) {
     /* which rows (src/bam_reader.c:601-671): region(s) through the index; else, with an index and more than one contig,
      * contig by contig (reads without a contig are then never returned); else the whole file in order */
     int rc = dh_bam_set_projection(b->bam, mask, tags, n_tags);
+    if (rc == DH_OK) {   /* the MAP leaves out the tags served as typed columns (bam_reader.c:976) */
+        char excl[2 * N_STD_TAGS];
+        for (int k = 0; k < N_STD_TAGS; ++k) { excl[2 * k] = STD_TAGS[4 * k]; excl[2 * k + 1] = STD_TAGS[4 * k + 1]; }
+        rc = dh_bam_set_aux_map(b->bam, want_map, excl, b->standard_tags ? N_STD_TAGS : 0);
+    }
     char err[1200];
     err[0] = 0;
     if (rc != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
@@ -300,6 +313,38 @@ static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
     for (idx_t i = 0; i < l->n_proj; ++i) {
         duckdb_vector vec = api.duckdb_data_chunk_get_vector(output, i);
         const int ac = l->abi_col[i];
+        if (ac == -2) {   /* AUXILIARY_TAGS: list entries re-based onto the vector's child, key / value cells appended */
+            const duckdb_list_entry *cells = (const duckdb_list_entry *)l->batch.aux_map + r0;
+            const uint64_t *valid = l->batch.aux_map_validity;
+            duckdb_list_entry *out = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
+            uint64_t *val = NULL;
+            idx_t total = api.duckdb_list_vector_get_size(vec), need = total;
+            for (idx_t r = 0; r < n; ++r) need += cells[r].length;
+            api.duckdb_list_vector_reserve(vec, need);
+            api.duckdb_list_vector_set_size(vec, need);
+            duckdb_vector child = api.duckdb_list_vector_get_child(vec);
+            duckdb_vector kv[2] = {api.duckdb_struct_vector_get_child(child, 0), api.duckdb_struct_vector_get_child(child, 1)};
+            const duckdb_string_t *src[2] = {(const duckdb_string_t *)l->batch.aux_keys, (const duckdb_string_t *)l->batch.aux_values};
+            for (idx_t r = 0; r < n; ++r) {
+                out[r].offset = total;
+                out[r].length = cells[r].length;
+                if (!((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) {
+                    if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
+                    api.duckdb_validity_set_row_invalid(val, r);
+                    continue;
+                }
+                for (int q = 0; q < 2; ++q) {
+                    duckdb_string_t *dst = (duckdb_string_t *)api.duckdb_vector_get_data(kv[q]);
+                    for (uint64_t e = 0; e < cells[r].length; ++e) {
+                        const duckdb_string_t *cl = &src[q][cells[r].offset + e];
+                        if (cl->value.inlined.length <= 12) dst[total + e] = *cl;
+                        else api.duckdb_vector_assign_string_element_len(kv[q], total + e, cl->value.pointer.ptr, cl->value.inlined.length);
+                    }
+                }
+                total += cells[r].length;
+            }
+            continue;
+        }
         if (ac < 0) {   /* column not served: all NULL */
             api.duckdb_vector_ensure_validity_writable(vec);
             uint64_t *val = api.duckdb_vector_get_validity(vec);

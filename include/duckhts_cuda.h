@@ -137,6 +137,12 @@ typedef struct {
 } dh_tag_req;
 int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, int n_tags);
 
+/* A16: the auxiliary_tags := true column (bam_reader.c:539-549, 967-1031): every aux entry of the record, in record
+ * order, as key = tag / value = bam_aux_to_string text (bam_reader.c:140-183; integers "%" PRId64, floats "%g", B
+ * arrays "sub,v,v,..").  `exclude` = n_exclude two-byte tags left out of the map (the reference leaves out the
+ * tags that standard_tags := true serves as typed columns).  Call before a scan begins. */
+int dh_bam_set_aux_map(dh_bam *b, int enable, const char *exclude, int n_exclude);
+
 /* Pipeline knobs (0 = keep): compressed bytes per inflate segment, rows per output batch, carry buffer for
  * records that straddle segments.  Small values exercise the multi-segment paths in tests. */
 int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, uint64_t carry_bytes);
@@ -171,6 +177,14 @@ typedef struct {
     const uint8_t *heap;
     uint64_t heap_bytes;
     uint64_t bytes;       /* bytes copied device -> host for this batch */
+    /* AUXILIARY_TAGS MAP(VARCHAR, VARCHAR) column, when dh_bam_set_aux_map enabled it (else NULL / 0): one
+     * duckdb_list_entry {offset, length} per row into the n_aux key / value cells (duckdb_string_t, long values point
+     * into `heap`); rows without a pair are NULL (validity bit 0) as at bam_reader.c:982-991. */
+    const void *aux_map;
+    const uint64_t *aux_map_validity;
+    const void *aux_keys;
+    const void *aux_values;
+    uint64_t n_aux;
 } dh_bam_batch;
 /* Returns 1 and fills *out (buffers stay valid until the next call on this handle), 0 at end of scan, < 0 on
  * error. */

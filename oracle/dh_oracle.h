@@ -95,6 +95,9 @@ typedef struct {
  * htslib/header.c sam_hdr_find_tag_id (RG ID -> SM).  `u` = inflated byte stream of a whole BAM file.
  * Returns 0, or -1 if the header itself is invalid (the reference fails in bind). */
 int dho_bam_decode(const uint8_t *u, uint64_t n, const dho_tag_req *tags, int n_tags, dho_bam_columns *out);
+/* A16: tag request type 'M' = the AUXILIARY_TAGS MAP of the row (bam_reader.c:967-1031), serialised in the string column as
+ * key NUL value NUL ...; dho_set_aux_exclude names the n two-byte tags left out (standard_tags := true: BAM_STD_TAGS). */
+void dho_set_aux_exclude(const char *tags, int n);
 void dho_bam_free(dho_bam_columns *c);
 
 /* ---- A8: BAI/CSI index + iterators (dh_oracle_idx.inc) ------------------------------------------------

@@ -117,6 +117,16 @@ def strcol_list(col):
     return [heap[int(off[i]):int(off[i + 1])] if valid[i] else None for i in range(len(valid))]
 
 
+# the SAMtags columns of standard_tags := true (src/bam_reader.c:54-70), the tags the AUXILIARY_TAGS map then leaves out
+STD_TAGS = ("AM AS BC BQ BZ CB CC CG CM CO CP CQ CR CS CT CY E2 FI FS FZ H0 H1 H2 HI IH LB MC MD MI ML MM MN MQ NH NM OA OC OP OQ OX PG "
+            "PQ PT PU Q2 QT QX R2 RG RX SA SM TC TS U2 UQ").split()
+
+
+def set_aux_exclude(tags=()):
+    ex = b"".join(t if isinstance(t, bytes) else t.encode() for t in tags)
+    lib().dho_set_aux_exclude(ex, len(ex) // 2)
+
+
 def bam_decode(inflated, tags=()):
     """Reference-order columns of a whole inflated BAM stream.  tags: iterable of (b'NM', 'i') ..."""
     a = _u8(inflated)
@@ -151,6 +161,16 @@ def bam_decode(inflated, tags=()):
             d["i"] = np.ctypeslib.as_array(tc.i, shape=(max(n, 1),))[:n].copy()
         elif ty == "f":
             d["f"] = np.ctypeslib.as_array(tc.f, shape=(max(n, 1),))[:n].copy()
+        elif ty == "M":
+            # AUXILIARY_TAGS: key NUL value NUL ... -> [(key, value), ...]
+            rows = []
+            for x in strcol_list(_strcol(tc.s, n)):
+                if x is None:
+                    rows.append(None)
+                else:
+                    f = x.split(b"\0")[:-1]
+                    rows.append(list(zip(f[0::2], f[1::2])))
+            d["m"] = rows
         elif ty[0] == "B":
             d["b"] = [None if x is None else np.frombuffer(x, dtype=np.int64) for x in strcol_list(_strcol(tc.s, n))]
         else:

@@ -67,6 +67,65 @@ def test_b_array_list_tags(ctx):
     assert [None if x is None else x.tolist() for x in got["tags"][0]["b"]] == [[0, 0], [-5, 300], []]
 
 
+def map_both(ctx, img, exclude, **kw):
+    rc, infl, _ = orc.bgzf_inflate(img)
+    assert rc == 0
+    orc.set_aux_exclude(exclude)
+    try:
+        exp = orc.bam_decode(infl, [(b"\0\0", "M")])
+    finally:
+        orc.set_aux_exclude(())
+    got = dh.bam_scan(ctx, img, tags=(), col_mask=1, aux_map=exclude, **kw)
+    assert got["n"] == exp["n"] and got["status"] == exp["status"]
+    e = exp["tags"][0]["m"]
+    for r, (g, x) in enumerate(zip(got["aux_map"], e)):
+        assert g == x, (r, g, x)
+    return got, e
+
+
+def test_auxiliary_tags_map(ctx):
+    """A16: MAP(VARCHAR, VARCHAR) of every aux entry (bam_reader.c:967-1031): all aux types, B arrays, the standard_tags
+    exclusion, NULL rows, long values in the heap next to the other columns' slots."""
+    img = util.synth_bam_bytes(n_records=30000, seed=80, paired=True, extra=("--btags",))
+    got, e = map_both(ctx, img, orc.STD_TAGS)
+    assert any(x is None for x in e) and any(x and any(len(v) > 12 for _, v in x) for x in e)
+    map_both(ctx, img, (), seg_comp=1 << 16, batch_rows=501)
+    # with every other column projected too (shared heap)
+    tags = [(b"ML", "Bi"), (b"MD", "Z"), (b"XZ", "Z")]
+    full = dh.bam_scan(ctx, img, tags=tags, aux_map=orc.STD_TAGS, batch_rows=4000)
+    assert full["aux_map"] == got["aux_map"]
+    rc, infl, _ = orc.bgzf_inflate(img)
+    util.assert_bam_equal(full, orc.bam_decode(infl, tags))
+    # edge records: CG consumed by bam_tag2cigar, unknown aux type, value cut by the record end, unterminated Z
+    stream = bam_header(REFS, TEXT) + b"".join(edge_records())
+    for block in (0xff00, 333):
+        map_both(ctx, util.make_bgzf(stream, block=block), (), batch_rows=5)
+        map_both(ctx, util.make_bgzf(stream, block=block), orc.STD_TAGS, batch_rows=5)
+
+
+def test_auxiliary_tags_float_text_is_printf_g(ctx):
+    """\"%g\" on the GPU (exact big-integer digit generation) against the C library's, bit pattern by bit pattern: random doubles
+    and floats, powers of ten, round-half cases, subnormals, infinities and NaNs."""
+    rng = np.random.default_rng(5)
+    dbl = [0.0, -0.0, 1.0, 0.1, 0.5, 1e-5, 1e-4, 9.9999949999e-5, 0.000123456, 999999.5, 999999.4999, 1000005.0, 1000015.0, 100000.5,
+           100001.5, 2.5e-5, 1e22, 1e23, 1.7976931348623157e308, 5e-324, 2.2250738585072014e-308, 123456.5, 123455.5, 0.3, 2.0 / 3.0,
+           float("inf"), float("-inf"), float("nan"), 1e100, 1e-100, 299792458.0, 6.02214076e23, 1.5, 2.5, 1234565.0, 1234575.0]
+    dbl += [10.0 ** k for k in range(-30, 31)] + [-(10.0 ** k) * 1.0000005 for k in range(-10, 11)]
+    dbl += list(rng.integers(0, 1 << 64, 3000, dtype=np.uint64).view(np.float64))
+    dbl += list((rng.random(2000) * 10.0 ** rng.integers(-8, 9, 2000)).astype(np.float64))
+    flt = list(rng.integers(0, 1 << 32, 3000, dtype=np.uint64).astype(np.uint32).view(np.float32)) + [np.float32(x) for x in (3.14159274, 1e-45, 3.4028235e38, 1e-5, 1e-4, 16777216.0, 0.1)]
+    recs = []
+    for i in range(0, len(dbl), 25):
+        aux = b"".join(b"D" + bytes([65 + k]) + b"d" + struct.pack("<d", v) for k, v in enumerate(dbl[i:i + 25]))
+        recs.append(bam_record(b"d%d" % i, aux=aux))
+    for i in range(0, len(flt), 25):
+        aux = b"".join(b"F" + bytes([65 + k]) + b"f" + struct.pack("<f", v) for k, v in enumerate(flt[i:i + 25]))
+        aux += b"FBBf" + struct.pack("<I", len(flt[i:i + 25])) + b"".join(struct.pack("<f", v) for v in flt[i:i + 25])
+        recs.append(bam_record(b"f%d" % i, aux=aux))
+    got, e = map_both(ctx, util.make_bgzf(bam_header(REFS, TEXT) + b"".join(recs)), ())
+    assert (b"DA", b"0") in e[0] and (b"DB", b"-0") in e[0]
+
+
 def test_unplaced_reads_are_returned_in_sequential_mode(ctx):
     img = util.synth_bam_bytes(n_records=3000, seed=14, paired=True, extra=("--unplaced", "50"))
     got, exp = both(ctx, img)

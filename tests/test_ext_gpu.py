@@ -63,6 +63,19 @@ def test_b_array_list_columns(tmp_path):
     assert "[" in out_r
 
 
+@pytest.mark.parametrize("std", [True, False])
+def test_auxiliary_tags_map_column(std):
+    # A16: MAP(VARCHAR, VARCHAR) column, alone and next to every other column; schema line included
+    extra = ("standard_tags=true",) if std else ()
+    paths = [util.synth_path("bam", n_records=20000, seed=77, paired=True, extra=("--btags",))] + [os.path.join(GOLD, n + ".bam") for n in ("auxf_values", "aux_tags", "range", "ce_unmap2")]
+    for path in paths:
+        for cols in ((str(69 if std else 13),), ()):
+            args = ("read_bam", path, "auxiliary_tags=true") + extra + (("--cols", cols[0]) if cols else ())
+            (rc_r, out_r, _), (rc_o, out_o, err_o) = both(*args)
+            assert rc_r == 0 and rc_o == 0, err_o
+            assert out_o == out_r, (path, cols)
+
+
 @pytest.mark.parametrize("cols", ["0", "1,3,4", "9,10", "12,11,2", "5,0,8,6", "3"])
 def test_projection_pushdown(cols):
     path = os.path.join(GOLD, "range.bam")
