@@ -121,6 +121,7 @@ SIGNATURES = {
     "dh_bcf_configure": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64]),
     "dh_bcf_set_mode": (C.c_int, [C.c_void_p, C.c_uint32]),
     "dh_bcf_scan_begin": (C.c_int, [C.c_void_p]),
+    "dh_bcf_scan_region": (C.c_int, [C.c_void_p, C.c_void_p, C.c_char_p]),
     "dh_bcf_next_batch": (C.c_int, [C.c_void_p, C.POINTER(BcfBatch)]),
     "dh_bcf_scan_stats_get": (C.c_int, [C.c_void_p, C.POINTER(BamScanStats)]),
     "dh_ctx_sync": (C.c_int, [C.c_void_p]),

@@ -7,6 +7,8 @@ import ctypes as C
 import numpy as np
 
 from ._lib import BamScanStats, BcfBatch, BcfField, DuckhtsError, check, lib
+
+DH_ENOREGION = -7
 from .bam import cells_to_list, validity_to_bool
 from .bgzf import _as_u8
 
@@ -68,6 +70,14 @@ class BcfFile:
     def scan_begin(self):
         check(lib().dh_bcf_scan_begin(self.h), "dh_bcf_scan_begin")
 
+    def scan_region(self, index, region):
+        """One region through the CSI index (bcf_itr_querys); False when the region names no contig of the file."""
+        rc = lib().dh_bcf_scan_region(self.h, index.h, region if isinstance(region, bytes) else region.encode())
+        if rc == DH_ENOREGION:
+            return False
+        check(rc, "dh_bcf_scan_region")
+        return True
+
     def next_batch(self):
         b = BcfBatch()
         rc = check(lib().dh_bcf_next_batch(self.h, C.byref(b)), "dh_bcf_next_batch")
@@ -85,6 +95,14 @@ class BcfFile:
             if b is None:
                 return n
             n += b.n_records
+
+
+class _NoIndex:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
 
 
 def _esc(b):
@@ -151,18 +169,29 @@ def schema_names(bf, tidy):
     return names
 
 
-def rows_text(ctx, data, tidy=True, batch_records=0, seg_comp=0):
-    """Whole scan as text lines (header line first), like `fake_duckdb EXT read_bcf FILE [tidy_format=true] --dump`."""
-    with BcfFile(ctx, data) as bf:
+def rows_text(ctx, data, tidy=True, batch_records=0, seg_comp=0, index=None, regions=None):
+    """Whole scan as text lines (header line first), like `fake_duckdb EXT read_bcf FILE [tidy_format=true] --dump`.
+    index = CSI bytes + regions = list of region strings: the reference's chained single-region scans (bcf_reader.c:917-951)."""
+    from .bam import Index
+    with BcfFile(ctx, data) as bf, (Index(ctx, index) if index is not None else _NoIndex()) as ix:
         bf.configure(seg_comp, batch_records, 0)
-        bf.scan_begin()
         lines = ["\t".join(schema_names(bf, tidy))]
         ns = len(bf.samples)
         status = 0
-        while True:
-            b = bf.next_batch()
-            if b is None:
-                break
+
+        def batches():
+            if regions is None:
+                bf.scan_begin()
+                while (bt := bf.next_batch()) is not None:
+                    yield bt
+                return
+            for rg in regions:                      # chained single-region scans, in the order given
+                if not bf.scan_region(ix, rg):
+                    continue                        # "Region query returned no iterator; skipping region"
+                while (bt := bf.next_batch()) is not None:
+                    yield bt
+
+        for b in batches():
             status = b.status
             n = int(b.n_records)
             heap = b.heap or 0

@@ -262,6 +262,14 @@ __global__ void __launch_bounds__(128) bcf_walk_kernel(const WalkParams p, const
         if (p.is_final && off == p.seg_end) break;
         const int rc = bcf_parse(u, off, p.seg_end, p.is_final != 0, t, r, nullptr);
         if (rc != 0) { w.stop = rc; break; }
+        if (p.filt_mode) {
+            // region query: bcf_readrec hands hts_itr_next (tid, beg, end) = (rid, pos, pos + rlen) (htslib/vcf.c:2267-2276); the
+            // iterator keeps `end > beg_q && end_q > beg` on the queried contig (hts.c:4304-4313)
+            bool keep = false;
+            for (uint32_t q = 0; q < p.filt_n && !keep; ++q)
+                keep = p.filt[q].tid == r.rid && r.pos + (int64_t)r.rlen > p.filt[q].beg && p.filt[q].end > r.pos;
+            if (!keep) { off = r.end; continue; }
+        }
         w.heap_bytes += r.need;
         rec[w.count] = (uint16_t)(off - start);
         w.count++;

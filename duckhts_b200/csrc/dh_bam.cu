@@ -939,6 +939,7 @@ namespace dh {
 int scan_ensure_events(dh_bam *b) { return ensure_events(b); }
 int scan_begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh) { return begin_range(b, voff_beg, voff_end, fresh); }
 int scan_have_work(dh_bam *b) { return have_work(b); }
+int scan_start_filtered(dh_bam *b, const dh_index *idx, int mode) { return start_filtered(b, idx, mode); }
 int scan_inflate_head(dh_bam *b, uint64_t want, std::vector<uint8_t> &u) {
     const size_t nb = b->bt.blocks.size();
     size_t take = 0;

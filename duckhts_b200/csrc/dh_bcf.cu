@@ -541,6 +541,17 @@ int dh_bcf_scan_begin(dh_bcf *h) {
     return scan_begin_range(h->scan, 0, UINT64_MAX, true);
 }
 
+int dh_bcf_scan_region(dh_bcf *h, const dh_index *idx, const char *region) {
+    if (!h || !idx || !region) { set_error("dh_bcf_scan_region: bad arguments"); return DH_EINVAL; }
+    dh_bam *b = h->scan;
+    std::string err;
+    const char *one[1] = {region};
+    const int n = regions_to_intervals(one, 1, b->bcf->ctg, b->filt, err);
+    if (n < 0) { set_error("%s", err.c_str()); return DH_EINVAL; }
+    if (n == 0) { set_error("region '%s' names no contig of this file", region); return DH_ENOREGION; }
+    return scan_start_filtered(b, idx, 2);
+}
+
 int dh_bcf_next_batch(dh_bcf *h, dh_bcf_batch *out) {
     if (!h || !out || !h->scan->scanning) { set_error("dh_bcf_next_batch: no scan in progress"); return DH_EINVAL; }
     dh_bam *b = h->scan;
@@ -558,6 +569,12 @@ int dh_bcf_next_batch(dh_bcf *h, dh_bcf_batch *out) {
     };
     int rc = top_up();
     if (rc != DH_OK) { b->scanning = false; return rc; }
+    while (b->inflight.empty() && !b->pending.empty() && b->final_status == 0) {
+        // this virtual-offset range of the region query is exhausted: go on with the next one
+        const IdxChunk c = b->pending.front();
+        b->pending.pop_front();
+        if ((rc = scan_begin_range(b, c.u, c.v, false)) != DH_OK || (rc = top_up()) != DH_OK) { b->scanning = false; return rc; }
+    }
     if (b->inflight.empty()) {
         b->st.rows = b->rows_total;
         b->st.status = b->final_status;

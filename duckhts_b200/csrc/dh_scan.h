@@ -113,6 +113,8 @@ int scan_ensure_events(dh_bam *b);
 int scan_begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh);
 // 1 = a batch of the current segment is ready to be issued, 0 = scan exhausted, < 0 error
 int scan_have_work(dh_bam *b);
+// indexed scan over b->filt (intervals): plans the virtual-offset ranges, uploads the filter, begins the first range
+int scan_start_filtered(dh_bam *b, const dh_index *idx, int mode);
 // inflate the leading blocks of the image until `want` inflated bytes are available (or the file ends)
 int scan_inflate_head(dh_bam *b, uint64_t want, std::vector<uint8_t> &u);
 // BCF side (dh_bcf.cu)

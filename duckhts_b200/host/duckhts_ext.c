@@ -81,6 +81,31 @@ static int named_bool(duckdb_bind_info info, const char *name, int dflt) {
 }
 static int file_exists(const char *p) { struct stat st; return p && stat(p, &st) == 0; }
 
+/* index lookup like sam_index_load3 / bcf_index_load3(path, index_path, HTS_IDX_SILENT_FAIL) (htslib/hts.c idx_find_and_load):
+ * the explicit path, else PATH.csi, PATH with its suffix replaced by .csi[, PATH.bai, PATH with .bai]; n_ext = 2 for BAM, 1 for BCF */
+static dh_index *find_index(dh_ctx *ctx, const char *path, const char *index_path, int n_ext) {
+    char cand[5][1100];
+    int nc = 0;
+    dh_index *ix = NULL;
+    if (index_path) snprintf(cand[nc++], sizeof cand[0], "%s", index_path);
+    else {
+        static const char *const EXT[2] = {".csi", ".bai"};
+        const char *dot = strrchr(path, '.'), *slash = strrchr(path, '/');
+        for (int e = 0; e < n_ext; ++e) {
+            snprintf(cand[nc++], sizeof cand[0], "%s%s", path, EXT[e]);
+            if (dot && (!slash || dot > slash)) snprintf(cand[nc++], sizeof cand[0], "%.*s%s", (int)(dot - path), path, EXT[e]);
+        }
+    }
+    for (int i = 0; i < nc && !ix; ++i) {
+        if (!file_exists(cand[i])) continue;
+        uint64_t isz = 0;
+        uint8_t *ibuf = slurp_pinned(cand[i], &isz);
+        if (ibuf) { ix = dh_index_load(ctx, ibuf, isz); dh_host_free(ibuf); }
+        if (!index_path) break;        /* the first file that exists is the one htslib reads */
+    }
+    return ix;
+}
+
 /* ================================================================================================================
  * read_bam
  * ================================================================================================================ */
@@ -167,29 +192,8 @@ static void read_bam_bind(duckdb_bind_info info) {
     b->standard_tags = standard_tags;
     b->n_contigs = dh_bam_n_ref(b->bam);
     if (region && region[0]) b->region = strdup(region);
-    /* index lookup like sam_index_load3(fp, path, index_path, HTS_IDX_SILENT_FAIL) (htslib/hts.c idx_find_and_load):
-     * explicit path, else PATH.csi, PATH with its suffix replaced by .csi, PATH.bai, PATH with .bai */
-    {
-        char cand[5][1100];
-        int nc = 0;
-        if (index_path) snprintf(cand[nc++], sizeof cand[0], "%s", index_path);
-        else {
-            static const char *const EXT[2] = {".csi", ".bai"};
-            const char *dot = strrchr(path, '.'), *slash = strrchr(path, '/');
-            for (int e = 0; e < 2; ++e) {
-                snprintf(cand[nc++], sizeof cand[0], "%s%s", path, EXT[e]);
-                if (dot && (!slash || dot > slash)) snprintf(cand[nc++], sizeof cand[0], "%.*s%s", (int)(dot - path), path, EXT[e]);
-            }
-        }
-        for (int i = 0; i < nc && !b->index; ++i) {
-            if (!file_exists(cand[i])) continue;
-            uint64_t isz = 0;
-            uint8_t *ibuf = slurp_pinned(cand[i], &isz);
-            if (ibuf) { b->index = dh_index_load(ctx, ibuf, isz); dh_host_free(ibuf); }
-            if (!index_path) break;        /* the first file that exists is the one htslib reads */
-        }
-        b->has_index = b->index != NULL;
-    }
+    b->index = find_index(ctx, path, index_path, 2);
+    b->has_index = b->index != NULL;
     duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER),
                         t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT), t_usmall = api.duckdb_create_logical_type(DUCKDB_TYPE_USMALLINT),
                         t_double = api.duckdb_create_logical_type(DUCKDB_TYPE_DOUBLE);
@@ -433,6 +437,10 @@ typedef struct {
     int tidy, n_samples, n_info, n_fmt, default_gt;
     int info_start, sample_id_col, fmt_start, n_cols;
     dh_bcf_field *info, *fmt;
+    dh_index *index;         /* CSI, loaded when a region is given (bcf_reader.c:902-915) */
+    char *region;            /* the parameter as given */
+    char **regions;          /* comma-separated, blanks trimmed, empty tokens dropped (parse_regions_duckdb, bcf_reader.c:286-329) */
+    int n_regions;
 } bcf_bind_t;
 
 typedef struct {
@@ -441,13 +449,28 @@ typedef struct {
     dh_bcf_batch batch;
     uint64_t cursor;        /* next row of the batch: records (wide) or records x samples (tidy) */
     int have_batch, done;
+    int next_region;        /* region cursor of a chained region scan (bcf_reader.c:172, 1318-1333) */
 } bcf_local_t;
+
+/* start the scan of the next region that yields an iterator: 1 started, 0 none left, < 0 error */
+static int bcf_next_region(bcf_bind_t *b, bcf_local_t *l) {
+    while (l->next_region < b->n_regions) {
+        const int rc = dh_bcf_scan_region(b->bcf, b->index, b->regions[l->next_region++]);
+        if (rc == DH_OK) return 1;
+        if (rc != DH_ENOREGION) return rc;      /* unknown contig: "Region query returned no iterator; skipping region" */
+    }
+    return 0;
+}
 
 static void bcf_bind_free(void *p) {
     bcf_bind_t *b = (bcf_bind_t *)p;
     if (!b) return;
     if (b->bcf) dh_bcf_close(b->bcf);
     if (b->image) dh_host_free(b->image);
+    if (b->index) dh_index_free(b->index);
+    free(b->region);
+    for (int i = 0; i < b->n_regions; ++i) free(b->regions[i]);
+    free(b->regions);
     free(b->info);
     free(b->fmt);
     api.duckdb_free(b);
@@ -483,10 +506,22 @@ static void read_bcf_bind(duckdb_bind_info info) {
     bcf_bind_t *b = NULL;
     dh_ctx *ctx = shared_ctx();
     if (!ctx) snprintf(err, sizeof err, "read_bcf: no usable CUDA device (%s)", dh_last_error());
-    else if (region && region[0]) snprintf(err, sizeof err, "read_bcf: region queries are not available in this build");
     else {
         b = (bcf_bind_t *)api.duckdb_malloc(sizeof *b);
         memset(b, 0, sizeof *b);
+        if (region && region[0]) {
+            b->region = strdup(region);
+            b->regions = (char **)calloc(strlen(region) + 1, sizeof(char *));
+            char *dup = strdup(region), *save = NULL;
+            for (char *tok = strtok_r(dup, ",", &save); tok; tok = strtok_r(NULL, ",", &save)) {
+                while (*tok == ' ' || *tok == '\t') ++tok;
+                size_t len = strlen(tok);
+                while (len > 0 && (tok[len - 1] == ' ' || tok[len - 1] == '\t')) tok[--len] = 0;
+                if (len) b->regions[b->n_regions++] = strdup(tok);
+            }
+            free(dup);
+            if (b->n_regions) b->index = find_index(ctx, path, index_path, 1);
+        }
         b->image = slurp_pinned(path, &b->size);
         if (!b->image) snprintf(err, sizeof err, "Failed to open BCF/VCF file: %s", path);
         else if (!(b->bcf = dh_bcf_open(ctx, b->image, b->size))) snprintf(err, sizeof err, "Failed to read BCF/VCF header");
@@ -584,7 +619,22 @@ static void read_bcf_local_init(duckdb_init_info info) {
     const int rc = dh_bcf_set_projection(b->bcf, core_mask, iw, b->default_gt ? NULL : fw);
     free(iw);
     free(fw);
-    if (rc != DH_OK || dh_bcf_scan_begin(b->bcf) != DH_OK) {
+    if (rc == DH_OK && b->n_regions > 0) {
+        if (!b->index) {
+            char err[600];
+            snprintf(err, sizeof err, "Region query requires an index file (.tbi or .csi). Region: %s", b->region);
+            api.duckdb_init_set_error(info, err);
+            bcf_local_free(l);
+            return;
+        }
+        const int started = bcf_next_region(b, l);
+        if (started < 0) {
+            api.duckdb_init_set_error(info, dh_last_error());
+            bcf_local_free(l);
+            return;
+        }
+        if (!started) l->done = 1;              /* no region named a contig: an empty result, not an error (bcf_reader.c:952-956) */
+    } else if (rc != DH_OK || dh_bcf_scan_begin(b->bcf) != DH_OK) {
         api.duckdb_init_set_error(info, dh_last_error());
         bcf_local_free(l);
         return;
@@ -643,6 +693,12 @@ static void read_bcf_scan(duckdb_function_info info, duckdb_data_chunk output) {
     while (!l->have_batch || l->cursor >= l->batch.n_records * per_rec) {
         const int rc = dh_bcf_next_batch(b->bcf, &l->batch);
         if (rc == 1) { l->have_batch = 1; l->cursor = 0; continue; }
+        l->have_batch = 0;
+        if ((rc == 0 || rc == DH_EDATA || rc == DH_EFORMAT) && b->n_regions > 0) {   /* end of this region's iterator: chain the next one */
+            const int started = bcf_next_region(b, l);
+            if (started == 1) continue;
+            if (started < 0) api.duckdb_function_set_error(info, dh_last_error());
+        }
         l->done = 1;
         if (rc < 0 && rc != DH_EDATA && rc != DH_EFORMAT) api.duckdb_function_set_error(info, dh_last_error());   /* a bad record / block ends the scan silently (bcf_reader.c:1311-1338) */
         api.duckdb_data_chunk_set_size(output, 0);

@@ -279,6 +279,12 @@ int dh_bcf_set_projection(dh_bcf *b, uint32_t core_mask, const uint8_t *info_wan
 int dh_bcf_configure(dh_bcf *b, uint64_t seg_comp_bytes, uint32_t batch_records, uint64_t string_bytes);
 int dh_bcf_set_mode(dh_bcf *b, uint32_t flags);      /* DH_BAM_DEVICE_INPUT / DH_BAM_DEVICE_OUTPUT, as for dh_bam */
 int dh_bcf_scan_begin(dh_bcf *b);
+/* Region query through the CSI index (bcf_itr_querys + bcf_itr_next, htslib/vcf.h:1321-1330; used by
+ * src/bcf_reader.c:917-951): the records with rid == contig, pos < end and pos + rlen > beg, in file order.  One
+ * region per scan; the reference chains several regions as a union of single-region iterators (duplicates kept), the
+ * caller does the same with one scan per region.  DH_ENOREGION: the region names no contig (the reference warns and
+ * skips it). */
+int dh_bcf_scan_region(dh_bcf *b, const dh_index *idx, const char *region);
 typedef struct {
     uint64_t n_records;
     uint64_t n_samples;

@@ -194,8 +194,37 @@ def _num_text(w, ht):
     return "%.9g" % struct.unpack("<f", struct.pack("<I", w))[0]
 
 
-def scan(u, tidy):
-    """u: inflated bytes of a BCF file.  Returns (lines, status)."""
+def scan(u, tidy, regions=None):
+    """u: inflated bytes of a BCF file.  Returns (lines, status).
+    regions: list of region strings = the reference's chained single-region scans (src/bcf_reader.c:917-951, 1318-1333):
+    one pass per region that names a contig, in the order given, keeping the records bcf_itr_next returns -- those with
+    rid == tid, pos < end and pos + rlen > beg (bcf_readrec, htslib/vcf.c:2267-2276; hts_itr_next, hts.c:4304-4313).  On a
+    coordinate-sorted file (the only kind that can be indexed) the index only decides which blocks are read, not which
+    records qualify."""
+    if regions is not None:
+        from oracle.dh_oracle_py import parse_region
+        head = _scan(u, tidy, lambda rid, pos, rlen: False)[0][:1]
+        names = _contig_names(u)
+        lines, status = list(head), 0
+        for rg in regions:
+            iv = parse_region(rg, names)
+            if iv is None or iv[0] < 0:
+                continue
+            tid, beg, end = iv
+            part, status = _scan(u, tidy, lambda rid, pos, rlen: rid == tid and pos < end and pos + rlen > beg)
+            lines += part[1:]
+        return lines, status
+    return _scan(u, tidy, None)
+
+
+def _contig_names(u):
+    u = bytes(u)
+    l_text = struct.unpack_from("<I", u, 5)[0]
+    h = Header(u[9:9 + l_text].split(b"\0")[0].decode("utf-8", "replace"))
+    return [c if c is not None else "" for c in h.ctg]
+
+
+def _scan(u, tidy, keep):
     u = bytes(u)
     if u[:3] != b"BCF" or u[3] != 2:
         raise ValueError("not BCF")
@@ -285,6 +314,9 @@ def scan(u, tidy):
         except (ValueError, struct.error):
             status = -2                                            # bcf_read < -1: the scan ends silently (bcf_reader.c:1311-1338)
             break
+        if keep is not None and not keep(rid, -1 if pos == 0xffffffff else pos, rlen):
+            p = end
+            continue
         # ---- site-level cells ----
         site = [_esc(h.ctg[rid].encode()), str((-1 if pos == 0xffffffff else pos) + 1), "\\N" if ident == b"." else _esc(ident), _esc(alleles[0]),
                 "[" + ",".join(_esc(a) for a in alleles[1:]) + "]",

@@ -139,3 +139,21 @@ def test_projection_returns_only_requested_columns(ctx):
         assert all((b.format[i] is not None) == (i == gt) for i in range(len(bf.format)))
         assert all(b.info[i] is None for i in range(len(bf.info)))
         assert bf.next_batch() is None
+
+
+# ---- region queries through the CSI index (bcf_itr_querys / bcf_itr_next; src/bcf_reader.c:917-951, 1318-1333) ------------
+@pytest.mark.skipif(not os.path.exists(GEN), reason="generator absent")
+def test_read_bcf_region_queries_match_oracle(ctx, tmp_path):
+    from duckhts_b200 import bcf
+    from tests.test_oracle_bcf import BCF_REGIONS, indexed_bcf, split_regions
+    path = indexed_bcf(tmp_path, n_sites=6000, n_samples=7, seed=12, contigs=5)
+    img = np.fromfile(path, dtype=np.uint8)
+    csi = np.fromfile(path + ".csi", dtype=np.uint8)
+    (_, _), infl = oracle_lines(img, False)
+    from oracle import bcf_oracle
+    for region in BCF_REGIONS:
+        regs = split_regions(region)
+        for tidy, kw in ((False, {}), (True, dict(batch_records=64, seg_comp=1 << 16))):
+            exp, est = bcf_oracle.scan(infl.tobytes(), tidy, regions=regs)
+            got, status, _ = bcf.rows_text(ctx, img, tidy=tidy, index=csi, regions=regs, **kw)
+            assert status == est == 0 and got == exp, (region, tidy, first_diff(got, exp))

@@ -194,6 +194,24 @@ def test_read_bcf_synthetic_2504_samples_hashes():
     assert out_o == out_r
 
 
+def test_read_bcf_region_queries(tmp_path):
+    # chained single-region iterators through the CSI index (src/bcf_reader.c:917-951); explicit index_path; the errors
+    from tests.test_oracle_bcf import BCF_REGIONS, indexed_bcf
+    path = indexed_bcf(tmp_path, n_sites=5000, n_samples=9, seed=13, contigs=6)
+    for region in BCF_REGIONS:
+        for extra in ((), ("tidy_format=true",)):
+            (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bcf", path, "region=" + region, *extra)
+            assert rc_r == 0 and rc_o == 0, err_o
+            assert out_o == out_r, (region, extra)
+    import shutil
+    alt = str(tmp_path / "elsewhere.csi")
+    shutil.move(path + ".csi", alt)
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bcf", path, "region=chr2:1-9000000", "index_path=" + alt)
+    assert rc_r == 0 and rc_o == 0 and out_o == out_r and len(out_r.splitlines()) > 10, err_o
+    (rc_r, out_r, _), (rc_o, out_o, _) = both("read_bcf", path, "region=chr2")      # no index next to the file any more
+    assert rc_r == 1 and rc_o == 1 and out_o == out_r
+
+
 def test_read_bcf_bind_errors(tmp_path):
     for args in (("read_bcf", str(tmp_path / "missing.bcf")), ("read_bcf", "")):
         (rc_r, out_r, _), (rc_o, out_o, _) = both(*args)

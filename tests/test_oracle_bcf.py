@@ -64,3 +64,36 @@ def test_bcf_oracle_stops_at_a_bad_record():
     struct.pack_into("<i", u, p + 8, 9999)
     got, status = bcf_oracle.scan(bytes(u), False)
     assert status == -2 and got == full[:8]
+
+
+BCF_REGIONS = ["chr1", "chr2:1000000-8000000", "chr3:5,000,000-9000000,chr1:1-3000000,chr3:8000000-12000000", "nosuch,chr4:100-",
+               " chr2:7,000,000-7,900,000 ,, chr2:7,500,000-", "chr9", "chr4:-2000000"]
+
+
+def indexed_bcf(tmp_path, n_sites=3000, n_samples=5, seed=11, contigs=4):
+    path = str(tmp_path / "r.bcf")
+    subprocess.check_call([GEN, path, str(n_sites), str(n_samples), str(seed), "--contigs", str(contigs), "--edge", "--index"], stderr=subprocess.DEVNULL)
+    return path
+
+
+def split_regions(region):      # parse_regions_duckdb (src/bcf_reader.c:286-329)
+    return [t.strip(" \t") for t in region.split(",") if t.strip(" \t")]
+
+
+@pytest.mark.skipif(not (os.path.exists(HOST) and os.path.exists(REF_EXT) and os.path.exists(GEN)), reason="prebuilt reference extension / generator absent")
+def test_bcf_oracle_region_queries_match_live_reference(tmp_path):
+    """read_bcf(region := ...) through the CSI index: chained single-region iterators, duplicates kept, unknown contigs skipped."""
+    path = indexed_bcf(tmp_path)
+    u = inflated(path)
+    full = subprocess.run([HOST, REF_EXT, "read_bcf", path, "--cols", "0,1,3"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL).stdout.decode().split("\n")[1:-1]
+    # a record with a multi-base REF: queried by its last base only (pos + rlen > beg), and just past it
+    chrom, pos, ref = next(r.split("\t") for r in full if len(r.split("\t")[2]) > 2)
+    last = int(pos) + len(ref) - 1
+    extra = ["%s:%d-%d" % (chrom, last, last), "%s:%d-%d" % (chrom, last + 1, last + 1)]
+    for region in BCF_REGIONS + extra:
+        for tidy in (False, True):
+            args = ["region=" + region] + (["tidy_format=true"] if tidy else [])
+            ref_out = subprocess.run([HOST, REF_EXT, "read_bcf", path, *args, "--dump"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL).stdout.decode("utf-8", "replace").split("\n")[:-1]
+            got, status = bcf_oracle.scan(u, tidy, regions=split_regions(region))
+            assert status == 0 and got == ref_out, (region, tidy)
+    assert len(bcf_oracle.scan(u, False, regions=[extra[0]])[0]) >= 2
