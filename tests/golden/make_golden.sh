@@ -50,6 +50,7 @@ $D dumpcontigs range.bam $TAGS > range.contigs.tsv
 # fake DuckDB host prints every cell; the files are the reference's own fixture and a small seeded --edge file.
 H=../../harness/_bin/fake_duckdb; RX=../../oracle/_ref/libduckhts_ref.so
 cp $REF/test/data/vcf_file.bcf vcf_file.bcf; chmod u+w vcf_file.bcf
+cp $REF/test/data/vcf_file.bcf.csi vcf_file.bcf.csi; chmod u+w vcf_file.bcf.csi   # the index the reference's region tests use (test/sql/duckhts.test:86-105)
 ../../harness/_bin/gen_bcf edge_small.bcf 60 5 0x51 --edge --contigs 3
 ../../harness/_bin/gen_bcf plain_small.bcf 40 9 0x52 --contigs 2
 for f in vcf_file edge_small plain_small; do

@@ -157,3 +157,19 @@ def test_read_bcf_region_queries_match_oracle(ctx, tmp_path):
             exp, est = bcf_oracle.scan(infl.tobytes(), tidy, regions=regs)
             got, status, _ = bcf.rows_text(ctx, img, tidy=tidy, index=csi, regions=regs, **kw)
             assert status == est == 0 and got == exp, (region, tidy, first_diff(got, exp))
+
+
+def test_reference_sqllogictest_region_answers(ctx):
+    """test/sql/duckhts.test:86-105 on the reference's own vcf_file.bcf + .csi (test/data, bcftools index)."""
+    from duckhts_b200 import bcf
+    img = np.fromfile(os.path.join(GOLD, "vcf_file.bcf"), dtype=np.uint8)
+    csi = np.fromfile(os.path.join(GOLD, "vcf_file.bcf.csi"), dtype=np.uint8)
+    n = lambda regs: len(bcf.rows_text(ctx, img, tidy=False, index=csi, regions=regs)[0]) - 1
+    assert n(["1:3000150-3000151"]) == 2
+    assert n(["1:3000150-3000151", "1:3062915-3062915"]) == n(["1:3000150-3000151"]) + n(["1:3062915-3062915"]) > 2
+    from oracle import bcf_oracle
+    (_, _), infl = oracle_lines(img, False)
+    for regs in (["1"], ["2", "1:3062915-3062915"], ["4:3258448-"], ["X"], ["20"]):
+        exp, _ = bcf_oracle.scan(infl.tobytes(), True, regions=regs)
+        got, status, _ = bcf.rows_text(ctx, img, tidy=True, index=csi, regions=regs)
+        assert status == 0 and got == exp, (regs, first_diff(got, exp))

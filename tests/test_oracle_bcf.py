@@ -39,6 +39,14 @@ def test_known_answers_of_duckhts_sqllogictest_bcf():
     assert got[1].split("\t")[:5] == ["1", "3000150", "\\N", "C", "[T]"]
 
 
+def test_known_answers_of_duckhts_sqllogictest_bcf_regions():
+    """test/sql/duckhts.test:86-105: region := '1:3000150-3000151' has 2 records; a comma-separated list is the sum of its parts."""
+    u = inflated(os.path.join(util.GOLDEN, "vcf_file.bcf"))
+    n = lambda regs: len(bcf_oracle.scan(u, False, regions=regs)[0]) - 1
+    assert n(["1:3000150-3000151"]) == 2
+    assert n(["1:3000150-3000151", "1:3062915-3062915"]) == n(["1:3000150-3000151"]) + n(["1:3062915-3062915"]) > 2
+
+
 @pytest.mark.skipif(not (os.path.exists(HOST) and os.path.exists(REF_EXT) and os.path.exists(GEN)), reason="prebuilt reference extension / generator absent")
 @pytest.mark.parametrize("n_sites,n_samples,seed", [(400, 12, 0x81), (150, 0, 0x82), (60, 120, 0x83)])
 def test_bcf_oracle_matches_live_reference_on_synthetic(n_sites, n_samples, seed, tmp_path):
