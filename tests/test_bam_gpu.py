@@ -1,5 +1,6 @@
 """Parity of the read_bam scan (BGZF inflate -> boundary walk -> columnar decode, through the C-ABI) against the
 oracle's restatement of bam_read1 + bam_read_function.  Bit-exact: values, row order, NULLs, stop-on-error."""
+import os
 import struct
 
 import numpy as np
@@ -101,6 +102,15 @@ def test_auxiliary_tags_map(ctx):
     for block in (0xff00, 333):
         map_both(ctx, util.make_bgzf(stream, block=block), (), batch_rows=5)
         map_both(ctx, util.make_bgzf(stream, block=block), orc.STD_TAGS, batch_rows=5)
+
+
+def test_reference_sqllogictest_standard_and_auxiliary_tags(ctx):
+    """test/sql/duckhts.test:180-185: RG, NM, map_extract(AUXILIARY_TAGS, 'XZ') of aux_tags, standard_tags + auxiliary_tags -> x1, 2, [foo]."""
+    img = np.fromfile(os.path.join(util.GOLDEN, "aux_tags.bam"), dtype=np.uint8)
+    got = dh.bam_scan(ctx, img, tags=[(b"RG", "Z"), (b"NM", "i")], aux_map=orc.STD_TAGS)
+    assert got["tags"][0]["s"][0] == b"x1" and got["tags"][1]["i"][0] == 2
+    assert [v for k, v in got["aux_map"][0] if k == b"XZ"] == [b"foo"]
+    assert all(k.decode() not in orc.STD_TAGS for k, _ in got["aux_map"][0])
 
 
 def test_auxiliary_tags_float_text_is_printf_g(ctx):
