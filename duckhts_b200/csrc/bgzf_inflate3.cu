@@ -112,7 +112,26 @@ struct Bits {
         bitpos = (uint32_t)((uintptr_t)payload & 15u) * 8u;
         while (bitpos >= 32u) advance();
     }
-    __device__ __forceinline__ void normalize() { if (bitpos >= 32u) advance(); }
+    // Branch-free form of `if (bitpos >= 32) advance()` for the symbol loop.  ncu (r1h) showed the two refill blocks of a step
+    // as 27 % of its instructions with 5-9 of 32 lanes active: some lane crosses a word in almost every step, so the warp
+    // paid for the divergent block anyway.  Here every lane loads its next ring word and selects; the refill of the ring
+    // (one 16-byte cp.async per four words) and its commit are predicated instructions, and wait_group 1 runs every time
+    // (it only ever has to wait for the chunk that is about to be read).
+    __device__ __forceinline__ void normalize() {
+        const bool adv = bitpos >= 32u;
+        const uint32_t c = wi >> 2, k = wi & 3u;
+        const uint32_t slot = ring + ((c & 1u) << 9);
+        cp_async_wait1();
+        const uint32_t nw = lds32(slot + (k << 2));
+        const uint32_t issue = (adv && k == 3u) ? 1u : 0u;
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p cp.async.cg.shared.global [%1], [%2], 16;\n\t@p cp.async.commit_group;\n\t}"
+                     ::"r"(issue), "r"(slot), "l"(g + ((size_t)(c + 2u) << 4)) : "memory");
+        w0 = adv ? w1 : w0;
+        w1 = adv ? w2 : w1;
+        w2 = adv ? nw : w2;
+        bitpos -= adv ? 32u : 0u;
+        wi += adv ? 1u : 0u;
+    }
     __device__ __forceinline__ uint32_t window() const { return __funnelshift_r(w0, w1, bitpos); }  // next 32 bits
     // header-path helpers (n <= 25)
     __device__ __forceinline__ uint32_t take(uint32_t n) {
