@@ -33,19 +33,42 @@
 namespace dh {
 namespace v3 {
 
-constexpr int WARPS = 4;
-constexpr int THREADS = WARPS * 32;
-constexpr int LROOT = 8, DROOT = 7;
-constexpr int LIT_N = 660;          // worst case for 286 symbols, root 8, max length 15
-constexpr int DIST_N = 232;         // capacity; worst case for 30 symbols, root 7 is 400 -> fallback above DIST_N
-constexpr int TAB_N = LIT_N + DIST_N;
-constexpr int SCR_LENS = LIT_N;           // litlen build: code lengths, two per entry, in the distance region [0,158)
-constexpr int SCR_NC = LIT_N + 160;       // litlen build: next_code[16] in the distance region [160,176)
+#ifndef DH_P1_WARPS
+#define DH_P1_WARPS 6
+#endif
+#ifndef DH_LROOT
+#define DH_LROOT 7
+#endif
+#ifndef DH_DROOT
+#define DH_DROOT 6
+#endif
+constexpr int LROOT = DH_LROOT, DROOT = DH_DROOT;
 constexpr unsigned FULL = 0xffffffffu;
-
-// per warp: tables [TAB_N][32] u16, then the input ring [2 chunks][32 lanes][16 bytes]
-constexpr int WARP_SMEM = TAB_N * 64 + 2 * 512;
-static_assert(WARP_SMEM * WARPS == 232448, "phase 1 is sized to fill the 227 KB of one SM exactly");
+// One pool of TAB_N u16 entries per stream: the literal/length table (root 7 + sub-tables) at [0, L), the distance table
+// (root 6 + sub-tables) right behind it at [L, L + D).  The second-level lookup of a step is always issued, so small roots cost
+// no instructions; they make the tables smaller and the root fill of the header pass shorter.  zlib level-6 BAM blocks measure
+// L <= 470 and L + D <= 602 (median 546, p99 578) at roots 7/6, BCF genotype blocks L + D <= 508 (worst cases: L = 660 at root 8,
+// D = 400 at root 7).  The kernel is bound by the issue latency of one dependent chain per warp (ncu: 25 % issue slots busy with
+// 4 warps per SM), so more warps per SM is the lever and the pool size decides how many fit into the 227 KB of an SM:
+//   W = 4: 892 entries (every BAM/BCF stream seen fits), W = 6: 589 entries (~1 % of the BAM blocks do not fit).
+// The main pass runs P1<DH_P1_WARPS>; a lane whose tables do not fit queues its block, and a second launch of the same kernel as
+// P1<4> redoes the queued blocks (a fraction of one wave).  What still does not fit there is flagged INF_NEEDS_V1 and redone by
+// the lane-group kernel (bgzf_inflate.cu), as before.
+template <int W>
+struct P1 {
+    static constexpr int WARPS = W, THREADS = W * 32;
+    static constexpr int TAB_N = (232448 / THREADS - 32) / 2;
+    static constexpr int SCR_N = 96;                 // build scratch at the end of the pool (free again before the distance table is built)
+    static constexpr int SCR_LENS = TAB_N - SCR_N;   // litlen + distance code lengths, FOUR per entry (<= 316 lengths = 79 entries)
+    static constexpr int SCR_NC = TAB_N - 16;        // next_code[16]
+    // the literal/length table may not reach the scratch while it is being built; link entries carry a 9-bit sub-table offset
+    static constexpr int LIT_CAP = TAB_N - SCR_N < (1 << LROOT) + 512 ? TAB_N - SCR_N : (1 << LROOT) + 512;
+    // per warp: tables [TAB_N][32] u16, then the input ring [2 chunks][32 lanes][16 bytes]
+    static constexpr int WARP_SMEM = TAB_N * 64 + 2 * 512;
+    static_assert(WARP_SMEM * WARPS <= 232448, "phase 1 is sized to fill the 227 KB of one SM");
+};
+using P1Main = P1<DH_P1_WARPS>;
+using P1Retry = P1<4>;
 
 // ---- table entries (u16) ---------------------------------------------------------------------------------
 // litlen:  bit15 = 1: length code   [14:12] extra bits  [11:4] base-3  [3:0] code length
@@ -148,6 +171,7 @@ struct Bits {
 struct Lane {
     Bits in;
     uint32_t tab;         // shared address of this lane's column: entry i at tab + i * 64
+    uint32_t dbase;       // entry index of the distance root table (= size of the literal/length table)
     uint8_t *lit;         // literal stream (grows upwards, 4 bytes per store)
     uint32_t *cmd_top;    // command k is stored at cmd_top[-k]
     uint32_t lit_acc, nlit, ncmd, lit_run, pos, isize;
@@ -180,6 +204,14 @@ struct Counts {
         c2 += q == 2 ? one : 0ull;
         c3 += q == 3 ? one : 0ull;
     }
+    __device__ __forceinline__ void addv(uint32_t l, uint32_t v) {
+        const uint64_t val = (uint64_t)v << ((l & 3u) * 16u);
+        const uint32_t q = l >> 2;
+        c0 += q == 0 ? val : 0ull;
+        c1 += q == 1 ? val : 0ull;
+        c2 += q == 2 ? val : 0ull;
+        c3 += q == 3 ? val : 0ull;
+    }
     __device__ __forceinline__ uint32_t get(int l) const {
         const int q = l >> 2;
         const uint64_t w = q == 0 ? c0 : q == 1 ? c1 : q == 2 ? c2 : c3;
@@ -207,7 +239,7 @@ __device__ __forceinline__ int check_lengths(const Counts &c, int err, int &maxl
 // mark(p, bits) / finish(p) -> stores; shared by both builds through lambdas on the code ranges.
 template <typename FirstFn>
 __device__ __forceinline__ int layout_subtables(const Lane &s, const Counts &c, const int base, const int root, const int cap,
-                                                const int maxlen, const uint32_t link_kind, FirstFn first_code) {
+                                                const int maxlen, const uint32_t link_kind, int &used, FirstFn first_code) {
     const int nroot = 1 << root;
     int p_first = nroot;
     for (int l = root + 1; l <= maxlen; ++l) {
@@ -227,6 +259,7 @@ __device__ __forceinline__ int layout_subtables(const Lane &s, const Counts &c, 
         if (next_free > cap) return INF_NEEDS_V1;
         tput(s, ri, link_kind | ((uint32_t)(off - nroot) << 4) | bits);
     }
+    used = next_free;
     return INF_OK;
 }
 
@@ -244,152 +277,216 @@ __device__ __forceinline__ void place_code(const Lane &s, const int base, const 
     }
 }
 
-// literal/length table from the n code lengths parked (two per entry) at SCR_LENS
-__device__ __forceinline__ uint32_t parked_len(const Lane &s, uint32_t j) { return (tget(s, SCR_LENS + (j >> 1)) >> (8u * (j & 1u))) & 255u; }
+// ---- table builds: every lane of `hm` (the lanes that are at a deflate block header) goes through them together ----
+// ncu source page (profiles/r1j): the header code ran with 3-7 of 32 threads per instruction.  The lanes enter it together but
+// drift apart in the code-length loop and, with error returns inside the loops, the compiler only reconverged them at the end
+// of the header.  Now nothing returns early: a lane that failed (or holds a stored block) carries n = 0 through the builds,
+// the symbol loops have constant trip counts, and __syncwarp(hm) closes every iteration, so the replication loops of
+// place_code run side by side.
+template <class K>
+__device__ __forceinline__ uint32_t parked_len(const Lane &s, uint32_t j) { return (tget(s, K::SCR_LENS + (j >> 2)) >> (4u * (j & 3u))) & 15u; }
 
-__device__ __forceinline__ int build_litlen(const Lane &s, const int n) {
+// literal/length table from the n code lengths parked (four per entry) at K::SCR_LENS; `used` = entries it occupies
+template <class K>
+__device__ __forceinline__ int build_litlen(const Lane &s, const unsigned hm, const int n, int &used) {
     Counts c;
-    for (int j = 0; j < n; ++j) c.add(parked_len(s, (uint32_t)j));
+    for (int j = 0; j < 288; j += 4) {
+        const uint32_t w = tget(s, K::SCR_LENS + (j >> 2));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) c.add(j + q < n ? (w >> (4 * q)) & 15u : 0u);
+    }
     c.c0 &= ~0xffffull;  // length 0 = unused symbol
     int maxlen, left;
     int rc = check_lengths(c, INF_ERR_LITLEN_SET, maxlen, left);
-    if (rc != INF_OK) return rc;
-    uint32_t code = 0;
+    used = 1 << LROOT;
+    bool ok = rc == INF_OK && n > 0;
+    if (ok) {
+        uint32_t code = 0;
 #pragma unroll
-    for (int l = 1; l <= 15; ++l) {                 // next_code[l]: first canonical code of length l
-        tput(s, SCR_NC + l, code);
-        code = (code + c.get(l)) << 1;
+        for (int l = 1; l <= 15; ++l) {                 // next_code[l]: first canonical code of length l
+            tput(s, K::SCR_NC + l, code);
+            code = (code + c.get(l)) << 1;
+        }
+        if (left > 0 || maxlen == 0)
+            for (int k = 0; k < (1 << LROOT); ++k) tput(s, k, LIT_BAD);
+        if (maxlen > LROOT) {
+            rc = layout_subtables(s, c, 0, LROOT, K::LIT_CAP, maxlen, 2u << 13, used, [&](int l) -> uint32_t { return tget(s, K::SCR_NC + l); });
+            ok = rc == INF_OK;
+        }
     }
-    if (left > 0 || maxlen == 0)
-        for (int k = 0; k < (1 << LROOT); ++k) tput(s, k, LIT_BAD);
-    if (maxlen > LROOT) {
-        rc = layout_subtables(s, c, 0, LROOT, LIT_N, maxlen, 2u << 13, [&](int l) -> uint32_t { return tget(s, SCR_NC + l); });
-        if (rc != INF_OK) return rc;
+    __syncwarp(hm);
+    const int m = ok ? n : 0;
+    for (int j = 0; j < 288; j += 4) {
+        const uint32_t w = tget(s, K::SCR_LENS + (j >> 2));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t l = j + q < m ? (w >> (4 * q)) & 15u : 0u;
+            if (l) {
+                const uint32_t cd = tget(s, K::SCR_NC + l);
+                tput(s, K::SCR_NC + l, cd + 1u);
+                place_code(s, 0, LROOT, cd, l, lit_entry((uint32_t)(j + q), l));
+            }
+            __syncwarp(hm);
+        }
     }
-    for (int j = 0; j < n; ++j) {
-        const uint32_t l = parked_len(s, (uint32_t)j);
-        if (!l) continue;
-        const uint32_t cd = tget(s, SCR_NC + l);
-        tput(s, SCR_NC + l, cd + 1u);
-        place_code(s, 0, LROOT, cd, l, lit_entry((uint32_t)j, l));
+    return rc;
+}
+
+// distance table at [base, K::TAB_N) from n <= 32 code lengths held as nibbles in four registers; needs no scratch
+template <class K>
+__device__ __forceinline__ int build_dist(const Lane &s, const unsigned hm, const int base, const int n, const uint32_t d0,
+                                       const uint32_t d1, const uint32_t d2, const uint32_t d3) {
+    auto nib = [&](int j) -> uint32_t { const uint32_t w = j < 8 ? d0 : j < 16 ? d1 : j < 24 ? d2 : d3; return (w >> (4 * (j & 7))) & 15u; };
+    int rc = (n > 0 && base + (1 << DROOT) > K::TAB_N) ? INF_NEEDS_V1 : INF_OK;
+    Counts c;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) c.add(j < n ? nib(j) : 0u);
+    c.c0 &= ~0xffffull;
+    int maxlen = 0, left = 0;
+    if (rc == INF_OK) rc = check_lengths(c, INF_ERR_DIST_SET, maxlen, left);
+    bool ok = rc == INF_OK && n > 0;
+    Counts nc;                                          // next canonical code of every length, 16-bit fields like the counts
+    if (ok) {
+        if (left > 0 || maxlen == 0)
+            for (int k = 0; k < (1 << DROOT); ++k) tput(s, base + k, DIST_BAD);
+        if (maxlen > DROOT) {
+            int used;
+            const int room = K::TAB_N - base, cap = room < (1 << DROOT) + 512 ? room : (1 << DROOT) + 512;
+            rc = layout_subtables(s, c, base, DROOT, cap, maxlen, 2u << 14, used, [&](int l) -> uint32_t {
+                uint32_t code = 0;
+                for (int q = 1; q < l; ++q) code = (code + c.get(q)) << 1;
+                return code;
+            });
+            ok = rc == INF_OK;
+        }
+        uint32_t code = 0;
+#pragma unroll
+        for (int l = 1; l <= 15; ++l) {
+            nc.addv((uint32_t)l, code);
+            code = (code + c.get(l)) << 1;
+        }
     }
+    __syncwarp(hm);
+    const int m = ok ? n : 0;
+#pragma unroll 4
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t l = j < m ? nib(j) : 0u;
+        if (l) {
+            const uint32_t cd = nc.get((int)l);
+            nc.add(l);
+            place_code(s, base, DROOT, cd, l, dist_entry((uint32_t)j, l));
+        }
+        __syncwarp(hm);
+    }
+    return rc;
+}
+
+// ---- deflate block header (RFC 1951 3.2.3-3.2.7) ------------------------------------------------------------------------
+// stored block: LEN/NLEN, then the bytes go through the literal path
+__device__ __forceinline__ int copy_stored(Lane &s) {
+    s.in.bitpos = (s.in.bitpos + 7u) & ~7u;            // LEN/NLEN start at the next byte boundary
+    const uint32_t len = s.in.take(16), nlen = s.in.take(16);
+    if ((len ^ 0xffffu) != nlen) return INF_ERR_STORED_LEN;
+    if (s.pos + len > s.isize) return INF_ERR_ISIZE;
+    if (s.in.consumed() + 8u * len > s.end_bits) return INF_ERR_IN_OVERRUN;
+    for (uint32_t i = 0; i < len; ++i) put_literal(s, s.in.take(8));
     return INF_OK;
 }
 
-// distance table from n <= 32 code lengths held as nibbles in four registers; needs no scratch
-__device__ __forceinline__ int build_dist(const Lane &s, const int n, const uint32_t d0, const uint32_t d1, const uint32_t d2,
-                                       const uint32_t d3) {
-    auto nib = [&](int j) -> uint32_t { const uint32_t w = j < 8 ? d0 : j < 16 ? d1 : j < 24 ? d2 : d3; return (w >> (4 * (j & 7))) & 15u; };
-    Counts c;
-    for (int j = 0; j < n; ++j) c.add(nib(j));
-    c.c0 &= ~0xffffull;
-    int maxlen, left;
-    int rc = check_lengths(c, INF_ERR_DIST_SET, maxlen, left);
-    if (rc != INF_OK) return rc;
-    if (left > 0 || maxlen == 0)
-        for (int k = 0; k < (1 << DROOT); ++k) tput(s, LIT_N + k, DIST_BAD);
-    if (maxlen > DROOT) {
-        rc = layout_subtables(s, c, LIT_N, DROOT, DIST_N, maxlen, 2u << 14, [&](int l) -> uint32_t {
-            uint32_t code = 0;
-            for (int q = 1; q < l; ++q) code = (code + c.get(q)) << 1;
-            return code;
-        });
-        if (rc != INF_OK) return rc;
+// dynamic block: HLIT/HDIST/HCLEN, the code-length code, then the litlen + distance code lengths parked at K::SCR_LENS
+// (distance lengths also returned as nibbles in d0..d3).  Per-lane control flow; the lanes meet again behind it.
+template <class K>
+__device__ __forceinline__ int read_code_lengths(Lane &s, uint32_t &hlit, uint32_t &hdist, uint32_t &d0, uint32_t &d1, uint32_t &d2,
+                                                 uint32_t &d3) {
+    hlit = s.in.take(5) + 257u;
+    hdist = s.in.take(5) + 1u;
+    const uint32_t hclen = s.in.take(4) + 4u;
+    if (hlit > 286u || hdist > 30u) return INF_ERR_TOO_MANY_SYMS;
+    // code-length code: 19 x 3 bits, kept in one register
+    uint64_t pl = 0;
+    for (uint32_t i = 0; i < hclen; ++i) pl |= (uint64_t)s.in.take(3) << (3u * precode_order(i));
+    {
+        Counts c;
+        for (int sym = 0; sym < 19; ++sym) c.add((uint32_t)(pl >> (3 * sym)) & 7u);
+        c.c0 &= ~0xffffull;
+        int left = 1;
+#pragma unroll
+        for (int q = 1; q < 8; ++q) { left = (left << 1) - (int)c.get(q); if (left < 0) return INF_ERR_PRECODE; }
+        if (left > 0) return INF_ERR_PRECODE;   // an incomplete code-length code is never allowed (zlib CODES rule)
     }
+    // 7-bit direct table in litlen-region slots [0,128): entry = sym << 4 | len
     uint32_t code = 0;
-    for (int l = 1; l <= maxlen; ++l) {
-        if (c.get(l))
-            for (int j = 0; j < n; ++j)
-                if (nib(j) == (uint32_t)l) place_code(s, LIT_N, DROOT, code++, (uint32_t)l, dist_entry((uint32_t)j, (uint32_t)l));
+    for (uint32_t l = 1; l < 8u; ++l) {
+        for (uint32_t sym = 0; sym < 19u; ++sym) {
+            if (((uint32_t)(pl >> (3u * sym)) & 7u) != l) continue;
+            const uint32_t rev = __brev(code) >> (32u - l);
+            for (uint32_t k = rev; k < 128u; k += 1u << l) tput(s, k, (sym << 4) | l);
+            ++code;
+        }
         code <<= 1;
     }
+    // litlen + distance code lengths, parked four per entry
+    const uint32_t n = hlit + hdist;
+    uint32_t i = 0, prev = 0, pend = 0;
+    auto put_len = [&](uint32_t idx, uint32_t v) {
+        pend |= v << (4u * (idx & 3u));
+        if ((idx & 3u) == 3u) { tput(s, K::SCR_LENS + (idx >> 2), pend); pend = 0u; }
+    };
+    while (i < n) {
+        s.in.normalize();
+        const uint32_t e = tget(s, s.in.window() & 127u);
+        s.in.bitpos += e & 15u;
+        const uint32_t sym = e >> 4;
+        if (sym < 16u) { put_len(i, sym); prev = sym; ++i; continue; }
+        uint32_t rep, val;
+        if (sym == 16u) { if (i == 0u) return INF_ERR_LENS_REPEAT; rep = 3u + s.in.take(2); val = prev; }
+        else if (sym == 17u) { rep = 3u + s.in.take(3); val = 0u; }
+        else { rep = 11u + s.in.take(7); val = 0u; }
+        if (i + rep > n) return INF_ERR_LENS_REPEAT;
+        for (uint32_t k = 0; k < rep; ++k) put_len(i + k, val);
+        i += rep;
+        prev = val;
+    }
+    if (n & 3u) tput(s, K::SCR_LENS + (n >> 2), pend);
+    if (s.in.consumed() > s.end_bits) return INF_ERR_IN_OVERRUN;
+    if (parked_len<K>(s, 256u) == 0u) return INF_ERR_NO_EOB;
+    d0 = d1 = d2 = d3 = 0u;
+    for (uint32_t k = 0; k < hdist; ++k) {
+        const uint32_t v = parked_len<K>(s, hlit + k) << (4u * (k & 7u)), q = k >> 3;
+        d0 |= q == 0u ? v : 0u; d1 |= q == 1u ? v : 0u; d2 |= q == 2u ? v : 0u; d3 |= q == 3u ? v : 0u;
+    }
     return INF_OK;
 }
 
-// ---- deflate block header (RFC 1951 3.2.3-3.2.7): returns INF_OK with tables built, or an error / INF_NEEDS_V1 -----
-// stored blocks are copied through the literal path here and return with *stored = true
-__device__ __forceinline__ int read_block_header(Lane &s, uint32_t &bfinal, bool &stored) {
+// returns INF_OK with tables built (or, *stored = true, with a stored block copied), or an error / INF_NEEDS_V1.
+// Called by all lanes of `hm` together; nothing in it returns before the last line.
+template <class K>
+__device__ __forceinline__ int read_block_header(Lane &s, const unsigned hm, uint32_t &bfinal, bool &stored) {
+    int rc = INF_OK;
     stored = false;
     bfinal = s.in.take(1);
     const uint32_t btype = s.in.take(2);
-    if (btype == 3u) return INF_ERR_BTYPE;
-    if (btype == 0u) {
-        stored = true;
-        s.in.bitpos = (s.in.bitpos + 7u) & ~7u;        // LEN/NLEN start at the next byte boundary
-        const uint32_t len = s.in.take(16), nlen = s.in.take(16);
-        if ((len ^ 0xffffu) != nlen) return INF_ERR_STORED_LEN;
-        if (s.pos + len > s.isize) return INF_ERR_ISIZE;
-        if (s.in.consumed() + 8u * len > s.end_bits) return INF_ERR_IN_OVERRUN;
-        for (uint32_t i = 0; i < len; ++i) put_literal(s, s.in.take(8));
-        return INF_OK;
-    }
     uint32_t hlit = 288u, hdist = 32u;
     uint32_t d0 = 0x55555555u, d1 = 0x55555555u, d2 = 0x55555555u, d3 = 0x55555555u;  // fixed code: 32 distance codes of 5 bits
-    if (btype == 1u) {
+    if (btype == 3u) rc = INF_ERR_BTYPE;
+    else if (btype == 0u) { stored = true; rc = copy_stored(s); }
+    else if (btype == 1u) {
         // fixed Huffman code (RFC 1951 3.2.6): lengths parked where the dynamic path would put them
-        for (uint32_t j = 0; j < 288u; j += 2u) {
+        for (uint32_t j = 0; j < 288u; j += 4u) {
             const uint32_t l = j < 144u ? 8u : j < 256u ? 9u : j < 280u ? 7u : 8u;
-            tput(s, SCR_LENS + (j >> 1), l | (l << 8));
+            tput(s, K::SCR_LENS + (j >> 2), l * 0x1111u);
         }
-    } else {
-        hlit = s.in.take(5) + 257u;
-        hdist = s.in.take(5) + 1u;
-        const uint32_t hclen = s.in.take(4) + 4u;
-        if (hlit > 286u || hdist > 30u) return INF_ERR_TOO_MANY_SYMS;
-        // code-length code: 19 x 3 bits, kept in one register
-        uint64_t pl = 0;
-        for (uint32_t i = 0; i < hclen; ++i) pl |= (uint64_t)s.in.take(3) << (3u * precode_order(i));
-        {
-            Counts c;
-            for (int sym = 0; sym < 19; ++sym) c.add((uint32_t)(pl >> (3 * sym)) & 7u);
-            c.c0 &= ~0xffffull;
-            int left = 1;
-#pragma unroll
-            for (int q = 1; q < 8; ++q) { left = (left << 1) - (int)c.get(q); if (left < 0) return INF_ERR_PRECODE; }
-            if (left > 0) return INF_ERR_PRECODE;   // an incomplete code-length code is never allowed (zlib CODES rule)
-        }
-        // 7-bit direct table in litlen-region slots [0,128): entry = sym << 4 | len
-        uint32_t code = 0;
-        for (uint32_t l = 1; l < 8u; ++l) {
-            for (uint32_t sym = 0; sym < 19u; ++sym) {
-                if (((uint32_t)(pl >> (3u * sym)) & 7u) != l) continue;
-                const uint32_t rev = __brev(code) >> (32u - l);
-                for (uint32_t k = rev; k < 128u; k += 1u << l) tput(s, k, (sym << 4) | l);
-                ++code;
-            }
-            code <<= 1;
-        }
-        // litlen + distance code lengths, parked two per entry
-        const uint32_t n = hlit + hdist;
-        uint32_t i = 0, prev = 0, pend = 0;
-        auto put_len = [&](uint32_t idx, uint32_t v) { if (idx & 1u) tput(s, SCR_LENS + (idx >> 1), pend | (v << 8)); else pend = v; };
-        while (i < n) {
-            s.in.normalize();
-            const uint32_t e = tget(s, s.in.window() & 127u);
-            s.in.bitpos += e & 15u;
-            const uint32_t sym = e >> 4;
-            if (sym < 16u) { put_len(i, sym); prev = sym; ++i; continue; }
-            uint32_t rep, val;
-            if (sym == 16u) { if (i == 0u) return INF_ERR_LENS_REPEAT; rep = 3u + s.in.take(2); val = prev; }
-            else if (sym == 17u) { rep = 3u + s.in.take(3); val = 0u; }
-            else { rep = 11u + s.in.take(7); val = 0u; }
-            if (i + rep > n) return INF_ERR_LENS_REPEAT;
-            for (uint32_t k = 0; k < rep; ++k) put_len(i + k, val);
-            i += rep;
-            prev = val;
-        }
-        if (n & 1u) tput(s, SCR_LENS + (n >> 1), pend);
-        if (s.in.consumed() > s.end_bits) return INF_ERR_IN_OVERRUN;
-        if (parked_len(s, 256u) == 0u) return INF_ERR_NO_EOB;
-        d0 = d1 = d2 = d3 = 0u;
-        for (uint32_t k = 0; k < hdist; ++k) {
-            const uint32_t v = parked_len(s, hlit + k) << (4u * (k & 7u)), q = k >> 3;
-            d0 |= q == 0u ? v : 0u; d1 |= q == 1u ? v : 0u; d2 |= q == 2u ? v : 0u; d3 |= q == 3u ? v : 0u;
-        }
-    }
-    int rc = build_litlen(s, (int)hlit);
-    if (rc != INF_OK) return rc;
-    return build_dist(s, (int)hdist, d0, d1, d2, d3);
+    } else rc = read_code_lengths<K>(s, hlit, hdist, d0, d1, d2, d3);
+    __syncwarp(hm);
+    const bool want = rc == INF_OK && !stored;
+    int lit_used;
+    const int rl = build_litlen<K>(s, hm, want ? (int)hlit : 0, lit_used);
+    if (want && rl != INF_OK) rc = rl;
+    const bool want_d = want && rl == INF_OK;
+    s.dbase = (uint32_t)lit_used;
+    const int rd = build_dist<K>(s, hm, lit_used, want_d ? (int)hdist : 0, d0, d1, d2, d3);
+    if (want_d && rd != INF_OK) rc = rd;
+    return rc;
 }
 
 }  // namespace v3
@@ -401,24 +498,30 @@ using namespace v3;
 // =========================================================================================================
 // commands (32 bits):  [31]=0 match:   [30:23] literals since the previous command (0..254)  [22:15] length-3  [14:0] distance-1
 //                      [31]=1 literals: [30:0] run of literals with no match behind it (255 inside a run, or the tail)
-__global__ void __launch_bounds__(THREADS, 1)
+// `retry` = {count, ticket} + the queue of block indices behind it.  RETRY = false: the main pass over blocks [0, nblocks); a lane whose
+// tables do not fit appends its block to the queue.  RETRY = true: the pass over the queued blocks with the larger pool.
+template <class K, bool RETRY>
+__global__ void __launch_bounds__(K::THREADS, 1)
 bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, uint32_t nblocks,
                     int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
-                    unsigned int *__restrict__ counter) {
+                    unsigned int *__restrict__ counter, unsigned int *__restrict__ retry) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t warp_base = (uint32_t)__cvta_generic_to_shared(smem_raw) + warp * (uint32_t)WARP_SMEM;
+    const uint32_t warp_base = (uint32_t)__cvta_generic_to_shared(smem_raw) + warp * (uint32_t)K::WARP_SMEM;
     enum { ST_HEADER = 0, ST_RUN = 1, ST_DONE = 2 };
 
     for (;;) {
         // ---- a generation: 32 consecutive blocks, one per lane ----
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(counter, 32u);
+        if (lane == 0) base = atomicAdd(RETRY ? retry + 1 : counter, 32u);
         base = __shfl_sync(FULL, base, 0);
-        if (base >= nblocks) break;
-        const uint32_t b = base + lane;
+        const uint32_t nwork = RETRY ? *reinterpret_cast<volatile unsigned int *>(retry) : nblocks;
+        if (base >= nwork) break;
+        uint32_t b = nblocks;
+        if (base + lane < nwork) b = RETRY ? retry[2u + base + lane] : base + lane;
         Lane s;
         s.tab = warp_base + lane * 2u;
+        s.dbase = 1u << LROOT;
         s.status = INF_OK;
         s.lit_acc = s.nlit = s.ncmd = s.lit_run = s.pos = s.isize = 0u;
         s.end_bits = 0u;
@@ -432,7 +535,7 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
             s.isize = d.isize;
             s.lit = work + d.cmd_off;
             s.cmd_top = reinterpret_cast<uint32_t *>(work + d.cmd_off + inflate_work_cap(d.isize)) - 1;
-            s.in.open(comp + d.in_off, warp_base + (uint32_t)TAB_N * 64u + lane * 16u);
+            s.in.open(comp + d.in_off, warp_base + (uint32_t)K::TAB_N * 64u + lane * 16u);
             const uint32_t mis = (uint32_t)((uintptr_t)(comp + d.in_off) & 15u);
             s.end_bits = (mis + d.in_len) * 8u;
             s.wi_limit = ((mis + d.in_len + 3u) >> 2) + 8u;
@@ -450,9 +553,10 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
 
         while (__any_sync(FULL, st != ST_DONE)) {
             // ---------------- deflate block headers (in lock-step for zlib-made streams) ----------------
+            const unsigned hm = __ballot_sync(FULL, st == ST_HEADER);
             if (st == ST_HEADER) {
                 bool stored;
-                const int rc = read_block_header(s, bfinal, stored);
+                const int rc = read_block_header<K>(s, hm, bfinal, stored);
                 if (rc != INF_OK) fail(rc);
                 else if (!stored) st = ST_RUN;
                 else if (bfinal) finish();
@@ -466,10 +570,10 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
                     if (st == ST_RUN) {
                         s.in.normalize();
                         uint32_t bits = s.in.window();
-                        e = tget(s, bits & 255u);
+                        e = tget(s, bits & ((1u << LROOT) - 1u));
                         {   // second level: always issued, so that the step is straight-line code
                             const bool link = (e >> 13) == 2u;
-                            const uint32_t sub = 256u + ((e >> 4) & 511u) + ((bits >> 8) & ((1u << (e & 15u)) - 1u));
+                            const uint32_t sub = (1u << LROOT) + ((e >> 4) & 511u) + ((bits >> LROOT) & ((1u << (e & 15u)) - 1u));
                             const uint32_t e2 = tget(s, link ? sub : 0u);
                             e = link ? e2 : e;
                         }
@@ -493,7 +597,7 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
                         s.in.bitpos += xb;
                         s.in.normalize();
                         bits = s.in.window();
-                        const uint32_t tb = is_match ? (uint32_t)LIT_N : 0u, rb = is_match ? 7u : 8u;
+                        const uint32_t tb = is_match ? s.dbase : 0u, rb = is_match ? (uint32_t)DROOT : (uint32_t)LROOT;
                         uint32_t d = tget(s, tb + (bits & ((1u << rb) - 1u)));
                         {
                             const bool link = is_match ? (d >> 14) == 2u : (d >> 13) == 2u;
@@ -550,6 +654,7 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
         if (b < nblocks) {
             status[b] = s.status;
             ncmd_out[b] = s.ncmd;
+            if (!RETRY && s.status == INF_NEEDS_V1) retry[2u + atomicAdd(retry, 1u)] = b;
         }
     }
     cp_async_wait0();
@@ -564,7 +669,10 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
 constexpr int CRC3_WORDS = 5 * 256 + 32;
 __device__ uint32_t g_crc3[CRC3_WORDS];
 
-constexpr uint32_t LONG_COPY = 64;   // copies of at least this many bytes are done by the whole warp
+#ifndef DH_LONG_COPY
+#define DH_LONG_COPY 64
+#endif
+constexpr uint32_t LONG_COPY = DH_LONG_COPY;   // copies of at least this many bytes are done by the whole warp
 
 __global__ void __launch_bounds__(256, 4)
 bgzf_resolve3_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uint8_t *__restrict__ outbuf,
@@ -705,7 +813,11 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
         build_crc3_tables(host_tabs);
         e = cudaMemcpyToSymbol(g_crc3, host_tabs, sizeof host_tabs);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(bgzf_decode3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WARP_SMEM * WARPS);
+        e = cudaFuncSetAttribute(bgzf_decode3_kernel<P1Main, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 P1Main::WARP_SMEM * P1Main::WARPS);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(bgzf_decode3_kernel<P1Retry, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 P1Retry::WARP_SMEM * P1Retry::WARPS);
         if (e != cudaSuccess) return e;
         ready[dev] = true;
     }
@@ -713,10 +825,21 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     if (e != cudaSuccess) return e;
     if (nblocks == 0) return cudaSuccess;
     uint32_t *ncmd = reinterpret_cast<uint32_t *>(work);
+    unsigned int *retry = reinterpret_cast<unsigned int *>(work + inflate_work_retry(nblocks));   // {count, ticket, queue[nblocks]}
     uint8_t *areas = work + inflate_work_header(nblocks);
-    uint32_t ctas = (nblocks + THREADS - 1) / THREADS;
+    e = cudaMemsetAsync(retry, 0, 2 * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    uint32_t ctas = (nblocks + P1Main::THREADS - 1) / P1Main::THREADS;
     if (ctas > (uint32_t)sm_count) ctas = (uint32_t)sm_count;
-    bgzf_decode3_kernel<<<ctas, THREADS, WARP_SMEM * WARPS, stream>>>(comp, blocks, nblocks, status, ncmd, areas, counter);
+    bgzf_decode3_kernel<P1Main, false><<<ctas, P1Main::THREADS, P1Main::WARP_SMEM * P1Main::WARPS, stream>>>(
+        comp, blocks, nblocks, status, ncmd, areas, counter, retry);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    // blocks whose tables did not fit the main pass's pool: the queue is short (a fraction of one wave) or empty
+    ctas = (nblocks + P1Retry::THREADS - 1) / P1Retry::THREADS;
+    if (ctas > (uint32_t)sm_count) ctas = (uint32_t)sm_count;
+    bgzf_decode3_kernel<P1Retry, true><<<ctas, P1Retry::THREADS, P1Retry::WARP_SMEM * P1Retry::WARPS, stream>>>(
+        comp, blocks, nblocks, status, ncmd, areas, counter, retry);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (between_phases && (e = cudaEventRecord(between_phases, stream)) != cudaSuccess) return e;

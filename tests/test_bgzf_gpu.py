@@ -111,3 +111,25 @@ def test_checksum_of_checksums_large(ctx):
         off, cs, isz, crc = blocks[k]
         assert zlib.crc32(out[pos:pos + isz].tobytes()) & 0xffffffff == crc
     assert st.out_bytes == sum(b[2] for b in blocks)
+
+
+def test_table_pool_overflow_paths(ctx):
+    """Streams whose Huffman tables outgrow the decoder's table pool: 1 chain fits the main pass (6 warps per SM, 589
+    entries per stream), 2 chains are queued for the retry pass (4 warps, 892 entries), 3 chains need the lane-group
+    kernel.  Mixed with ordinary blocks so that all three paths run inside one launch; the bytes must not differ."""
+    rng = np.random.default_rng(5)
+    acgt = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), 300000))
+    parts = []
+    for rep in range(3):
+        for k in (1, 2, 3, 2, 1, 3):
+            payload, raw = util.chain_code_deflate(k, seed=10 * rep + k)
+            parts.append(util.bgzf_block(payload, raw_deflate=raw))
+            parts.append(util.make_bgzf(acgt[rep * 50000:(rep + 2) * 50000], eof=False))
+    parts.append(util.BGZF_EOF)
+    check(ctx, b"".join(parts))
+    # a launch where EVERY block overflows the main pool (the retry queue holds all of them)
+    blocks = []
+    for i in range(70):
+        payload, raw = util.chain_code_deflate(2, n_tokens=3000, seed=100 + i)
+        blocks.append(util.bgzf_block(payload, raw_deflate=raw))
+    check(ctx, b"".join(blocks) + util.BGZF_EOF)

@@ -41,6 +41,87 @@ def make_bgzf(data, level=6, block=0xff00, eof=True, strategy=zlib.Z_DEFAULT_STR
     return b"".join(out)
 
 
+def chain_code_deflate(n_chains, n_tokens=20000, seed=0):
+    """(payload, raw deflate) of one dynamic-Huffman block whose literal/length code is built to need large decode
+    tables: 128 - n_chains codes of 7 bits plus n_chains "chains" of lengths 8, 9, ..., 14, 15, 15 (a chain fills one
+    7-bit prefix and forces a 256-entry sub-table behind a 7-bit root).  Exercises the table-pool overflow paths of the
+    inflate kernel (main pass / retry pass with the larger pool / lane-group kernel).  RFC 1951 3.2.7 encoder, no RLE
+    of the code lengths (code-length code: symbols 0..15, 4 bits each)."""
+    rng = np.random.default_rng(seed)
+    lit_len = [0] * 286
+    short = list(range(0, 128 - n_chains - 6)) + [256, 257, 258, 259, 260, 261]      # 7-bit codes; 257..261 = lengths 3..7
+    for sym in short:
+        lit_len[sym] = 7
+    chain_syms = []
+    nxt = 128 - n_chains - 6
+    for _ in range(n_chains):
+        for l in (8, 9, 10, 11, 12, 13, 14, 15, 15):
+            lit_len[nxt] = l
+            chain_syms.append(nxt)
+            nxt += 1
+    assert nxt <= 256 and abs(sum(2.0 ** -l for l in lit_len if l) - 1.0) < 1e-12
+    dist_len = [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 10]                                  # distance symbols 0..10 (1..48)
+    assert abs(sum(2.0 ** -l for l in dist_len) - 1.0) < 1e-12
+
+    def canon(lens):
+        code, nc = 0, {}
+        for l in range(1, 16):
+            nc[l] = code
+            code = (code + sum(1 for x in lens if x == l)) << 1
+        out = {}
+        for sym, l in enumerate(lens):
+            if l:
+                out[sym] = (nc[l], l)
+                nc[l] += 1
+        return out
+
+    bits = []
+
+    def put(v, n):                       # LSB-first field
+        for i in range(n):
+            bits.append((v >> i) & 1)
+
+    def put_code(c):                     # Huffman code, MSB-first
+        code, l = c
+        for i in range(l - 1, -1, -1):
+            bits.append((code >> i) & 1)
+
+    order = [16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15]
+    pre_len = [4] * 16 + [0, 0, 0]
+    pre = canon(pre_len)
+    put(1, 1); put(2, 2)
+    put(len(lit_len) - 257, 5); put(len(dist_len) - 1, 5); put(19 - 4, 4)
+    for sym in order:
+        put(pre_len[sym], 3)
+    for l in lit_len + dist_len:
+        put_code(pre[l])
+    lc, dc = canon(lit_len), canon(dist_len)
+    lits = [s_ for s_ in short if s_ < 256] + chain_syms
+    dist_base = [1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33]
+    dist_extra = [0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4]
+    out = bytearray()
+    for _ in range(n_tokens):
+        if len(out) > 64 and rng.random() < 0.3:
+            ln = int(rng.integers(3, 8))
+            ds = int(rng.integers(0, len(dist_len)))
+            ex = int(rng.integers(0, 1 << dist_extra[ds]))
+            d = dist_base[ds] + ex
+            put_code(lc[257 + ln - 3]); put_code(dc[ds]); put(ex, dist_extra[ds])
+            for _k in range(ln):
+                out.append(out[-d])
+        else:
+            b = lits[int(rng.integers(0, len(lits)))] if rng.random() < 0.5 else chain_syms[int(rng.integers(0, len(chain_syms)))]
+            put_code(lc[b])
+            out.append(b)
+        if len(out) > 65000:
+            break
+    put_code(lc[256])
+    while len(bits) % 8:
+        bits.append(0)
+    raw = np.packbits(np.array(bits, dtype=np.uint8), bitorder="little").tobytes()
+    return bytes(out), raw
+
+
 def have_gen():
     return os.path.exists(GEN)
 

@@ -1,0 +1,28 @@
+#!/bin/bash
+# A/B on the GPU box: for the default library and every variants/<name>/libduckhts_cuda.so, run the inflate + scan parity
+# tests and one bench (JSON line -> gpurun_out/ab_<name>.json), print one summary line each.
+mkdir -p gpurun_out
+cp duckhts_b200/lib/libduckhts_cuda.so /tmp/default_lib.so
+run_one() {
+  name=$1
+  python -m pytest tests/test_bgzf_gpu.py tests/test_bam_gpu.py -m gpu -x -q 2>&1 | tail -1
+  python bench.py --steps 3 --warmup 3 ${AB_BENCH_ARGS} > gpurun_out/ab_$name.json 2> gpurun_out/ab_$name.err
+  python - $name <<'PY'
+import json, sys
+n = sys.argv[1]
+try:
+    j = json.loads(open(f"gpurun_out/ab_{n}.json").read().strip().splitlines()[-1])
+    print(n, "value", round(j["value"], 1), "e2e", round(j["e2e"]["value"], 1), "inflate GB/s", round(j["inflate"]["value"], 1),
+          {k: round(v, 1) for k, v in j["inflate"]["phase_ms"].items()}, "bcf", round(j.get("read_bcf", {}).get("value", 0)),
+          {k: round(v, 1) for k, v in j["kernel_ms_per_step"].items()})
+except Exception as e:
+    print(n, "failed", e); print(open(f"gpurun_out/ab_{n}.err").read()[-1500:])
+PY
+}
+run_one default
+for d in variants/*/; do
+  [ -f "$d/libduckhts_cuda.so" ] || continue
+  cp "$d/libduckhts_cuda.so" duckhts_b200/lib/libduckhts_cuda.so
+  run_one "$(basename $d)"
+done
+cp /tmp/default_lib.so duckhts_b200/lib/libduckhts_cuda.so
