@@ -26,9 +26,9 @@ struct BlockDesc {
 __host__ __device__
 #endif
 inline uint32_t inflate_work_cap(uint32_t isize) { return (isize + isize / 3u + 64u + 15u) & ~15u; }
-// in front of the areas: the per-block command counts, then the retry queue of phase 1 ({count, ticket} + one index per block)
+// in front of the areas: the per-block command counts, then the retry queue of phase 1 (a 16-byte header + 32 bytes per block, in 64 + 32 n bytes)
 inline size_t inflate_work_retry(uint32_t nblocks) { return (size_t)((nblocks + 63u) & ~63u) * 4u; }
-inline size_t inflate_work_header(uint32_t nblocks) { return inflate_work_retry(nblocks) * 2u + 64u; }
+inline size_t inflate_work_header(uint32_t nblocks) { return inflate_work_retry(nblocks) + 64u + (size_t)((nblocks + 63u) & ~63u) * 32u; }
 // work-buffer bytes for a launch over `nblocks` blocks whose areas total `area_bytes`
 inline size_t inflate_work_bytes(uint32_t nblocks, uint64_t area_bytes) { return inflate_work_header(nblocks) + (size_t)area_bytes + 256u; }
 

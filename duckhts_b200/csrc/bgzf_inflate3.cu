@@ -9,8 +9,11 @@
 // from DRAM because 300k threads with 64 KB working sets thrash L2.  Generation 3:
 //
 //   phase 1  bgzf_decode3_kernel — still ONE DEFLATE STREAM PER LANE (Huffman decoding is bit-serial), but
-//     * 4 warps per SM (one per scheduler): litlen root 8 (worst case 660 entries, enumerated in DESIGN.md) +
-//       distance root 7 capped at 232 entries = 892 u16 entries per stream, lane-interleaved; exactly 227 KB/SM;
+//     * 6 warps per SM: one pool of 589 u16 entries per stream (litlen root 7 + distance root 6 and their sub-tables,
+//       lane-interleaved) fills the 227 KB of an SM; the few streams whose tables need more are handed, at the header
+//       that overflowed, to 4 retry CTAs of the same grid that run 4 warps on 892-entry pools (see P1<> below);
+//     * the header pass (code-length decode, table builds) keeps the lanes converged: nothing returns early, the
+//       symbol loops have constant trip counts and end in __syncwarp (r1j: 3-7 of 32 threads per instruction before);
 //     * compressed bytes reach each lane through a private 2 x 16-byte shared-memory ring filled by cp.async
 //       (one 16-byte chunk in flight while the other is consumed), so the symbol loop never waits on L2/DRAM;
 //     * the bit reader is a 64-bit window (w0,w1) + one funnel shift per lookup, no 64-bit shifts;
@@ -24,8 +27,8 @@
 //     waits only for earlier lanes of the same step whose destination it reads), then the warp computes the CRC-32
 //     of the finished block with coalesced loads (lane-interleaved Horner form: H = H*x^1024 + w through four
 //     256-entry tables) and compares CRC and ISIZE with the BGZF footer.
-// Streams whose distance code needs more than 232 table entries (worst case 400; never seen from zlib/libdeflate)
-// are flagged INF_NEEDS_V1 and redone by the lane-group kernel (bgzf_inflate.cu) in filter mode.
+// Streams whose tables do not fit the 892-entry pool either (litlen > 640 or litlen + distance > 892 entries; never
+// seen from zlib/libdeflate) stay flagged INF_NEEDS_V1 and are redone by the lane-group kernel (bgzf_inflate.cu).
 #include "bgzf_inflate.cuh"
 #include "crc32_core.cuh"
 #include "inflate_core.cuh"
@@ -51,9 +54,9 @@ constexpr unsigned FULL = 0xffffffffu;
 // D = 400 at root 7).  The kernel is bound by the issue latency of one dependent chain per warp (ncu: 25 % issue slots busy with
 // 4 warps per SM), so more warps per SM is the lever and the pool size decides how many fit into the 227 KB of an SM:
 //   W = 4: 892 entries (every BAM/BCF stream seen fits), W = 6: 589 entries (~1 % of the BAM blocks do not fit).
-// The main pass runs P1<DH_P1_WARPS>; a lane whose tables do not fit queues its block, and a second launch of the same kernel as
-// P1<4> redoes the queued blocks (a fraction of one wave).  What still does not fit there is flagged INF_NEEDS_V1 and redone by
-// the lane-group kernel (bgzf_inflate.cu), as before.
+// The main CTAs run P1<DH_P1_WARPS>; a lane whose tables do not fit queues its stream (as it stood at that deflate block header),
+// and the retry CTAs of the same grid resume it as P1<4> (decode_pass<P1Retry, true> below).  What does not fit there either
+// is flagged INF_NEEDS_V1 and redone by the lane-group kernel (bgzf_inflate.cu), as before.
 template <int W>
 struct P1 {
     static constexpr int WARPS = W, THREADS = W * 32;
@@ -67,8 +70,13 @@ struct P1 {
     static constexpr int WARP_SMEM = TAB_N * 64 + 2 * 512;
     static_assert(WARP_SMEM * WARPS <= 232448, "phase 1 is sized to fill the 227 KB of one SM");
 };
+#ifndef DH_RETRY_CTAS
+#define DH_RETRY_CTAS 4
+#endif
 using P1Main = P1<DH_P1_WARPS>;
 using P1Retry = P1<4>;
+constexpr int P1_SMEM = P1Main::WARP_SMEM * P1Main::WARPS > P1Retry::WARP_SMEM * P1Retry::WARPS ? P1Main::WARP_SMEM * P1Main::WARPS
+                                                                                                 : P1Retry::WARP_SMEM * P1Retry::WARPS;
 
 // ---- table entries (u16) ---------------------------------------------------------------------------------
 // litlen:  bit15 = 1: length code   [14:12] extra bits  [11:4] base-3  [3:0] code length
@@ -119,9 +127,10 @@ struct Bits {
         if (k == 3u) { cp_async16(ring + ((c & 1u) << 9), g + ((size_t)(c + 2u) << 4)); cp_async_commit(); }
         ++wi;
     }
-    __device__ __forceinline__ void open(const uint8_t *payload, uint32_t ring_addr) {
+    // start reading `bit` bits behind the 16-byte aligned address g0 (bit < 128: the start of a payload; more: a resumed stream)
+    __device__ __forceinline__ void open(const uint8_t *g0, uint32_t bit, uint32_t ring_addr) {
         ring = ring_addr;
-        g = reinterpret_cast<const uint8_t *>((uintptr_t)payload & ~(uintptr_t)15);
+        g = g0 + ((size_t)(bit >> 7) << 4);
         cp_async_wait0();                                    // nothing of the previous stream may still be landing
         cp_async16(ring, g);
         cp_async_commit();
@@ -132,7 +141,7 @@ struct Bits {
         w1 = lds32(ring + 4u);
         w2 = lds32(ring + 8u);
         wi = 3u;
-        bitpos = (uint32_t)((uintptr_t)payload & 15u) * 8u;
+        bitpos = bit & 127u;
         while (bitpos >= 32u) advance();
     }
     // Branch-free form of `if (bitpos >= 32) advance()` for the symbol loop.  ncu (r1h) showed the two refill blocks of a step
@@ -175,6 +184,7 @@ struct Lane {
     uint8_t *lit;         // literal stream (grows upwards, 4 bytes per store)
     uint32_t *cmd_top;    // command k is stored at cmd_top[-k]
     uint32_t lit_acc, nlit, ncmd, lit_run, pos, isize;
+    uint32_t bit_base;    // bits in front of the 16-byte chunk the reader was opened at (0 unless the stream was resumed)
     uint32_t end_bits;    // consumed() value at the end of the payload
     uint32_t wi_limit;    // a corrupt stream may not fetch words beyond this
     int status;
@@ -498,13 +508,19 @@ using namespace v3;
 // =========================================================================================================
 // commands (32 bits):  [31]=0 match:   [30:23] literals since the previous command (0..254)  [22:15] length-3  [14:0] distance-1
 //                      [31]=1 literals: [30:0] run of literals with no match behind it (255 inside a run, or the tail)
-// `retry` = {count, ticket} + the queue of block indices behind it.  RETRY = false: the main pass over blocks [0, nblocks); a lane whose
-// tables do not fit appends its block to the queue.  RETRY = true: the pass over the queued blocks with the larger pool.
+// The retry queue: `retry` = {count, ticket, finished main warps, -} + 8 words per entry {block, bit position of the deflate block
+// header that did not fit, nlit, ncmd, lit_run, pos, lit_acc, -}; word 0 of every entry is 0xffffffff until the entry is complete.
+// The LAST `retry_ctas` CTAs of the grid run decode_pass<P1Retry, true> (4 warps, the larger pool) next to the main CTAs: they take
+// queued streams in groups of 32 as they arrive and RESUME them at the header that overflowed, so almost all of the retry work
+// hides behind the main pass (a separate retry launch cost one generation, ~6.5 ms, per launch).  Every wait is bounded: a retry
+// warp that gives up leaves its blocks flagged INF_NEEDS_V1, and the lane-group kernel redoes them.
+__device__ __forceinline__ uint32_t ld_vol(const unsigned int *p) { return *reinterpret_cast<const volatile unsigned int *>(p); }
+constexpr uint32_t RETRY_HDR = 4, RETRY_ENTRY = 8, SPIN_LIMIT = 1u << 21;
+
 template <class K, bool RETRY>
-__global__ void __launch_bounds__(K::THREADS, 1)
-bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, uint32_t nblocks,
-                    int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
-                    unsigned int *__restrict__ counter, unsigned int *__restrict__ retry) {
+__device__ __forceinline__ void decode_pass(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, const uint32_t nblocks,
+                                            int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
+                                            unsigned int *__restrict__ counter, unsigned int *retry, const uint32_t n_main_warps) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t warp_base = (uint32_t)__cvta_generic_to_shared(smem_raw) + warp * (uint32_t)K::WARP_SMEM;
@@ -512,18 +528,50 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
 
     for (;;) {
         // ---- a generation: 32 consecutive blocks, one per lane ----
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(RETRY ? retry + 1 : counter, 32u);
-        base = __shfl_sync(FULL, base, 0);
-        const uint32_t nwork = RETRY ? *reinterpret_cast<volatile unsigned int *>(retry) : nblocks;
-        if (base >= nwork) break;
-        uint32_t b = nblocks;
-        if (base + lane < nwork) b = RETRY ? retry[2u + base + lane] : base + lane;
+        uint32_t base = 0, b = nblocks, start_bit = 0xffffffffu;
         Lane s;
+        s.lit_acc = s.nlit = s.ncmd = s.lit_run = s.pos = 0u;
+        if (!RETRY) {
+            if (lane == 0) base = atomicAdd(counter, 32u);
+            base = __shfl_sync(FULL, base, 0);
+            if (base >= nblocks) break;
+            b = base + lane;
+        } else {
+            uint32_t take = 0;
+            if (lane == 0) {
+                for (uint32_t spins = 0; spins < SPIN_LIMIT; ++spins) {
+                    const bool all_in = ld_vol(retry + 2) == n_main_warps;      // read before the count: all_in => the count is final
+                    __threadfence();
+                    const uint32_t tk = ld_vol(retry + 1), avail = ld_vol(retry) - tk;
+                    if (avail >= 32u || (all_in && avail)) {
+                        const uint32_t want = avail < 32u ? avail : 32u;
+                        if (atomicCAS(retry + 1, tk, tk + want) == tk) { base = tk; take = want; break; }
+                        continue;
+                    }
+                    if (all_in) break;
+                    __nanosleep(2000);
+                }
+            }
+            take = __shfl_sync(FULL, take, 0);
+            base = __shfl_sync(FULL, base, 0);
+            if (!take) break;
+            if (lane < take) {
+                const unsigned int *q = retry + RETRY_HDR + (size_t)(base + lane) * RETRY_ENTRY;
+                uint32_t qb = 0xffffffffu;
+                for (uint32_t spins = 0; spins < SPIN_LIMIT && (qb = ld_vol(q)) == 0xffffffffu; ++spins) __nanosleep(500);
+                __threadfence();
+                if (qb < nblocks) {
+                    b = qb;
+                    start_bit = ld_vol(q + 1);
+                    s.nlit = ld_vol(q + 2); s.ncmd = ld_vol(q + 3); s.lit_run = ld_vol(q + 4); s.pos = ld_vol(q + 5); s.lit_acc = ld_vol(q + 6);
+                }
+            }
+        }
+        bool queued = false;
         s.tab = warp_base + lane * 2u;
         s.dbase = 1u << LROOT;
         s.status = INF_OK;
-        s.lit_acc = s.nlit = s.ncmd = s.lit_run = s.pos = s.isize = 0u;
+        s.isize = 0u;
         s.end_bits = 0u;
         s.wi_limit = 0u;
         s.lit = work;
@@ -535,10 +583,12 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
             s.isize = d.isize;
             s.lit = work + d.cmd_off;
             s.cmd_top = reinterpret_cast<uint32_t *>(work + d.cmd_off + inflate_work_cap(d.isize)) - 1;
-            s.in.open(comp + d.in_off, warp_base + (uint32_t)K::TAB_N * 64u + lane * 16u);
             const uint32_t mis = (uint32_t)((uintptr_t)(comp + d.in_off) & 15u);
-            s.end_bits = (mis + d.in_len) * 8u;
-            s.wi_limit = ((mis + d.in_len + 3u) >> 2) + 8u;
+            if (!RETRY) start_bit = mis * 8u;
+            s.in.open(comp + d.in_off - mis, start_bit, warp_base + (uint32_t)K::TAB_N * 64u + lane * 16u);
+            s.bit_base = start_bit & ~127u;                  // consumed() counts from the 16-byte chunk the reader was opened at
+            s.end_bits = (mis + d.in_len) * 8u - s.bit_base;
+            s.wi_limit = ((mis + d.in_len + 3u) >> 2) + 8u - (s.bit_base >> 5);
             st = ST_HEADER;
         }
         auto fail = [&](int code) { s.status = code; st = ST_DONE; };
@@ -556,7 +606,17 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
             const unsigned hm = __ballot_sync(FULL, st == ST_HEADER);
             if (st == ST_HEADER) {
                 bool stored;
+                const uint32_t hdr_bit = s.in.consumed() + s.bit_base;
                 const int rc = read_block_header<K>(s, hm, bfinal, stored);
+                if (!RETRY && rc == INF_NEEDS_V1 && n_main_warps) {
+                    // the tables do not fit this pool: hand the stream, as it stood at this header, to the retry CTAs
+                    status[b] = INF_NEEDS_V1;
+                    unsigned int *q = retry + RETRY_HDR + (size_t)atomicAdd(retry, 1u) * RETRY_ENTRY;
+                    q[1] = hdr_bit; q[2] = s.nlit; q[3] = s.ncmd; q[4] = s.lit_run; q[5] = s.pos; q[6] = s.lit_acc;
+                    __threadfence();
+                    *reinterpret_cast<volatile unsigned int *>(q) = b;
+                    queued = true;
+                }
                 if (rc != INF_OK) fail(rc);
                 else if (!stored) st = ST_RUN;
                 else if (bfinal) finish();
@@ -651,13 +711,27 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
                 }
             }
         }
-        if (b < nblocks) {
+        if (b < nblocks && !queued) {
             status[b] = s.status;
             ncmd_out[b] = s.ncmd;
-            if (!RETRY && s.status == INF_NEEDS_V1) retry[2u + atomicAdd(retry, 1u)] = b;
         }
     }
     cp_async_wait0();
+    if (!RETRY && lane == 0) { __threadfence(); atomicAdd(retry + 2, 1u); }
+}
+
+// n_main_warps = 0: no retry CTAs in this grid (every lane keeps its INF_NEEDS_V1 verdict)
+__global__ void __launch_bounds__(P1Main::THREADS, 1)
+bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, uint32_t nblocks,
+                    int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
+                    unsigned int *__restrict__ counter, unsigned int *retry, uint32_t retry_ctas) {
+    static_assert(P1Retry::THREADS <= P1Main::THREADS, "the retry role uses a subset of the CTA's warps");
+    const uint32_t main_ctas = gridDim.x - retry_ctas;
+    const uint32_t n_main_warps = retry_ctas ? main_ctas * (uint32_t)P1Main::WARPS : 0u;
+    if (blockIdx.x < main_ctas)
+        decode_pass<P1Main, false>(comp, blocks, nblocks, status, ncmd_out, work, counter, retry, n_main_warps);
+    else if (threadIdx.x < P1Retry::THREADS)
+        decode_pass<P1Retry, true>(comp, blocks, nblocks, status, ncmd_out, work, counter, retry, n_main_warps);
 }
 
 // =========================================================================================================
@@ -670,7 +744,7 @@ constexpr int CRC3_WORDS = 5 * 256 + 32;
 __device__ uint32_t g_crc3[CRC3_WORDS];
 
 #ifndef DH_LONG_COPY
-#define DH_LONG_COPY 64
+#define DH_LONG_COPY 16
 #endif
 constexpr uint32_t LONG_COPY = DH_LONG_COPY;   // copies of at least this many bytes are done by the whole warp
 
@@ -813,11 +887,7 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
         build_crc3_tables(host_tabs);
         e = cudaMemcpyToSymbol(g_crc3, host_tabs, sizeof host_tabs);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(bgzf_decode3_kernel<P1Main, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 P1Main::WARP_SMEM * P1Main::WARPS);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(bgzf_decode3_kernel<P1Retry, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 P1Retry::WARP_SMEM * P1Retry::WARPS);
+        e = cudaFuncSetAttribute(bgzf_decode3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P1_SMEM);
         if (e != cudaSuccess) return e;
         ready[dev] = true;
     }
@@ -825,21 +895,18 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     if (e != cudaSuccess) return e;
     if (nblocks == 0) return cudaSuccess;
     uint32_t *ncmd = reinterpret_cast<uint32_t *>(work);
-    unsigned int *retry = reinterpret_cast<unsigned int *>(work + inflate_work_retry(nblocks));   // {count, ticket, queue[nblocks]}
+    unsigned int *retry = reinterpret_cast<unsigned int *>(work + inflate_work_retry(nblocks));   // queue header + 8 words per block
     uint8_t *areas = work + inflate_work_header(nblocks);
-    e = cudaMemsetAsync(retry, 0, 2 * sizeof(unsigned int), stream);
+    e = cudaMemsetAsync(retry, 0xff, inflate_work_header(nblocks) - inflate_work_retry(nblocks), stream);
     if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(retry, 0, RETRY_HDR * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    // main CTAs: one per SM at most, 6 warps x 32 streams each; retry CTAs (same pool as the main pass => none needed)
+    uint32_t retry_ctas = P1Main::TAB_N < P1Retry::TAB_N ? (sm_count >= 64 ? (uint32_t)DH_RETRY_CTAS : sm_count >= 8 ? 1u : 0u) : 0u;
     uint32_t ctas = (nblocks + P1Main::THREADS - 1) / P1Main::THREADS;
-    if (ctas > (uint32_t)sm_count) ctas = (uint32_t)sm_count;
-    bgzf_decode3_kernel<P1Main, false><<<ctas, P1Main::THREADS, P1Main::WARP_SMEM * P1Main::WARPS, stream>>>(
-        comp, blocks, nblocks, status, ncmd, areas, counter, retry);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    // blocks whose tables did not fit the main pass's pool: the queue is short (a fraction of one wave) or empty
-    ctas = (nblocks + P1Retry::THREADS - 1) / P1Retry::THREADS;
-    if (ctas > (uint32_t)sm_count) ctas = (uint32_t)sm_count;
-    bgzf_decode3_kernel<P1Retry, true><<<ctas, P1Retry::THREADS, P1Retry::WARP_SMEM * P1Retry::WARPS, stream>>>(
-        comp, blocks, nblocks, status, ncmd, areas, counter, retry);
+    if (ctas > (uint32_t)sm_count - retry_ctas) ctas = (uint32_t)sm_count - retry_ctas;
+    bgzf_decode3_kernel<<<ctas + retry_ctas, P1Main::THREADS, P1_SMEM, stream>>>(comp, blocks, nblocks, status, ncmd, areas, counter,
+                                                                                 retry, retry_ctas);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (between_phases && (e = cudaEventRecord(between_phases, stream)) != cudaSuccess) return e;

@@ -126,7 +126,7 @@ int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint3
     if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[2], stream));
     DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, stream, true));
     if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[3], stream));
-    c->launches += 4;   // phase 1, its retry pass, phase 2, the lane-group filter
+    c->launches += 3;   // phase 1 (main + retry CTAs in one grid), phase 2, the lane-group filter
     return DH_OK;
 }
 
