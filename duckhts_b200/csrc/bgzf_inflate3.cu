@@ -70,6 +70,12 @@ struct P1 {
     static constexpr int WARP_SMEM = TAB_N * 64 + 2 * 512;
     static_assert(WARP_SMEM * WARPS <= 232448, "phase 1 is sized to fill the 227 KB of one SM");
 };
+#ifndef DH_TAIL_TAKE
+#define DH_TAIL_TAKE 1
+#endif
+#ifndef DH_CONVERT
+#define DH_CONVERT 1
+#endif
 #ifndef DH_RETRY_CTAS
 #define DH_RETRY_CTAS 4
 #endif
@@ -520,7 +526,8 @@ constexpr uint32_t RETRY_HDR = 4, RETRY_ENTRY = 8, SPIN_LIMIT = 1u << 21;
 template <class K, bool RETRY>
 __device__ __forceinline__ void decode_pass(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, const uint32_t nblocks,
                                             int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
-                                            unsigned int *__restrict__ counter, unsigned int *retry, const uint32_t n_main_warps) {
+                                            unsigned int *__restrict__ counter, unsigned int *retry, const uint32_t n_main_warps,
+                                            const bool linger = true) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t warp_base = (uint32_t)__cvta_generic_to_shared(smem_raw) + warp * (uint32_t)K::WARP_SMEM;
@@ -543,12 +550,15 @@ __device__ __forceinline__ void decode_pass(const uint8_t *__restrict__ comp, co
                     const bool all_in = ld_vol(retry + 2) == n_main_warps;      // read before the count: all_in => the count is final
                     __threadfence();
                     const uint32_t tk = ld_vol(retry + 1), avail = ld_vol(retry) - tk;
-                    if (avail >= 32u || (all_in && avail)) {
+                    // full groups while the main pass is in full swing; once its last generations have been handed out (and the main
+                    // CTAs that finish turn into retry CTAs, see the kernel), whatever is there, so that no stream waits for company
+                    const bool last_round = DH_TAIL_TAKE && ld_vol(counter) >= nblocks;
+                    if (avail >= 32u || ((all_in || last_round) && avail)) {
                         const uint32_t want = avail < 32u ? avail : 32u;
                         if (atomicCAS(retry + 1, tk, tk + want) == tk) { base = tk; take = want; break; }
                         continue;
                     }
-                    if (all_in) break;
+                    if (all_in || !linger) break;     // a converted main CTA does not wait for work: it would hold its SM
                     __nanosleep(2000);
                 }
             }
@@ -728,10 +738,17 @@ bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
     static_assert(P1Retry::THREADS <= P1Main::THREADS, "the retry role uses a subset of the CTA's warps");
     const uint32_t main_ctas = gridDim.x - retry_ctas;
     const uint32_t n_main_warps = retry_ctas ? main_ctas * (uint32_t)P1Main::WARPS : 0u;
-    if (blockIdx.x < main_ctas)
+    if (blockIdx.x < main_ctas) {
         decode_pass<P1Main, false>(comp, blocks, nblocks, status, ncmd_out, work, counter, retry, n_main_warps);
-    else if (threadIdx.x < P1Retry::THREADS)
-        decode_pass<P1Retry, true>(comp, blocks, nblocks, status, ncmd_out, work, counter, retry, n_main_warps);
+        if (!retry_ctas || !DH_CONVERT) return;
+        __syncthreads();          // all warps of this CTA are out of the main pass: its shared memory can be laid out for the retry role
+    }
+    // retry role: the dedicated CTAs from the start and until the queue is final and empty; every main CTA once it has run out of
+    // main work, for as long as it finds queued streams (the backlog would otherwise keep 16 warps busy for most of a generation
+    // while 140 SMs idle: r1k capture, 11.4 ms instead of 7.1).  A converted CTA that finds the queue empty exits: inside the
+    // scan pipeline the column kernels of the other stream are waiting for its SM (lingering there cost 25 % of the scan rate).
+    if (threadIdx.x < P1Retry::THREADS)
+        decode_pass<P1Retry, true>(comp, blocks, nblocks, status, ncmd_out, work, counter, retry, n_main_warps, blockIdx.x >= main_ctas);
 }
 
 // =========================================================================================================

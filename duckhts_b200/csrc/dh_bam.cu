@@ -199,9 +199,19 @@ cudaStream_t s_comp(dh_bam *b) { return b->ctx->stream; }
 cudaStream_t s_copy(dh_bam *b) { return b->ctx->copy_streams[0]; }
 cudaStream_t s_d2h(dh_bam *b) { return b->ctx->copy_streams[1]; }
 cudaStream_t s_inf(dh_bam *b) { return b->ctx->copy_streams[2]; }
+#ifndef DH_SM_RESERVE_DEVICE
+#define DH_SM_RESERVE_DEVICE 32
+#endif
 // Phase 1 of the inflate is a persistent kernel that takes whole SMs (227 KB of shared memory each).  When batches go
 // back to the host, a few SMs stay free so that the decode kernels feeding the D2H copy engine are never locked out.
-int inflate_sms(const dh_bam *b) { return (b->mode & DH_BAM_DEVICE_OUTPUT) ? b->ctx->sm_count : b->ctx->sm_count - 8; }
+// With column batches left on the device the walk/decode kernels of the previous segment are the second half of the work:
+// measured on the 100 M-record scan (r1k, DH_INFLATE_SM_RESERVE = 0 / 8 / 16 / 24 / 32 / 48): 226 / 251 / 270 / 284 / 301 / 285
+// Mrecords/s, so 32 SMs are left to them.
+int inflate_sms(const dh_bam *b) {
+    static const int reserve_dev = getenv("DH_INFLATE_SM_RESERVE") ? atoi(getenv("DH_INFLATE_SM_RESERVE")) : DH_SM_RESERVE_DEVICE;
+    const int reserve = (b->mode & DH_BAM_DEVICE_OUTPUT) ? reserve_dev : 8;
+    return reserve < b->ctx->sm_count ? b->ctx->sm_count - reserve : b->ctx->sm_count;
+}
 
 int ensure_events(dh_bam *b) {
     for (auto &s : b->ss)
