@@ -43,7 +43,7 @@ def test_product_does_not_reference_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".h", ".c", ".cpp", "Makefile")):
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
-                assert "oracle" not in txt.lower() or f == "__init__.py" and "oracle" not in txt, f"{f} mentions oracle"
+                assert "oracle" not in txt.lower(), f"{f} mentions oracle"
 
 
 def test_host_framing_matches_oracle():
