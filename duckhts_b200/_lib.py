@@ -34,7 +34,7 @@ class BamBatch(C.Structure):
                 ("data", C.c_void_p * DH_BAM_MAX_COLS), ("validity", C.c_void_p * DH_BAM_MAX_COLS),
                 ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64),
                 ("aux_map", C.c_void_p), ("aux_map_validity", C.c_void_p), ("aux_keys", C.c_void_p), ("aux_values", C.c_void_p),
-                ("n_aux", C.c_uint64)]
+                ("n_aux", C.c_uint64), ("slot", C.c_int32), ("layout", C.c_uint32), ("rec_off", C.c_void_p)]
 
 
 class BamScanStats(C.Structure):
@@ -52,9 +52,7 @@ class BcfBatch(C.Structure):
                 ("core", C.c_void_p * 7), ("core_validity", C.c_void_p * 7),
                 ("info", C.POINTER(C.c_void_p)), ("info_validity", C.POINTER(C.c_void_p)),
                 ("format", C.POINTER(C.c_void_p)), ("format_validity", C.POINTER(C.c_void_p)),
-                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64),
-                ("aux_map", C.c_void_p), ("aux_map_validity", C.c_void_p), ("aux_keys", C.c_void_p), ("aux_values", C.c_void_p),
-                ("n_aux", C.c_uint64)]
+                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64), ("slot", C.c_int32), ("pad2", C.c_int32)]
 
 
 _lib = None
@@ -95,6 +93,21 @@ SIGNATURES = {
     "dh_bam_set_mode": (C.c_int, [C.c_void_p, C.c_uint32]),
     "dh_bam_scan_begin": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64]),
     "dh_bam_next_batch": (C.c_int, [C.c_void_p, C.POINTER(BamBatch)]),
+    "dh_bam_set_slots": (C.c_int, [C.c_void_p, C.c_int]),
+    "dh_bam_prefetch": (C.c_int, [C.c_void_p]),
+    "dh_bam_acquire_batch": (C.c_int, [C.c_void_p, C.POINTER(BamBatch)]),
+    "dh_bam_release_batch": (C.c_int, [C.c_void_p, C.c_int32]),
+    "dh_bam_batch_checksum": (C.c_int, [C.c_void_p, C.POINTER(BamBatch), C.POINTER(C.c_uint64)]),
+    "dh_bam_n_rg": (C.c_int32, [C.c_void_p]),
+    "dh_bam_rg_id": (C.c_void_p, [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32)]),
+    "dh_bam_rg_sample": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "dh_bam_clone": (C.c_void_p, [C.c_void_p, C.c_void_p]),
+    "dh_bam_set_filter": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "dh_index_split_contigs": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32)]),
+    "dh_bgzf_inflate_fd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(InflateStats)]),
+    "dh_bcf_set_slots": (C.c_int, [C.c_void_p, C.c_int]),
+    "dh_bcf_acquire_batch": (C.c_int, [C.c_void_p, C.POINTER(BcfBatch)]),
+    "dh_bcf_release_batch": (C.c_int, [C.c_void_p, C.c_int32]),
     "dh_bam_scan_stats_get": (C.c_int, [C.c_void_p, C.POINTER(BamScanStats)]),
     "dh_bam_split": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]),
     "dh_index_load": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),

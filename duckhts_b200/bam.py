@@ -137,8 +137,66 @@ class BamFile:
     def configure(self, seg_comp=0, batch_rows=0, carry=0):
         check(lib().dh_bam_configure(self.h, seg_comp, batch_rows, carry), "dh_bam_configure")
 
-    def set_mode(self, device_input=False, device_output=False):
-        check(lib().dh_bam_set_mode(self.h, (1 if device_input else 0) | (2 if device_output else 0)), "dh_bam_set_mode")
+    def set_mode(self, device_input=False, device_output=False, compact=False):
+        """compact: batches in the compact wire layout (DH_BAM_COMPACT_OUTPUT) instead of DuckDB vector layout."""
+        check(lib().dh_bam_set_mode(self.h, (1 if device_input else 0) | (2 if device_output else 0) | (4 if compact else 0)), "dh_bam_set_mode")
+
+    def set_filter(self, flag_require=0, flag_exclude=0, min_mapq=0):
+        check(lib().dh_bam_set_filter(self.h, flag_require, flag_exclude, min_mapq), "dh_bam_set_filter")
+
+    def set_slots(self, n):
+        check(lib().dh_bam_set_slots(self.h, n), "dh_bam_set_slots")
+
+    def prefetch(self):
+        check(lib().dh_bam_prefetch(self.h), "dh_bam_prefetch")
+
+    def clone(self, ctx):
+        """A second handle on the same image for another context (another GPU): dh_bam_clone."""
+        o = BamFile.__new__(BamFile)
+        o.a, o.ctx, o.tags = self.a, ctx, list(self.tags)
+        o.h = lib().dh_bam_clone(self.h, ctx.h)
+        if not o.h:
+            raise DuckhtsError("dh_bam_clone failed: " + lib().dh_last_error().decode())
+        if hasattr(self, "col_mask"):
+            o.col_mask = self.col_mask
+        return o
+
+    @property
+    def rg(self):
+        """[(id bytes, sample bytes | None)] in header order: the dictionary SAMPLE_ID codes of the compact layout index."""
+        out = []
+        for i in range(lib().dh_bam_n_rg(self.h)):
+            n = C.c_uint32(0)
+            p = lib().dh_bam_rg_id(self.h, i, C.byref(n))
+            out.append((C.string_at(p, n.value), lib().dh_bam_rg_sample(self.h, i)))
+        return out
+
+    def acquire(self):
+        """dh_bam_acquire_batch: the batch stays valid until release(batch.slot)."""
+        b = BamBatch()
+        rc = check(lib().dh_bam_acquire_batch(self.h, C.byref(b)), "dh_bam_acquire_batch")
+        return b if rc == 1 else None
+
+    def release(self, slot):
+        check(lib().dh_bam_release_batch(self.h, slot), "dh_bam_release_batch")
+
+    def checksum(self, batch, sums=None):
+        """Adds the per-column checksums of a held batch to `sums` (numpy uint64[DH_BAM_MAX_COLS])."""
+        if sums is None:
+            sums = np.zeros(DH_BAM_CORE_COLS + 63, dtype=np.uint64)
+        check(lib().dh_bam_batch_checksum(self.h, C.byref(batch), sums.ctypes.data_as(C.POINTER(C.c_uint64))), "dh_bam_batch_checksum")
+        return sums
+
+    def drain_checksums(self):
+        """Run the scan to the end; returns (rows, per-column checksums)."""
+        sums = np.zeros(DH_BAM_CORE_COLS + 63, dtype=np.uint64)
+        rows = 0
+        while True:
+            b = self.next_batch()
+            if b is None:
+                return rows, sums
+            rows += b.n_rows
+            self.checksum(b, sums)
 
     def split(self, n_parts):
         v = (C.c_uint64 * (n_parts + 1))()
@@ -186,8 +244,96 @@ class BamFile:
             rows += b.n_rows
 
 
+COMPACT = 4
+_COMPACT_FIX = {"flag": np.uint16, "pos": np.int32, "mapq": np.uint8, "pnext": np.int32, "tlen": np.int32}
+
+
+def _compact_batch_to_columns(bf, b):
+    """A batch in the compact wire layout (include/duckhts_cuda.h, DH_BAM_COMPACT_OUTPUT) -> the same dict as the DuckDB
+    layout gives: the expansion a consumer does (widening, dictionary lookup, one string per length word)."""
+    n = int(b.n_rows)
+    out = {"n": n}
+    heap = C.string_at(b.heap, int(b.heap_bytes)) if b.heap_bytes else b""
+    rec_off = np.frombuffer(C.string_at(b.rec_off, 4 * n), dtype=np.uint32) if n else np.zeros(0, np.uint32)
+    names, rgs = bf.ref_names, bf.rg
+
+    def arr(c, dt):
+        dt = np.dtype(dt)
+        return np.frombuffer(C.string_at(b.data[c], n * dt.itemsize), dtype=dt).copy() if n else np.zeros(0, dt)
+
+    on = lambda c: c >= 64 or (bf.col_mask >> c) & 1  # noqa: E731
+    for c, name in enumerate(CORE_NAMES):
+        if not on(c):
+            continue
+        if name in _COMPACT_FIX:
+            v = arr(c, _COMPACT_FIX[name])
+            out[name] = (v.astype(np.int64) + 1) if name in ("pos", "pnext") else v.astype(CORE_DTYPES[name])
+        elif name in ("rname", "rnext"):
+            out[name] = [names[t] if 0 <= t < len(names) else b"*" for t in arr(c, np.int32)]
+        elif name == "sample":
+            valid = validity_to_bool(b.validity[c], n)
+            out[name] = [rgs[k][1] if valid[i] else None for i, k in enumerate(arr(c, np.int32))]
+    # string slots of every row, in slot order
+    slot_cols = [(c, CORE_NAMES[c], "q" if c == 0 else "u" if c == 10 else "s") for c in (0, 5, 9, 10) if on(c)]
+    for k, (tg, ty) in enumerate(bf.tags):
+        c = DH_BAM_CORE_COLS + k
+        if on(c) and (ty == "Z" or ty[0] == "B"):
+            slot_cols.append((c, k, "b" if ty[0] == "B" else "s"))
+    if on(11):
+        slot_cols.append((11, "rg", "s"))
+    lens = {c: (arr(c, np.uint32) if kind != "b" else arr(c, np.uint64).reshape(n, 2)) for c, _, kind in slot_cols}
+    valids = {c: validity_to_bool(b.validity[c], n) for c, _, _ in slot_cols}
+    vals = {c: [None] * n for c, _, _ in slot_cols}
+    for r in range(n):
+        off = int(rec_off[r])
+        for c, _, kind in slot_cols:
+            if valids[c] is not None and not valids[c][r]:
+                continue
+            if kind == "b":
+                o8, ln = int(lens[c][r, 0]), int(lens[c][r, 1])
+                vals[c][r] = np.frombuffer(heap[8 * o8:8 * o8 + 8 * ln], dtype=np.int64).copy()
+                off += 4 + 8 * ln
+                continue
+            v = int(lens[c][r])
+            cap, flagged = v & 0x7fffffff, v >> 31
+            raw = heap[off:off + cap]
+            if kind == "q":
+                raw = raw.split(b"\0")[0] if flagged else raw[:cap - 1]
+            elif flagged:
+                raw = raw.split(b"\0")[0]
+            vals[c][r] = raw
+            off += (cap + 3) & ~3
+    for c, key, kind in slot_cols:
+        if c < DH_BAM_CORE_COLS:
+            out[CORE_NAMES[c]] = vals[c]
+    tags = []
+    for k, (tg, ty) in enumerate(bf.tags):
+        c = DH_BAM_CORE_COLS + k
+        if not on(c):
+            tags.append(None)
+            continue
+        valid = validity_to_bool(b.validity[c], n)
+        d = {"valid": valid if valid is not None else np.zeros(0, bool)}
+        if ty == "i":
+            d["i"] = arr(c, np.int64)
+        elif ty == "f":
+            d["f"] = arr(c, np.float64)
+        elif ty[0] == "B":
+            d["b"] = vals[c]
+        elif ty == "A":
+            ch = arr(c, np.uint8)
+            d["s"] = [(bytes([x]) if x else b"") if valid[i] else None for i, x in enumerate(ch)]
+        else:
+            d["s"] = vals[c]
+        tags.append(d)
+    out["tags"] = tags
+    return out
+
+
 def batch_to_columns(bf, b):
     """One dh_bam_batch -> dict of numpy arrays / lists of bytes (None = NULL)."""
+    if b.layout == COMPACT:
+        return _compact_batch_to_columns(bf, b)
     n = int(b.n_rows)
     out = {"n": n}
     for c, name in enumerate(CORE_NAMES):
@@ -238,7 +384,7 @@ def batch_to_columns(bf, b):
 
 
 def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, batch_rows=0, carry=0, index=None,
-             regions=None, contigs=None, aux_map=None):
+             regions=None, contigs=None, aux_map=None, compact=False, filt=None):
     """Whole scan -> one dict of columns in row order (test/inspection helper; the product API is batch-wise).
     index = index file bytes; with it, regions = list of region strings, or contigs = (tid_lo, tid_hi) / True."""
     with BamFile(ctx, data) as bf:
@@ -246,6 +392,10 @@ def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, 
         if aux_map is not None:          # aux_map = iterable of excluded tags (may be empty)
             bf.set_aux_map(True, aux_map)
         bf.configure(seg_comp, batch_rows, carry)
+        if compact:
+            bf.set_mode(compact=True)
+        if filt:
+            bf.set_filter(*filt)
         if index is not None:
             with Index(ctx, index) as ix:
                 if regions is not None:

@@ -309,11 +309,22 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
         int rc = parse_record(u, off, p.seg_end, p.is_final != 0, t.n_ref, r);
         if (rc != 0) { w.stop = rc; break; }
         if (p.filt_mode && !region_pass(p, r)) { off = r.end; continue; }   // hts_itr_next / hts_itr_multi_next overlap test
+        // N3 predicate pushdown (dh_bam_set_filter): the conjunction of flag tests and the MAPQ floor
+        if ((r.flag & t.flag_require) != t.flag_require || (r.flag & t.flag_exclude) != 0u || r.mapq < t.min_mapq) { off = r.end; continue; }
         uint64_t need = 0;
-        if ((t.col_mask >> COL_QNAME) & 1ull) need += slot_bytes(r.l_qname);
-        if ((t.col_mask >> COL_CIGAR) & 1ull) need += slot_bytes(r.cigar_text_len);
-        if ((t.col_mask >> COL_SEQ) & 1ull) need += slot_bytes((uint32_t)r.l_qseq);
-        if (((t.col_mask >> COL_QUAL) & 1ull) && !qual_absent(u, r)) need += slot_bytes((uint32_t)r.l_qseq);
+        const bool compact = t.compact != 0u;
+        if (compact) {   // every string has a slot (bytes padded to 4), "*" placeholders included: compact_slots() below
+            const uint32_t L = (uint32_t)r.l_qseq;
+            if ((t.col_mask >> COL_QNAME) & 1ull) need += align4(r.l_qname);
+            if ((t.col_mask >> COL_CIGAR) & 1ull) need += align4(r.cig_n ? r.cigar_text_len : 1u);
+            if ((t.col_mask >> COL_SEQ) & 1ull) need += align4(L ? L : 1u);
+            if ((t.col_mask >> COL_QUAL) & 1ull) need += align4(qual_absent(u, r) ? 1u : L);
+        } else {
+            if ((t.col_mask >> COL_QNAME) & 1ull) need += slot_bytes(r.l_qname);
+            if ((t.col_mask >> COL_CIGAR) & 1ull) need += slot_bytes(r.cigar_text_len);
+            if ((t.col_mask >> COL_SEQ) & 1ull) need += slot_bytes((uint32_t)r.l_qseq);
+            if (((t.col_mask >> COL_QUAL) & 1ull) && !qual_absent(u, r)) need += slot_bytes((uint32_t)r.l_qseq);
+        }
         if (want_aux_strings && r.end - r.aux > 2) {
             // every Z/H value longer than 12 bytes whose tag is a projected string column gets a slot
             int64_t s = r.aux + 2;
@@ -328,13 +339,13 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
                 uint32_t ty = ld8(u, s);
                 if (nx != NONE && complete && (ty == 'Z' || ty == 'H')) {
                     uint32_t len = (uint32_t)(nx - 1 - (s + 1));
-                    if (len > 12u) {
+                    if (len > (compact ? 0u : 12u)) {
                         uint32_t t0 = ld8(u, s - 2), t1 = ld8(u, s - 1);
-                        bool wanted = (t0 == 'R' && t1 == 'G' && ((t.col_mask >> COL_RG) & 1ull));
-                        for (uint32_t k = 0; k < t.n_tags && !wanted; ++k)
-                            wanted = t.tags[k].t0 == t0 && t.tags[k].t1 == t1 && t.tags[k].type == 'Z' &&
-                                     t.tags[k].want;
-                        if (wanted) need += align4(len);
+                        // one slot per destination column: READ_GROUP_ID and an RG tag column each get their own copy
+                        uint32_t wanted = (t0 == 'R' && t1 == 'G' && ((t.col_mask >> COL_RG) & 1ull)) ? 1u : 0u;
+                        for (uint32_t k = 0; k < t.n_tags; ++k)
+                            wanted += (t.tags[k].t0 == t0 && t.tags[k].t1 == t1 && t.tags[k].type == 'Z' && t.tags[k].want) ? 1u : 0u;
+                        need += (uint64_t)wanted * align4(len);
                     }
                 }
                 if (nx != NONE && ty == 'B') {   // children of a projected B-array LIST column: 8 bytes each (+4 to reach 8-byte alignment)
@@ -777,6 +788,313 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
 
 
 // =======================================================================================================
+// columnar decode, COMPACT WIRE LAYOUT (DH_BAM_COMPACT_OUTPUT, include/duckhts_cuda.h): same conversions, fewer bytes
+// =======================================================================================================
+// Same step structure as bam_decode_kernel.  What leaves differs: BAM's 32-bit fields stay 32-bit, dictionary columns are
+// codes, and a VARCHAR cell is a 4-byte length with the bytes in the row's heap slots (every string, short ones too;
+// slots 4-byte aligned, rec_off[row] = first slot).  514 -> ~410 bytes per record on the WGS-like bench file: the
+// device-to-host link is the binding resource of the scan, and the host touches every cell anyway when it fills DuckDB's vectors.
+constexpr uint32_t LEN_FLAG = 0x80000000u;   // QNAME / QUAL length words: the value ends at an embedded NUL (host: strnlen)
+__device__ __forceinline__ void put_short(uint8_t *dst, uint32_t len, uint32_t w0, uint32_t w1, uint32_t w2) {
+    uint32_t *d = reinterpret_cast<uint32_t *>(dst);
+    if (len > 0u) d[0] = w0;
+    if (len > 4u) d[1] = w1;
+    if (len > 8u) d[2] = w2;
+}
+
+__global__ void __launch_bounds__(128) bam_decode_compact_kernel(const __grid_constant__ DecodeParams p, const ScanTables t) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t bi = p.b_lo + blockIdx.x * 4u + (threadIdx.x >> 5);
+    if (bi >= p.b_hi) return;
+    const uint32_t count = p.walk[bi].count;
+    if (!count) return;
+    const uint8_t *u = p.u;
+    const int64_t bstart = p.blk_start[bi];
+    const uint16_t *rec = p.rec + ((bstart - p.rec_bias) / 36 + (int64_t)bi);
+    const uint64_t mask = t.col_mask;
+    const bool cQ = (mask >> COL_QNAME) & 1, cC = (mask >> COL_CIGAR) & 1, cS = (mask >> COL_SEQ) & 1, cU = (mask >> COL_QUAL) & 1,
+               cRG = (mask >> COL_RG) & 1, cSM = (mask >> COL_SAMPLE) & 1;
+    const bool any_tag_cols = t.any_tag_cols != 0;
+    uint32_t row0 = p.row_base[bi];
+    uint64_t hp = p.heap_base[bi];
+
+    for (uint32_t g = 0; g < count; g += 32u, row0 += 32u) {
+        const uint32_t cnt = count - g < 32u ? count - g : 32u;
+        const bool act = lane < cnt;
+        const uint32_t row = row0 + lane;
+        // ---------------- A: own record, fixed-width columns at BAM's own widths ----------------
+        Rec r;
+        r.off = r.end = r.qname = r.cigar = r.seq = r.qual = r.aux = 0;
+        r.cg_lo = r.cg_hi = NONE;
+        r.block_len = r.n_cigar = r.cig_n = r.flag = r.mapq = r.cigar_text_len = 0u;
+        r.l_qname = 1u;
+        r.tid = r.pos = r.mtid = r.mpos = r.isize = -1;
+        r.l_qseq = 0;
+        uint32_t roff = 0;
+        if (act) {
+            roff = rec[g + lane];
+            parse_record(u, bstart + roff, INT64_MAX / 2, false, t.n_ref, r);
+            if ((mask >> COL_FLAG) & 1) reinterpret_cast<uint16_t *>(p.col[COL_FLAG])[row] = (uint16_t)r.flag;
+            if ((mask >> COL_POS) & 1) reinterpret_cast<int32_t *>(p.col[COL_POS])[row] = r.pos;
+            if ((mask >> COL_MAPQ) & 1) p.col[COL_MAPQ][row] = (uint8_t)r.mapq;
+            if ((mask >> COL_PNEXT) & 1) reinterpret_cast<int32_t *>(p.col[COL_PNEXT])[row] = r.mpos;
+            if ((mask >> COL_TLEN) & 1) reinterpret_cast<int32_t *>(p.col[COL_TLEN])[row] = r.isize;
+            if ((mask >> COL_RNAME) & 1) reinterpret_cast<int32_t *>(p.col[COL_RNAME])[row] = r.tid >= 0 ? r.tid : -1;
+            if ((mask >> COL_RNEXT) & 1) reinterpret_cast<int32_t *>(p.col[COL_RNEXT])[row] = r.mtid >= 0 ? r.mtid : -1;
+        }
+        const uint32_t L = (uint32_t)r.l_qseq;
+        const bool absent = !act || qual_absent(u, r);
+        uint32_t qn = r.l_qname;   // strlen of the name within l_qname bytes
+        if (act && cQ) {
+            for (uint32_t k = 0; k < r.l_qname; k += 4u) {
+                const uint32_t z = first_zero_byte(ld32u(u, r.qname + k));
+                if (z < 4u) { if (k + z < qn) qn = k + z; break; }
+            }
+        }
+        // ---------------- B: heap slots (the rules of the walk; every string has one) ----------------
+        const uint32_t ce = r.cig_n ? r.cigar_text_len : 1u, se = L ? L : 1u, ue = absent ? 1u : L;
+        const uint32_t s_q = cQ ? align4(r.l_qname) : 0u, s_c = cC ? align4(ce) : 0u, s_s = cS ? align4(se) : 0u, s_u = cU ? align4(ue) : 0u;
+        uint32_t need = act ? s_q + s_c + s_s + s_u : 0u;
+        const uint32_t aux_slot0 = need;
+        int64_t h_rg = NONE;
+        int32_t z_rg = -1;
+        if (act && (cRG || cSM)) {
+            h_rg = aux_find(u, r, 'R' | ('G' << 8));
+            z_rg = aux_zlen(u, r, h_rg);
+        }
+        if (act && any_tag_cols)
+            for (uint32_t k = 0; k < t.n_tags; ++k) {
+                if ((t.tags[k].type != 'Z' && t.tags[k].type != 'B') || !t.tags[k].want) continue;
+                const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
+                if (t.tags[k].type == 'B') {
+                    if (a != NONE && ld8(u, a) == 'B') need += 4u + 8u * ld32u(u, a + 2);
+                    continue;
+                }
+                const int32_t zl = aux_zlen(u, r, a);
+                if (zl > 0) need += align4((uint32_t)zl);
+            }
+        if (act && cRG && z_rg > 0) need += align4((uint32_t)z_rg);
+        uint32_t incl = need;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, sft); if (lane >= (uint32_t)sft) incl += v; }
+        const uint32_t rel = incl - need;
+        const uint32_t total = __shfl_sync(FULL, incl, 31);
+        if (act) p.rec_off[row] = (uint32_t)(hp + rel);
+        // ---------------- C: strings longer than 12 bytes, record by record, whole warp ----------------
+        uint32_t qcut = L;
+        const uint32_t lqnc = r.l_qname | (r.n_cigar << 8), lab = L | (absent ? 0x80000000u : 0u);
+        for (uint32_t q = 0; q < cnt; ++q) {
+            const uint32_t o_ = __shfl_sync(FULL, roff, q), lq_ = __shfl_sync(FULL, lqnc, q), la_ = __shfl_sync(FULL, lab, q),
+                           ct_ = __shfl_sync(FULL, r.cigar_text_len, q), rel_ = __shfl_sync(FULL, rel, q), cn = __shfl_sync(FULL, r.cig_n, q);
+            const uint32_t lqn = lq_ & 0xffu, ncg = lq_ >> 8, Lq = la_ & 0x7fffffffu;
+            const bool abs_ = (la_ >> 31) != 0u;
+            const int64_t qname = bstart + o_ + 36, seq = qname + lqn + 4ll * ncg, qual = seq + (((int64_t)Lq + 1) >> 1);
+            uint8_t *slot = p.heap + hp + rel_;
+            if (cQ) {
+                if (lqn > 12u) {
+                    uint32_t *d = reinterpret_cast<uint32_t *>(slot);
+                    for (uint32_t k = lane; 4u * k < lqn; k += 32u) d[k] = mask_bytes(ld32u(u, qname + 4ll * k), lqn - 4u * k);
+                }
+                slot += align4(lqn);
+            }
+            if (cC) {
+                if (cn && ct_ > 12u) {
+                    const int64_t cig = bstart + __shfl_sync(FULL, (int32_t)(r.cigar - bstart), q);
+                    uint32_t base = 0;
+                    for (uint32_t k0 = 0; k0 < cn; k0 += 32u) {
+                        const uint32_t k = k0 + lane;
+                        uint32_t c = 0, dgt = 0;
+                        if (k < cn) { c = ld32u(u, cig + 4ll * k); dgt = dec_digits(c >> 4) + 1u; }
+                        uint32_t inc = dgt;
+#pragma unroll
+                        for (int sft = 1; sft < 32; sft <<= 1) { const uint32_t v = __shfl_up_sync(FULL, inc, sft); if (lane >= (uint32_t)sft) inc += v; }
+                        if (k < cn) {
+                            uint32_t v = c >> 4, at = base + inc - 1u;
+                            slot[at] = (uint8_t)"MIDNSHP=XB??????"[c & 15u];
+                            for (uint32_t j = dgt - 1u; j-- > 0;) { slot[--at] = (uint8_t)('0' + v % 10u); v /= 10u; }
+                        }
+                        base += __shfl_sync(FULL, inc, 31);
+                    }
+                }
+                slot += align4(cn ? ct_ : 1u);
+            }
+            if (cS) {
+                if (Lq > 12u) {
+                    uint32_t *d = reinterpret_cast<uint32_t *>(slot);
+                    for (uint32_t k = lane; 8u * k < Lq; k += 32u) {
+                        const uint32_t pk = ld32u(u, seq + 4ll * k);
+                        d[2u * k] = mask_bytes(seq4(pk & 0xffffu), Lq - 8u * k);
+                        if (8u * k + 4u < Lq) d[2u * k + 1u] = mask_bytes(seq4(pk >> 16), Lq - 8u * k - 4u);
+                    }
+                }
+                slot += align4(Lq ? Lq : 1u);
+            }
+            if (cU) {
+                if (!abs_ && Lq > 12u) {
+                    uint32_t *d = reinterpret_cast<uint32_t *>(slot);
+                    uint32_t zpos = 0xffffffffu;
+                    for (uint32_t k = lane; 8u * k < Lq; k += 32u) {
+                        const uint32_t a = mask_bytes(qual4(ld32u(u, qual + 8ll * k)), Lq - 8u * k) | (Lq - 8u * k < 4u ? 0xffffffffu << (8u * (Lq - 8u * k)) : 0u);
+                        d[2u * k] = mask_bytes(a, Lq - 8u * k);
+                        uint32_t z = first_zero_byte(a);
+                        if (z < 4u && zpos == 0xffffffffu) zpos = 8u * k + z;
+                        if (8u * k + 4u < Lq) {
+                            const uint32_t rem = Lq - 8u * k - 4u;
+                            const uint32_t b = mask_bytes(qual4(ld32u(u, qual + 8ll * k + 4)), rem) | (rem < 4u ? 0xffffffffu << (8u * rem) : 0u);
+                            d[2u * k + 1u] = mask_bytes(b, rem);
+                            z = first_zero_byte(b);
+                            if (z < 4u && zpos == 0xffffffffu) zpos = 8u * k + 4u + z;
+                        }
+                    }
+                    zpos = __reduce_min_sync(FULL, zpos);
+                    if (lane == q && zpos < qcut) qcut = zpos;
+                }
+                slot += align4(abs_ ? 1u : Lq);
+            }
+        }
+        __syncwarp();
+        // ---------------- D: short strings and length words of the lane's own row ----------------
+        uint8_t *const slot0 = p.heap + hp + rel;
+        if (act) {
+            uint8_t *hs = slot0;
+            if (cQ) {
+                if (r.l_qname <= 12u) { uint32_t w0, w1, w2; inline_words(u, r.qname, r.l_qname, w0, w1, w2); put_short(hs, r.l_qname, w0, w1, w2); }
+                reinterpret_cast<uint32_t *>(p.col[COL_QNAME])[row] = r.l_qname | (qn != r.l_qname - 1u ? LEN_FLAG : 0u);
+                hs += s_q;
+            }
+            if (cC) {
+                if (r.cig_n == 0u) put_short(hs, 1u, '*', 0u, 0u);
+                else if (ce <= 12u) { uint32_t w0, w1, w2; cigar_inline(u, r, w0, w1, w2); put_short(hs, ce, w0, w1, w2); }
+                reinterpret_cast<uint32_t *>(p.col[COL_CIGAR])[row] = ce;
+                hs += s_c;
+            }
+            if (cS) {
+                if (L == 0u) put_short(hs, 1u, '*', 0u, 0u);
+                else if (L <= 12u) {
+                    const uint32_t p0 = ld32u(u, r.seq), p1 = L > 8u ? ld32u(u, r.seq + 4) : 0u;
+                    put_short(hs, L, mask_bytes(seq4(p0 & 0xffffu), L), L > 4u ? mask_bytes(seq4(p0 >> 16), L - 4u) : 0u,
+                              L > 8u ? mask_bytes(seq4(p1 & 0xffffu), L - 8u) : 0u);
+                }
+                reinterpret_cast<uint32_t *>(p.col[COL_SEQ])[row] = se;
+                hs += s_s;
+            }
+            if (cU) {
+                uint32_t cut = qcut;
+                if (absent) put_short(hs, 1u, '*', 0u, 0u);
+                else if (L <= 12u) {
+                    const uint32_t w0 = mask_bytes(qual4(ld32u(u, r.qual)), L), w1 = L > 4u ? mask_bytes(qual4(ld32u(u, r.qual + 4)), L - 4u) : 0u,
+                                   w2 = L > 8u ? mask_bytes(qual4(ld32u(u, r.qual + 8)), L - 8u) : 0u;
+                    put_short(hs, L, w0, w1, w2);
+                    uint32_t z = first_zero_byte(w0 | (L < 4u ? 0xffffffffu << (8u * L) : 0u));
+                    if (z < 4u) cut = z;
+                    else if (L > 4u && (z = first_zero_byte(w1 | (L < 8u ? 0xffffffffu << (8u * (L - 4u)) : 0u))) < 4u) cut = 4u + z;
+                    else if (L > 8u && (z = first_zero_byte(w2 | (L < 12u ? 0xffffffffu << (8u * (L - 8u)) : 0u))) < 4u) cut = 8u + z;
+                }
+                reinterpret_cast<uint32_t *>(p.col[COL_QUAL])[row] = absent ? 1u : (L | (cut != L ? LEN_FLAG : 0u));
+                hs += s_u;
+            }
+        }
+        // typed standard tags
+        uint8_t *hz = slot0 + aux_slot0;
+        if (any_tag_cols)
+            for (uint32_t k = 0; k < t.n_tags; ++k) {
+                const int c = BAM_CORE_COLS + (int)k;
+                if (!t.tags[k].want) continue;
+                const uint32_t ty_req = t.tags[k].type;
+                bool valid = false;
+                if (act) {
+                    const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
+                    if (ty_req == 'B') {
+                        uint64_t off8 = 0, len = 0;
+                        if (a != NONE && ld8(u, a) == 'B') {
+                            valid = true;
+                            const uint32_t sub = ld8(u, a + 1);
+                            len = ld32u(u, a + 2);
+                            const uint64_t ho = (uint64_t)(hz - p.heap), h8 = (ho + 7ull) & ~7ull;
+                            off8 = h8 >> 3;
+                            unsigned long long *dst = reinterpret_cast<unsigned long long *>(p.heap + h8);
+                            for (uint32_t e = 0; e < len; ++e) {
+                                long long iv = 0;
+                                bool is_int = true;
+                                switch (sub) {
+                                case 'c': iv = (int8_t)ld8(u, a + 6 + e); break;
+                                case 'C': iv = ld8(u, a + 6 + e); break;
+                                case 's': iv = (int16_t)(ld8(u, a + 6 + 2ll * e) | (ld8(u, a + 7 + 2ll * e) << 8)); break;
+                                case 'S': iv = ld8(u, a + 6 + 2ll * e) | (ld8(u, a + 7 + 2ll * e) << 8); break;
+                                case 'i': iv = (int32_t)ld32u(u, a + 6 + 4ll * e); break;
+                                case 'I': iv = ld32u(u, a + 6 + 4ll * e); break;
+                                default: is_int = false; break;
+                                }
+                                if (sub == 'f') dst[e] = (unsigned long long)__double_as_longlong((double)__uint_as_float(ld32u(u, a + 6 + 4ll * e)));
+                                else if (sub == 'd') dst[e] = 0ull;
+                                else dst[e] = is_int ? (unsigned long long)iv : 0ull;
+                            }
+                            hz += 4ull + 8ull * len;
+                        }
+                        reinterpret_cast<ulonglong2 *>(p.col[c])[row] = make_ulonglong2(off8, len);
+                    } else if (ty_req == 'Z') {
+                        const int32_t zl = aux_zlen(u, r, a);
+                        if (zl >= 0) {
+                            valid = true;
+                            if (zl > 0) copy_bytes(hz, u, a + 1, (uint32_t)zl);
+                            hz += align4((uint32_t)zl);
+                        }
+                        reinterpret_cast<uint32_t *>(p.col[c])[row] = zl >= 0 ? (uint32_t)zl : 0u;
+                    } else if (a == NONE) {
+                        if (ty_req == 'A') p.col[c][row] = 0;
+                    } else {
+                        valid = true;
+                        const uint32_t ty = ld8(u, a);
+                        int64_t iv = 0;
+                        bool is_int = true;
+                        switch (ty) {
+                        case 'c': iv = (int8_t)ld8(u, a + 1); break;
+                        case 'C': iv = ld8(u, a + 1); break;
+                        case 's': iv = (int16_t)(ld8(u, a + 1) | (ld8(u, a + 2) << 8)); break;
+                        case 'S': iv = ld8(u, a + 1) | (ld8(u, a + 2) << 8); break;
+                        case 'i': iv = (int32_t)ld32u(u, a + 1); break;
+                        case 'I': iv = ld32u(u, a + 1); break;
+                        default: is_int = false; break;
+                        }
+                        if (ty_req == 'i') reinterpret_cast<int64_t *>(p.col[c])[row] = iv;
+                        else if (ty_req == 'f') {
+                            double dv;
+                            if (ty == 'd') dv = __longlong_as_double(((long long)ld32u(u, a + 5) << 32) | ld32u(u, a + 1));
+                            else if (ty == 'f') dv = (double)__uint_as_float(ld32u(u, a + 1));
+                            else dv = is_int ? (double)iv : 0.0;
+                            reinterpret_cast<double *>(p.col[c])[row] = dv;
+                        } else p.col[c][row] = ty == 'A' ? (uint8_t)ld8(u, a + 1) : (uint8_t)0;
+                    }
+                }
+                set_valid_group(p.valid[c], row0, __ballot_sync(FULL, valid), lane);
+            }
+        if (cRG) {
+            if (act) {
+                if (z_rg > 0) copy_bytes(hz, u, h_rg + 1, (uint32_t)z_rg);
+                reinterpret_cast<uint32_t *>(p.col[COL_RG])[row] = z_rg >= 0 ? (uint32_t)z_rg : 0u;
+            }
+            set_valid_group(p.valid[COL_RG], row0, __ballot_sync(FULL, act && z_rg >= 0), lane);
+        }
+        if (cSM) {
+            int found = -1;
+            if (act && z_rg >= 0)
+                for (uint32_t e = 0; e < t.n_rg && found < 0; ++e) {
+                    if (t.rg[e].id_len != (uint32_t)z_rg) continue;
+                    const uint8_t *id = t.rg_ids + t.rg[e].id_off;
+                    bool m = true;
+                    for (int32_t q = 0; q < z_rg && m; ++q) m = id[q] == ld8(u, h_rg + 1 + q);
+                    if (m) found = (int)e;
+                }
+            const bool ok = found >= 0 && t.rg[found].has_sample;
+            if (act) reinterpret_cast<int32_t *>(p.col[COL_SAMPLE])[row] = ok ? found : -1;
+            set_valid_group(p.valid[COL_SAMPLE], row0, __ballot_sync(FULL, ok), lane);
+        }
+        hp += total;
+    }
+}
+
+
+// =======================================================================================================
 // AUXILIARY_TAGS MAP column (A16)
 // =======================================================================================================
 // printf("%g") of a double, exactly as glibc rounds it (correct rounding of the exact binary value, ties to even): the six
@@ -1049,6 +1367,11 @@ cudaError_t launch_bam_auxmap(const AuxMapParams &p, const ScanTables &t, cudaSt
 cudaError_t launch_bam_decode(const DecodeParams &p, const ScanTables &t, cudaStream_t stream) {
     if (p.b_hi <= p.b_lo) return cudaSuccess;
     bam_decode_kernel<<<(p.b_hi - p.b_lo + 3u) / 4u, 128, 0, stream>>>(p, t);
+    return cudaGetLastError();
+}
+cudaError_t launch_bam_decode_compact(const DecodeParams &p, const ScanTables &t, cudaStream_t stream) {
+    if (p.b_hi <= p.b_lo) return cudaSuccess;
+    bam_decode_compact_kernel<<<(p.b_hi - p.b_lo + 3u) / 4u, 128, 0, stream>>>(p, t);
     return cudaGetLastError();
 }
 

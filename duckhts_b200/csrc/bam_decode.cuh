@@ -43,9 +43,11 @@ struct ScanTables {
     uint32_t n_tags;
     uint32_t any_tag_cols;     // any tag column projected
     uint32_t aux_map;          // the AUXILIARY_TAGS MAP column is projected (A16)
-    uint32_t pad;
+    uint32_t compact;          // compact wire layout (DH_BAM_COMPACT_OUTPUT): heap slots for every string, 4-byte aligned
     const uint32_t *aux_excl;  // 65,536-bit set of tags (t0 | t1 << 8) left out of the MAP (the standard_tags columns), or nullptr
     uint64_t col_mask;         // bit c set = core column c projected (tag columns: TagReq.want)
+    // N3 predicate pushdown (dh_bam_set_filter): FLAG bits that must be set / clear, MAPQ floor; all 0 = none
+    uint32_t flag_require, flag_exclude, min_mapq, pad2;
 };
 
 // per BGZF block result of the boundary walk (device -> host)
@@ -99,6 +101,7 @@ struct DecodeParams {
     unsigned long long *valid[BAM_MAX_COLS];  // validity words (bit = 1 valid); nullptr = column has no NULLs
     uint8_t *heap;                // device heap
     uint64_t heap_host;           // host address the heap will be copied to
+    uint32_t *rec_off;            // compact layout: heap offset of each row's slots (nullptr in the DuckDB layout)
 };
 
 // AUXILIARY_TAGS MAP(VARCHAR, VARCHAR) column (bam_reader.c:967-1031): one list entry per row, key / value cells per pair
@@ -122,5 +125,43 @@ struct AuxMapParams {
 cudaError_t launch_bam_auxmap(const AuxMapParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_decode(const DecodeParams &p, const ScanTables &t, cudaStream_t stream);
+cudaError_t launch_bam_decode_compact(const DecodeParams &p, const ScanTables &t, cudaStream_t stream);
+
+// ---- per-column checksums of a batch (dh_bam_batch_checksum) ----------------------------------------------------------
+// One definition for the device kernel, the host threads and the test-side restatement: cell hash = mix64 of the value
+// (fixed width), of a Horner polynomial over the bytes (strings) or over the 8-byte children (lists); NULL = a constant.
+constexpr uint64_t CK_NULL = 0x9e3779b97f4a7c15ull, CK_K = 0x100000001b3ull;
+__host__ __device__ inline uint64_t ck_mix(uint64_t x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31;
+    return x;
+}
+__host__ __device__ inline uint64_t ck_bytes(const uint8_t *p, uint32_t n) {
+    uint64_t h = 0;
+    for (uint32_t i = 0; i < n; ++i) h = h * CK_K + (uint64_t)p[i] + 1ull;
+    return ck_mix(h ^ ((uint64_t)n * CK_NULL));
+}
+__host__ __device__ inline uint64_t ck_words(const uint64_t *p, uint64_t n) {
+    uint64_t h = 0;
+    for (uint64_t i = 0; i < n; ++i) h = h * CK_K + p[i] + 1ull;
+    return ck_mix(h ^ (n * CK_NULL));
+}
+enum { CK_SKIP = 0, CK_U16, CK_MAPQ, CK_POS, CK_TLEN, CK_STR, CK_DICT, CK_SAMPLE, CK_TAG_I, CK_TAG_F, CK_TAG_A, CK_TAG_B };
+struct ChecksumParams {
+    DecodeParams dp;              // column pointers of the batch (device or host addresses, all on one side)
+    uint64_t n_rows;
+    uint64_t heap_bytes;
+    uint32_t compact;
+    uint32_t n_cols;
+    uint8_t kind[BAM_MAX_COLS];   // CK_* per column
+    const uint64_t *ref_hash;     // n_ref + 1 hashes of the contig names ([n_ref] = "*"): compact RNAME / RNEXT
+    const uint64_t *sample_hash;  // per @RG entry: hash of its SM value: compact SAMPLE_ID
+    const uint64_t *dict_ptr;     // DuckDB layout: host addresses of dictionary strings longer than 12 bytes, sorted ...
+    const uint64_t *dict_hash;    // ... and their hashes
+    uint32_t n_dict;
+    int32_t n_ref;
+    uint64_t *sums;               // BAM_MAX_COLS accumulators
+};
+cudaError_t launch_bam_checksum(const ChecksumParams &p, cudaStream_t stream);
+void bam_checksum_host(const ChecksumParams &p, int n_threads);
 
 }  // namespace dh

@@ -20,6 +20,8 @@
 //     back-references re-read the group's own recent output through L1/L2.
 //   * After end-of-stream the group computes CRC-32 over its output in 8 parallel segments
 //     (slice-by-8 tables shared by the CTA) and merges them with GF(2) polynomial shifts.
+#include <mutex>
+
 #include "bgzf_inflate.cuh"
 #include "crc32_core.cuh"
 #include "inflate_core.cuh"
@@ -306,15 +308,23 @@ bgzf_inflate_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restric
 
 cudaError_t launch_bgzf_inflate(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out,
                                 int *status, unsigned int *counter, int sm_count, cudaStream_t stream, bool only_flagged) {
-    static bool configured = false;
+    // the attribute is per device (one process may drive several GPUs, one dh_ctx each) and set once per device
+    static std::mutex mu;
+    static bool configured[64] = {};
     const size_t smem = sizeof(CtaSmem);
-    if (!configured) {
-        cudaError_t e =
-            cudaFuncSetAttribute(bgzf_inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = true;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!configured[dev]) {
+            e = cudaFuncSetAttribute(bgzf_inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+            configured[dev] = true;
+        }
     }
-    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream);
+    e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     if (nblocks == 0) return cudaSuccess;
     // persistent: one CTA per SM; fewer if there is not enough work for every lane-group

@@ -29,6 +29,8 @@
 //     256-entry tables) and compares CRC and ISIZE with the BGZF footer.
 // Streams whose tables do not fit the 892-entry pool either (litlen > 640 or litlen + distance > 892 entries; never
 // seen from zlib/libdeflate) stay flagged INF_NEEDS_V1 and are redone by the lane-group kernel (bgzf_inflate.cu).
+#include <mutex>
+
 #include "bgzf_inflate.cuh"
 #include "crc32_core.cuh"
 #include "inflate_core.cuh"
@@ -894,19 +896,23 @@ static void build_crc3_tables(uint32_t *t) {
 
 cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
                                    uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream, cudaEvent_t between_phases) {
+    static std::mutex mu;
     static bool ready[64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    if (!ready[dev]) {
-        static uint32_t host_tabs[CRC3_WORDS];
-        build_crc3_tables(host_tabs);
-        e = cudaMemcpyToSymbol(g_crc3, host_tabs, sizeof host_tabs);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(bgzf_decode3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P1_SMEM);
-        if (e != cudaSuccess) return e;
-        ready[dev] = true;
+    {
+        std::lock_guard<std::mutex> lk(mu);   // several contexts (threads, devices) may arrive here at once
+        if (!ready[dev]) {
+            static uint32_t host_tabs[CRC3_WORDS];
+            build_crc3_tables(host_tabs);
+            e = cudaMemcpyToSymbol(g_crc3, host_tabs, sizeof host_tabs);
+            if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(bgzf_decode3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P1_SMEM);
+            if (e != cudaSuccess) return e;
+            ready[dev] = true;
+        }
     }
     e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;

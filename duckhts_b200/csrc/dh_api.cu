@@ -1,11 +1,16 @@
 // dh_api.cu — C-ABI of libduckhts_cuda.so: contexts, BGZF framing (A1), inflate entry points (A2/A3).
 // Declarations and the reference interfaces each one replaces: include/duckhts_cuda.h.
+#include <errno.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <algorithm>
+#include <thread>
+#include <vector>
 
 #include "dh_internal.h"
 #include "inflate_core.cuh"
@@ -43,8 +48,8 @@ int PinBuf::reserve(size_t n) {
     if (n <= cap) return DH_OK;
     release();
     size_t want = std::max(n, (size_t)1 << 16);
-    cudaError_t e = cudaMallocHost(&p, want);
-    if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMallocHost"); }
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocPortable);
+    if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaHostAlloc"); }
     cap = want;
     return DH_OK;
 }
@@ -185,7 +190,7 @@ void dh_ctx_destroy(dh_ctx *c) {
     for (int i = 0; i < 3; ++i) {
         auto &s = c->slots[i];
         s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release();
-        s.h_desc.release(); s.h_status.release();
+        s.h_desc.release(); s.h_status.release(); s.h_comp.release(); s.h_out.release();
         if (s.ev_k0) cudaEventDestroy(s.ev_k0);
         if (s.ev_k1) cudaEventDestroy(s.ev_k1);
         if (s.ev_done) cudaEventDestroy(s.ev_done);
@@ -205,7 +210,8 @@ uint64_t dh_ctx_launch_count(const dh_ctx *c) { return c ? c->launches : 0; }
 
 void *dh_host_alloc(size_t bytes) {
     void *p = nullptr;
-    cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 1);
+    // portable: pinned for every context of the process (one image feeds the pipelines of several GPUs)
+    cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
     if (e != cudaSuccess) { cuda_fail(e, "cudaMallocHost"); return nullptr; }
     return p;
 }
@@ -346,6 +352,169 @@ int dh_bgzf_inflate_host(dh_ctx *c, const uint8_t *comp, uint64_t comp_size, uin
     st->kernel_ms = kernel_ms;
     if (rc != DH_OK) return rc;
     if (st->bad_block >= 0) {
+        set_error("BGZF block %lld failed inflate/CRC check (code %d)", (long long)st->bad_block, st->bad_code);
+        return DH_EDATA;
+    }
+    return DH_OK;
+}
+
+// ---- A2/A3 file -> file, streaming (bgunzip) ---------------------------------------------------------------
+// pread / pwrite of one big range by a few threads: one thread moves page-cache bytes at a fraction of what the GPU takes
+static bool parallel_io(int fd, uint8_t *buf, uint64_t n, uint64_t off, bool write) {
+    if (n == 0) return true;
+    int nt = (int)std::min<uint64_t>(8, (n + (32ull << 20) - 1) / (32ull << 20));
+    std::vector<int> ok((size_t)nt, 1);
+    auto work = [&](int t) {
+        uint64_t lo = n * (uint64_t)t / (uint64_t)nt, hi = n * (uint64_t)(t + 1) / (uint64_t)nt;
+        while (lo < hi) {
+            const size_t want = (size_t)std::min<uint64_t>(hi - lo, 64ull << 20);
+            const ssize_t k = write ? pwrite(fd, buf + lo, want, (off_t)(off + lo)) : pread(fd, buf + lo, want, (off_t)(off + lo));
+            if (k < 0 && errno == EINTR) continue;
+            if (k <= 0) { ok[(size_t)t] = 0; return; }
+            lo += (uint64_t)k;
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    for (int v : ok) if (!v) return false;
+    return true;
+}
+
+int dh_bgzf_inflate_fd(dh_ctx *c, int in_fd, int out_fd, dh_inflate_stats *st) {
+    if (!c || in_fd < 0 || out_fd < 0) { set_error("dh_bgzf_inflate_fd: bad arguments"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(c->device));
+    dh_inflate_stats local;
+    if (!st) st = &local;
+    memset(st, 0, sizeof *st);
+    st->bad_block = -1;
+    struct stat sb;
+    if (fstat(in_fd, &sb) != 0) { set_error("fstat: %s", strerror(errno)); return DH_EIO; }
+    const uint64_t fsize = (uint64_t)sb.st_size;
+    // per segment: compressed bytes read, inflated bytes written (DH_FD_SEG_MB shrinks both: tests drive many segments through small files)
+    static const uint64_t seg_mb = getenv("DH_FD_SEG_MB") ? std::max(1, atoi(getenv("DH_FD_SEG_MB"))) : 192;
+    const uint64_t F_COMP = seg_mb << 20, F_OUT = 4 * F_COMP;
+
+    cudaEvent_t ev_begin, ev_end;
+    DH_CUDA(cudaEventCreate(&ev_begin));
+    DH_CUDA(cudaEventCreate(&ev_end));
+    DH_CUDA(cudaEventRecord(ev_begin, c->copy_streams[0]));
+    struct Pending { uint64_t blk0, nblk, out_off, obytes; bool live; };
+    Pending pend[3] = {};
+    float kernel_ms = 0.f;
+    int rc = DH_OK;
+    // wait for a segment, check its blocks, write its bytes
+    auto retire = [&](int slot) -> int {
+        Pending &p = pend[slot];
+        if (!p.live) return DH_OK;
+        auto &s = c->slots[slot];
+        p.live = false;
+        DH_CUDA(cudaEventSynchronize(s.ev_done));
+        float ms = 0.f;
+        DH_CUDA(cudaEventElapsedTime(&ms, s.ev_k0, s.ev_k1));
+        kernel_ms += ms;
+        const int *hs = (const int *)s.h_status.p;
+        uint64_t good = p.obytes;
+        for (uint64_t i = 0; i < p.nblk; ++i)
+            if (hs[i] != 0) {
+                if (st->bad_block < 0) { st->bad_block = (int64_t)(p.blk0 + i); st->bad_code = hs[i]; }
+                good = ((const BlockDesc *)s.h_desc.p)[i].out_off;       // the bytes in front of the failing block are still written
+                break;
+            }
+        if (st->bad_block >= 0 && (uint64_t)st->bad_block < p.blk0) return DH_OK;   // an earlier segment already failed
+        if (!parallel_io(out_fd, (uint8_t *)s.h_out.p, good, p.out_off, true)) { set_error("write: %s", strerror(errno)); return DH_EIO; }
+        return DH_OK;
+    };
+
+    uint64_t foff = 0, out_off = 0, nblocks = 0;
+    int seg = 0;
+    bool format_error = false;
+    while (foff < fsize && rc == DH_OK && st->bad_block < 0) {
+        const int slot = seg % 3;
+        auto &s = c->slots[slot];
+        cudaStream_t strm = c->copy_streams[slot];
+        if ((rc = retire(slot)) != DH_OK || st->bad_block >= 0) break;
+        const uint64_t want = std::min<uint64_t>(F_COMP, fsize - foff);
+        if ((rc = s.h_comp.reserve(F_COMP + 64)) != DH_OK || (rc = s.h_out.reserve(F_OUT + BGZF_MAX_OUT)) != DH_OK) break;
+        if (!parallel_io(in_fd, (uint8_t *)s.h_comp.p, want, foff, false)) { set_error("read: %s", strerror(errno)); rc = DH_EIO; break; }
+        // frame the blocks that lie whole in the buffer (A1); the partial block at its end starts the next segment
+        BlockTable bt;
+        const uint8_t *buf = (const uint8_t *)s.h_comp.p;
+        uint64_t off = 0, u = 0;
+        bt.uoff.push_back(0);
+        while (off < want) {
+            if (want - off < 18) break;
+            if (!bgzf_header_ok(buf + off)) { format_error = true; break; }
+            const uint32_t bsize = (uint32_t)(buf[off + 16] | (buf[off + 17] << 8)) + 1;
+            if (bsize < 18 + 8) { format_error = true; break; }
+            if (want - off < bsize) break;
+            dh_bgzf_block b;
+            b.coffset = off;
+            b.csize = bsize;
+            b.crc = le32(buf + off + bsize - 8);
+            b.isize = le32(buf + off + bsize - 4);
+            b.reserved = 0;
+            if (b.isize > BGZF_MAX_OUT) { format_error = true; break; }
+            if (u + b.isize > F_OUT) break;
+            bt.blocks.push_back(b);
+            u += b.isize;
+            bt.uoff.push_back(u);
+            st->eof_marker = (bsize == 28 && b.isize == 0);
+            off += bsize;
+        }
+        const size_t nb = bt.blocks.size();
+        if (nb == 0) {
+            // nothing whole in front of the end of the file (a cut block) or a bad header: the read error bgzf_read reports
+            if (!format_error && foff + want < fsize) { set_error("internal: no BGZF block fits a segment"); rc = DH_EINVAL; break; }
+            st->bad_block = (int64_t)nblocks;
+            st->bad_code = INF_ERR_HEADER;
+            break;
+        }
+        if ((rc = s.comp.reserve(off + DH_COMP_PAD)) != DH_OK || (rc = s.out.reserve(u + BGZF_MAX_OUT)) != DH_OK ||
+            (rc = s.desc.reserve(nb * sizeof(BlockDesc))) != DH_OK || (rc = s.status.reserve(nb * sizeof(int))) != DH_OK ||
+            (rc = s.h_desc.reserve(nb * sizeof(BlockDesc))) != DH_OK || (rc = s.h_status.reserve(nb * sizeof(int))) != DH_OK)
+            break;
+        const uint64_t cw = fill_descs(bt, 0, nb, 0, 0, 0, (BlockDesc *)s.h_desc.p);
+        DH_CUDA(cudaMemcpyAsync(s.comp.p, buf, off, cudaMemcpyHostToDevice, strm));
+        DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + off, 0, DH_COMP_PAD, strm));
+        DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, nb * sizeof(BlockDesc), cudaMemcpyHostToDevice, strm));
+        DH_CUDA(cudaEventRecord(s.ev_k0, strm));
+        if ((rc = inflate_blocks(c, (const uint8_t *)s.comp.p, (const BlockDesc *)s.desc.p, (uint32_t)nb, cw, (uint8_t *)s.out.p, (int *)s.status.p,
+                                 s.work, (unsigned int *)c->counter.p + 2 + 2 * slot, strm)) != DH_OK)
+            break;
+        DH_CUDA(cudaEventRecord(s.ev_k1, strm));
+        if (u) DH_CUDA(cudaMemcpyAsync(s.h_out.p, s.out.p, u, cudaMemcpyDeviceToHost, strm));
+        DH_CUDA(cudaMemcpyAsync(s.h_status.p, s.status.p, nb * sizeof(int), cudaMemcpyDeviceToHost, strm));
+        DH_CUDA(cudaEventRecord(s.ev_done, strm));
+        pend[slot] = Pending{nblocks, nb, out_off, u, true};
+        nblocks += nb;
+        out_off += u;
+        foff += off;
+        st->comp_bytes += off;
+        ++seg;
+        if (format_error) { st->bad_block = (int64_t)nblocks; st->bad_code = INF_ERR_HEADER; }
+    }
+    // retire in issue order so that bad_block is the FIRST failing block and the bytes in front of it reach the file
+    const int64_t framing_bad = st->bad_block;
+    st->bad_block = -1;
+    for (int i = 0; i < 3; ++i) {
+        const int r2 = retire((seg + i) % 3);
+        if (rc == DH_OK) rc = r2;
+    }
+    if (st->bad_block < 0) st->bad_block = framing_bad;
+    for (int i = 0; i < 3; ++i) cudaStreamSynchronize(c->copy_streams[i]);
+    cudaEventRecord(ev_end, c->copy_streams[0]);
+    cudaEventSynchronize(ev_end);
+    cudaEventElapsedTime(&st->total_ms, ev_begin, ev_end);
+    cudaEventDestroy(ev_begin);
+    cudaEventDestroy(ev_end);
+    st->kernel_ms = kernel_ms;
+    st->n_blocks = nblocks;
+    st->out_bytes = out_off;
+    if (rc != DH_OK) return rc;
+    if (st->bad_block >= 0) {
+        if (st->bad_code == INF_ERR_HEADER) { set_error("invalid or truncated BGZF block %lld", (long long)st->bad_block); return DH_EFORMAT; }
         set_error("BGZF block %lld failed inflate/CRC check (code %d)", (long long)st->bad_block, st->bad_code);
         return DH_EDATA;
     }

@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <deque>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "dh_scan.h"
@@ -35,6 +36,18 @@ uint32_t col_width(const dh_bam *b, int c) {
     return (t == 'i' || t == 'f') ? 8 : 16;
 }
 bool col_nullable(int c) { return c == COL_RG || c == COL_SAMPLE || c >= BAM_CORE_COLS; }
+// compact wire layout (DH_BAM_COMPACT_OUTPUT, include/duckhts_cuda.h)
+uint32_t col_width_compact(const dh_bam *b, int c) {
+    switch (c) {
+    case COL_FLAG: return 2;
+    case COL_MAPQ: return 1;
+    default: break;
+    }
+    if (c < BAM_CORE_COLS) return 4;   // POS, PNEXT, TLEN int32; RNAME, RNEXT, SAMPLE_ID codes; string lengths
+    const char t = (char)b->tags[c - BAM_CORE_COLS].type;
+    return (t == 'i' || t == 'f') ? 8 : t == 'B' ? 16 : t == 'A' ? 1 : 4;
+}
+bool is_compact(const dh_bam *b) { return (b->mode & DH_BAM_COMPACT_OUTPUT) != 0; }
 
 StrCell make_cell(dh_bam *b, const std::string &s) {
     StrCell c;
@@ -125,6 +138,7 @@ void build_dictionaries(dh_bam *b) {
     b->ref_cells.push_back(make_cell(b, "*"));
     b->rg.clear();
     b->rg_ids.clear();
+    b->rg_samples.clear();
     const std::string &t = b->text;
     size_t p = 0;
     while (p < t.size()) {
@@ -153,6 +167,7 @@ void build_dictionaries(dh_bam *b) {
                 e.has_sample = has_sm && !sm.empty();
                 if (e.has_sample) e.sample = make_cell(b, sm);
                 b->rg.push_back(e);
+                b->rg_samples.push_back(e.has_sample ? sm : std::string());
             }
         }
         p = eol + 1;
@@ -184,7 +199,11 @@ int upload_tables(dh_bam *b) {
     t.n_tags = (uint32_t)b->tags.size();
     t.any_tag_cols = any_tag;
     t.aux_map = b->aux_map ? 1u : 0u;
-    t.pad = 0;
+    t.compact = is_compact(b) ? 1u : 0u;
+    t.flag_require = b->flag_require;
+    t.flag_exclude = b->flag_exclude;
+    t.min_mapq = b->min_mapq;
+    t.pad2 = 0;
     t.aux_excl = nullptr;
     if (b->aux_map && !b->aux_excl.empty()) {
         if ((rc = b->d_aux_excl.reserve(b->aux_excl.size() * 4)) != DH_OK) return rc;
@@ -226,14 +245,28 @@ int ensure_events(dh_bam *b) {
             DH_CUDA(cudaEventCreate(&s.ev_walk1));
             DH_CUDA(cudaEventCreate(&s.ev_walk2));
         }
-    for (auto &s : b->bs)
-        if (!s.ev_done) {
+    for (int i = 0; i < b->n_slots; ++i) {
+        BatchSlot &s = b->bs[i];
+        if (s.ev_done) continue;
+        {
             DH_CUDA(cudaEventCreate(&s.ev_k0));
             DH_CUDA(cudaEventCreate(&s.ev_k1));
             DH_CUDA(cudaEventCreate(&s.ev_c0));
             DH_CUDA(cudaEventCreate(&s.ev_done));
         }
+    }
     return DH_OK;
+}
+
+int take_slot(dh_bam *b) {
+    for (int i = 0; i < b->n_slots; ++i)
+        if (b->bs[i].state == SLOT_FREE) return i;
+    return -1;
+}
+int free_slots(const dh_bam *b) {
+    int n = 0;
+    for (int i = 0; i < b->n_slots; ++i) n += b->bs[i].state == SLOT_FREE;
+    return n;
 }
 
 // H2D + inflate of segment k into slot k % NSEG (asynchronous)
@@ -409,7 +442,8 @@ int walk_segment(dh_bam *b, int k) {
     Batch cur{0, 0, 0, 0, b->rows_total};
     for (uint32_t i = 0; i <= last; ++i) {
         const BlockWalk &w = hw[i];
-        if (cur.rows > 0 && cur.rows + w.count > b->batch_rows) {
+        // a batch ends at batch_rows rows or 2 GiB of string heap (32-bit heap offsets of the compact layout; bounded pinned arenas)
+        if (cur.rows > 0 && (cur.rows + w.count > b->batch_rows || cur.heap + w.heap_bytes > (2ull << 30))) {
             cur.b_hi = i;
             b->batches.push_back(cur);
             cur = Batch{i, i, 0, 0, cur.row0 + cur.rows};
@@ -444,34 +478,43 @@ int walk_segment(dh_bam *b, int k) {
     } else if (stopped && lw.stop == 1) {
         b->carry = (int64_t)s.obytes - lw.exit_off;
         if ((uint64_t)b->carry > b->carry_cap) {
-            set_error("BAM record of more than %llu bytes straddles a segment: raise the carry buffer (dh_bam_configure)",
+            // a limit of this pipeline, not a read error of the file: reported, never a silent end of scan
+            set_error("a record of more than %llu bytes straddles two inflate segments: raise the carry buffer (dh_bam_configure)",
                       (unsigned long long)b->carry_cap);
-            return DH_EFORMAT;
+            return DH_ENOMEM;
         }
         if ((size_t)k + 1 >= b->segs.size()) {
-            // range scan whose last record runs past the inflated look-ahead
-            set_error("record at the end of the scan range extends beyond the look-ahead blocks");
-            return DH_EFORMAT;
+            // range scan whose last record runs past the inflated look-ahead (carry_cap bytes behind the range end)
+            set_error("the record at the end of the scan range is longer than the %llu-byte look-ahead: raise the carry buffer (dh_bam_configure)",
+                      (unsigned long long)b->carry_cap);
+            return DH_ENOMEM;
         }
     } else {
         b->st.end_voffset = voff_of(lw.exit_off);
-        if ((size_t)k + 1 >= b->segs.size()) b->chain_done = true;
+        if ((size_t)k + 1 >= b->segs.size()) {
+            b->chain_done = true;
+            // behind the last good block of a truncated image htslib's next read fails (bam_read1: bgzf_read != 4 and != 0 -> -2)
+            if (b->truncated && is_final && b->final_status == 0) b->final_status = -2;
+        }
     }
     return DH_OK;
 }
 
 int issue_batch(dh_bam *b) {
+    const int slot = take_slot(b);
+    if (slot < 0) { set_error("internal: no free batch slot"); return DH_EINVAL; }
     const Batch &bb = b->batches[b->next_batch_i++];
     SegSlot &s = b->ss[b->cur_seg % NSEG];
-    BatchSlot &o = b->bs[b->issued % NBATCH];
-    // arena layout: [col data | validity]* aligned to 256, heap last
+    BatchSlot &o = b->bs[slot];
+    const bool compact = is_compact(b);
+    // arena layout: [col data | validity]* aligned to 256, (compact: rec_off,) heap last
     uint64_t off = 0, coff[BAM_MAX_COLS], voff[BAM_MAX_COLS];
     const int ncols = BAM_CORE_COLS + (int)b->tags.size();
     for (int c = 0; c < ncols; ++c) {
         coff[c] = voff[c] = UINT64_MAX;
         if (!col_on(b, c)) continue;
         coff[c] = off;
-        off = (off + (uint64_t)col_width(b, c) * bb.rows + A256) & ~A256;
+        off = (off + (uint64_t)(compact ? col_width_compact(b, c) : col_width(b, c)) * bb.rows + A256) & ~A256;
         if (col_nullable(c)) {
             voff[c] = off;
             off = (off + ((bb.rows + 63) / 64) * 8 + A256) & ~A256;
@@ -482,6 +525,8 @@ int issue_batch(dh_bam *b) {
         const uint64_t sz[4] = {16 * bb.rows, ((bb.rows + 63) / 64) * 8, 16 * bb.map, 16 * bb.map};
         for (int q = 0; q < 4; ++q) { map_off[q] = off; off = (off + sz[q] + A256) & ~A256; }
     }
+    uint64_t recoff_off = 0;
+    if (compact) { recoff_off = off; off = (off + 4 * bb.rows + A256) & ~A256; }
     const uint64_t heap_off = off, total = off + bb.heap;
     int rc;
     if ((rc = o.arena.reserve(total + 256)) != DH_OK) return rc;
@@ -500,6 +545,7 @@ int issue_batch(dh_bam *b) {
     dp.b_hi = bb.b_hi;
     dp.heap = (uint8_t *)o.arena.p + heap_off;
     dp.heap_host = (uint64_t)(uintptr_t)((uint8_t *)o.h_arena.p + heap_off);
+    dp.rec_off = compact ? (uint32_t *)((uint8_t *)o.arena.p + recoff_off) : nullptr;
     memset(&o.desc, 0, sizeof o.desc);
     for (int c = 0; c < ncols; ++c) {
         if (coff[c] == UINT64_MAX) continue;
@@ -512,8 +558,10 @@ int issue_batch(dh_bam *b) {
         }
     }
     DH_CUDA(cudaEventRecord(o.ev_k0, sk));
-    DH_CUDA(launch_bam_decode(dp, b->tabs, sk));
+    DH_CUDA(compact ? launch_bam_decode_compact(dp, b->tabs, sk) : launch_bam_decode(dp, b->tabs, sk));
     b->ctx->launches++;
+    o.dp = dp;
+    o.dev_recoff = recoff_off;
     if (b->aux_map) {
         AuxMapParams mp;
         memset(&mp, 0, sizeof mp);
@@ -550,8 +598,14 @@ int issue_batch(dh_bam *b) {
     o.desc.heap = (const uint8_t *)o.h_arena.p + heap_off;
     o.desc.heap_bytes = bb.heap;
     o.desc.bytes = total;
+    o.desc.slot = slot;
+    o.desc.layout = compact ? DH_BAM_COMPACT_OUTPUT : 0u;
+    o.desc.rec_off = compact ? (const uint32_t *)((const uint8_t *)o.h_arena.p + recoff_off) : nullptr;
+    o.on_device = keep;
+    o.last = false;
+    o.state = SLOT_INFLIGHT;
     b->st.d2h_bytes += keep ? 0 : total;
-    b->inflight.push_back(b->issued);
+    b->inflight.push_back(slot);
     b->issued++;
     return DH_OK;
 }
@@ -591,9 +645,15 @@ dh_bam *dh_bam_open(dh_ctx *ctx, const uint8_t *data, uint64_t size) {
     memset(&b->st, 0, sizeof b->st);
     uint64_t bad = 0;
     if (walk_blocks(data, size, 0, b->bt, &bad) != DH_OK) {
-        set_error("invalid BGZF header at offset %llu", (unsigned long long)bad);
-        delete b;
-        return nullptr;
+        // htslib opens a truncated BAM or one with garbage behind a block and returns every record in front of the broken block; the
+        // read then fails (bgzf_read -> -1, bam_read1 -> -2 / -3 / -4) and the reference ends the scan silently (bam_reader.c:754-765)
+        if (b->bt.blocks.empty()) {
+            set_error("invalid BGZF header at offset %llu", (unsigned long long)bad);
+            delete b;
+            return nullptr;
+        }
+        b->bt.end_off = bad;
+        b->truncated = true;
     }
     if (b->bt.blocks.empty()) { set_error("empty file"); delete b; return nullptr; }
     if (parse_header(b) != DH_OK) { delete b; return nullptr; }
@@ -616,6 +676,9 @@ void dh_bam_close(dh_bam *b) {
         s.arena.release(); s.h_arena.release();
         for (cudaEvent_t e : {s.ev_k0, s.ev_k1, s.ev_c0, s.ev_done}) if (e) cudaEventDestroy(e);
     }
+    b->d_dict_ptr.release(); b->d_dict_hash.release(); b->d_ref_hash.release(); b->d_sample_hash.release(); b->d_sums.release(); b->h_sums.release();
+    b->d_aux_excl.release();
+    if (b->ev_scan0) cudaEventDestroy(b->ev_scan0);
     b->d_ref_cells.release(); b->d_rg.release(); b->d_rg_ids.release(); b->d_tags.release(); b->d_image.release(); b->d_filt.release();
     if (b->bcf) bcf_state_free(b->bcf);
     delete b;
@@ -642,6 +705,7 @@ uint64_t dh_bam_n_blocks(const dh_bam *b) { return b ? b->bt.blocks.size() : 0; 
 
 int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, int n_tags) {
     if (!b || n_tags < 0 || n_tags > BAM_MAX_TAGS || (n_tags && !tags)) { set_error("dh_bam_set_projection: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
     if (b->scanning && !b->inflight.empty()) { set_error("dh_bam_set_projection: scan in progress"); return DH_EINVAL; }
     b->tags.clear();
     for (int i = 0; i < n_tags; ++i) {
@@ -662,6 +726,7 @@ int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, 
 
 int dh_bam_set_aux_map(dh_bam *b, int enable, const char *exclude, int n_exclude) {
     if (!b || n_exclude < 0 || (n_exclude && !exclude)) { set_error("dh_bam_set_aux_map: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
     if (b->scanning && !b->inflight.empty()) { set_error("dh_bam_set_aux_map: scan in progress"); return DH_EINVAL; }
     b->aux_map = enable != 0;
     b->aux_excl.clear();
@@ -698,7 +763,56 @@ int dh_bam_set_mode(dh_bam *b, uint32_t flags) {
     }
     if (!(flags & DH_BAM_DEVICE_INPUT)) b->d_image.release();
     b->mode = flags;
+    b->tabs.compact = is_compact(b) ? 1u : 0u;
     return DH_OK;
+}
+
+int dh_bam_set_filter(dh_bam *b, uint32_t flag_require, uint32_t flag_exclude, uint32_t min_mapq) {
+    if (!b) { set_error("dh_bam_set_filter: null handle"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (b->scanning && !b->inflight.empty()) { set_error("dh_bam_set_filter: scan in progress"); return DH_EINVAL; }
+    b->flag_require = flag_require & 0xffffu;
+    b->flag_exclude = flag_exclude & 0xffffu;
+    b->min_mapq = min_mapq;
+    b->tabs.flag_require = b->flag_require;
+    b->tabs.flag_exclude = b->flag_exclude;
+    b->tabs.min_mapq = b->min_mapq;
+    return DH_OK;
+}
+
+int32_t dh_bam_n_rg(const dh_bam *b) { return b ? (int32_t)b->rg.size() : 0; }
+const char *dh_bam_rg_id(const dh_bam *b, int32_t i, uint32_t *len) {
+    if (!b || i < 0 || (size_t)i >= b->rg.size()) return nullptr;
+    if (len) *len = b->rg[(size_t)i].id_len;
+    return b->rg_ids.data() + b->rg[(size_t)i].id_off;
+}
+const char *dh_bam_rg_sample(const dh_bam *b, int32_t i) {
+    if (!b || i < 0 || (size_t)i >= b->rg.size() || !b->rg[(size_t)i].has_sample) return nullptr;
+    return b->rg_samples[(size_t)i].c_str();
+}
+
+dh_bam *dh_bam_clone(const dh_bam *src, dh_ctx *ctx) {
+    if (!src || !ctx || src->kind != 0) { set_error("dh_bam_clone: bad arguments"); return nullptr; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return nullptr; }
+    dh_bam *b = new dh_bam();
+    b->ctx = ctx;
+    b->data = src->data;
+    b->size = src->size;
+    b->bt = src->bt;
+    b->text = src->text;
+    b->ref_names = src->ref_names;
+    b->ref_lens = src->ref_lens;
+    b->first_blk = src->first_blk;
+    b->first_off = src->first_off;
+    b->truncated = src->truncated;
+    b->seg_comp = src->seg_comp;
+    b->batch_rows = src->batch_rows;
+    b->carry_cap = src->carry_cap;
+    b->n_slots = src->n_slots;
+    memset(&b->st, 0, sizeof b->st);
+    build_dictionaries(b);
+    if (ensure_events(b) != DH_OK || upload_tables(b) != DH_OK) { dh_bam_close(b); return nullptr; }
+    return b;
 }
 
 // (block, in-block offset) of a virtual offset.  htslib's bgzf_tell reports "end of block k" as (k, isize) while the next
@@ -720,7 +834,9 @@ static int locate_voff(const dh_bam *b, uint64_t voff, const char *what, size_t 
 // Start scanning one virtual-offset range.  `fresh` = first range of a scan: counters and statistics restart.
 static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh) {
     DH_CUDA(cudaSetDevice(b->ctx->device));
-    DH_CUDA(cudaDeviceSynchronize());  // drop whatever an abandoned scan left in flight
+    // drop whatever an abandoned scan left in flight (this context's streams only: other contexts may share the device)
+    DH_CUDA(cudaStreamSynchronize(b->ctx->stream));
+    for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(b->ctx->copy_streams[i]));
     const BlockTable &bt = b->bt;
     const size_t nb = bt.blocks.size();
     size_t b_first = b->first_blk;
@@ -732,8 +848,12 @@ static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fre
     if (!b->to_eof) {
         if ((rc = locate_voff(b, voff_end, "voff_end", b->limit_blk, b->limit_off)) != DH_OK) return rc;
         if (b->limit_blk >= nb) b->to_eof = true;
-        // inflate up to the limit block plus look-ahead for a record that straddles the range end
-        else b_stop = std::min(nb, b->limit_blk + (b->limit_off ? 1 : 0) + 2);
+        // inflate up to the limit block plus look-ahead for a record that straddles the range end: at least two blocks, and as many
+        // as hold carry_cap inflated bytes (a 150 kb long read is several blocks; the look-ahead costs a few MB per range)
+        else {
+            b_stop = std::min(nb, b->limit_blk + (b->limit_off ? 1 : 0) + 2);
+            while (b_stop < nb && bt.uoff[b_stop] - bt.uoff[b->limit_blk] < b->carry_cap) ++b_stop;
+        }
     }
     b->end_blk = b_stop;
     b->segs.clear();
@@ -758,6 +878,8 @@ static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fre
     b->carry = 0;
     b->chain_done = b->segs.empty();
     if (fresh) {
+        for (auto &o : b->bs) o.state = SLOT_FREE;   // whatever the caller still held belongs to the abandoned scan
+        b->auto_slot = -1;
         b->rows_total = 0;
         b->final_status = 0;
         memset(&b->st, 0, sizeof b->st);
@@ -769,8 +891,15 @@ static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fre
     return DH_OK;
 }
 
+static int check_layout(const dh_bam *b) {
+    if (is_compact(b) && b->aux_map) { set_error("the compact layout does not carry the AUXILIARY_TAGS column: scan in the DuckDB layout"); return DH_EINVAL; }
+    return DH_OK;
+}
+
 int dh_bam_scan_begin(dh_bam *b, uint64_t voff_beg, uint64_t voff_end) {
     if (!b) { set_error("dh_bam_scan_begin: null handle"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (check_layout(b) != DH_OK) return DH_EINVAL;
     b->filt_mode = 0;
     b->filt.clear();
     b->pending.clear();
@@ -823,6 +952,8 @@ static int start_filtered(dh_bam *b, const dh_index *idx, int mode) {
 
 int dh_bam_scan_regions(dh_bam *b, const dh_index *idx, const char *const *regions, int n_regions) {
     if (!b || !idx || (n_regions > 0 && !regions)) { set_error("dh_bam_scan_regions: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (check_layout(b) != DH_OK) return DH_EINVAL;
     std::string err;
     const int n = regions_to_intervals(regions, n_regions, b->ref_names, b->filt, err);
     if (n < 0) { set_error("%s", err.c_str()); return DH_EINVAL; }
@@ -832,6 +963,8 @@ int dh_bam_scan_regions(dh_bam *b, const dh_index *idx, const char *const *regio
 
 int dh_bam_scan_contigs(dh_bam *b, const dh_index *idx, int32_t tid_lo, int32_t tid_hi) {
     if (!b || !idx) { set_error("dh_bam_scan_contigs: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (check_layout(b) != DH_OK) return DH_EINVAL;
     const int32_t n_ref = (int32_t)b->ref_names.size();
     tid_lo = std::max(tid_lo, 0);
     tid_hi = std::min(tid_hi, n_ref);
@@ -846,30 +979,21 @@ int dh_bam_scan_contigs(dh_bam *b, const dh_index *idx, int32_t tid_lo, int32_t 
 
 int dh_bam_split_contigs(const dh_bam *b, const dh_index *idx, int n_parts, int32_t *tid_bounds) {
     if (!b || !idx || n_parts < 1 || !tid_bounds) { set_error("dh_bam_split_contigs: bad arguments"); return DH_EINVAL; }
+    // the index may cover fewer or more references than the header names: bounds are over the header's contigs
     const int32_t n_ref = (int32_t)b->ref_names.size();
-    std::vector<uint64_t> pre((size_t)n_ref + 1, 0);   // compressed bytes of contigs [0, t)
-    for (int32_t t = 0; t < n_ref; ++t) {
-        uint64_t u, v, w = 0;
-        if (contig_span(idx->ix, t, u, v) && (v >> 16) >= (u >> 16)) w = (v >> 16) - (u >> 16) + 1;
-        pre[(size_t)t + 1] = pre[(size_t)t] + w;
-    }
-    tid_bounds[0] = 0;
-    for (int p = 1; p < n_parts; ++p) {
-        const uint64_t target = pre[(size_t)n_ref] / (uint64_t)n_parts * (uint64_t)p;
-        int32_t t = (int32_t)(std::lower_bound(pre.begin(), pre.end(), target) - pre.begin());
-        // cut at the contig boundary nearest to the target
-        if (t > 0 && target - pre[(size_t)t - 1] < pre[(size_t)std::min(t, n_ref)] - target) --t;
-        tid_bounds[p] = std::min(std::max(t, tid_bounds[p - 1]), n_ref);
-    }
+    int rc = dh_index_split_contigs(idx, n_parts, tid_bounds);
+    if (rc != DH_OK) return rc;
+    for (int p = 0; p <= n_parts; ++p) tid_bounds[p] = std::min(tid_bounds[p], n_ref);
     tid_bounds[n_parts] = n_ref;
     return DH_OK;
 }
 
-int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
-    if (!b || !out || !b->scanning) { set_error("dh_bam_next_batch: no scan in progress"); return DH_EINVAL; }
+// Pipeline step shared by the three entry points below (caller holds b->mu): refill the free slots, wait for the oldest
+// batch in flight and hand its slot over as HELD.
+static int acquire_locked(dh_bam *b, dh_bam_batch *out) {
     DH_CUDA(cudaSetDevice(b->ctx->device));
     auto top_up = [&]() -> int {
-        while (b->inflight.size() < NBATCH - 1) {
+        while (free_slots(b) > 0) {
             int w = have_work(b);
             if (w < 0) return w;
             if (w == 0) break;
@@ -889,11 +1013,17 @@ int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
     if (b->inflight.empty()) {
         b->st.rows = b->rows_total;
         b->st.status = b->final_status;
+        if (free_slots(b) == 0 && !b->chain_done) {
+            set_error("every batch slot is held by the caller: release one (dh_bam_release_batch) or raise dh_bam_set_slots");
+            return DH_EBUSY;
+        }
         return 0;
     }
-    BatchSlot &o = b->bs[b->inflight.front() % NBATCH];
+    const int slot = b->inflight.front();
+    BatchSlot &o = b->bs[slot];
     b->inflight.pop_front();
     DH_CUDA(cudaEventSynchronize(o.ev_done));
+    o.state = SLOT_HELD;
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, o.ev_k0, o.ev_k1) == cudaSuccess) b->st.decode_ms += ms;
     static const bool trace = getenv("DH_TRACE") != nullptr;
@@ -916,16 +1046,214 @@ int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
     return 1;
 }
 
+int dh_bam_prefetch(dh_bam *b) {
+    if (!b) { set_error("dh_bam_prefetch: null handle"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (!b->scanning) { set_error("dh_bam_prefetch: no scan in progress"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    // uploads + inflate of the first segments are enqueued (asynchronous); the boundary walk, which needs their result on the
+    // host, is left to the first acquire
+    if (b->cur_seg != -1 || b->chain_done) return DH_OK;
+    for (int k = 0; k < NSEG && (size_t)k < b->segs.size(); ++k) {
+        const int rc = issue_inflate(b, k);
+        if (rc != DH_OK) { b->scanning = false; return rc; }
+    }
+    return DH_OK;
+}
+
+int dh_bam_acquire_batch(dh_bam *b, dh_bam_batch *out) {
+    if (!b || !out) { set_error("dh_bam_acquire_batch: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (!b->scanning) { set_error("dh_bam_acquire_batch: no scan in progress"); return DH_EINVAL; }
+    return acquire_locked(b, out);
+}
+
+int dh_bam_release_batch(dh_bam *b, int32_t slot) {
+    if (!b || slot < 0 || slot >= b->n_slots) { set_error("dh_bam_release_batch: bad slot"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (b->bs[slot].state != SLOT_HELD) { set_error("dh_bam_release_batch: slot %d is not held", slot); return DH_EINVAL; }
+    b->bs[slot].state = SLOT_FREE;
+    if (b->auto_slot == slot) b->auto_slot = -1;
+    return DH_OK;
+}
+
+int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out) {
+    if (!b || !out) { set_error("dh_bam_next_batch: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (!b->scanning) { set_error("dh_bam_next_batch: no scan in progress"); return DH_EINVAL; }
+    if (b->auto_slot >= 0 && b->bs[b->auto_slot].state == SLOT_HELD) b->bs[b->auto_slot].state = SLOT_FREE;   // "valid until the next call"
+    b->auto_slot = -1;
+    const int rc = acquire_locked(b, out);
+    if (rc == 1) b->auto_slot = out->slot;
+    return rc;
+}
+
+int dh_bam_set_slots(dh_bam *b, int n_slots) {
+    if (!b || n_slots < 3 || n_slots > MAX_SLOTS) { set_error("dh_bam_set_slots: 3..%d slots", MAX_SLOTS); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (n_slots == b->n_slots) return DH_OK;
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    // whatever scan was under way is abandoned: its batches are forgotten once the streams are idle
+    DH_CUDA(cudaStreamSynchronize(b->ctx->stream));
+    for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(b->ctx->copy_streams[i]));
+    for (auto &o : b->bs) o.state = SLOT_FREE;
+    b->inflight.clear();
+    b->auto_slot = -1;
+    b->scanning = false;
+    b->n_slots = n_slots;
+    return ensure_events(b);
+}
+
+// ---- per-column checksums of a held batch (parity at sizes no cell-by-cell comparison reaches) -----------------------------
+static int checksum_tables(dh_bam *b) {
+    if (b->checksum_tables) return DH_OK;
+    b->h_ref_hash.clear(); b->h_sample_hash.clear(); b->h_dict_ptr.clear(); b->h_dict_hash.clear();
+    for (auto &n : b->ref_names) b->h_ref_hash.push_back(ck_bytes((const uint8_t *)n.data(), (uint32_t)n.size()));
+    b->h_ref_hash.push_back(ck_bytes((const uint8_t *)"*", 1));
+    for (auto &sm : b->rg_samples) b->h_sample_hash.push_back(ck_bytes((const uint8_t *)sm.data(), (uint32_t)sm.size()));
+    std::vector<std::pair<uint64_t, uint64_t>> d;
+    for (auto &str : b->dict) d.emplace_back((uint64_t)(uintptr_t)str.data(), ck_bytes((const uint8_t *)str.data(), (uint32_t)str.size()));
+    std::sort(d.begin(), d.end());
+    for (auto &e : d) { b->h_dict_ptr.push_back(e.first); b->h_dict_hash.push_back(e.second); }
+    auto up = [&](DevBuf &buf, const std::vector<uint64_t> &v) -> int {
+        int rc = buf.reserve(std::max<size_t>(1, v.size()) * 8);
+        if (rc != DH_OK) return rc;
+        if (!v.empty()) DH_CUDA(cudaMemcpy(buf.p, v.data(), v.size() * 8, cudaMemcpyHostToDevice));
+        return DH_OK;
+    };
+    int rc;
+    if ((rc = up(b->d_ref_hash, b->h_ref_hash)) != DH_OK || (rc = up(b->d_sample_hash, b->h_sample_hash)) != DH_OK ||
+        (rc = up(b->d_dict_ptr, b->h_dict_ptr)) != DH_OK || (rc = up(b->d_dict_hash, b->h_dict_hash)) != DH_OK ||
+        (rc = b->d_sums.reserve(BAM_MAX_COLS * 8)) != DH_OK || (rc = b->h_sums.reserve(BAM_MAX_COLS * 8)) != DH_OK)
+        return rc;
+    b->checksum_tables = true;
+    return DH_OK;
+}
+
+int dh_bam_batch_checksum(dh_bam *b, const dh_bam_batch *batch, uint64_t *sums) {
+    if (!b || !batch || !sums || batch->slot < 0 || batch->slot >= b->n_slots || b->kind != 0) { set_error("dh_bam_batch_checksum: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    BatchSlot &o = b->bs[batch->slot];
+    if (o.state != SLOT_HELD) { set_error("dh_bam_batch_checksum: the batch is not held by the caller"); return DH_EINVAL; }
+    DH_CUDA(cudaSetDevice(b->ctx->device));
+    int rc = checksum_tables(b);
+    if (rc != DH_OK) return rc;
+    ChecksumParams cp;
+    memset(&cp, 0, sizeof cp);
+    const int ncols = BAM_CORE_COLS + (int)b->tags.size();
+    cp.n_rows = o.desc.n_rows;
+    cp.heap_bytes = o.desc.heap_bytes;
+    cp.compact = o.desc.layout == DH_BAM_COMPACT_OUTPUT ? 1u : 0u;
+    cp.n_cols = (uint32_t)ncols;
+    cp.n_ref = (int32_t)b->ref_names.size();
+    cp.n_dict = (uint32_t)b->h_dict_ptr.size();
+    static const uint8_t CORE_KIND[BAM_CORE_COLS] = {CK_STR, CK_U16, CK_DICT, CK_POS, CK_MAPQ, CK_STR, CK_DICT, CK_POS, CK_TLEN, CK_STR, CK_STR, CK_STR, CK_SAMPLE};
+    for (int c = 0; c < ncols; ++c) {
+        if (c < BAM_CORE_COLS) cp.kind[c] = CORE_KIND[c];
+        else {
+            const char t = (char)b->tags[(size_t)(c - BAM_CORE_COLS)].type;
+            cp.kind[c] = t == 'i' ? CK_TAG_I : t == 'f' ? CK_TAG_F : t == 'A' ? CK_TAG_A : t == 'B' ? CK_TAG_B : CK_STR;
+        }
+    }
+    if (o.on_device) {
+        cp.dp = o.dp;
+        cp.ref_hash = (const uint64_t *)b->d_ref_hash.p;
+        cp.sample_hash = (const uint64_t *)b->d_sample_hash.p;
+        cp.dict_ptr = (const uint64_t *)b->d_dict_ptr.p;
+        cp.dict_hash = (const uint64_t *)b->d_dict_hash.p;
+        cp.sums = (uint64_t *)b->d_sums.p;
+        cudaStream_t sk = s_comp(b);
+        DH_CUDA(cudaMemsetAsync(b->d_sums.p, 0, BAM_MAX_COLS * 8, sk));
+        DH_CUDA(launch_bam_checksum(cp, sk));
+        b->ctx->launches++;
+        DH_CUDA(cudaMemcpyAsync(b->h_sums.p, b->d_sums.p, BAM_MAX_COLS * 8, cudaMemcpyDeviceToHost, sk));
+        DH_CUDA(cudaStreamSynchronize(sk));
+        for (int c = 0; c < ncols; ++c) sums[c] += ((const uint64_t *)b->h_sums.p)[c];
+    } else {
+        for (int c = 0; c < ncols; ++c) {
+            cp.dp.col[c] = (uint8_t *)o.desc.data[c];
+            cp.dp.valid[c] = (unsigned long long *)o.desc.validity[c];
+        }
+        cp.dp.heap = (uint8_t *)o.desc.heap;
+        cp.dp.rec_off = (uint32_t *)o.desc.rec_off;
+        cp.ref_hash = b->h_ref_hash.data();
+        cp.sample_hash = b->h_sample_hash.data();
+        cp.dict_ptr = b->h_dict_ptr.data();
+        cp.dict_hash = b->h_dict_hash.data();
+        uint64_t local[BAM_MAX_COLS] = {};
+        cp.sums = local;
+        static const int nthr = getenv("DH_HOST_THREADS") ? atoi(getenv("DH_HOST_THREADS")) : (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+        bam_checksum_host(cp, nthr);
+        for (int c = 0; c < ncols; ++c) sums[c] += local[c];
+    }
+    return DH_OK;
+}
+
+int dh_index_split_contigs(const dh_index *idx, int n_parts, int32_t *tid_bounds) {
+    if (!idx || n_parts < 1 || !tid_bounds) { set_error("dh_index_split_contigs: bad arguments"); return DH_EINVAL; }
+    const int32_t n_ref = (int32_t)idx->ix.refs.size();
+    std::vector<uint64_t> pre((size_t)n_ref + 1, 0);   // compressed bytes of contigs [0, t)
+    for (int32_t t = 0; t < n_ref; ++t) {
+        uint64_t u, v, w = 0;
+        if (contig_span(idx->ix, t, u, v) && (v >> 16) >= (u >> 16)) w = (v >> 16) - (u >> 16) + 1;
+        pre[(size_t)t + 1] = pre[(size_t)t] + w;
+    }
+    tid_bounds[0] = 0;
+    for (int p = 1; p < n_parts; ++p) {
+        const uint64_t target = pre[(size_t)n_ref] / (uint64_t)n_parts * (uint64_t)p;
+        int32_t t = (int32_t)(std::lower_bound(pre.begin(), pre.end(), target) - pre.begin());
+        // cut at the contig boundary nearest to the target
+        if (t > 0 && target - pre[(size_t)t - 1] < pre[(size_t)std::min(t, n_ref)] - target) --t;
+        tid_bounds[p] = std::min(std::max(t, tid_bounds[p - 1]), n_ref);
+    }
+    tid_bounds[n_parts] = n_ref;
+    return DH_OK;
+}
+
 int dh_bam_scan_stats_get(const dh_bam *b, dh_bam_scan_stats *out) {
     if (!b || !out) return DH_EINVAL;
+    std::lock_guard<std::mutex> lk(b->mu);
     *out = b->st;
     out->rows = b->rows_total;
     out->status = b->final_status;
     return DH_OK;
 }
 
+// Does a record start at offset 0 of block `blk`?  htslib starts a block at a record boundary whenever the next record does not fit
+// the current one (bgzf_flush_try, htslib/sam.c:883), but the blocks behind a record longer than a block start in the middle of it,
+// and foreign writers cut anywhere (htslib/test/bgzf_boundaries).  The block is inflated (GPU) and its records are chained on the
+// host: every header must be plausible and the chain must end exactly at the block end or run past it with its last record.
+static bool block_starts_a_record(const dh_bam *b, size_t blk) {
+    const BlockTable &bt = b->bt;
+    const dh_bgzf_block &B = bt.blocks[blk];
+    if (B.isize < 36) return false;
+    std::vector<uint8_t> u((size_t)B.isize + 8);
+    uint64_t n = 0;
+    if (dh_bgzf_inflate_host(b->ctx, b->data + B.coffset, B.csize, u.data(), u.size(), &n, nullptr) != DH_OK || n != B.isize) return false;
+    const int32_t n_ref = (int32_t)b->ref_names.size();
+    auto le32 = [&](uint64_t p) { return (uint32_t)u[p] | ((uint32_t)u[p + 1] << 8) | ((uint32_t)u[p + 2] << 16) | ((uint32_t)u[p + 3] << 24); };
+    uint64_t off = 0;
+    int seen = 0;
+    while (off + 36 <= n) {
+        const uint32_t bl = le32(off);
+        if (bl < 32u || bl >= (1u << 28)) return false;
+        const int32_t tid = (int32_t)le32(off + 4), pos = (int32_t)le32(off + 8), l_qseq = (int32_t)le32(off + 20), mtid = (int32_t)le32(off + 24),
+                      mpos = (int32_t)le32(off + 28);
+        const uint32_t l_qname = u[off + 12], n_cigar = le32(off + 16) & 0xffffu;
+        if (tid < -1 || tid >= n_ref || mtid < -1 || mtid >= n_ref || pos < -1 || mpos < -1 || l_qname < 1 || l_qseq < 0) return false;
+        if (32ull + l_qname + 4ull * n_cigar + (((uint64_t)l_qseq + 1) >> 1) + (uint64_t)l_qseq > bl) return false;
+        const uint64_t qend = off + 36 + l_qname - 1;
+        if (qend < n && u[qend] != 0) return false;
+        off += 4ull + bl;
+        ++seen;
+    }
+    return seen > 0 && off >= n;      // off < n: fewer than 36 bytes left that are no record header
+}
+
 int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs) {
     if (!b || n_parts < 1 || !voffs) { set_error("dh_bam_split: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (cudaSetDevice(b->ctx->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return DH_ECUDA; }
     const BlockTable &bt = b->bt;
     const size_t nb = bt.blocks.size();
     voffs[0] = dh_bam_first_voffset(b);
@@ -933,11 +1261,20 @@ int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs) {
     size_t lo = std::min(nb, b->first_blk + (b->first_off ? 1 : 0));
     const uint64_t c0 = lo < nb ? bt.blocks[lo].coffset : bt.end_off, c1 = bt.end_off;
     size_t prev = lo;
+    bool collapsed = false;
     for (int p = 1; p < n_parts; ++p) {
         uint64_t target = c0 + (c1 - c0) * (uint64_t)p / (uint64_t)n_parts;
         size_t blk = std::max(block_of(b, target), prev);
-        voffs[p] = blk < nb ? (bt.blocks[blk].coffset << 16) : UINT64_MAX;
-        prev = blk;
+        // a cut must be a record boundary: move on to the next block that verifiably starts one (a few tries: the blocks behind a long
+        // read); a file whose blocks do not start records at all (foreign writer) is not cut: part 0 gets everything
+        int tries = 0;
+        while (!collapsed && blk < nb && bt.blocks[blk].isize > 0 && !block_starts_a_record(b, blk)) {
+            ++blk;
+            if (++tries >= 64) collapsed = true;
+        }
+        while (!collapsed && blk < nb && bt.blocks[blk].isize == 0) ++blk;    // empty blocks (EOF marker) hold no record
+        voffs[p] = (collapsed || blk >= nb) ? UINT64_MAX : (bt.blocks[blk].coffset << 16);
+        prev = std::min(blk, nb);
     }
     voffs[n_parts] = UINT64_MAX;
     return DH_OK;
@@ -950,6 +1287,9 @@ namespace dh {
 int scan_ensure_events(dh_bam *b) { return ensure_events(b); }
 int scan_begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh) { return begin_range(b, voff_beg, voff_end, fresh); }
 int scan_have_work(dh_bam *b) { return have_work(b); }
+int scan_take_slot(dh_bam *b) { return take_slot(b); }
+void scan_release_slot(dh_bam *b, int slot) { b->bs[slot].state = SLOT_FREE; if (b->auto_slot == slot) b->auto_slot = -1; }
+int scan_free_slots(const dh_bam *b) { return free_slots(b); }
 int scan_start_filtered(dh_bam *b, const dh_index *idx, int mode) { return start_filtered(b, idx, mode); }
 int scan_inflate_head(dh_bam *b, uint64_t want, std::vector<uint8_t> &u) {
     const size_t nb = b->bt.blocks.size();

@@ -53,11 +53,11 @@ struct dh_bcf_state {
     std::vector<uint8_t> info_want, fmt_want;
     uint64_t bump_cap = 64ull << 20;
     // per batch slot: pointer tables (pinned, read by the kernel) and the host views handed to the caller
-    PinBuf h_ptrs[NBATCH];
-    std::vector<const void *> out_info[NBATCH], out_fmt[NBATCH];
-    std::vector<const uint64_t *> out_info_v[NBATCH], out_fmt_v[NBATCH];
-    dh_bcf_batch desc[NBATCH];
-    uint64_t bump_off[NBATCH] = {};       // where the bump counter sits in the arena
+    PinBuf h_ptrs[MAX_SLOTS];
+    std::vector<const void *> out_info[MAX_SLOTS], out_fmt[MAX_SLOTS];
+    std::vector<const uint64_t *> out_info_v[MAX_SLOTS], out_fmt_v[MAX_SLOTS];
+    dh_bcf_batch desc[MAX_SLOTS];
+    uint64_t bump_off[MAX_SLOTS] = {};    // where the bump counter sits in the arena
 };
 
 struct dh_bcf {
@@ -301,7 +301,8 @@ int issue_bcf_batch(dh_bam *b) {
     dh_bcf_state *st = b->bcf;
     const Batch &bb = b->batches[b->next_batch_i++];
     SegSlot &s = b->ss[b->cur_seg % NSEG];
-    const int slot = (int)(b->issued % NBATCH);
+    const int slot = scan_take_slot(b);
+    if (slot < 0) { set_error("internal: no free batch slot"); return DH_EINVAL; }
     BatchSlot &o = b->bs[slot];
     const uint64_t n_rec = bb.rows, ns = st->samples.size(), rows = n_rec * ns;
     const size_t ni = st->info.size(), nf = st->fmt.size();
@@ -409,9 +410,12 @@ int issue_bcf_batch(dh_bam *b) {
     d.heap = host + heap_off;
     d.heap_bytes = fixed;
     d.bytes = keep ? 0 : main_bytes;
+    d.slot = slot;
     st->bump_off[slot] = main_bytes;
+    o.on_device = keep;
+    o.state = SLOT_INFLIGHT;
     b->st.d2h_bytes += d.bytes;
-    b->inflight.push_back(b->issued);
+    b->inflight.push_back(slot);
     b->issued++;
     return DH_OK;
 }
@@ -536,6 +540,7 @@ int dh_bcf_set_mode(dh_bcf *h, uint32_t flags) { return h ? dh_bam_set_mode(h->s
 
 int dh_bcf_scan_begin(dh_bcf *h) {
     if (!h) { set_error("dh_bcf_scan_begin: null handle"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->scan->mu);
     h->scan->filt_mode = 0;
     h->scan->pending.clear();
     return scan_begin_range(h->scan, 0, UINT64_MAX, true);
@@ -544,6 +549,7 @@ int dh_bcf_scan_begin(dh_bcf *h) {
 int dh_bcf_scan_region(dh_bcf *h, const dh_index *idx, const char *region) {
     if (!h || !idx || !region) { set_error("dh_bcf_scan_region: bad arguments"); return DH_EINVAL; }
     dh_bam *b = h->scan;
+    std::lock_guard<std::mutex> lk(b->mu);
     std::string err;
     const char *one[1] = {region};
     const int n = regions_to_intervals(one, 1, b->bcf->ctg, b->filt, err);
@@ -552,13 +558,11 @@ int dh_bcf_scan_region(dh_bcf *h, const dh_index *idx, const char *region) {
     return scan_start_filtered(b, idx, 2);
 }
 
-int dh_bcf_next_batch(dh_bcf *h, dh_bcf_batch *out) {
-    if (!h || !out || !h->scan->scanning) { set_error("dh_bcf_next_batch: no scan in progress"); return DH_EINVAL; }
-    dh_bam *b = h->scan;
+static int bcf_acquire_locked(dh_bam *b, dh_bcf_batch *out) {
     dh_bcf_state *st = b->bcf;
     DH_CUDA(cudaSetDevice(b->ctx->device));
     auto top_up = [&]() -> int {
-        while (b->inflight.size() < NBATCH - 1) {
+        while (scan_free_slots(b) > 0) {
             int w = scan_have_work(b);
             if (w < 0) return w;
             if (w == 0) break;
@@ -578,12 +582,17 @@ int dh_bcf_next_batch(dh_bcf *h, dh_bcf_batch *out) {
     if (b->inflight.empty()) {
         b->st.rows = b->rows_total;
         b->st.status = b->final_status;
+        if (scan_free_slots(b) == 0 && !b->chain_done) {
+            set_error("every batch slot is held by the caller: release one (dh_bcf_release_batch) or raise dh_bcf_set_slots");
+            return DH_EBUSY;
+        }
         return 0;
     }
-    const int slot = (int)(b->inflight.front() % NBATCH);
+    const int slot = b->inflight.front();
     BatchSlot &o = b->bs[slot];
     b->inflight.pop_front();
     DH_CUDA(cudaEventSynchronize(o.ev_done));
+    o.state = SLOT_HELD;
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, o.ev_k0, o.ev_k1) == cudaSuccess) b->st.decode_ms += ms;
     // strings longer than 12 bytes / string-list cells live in a region whose use is only known now
@@ -611,6 +620,36 @@ int dh_bcf_next_batch(dh_bcf *h, dh_bcf_batch *out) {
     b->st.status = b->final_status;
     return 1;
 }
+
+int dh_bcf_acquire_batch(dh_bcf *h, dh_bcf_batch *out) {
+    if (!h || !out) { set_error("dh_bcf_acquire_batch: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->scan->mu);
+    if (!h->scan->scanning) { set_error("dh_bcf_acquire_batch: no scan in progress"); return DH_EINVAL; }
+    return bcf_acquire_locked(h->scan, out);
+}
+
+int dh_bcf_release_batch(dh_bcf *h, int32_t slot) {
+    if (!h || slot < 0 || slot >= h->scan->n_slots) { set_error("dh_bcf_release_batch: bad slot"); return DH_EINVAL; }
+    dh_bam *b = h->scan;
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (b->bs[slot].state != SLOT_HELD) { set_error("dh_bcf_release_batch: slot %d is not held", slot); return DH_EINVAL; }
+    scan_release_slot(b, slot);
+    return DH_OK;
+}
+
+int dh_bcf_next_batch(dh_bcf *h, dh_bcf_batch *out) {
+    if (!h || !out) { set_error("dh_bcf_next_batch: bad arguments"); return DH_EINVAL; }
+    dh_bam *b = h->scan;
+    std::lock_guard<std::mutex> lk(b->mu);
+    if (!b->scanning) { set_error("dh_bcf_next_batch: no scan in progress"); return DH_EINVAL; }
+    if (b->auto_slot >= 0 && b->bs[b->auto_slot].state == SLOT_HELD) scan_release_slot(b, b->auto_slot);
+    b->auto_slot = -1;
+    const int rc = bcf_acquire_locked(b, out);
+    if (rc == 1) b->auto_slot = out->slot;
+    return rc;
+}
+
+int dh_bcf_set_slots(dh_bcf *h, int n_slots) { return h ? dh_bam_set_slots(h->scan, n_slots) : DH_EINVAL; }
 
 int dh_bcf_scan_stats_get(const dh_bcf *h, dh_bam_scan_stats *out) { return h ? dh_bam_scan_stats_get(h->scan, out) : DH_EINVAL; }
 

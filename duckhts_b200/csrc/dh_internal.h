@@ -73,6 +73,7 @@ struct dh_ctx {
     struct Slot {
         dh::DevBuf comp, out, desc, status, work;
         dh::PinBuf h_desc, h_status;
+        dh::PinBuf h_comp, h_out;            // staging of the streaming file-to-file inflate (dh_bgzf_inflate_fd)
         cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
     } slots[3];
 };

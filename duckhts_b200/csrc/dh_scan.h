@@ -2,6 +2,7 @@
 // dh_bcf.cu (H2D -> inflate -> boundary walk -> per-batch columnar decode -> D2H).  Internal, not part of the C-ABI.
 #pragma once
 #include <deque>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -11,7 +12,8 @@
 
 namespace dh {
 
-constexpr int NSEG = 3, NBATCH = 6;
+constexpr int NSEG = 3;
+constexpr int MAX_SLOTS = 32, DEFAULT_SLOTS = 6;   // batch slots of the pipeline (dh_bam_set_slots)
 constexpr uint64_t A256 = 255;
 
 struct Batch {           // one output batch of the current segment
@@ -31,12 +33,18 @@ struct SegSlot {
     int issued_for = -1;    // segment index whose inflate was issued into this slot
 };
 
+enum { SLOT_FREE = 0, SLOT_INFLIGHT = 1, SLOT_HELD = 2 };
 struct BatchSlot {
     DevBuf arena;
     PinBuf h_arena;
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c0 = nullptr, ev_done = nullptr;
     dh_bam_batch desc;
+    DecodeParams dp;          // device view of the batch (dh_bam_batch_checksum on device-resident batches)
+    uint64_t dev_recoff = 0;  // arena offset of the compact layout's rec_off array
     bool timed = false;
+    bool on_device = false;   // DH_BAM_DEVICE_OUTPUT batch: the host arena was not filled
+    bool last = false;        // the scan ends with this batch: it carries the final status
+    int state = SLOT_FREE;
 };
 
 struct Seg { size_t b0, b1; };
@@ -53,6 +61,7 @@ struct dh_bam {
     const uint8_t *data = nullptr;
     uint64_t size = 0;
     BlockTable bt;
+    bool truncated = false;        // the image ends in a broken / cut block: the scan returns what lies in front of it, then status -2
     // header
     std::string text;
     std::vector<std::string> ref_names;
@@ -63,6 +72,7 @@ struct dh_bam {
     std::deque<std::string> dict;
     std::vector<StrCell> ref_cells;
     std::vector<RgEntry> rg;
+    std::vector<std::string> rg_samples;   // SM value of every rg entry ("" = none)
     std::string rg_ids;
     DevBuf d_ref_cells, d_rg, d_rg_ids, d_tags;
     DevBuf d_image;                // whole compressed image staged in HBM (DH_BAM_DEVICE_INPUT)
@@ -81,13 +91,16 @@ struct dh_bam {
     // scan state
     std::vector<Seg> segs;
     SegSlot ss[NSEG];
-    BatchSlot bs[NBATCH];
+    BatchSlot bs[MAX_SLOTS];
+    int n_slots = DEFAULT_SLOTS;
+    int auto_slot = -1;            // slot handed out by dh_bam_next_batch: released by the next call
+    mutable std::mutex mu;         // serialises the entry points that touch the scan state (worker threads of one query)
     bool scanning = false;
     int cur_seg = -1;              // segment whose batches are being issued
     std::vector<Batch> batches;    // of cur_seg
     size_t next_batch_i = 0;
-    uint64_t issued = 0, returned = 0;  // batch counters (slot = counter % NBATCH)
-    std::deque<uint64_t> inflight;
+    uint64_t issued = 0, returned = 0;  // batch counters
+    std::deque<int> inflight;           // slots in issue order
     uint64_t rows_total = 0;
     int64_t carry = 0;             // bytes of the incomplete record at the end of the previous segment
     int final_status = 0;
@@ -104,6 +117,13 @@ struct dh_bam {
     std::vector<RegIntv> filt;
     DevBuf d_filt;
     std::deque<IdxChunk> pending;
+    // N3: record predicate evaluated by the walk kernel (dh_bam_set_filter)
+    uint32_t flag_require = 0, flag_exclude = 0, min_mapq = 0;
+    // dh_bam_batch_checksum: dictionary strings the device cannot follow (host pointers in cells) -> their hashes
+    DevBuf d_dict_ptr, d_dict_hash, d_ref_hash, d_sample_hash, d_sums;
+    PinBuf h_sums;
+    bool checksum_tables = false;
+    std::vector<uint64_t> h_ref_hash, h_sample_hash, h_dict_ptr, h_dict_hash;
 };
 
 
@@ -113,6 +133,10 @@ int scan_ensure_events(dh_bam *b);
 int scan_begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fresh);
 // 1 = a batch of the current segment is ready to be issued, 0 = scan exhausted, < 0 error
 int scan_have_work(dh_bam *b);
+// batch slots: a free slot or -1; give a held slot back
+int scan_take_slot(dh_bam *b);
+void scan_release_slot(dh_bam *b, int slot);
+int scan_free_slots(const dh_bam *b);
 // indexed scan over b->filt (intervals): plans the virtual-offset ranges, uploads the filter, begins the first range
 int scan_start_filtered(dh_bam *b, const dh_index *idx, int mode);
 // inflate the leading blocks of the image until `want` inflated bytes are available (or the file ends)

@@ -1,23 +1,30 @@
-/* duckhts_ext.c — the DuckDB side of duckhts_b200: a C extension that registers `read_bam` and `bgunzip` with the
- * same names, parameters, column schemas and error behaviour as the reference (src/bam_reader.c:1044-1068,
- * src/bgzip.c:359-380) and serves them from the GPU through the C-ABI of libduckhts_cuda.so
+/* duckhts_ext.c — the DuckDB side of duckhts_b200: a C extension that registers `read_bam`, `read_bcf` and `bgunzip`
+ * with the same names, parameters, column schemas and error behaviour as the reference (src/bam_reader.c:1044-1068,
+ * src/bcf_reader.c:2055-2081, src/bgzip.c:359-380) and serves them from the GPU through the C-ABI of libduckhts_cuda.so
  * (include/duckhts_cuda.h).  Host code in C, as the reference's; no htslib, no CPU decode path.
  *
  * Entry point: duckhts_init_c_api (reference duckdb_capi/duckdb_extension.h:1179-1195) — the extension is a
- * drop-in for the reference's shared object as far as these two table functions go.
+ * drop-in for the reference's shared object as far as these table functions go.
  *
  * How a scan maps onto the reference's callbacks (src/bam_reader.c:410-1038):
- *   bind        reads the file into pinned memory, dh_bam_open (BGZF framing on the host, header inflated on the GPU),
- *               declares the schema (13 SAM columns [+ 56 SAMtags columns] — same order and types)
- *   global init max_threads = 1: the GPU is the parallelism; rows come back in file order (the reference's sequential
- *               order; in its contig-parallel mode DuckDB interleaves threads nondeterministically)
- *   local init  projection pushdown -> dh_bam_set_projection, dh_bam_scan_begin
- *   scan        copies up to duckdb_vector_size() rows of the current dh_bam_batch into the output chunk: fixed-width
- *               columns by memcpy, VARCHAR cells of <= 12 bytes by a 16-byte store (the kernel wrote duckdb_string_t),
- *               longer strings through duckdb_vector_assign_string_element_len, NULLs through the validity mask.
+ *   bind        opens the file on the first GPU (BGZF framing on the host, header inflated on the GPU) in a dh_ctx of its
+ *               own (queries never share streams), declares the schema (13 SAM columns [+ 56 SAMtags columns] [+ MAP])
+ *   global init projection pushdown -> dh_bam_set_projection; cuts the file into one SOURCE per GPU (contig groups from
+ *               the index where the reference scans contig by contig, else virtual-offset ranges; a region query stays on
+ *               one GPU), starts every source's pipeline, max_threads = 64
+ *   local init  numbers the worker
+ *   scan        a worker CLAIMS the next duckdb_vector_size() rows of a source's current batch under that source's lock and
+ *               fills its chunk outside the lock: fixed-width columns by memcpy / widening loops, VARCHAR cells of <= 12
+ *               bytes by a 16-byte store, longer strings through duckdb_vector_assign_string_element_len, NULLs through
+ *               the validity mask.  Batches are reference-counted and go back to the pipeline when their last claim is
+ *               filled.  One worker walks the sources in order = file order (the reference's order); several
+ *               workers interleave chunks like DuckDB interleaves the reference's threads.
+ * Batches cross PCIe in the compact wire layout (include/duckhts_cuda.h, DH_BAM_COMPACT_OUTPUT) unless AUXILIARY_TAGS is
+ * projected or DUCKHTS_LAYOUT=duckdb asks for ready-made DuckDB vectors.
  */
 #define _GNU_SOURCE
 #include <errno.h>
+#include <fcntl.h>
 #include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -30,37 +37,67 @@
 
 static duckdb_ext_api_v1 api;   /* the host's function table, copied by value like DUCKDB_EXTENSION_API_INIT does */
 
-/* ---- one GPU context per process (device from DUCKHTS_DEVICE, default 0) ------------------------------------------ */
-static pthread_mutex_t g_lock = PTHREAD_MUTEX_INITIALIZER;
-static dh_ctx *g_ctx;
-static dh_ctx *shared_ctx(void) {
-    pthread_mutex_lock(&g_lock);
-    if (!g_ctx) {
-        const char *d = getenv("DUCKHTS_DEVICE");
-        g_ctx = dh_ctx_create(d ? atoi(d) : 0);
+/* ---- GPUs ----------------------------------------------------------------------------------------------------------
+ * DUCKHTS_DEVICES = comma-separated CUDA device ordinals a query may use (a device may be named twice: two pipelines on
+ * one GPU); DUCKHTS_DEVICE = one ordinal (older spelling); default: every visible device.  The first entry serves bind. */
+#define MAX_SOURCES 16
+static int device_list(int *devs) {
+    int n = 0;
+    const char *e = getenv("DUCKHTS_DEVICES");
+    if (e && *e) {
+        char *dup = strdup(e), *save = NULL;
+        for (char *tok = strtok_r(dup, ",", &save); tok && n < MAX_SOURCES; tok = strtok_r(NULL, ",", &save)) devs[n++] = atoi(tok);
+        free(dup);
+    } else if ((e = getenv("DUCKHTS_DEVICE")) && *e) devs[n++] = atoi(e);
+    else {
+        const int have = dh_device_count();
+        for (int d = 0; d < have && n < MAX_SOURCES; ++d) devs[n++] = d;
     }
-    dh_ctx *c = g_ctx;
-    pthread_mutex_unlock(&g_lock);
-    return c;
+    if (n == 0) devs[n++] = 0;
+    return n;
+}
+static uint64_t env_u64(const char *name, uint64_t dflt) {
+    const char *e = getenv(name);
+    return (e && *e) ? strtoull(e, NULL, 0) : dflt;
 }
 
-/* whole file -> pinned host memory (the C-ABI copies from it at full PCIe rate) */
-static uint8_t *slurp_pinned(const char *path, uint64_t *size_out) {
-    FILE *f = fopen(path, "rb");
-    if (!f) return NULL;
-    struct stat st;
-    if (fstat(fileno(f), &st) != 0 || !S_ISREG(st.st_mode)) { fclose(f); return NULL; }
-    uint64_t n = (uint64_t)st.st_size;
-    uint8_t *p = (uint8_t *)dh_host_alloc(n ? n : 1);
-    if (!p) { fclose(f); return NULL; }
+/* whole file -> pinned host memory (the C-ABI copies from it at full PCIe rate); read by a few threads, because one
+ * thread copies out of the page cache at a fraction of what the GPU takes */
+typedef struct { int fd; uint8_t *dst; uint64_t off, len; int ok; } slurp_part;
+static void *slurp_worker(void *arg) {
+    slurp_part *p = (slurp_part *)arg;
     uint64_t got = 0;
-    while (got < n) {
-        size_t k = fread(p + got, 1, (size_t)((n - got) < (64u << 20) ? (n - got) : (64u << 20)), f);
-        if (k == 0) break;
-        got += k;
+    p->ok = 1;
+    while (got < p->len) {
+        const ssize_t k = pread(p->fd, p->dst + got, (size_t)((p->len - got) < (64u << 20) ? (p->len - got) : (64u << 20)), (off_t)(p->off + got));
+        if (k <= 0) { if (k < 0 && errno == EINTR) continue; p->ok = 0; break; }
+        got += (uint64_t)k;
     }
-    fclose(f);
-    if (got != n) { dh_host_free(p); return NULL; }
+    return NULL;
+}
+static uint8_t *slurp_pinned(const char *path, uint64_t *size_out) {
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return NULL;
+    struct stat st;
+    if (fstat(fd, &st) != 0 || !S_ISREG(st.st_mode)) { close(fd); return NULL; }
+    const uint64_t n = (uint64_t)st.st_size;
+    uint8_t *p = (uint8_t *)dh_host_alloc(n ? n : 1);
+    if (!p) { close(fd); return NULL; }
+    int nt = (int)(n >> 26);            /* one reader per 64 MiB, at most 8 */
+    if (nt < 1) nt = 1;
+    if (nt > 8) nt = 8;
+    slurp_part parts[8];
+    pthread_t th[8];
+    for (int i = 0; i < nt; ++i) {
+        parts[i].fd = fd; parts[i].dst = p + n * (uint64_t)i / (uint64_t)nt; parts[i].off = n * (uint64_t)i / (uint64_t)nt;
+        parts[i].len = n * (uint64_t)(i + 1) / (uint64_t)nt - parts[i].off; parts[i].ok = 0;
+        if (i > 0 && pthread_create(&th[i], NULL, slurp_worker, &parts[i]) != 0) { slurp_worker(&parts[i]); th[i] = 0; }
+    }
+    slurp_worker(&parts[0]);
+    int ok = parts[0].ok;
+    for (int i = 1; i < nt; ++i) { if (th[i]) pthread_join(th[i], NULL); ok = ok && parts[i].ok; }
+    close(fd);
+    if (!ok) { dh_host_free(p); return NULL; }
     *size_out = n;
     return p;
 }
@@ -76,6 +113,13 @@ static int named_bool(duckdb_bind_info info, const char *name, int dflt) {
     duckdb_value v = api.duckdb_bind_get_named_parameter(info, name);
     int r = dflt;
     if (v && !api.duckdb_is_null_value(v)) r = api.duckdb_get_bool(v) ? 1 : 0;
+    if (v) api.duckdb_destroy_value(&v);
+    return r;
+}
+static int64_t named_int(duckdb_bind_info info, const char *name, int64_t dflt) {
+    duckdb_value v = api.duckdb_bind_get_named_parameter(info, name);
+    int64_t r = dflt;
+    if (v && !api.duckdb_is_null_value(v)) r = api.duckdb_get_int64(v);
     if (v) api.duckdb_destroy_value(&v);
     return r;
 }
@@ -106,6 +150,60 @@ static dh_index *find_index(dh_ctx *ctx, const char *path, const char *index_pat
     return ix;
 }
 
+/* ---- helpers shared by the fillers -------------------------------------------------------------------------------------- */
+static inline int bit_valid(const uint64_t *v, uint64_t i) { return !v || ((v[i >> 6] >> (i & 63)) & 1); }
+/* 1 if rows [r0, r0 + n) are all valid */
+static int range_all_valid(const uint64_t *v, uint64_t r0, uint64_t n) {
+    if (!v || !n) return 1;
+    const uint64_t r1 = r0 + n;
+    uint64_t w = r0 >> 6;
+    const uint64_t w1 = (r1 - 1) >> 6;
+    for (; w <= w1; ++w) {
+        uint64_t m = ~0ull;
+        if (w == (r0 >> 6)) m &= ~0ull << (r0 & 63);
+        if (w == w1 && (r1 & 63)) m &= ~0ull >> (64 - (r1 & 63));
+        if ((v[w] & m) != m) return 0;
+    }
+    return 1;
+}
+/* validity bits [r0, r0 + n) of a batch column -> rows [0, n) of the vector's mask (word copies) */
+static void copy_validity(duckdb_vector vec, const uint64_t *v, uint64_t r0, idx_t n) {
+    if (range_all_valid(v, r0, n)) return;
+    api.duckdb_vector_ensure_validity_writable(vec);
+    uint64_t *dst = api.duckdb_vector_get_validity(vec);
+    const unsigned sh = (unsigned)(r0 & 63);
+    const uint64_t w0 = r0 >> 6;
+    for (idx_t w = 0; w * 64 < n; ++w) {
+        uint64_t bits = v[w0 + w] >> sh;
+        if (sh && (w * 64 + (64 - sh)) < n) bits |= v[w0 + w + 1] << (64 - sh);
+        const idx_t left = n - w * 64;
+        if (left < 64) bits |= ~0ull << left;   /* rows past the chunk stay valid */
+        dst[w] = bits;
+    }
+}
+static inline void put_string(duckdb_vector vec, duckdb_string_t *out, idx_t row, const char *p, uint32_t len) {
+    if (len <= 12) {
+        duckdb_string_t c;
+        memset(&c, 0, sizeof c);
+        c.value.inlined.length = len;
+        memcpy(c.value.inlined.inlined, p, len);
+        out[row] = c;
+    } else api.duckdb_vector_assign_string_element_len(vec, row, p, len);
+}
+static inline void put_cell(duckdb_vector vec, duckdb_string_t *out, idx_t row, const duckdb_string_t *cell) {
+    if (cell->value.inlined.length <= 12) out[row] = *cell;
+    else api.duckdb_vector_assign_string_element_len(vec, row, cell->value.pointer.ptr, cell->value.inlined.length);
+}
+static duckdb_string_t make_const_cell(const char *s) {   /* cell over memory that outlives the query's chunks only if <= 12 bytes: longer ones are copied per row */
+    duckdb_string_t c;
+    memset(&c, 0, sizeof c);
+    const size_t n = s ? strlen(s) : 0;
+    c.value.inlined.length = (uint32_t)n;
+    if (n <= 12) memcpy(c.value.inlined.inlined, s, n);
+    else { memcpy(c.value.pointer.prefix, s, 4); c.value.pointer.ptr = (char *)s; }
+    return c;
+}
+
 /* ================================================================================================================
  * read_bam
  * ================================================================================================================ */
@@ -121,39 +219,83 @@ typedef struct {
     char *path;
     uint8_t *image;
     uint64_t size;
+    dh_ctx *ctx;             /* this query's context on the first device */
     dh_bam *bam;
     dh_index *index;         /* BAI/CSI next to the file (or index_path), NULL if none: sam_index_load3, bam_reader.c:499 */
     char *region;            /* the `region` parameter as given (comma separated), NULL if absent or empty */
     int standard_tags, has_index, n_contigs;
     int n_cols;
     int aux_col;             /* schema index of AUXILIARY_TAGS (auxiliary_tags := true), else -1 */
+    uint32_t flag_require, flag_exclude, min_mapq;   /* N3 predicate pushdown (extra named parameters; 0 = none) */
 } bam_bind_t;
 
+/* a batch shared by the workers that claimed rows of it */
 typedef struct {
+    dh_bam_batch b;
+    int refs, closed;
+} bam_batch_ref;
+
+typedef struct {
+    dh_ctx *ctx;             /* NULL for the source that uses the bind's context / handle */
+    dh_bam *bam;
+    int owns;
+    pthread_mutex_t mu;
+    bam_batch_ref *cur;
+    uint64_t cursor;         /* next row of `cur` to hand out */
+    int done;
+} bam_source_t;
+
+enum { SC_QNAME, SC_QUAL, SC_STR, SC_LIST };
+typedef struct { int abi_col, out, kind, nullable; } slot_col_t;
+
+typedef struct {
+    bam_bind_t *bind;
+    int n_src;
+    bam_source_t src[MAX_SOURCES];
     idx_t n_proj;
     idx_t *col_ids;          /* schema column of output vector i */
-    int *abi_col;            /* its column in dh_bam_batch, or -1 for a column this build always returns NULL for */
-    dh_bam_batch batch;
-    uint64_t cursor;         /* next row of `batch` to hand out */
-    int have_batch, done;
-} bam_local_t;
+    int *abi_col;            /* its column in dh_bam_batch, -2 = AUXILIARY_TAGS, -1 = a column this build always returns NULL for */
+    int *out_of_abi;         /* inverse: output vector of a batch column, or -1 */
+    int compact;
+    int n_slot_cols;
+    slot_col_t slot_cols[DH_BAM_MAX_COLS + 1];   /* compact layout: string columns in heap-slot order */
+    duckdb_string_t *ref_cells;                  /* n_ref + 1 ("*") */
+    int n_ref;
+    duckdb_string_t *sample_cells;               /* per @RG entry */
+    int n_rg;
+    int next_worker;         /* atomic */
+    int cancel_from;         /* atomic: sources >= this are not read (an earlier one ended in an error / invalid record) */
+    char type_of[DH_BAM_MAX_COLS];               /* per batch column: tag type letter, 0 for core columns */
+} bam_global_t;
+
+typedef struct { int worker; } bam_local_t;
 
 static void bam_bind_free(void *p) {
     bam_bind_t *b = (bam_bind_t *)p;
     if (!b) return;
     if (b->bam) dh_bam_close(b->bam);
     if (b->index) dh_index_free(b->index);
+    if (b->ctx) dh_ctx_destroy(b->ctx);
     if (b->image) dh_host_free(b->image);
     free(b->path);
     free(b->region);
     api.duckdb_free(b);
 }
-static void bam_local_free(void *p) {
-    bam_local_t *l = (bam_local_t *)p;
-    if (!l) return;
-    free(l->col_ids);
-    free(l->abi_col);
-    api.duckdb_free(l);
+static void bam_release_ref(bam_source_t *s, bam_batch_ref *br) {
+    dh_bam_release_batch(s->bam, br->b.slot);
+    free(br);
+}
+static void bam_global_free(void *p) {
+    bam_global_t *g = (bam_global_t *)p;
+    if (!g) return;
+    for (int i = 0; i < g->n_src; ++i) {
+        bam_source_t *s = &g->src[i];
+        if (s->cur) { free(s->cur); s->cur = NULL; }     /* the handle forgets its held slots at the next scan / close */
+        if (s->owns) { if (s->bam) dh_bam_close(s->bam); if (s->ctx) dh_ctx_destroy(s->ctx); }
+        pthread_mutex_destroy(&s->mu);
+    }
+    free(g->col_ids); free(g->abi_col); free(g->out_of_abi); free(g->ref_cells); free(g->sample_cells);
+    api.duckdb_free(g);
 }
 
 static void read_bam_bind(duckdb_bind_info info) {
@@ -169,15 +311,16 @@ static void read_bam_bind(duckdb_bind_info info) {
     const int standard_tags = named_bool(info, "standard_tags", 0), auxiliary_tags = named_bool(info, "auxiliary_tags", 0);
     char err[768];
     err[0] = 0;
-    bam_bind_t *b = NULL;
-    dh_ctx *ctx = shared_ctx();
-    if (!ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
+    bam_bind_t *b = (bam_bind_t *)api.duckdb_malloc(sizeof *b);
+    memset(b, 0, sizeof *b);
+    int devs[MAX_SOURCES];
+    device_list(devs);
+    b->ctx = dh_ctx_create(devs[0]);
+    if (!b->ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
     else {
-        b = (bam_bind_t *)api.duckdb_malloc(sizeof *b);
-        memset(b, 0, sizeof *b);
         b->image = slurp_pinned(path, &b->size);
         if (!b->image) snprintf(err, sizeof err, "Failed to open SAM/BAM/CRAM file: %s", path);
-        else if (!(b->bam = dh_bam_open(ctx, b->image, b->size))) snprintf(err, sizeof err, "Failed to read SAM/BAM/CRAM header");
+        else if (!(b->bam = dh_bam_open(b->ctx, b->image, b->size))) snprintf(err, sizeof err, "Failed to read SAM/BAM/CRAM header");
     }
     if (err[0]) {
         api.duckdb_bind_set_error(info, err);
@@ -191,8 +334,12 @@ static void read_bam_bind(duckdb_bind_info info) {
     b->path = strdup(path);
     b->standard_tags = standard_tags;
     b->n_contigs = dh_bam_n_ref(b->bam);
+    /* N3 (not in the reference's signature; absent = no filter): rows whose FLAG / MAPQ fail are dropped on the GPU */
+    b->flag_require = (uint32_t)named_int(info, "flag_require", 0);
+    b->flag_exclude = (uint32_t)named_int(info, "flag_exclude", 0);
+    b->min_mapq = (uint32_t)named_int(info, "min_mapq", 0);
     if (region && region[0]) b->region = strdup(region);
-    b->index = find_index(ctx, path, index_path, 2);
+    b->index = find_index(b->ctx, path, index_path, 2);
     b->has_index = b->index != NULL;
     duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER),
                         t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT), t_usmall = api.duckdb_create_logical_type(DUCKDB_TYPE_USMALLINT),
@@ -231,152 +378,213 @@ static void read_bam_bind(duckdb_bind_info info) {
     if (reference) api.duckdb_free(reference);
 }
 
+/* global init: projection pushdown (src/bam_reader.c:676-679 does it per thread; one GPU pipeline serves all threads here),
+ * the sources (one per GPU) and which rows each of them scans (src/bam_reader.c:577-585, 601-671, 689-716) */
 static void read_bam_init(duckdb_init_info info) {
-    api.duckdb_init_set_max_threads(info, 1);
-    api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free);
-}
-
-static void read_bam_local_init(duckdb_init_info info) {
     bam_bind_t *b = (bam_bind_t *)api.duckdb_init_get_bind_data(info);
-    bam_local_t *l = (bam_local_t *)api.duckdb_malloc(sizeof *l);
-    memset(l, 0, sizeof *l);
-    l->n_proj = api.duckdb_init_get_column_count(info);
-    l->col_ids = (idx_t *)calloc(l->n_proj ? l->n_proj : 1, sizeof(idx_t));
-    l->abi_col = (int *)calloc(l->n_proj ? l->n_proj : 1, sizeof(int));
-    /* projection pushdown (src/bam_reader.c:676-679): only projected columns are decoded on the GPU.  Tag columns are
-     * requested from the C-ABI in projection order; tag k of the request is column 13 + k of every batch. */
+    bam_global_t *g = (bam_global_t *)api.duckdb_malloc(sizeof *g);
+    memset(g, 0, sizeof *g);
+    g->bind = b;
+    g->cancel_from = MAX_SOURCES + 1;
+    g->n_proj = api.duckdb_init_get_column_count(info);
+    g->col_ids = (idx_t *)calloc(g->n_proj ? g->n_proj : 1, sizeof(idx_t));
+    g->abi_col = (int *)calloc(g->n_proj ? g->n_proj : 1, sizeof(int));
+    g->out_of_abi = (int *)malloc(sizeof(int) * DH_BAM_MAX_COLS);
+    for (int c = 0; c < DH_BAM_MAX_COLS; ++c) g->out_of_abi[c] = -1;
+    /* Tag columns are requested from the C-ABI in projection order; tag k of the request is column 13 + k of every batch. */
     uint64_t mask = 0;
     dh_tag_req tags[DH_BAM_MAX_TAGS];
     int n_tags = 0, want_map = 0;
-    for (idx_t i = 0; i < l->n_proj; ++i) {
+    for (idx_t i = 0; i < g->n_proj; ++i) {
         const idx_t c = api.duckdb_init_get_column_index(info, i);
-        l->col_ids[i] = c;
-        if (c < N_CORE) { l->abi_col[i] = (int)c; mask |= 1ull << c; continue; }
-        if ((int)c == b->aux_col) { l->abi_col[i] = -2; want_map = 1; continue; }
+        g->col_ids[i] = c;
+        if (c < N_CORE) { g->abi_col[i] = (int)c; mask |= 1ull << c; continue; }
+        if ((int)c == b->aux_col) { g->abi_col[i] = -2; want_map = 1; continue; }
         const char *e = STD_TAGS + 4 * (c - N_CORE);
-        if (c - N_CORE >= N_STD_TAGS || n_tags >= DH_BAM_MAX_TAGS) { l->abi_col[i] = -1; continue; }
+        if (c - N_CORE >= N_STD_TAGS || n_tags >= DH_BAM_MAX_TAGS) { g->abi_col[i] = -1; continue; }
         tags[n_tags].tag[0] = e[0]; tags[n_tags].tag[1] = e[1]; tags[n_tags].type = e[2]; tags[n_tags].pad = e[2] == 'B' ? e[3] : 0;
-        l->abi_col[i] = N_CORE + n_tags;
+        g->abi_col[i] = N_CORE + n_tags;
+        g->type_of[N_CORE + n_tags] = e[2];
         if (N_CORE + n_tags < 64) mask |= 1ull << (N_CORE + n_tags);   /* tag columns past bit 63 are always projected */
         ++n_tags;
     }
-    /* which rows (src/bam_reader.c:601-671): region(s) through the index; else, with an index and more than one contig,
-     * contig by contig (reads without a contig are then never returned); else the whole file in order */
-    int rc = dh_bam_set_projection(b->bam, mask, tags, n_tags);
-    if (rc == DH_OK) {   /* the MAP leaves out the tags served as typed columns (bam_reader.c:976) */
-        char excl[2 * N_STD_TAGS];
-        for (int k = 0; k < N_STD_TAGS; ++k) { excl[2 * k] = STD_TAGS[4 * k]; excl[2 * k + 1] = STD_TAGS[4 * k + 1]; }
-        rc = dh_bam_set_aux_map(b->bam, want_map, excl, b->standard_tags ? N_STD_TAGS : 0);
-    }
+    /* a column projected twice is filled once per output vector: keep the first for the slot walk, the rest are copies */
+    for (idx_t i = 0; i < g->n_proj; ++i)
+        if (g->abi_col[i] >= 0 && g->out_of_abi[g->abi_col[i]] < 0) g->out_of_abi[g->abi_col[i]] = (int)i;
+    const char *lay = getenv("DUCKHTS_LAYOUT");
+    g->compact = !want_map && !(lay && !strcmp(lay, "duckdb"));
+    /* the compact fill walks each row's heap slots once, so every output vector needs its own batch column */
+    for (idx_t i = 0; i < g->n_proj && g->compact; ++i)
+        if (g->abi_col[i] >= 0 && g->out_of_abi[g->abi_col[i]] != (int)i) g->compact = 0;
+
     char err[1200];
     err[0] = 0;
-    if (rc != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
-    else if (b->region) {
-        if (!b->index) snprintf(err, sizeof err, "Region query requires an index (.bai/.csi/.crai)");
+    char excl[2 * N_STD_TAGS];
+    for (int k = 0; k < N_STD_TAGS; ++k) { excl[2 * k] = STD_TAGS[4 * k]; excl[2 * k + 1] = STD_TAGS[4 * k + 1]; }
+    /* how many GPUs: a region query stays on one; otherwise one source per listed device while shards stay above
+     * DUCKHTS_MIN_SHARD_BYTES of compressed input (default 256 MiB: below that the second GPU's start-up costs more than it saves) */
+    int devs[MAX_SOURCES];
+    int n_dev = device_list(devs);
+    const uint64_t min_shard = env_u64("DUCKHTS_MIN_SHARD_BYTES", 256ull << 20);
+    int n_src = 1;
+    const int contig_mode = !b->region && b->index && b->n_contigs > 1;
+    if (!b->region) {
+        n_src = n_dev;
+        while (n_src > 1 && b->size / (uint64_t)n_src < min_shard) --n_src;
+        if (contig_mode && n_src > b->n_contigs) n_src = b->n_contigs;
+    }
+    const int n_slots = (int)env_u64("DUCKHTS_SLOTS", 8);
+    const uint32_t batch_rows = (uint32_t)env_u64("DUCKHTS_BATCH_ROWS", 256u << 10);
+    int32_t tid_bounds[MAX_SOURCES + 1];
+    uint64_t voffs[MAX_SOURCES + 1];
+    if (n_src > 1) {
+        const int rc = contig_mode ? dh_bam_split_contigs(b->bam, b->index, n_src, tid_bounds) : dh_bam_split(b->bam, n_src, voffs);
+        if (rc != DH_OK) n_src = 1;
+    }
+    for (int i = 0; i < n_src && !err[0]; ++i) {
+        bam_source_t *s = &g->src[i];
+        pthread_mutex_init(&s->mu, NULL);
+        g->n_src = i + 1;
+        if (i == 0) { s->bam = b->bam; s->ctx = NULL; s->owns = 0; }
         else {
-            char *dup = strdup(b->region), *save = NULL;
-            const char *regs[1024];
-            int nreg = 0;
-            for (char *tok = strtok_r(dup, ",", &save); tok && nreg < 1024; tok = strtok_r(NULL, ",", &save)) regs[nreg++] = tok;
-            rc = dh_bam_scan_regions(b->bam, b->index, regs, nreg);
-            if (rc == DH_ENOREGION) snprintf(err, sizeof err, "No reads found for region(s): %s", b->region);
-            else if (rc != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
-            free(dup);
+            s->owns = 1;
+            s->ctx = dh_ctx_create(devs[i]);
+            s->bam = s->ctx ? dh_bam_clone(b->bam, s->ctx) : NULL;
+            if (!s->bam) { snprintf(err, sizeof err, "read_bam: cannot start a pipeline on device %d: %s", devs[i], dh_last_error()); break; }
         }
-    } else if (b->index && b->n_contigs > 1) {
-        if (dh_bam_scan_contigs(b->bam, b->index, 0, b->n_contigs) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
-    } else if (dh_bam_scan_begin(b->bam, 0, UINT64_MAX) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+        int rc = dh_bam_set_projection(s->bam, mask, tags, n_tags);
+        if (rc == DH_OK) rc = dh_bam_set_aux_map(s->bam, want_map, excl, b->standard_tags ? N_STD_TAGS : 0);   /* the MAP leaves out the typed columns (bam_reader.c:976) */
+        if (rc == DH_OK) rc = dh_bam_set_mode(s->bam, g->compact ? DH_BAM_COMPACT_OUTPUT : 0u);
+        if (rc == DH_OK) rc = dh_bam_set_filter(s->bam, b->flag_require, b->flag_exclude, b->min_mapq);
+        if (rc == DH_OK) rc = dh_bam_configure(s->bam, 0, batch_rows, 0);
+        if (rc == DH_OK) rc = dh_bam_set_slots(s->bam, n_slots);
+        if (rc != DH_OK) { snprintf(err, sizeof err, "%s", dh_last_error()); break; }
+        /* which rows (src/bam_reader.c:601-671): region(s) through the index; else, with an index and more than one contig,
+         * contig by contig (reads without a contig are then never returned); else the whole file in order */
+        if (b->region) {
+            if (!b->index) snprintf(err, sizeof err, "Region query requires an index (.bai/.csi/.crai)");
+            else {
+                char *dup = strdup(b->region), *save = NULL;
+                const char *regs[1024];
+                int nreg = 0;
+                for (char *tok = strtok_r(dup, ",", &save); tok && nreg < 1024; tok = strtok_r(NULL, ",", &save)) regs[nreg++] = tok;
+                rc = dh_bam_scan_regions(s->bam, b->index, regs, nreg);
+                if (rc == DH_ENOREGION) snprintf(err, sizeof err, "No reads found for region(s): %s", b->region);
+                else if (rc != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+                free(dup);
+            }
+        } else if (contig_mode) {
+            const int32_t lo = n_src > 1 ? tid_bounds[i] : 0, hi = n_src > 1 ? tid_bounds[i + 1] : b->n_contigs;
+            if (dh_bam_scan_contigs(s->bam, b->index, lo, hi) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+        } else {
+            const uint64_t lo = n_src > 1 ? voffs[i] : 0, hi = n_src > 1 ? voffs[i + 1] : UINT64_MAX;
+            if (lo == UINT64_MAX) { s->done = 1; continue; }             /* more parts than blocks */
+            if (dh_bam_scan_begin(s->bam, lo, hi) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+        }
+    }
+    /* every GPU starts uploading and inflating now, not when a worker first asks it for rows */
+    for (int i = 0; i < g->n_src && !err[0]; ++i)
+        if (!g->src[i].done && dh_bam_prefetch(g->src[i].bam) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
     if (err[0]) {
         api.duckdb_init_set_error(info, err);
-        bam_local_free(l);
+        bam_global_free(g);
         return;
     }
-    api.duckdb_init_set_init_data(info, l, bam_local_free);
+    /* compact layout: what the fillers need besides the batch */
+    if (g->compact) {
+        g->n_ref = b->n_contigs;
+        g->ref_cells = (duckdb_string_t *)calloc((size_t)g->n_ref + 1, sizeof(duckdb_string_t));
+        for (int t = 0; t < g->n_ref; ++t) g->ref_cells[t] = make_const_cell(dh_bam_ref_name(b->bam, t));
+        g->ref_cells[g->n_ref] = make_const_cell("*");
+        g->n_rg = dh_bam_n_rg(b->bam);
+        g->sample_cells = (duckdb_string_t *)calloc((size_t)g->n_rg + 1, sizeof(duckdb_string_t));
+        for (int r = 0; r < g->n_rg; ++r) g->sample_cells[r] = make_const_cell(dh_bam_rg_sample(b->bam, r));
+        /* heap-slot order of a row: QNAME, CIGAR, SEQ, QUAL, 'Z' / 'B' tag columns in request order, READ_GROUP_ID */
+        static const int CORE_SLOTS[4] = {0, 5, 9, 10};
+        int ns = 0;
+        for (int q = 0; q < 4; ++q)
+            if (g->out_of_abi[CORE_SLOTS[q]] >= 0) {
+                slot_col_t sc = {CORE_SLOTS[q], g->out_of_abi[CORE_SLOTS[q]], q == 0 ? SC_QNAME : q == 3 ? SC_QUAL : SC_STR, 0};
+                g->slot_cols[ns++] = sc;
+            }
+        for (int k = 0; k < n_tags; ++k) {
+            const char ty = g->type_of[N_CORE + k];
+            if (ty != 'Z' && ty != 'B') continue;
+            slot_col_t sc = {N_CORE + k, g->out_of_abi[N_CORE + k], ty == 'B' ? SC_LIST : SC_STR, 1};
+            g->slot_cols[ns++] = sc;
+        }
+        if (g->out_of_abi[11] >= 0) { slot_col_t sc = {11, g->out_of_abi[11], SC_STR, 1}; g->slot_cols[ns++] = sc; }
+        g->n_slot_cols = ns;
+    }
+    api.duckdb_init_set_max_threads(info, 64);
+    api.duckdb_init_set_init_data(info, g, bam_global_free);
+}
+
+static void read_bam_local_init(duckdb_init_info info) {
+    bam_local_t *l = (bam_local_t *)api.duckdb_malloc(sizeof *l);
+    l->worker = -1;     /* numbered at the first scan call (the global state is not reachable from here in the stable API) */
+    api.duckdb_init_set_init_data(info, l, api.duckdb_free);
 }
 
 static size_t core_width(idx_t c) { return c == 1 ? 2 : c == 4 ? 4 : (c == 3 || c == 7 || c == 8) ? 8 : 16; }
 
-static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
-    bam_bind_t *b = (bam_bind_t *)api.duckdb_function_get_bind_data(info);
-    bam_local_t *l = (bam_local_t *)api.duckdb_function_get_local_init_data(info);
-    if (!l || l->done) { api.duckdb_data_chunk_set_size(output, 0); return; }
-    while (!l->have_batch || l->cursor >= l->batch.n_rows) {
-        const int rc = dh_bam_next_batch(b->bam, &l->batch);
-        if (rc == 1) { l->have_batch = 1; l->cursor = 0; continue; }
-        l->done = 1;
-        /* rc == 0: end of file, or an invalid record ended the scan: the reference stops silently there too
-         * (src/bam_reader.c:754-765).  A failed BGZF block (DH_EDATA) is a read error to htslib = the same silent end.
-         * Anything else is a CUDA/runtime failure and is reported. */
-        if (rc < 0 && rc != DH_EDATA && rc != DH_EFORMAT) api.duckdb_function_set_error(info, dh_last_error());
-        api.duckdb_data_chunk_set_size(output, 0);
-        return;
-    }
-    const idx_t vs = api.duckdb_vector_size();
-    const uint64_t r0 = l->cursor;
-    const idx_t n = l->batch.n_rows - r0 < vs ? (idx_t)(l->batch.n_rows - r0) : vs;
-    for (idx_t i = 0; i < l->n_proj; ++i) {
+/* rows [r0, r0 + n) of a DuckDB-layout batch -> the output chunk */
+static void fill_duckdb_layout(bam_global_t *g, const dh_bam_batch *bt, uint64_t r0, idx_t n, duckdb_data_chunk output) {
+    for (idx_t i = 0; i < g->n_proj; ++i) {
         duckdb_vector vec = api.duckdb_data_chunk_get_vector(output, i);
-        const int ac = l->abi_col[i];
+        const int ac = g->abi_col[i];
         if (ac == -2) {   /* AUXILIARY_TAGS: list entries re-based onto the vector's child, key / value cells appended */
-            const duckdb_list_entry *cells = (const duckdb_list_entry *)l->batch.aux_map + r0;
-            const uint64_t *valid = l->batch.aux_map_validity;
+            const duckdb_list_entry *cells = (const duckdb_list_entry *)bt->aux_map + r0;
+            const uint64_t *valid = bt->aux_map_validity;
             duckdb_list_entry *out = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
-            uint64_t *val = NULL;
             idx_t total = api.duckdb_list_vector_get_size(vec), need = total;
             for (idx_t r = 0; r < n; ++r) need += cells[r].length;
             api.duckdb_list_vector_reserve(vec, need);
             api.duckdb_list_vector_set_size(vec, need);
             duckdb_vector child = api.duckdb_list_vector_get_child(vec);
             duckdb_vector kv[2] = {api.duckdb_struct_vector_get_child(child, 0), api.duckdb_struct_vector_get_child(child, 1)};
-            const duckdb_string_t *src[2] = {(const duckdb_string_t *)l->batch.aux_keys, (const duckdb_string_t *)l->batch.aux_values};
+            const duckdb_string_t *src[2] = {(const duckdb_string_t *)bt->aux_keys, (const duckdb_string_t *)bt->aux_values};
+            duckdb_string_t *dst[2] = {(duckdb_string_t *)api.duckdb_vector_get_data(kv[0]), (duckdb_string_t *)api.duckdb_vector_get_data(kv[1])};
             for (idx_t r = 0; r < n; ++r) {
                 out[r].offset = total;
                 out[r].length = cells[r].length;
-                if (!((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) {
-                    if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
-                    api.duckdb_validity_set_row_invalid(val, r);
-                    continue;
-                }
-                for (int q = 0; q < 2; ++q) {
-                    duckdb_string_t *dst = (duckdb_string_t *)api.duckdb_vector_get_data(kv[q]);
-                    for (uint64_t e = 0; e < cells[r].length; ++e) {
-                        const duckdb_string_t *cl = &src[q][cells[r].offset + e];
-                        if (cl->value.inlined.length <= 12) dst[total + e] = *cl;
-                        else api.duckdb_vector_assign_string_element_len(kv[q], total + e, cl->value.pointer.ptr, cl->value.inlined.length);
-                    }
-                }
+                if (!bit_valid(valid, r0 + r)) continue;
+                for (int q = 0; q < 2; ++q)
+                    for (uint64_t e = 0; e < cells[r].length; ++e) put_cell(kv[q], dst[q], total + e, &src[q][cells[r].offset + e]);
                 total += cells[r].length;
             }
+            copy_validity(vec, valid, r0, n);
             continue;
         }
         if (ac < 0) {   /* column not served: all NULL */
             api.duckdb_vector_ensure_validity_writable(vec);
             uint64_t *val = api.duckdb_vector_get_validity(vec);
             for (idx_t r = 0; r < n; ++r) api.duckdb_validity_set_row_invalid(val, r);
-            if (STD_TAGS[4 * (l->col_ids[i] - N_CORE) + 2] == 'B') {
+            if (STD_TAGS[4 * (g->col_ids[i] - N_CORE) + 2] == 'B') {
                 duckdb_list_entry *le = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
                 for (idx_t r = 0; r < n; ++r) { le[r].offset = 0; le[r].length = 0; }
             }
             continue;
         }
-        const idx_t c = l->col_ids[i];
-        size_t w = c < N_CORE ? core_width(c) : (STD_TAGS[4 * (c - N_CORE) + 2] == 'i' || STD_TAGS[4 * (c - N_CORE) + 2] == 'f') ? 8 : 16;
-        const uint8_t *src = (const uint8_t *)l->batch.data[ac] + r0 * w;
+        const idx_t c = g->col_ids[i];
+        const char ty = g->type_of[ac];
+        const size_t w = c < N_CORE ? core_width(c) : (ty == 'i' || ty == 'f') ? 8 : 16;
+        const uint8_t *src = (const uint8_t *)bt->data[ac] + r0 * w;
         void *dst = api.duckdb_vector_get_data(vec);
-        const uint64_t *valid = l->batch.validity[ac];
-        if (c >= N_CORE && STD_TAGS[4 * (c - N_CORE) + 2] == 'B') {
+        const uint64_t *valid = bt->validity[ac];
+        if (ty == 'B') {
             /* LIST cells (bam_assign_list_int/_double, src/bam_reader.c:106-138): children are appended to the list child */
             const duckdb_list_entry *cells = (const duckdb_list_entry *)src;
             duckdb_list_entry *out = (duckdb_list_entry *)dst;
             idx_t total = api.duckdb_list_vector_get_size(vec), need = total;
             for (idx_t r = 0; r < n; ++r)
-                if (!valid || ((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) need += cells[r].length;
+                if (bit_valid(valid, r0 + r)) need += cells[r].length;
             api.duckdb_list_vector_reserve(vec, need);
             api.duckdb_list_vector_set_size(vec, need);
             uint64_t *child = (uint64_t *)api.duckdb_vector_get_data(api.duckdb_list_vector_get_child(vec));
             for (idx_t r = 0; r < n; ++r) {
-                if (valid && !((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) continue;
-                memcpy(child + total, (const uint64_t *)l->batch.heap + cells[r].offset, 8 * cells[r].length);
+                if (!bit_valid(valid, r0 + r)) continue;
+                memcpy(child + total, (const uint64_t *)bt->heap + cells[r].offset, 8 * cells[r].length);
                 out[r].offset = total;
                 out[r].length = cells[r].length;
                 total += cells[r].length;
@@ -385,28 +593,199 @@ static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
         else {
             const duckdb_string_t *cells = (const duckdb_string_t *)src;
             duckdb_string_t *out = (duckdb_string_t *)dst;
-            for (idx_t r = 0; r < n; ++r) {
-                if (valid && !((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) continue;
-                if (cells[r].value.inlined.length <= 12) out[r] = cells[r];
-                else api.duckdb_vector_assign_string_element_len(vec, r, cells[r].value.pointer.ptr, cells[r].value.inlined.length);
-            }
+            if (range_all_valid(valid, r0, n)) for (idx_t r = 0; r < n; ++r) put_cell(vec, out, r, &cells[r]);
+            else for (idx_t r = 0; r < n; ++r) if (bit_valid(valid, r0 + r)) put_cell(vec, out, r, &cells[r]);
         }
-        if (valid) {
-            uint64_t *val = NULL;
+        copy_validity(vec, valid, r0, n);
+    }
+}
+
+/* rows [r0, r0 + n) of a compact-layout batch -> the output chunk (the expansion the GPU left to the host: widening, dictionary
+ * cells, one cell per string; include/duckhts_cuda.h DH_BAM_COMPACT_OUTPUT) */
+static void fill_compact_layout(bam_global_t *g, const dh_bam_batch *bt, uint64_t r0, idx_t n, duckdb_data_chunk output) {
+    /* fixed-width, dictionary and typed-scalar columns, one column at a time */
+    for (idx_t i = 0; i < g->n_proj; ++i) {
+        const int ac = g->abi_col[i];
+        duckdb_vector vec = api.duckdb_data_chunk_get_vector(output, i);
+        if (ac < 0) {   /* column not served: all NULL */
+            api.duckdb_vector_ensure_validity_writable(vec);
+            uint64_t *val = api.duckdb_vector_get_validity(vec);
+            for (idx_t r = 0; r < n; ++r) api.duckdb_validity_set_row_invalid(val, r);
+            if (STD_TAGS[4 * (g->col_ids[i] - N_CORE) + 2] == 'B') {
+                duckdb_list_entry *le = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
+                for (idx_t r = 0; r < n; ++r) { le[r].offset = 0; le[r].length = 0; }
+            }
+            continue;
+        }
+        void *dst = api.duckdb_vector_get_data(vec);
+        const uint64_t *valid = bt->validity[ac];
+        switch (ac) {
+        case 1: memcpy(dst, (const uint16_t *)bt->data[ac] + r0, n * 2); break;                                   /* FLAG */
+        case 4: { const uint8_t *s = (const uint8_t *)bt->data[ac] + r0; int32_t *d = (int32_t *)dst; for (idx_t r = 0; r < n; ++r) d[r] = s[r]; break; }
+        case 3: case 7: { const int32_t *s = (const int32_t *)bt->data[ac] + r0; int64_t *d = (int64_t *)dst; for (idx_t r = 0; r < n; ++r) d[r] = (int64_t)s[r] + 1; break; }   /* POS = pos + 1 (bam_reader.c:803), PNEXT */
+        case 8: { const int32_t *s = (const int32_t *)bt->data[ac] + r0; int64_t *d = (int64_t *)dst; for (idx_t r = 0; r < n; ++r) d[r] = s[r]; break; }
+        case 2: case 6: {                                                                                          /* RNAME / RNEXT: sam_hdr_tid2name or "*" */
+            const int32_t *s = (const int32_t *)bt->data[ac] + r0;
+            duckdb_string_t *d = (duckdb_string_t *)dst;
+            for (idx_t r = 0; r < n; ++r) put_cell(vec, d, r, &g->ref_cells[(s[r] >= 0 && s[r] < g->n_ref) ? s[r] : g->n_ref]);
+            break;
+        }
+        case 12: {                                                                                                 /* SAMPLE_ID: SM of the read's @RG line */
+            const int32_t *s = (const int32_t *)bt->data[ac] + r0;
+            duckdb_string_t *d = (duckdb_string_t *)dst;
             for (idx_t r = 0; r < n; ++r)
-                if (!((valid[(r0 + r) >> 6] >> ((r0 + r) & 63)) & 1)) {
-                    if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
-                    api.duckdb_validity_set_row_invalid(val, r);
-                }
+                if (bit_valid(valid, r0 + r) && s[r] >= 0 && s[r] < g->n_rg) put_cell(vec, d, r, &g->sample_cells[s[r]]);
+            copy_validity(vec, valid, r0, n);
+            break;
+        }
+        default: {
+            const char ty = g->type_of[ac];
+            if (ty == 'i' || ty == 'f') { memcpy(dst, (const uint64_t *)bt->data[ac] + r0, n * 8); copy_validity(vec, valid, r0, n); }
+            else if (ty == 'A') {
+                const uint8_t *s = (const uint8_t *)bt->data[ac] + r0;
+                duckdb_string_t *d = (duckdb_string_t *)dst;
+                for (idx_t r = 0; r < n; ++r) { memset(&d[r], 0, sizeof d[r]); if (s[r]) { d[r].value.inlined.length = 1; d[r].value.inlined.inlined[0] = (char)s[r]; } }
+                copy_validity(vec, valid, r0, n);
+            }
+            break;   /* string columns: the slot walk below */
+        }
         }
     }
-    l->cursor += n;
-    api.duckdb_data_chunk_set_size(output, n);
+    /* string columns: one walk over each row's heap slots */
+    const int ns = g->n_slot_cols;
+    if (!ns) return;
+    duckdb_vector vecs[DH_BAM_MAX_COLS + 1];
+    void *outp[DH_BAM_MAX_COLS + 1];
+    const uint32_t *lens[DH_BAM_MAX_COLS + 1];
+    const uint64_t *valids[DH_BAM_MAX_COLS + 1];
+    idx_t list_total[DH_BAM_MAX_COLS + 1];
+    uint64_t *list_child[DH_BAM_MAX_COLS + 1];
+    for (int q = 0; q < ns; ++q) {
+        const slot_col_t *sc = &g->slot_cols[q];
+        vecs[q] = api.duckdb_data_chunk_get_vector(output, (idx_t)sc->out);
+        outp[q] = api.duckdb_vector_get_data(vecs[q]);
+        lens[q] = (const uint32_t *)bt->data[sc->abi_col];
+        valids[q] = sc->nullable ? bt->validity[sc->abi_col] : NULL;
+        list_total[q] = 0;
+        list_child[q] = NULL;
+        if (sc->kind == SC_LIST) {   /* one reserve per chunk: the children of the chunk's cells */
+            const duckdb_list_entry *cells = (const duckdb_list_entry *)bt->data[sc->abi_col] + r0;
+            idx_t total = api.duckdb_list_vector_get_size(vecs[q]), need = total;
+            for (idx_t r = 0; r < n; ++r) if (bit_valid(valids[q], r0 + r)) need += cells[r].length;
+            api.duckdb_list_vector_reserve(vecs[q], need);
+            api.duckdb_list_vector_set_size(vecs[q], need);
+            list_total[q] = total;
+            list_child[q] = (uint64_t *)api.duckdb_vector_get_data(api.duckdb_list_vector_get_child(vecs[q]));
+        }
+    }
+    const uint8_t *heap = bt->heap;
+    for (idx_t r = 0; r < n; ++r) {
+        const uint64_t row = r0 + r;
+        uint64_t off = bt->rec_off[row];
+        for (int q = 0; q < ns; ++q) {
+            const slot_col_t *sc = &g->slot_cols[q];
+            if (valids[q] && !bit_valid(valids[q], row)) {
+                if (sc->kind == SC_LIST) { duckdb_list_entry *o = (duckdb_list_entry *)outp[q]; o[r].offset = list_total[q]; o[r].length = 0; }
+                continue;
+            }
+            const char *p = (const char *)heap + off;
+            if (sc->kind == SC_LIST) {
+                const duckdb_list_entry e = ((const duckdb_list_entry *)bt->data[sc->abi_col])[row];
+                duckdb_list_entry *o = (duckdb_list_entry *)outp[q];
+                memcpy(list_child[q] + list_total[q], (const uint64_t *)heap + e.offset, 8 * e.length);
+                o[r].offset = list_total[q];
+                o[r].length = e.length;
+                list_total[q] += e.length;
+                off += 4 + 8 * e.length;
+                continue;
+            }
+            const uint32_t v = lens[q][row], cap = v & 0x7fffffffu;
+            uint32_t len = cap;
+            if (sc->kind == SC_QNAME) len = (v >> 31) ? (uint32_t)strnlen(p, cap) : cap - 1;      /* C-string semantics */
+            else if (v >> 31) len = (uint32_t)strnlen(p, cap);                                   /* QUAL cut at a byte that wrapped to NUL */
+            put_string(vecs[q], (duckdb_string_t *)outp[q], r, p, len);
+            off += (cap + 3u) & ~3u;
+        }
+    }
+    for (int q = 0; q < ns; ++q)
+        if (valids[q]) copy_validity(vecs[q], valids[q], r0, n);
+}
+
+static int pick_source(bam_global_t *g, int worker) {
+    const int cancel = __atomic_load_n(&g->cancel_from, __ATOMIC_ACQUIRE);
+    const int pref = worker % g->n_src;
+    if (pref < cancel && !__atomic_load_n(&g->src[pref].done, __ATOMIC_ACQUIRE)) return pref;
+    for (int s = 0; s < g->n_src && s < cancel; ++s)
+        if (!__atomic_load_n(&g->src[s].done, __ATOMIC_ACQUIRE)) return s;
+    return -1;
+}
+
+static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
+    bam_global_t *g = (bam_global_t *)api.duckdb_function_get_init_data(info);
+    bam_local_t *l = (bam_local_t *)api.duckdb_function_get_local_init_data(info);
+    if (!g || !l) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    if (l->worker < 0) l->worker = __atomic_fetch_add(&g->next_worker, 1, __ATOMIC_RELAXED);
+    const idx_t vs = api.duckdb_vector_size();
+    for (;;) {
+        const int si = pick_source(g, l->worker);
+        if (si < 0) { api.duckdb_data_chunk_set_size(output, 0); return; }
+        bam_source_t *s = &g->src[si];
+        pthread_mutex_lock(&s->mu);
+        if (s->done) { pthread_mutex_unlock(&s->mu); continue; }
+        if (!s->cur || s->cursor >= s->cur->b.n_rows) {
+            if (s->cur) {   /* every row of it is claimed: it goes back when the last claim is filled */
+                s->cur->closed = 1;
+                if (s->cur->refs == 0) bam_release_ref(s, s->cur);
+                s->cur = NULL;
+            }
+            bam_batch_ref *br = (bam_batch_ref *)calloc(1, sizeof *br);
+            const int rc = dh_bam_acquire_batch(s->bam, &br->b);
+            if (rc == 1) { s->cur = br; s->cursor = 0; }
+            else {
+                free(br);
+                if (rc == DH_EBUSY) { pthread_mutex_unlock(&s->mu); usleep(100); continue; }   /* every slot is being filled from: wait for a release */
+                __atomic_store_n(&s->done, 1, __ATOMIC_RELEASE);
+                /* rc == 0: end of this source's rows — or an invalid record ended them: the reference stops silently there
+                 * (src/bam_reader.c:754-765), and so must everything behind it in file order.  A failed BGZF block (DH_EDATA) is
+                 * a read error to htslib = the same silent end.  Anything else (CUDA failure, a pipeline limit) is reported. */
+                dh_bam_scan_stats st;
+                memset(&st, 0, sizeof st);
+                dh_bam_scan_stats_get(s->bam, &st);
+                if (rc == DH_EDATA || (rc == 0 && st.status != 0)) {
+                    int cur = __atomic_load_n(&g->cancel_from, __ATOMIC_ACQUIRE);
+                    while (si + 1 < cur && !__atomic_compare_exchange_n(&g->cancel_from, &cur, si + 1, 0, __ATOMIC_ACQ_REL, __ATOMIC_ACQUIRE)) {}
+                }
+                pthread_mutex_unlock(&s->mu);
+                if (rc < 0 && rc != DH_EDATA) {
+                    api.duckdb_function_set_error(info, dh_last_error());
+                    api.duckdb_data_chunk_set_size(output, 0);
+                    return;
+                }
+                continue;
+            }
+        }
+        bam_batch_ref *br = s->cur;
+        const uint64_t r0 = s->cursor;
+        const idx_t n = br->b.n_rows - r0 < vs ? (idx_t)(br->b.n_rows - r0) : vs;
+        s->cursor += n;
+        br->refs++;
+        pthread_mutex_unlock(&s->mu);
+
+        if (br->b.layout == DH_BAM_COMPACT_OUTPUT) fill_compact_layout(g, &br->b, r0, n, output);
+        else fill_duckdb_layout(g, &br->b, r0, n, output);
+
+        pthread_mutex_lock(&s->mu);
+        if (--br->refs == 0 && br->closed) bam_release_ref(s, br);
+        pthread_mutex_unlock(&s->mu);
+        api.duckdb_data_chunk_set_size(output, n);
+        return;
+    }
 }
 
 static void register_read_bam(duckdb_connection con) {
     duckdb_table_function tf = api.duckdb_create_table_function();
-    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN);
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN),
+                        t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER);
     api.duckdb_table_function_set_name(tf, "read_bam");
     api.duckdb_table_function_add_parameter(tf, t_varchar);
     api.duckdb_table_function_add_named_parameter(tf, "region", t_varchar);
@@ -414,6 +793,10 @@ static void register_read_bam(duckdb_connection con) {
     api.duckdb_table_function_add_named_parameter(tf, "reference", t_varchar);
     api.duckdb_table_function_add_named_parameter(tf, "standard_tags", t_bool);
     api.duckdb_table_function_add_named_parameter(tf, "auxiliary_tags", t_bool);
+    /* N3, additions to the reference's signature: predicates evaluated on the GPU (dh_bam_set_filter) */
+    api.duckdb_table_function_add_named_parameter(tf, "flag_require", t_int);
+    api.duckdb_table_function_add_named_parameter(tf, "flag_exclude", t_int);
+    api.duckdb_table_function_add_named_parameter(tf, "min_mapq", t_int);
     api.duckdb_table_function_set_bind(tf, read_bam_bind);
     api.duckdb_table_function_set_init(tf, read_bam_init);
     api.duckdb_table_function_set_local_init(tf, read_bam_local_init);
@@ -423,6 +806,7 @@ static void register_read_bam(duckdb_connection con) {
     api.duckdb_destroy_table_function(&tf);
     api.duckdb_destroy_logical_type(&t_varchar);
     api.duckdb_destroy_logical_type(&t_bool);
+    api.duckdb_destroy_logical_type(&t_int);
 }
 
 /* ================================================================================================================
@@ -433,6 +817,7 @@ static void register_read_bam(duckdb_connection con) {
 typedef struct {
     uint8_t *image;
     uint64_t size;
+    dh_ctx *ctx;             /* this query's context */
     dh_bcf *bcf;
     int tidy, n_samples, n_info, n_fmt, default_gt;
     int info_start, sample_id_col, fmt_start, n_cols;
@@ -441,19 +826,28 @@ typedef struct {
     char *region;            /* the parameter as given */
     char **regions;          /* comma-separated, blanks trimmed, empty tokens dropped (parse_regions_duckdb, bcf_reader.c:286-329) */
     int n_regions;
+    duckdb_string_t *sample_cells;   /* SAMPLE_ID cells of the tidy rows, one per sample */
 } bcf_bind_t;
 
 typedef struct {
+    dh_bcf_batch b;
+    int refs, closed;
+} bcf_batch_ref;
+
+/* the scan all workers of a query share: one GPU pipeline, rows handed out chunk by chunk */
+typedef struct {
+    bcf_bind_t *bind;
     idx_t n_proj;
     idx_t *col_ids;
-    dh_bcf_batch batch;
+    pthread_mutex_t mu;
+    bcf_batch_ref *cur;
     uint64_t cursor;        /* next row of the batch: records (wide) or records x samples (tidy) */
-    int have_batch, done;
+    int done;
     int next_region;        /* region cursor of a chained region scan (bcf_reader.c:172, 1318-1333) */
-} bcf_local_t;
+} bcf_global_t;
 
 /* start the scan of the next region that yields an iterator: 1 started, 0 none left, < 0 error */
-static int bcf_next_region(bcf_bind_t *b, bcf_local_t *l) {
+static int bcf_next_region(bcf_bind_t *b, bcf_global_t *l) {
     while (l->next_region < b->n_regions) {
         const int rc = dh_bcf_scan_region(b->bcf, b->index, b->regions[l->next_region++]);
         if (rc == DH_OK) return 1;
@@ -466,19 +860,23 @@ static void bcf_bind_free(void *p) {
     bcf_bind_t *b = (bcf_bind_t *)p;
     if (!b) return;
     if (b->bcf) dh_bcf_close(b->bcf);
-    if (b->image) dh_host_free(b->image);
     if (b->index) dh_index_free(b->index);
+    if (b->ctx) dh_ctx_destroy(b->ctx);
+    if (b->image) dh_host_free(b->image);
     free(b->region);
     for (int i = 0; i < b->n_regions; ++i) free(b->regions[i]);
     free(b->regions);
     free(b->info);
     free(b->fmt);
+    free(b->sample_cells);
     api.duckdb_free(b);
 }
-static void bcf_local_free(void *p) {
-    bcf_local_t *l = (bcf_local_t *)p;
+static void bcf_global_free(void *p) {
+    bcf_global_t *l = (bcf_global_t *)p;
     if (!l) return;
+    free(l->cur);
     free(l->col_ids);
+    pthread_mutex_destroy(&l->mu);
     api.duckdb_free(l);
 }
 
@@ -503,12 +901,13 @@ static void read_bcf_bind(duckdb_bind_info info) {
     const int tidy = named_bool(info, "tidy_format", 0);
     char err[768];
     err[0] = 0;
-    bcf_bind_t *b = NULL;
-    dh_ctx *ctx = shared_ctx();
+    bcf_bind_t *b = (bcf_bind_t *)api.duckdb_malloc(sizeof *b);
+    memset(b, 0, sizeof *b);
+    int devs[MAX_SOURCES];
+    device_list(devs);
+    dh_ctx *ctx = b->ctx = dh_ctx_create(devs[0]);
     if (!ctx) snprintf(err, sizeof err, "read_bcf: no usable CUDA device (%s)", dh_last_error());
     else {
-        b = (bcf_bind_t *)api.duckdb_malloc(sizeof *b);
-        memset(b, 0, sizeof *b);
         if (region && region[0]) {
             b->region = strdup(region);
             b->regions = (char **)calloc(strlen(region) + 1, sizeof(char *));
@@ -587,6 +986,8 @@ static void read_bcf_bind(duckdb_bind_info info) {
             }
         }
         b->n_cols = col;
+        b->sample_cells = (duckdb_string_t *)calloc((size_t)b->n_samples + 1, sizeof(duckdb_string_t));
+        for (int sidx = 0; sidx < b->n_samples; ++sidx) b->sample_cells[sidx] = make_const_cell(dh_bcf_sample_name(b->bcf, sidx));
         api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_bigint); api.duckdb_destroy_logical_type(&t_double);
         api.duckdb_destroy_logical_type(&t_vlist);
         api.duckdb_bind_set_bind_data(info, b, bcf_bind_free);
@@ -596,15 +997,13 @@ static void read_bcf_bind(duckdb_bind_info info) {
     if (index_path) api.duckdb_free(index_path);
 }
 
+/* global init: projection pushdown and the start of the scan; max_threads = 64 workers share the one pipeline */
 static void read_bcf_init(duckdb_init_info info) {
-    api.duckdb_init_set_max_threads(info, 1);
-    api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free);
-}
-
-static void read_bcf_local_init(duckdb_init_info info) {
     bcf_bind_t *b = (bcf_bind_t *)api.duckdb_init_get_bind_data(info);
-    bcf_local_t *l = (bcf_local_t *)api.duckdb_malloc(sizeof *l);
+    bcf_global_t *l = (bcf_global_t *)api.duckdb_malloc(sizeof *l);
     memset(l, 0, sizeof *l);
+    pthread_mutex_init(&l->mu, NULL);
+    l->bind = b;
     l->n_proj = api.duckdb_init_get_column_count(info);
     l->col_ids = (idx_t *)calloc(l->n_proj ? l->n_proj : 1, sizeof(idx_t));
     uint32_t core_mask = 0;
@@ -616,117 +1015,192 @@ static void read_bcf_local_init(duckdb_init_info info) {
         else if ((int)c < b->info_start + b->n_info) iw[c - (idx_t)b->info_start] = 1;
         else if ((int)c >= b->fmt_start && (int)c != b->sample_id_col) fw[(c - (idx_t)b->fmt_start) % (idx_t)b->n_fmt] = 1;
     }
-    const int rc = dh_bcf_set_projection(b->bcf, core_mask, iw, b->default_gt ? NULL : fw);
+    int rc = dh_bcf_set_projection(b->bcf, core_mask, iw, b->default_gt ? NULL : fw);
     free(iw);
     free(fw);
+    if (rc == DH_OK) rc = dh_bcf_set_slots(b->bcf, (int)env_u64("DUCKHTS_SLOTS", 8));
     if (rc == DH_OK && b->n_regions > 0) {
         if (!b->index) {
             char err[600];
             snprintf(err, sizeof err, "Region query requires an index file (.tbi or .csi). Region: %s", b->region);
             api.duckdb_init_set_error(info, err);
-            bcf_local_free(l);
+            bcf_global_free(l);
             return;
         }
         const int started = bcf_next_region(b, l);
         if (started < 0) {
             api.duckdb_init_set_error(info, dh_last_error());
-            bcf_local_free(l);
+            bcf_global_free(l);
             return;
         }
         if (!started) l->done = 1;              /* no region named a contig: an empty result, not an error (bcf_reader.c:952-956) */
     } else if (rc != DH_OK || dh_bcf_scan_begin(b->bcf) != DH_OK) {
         api.duckdb_init_set_error(info, dh_last_error());
-        bcf_local_free(l);
+        bcf_global_free(l);
         return;
     }
-    api.duckdb_init_set_init_data(info, l, bcf_local_free);
+    api.duckdb_init_set_max_threads(info, 64);
+    api.duckdb_init_set_init_data(info, l, bcf_global_free);
 }
 
-static int cell_valid(const uint64_t *v, uint64_t i) { return !v || ((v[i >> 6] >> (i & 63)) & 1); }
-static void set_null(duckdb_vector vec, idx_t row) {
-    api.duckdb_vector_ensure_validity_writable(vec);
-    api.duckdb_validity_set_row_invalid(api.duckdb_vector_get_validity(vec), row);
-}
-static void put_varchar(duckdb_vector vec, idx_t row, const duckdb_string_t *cell) {
-    if (cell->value.inlined.length <= 12) ((duckdb_string_t *)api.duckdb_vector_get_data(vec))[row] = *cell;
-    else api.duckdb_vector_assign_string_element_len(vec, row, cell->value.pointer.ptr, cell->value.inlined.length);
-}
-/* one cell of a batch column -> row `row` of `vec`.  type: 0 BOOLEAN 1 INTEGER 2 FLOAT 3 VARCHAR 4 BIGINT 5 DOUBLE */
-static void emit_cell(duckdb_vector vec, idx_t row, int type, int is_list, const void *col, const uint64_t *validity, uint64_t i, const uint8_t *heap) {
-    const int ok = col && cell_valid(validity, i);
-    if (is_list) {
-        duckdb_list_entry *out = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
-        duckdb_list_entry e;
-        e.offset = api.duckdb_list_vector_get_size(vec);
-        e.length = 0;
-        if (ok) {
-            const duckdb_list_entry src = ((const duckdb_list_entry *)col)[i];
-            e.length = src.length;
-            if (e.length) {
-                api.duckdb_list_vector_reserve(vec, e.offset + e.length);
-                api.duckdb_list_vector_set_size(vec, e.offset + e.length);
-                duckdb_vector child = api.duckdb_list_vector_get_child(vec);
-                if (type == 3) {
-                    const duckdb_string_t *cells = (const duckdb_string_t *)(heap + 16 * src.offset);
-                    for (uint64_t k = 0; k < src.length; ++k) put_varchar(child, e.offset + k, &cells[k]);
-                } else memcpy((uint8_t *)api.duckdb_vector_get_data(child) + 4 * e.offset, heap + 4 * src.offset, 4 * src.length);
-            }
-        } else set_null(vec, row);
-        out[row] = e;
+static void read_bcf_local_init(duckdb_init_info info) { api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free); }
+
+/* ---- column fillers: one batch column -> one output vector, rows [0, n) of the chunk -------------------------------------
+ * Cell k of the chunk comes from batch cell idx(k) = (i0 + k) / div * mul + add: site-level columns of tidy rows repeat
+ * (div = n_samples), FORMAT columns of tidy rows run on (div = 1), wide FORMAT columns stride by n_samples.
+ * type: 0 BOOLEAN 1 INTEGER 2 FLOAT 3 VARCHAR 4 BIGINT 5 DOUBLE */
+typedef struct { uint64_t i0, div, mul, add; } cell_map;
+static inline uint64_t map_idx(const cell_map *m, idx_t k) { return (m->i0 + k) / m->div * m->mul + m->add; }
+
+static void fill_bcf_column(duckdb_vector vec, idx_t n, int type, int is_list, const void *col, const uint64_t *validity, const cell_map *m, const uint8_t *heap) {
+    const int contiguous = m->div == 1 && m->mul == 1;
+    uint64_t *val = NULL;
+    if (!col) {      /* not produced: NULL everywhere */
+        api.duckdb_vector_ensure_validity_writable(vec);
+        val = api.duckdb_vector_get_validity(vec);
+        for (idx_t k = 0; k < n; ++k) api.duckdb_validity_set_row_invalid(val, k);
+        if (is_list) { duckdb_list_entry *out = (duckdb_list_entry *)api.duckdb_vector_get_data(vec); const idx_t t0 = api.duckdb_list_vector_get_size(vec); for (idx_t k = 0; k < n; ++k) { out[k].offset = t0; out[k].length = 0; } }
         return;
     }
-    if (!ok) { set_null(vec, row); return; }
     void *dst = api.duckdb_vector_get_data(vec);
-    switch (type) {
-    case 0: ((uint8_t *)dst)[row] = ((const uint8_t *)col)[i]; break;
-    case 1: case 2: ((uint32_t *)dst)[row] = ((const uint32_t *)col)[i]; break;
-    case 3: put_varchar(vec, row, &((const duckdb_string_t *)col)[i]); break;
-    default: ((uint64_t *)dst)[row] = ((const uint64_t *)col)[i]; break;
+    if (is_list) {
+        /* one count pass, one reserve / set_size per chunk, one fill pass (the reference does a reserve per cell, bcf_reader.c:1542-1733) */
+        const duckdb_list_entry *cells = (const duckdb_list_entry *)col;
+        duckdb_list_entry *out = (duckdb_list_entry *)dst;
+        idx_t total = api.duckdb_list_vector_get_size(vec), need = total;
+        for (idx_t k = 0; k < n; ++k) { const uint64_t i = map_idx(m, k); if (bit_valid(validity, i)) need += cells[i].length; }
+        api.duckdb_list_vector_reserve(vec, need);
+        api.duckdb_list_vector_set_size(vec, need);
+        duckdb_vector child = api.duckdb_list_vector_get_child(vec);
+        void *cd = api.duckdb_vector_get_data(child);
+        for (idx_t k = 0; k < n; ++k) {
+            const uint64_t i = map_idx(m, k);
+            out[k].offset = total;
+            out[k].length = 0;
+            if (!bit_valid(validity, i)) {
+                if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
+                api.duckdb_validity_set_row_invalid(val, k);
+                continue;
+            }
+            const duckdb_list_entry src = cells[i];
+            out[k].length = src.length;
+            if (type == 3) {
+                const duckdb_string_t *sc = (const duckdb_string_t *)(heap + 16 * src.offset);
+                for (uint64_t e = 0; e < src.length; ++e) put_cell(child, (duckdb_string_t *)cd, total + e, &sc[e]);
+            } else memcpy((uint8_t *)cd + 4 * total, heap + 4 * src.offset, 4 * src.length);
+            total += src.length;
+        }
+        return;
+    }
+    const size_t w = type == 0 ? 1 : (type == 1 || type == 2) ? 4 : type == 3 ? 16 : 8;
+    if (contiguous) {
+        const uint64_t i0 = m->i0 + m->add;
+        if (type != 3) memcpy(dst, (const uint8_t *)col + i0 * w, n * w);
+        else {
+            const duckdb_string_t *cells = (const duckdb_string_t *)col + i0;
+            duckdb_string_t *out = (duckdb_string_t *)dst;
+            if (range_all_valid(validity, i0, n)) for (idx_t k = 0; k < n; ++k) put_cell(vec, out, k, &cells[k]);
+            else for (idx_t k = 0; k < n; ++k) if (bit_valid(validity, i0 + k)) put_cell(vec, out, k, &cells[k]);
+        }
+        copy_validity(vec, validity, i0, n);
+        return;
+    }
+    /* repeated or strided cells: runs of equal source index are filled from one load; a long string is copied into the
+     * vector once per run and its cell repeated (several cells may share one heap string) */
+    idx_t k = 0;
+    while (k < n) {
+        const uint64_t i = map_idx(m, k);
+        idx_t e = k + 1;
+        if (m->div > 1) { const uint64_t left = m->div - (m->i0 + k) % m->div; e = k + (idx_t)(left < n - k ? left : n - k); }
+        if (!bit_valid(validity, i)) {
+            if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
+            for (idx_t q = k; q < e; ++q) api.duckdb_validity_set_row_invalid(val, q);
+            k = e;
+            continue;
+        }
+        switch (type) {
+        case 0: memset((uint8_t *)dst + k, ((const uint8_t *)col)[i], e - k); break;
+        case 1: case 2: { const uint32_t v = ((const uint32_t *)col)[i]; uint32_t *d = (uint32_t *)dst; for (idx_t q = k; q < e; ++q) d[q] = v; break; }
+        case 3: {
+            duckdb_string_t *d = (duckdb_string_t *)dst;
+            put_cell(vec, d, k, &((const duckdb_string_t *)col)[i]);
+            for (idx_t q = k + 1; q < e; ++q) d[q] = d[k];
+            break;
+        }
+        default: { const uint64_t v = ((const uint64_t *)col)[i]; uint64_t *d = (uint64_t *)dst; for (idx_t q = k; q < e; ++q) d[q] = v; break; }
+        }
+        k = e;
     }
 }
 
 static void read_bcf_scan(duckdb_function_info info, duckdb_data_chunk output) {
-    bcf_bind_t *b = (bcf_bind_t *)api.duckdb_function_get_bind_data(info);
-    bcf_local_t *l = (bcf_local_t *)api.duckdb_function_get_local_init_data(info);
-    if (!l || l->done) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    bcf_global_t *l = (bcf_global_t *)api.duckdb_function_get_init_data(info);
+    if (!l) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    bcf_bind_t *b = l->bind;
     const uint64_t ns = (uint64_t)b->n_samples, per_rec = (b->tidy && ns) ? ns : 1;
-    while (!l->have_batch || l->cursor >= l->batch.n_records * per_rec) {
-        const int rc = dh_bcf_next_batch(b->bcf, &l->batch);
-        if (rc == 1) { l->have_batch = 1; l->cursor = 0; continue; }
-        l->have_batch = 0;
-        if ((rc == 0 || rc == DH_EDATA || rc == DH_EFORMAT) && b->n_regions > 0) {   /* end of this region's iterator: chain the next one */
-            const int started = bcf_next_region(b, l);
-            if (started == 1) continue;
-            if (started < 0) api.duckdb_function_set_error(info, dh_last_error());
-        }
-        l->done = 1;
-        if (rc < 0 && rc != DH_EDATA && rc != DH_EFORMAT) api.duckdb_function_set_error(info, dh_last_error());   /* a bad record / block ends the scan silently (bcf_reader.c:1311-1338) */
-        api.duckdb_data_chunk_set_size(output, 0);
-        return;
-    }
     const idx_t vs = api.duckdb_vector_size();
-    const uint64_t r0 = l->cursor, left = l->batch.n_records * per_rec - r0;
-    const idx_t n = left < vs ? (idx_t)left : vs;
+    bcf_batch_ref *br = NULL;
+    uint64_t r0 = 0;
+    idx_t n = 0;
+    for (;;) {
+        pthread_mutex_lock(&l->mu);
+        if (l->done) { pthread_mutex_unlock(&l->mu); api.duckdb_data_chunk_set_size(output, 0); return; }
+        if (!l->cur || l->cursor >= l->cur->b.n_records * per_rec) {
+            if (l->cur) {
+                l->cur->closed = 1;
+                if (l->cur->refs == 0) { dh_bcf_release_batch(b->bcf, l->cur->b.slot); free(l->cur); }
+                l->cur = NULL;
+            }
+            bcf_batch_ref *nb = (bcf_batch_ref *)calloc(1, sizeof *nb);
+            const int rc = dh_bcf_acquire_batch(b->bcf, &nb->b);
+            if (rc == 1) { l->cur = nb; l->cursor = 0; }
+            else {
+                free(nb);
+                if (rc == DH_EBUSY) { pthread_mutex_unlock(&l->mu); usleep(100); continue; }   /* every slot is being filled from: wait for a release */
+                if ((rc == 0 || rc == DH_EDATA) && b->n_regions > 0) {   /* end of this region's iterator: chain the next one */
+                    const int started = bcf_next_region(b, l);
+                    if (started == 1) { pthread_mutex_unlock(&l->mu); continue; }
+                    if (started < 0) api.duckdb_function_set_error(info, dh_last_error());
+                }
+                l->done = 1;
+                pthread_mutex_unlock(&l->mu);
+                if (rc < 0 && rc != DH_EDATA) api.duckdb_function_set_error(info, dh_last_error());   /* a bad record / block ends the scan silently (bcf_reader.c:1311-1338) */
+                api.duckdb_data_chunk_set_size(output, 0);
+                return;
+            }
+        }
+        br = l->cur;
+        r0 = l->cursor;
+        const uint64_t left = br->b.n_records * per_rec - r0;
+        n = left < vs ? (idx_t)left : vs;
+        l->cursor += n;
+        br->refs++;
+        pthread_mutex_unlock(&l->mu);
+        break;
+    }
     static const int CORE_TYPE[7] = {3, 4, 3, 3, 3, 5, 3};
-    const dh_bcf_batch *bt = &l->batch;
+    const dh_bcf_batch *bt = &br->b;
+    const cell_map site = {r0, per_rec, 1, 0};            /* record of row k: (r0 + k) / per_rec */
     for (idx_t i = 0; i < l->n_proj; ++i) {
         duckdb_vector vec = api.duckdb_data_chunk_get_vector(output, i);
         const idx_t c = l->col_ids[i];
-        for (idx_t r = 0; r < n; ++r) {
-            const uint64_t row = r0 + r, rec = row / per_rec, smp = row % per_rec;
-            if (c < 7) emit_cell(vec, r, CORE_TYPE[c], c == 4 || c == 6, bt->core[c], bt->core_validity[c], rec, bt->heap);
-            else if ((int)c < b->info_start + b->n_info) {
-                const int k = (int)c - b->info_start;
-                emit_cell(vec, r, b->info[k].type, b->info[k].is_list, bt->info[k], bt->info_validity[k], rec, bt->heap);
-            } else if ((int)c == b->sample_id_col) api.duckdb_vector_assign_string_element(vec, r, dh_bcf_sample_name(b->bcf, (int32_t)smp));
-            else {
-                const uint64_t k = c - (idx_t)b->fmt_start, f = k % (uint64_t)b->n_fmt, s_idx = b->tidy ? smp : k / (uint64_t)b->n_fmt;
-                if (b->default_gt) set_null(vec, r);
-                else emit_cell(vec, r, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], rec * ns + s_idx, bt->heap);
-            }
+        if (c < 7) fill_bcf_column(vec, n, CORE_TYPE[c], c == 4 || c == 6, bt->core[c], bt->core_validity[c], &site, bt->heap);
+        else if ((int)c < b->info_start + b->n_info) {
+            const int k = (int)c - b->info_start;
+            fill_bcf_column(vec, n, b->info[k].type, b->info[k].is_list, bt->info[k], bt->info_validity[k], &site, bt->heap);
+        } else if ((int)c == b->sample_id_col) {
+            duckdb_string_t *out = (duckdb_string_t *)api.duckdb_vector_get_data(vec);
+            for (idx_t k = 0; k < n; ++k) put_cell(vec, out, k, &b->sample_cells[(r0 + k) % ns]);
+        } else {
+            const uint64_t k = c - (idx_t)b->fmt_start, f = k % (uint64_t)b->n_fmt;
+            if (b->default_gt) fill_bcf_column(vec, n, 3, 0, NULL, NULL, &site, bt->heap);
+            else if (b->tidy) { const cell_map m = {r0, 1, 1, 0}; fill_bcf_column(vec, n, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], &m, bt->heap); }
+            else { const cell_map m = {r0, 1, ns, k / (uint64_t)b->n_fmt}; fill_bcf_column(vec, n, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], &m, bt->heap); }
         }
     }
-    l->cursor += n;
+    pthread_mutex_lock(&l->mu);
+    if (--br->refs == 0 && br->closed) { dh_bcf_release_batch(b->bcf, br->b.slot); free(br); }
+    pthread_mutex_unlock(&l->mu);
     api.duckdb_data_chunk_set_size(output, n);
 }
 
@@ -770,32 +1244,33 @@ static void bgunzip_bind(duckdb_bind_info info) {
         if (n > 3 && !strcmp(in + n - 3, ".gz")) snprintf(out_path, sizeof out_path, "%.*s", (int)(n - 3), in);
         else snprintf(out_path, sizeof out_path, "%s.out", in);
     }
-    uint8_t *comp = NULL, *plain = NULL;
+    /* one streaming pass, file to file (src/bgzip.c:154-200 is a bgzf_read / fwrite loop): neither file is held in memory, the
+     * inflated size is whatever the blocks hold; pinned memory = the three staging slots of dh_bgzf_inflate_fd */
     uint64_t csize = 0, usize = 0;
     dh_ctx *ctx = NULL;
+    int in_fd = -1, out_fd = -1;
     if (!overwrite && file_exists(out_path)) snprintf(err, sizeof err, "bgunzip: output '%s' already exists (use overwrite := TRUE to replace)", out_path);
-    else if (!(ctx = shared_ctx())) snprintf(err, sizeof err, "bgunzip: no usable CUDA device (%s)", dh_last_error());
-    else if (!(comp = slurp_pinned(in, &csize))) snprintf(err, sizeof err, "bgunzip: cannot open input %s", in);
     else {
-        dh_inflate_stats st;
-        int rc = dh_bgzf_inflate_host(ctx, comp, csize, NULL, 0, &usize, &st);      /* framing + verdicts, size of the output */
-        if (rc == DH_OK) {
-            plain = (uint8_t *)dh_host_alloc(usize ? usize : 1);
-            if (!plain) rc = DH_ENOMEM;
-            else rc = dh_bgzf_inflate_host(ctx, comp, csize, plain, usize, &usize, &st);
-        }
-        if (rc != DH_OK) snprintf(err, sizeof err, "bgunzip: read error");
+        int devs[MAX_SOURCES];
+        device_list(devs);
+        struct stat stt;
+        if ((in_fd = open(in, O_RDONLY)) < 0 || fstat(in_fd, &stt) != 0 || !S_ISREG(stt.st_mode)) snprintf(err, sizeof err, "bgunzip: cannot open input %s", in);
+        else if (!(ctx = dh_ctx_create(devs[0]))) snprintf(err, sizeof err, "bgunzip: no usable CUDA device (%s)", dh_last_error());
+        else if ((out_fd = open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0666)) < 0) snprintf(err, sizeof err, "bgunzip: cannot open output %s: %s", out_path, strerror(errno));
         else {
-            FILE *f = fopen(out_path, "wb");
-            if (!f) snprintf(err, sizeof err, "bgunzip: cannot open output %s: %s", out_path, strerror(errno));
-            else {
-                if (fwrite(plain, 1, usize, f) != usize) snprintf(err, sizeof err, "bgunzip: write error");
-                if (fclose(f) != 0 && !err[0]) snprintf(err, sizeof err, "bgunzip: close error");
-            }
+            dh_inflate_stats st;
+            const int rc = dh_bgzf_inflate_fd(ctx, in_fd, out_fd, &st);
+            if (rc == DH_EIO) snprintf(err, sizeof err, "bgunzip: write error");
+            else if (rc != DH_OK) snprintf(err, sizeof err, "bgunzip: read error");
+            csize = (uint64_t)stt.st_size;       /* bytes_in is the size of the input file (src/bgzip.c:208) */
+            usize = st.out_bytes;
+            if (close(out_fd) != 0 && !err[0]) snprintf(err, sizeof err, "bgunzip: close error");
+            out_fd = -1;
         }
     }
-    if (comp) dh_host_free(comp);
-    if (plain) dh_host_free(plain);
+    if (in_fd >= 0) close(in_fd);
+    if (out_fd >= 0) close(out_fd);
+    if (ctx) dh_ctx_destroy(ctx);
     if (err[0]) api.duckdb_bind_set_error(info, err);
     else {
         if (!keep) unlink(in);

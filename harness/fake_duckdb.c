@@ -45,8 +45,12 @@ typedef struct Vec {
     struct Vec *child;            /* LIST */
     idx_t list_size;
     struct Vec **members;         /* STRUCT */
-    char **heap;                  /* strings copied by assign_string_element */
-    size_t n_heap, cap_heap;
+    /* strings copied by assign_string_element live in an arena, like DuckDB's StringHeap (ArenaAllocator): a bump
+     * pointer over a list of blocks, rewound when the chunk is reset */
+    char **heap;                  /* arena blocks */
+    size_t *heap_cap;
+    size_t n_heap, cap_heap;      /* blocks allocated / slots in the block list */
+    size_t cur_blk, cur_off;      /* bump position */
 } Vec;
 
 typedef struct { Vec **vecs; idx_t ncols, size; } Chunk;
@@ -176,8 +180,7 @@ static void vec_reserve(Vec *v, idx_t cap) {
 }
 static void vec_reset(Vec *v) {
     free(v->validity); v->validity = NULL;
-    for (size_t i = 0; i < v->n_heap; ++i) free(v->heap[i]);
-    v->n_heap = 0;
+    v->cur_blk = 0; v->cur_off = 0;      /* rewind the string arena; the blocks are kept for the next chunk */
     v->list_size = 0;
     if (v->child) vec_reset(v->child);
     if (v->members) for (idx_t i = 0; i < v->type->n_members; ++i) vec_reset(v->members[i]);
@@ -185,7 +188,8 @@ static void vec_reset(Vec *v) {
 static void vec_free(Vec *v) {
     if (!v) return;
     vec_reset(v);
-    free(v->heap); free(v->data);
+    for (size_t i = 0; i < v->n_heap; ++i) free(v->heap[i]);
+    free(v->heap); free(v->heap_cap); free(v->data);
     vec_free(v->child);
     if (v->members) { for (idx_t i = 0; i < v->type->n_members; ++i) vec_free(v->members[i]); free(v->members); }
     free(v);
@@ -203,16 +207,33 @@ static void api_vector_ensure_validity_writable(duckdb_vector vv) {
 static duckdb_logical_type api_vector_get_column_type(duckdb_vector v) { return (duckdb_logical_type)ltype_copy(((Vec *)v)->type); }
 static void api_validity_set_row_invalid(uint64_t *validity, idx_t row) { if (validity) validity[row / 64] &= ~(1ull << (row % 64)); }
 static bool api_validity_row_is_valid(uint64_t *validity, idx_t row) { return !validity || ((validity[row / 64] >> (row % 64)) & 1); }
+#define ARENA_BLOCK (256u << 10)
+static char *arena_alloc(Vec *v, size_t len) {
+    while (v->cur_blk < v->n_heap && v->cur_off + len > v->heap_cap[v->cur_blk]) { ++v->cur_blk; v->cur_off = 0; }
+    if (v->cur_blk == v->n_heap) {
+        if (v->n_heap == v->cap_heap) {
+            v->cap_heap = v->cap_heap ? v->cap_heap * 2 : 8;
+            v->heap = realloc(v->heap, v->cap_heap * sizeof(char *));
+            v->heap_cap = realloc(v->heap_cap, v->cap_heap * sizeof(size_t));
+        }
+        const size_t cap = len > ARENA_BLOCK ? len : ARENA_BLOCK;
+        v->heap[v->n_heap] = malloc(cap);
+        if (!v->heap[v->n_heap]) { fprintf(stderr, "out of memory\n"); exit(2); }
+        v->heap_cap[v->n_heap++] = cap;
+        v->cur_off = 0;
+    }
+    char *p = v->heap[v->cur_blk] + v->cur_off;
+    v->cur_off += len;
+    return p;
+}
 static void api_assign_string_len(duckdb_vector vv, idx_t index, const char *str, idx_t len) {
     Vec *v = (Vec *)vv;
     duckdb_string_t *cell = (duckdb_string_t *)v->data + index;
     memset(cell, 0, sizeof *cell);
     cell->value.inlined.length = (uint32_t)len;
     if (len <= 12) { memcpy(cell->value.inlined.inlined, str, len); return; }
-    char *copy = xmalloc(len);
+    char *copy = arena_alloc(v, len);
     memcpy(copy, str, len);
-    if (v->n_heap == v->cap_heap) { v->cap_heap = v->cap_heap ? v->cap_heap * 2 : 256; v->heap = realloc(v->heap, v->cap_heap * sizeof(char *)); }
-    v->heap[v->n_heap++] = copy;
     memcpy(cell->value.pointer.prefix, str, 4);
     cell->value.pointer.ptr = copy;
 }
@@ -453,7 +474,7 @@ typedef struct {
     idx_t *col_ids; idx_t n_col_ids;
     int mode;
     pthread_mutex_t *out_lock;
-    uint64_t rows; uint64_t *hash; char *error;
+    uint64_t rows; uint64_t *hash, *mhash; char *error;
 } Worker;
 
 static double now_s(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + ts.tv_nsec * 1e-9; }
@@ -488,10 +509,15 @@ static void *worker_main(void *arg) {
                 size_t start = line.n;
                 format_cell(&line, ch.vecs[c], r);
                 if (w->mode == MODE_HASH) {
-                    uint64_t h = w->hash[c];
-                    for (size_t k = start; k < line.n; ++k) { h ^= (unsigned char)line.p[k]; h *= 1099511628211ull; }
+                    uint64_t h = w->hash[c], m = 1469598103934665603ull;
+                    for (size_t k = start; k < line.n; ++k) {
+                        h ^= (unsigned char)line.p[k]; h *= 1099511628211ull;
+                        m ^= (unsigned char)line.p[k]; m *= 1099511628211ull;
+                    }
                     h ^= 0xff; h *= 1099511628211ull;       /* cell separator */
                     w->hash[c] = h;
+                    m ^= m >> 30; m *= 0xbf58476d1ce4e5b9ull; m ^= m >> 27; m *= 0x94d049bb133111ebull; m ^= m >> 31;
+                    w->mhash[c] += m;                        /* multiset hash: independent of row order and of the thread that saw the row */
                 } else if (c + 1 < ch.ncols) buf_puts(&line, "\t");
             }
             if (w->mode == MODE_DUMP) { fwrite(line.p, 1, line.n, stdout); fputc('\n', stdout); }
@@ -563,6 +589,7 @@ int main(int argc, char **argv) {
     }
     double t0 = now_s();
     tf->bind((duckdb_bind_info)&bind);
+    const double t_bind = now_s() - t0;
     if (bind.error) { printf("BIND ERROR\t%s\n", bind.error); return 1; }
     idx_t *col_ids = xmalloc(sizeof(idx_t) * (bind.n_cols + 1));
     idx_t n_col_ids = 0;
@@ -590,6 +617,7 @@ int main(int argc, char **argv) {
         ws[i].tf = tf; ws[i].bind = &bind; ws[i].global = &global; ws[i].col_ids = col_ids; ws[i].n_col_ids = n_col_ids;
         ws[i].mode = mode; ws[i].out_lock = &lock;
         ws[i].hash = xmalloc(sizeof(uint64_t) * (n_col_ids + 1));
+        ws[i].mhash = xmalloc(sizeof(uint64_t) * (n_col_ids + 1));
         for (idx_t c = 0; c < n_col_ids; ++c) ws[i].hash[c] = 1469598103934665603ull;
         if (threads == 1) worker_main(&ws[i]); else pthread_create(&th[i], NULL, worker_main, &ws[i]);
     }
@@ -603,14 +631,18 @@ int main(int argc, char **argv) {
     double dt = now_s() - t0;
     if (mode == MODE_HASH) {
         printf("rows\t%" PRIu64 "\n", rows);
+        /* per column: the chained hash (row order matters; printed for one thread only, where the order is defined) and the
+         * multiset hash (sum of per-cell hashes: the same for any row order and any split of the rows over threads) */
         for (idx_t c = 0; c < n_col_ids; ++c) {
-            uint64_t hsum = 0;
-            for (int i = 0; i < threads; ++i) hsum += ws[i].hash[c];   /* order-insensitive across threads; exact with 1 thread */
-            printf("%s\t%016" PRIx64 "\n", bind.col_names[col_ids[c]], hsum);
+            uint64_t msum = 0;
+            for (int i = 0; i < threads; ++i) msum += ws[i].mhash[c];
+            if (threads == 1) printf("%s\t%016" PRIx64 "\t%016" PRIx64 "\n", bind.col_names[col_ids[c]], ws[0].hash[c], msum);
+            else printf("%s\t-\t%016" PRIx64 "\n", bind.col_names[col_ids[c]], msum);
         }
     }
     if (mode == MODE_TIME)
-        printf("{\"function\":\"%s\",\"threads\":%d,\"max_threads\":%" PRIu64 ",\"rows\":%" PRIu64 ",\"seconds\":%.6f}\n", fname, threads, global.max_threads, rows, dt);
+        printf("{\"function\":\"%s\",\"threads\":%d,\"max_threads\":%" PRIu64 ",\"rows\":%" PRIu64 ",\"seconds\":%.6f,\"bind_seconds\":%.6f}\n", fname, threads,
+               global.max_threads, rows, dt, t_bind);
     if (global.init_free && global.init_data) global.init_free(global.init_data);
     if (bind.bind_free && bind.bind_data) bind.bind_free(bind.bind_data);
     fflush(stdout);

@@ -6,7 +6,10 @@
  * third_party/htslib/).  INTEGRATION.md shows how the reference's src/bam_reader.c and src/bgzip.c
  * would bind these.
  *
- * Threading: a dh_ctx is bound to one CUDA device and may be used by one host thread at a time.
+ * Threading: a dh_ctx is bound to one CUDA device.  Scan handles (dh_bam, dh_bcf) lock internally, so any number of
+ * host threads may call dh_*_acquire_batch / dh_*_release_batch / dh_*_next_batch on ONE handle (the workers of one
+ * query); handles that may be driven at the same time (two queries, one handle per GPU) need a dh_ctx each, because
+ * streams, ticket counters and staging slots belong to the context.  Several contexts may share a device.
  * Errors: functions return 0 (DH_OK) or a negative DH_E* code; dh_last_error() gives the message of
  * the calling thread's last failure.  There is NO CPU fallback: without a usable CUDA device
  * dh_ctx_create fails and nothing else can be called.
@@ -27,6 +30,7 @@ extern "C" {
 #define DH_ENOMEM (-5)
 #define DH_EIO (-6)
 #define DH_ENOREGION (-7) /* no requested region names a reference sequence (sam_itr_regarray returned NULL) */
+#define DH_EBUSY (-8)     /* every batch slot of the scan is held by the caller: release one and call again */
 
 typedef struct dh_ctx dh_ctx;
 
@@ -81,6 +85,13 @@ typedef struct {
 } dh_inflate_stats;
 int dh_bgzf_inflate_host(dh_ctx *ctx, const uint8_t *comp, uint64_t comp_size, uint8_t *out, uint64_t out_cap,
                          uint64_t *out_size, dh_inflate_stats *stats);
+
+/* Streaming form, file descriptor to file descriptor — what bgunzip does (src/bgzip.c:154-200: a bgzf_read / write loop
+ * over 64 KB buffers; here segments of ~192 MB compressed travel through three pinned staging slots: pread -> H2D ->
+ * inflate -> D2H -> pwrite, the reads and writes of one segment overlapping the GPU work of the others).  Neither the
+ * input nor the output is ever held whole: pinned memory = the slots.  in_fd must be seekable (pread).  Returns DH_OK,
+ * DH_EFORMAT / DH_EDATA (read errors; stats->bad_block), DH_EIO (errno of the failing read / write in the message). */
+int dh_bgzf_inflate_fd(dh_ctx *ctx, int in_fd, int out_fd, dh_inflate_stats *stats);
 
 /* Device-resident variant used for kernel-level measurement and by the BAM scan: upload once, inflate
  * any number of times.  dh_bgzf_dev_load frames `comp` on the host, uploads it and the block table;
@@ -153,7 +164,26 @@ int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, ui
  * host out. */
 #define DH_BAM_DEVICE_INPUT 1u
 #define DH_BAM_DEVICE_OUTPUT 2u
+/* DH_BAM_COMPACT_OUTPUT: batches leave the GPU in the COMPACT WIRE LAYOUT instead of DuckDB vector layout (fewer bytes
+ * cross PCIe: 16-byte duckdb_string_t cells become 4-byte lengths, dictionary columns become codes, BAM's own 32-bit
+ * fields stay 32-bit).  The consumer expands it while it fills its vectors (duckhts_b200/host/duckhts_ext.c does).
+ *   data[c] per row:  FLAG uint16 | MAPQ uint8 | POS, PNEXT int32 = BAM pos / next_pos (0-based: add 1) | TLEN int32
+ *                     RNAME, RNEXT int32 = tid (-1 = "*"; names: dh_bam_ref_name) | SAMPLE_ID int32 = @RG entry
+ *                     (-1 = NULL; dh_bam_rg_sample) | 'i' tags int64, 'f' tags double | 'A' tags uint8 (0 = "") |
+ *                     'B' tags duckdb_list_entry as in the DuckDB layout | every other VARCHAR column uint32 = length.
+ *   String bytes: rec_off[row] = offset in `heap` of the row's slots, which follow one another in the order QNAME,
+ *   CIGAR, SEQ, QUAL, then the 'Z' and 'B' tag columns in request order, then READ_GROUP_ID; projected columns only;
+ *   a slot is the string padded to a multiple of 4 bytes ('B': 4 + 8 * length bytes, children 8-byte aligned; NULL
+ *   cells have no slot).  Two length words carry a flag in bit 31 for values htslib cuts at an embedded NUL (strlen
+ *   semantics of duckdb_vector_assign_string_element): QNAME = l_read_name (NUL included; the string is
+ *   l_read_name - 1 bytes, or, flagged, strnlen(slot, l_read_name)), QUAL = l_seq (flagged: strnlen(slot, l_seq)).
+ * validity[c] as in the DuckDB layout. */
+#define DH_BAM_COMPACT_OUTPUT 4u
 int dh_bam_set_mode(dh_bam *b, uint32_t flags);
+/* @RG dictionary of the header, in header order (entries with an ID): SAMPLE_ID codes of the compact layout index it. */
+int32_t dh_bam_n_rg(const dh_bam *b);
+const char *dh_bam_rg_id(const dh_bam *b, int32_t i, uint32_t *len);
+const char *dh_bam_rg_sample(const dh_bam *b, int32_t i);   /* SM value, NULL if the line has none (-> NULL cell) */
 
 /* Start a scan over the records that START at virtual offsets in [voff_beg, voff_end) (bgzf virtual offset =
  * coffset << 16 | uoffset, htslib/bgzf.h:261).  voff_beg = 0 means "first record"; voff_end = UINT64_MAX means
@@ -185,10 +215,33 @@ typedef struct {
     const void *aux_keys;
     const void *aux_values;
     uint64_t n_aux;
+    int32_t slot;               /* pipeline slot holding this batch: the argument of dh_bam_release_batch */
+    uint32_t layout;            /* 0 = DuckDB vector layout, DH_BAM_COMPACT_OUTPUT = compact wire layout */
+    const uint32_t *rec_off;    /* compact layout: heap offset of every row's string slots; else NULL */
 } dh_bam_batch;
 /* Returns 1 and fills *out (buffers stay valid until the next call on this handle), 0 at end of scan, < 0 on
  * error. */
 int dh_bam_next_batch(dh_bam *b, dh_bam_batch *out);
+/* The same with explicit lifetime, for consumers that work on several batches at once (the worker threads of one
+ * DuckDB query): an acquired batch stays valid until dh_bam_release_batch(b, out->slot).  The pipeline has
+ * dh_bam_set_slots() slots (default 6, at least 3, at most 32; set before the scan begins); slots that are neither
+ * held nor in flight are refilled ahead of the consumer.  Returns like dh_bam_next_batch; if every slot is held it
+ * returns DH_EBUSY rather than wait for a release that only the caller can make. */
+int dh_bam_set_slots(dh_bam *b, int n_slots);
+/* Starts the pipeline without waiting for anything: the host-to-device copies and the inflate of the first segments
+ * are enqueued and the call returns.  A consumer that drives several handles (one per GPU) calls this on each right
+ * after dh_bam_scan_*, so that every GPU is at work before the first batch is asked for. */
+int dh_bam_prefetch(dh_bam *b);
+int dh_bam_acquire_batch(dh_bam *b, dh_bam_batch *out);
+int dh_bam_release_batch(dh_bam *b, int32_t slot);
+
+/* Per-column 64-bit checksums of one batch: sums[c] += sum over rows of a hash of the cell's VALUE (strings by their
+ * bytes, NULL as a constant), so the result is independent of the layout (DuckDB / compact), of where the batch lives
+ * (host: computed by host threads; device output: by a kernel on the batch arena) and of how a scan is cut into
+ * batches, ranges or GPUs: checksums of disjoint row sets add up modulo 2^64.  Used for parity at sizes no cell-by-cell
+ * comparison reaches (bench.py: tiled input = tiles x the unit's checksums).  sums has DH_BAM_MAX_COLS entries; columns
+ * not projected are left alone.  The batch must be one this handle returned and still holds. */
+int dh_bam_batch_checksum(dh_bam *b, const dh_bam_batch *batch, uint64_t *sums);
 
 typedef struct {
     uint64_t rows;
@@ -234,6 +287,19 @@ int dh_bam_scan_contigs(dh_bam *b, const dh_index *idx, int32_t tid_lo, int32_t 
 /* n_parts + 1 contig bounds cutting [0, n_ref) into contiguous groups of about equal compressed size (from the
  * index's chunk offsets). */
 int dh_bam_split_contigs(const dh_bam *b, const dh_index *idx, int n_parts, int32_t *tid_bounds);
+/* The same from the index alone (host code, no GPU): contigs [0, dh_index_n_ref). */
+int dh_index_split_contigs(const dh_index *idx, int n_parts, int32_t *tid_bounds);
+/* A second handle on the same image for another context (= another GPU): block table, header and dictionaries are
+ * copied from `src` instead of being walked, inflated and parsed again.  This is how one query is spread over the
+ * GPUs of a box: one handle per GPU, each scanning the range / contig group dh_bam_split(_contigs) gives it. */
+dh_bam *dh_bam_clone(const dh_bam *src, dh_ctx *ctx);
+
+/* ---- N3: predicate pushdown ------------------------------------------------------------------------------------------
+ * Record filter evaluated in the boundary kernel next to the region test, so rejected records cost no row, no heap byte
+ * and no PCIe byte.  A record passes iff (FLAG & flag_require) == flag_require, (FLAG & flag_exclude) == 0 and
+ * MAPQ >= min_mapq: the conjunctions of the reference's flag predicates (is_paired, is_unmapped, is_reverse, ...,
+ * src/kmer_udf.c:1082-1183) and a mapping-quality floor.  All zero = no filter.  Set before the scan begins. */
+int dh_bam_set_filter(dh_bam *b, uint32_t flag_require, uint32_t flag_exclude, uint32_t min_mapq);
 
 /* ---- B1-B10: read_bcf scan --------------------------------------------------------------------------------------
  * Replaces, for one BCF image in host memory, what bcf_read_bind / bcf_read_local_init / bcf_read_function get from
@@ -300,9 +366,15 @@ typedef struct {
     const uint8_t *heap;
     uint64_t heap_bytes;
     uint64_t bytes;        /* bytes copied device -> host for this batch */
+    int32_t slot;          /* pipeline slot: the argument of dh_bcf_release_batch */
+    int32_t pad2;
 } dh_bcf_batch;
 /* Returns 1 and fills *out (buffers stay valid until the next call on this handle), 0 at end of scan, < 0 on error. */
 int dh_bcf_next_batch(dh_bcf *b, dh_bcf_batch *out);
+/* Explicit lifetime, as for dh_bam: valid until dh_bcf_release_batch(b, out->slot). */
+int dh_bcf_set_slots(dh_bcf *b, int n_slots);
+int dh_bcf_acquire_batch(dh_bcf *b, dh_bcf_batch *out);
+int dh_bcf_release_batch(dh_bcf *b, int32_t slot);
 int dh_bcf_scan_stats_get(const dh_bcf *b, dh_bam_scan_stats *out);
 
 /* CUDA-event timer on the context's stream (the stream every kernel of this library is launched on). */

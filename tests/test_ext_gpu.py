@@ -20,9 +20,17 @@ pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not (os.path.exists(HOST) and 
 B_COLS = (13 + 7, 13 + 19, 13 + 29)
 
 
-def run(ext, func, path, *args):
-    p = subprocess.run([HOST, ext, func, path, *args], stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+def run(ext, func, path, *args, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    p = subprocess.run([HOST, ext, func, path, *args], stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=900, env=e)
     return p.returncode, p.stdout.decode("utf-8", "replace"), p.stderr.decode("utf-8", "replace")
+
+
+def multiset(out):
+    """rows + the order-insensitive per-column hashes of a --hash run (third field of every column line)."""
+    lines = out.splitlines()
+    return [lines[0]] + [ln.split("\t")[0] + " " + ln.split("\t")[2] for ln in lines[1:]]
 
 
 def both(func, path, *args):
@@ -217,3 +225,174 @@ def test_read_bcf_bind_errors(tmp_path):
         (rc_r, out_r, _), (rc_o, out_o, _) = both(*args)
         assert rc_r == 1 and rc_o == 1
         assert out_o == out_r
+
+
+# ---- round 2: worker threads, layouts, several pipelines per query, BASELINE-scale parity -------------------------------------------
+ALL69 = ",".join(str(c) for c in range(13 + 56))
+BENCH_COLS = "0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14"      # 13 core columns + NM, MD, AS (bench.py's projection)
+
+
+@pytest.mark.parametrize("layout", ["compact", "duckdb"])
+def test_both_wire_layouts_fill_the_same_cells(layout):
+    env = {"DUCKHTS_LAYOUT": layout, "DUCKHTS_BATCH_ROWS": "5000"}
+    for path, args in ((os.path.join(GOLD, "range.bam"), ()), (os.path.join(GOLD, "auxf_values.bam"), ("standard_tags=true",)),
+                       (util.synth_path("bam", n_records=20000, seed=77, paired=True, extra=("--btags",)), ("standard_tags=true", "--cols", ALL69)),
+                       (util.synth_path("bam", n_records=20000, seed=77, paired=True, extra=("--btags",)), ("--cols", "10,0,0,3"))):
+        rc_r, out_r, _ = run(REF_EXT, "read_bam", path, *args)
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, *args, env=env)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r, (path, args)
+
+
+@pytest.mark.parametrize("threads", [2, 4, 16])
+def test_worker_threads_return_the_reference_rows(threads):
+    # several scan threads claim chunks of shared batches; row order across threads is not defined: multiset hashes
+    path = util.synth_path("bam", n_records=60000, seed=31, paired=True)
+    rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "standard_tags=true", "--cols", ALL69, "--hash")
+    for env in ({}, {"DUCKHTS_BATCH_ROWS": "3000", "DUCKHTS_SLOTS": "4"}, {"DUCKHTS_LAYOUT": "duckdb", "DUCKHTS_BATCH_ROWS": "7000"}):
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "standard_tags=true", "--cols", ALL69, "--hash", "--threads", str(threads), env=env)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert multiset(out_o) == multiset(out_r), env
+    # the reference's own contig-parallel mode (index next to the file) against ours, both with several threads
+    path = util.synth_path("bam", n_records=30000, seed=31, paired=True, extra=("--unplaced", "25"), index=True)
+    rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "--hash", "--threads", str(threads))
+    rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "--hash", "--threads", str(threads))
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert multiset(out_o) == multiset(out_r)
+
+
+def test_one_query_over_several_pipelines_keeps_file_order():
+    """One source per listed device (here: the same GPU three times), ranges from dh_bam_split / contig groups from
+    dh_bam_split_contigs; one scan thread walks the sources in order = the reference's row order, cell for cell."""
+    env = {"DUCKHTS_DEVICES": "0,0,0", "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "4096"}
+    seq = util.synth_path("bam", n_records=60000, seed=31, paired=True)
+    idx = util.synth_path("bam", n_records=30000, seed=31, paired=True, extra=("--unplaced", "25"), index=True)
+    for path in (seq, idx, os.path.join(GOLD, "range.bam")):
+        rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "standard_tags=true", "--cols", BENCH_COLS)
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "standard_tags=true", "--cols", BENCH_COLS, env=env)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r, path
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "standard_tags=true", "--cols", BENCH_COLS, "--hash", "--threads", "6", env=env)
+        rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "standard_tags=true", "--cols", BENCH_COLS, "--hash")
+        assert rc_o == 0 and multiset(out_o) == multiset(out_r), err_o
+    # a region query stays on one pipeline
+    (rc_r, out_r, _) = run(REF_EXT, "read_bam", idx, "region=chr3:10,000,000-20,000,000")
+    (rc_o, out_o, err_o) = run(OUR_EXT, "read_bam", idx, "region=chr3:10,000,000-20,000,000", env=env)
+    assert rc_r == 0 and rc_o == 0 and out_o == out_r, err_o
+
+
+def test_invalid_record_in_an_early_range_ends_the_whole_scan(tmp_path):
+    """Q8: the reference stops at the first invalid record; with the file cut into ranges, rows of later ranges must not appear."""
+    from tests.util import bam_header, bam_record
+    good = [bam_record(b"g%d" % i, 0, 0, i, 1, [(4, "M")], seq="ACGT", qual=[1] * 4) for i in range(4000)]
+    bad = bam_record(b"bad", 0, 0, 5, 1, [(5, "M")], seq="ACGT", qual=[1] * 4)            # CIGAR / l_seq mismatch: bam_read1 -> -4
+    # blocks hold whole records, like htslib writes them (the cut points of dh_bam_split must be record boundaries)
+    recs = good[:700] + [bad] + good[700:]
+    blocks = [util.bgzf_block(bam_header([(b"c1", 100000)]))] + [util.bgzf_block(b"".join(recs[i:i + 50])) for i in range(0, len(recs), 50)]
+    path = str(tmp_path / "bad.bam")
+    open(path, "wb").write(b"".join(blocks) + util.BGZF_EOF)
+    env = {"DUCKHTS_DEVICES": "0,0,0,0", "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "256"}
+    rc_r, out_r, _ = run(REF_EXT, "read_bam", path)
+    rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, env=env)
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r and len(out_r.splitlines()) == 701
+
+
+def test_truncated_bam_like_the_reference(tmp_path):
+    src = util.synth_path("bam", n_records=20000, seed=11)
+    data = open(src, "rb").read()
+    for cut in (len(data) // 2, len(data) - 40):
+        path = str(tmp_path / f"cut{cut}.bam")
+        open(path, "wb").write(data[:cut])
+        rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "--hash")
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "--hash")
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r and int(out_r.splitlines()[0].split("\t")[1]) > 1000
+
+
+def test_predicate_pushdown_parameters():
+    path = util.synth_path("bam", n_records=60000, seed=31, paired=True)
+    rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "--cols", "0,1,3,4")
+    rows = [ln.split("\t") for ln in out_r.splitlines()[1:]]
+    keep = [r for r in rows if (int(r[1]) & 0x4) == 0 and (int(r[1]) & 0x40) == 0x40 and int(r[3]) >= 30]
+    rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "flag_exclude=4", "flag_require=64", "min_mapq=30", "--cols", "0,1,3,4")
+    assert rc_o == 0, err_o
+    assert [ln.split("\t") for ln in out_o.splitlines()[1:]] == keep and 0 < len(keep) < len(rows)
+
+
+def _unit(n, paired):
+    import bench
+    return bench.gen_unit("bam", n, 0x9E3779B97F4A7C15, paired, os.cpu_count() or 1)
+
+
+def test_config1_one_million_single_end_records_cell_for_cell():
+    """BASELINE configs[0]: full-column scan of a 1 M-record single-end BAM; chained per-column hashes = every cell, in order."""
+    path = _unit(1000000, False)
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "--hash")
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r and out_r.splitlines()[0] == "rows\t1000000"
+
+
+def test_bench_unit_all_columns_against_the_reference_extension():
+    """The 4 M-record unit bench.py tiles to 100 M records, all 69 columns (standard_tags), through both extensions; then
+    with 8 scan threads on both sides (the reference in its sequential mode has one)."""
+    path = _unit(4000000, True)
+    (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path, "standard_tags=true", "--cols", ALL69, "--hash")
+    assert rc_r == 0 and rc_o == 0, err_o
+    assert out_o == out_r and int(out_r.splitlines()[0].split("\t")[1]) > 3900000
+    rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "standard_tags=true", "--cols", ALL69, "--hash", "--threads", "8")
+    assert rc_o == 0 and multiset(out_o) == multiset(out_r), err_o
+
+
+@pytest.mark.parametrize("threads", [1, 4])
+def test_read_bcf_worker_threads_and_wide_mode(threads):
+    path = os.path.join(util.CACHE, "ext_bcf_500x2504.bcf")
+    if not os.path.exists(path):
+        os.makedirs(util.CACHE, exist_ok=True)
+        subprocess.check_call([GEN_BCF, path + ".tmp", "500", "2504", "0x71"])
+        os.replace(path + ".tmp", path)
+    for args in (("tidy_format=true",), ("tidy_format=true", "--cols", "0,1,4,6,8,13,14,15,17"), ("--cols", "0,1,2,3,4,5,6,7,8,9,10,11,12,13,14,15,16,17,18,19,20,5000,5001,9000")):
+        rc_r, out_r, _ = run(REF_EXT, "read_bcf", path, *args, "--hash")
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bcf", path, *args, "--hash", "--threads", str(threads))
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert multiset(out_o) == multiset(out_r), args
+        if threads == 1:
+            assert out_o == out_r, args
+    edge = os.path.join(GOLD, "edge_small.bcf")
+    for args in ((), ("tidy_format=true",)):
+        rc_r, out_r, _ = run(REF_EXT, "read_bcf", edge, *args, "--hash")
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bcf", edge, *args, "--hash", "--threads", str(threads))
+        assert rc_r == 0 and rc_o == 0 and multiset(out_o) == multiset(out_r), err_o
+
+
+def test_bgunzip_streams_in_segments(tmp_path):
+    # several staging segments (DH_FD_SEG_MB shrinks them), output compared with the reference's byte for byte
+    src = util.synth_path("bam", n_records=60000, seed=31, paired=True)
+    outs = []
+    for tag, ext, env in (("ref", REF_EXT, {}), ("our", OUR_EXT, {"DH_FD_SEG_MB": "1"})):
+        out = str(tmp_path / f"{tag}.bin")
+        rc, text, err = run(ext, "bgunzip", src, f"output_path={out}", env=env)
+        assert rc == 0, err
+        outs.append((open(out, "rb").read(), text.splitlines()[1].split("\t")[2:]))
+    assert outs[0] == outs[1] and len(outs[0][0]) > 10_000_000
+    # a corrupt block in a later segment: read error like the reference's, same message
+    data = bytearray(open(src, "rb").read())
+    data[len(data) // 2] ^= 0x55
+    bad = str(tmp_path / "bad.bam")
+    open(bad, "wb").write(bytes(data))
+    msgs = []
+    for tag, ext, env in (("ref", REF_EXT, {}), ("our", OUR_EXT, {"DH_FD_SEG_MB": "1"})):
+        rc, text, _ = run(ext, "bgunzip", bad, f"output_path={tmp_path / (tag + '2.bin')}", env=env)
+        msgs.append((rc, text))
+    assert msgs[0] == msgs[1] and msgs[0][0] == 1
+
+
+def test_files_whose_blocks_do_not_start_records_are_not_cut(tmp_path):
+    """Foreign writers cut BGZF blocks anywhere (htslib/test/bgzf_boundaries): dh_bam_split finds no verifiable record boundary
+    and the query stays on one pipeline; blocks behind a read longer than a block are skipped as cut points."""
+    env = {"DUCKHTS_DEVICES": "0,0,0", "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "4096"}
+    for path in (util.synth_path("bgzf", n_records=30000, seed=13, paired=True), os.path.join(GOLD, "ce_large_seq.bam"), os.path.join(GOLD, "bgzf_boundaries2.bam")):
+        rc_r, out_r, _ = run(REF_EXT, "read_bam", path, "--hash")
+        rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "--hash", env=env)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r, path

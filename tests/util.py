@@ -279,3 +279,101 @@ def dump_lines(res, tags, from_oracle):
 
 def golden_names():
     return sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith(".bam"))
+
+
+# ---- per-column checksums (dh_bam_batch_checksum, duckhts_b200/csrc/dh_checksum.cu), restated with numpy over the oracle's columns ----
+CK_NULL = np.uint64(0x9e3779b97f4a7c15)
+CK_K = np.uint64(0x100000001b3)
+
+
+def ck_mix(x):
+    x = np.asarray(x, dtype=np.uint64).copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(30); x *= np.uint64(0xbf58476d1ce4e5b9)
+        x ^= x >> np.uint64(27); x *= np.uint64(0x94d049bb133111eb)
+        x ^= x >> np.uint64(31)
+    return x
+
+
+def _ck_segments(values, off):
+    """Per row r: mix(H ^ n * CK_NULL), H = Horner polynomial of values[off[r]:off[r+1]] (+1 each) in CK_K, n = its length."""
+    off = np.asarray(off, dtype=np.int64)
+    n = len(off) - 1
+    lens = off[1:] - off[:-1]
+    total = int(off[-1] - off[0])
+    with np.errstate(over="ignore"):
+        if total:
+            maxlen = int(lens.max())
+            kpow = np.ones(maxlen + 1, dtype=np.uint64)
+            for i in range(1, maxlen + 1):
+                kpow[i] = kpow[i - 1] * CK_K
+            row = np.repeat(np.arange(n), lens)
+            pos = np.arange(total) - np.repeat(off[:-1] - off[0], lens)
+            terms = (np.asarray(values[off[0]:off[-1]], dtype=np.uint64) + np.uint64(1)) * kpow[lens[row] - 1 - pos]
+            cs = np.concatenate([[np.uint64(0)], np.cumsum(terms, dtype=np.uint64)])
+            h = cs[off[1:] - off[0]] - cs[off[:-1] - off[0]]
+        else:
+            h = np.zeros(n, dtype=np.uint64)
+        return ck_mix(h ^ (lens.astype(np.uint64) * CK_NULL))
+
+
+def ck_strcol(col, rows=None):
+    """Checksum of an oracle string column {off, heap, valid} (NULL rows count CK_NULL)."""
+    cell = _ck_segments(col["heap"], col["off"])
+    cell = np.where(col["valid"], cell, CK_NULL)
+    if rows is not None:
+        cell = cell[rows]
+    with np.errstate(over="ignore"):
+        return int(cell.sum(dtype=np.uint64))
+
+
+def oracle_checksums(exp, tags, rows=None):
+    """Per-column checksums (13 core columns, then the tag columns) of an oracle bam_decode result; rows = boolean mask / index."""
+    def tot(cell):
+        cell = np.asarray(cell, dtype=np.uint64)
+        if rows is not None:
+            cell = cell[rows]
+        with np.errstate(over="ignore"):
+            return int(cell.sum(dtype=np.uint64))
+    out = []
+    for name in ("qname", "flag", "rname", "pos", "mapq", "cigar", "rnext", "pnext", "tlen", "seq", "qual", "rg", "sample"):
+        if name in FIX_COLS:
+            out.append(tot(ck_mix(exp[name].astype(np.int64).view(np.uint64))))
+        else:
+            out.append(ck_strcol(exp[name], rows))
+    for k, (tg, ty) in enumerate(tags):
+        t = exp["tags"][k]
+        if ty == "i":
+            out.append(tot(np.where(t["valid"], ck_mix(t["i"].astype(np.int64).view(np.uint64)), CK_NULL)))
+        elif ty == "f":
+            out.append(tot(np.where(t["valid"], ck_mix(t["f"].view(np.uint64)), CK_NULL)))
+        elif ty[0] == "B":
+            lens = np.array([0 if x is None else len(x) for x in t["b"]], dtype=np.int64)
+            vals = np.concatenate([np.zeros(0, np.int64)] + [x for x in t["b"] if x is not None]).view(np.uint64)
+            cell = _ck_segments_words(vals, np.concatenate([[0], np.cumsum(lens)]))
+            out.append(tot(np.where(t["valid"], cell, CK_NULL)))
+        else:
+            out.append(ck_strcol(t["s"], rows))
+    return out
+
+
+def _ck_segments_words(values, off):
+    """Like _ck_segments for 8-byte children: the addends are the words themselves (+1, modulo 2^64)."""
+    off = np.asarray(off, dtype=np.int64)
+    n = len(off) - 1
+    lens = off[1:] - off[:-1]
+    total = int(off[-1])
+    with np.errstate(over="ignore"):
+        if total:
+            maxlen = int(lens.max())
+            kpow = np.ones(maxlen + 1, dtype=np.uint64)
+            for i in range(1, maxlen + 1):
+                kpow[i] = kpow[i - 1] * CK_K
+            row = np.repeat(np.arange(n), lens)
+            pos = np.arange(total) - np.repeat(off[:-1], lens)
+            terms = (np.asarray(values, dtype=np.uint64) + np.uint64(1)) * kpow[lens[row] - 1 - pos]
+            cs = np.concatenate([[np.uint64(0)], np.cumsum(terms, dtype=np.uint64)])
+            h = cs[off[1:]] - cs[off[:-1]]
+        else:
+            h = np.zeros(n, dtype=np.uint64)
+        return ck_mix(h ^ (lens.astype(np.uint64) * CK_NULL))
