@@ -1,16 +1,17 @@
 #!/usr/bin/env python
 """bench.py — the driver's measurement contract for duckhts_b200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload read_bam|inflate]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over one rank's whole input:
-  * `value`   device-timed throughput with the compressed input already resident in HBM,
-  * `e2e`     the same metric through the C-ABI with HOST buffers (pinned), H2D + kernels + D2H all inside
-              the timed region,
-  * `roofline` for the dominant kernel (BGZF inflate), `cpu_baseline` (reference htslib on the host cores,
-              bounded sample), `clocks`, `gpu_launches`.
-Inputs are synthetic: a seeded unit written by the reference's htslib at BGZF level 6
-(harness/_bin/gen_synth), tiled up to the configured size (BGZF members concatenate).
+  * `value`     device-timed throughput with the compressed input already resident in HBM (batches left in HBM),
+  * `e2e`       the same scan through the C-ABI with HOST buffers (pinned): H2D + kernels + D2H inside the timed region,
+  * `ext_e2e`   the same scan through the DuckDB extension entry point (duckhts_init_c_api) under harness/fake_duckdb:
+                file on disk in, filled DuckDB vectors out; the reference extension under the same host beside it,
+  * `roofline`  for the dominant kernel pair (BGZF inflate), `cpu_baseline`, `clocks`, `gpu_launches`,
+  * `parity`    per-column checksums of the 100 M-record scan == tiles x the unit's, device == host, both layouts.
+Inputs are synthetic: a seeded unit written by the reference's htslib at BGZF level 6 (harness/_bin/gen_synth), its
+record blocks tiled up to the configured size (BGZF members concatenate).
 """
 import argparse
 import json
@@ -29,6 +30,10 @@ from tests import util  # noqa: E402  (input generation helpers; no oracle impor
 
 HARNESS = os.path.join(ROOT, "harness", "_bin")
 CACHE = util.CACHE
+FAKE_HOST = os.path.join(HARNESS, "fake_duckdb")
+REF_EXT = os.path.join(ROOT, "oracle", "_ref", "libduckhts_ref.so")
+OUR_EXT = os.path.join(ROOT, "duckhts_b200", "lib", "duckhts.duckdb_extension.so")
+M64 = (1 << 64) - 1
 
 
 def log(*a):
@@ -77,6 +82,14 @@ def gen_unit(kind, n_records, seed, paired, procs):
     os.replace(path + ".tmp", path)
     log(f"[bench] generated {path}: {os.path.getsize(path) / 1e6:.1f} MB in {time.time() - t0:.1f}s with {K} writers")
     return path
+
+
+def ensure_bai(path):
+    """BAI next to the unit, built by the reference's htslib (sam_index_build through harness/ref_dump)."""
+    exe = os.path.join(HARNESS, "ref_dump")
+    if not os.path.exists(path + ".bai") and os.path.exists(exe):
+        subprocess.check_call([exe, "index", path, "0"])
+    return os.path.exists(path + ".bai")
 
 
 def tile_image(dh, unit, target_bytes, header_blocks=0):
@@ -154,50 +167,50 @@ def measured_peaks():
 
 
 # ---------------------------------------------------------------------------------------------------------
-# reference arm / cpu baseline
+# the table functions under the fake DuckDB host (both extensions, same binary, same arguments)
 # ---------------------------------------------------------------------------------------------------------
+WORKLOAD = ("read_bam full-column scan (13 core columns + typed tags NM, MD, AS) of a synthetic 100M-record 2x150 bp paired "
+            "WGS-like BAM (BASELINE configs[2]); BGZF inflate GB/s of the same bytes reported alongside (configs[1])")
+TAGS = [(b"NM", "i"), (b"MD", "Z"), (b"AS", "i")]
+STD = ("AM AS BC BQ BZ CB CC CG CM CO CP CQ CR CS CT CY E2 FI FS FZ H0 H1 H2 HI IH LB MC MD MI ML MM MN MQ NH NM OA OC OP OQ OX PG "
+       "PQ PT PU Q2 QT QX R2 RG RX SA SM TC TS U2 UQ").split()
+# schema columns of read_bam(standard_tags := true) that bench.py's projection names: 13 core + NM, MD, AS
+EXT_COLS = ",".join(str(c) for c in list(range(13)) + [13 + STD.index("NM"), 13 + STD.index("MD"), 13 + STD.index("AS")])
+
+
+def host_run(ext, func, path, *args, threads=1, env=None, timeout=900):
+    """fake_duckdb EXT FUNC PATH ... --time -> {"rows", "seconds", "bind_seconds", ...}"""
+    e = dict(os.environ)
+    e.update(env or {})
+    out = subprocess.check_output([FAKE_HOST, ext, func, path, *args, "--threads", str(threads), "--time"], stderr=subprocess.DEVNULL, text=True, env=e, timeout=timeout)
+    return json.loads(out.strip().splitlines()[-1])
+
+
+def ref_read_bam(path, threads, steps, warmup):
+    """The unchanged reference extension (oracle/_ref/libduckhts_ref.so = /root/reference/src/*.c + htslib 1.23, zlib) scanning
+    `path` under the fake host: with the .bai next to it the reference runs its contig-parallel mode (src/bam_reader.c:577-585,
+    689-716: up to 16 scan threads x 2 htslib threads); without, one scan thread."""
+    for _ in range(warmup):
+        host_run(REF_EXT, "read_bam", path, "standard_tags=true", "--cols", EXT_COLS, threads=threads)
+    res = [host_run(REF_EXT, "read_bam", path, "standard_tags=true", "--cols", EXT_COLS, threads=threads) for _ in range(max(steps, 1))]
+    secs = float(np.mean([r["seconds"] for r in res]))
+    return {"value": res[0]["rows"] / 1e6 / secs, "unit": "Mrecords/s", "rows": res[0]["rows"], "seconds": secs, "threads": res[0]["threads"],
+            "max_threads": res[0]["max_threads"]}
+
+
 def run_ref_bench(mode, path, threads, limit):
     exe = os.path.join(HARNESS, "ref_bench")
     out = subprocess.check_output([exe, mode, path, str(threads), str(limit)], text=True)
     return json.loads(out.strip().splitlines()[-1])
 
 
-def cpu_baseline_inflate(unit_path, threads, out_limit):
-    """Reference htslib bgzf_read loop (src/bgzip.c:154-200) with bgzf_mt(threads) on a bounded sample."""
-    if os.path.exists(os.path.join(HARNESS, "ref_bench")):
-        r = run_ref_bench("bgunzip", unit_path, threads, out_limit)
-        return {"value": r["bytes_out"] / 1e9 / r["seconds"], "unit": "GB/s decompressed", "cores": threads, "kind": "reference",
-                "sample": f"first {r['bytes_out'] / 1e9:.2f} GB (inflated) of the seeded unit, htslib 1.23 bgzf_mt({threads}) + zlib"}
-    from oracle import dh_oracle_py as orc  # cpu_baseline leg: the one place bench.py may execute oracle/
-
-    data = np.fromfile(unit_path, dtype=np.uint8)
-    blocks, _ = orc.bgzf_walk(data)
-    cut, acc = 0, 0
-    for b in blocks:
-        acc += b[2]
-        cut = b[0] + b[1]
-        if acc >= out_limit:
-            break
-    t0 = time.time()
-    rc, _, _ = orc.bgzf_inflate(data[:cut], want_output=False)
-    dt = time.time() - t0
-    return {"value": acc / 1e9 / dt, "unit": "GB/s decompressed", "cores": 1, "kind": "port",
-            "sample": f"first {acc / 1e9:.2f} GB (inflated) of the seeded unit, oracle port (zlib), 1 thread"}
-
-
-# ---------------------------------------------------------------------------------------------------------
-WORKLOAD = ("read_bam full-column scan (13 core columns + typed tags NM, MD, AS) of a synthetic 100M-record 2x150 bp paired "
-            "WGS-like BAM (BASELINE configs[2]); BGZF inflate GB/s of the same bytes reported alongside (configs[1])")
-TAGS = [(b"NM", "i"), (b"MD", "Z"), (b"AS", "i")]
-
-
-def cpu_baseline_read_bam(unit_path, threads, max_records):
-    """The reference's htslib path (sam_read1 + the column conversions of src/bam_reader.c:779-966 through the same
-    htslib calls) with hts_set_threads(threads), on a bounded sample."""
-    r = run_ref_bench("sam_read1", unit_path, threads, max_records)
-    return {"value": r["records"] / 1e6 / r["seconds"], "unit": "Mrecords/s", "cores": threads, "kind": "reference",
-            "sample": f"first {r['records']} records of the seeded unit BAM; htslib 1.23 (zlib) sam_read1 + bam_reader.c conversions, "
-                      f"hts_set_threads({threads})"}
+def common_config(args):
+    """The same dict in both arms: what is scanned and how it is asked for."""
+    return {"workload": WORKLOAD,
+            "input": f"seeded unit ({args.unit_records} paired 2x150 records, 22 contigs, tags NM MD AS RG, written by the reference htslib at BGZF level 6); "
+                     "our arm tiles its record blocks to the target size, the reference arm scans the unit itself (bounded sample)",
+            "projection": "13 core columns + NM, MD, AS (read_bam(path, standard_tags := true), schema columns " + EXT_COLS + ")",
+            "records_per_gpu_target": int(args.records), "sharding": "contiguous virtual-offset range per GPU, no collective"}
 
 
 def gen_bcf(n_sites, n_samples, seed):
@@ -213,13 +226,12 @@ def gen_bcf(n_sites, n_samples, seed):
 
 
 def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
-    """BASELINE configs[4] shape (tidy FORMAT/GT + INFO decode, 2,504 samples), every column: sites/s and tidy rows/s."""
+    """BASELINE configs[4]: tidy FORMAT/GT + INFO decode of 1,000,000 sites x 2,504 samples, every column: sites/s and tidy rows/s."""
     ns = 2504
     if rank == 0:
         gen_bcf(args.bcf_sites, ns, 0x5eed)
     barrier()
     path = gen_bcf(args.bcf_sites, ns, 0x5eed)
-    from duckhts_b200.bgzf import PinnedBuffer
 
     raw = np.fromfile(path, dtype=np.uint8)
     # bcf_hdr_write flushes the BGZF stream after the header (htslib/vcf.c:1802): the record blocks can be tiled like the BAM unit's
@@ -235,9 +247,9 @@ def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
     n_sites = args.bcf_sites * reps
     bf = dh.BcfFile(ctx, pin)
     out = {"workload": f"read_bcf tidy_format scan, all columns (7 core + {len(bf.info)} INFO + SAMPLE_ID + {len(bf.format)} FORMAT), "
-                       f"{n_sites} biallelic sites x {ns} samples (BASELINE configs[4] shape; a seeded {args.bcf_sites}-site unit written by the "
+                       f"{n_sites} biallelic sites x {ns} samples (BASELINE configs[4]; a seeded {args.bcf_sites}-site unit written by the "
                        f"reference htslib at BGZF level 6, its record blocks tiled x{reps})",
-           "compressed_mb": pin.array.size / 1e6}
+           "sites": n_sites, "compressed_mb": pin.array.size / 1e6}
 
     def once():
         bf.scan_begin()
@@ -245,7 +257,7 @@ def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
         return n, bf.stats()
 
     bf.set_mode(device_input=True, device_output=True)
-    for _ in range(args.warmup):
+    for _ in range(min(args.warmup, 2)):
         n, st = once()
     assert st.status == 0 and n == n_sites, (st.status, n, n_sites)
     barrier()
@@ -261,7 +273,7 @@ def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
                 "kernel_ms_per_step": {"bgzf_inflate": k[0] / args.steps, "bcf_walk": k[1] / args.steps, "bcf_decode": k[2] / args.steps}})
     bf.set_mode(device_input=False, device_output=False)
     walls = []
-    for it in range(1 + args.steps):
+    for it in range(1 + min(args.steps, 2)):
         barrier()
         t0 = time.perf_counter()
         n, st = once()
@@ -272,21 +284,29 @@ def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
                   "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes),
                   "d2h_gbs": st.d2h_bytes / 1e9 / (w / 1e3)}
     bf.close()
-    host, ref = os.path.join(HARNESS, "fake_duckdb"), os.path.join(ROOT, "oracle", "_ref", "libduckhts_ref.so")
-    if rank == 0 and os.path.exists(host) and os.path.exists(ref):
-        sample = gen_bcf(min(args.bcf_sites, 3000), ns, 0x5eed)
-        r = json.loads(subprocess.check_output([host, ref, "read_bcf", sample, "tidy_format=true", "--time"], stderr=subprocess.DEVNULL, text=True).strip().splitlines()[-1])
-        out["cpu_baseline"] = {"value": r["rows"] / ns / r["seconds"], "unit": "sites/s", "rows_per_s": r["rows"] / r["seconds"], "cores": 1, "kind": "reference",
-                               "sample": f"{r['rows'] // ns} sites x {ns} samples; the unchanged reference extension (read_bcf, tidy_format) under harness/fake_duckdb, "
-                                         "1 scan thread (no index => the reference scans sequentially)"}
+    del pin
+    if rank == 0 and os.path.exists(FAKE_HOST):
+        # the table function itself (duckhts_init_c_api under the fake host) on the unit; the unchanged reference extension on a bounded sample
+        try:
+            ncpu = os.cpu_count() or 1
+            r = host_run(OUR_EXT, "read_bcf", path, "tidy_format=true", threads=min(ncpu, 16))
+            out["ext_e2e"] = {"value": r["rows"] / ns / r["seconds"], "unit": "sites/s", "rows_per_s": r["rows"] / r["seconds"], "threads": r["threads"],
+                              "sites": r["rows"] // ns, "seconds": r["seconds"], "bind_seconds": r["bind_seconds"]}
+        except Exception as e:  # noqa: BLE001
+            out["ext_e2e"] = {"error": str(e)[:300]}
+        if os.path.exists(REF_EXT):
+            sample = gen_bcf(min(args.bcf_sites, 3000), ns, 0x5eed)
+            r = host_run(REF_EXT, "read_bcf", sample, "tidy_format=true", threads=1)
+            out["cpu_baseline"] = {"value": r["rows"] / ns / r["seconds"], "unit": "sites/s", "rows_per_s": r["rows"] / r["seconds"], "cores": 1, "kind": "reference",
+                                   "sample": f"{r['rows'] // ns} sites x {ns} samples; the unchanged reference extension (read_bcf, tidy_format) under harness/fake_duckdb, "
+                                             "1 scan thread (no index => the reference scans sequentially)"}
     return out
 
 
 def bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rsum):
     """BASELINE configs[3]: BAI-driven scan, contig groups balanced by compressed bytes, one group per GPU (no collective)."""
-    exe = os.path.join(HARNESS, "ref_dump")
-    if rank == 0 and not os.path.exists(unit_path + ".bai") and os.path.exists(exe):
-        subprocess.check_call([exe, "index", unit_path, "0"])
+    if rank == 0:
+        ensure_bai(unit_path)
     barrier()
     if not os.path.exists(unit_path + ".bai"):
         return None
@@ -298,6 +318,7 @@ def bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rs
     bai = np.fromfile(unit_path + ".bai", dtype=np.uint8)
     bf = dh.BamFile(ctx, pin)
     bf.set_projection(None, TAGS)
+    bf.set_mode(compact=True)
     ix = dh.Index(ctx, bai)
     bounds = bf.split_contigs(ix, world)
     walls, rows = [], 0
@@ -314,8 +335,8 @@ def bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rs
     bf.close()
     ix.close()
     return {"workload": "read_bam over contig groups from the BAI index (chr1-chr22), host buffers in and out; the file is split over the GPUs "
-                        "(strong scaling on one 4M-record file)", "value": total / 1e6 / (w / 1e3), "unit": "Mrecords/s", "ms_per_step": w,
-            "records": int(total), "contig_bounds": bounds, "status": int(st.status)}
+                        "(strong scaling on the 4M-record unit: the tiled 100M image is not coordinate-sorted, so it has no BAI)", "value": total / 1e6 / (w / 1e3),
+            "unit": "Mrecords/s", "ms_per_step": w, "records": int(total), "contig_bounds": bounds, "status": int(st.status)}
 
 
 def main():
@@ -328,35 +349,43 @@ def main():
     ap.add_argument("--unit-records", type=int, default=4000000)
     ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x9E3779B97F4A7C15)
     ap.add_argument("--bcf-sites", type=int, default=20000, help="sites of the seeded 2,504-sample BCF unit (0 = skip the sub-benchmark)")
-    ap.add_argument("--bcf-tiles", type=int, default=5, help="how many times the unit's record blocks are repeated in the scanned image")
+    ap.add_argument("--bcf-tiles", type=int, default=50, help="how many times the unit's record blocks are repeated in the scanned image (50 x 20,000 = 1M sites)")
+    ap.add_argument("--no-ext", action="store_true", help="skip the extension-level runs (fake DuckDB host)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     ncpu = os.cpu_count() or 1
-    config = {"workload": WORKLOAD, "records_per_gpu_target": int(args.records),
-              "input": f"seeded unit ({args.unit_records} paired 2x150 records, 22 contigs, written by the reference htslib at BGZF level 6) "
-                       "with its record blocks tiled to the target size", "sharding": "contiguous virtual-offset range per GPU, no collective"}
+    config = common_config(args)
 
     if args.impl == "reference":
+        # The reference's own CPU implementation of the path, stock code: the unchanged extension under the fake DuckDB host, the .bai
+        # next to the file, all the threads its global init allows (min(n_contigs, 16) scan threads, 2 htslib threads each).
         if rank != 0:
             return 0
         unit_path = gen_unit("bam", args.unit_records, args.seed, True, ncpu)
-        limit = 2000000
-        for _ in range(min(args.warmup, 1)):
-            run_ref_bench("sam_read1", unit_path, ncpu, 200000)
-        res = [run_ref_bench("sam_read1", unit_path, ncpu, limit) for _ in range(args.steps)]
-        secs = sum(r["seconds"] for r in res)
-        recs = sum(r["records"] for r in res)
-        v = recs / 1e6 / secs
+        have_bai = ensure_bai(unit_path)
+        thr = min(16, ncpu)
+        par = ref_read_bam(unit_path, thr, args.steps, min(args.warmup, 1))
+        one = ref_read_bam(unit_path, 1, 1, 0)
+        extra = {}
+        try:
+            r = run_ref_bench("sam_read1", unit_path, ncpu, 2000000)
+            extra["htslib_loop"] = {"value": r["records"] / 1e6 / r["seconds"], "unit": "Mrecords/s", "cores": ncpu,
+                                    "what": "harness/ref_bench: sam_read1 + the conversions of src/bam_reader.c:779-966, one consumer, hts_set_threads(all cores), first 2M records"}
+        except Exception as e:  # noqa: BLE001
+            extra["htslib_loop"] = {"error": str(e)[:200]}
+        v = par["value"]
         cb = {"value": v, "unit": "Mrecords/s", "cores": ncpu, "kind": "reference",
-              "sample": f"first {res[0]['records']} records of the seeded unit BAM per step; htslib 1.23 (zlib) sam_read1 + "
-                        f"src/bam_reader.c column conversions, hts_set_threads({ncpu})"}
+              "sample": f"the whole {par['rows']}-record unit BAM per step ({'with' if have_bai else 'WITHOUT'} its .bai => contig-parallel mode), unchanged reference "
+                        f"extension under harness/fake_duckdb, {par['threads']} scan threads (max_threads {par['max_threads']}) x 2 htslib threads, zlib",
+              "threads_1": one, "threads_16": par}
+        cb.update(extra)
         line = {"impl": "reference", "metric": "read_bam_Mrecords_per_s", "value": v, "unit": "Mrecords/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * par["seconds"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config, "cpu_baseline": cb,
-                "e2e": {"value": v, "unit": "Mrecords/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+                "e2e": {"value": v, "unit": "Mrecords/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0, "host_cores": ncpu}
         print(json.dumps(line), flush=True)
         return 0
 
@@ -386,6 +415,15 @@ def main():
     rmax = lambda x: reduce(x, dist.ReduceOp.MAX) if world > 1 else x  # noqa: E731
     rsum = lambda x: reduce(x, dist.ReduceOp.SUM) if world > 1 else x  # noqa: E731
 
+    def sum_u64(vals):
+        """Sum of 64-bit checksums over the ranks, modulo 2^64 (32-bit halves ride in int64 words)."""
+        vals = [int(v) & M64 for v in vals]
+        if world == 1:
+            return vals
+        t = torch.tensor([[v & 0xffffffff, v >> 32] for v in vals], dtype=torch.int64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [(int(lo) + (int(hi) << 32)) & M64 for lo, hi in t.tolist()]
+
     torch.cuda.set_device(local_rank)
     if rank == 0:
         gen_unit("bam", args.unit_records, args.seed, True, ncpu)
@@ -394,65 +432,123 @@ def main():
     unit = np.fromfile(unit_path, dtype=np.uint8)
 
     ctx = dh.Context(local_rank)
-    with dh.BamFile(ctx, unit) as ub:   # where do the alignment blocks start, how many records does the unit hold
+    # ---- the unit: where its alignment blocks start, how many records it holds, its per-column checksums ------------------------
+    with dh.BamFile(ctx, unit) as ub:
         first_voff = ub.first_voffset
-        ub.set_projection(0, ())
+        ub.set_projection(None, TAGS)
+        ub.set_mode(device_input=True, device_output=True, compact=True)
         ub.scan_begin()
-        unit_rows = ub.drain()
+        unit_rows, unit_sums = ub.drain_checksums()
+        unit_sums = [int(x) for x in unit_sums]
     blocks, _ = dh.bgzf_walk(unit)
     header_blocks = next(i for i, b in enumerate(blocks) if b[0] == first_voff >> 16)
     assert first_voff & 0xffff == 0, "htslib flushes after the header: first record starts a block"
     body_bytes = blocks[-1][0] - blocks[header_blocks][0]
     reps = max(1, int(round(args.records / unit_rows)))
     pin, reps = tile_image(dh, unit, reps * body_bytes, header_blocks=header_blocks)
+    want_sums = [(s * reps) & M64 for s in unit_sums]
     h2d_gbs, d2h_gbs = ctx.measure_pcie(1 << 30)
     bf = dh.BamFile(ctx, pin)
     bf.set_projection(None, TAGS)
+    parity = {"what": "per-column 64-bit checksums (dh_bam_batch_checksum: sum over rows of a hash of every cell's value) of the tiled scan == tiles x the "
+                      "unit's, modulo 2^64; the unit itself is compared cell by cell with the reference extension in tests/test_ext_gpu.py",
+              "tiles": reps, "columns": 13 + len(TAGS), "checks": []}
+
+    def check_sums(name, rows, sums, want_rows, want):
+        ok = rows == want_rows and [int(x) & M64 for x in sums] == want
+        parity["checks"].append({"scan": name, "rows": int(rows), "ok": bool(ok)})
+        if not ok:
+            bad = [c for c, (a, b) in enumerate(zip(sums, want)) if (int(a) & M64) != b]
+            raise AssertionError(f"PARITY FAILURE in {name}: rows {rows} (want {want_rows}), columns that differ: {bad}")
 
     def scan_once():
         bf.scan_begin()
         rows = bf.drain()
         return rows, bf.stats()
 
-    # ---- value: compressed image resident in HBM, columns left in HBM; CUDA events on the kernels' stream --------
-    bf.set_mode(device_input=True, device_output=True)
-    for _ in range(args.warmup):
-        rows, st = scan_once()
-    assert st.status == 0 and rows == reps * unit_rows, (st.status, rows, reps * unit_rows)
-    barrier()
-    with ClockSampler(local_rank) as clk:
-        launches0 = ctx.launches
-        ctx.timer_start()
-        kms = [0.0, 0.0, 0.0]
-        for _ in range(args.steps):
+    def timed_value(compact):
+        """compressed image resident in HBM, batches left in HBM; CUDA events on the kernels' stream."""
+        bf.set_mode(device_input=True, device_output=True, compact=compact)
+        # warm-up scan 1 carries the parity check: the checksum kernel runs on every batch while it is held
+        bf.scan_begin()
+        rows, sums = bf.drain_checksums()
+        check_sums(f"device-resident, {'compact' if compact else 'DuckDB'} layout", rows, sums, reps * unit_rows, want_sums)
+        for _ in range(max(args.warmup - 1, 0)):
             rows, st = scan_once()
-            kms = [kms[0] + st.inflate_ms, kms[1] + st.walk_ms, kms[2] + st.decode_ms]
-        ms = ctx.timer_stop()
-        launches = ctx.launches - launches0
+        assert st.status == 0 and rows == reps * unit_rows, (st.status, rows, reps * unit_rows)
         barrier()
-    ms = rmax(ms)
-    ms_per_step = ms / args.steps
+        with ClockSampler(local_rank) as clk:
+            l0 = ctx.launches
+            ctx.timer_start()
+            kms = [0.0, 0.0, 0.0]
+            for _ in range(args.steps):
+                rows, st = scan_once()
+                kms = [kms[0] + st.inflate_ms, kms[1] + st.walk_ms, kms[2] + st.decode_ms]
+            ms = ctx.timer_stop()
+            launches = ctx.launches - l0
+            barrier()
+        return rmax(ms) / args.steps, rows, st, kms, launches, clk
+
+    # ---- value: the layout the product ships (compact), then the DuckDB layout for continuity with round 1 ----------------------
+    ms_per_step, rows, st, kms, launches, clk = timed_value(True)
     total_rows = rsum(float(rows))
     value = total_rows / 1e6 / (ms_per_step / 1e3)
-    comp_bytes, out_bytes, nblocks = st.h2d_bytes, st.inflated_bytes, st.n_blocks
+    nblocks = st.n_blocks
     comp_bytes = pin.nbytes
+    ms_duck, _, _, kms_duck, _, _ = timed_value(False)
 
-    # ---- e2e: pinned host image in, DuckDB-layout column batches in pinned host memory out -------------------------
-    bf.set_mode(device_input=False, device_output=False)
-    e2e_ms, d2h_bytes, h2d_bytes = [], 0, 0
-    for it in range(1 + args.steps):
-        barrier()
-        t0 = time.perf_counter()
-        rows, st = scan_once()
-        wall = (time.perf_counter() - t0) * 1e3
-        if it >= 1:
-            e2e_ms.append(rmax(wall))
-            d2h_bytes, h2d_bytes = st.d2h_bytes, st.h2d_bytes
-    e2e_step = float(np.mean(e2e_ms))
+    # ---- e2e: pinned host image in, column batches in pinned host memory out (C-ABI) ---------------------------------------------
+    def timed_e2e(compact):
+        bf.set_mode(device_input=False, device_output=False, compact=compact)
+        walls, d2h, h2d = [], 0, 0
+        for it in range(1 + args.steps):
+            barrier()
+            t0 = time.perf_counter()
+            if it == 0:      # untimed pass: host-side checksums of what crossed PCIe
+                bf.scan_begin()
+                r, sums = bf.drain_checksums()
+                check_sums(f"host-to-host, {'compact' if compact else 'DuckDB'} layout", r, sums, reps * unit_rows, want_sums)
+                continue
+            r, s = scan_once()
+            walls.append(rmax((time.perf_counter() - t0) * 1e3))
+            d2h, h2d = s.d2h_bytes, s.h2d_bytes
+        return float(np.mean(walls)), int(d2h), int(h2d)
+
+    e2e_step, d2h_bytes, h2d_bytes = timed_e2e(True)
     e2e_val = total_rows / 1e6 / (e2e_step / 1e3)
+    e2e_duck_step, d2h_duck, _ = timed_e2e(False)
+
+    # ---- strong scaling: ONE image, one contiguous virtual-offset range per GPU, merged rows and checksums == the whole scan ------
+    strong = None
+    if world > 1:
+        voffs = bf.split(world)
+        bf.set_mode(device_input=False, device_output=False, compact=True)
+        walls = []
+        for it in range(1 + args.steps):
+            barrier()
+            t0 = time.perf_counter()
+            if voffs[rank] != dh.VOFF_MAX:
+                bf.scan_begin(voffs[rank], voffs[rank + 1])
+                if it == 0:
+                    r, sums = bf.drain_checksums()
+                else:
+                    r = bf.drain()
+            else:
+                r, sums = 0, np.zeros(76, dtype=np.uint64)
+            w = rmax((time.perf_counter() - t0) * 1e3)
+            if it == 0:
+                merged_rows = int(rsum(float(r)))
+                merged = sum_u64(list(sums)[:13 + len(TAGS)])
+                check_sums(f"strong scaling, {world} ranges merged", merged_rows, merged + [0] * (76 - len(merged)), reps * unit_rows, want_sums)
+            else:
+                walls.append(w)
+        sw = float(np.mean(walls))
+        strong = {"workload": f"ONE {reps * unit_rows}-record image cut into {world} contiguous virtual-offset ranges (dh_bam_split), one per GPU, host buffers in and out, "
+                              "compact layout; merged row count and per-column checksums equal the single-GPU scan", "value": reps * unit_rows / 1e6 / (sw / 1e3),
+                  "unit": "Mrecords/s", "ms_per_step": sw, "scaling": "strong", "records": reps * unit_rows}
     bf.close()
 
-    # ---- the dominant kernel alone (BGZF inflate of the same bytes, device-resident): roofline + inflate GB/s -------
+    # ---- the dominant kernel pair alone (BGZF inflate of the same bytes, device-resident): roofline + inflate GB/s ----------------
     dev = dh.BgzfDevice(ctx, pin)
     ib_comp, ib_out = dev.comp_bytes, dev.out_bytes
     for _ in range(args.warmup):
@@ -483,19 +579,89 @@ def main():
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))["dram_bytes_per_inflated_byte"] * ib_out * args.steps / groups
 
+    # ---- configs[1] end to end + the table function itself: the tiled image as a FILE ---------------------------------------------
+    ext, bgunzip = None, None
+    big_path = os.path.join(CACHE, f"bench_tiled_{rank}.bam")
+    if rank == 0 and world == 1 and not args.no_ext and os.path.exists(FAKE_HOST):
+        try:
+            t0 = time.time()
+            with open(big_path, "wb") as f:
+                a = pin.array
+                for o in range(0, a.size, 1 << 28):
+                    f.write(memoryview(a[o:o + (1 << 28)]))
+            log(f"[bench] wrote {big_path}: {os.path.getsize(big_path) / 1e9:.2f} GB in {time.time() - t0:.1f}s")
+            # bgunzip-equivalent (configs[1]): file (page cache) -> pinned staging -> GPU inflate -> pinned staging -> write(2) to /dev/null
+            import ctypes as C
+            from duckhts_b200._lib import InflateStats, lib as L
+            fd_in, fd_out = os.open(big_path, os.O_RDONLY), os.open("/dev/null", os.O_WRONLY)
+            sti = InflateStats()
+            best = None
+            for _ in range(2):
+                t0 = time.perf_counter()
+                rc = L().dh_bgzf_inflate_fd(ctx.h, fd_in, fd_out, C.byref(sti))
+                dt = time.perf_counter() - t0
+                assert rc == 0, rc
+                best = dt if best is None else min(best, dt)
+            os.close(fd_in)
+            os.close(fd_out)
+            bgunzip = {"metric": "bgunzip_decompressed_GBps_host_to_host", "value": sti.out_bytes / 1e9 / best, "unit": "GB/s", "seconds": best,
+                       "compressed_gb": sti.comp_bytes / 1e9, "inflated_gb": sti.out_bytes / 1e9, "blocks": int(sti.n_blocks),
+                       "what": "dh_bgzf_inflate_fd (what the bgunzip table function runs): pread from the page cache, H2D, inflate + CRC, D2H, write(2) to /dev/null; "
+                               "3 pinned staging slots, nothing held whole",
+                       "d2h_bound_GBps": d2h_gbs}
+        except Exception as e:  # noqa: BLE001
+            bgunzip = {"error": str(e)[:300]}
+    del pin
+    if rank == 0 and world == 1 and not args.no_ext and os.path.exists(FAKE_HOST):
+        ext = {"what": "read_bam(path, standard_tags := true) projected on the bench columns, through duckhts_init_c_api under harness/fake_duckdb "
+                       "(bind: file -> pinned image + header; scan: GPU pipeline -> filled DuckDB vectors); seconds include bind",
+               "host_threads": min(16, ncpu)}
+        try:
+            ensure_bai(unit_path)
+            thr = min(16, ncpu)
+            for name, path in (("unit", unit_path), ("tiled_100M", big_path)):
+                if not os.path.exists(path):
+                    continue
+                o = {}
+                for t in (1, thr):
+                    runs = 2 if (t == thr or name == "unit") else 1
+                    r = min((host_run(OUR_EXT, "read_bam", path, "standard_tags=true", "--cols", EXT_COLS, threads=t) for _ in range(runs)), key=lambda x: x["seconds"])
+                    o[f"threads_{t}"] = {"value": r["rows"] / 1e6 / r["seconds"], "unit": "Mrecords/s", "rows": r["rows"], "seconds": r["seconds"], "bind_seconds": r["bind_seconds"],
+                                         "scan_Mrecords_per_s": r["rows"] / 1e6 / max(r["seconds"] - r["bind_seconds"], 1e-9)}
+                ext[name] = o
+            if os.path.exists(REF_EXT):
+                ext["reference_unit"] = {"threads_1": ref_read_bam(unit_path, 1, 1, 0), f"threads_{thr}": ref_read_bam(unit_path, thr, 2, 1)}
+            best = ext.get("tiled_100M", ext.get("unit", {})).get(f"threads_{thr}")
+            if best:
+                ext["value"] = best["value"]
+                ext["unit"] = "Mrecords/s"
+        except Exception as e:  # noqa: BLE001
+            ext["error"] = str(e)[:300]
+    if os.path.exists(big_path):
+        os.unlink(big_path)
+
     bcf_res = bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum) if args.bcf_sites > 0 and os.path.exists(os.path.join(HARNESS, "gen_bcf")) else None
     shard_res = bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rsum)
 
     if rank == 0:
-        cpu = cpu_baseline_read_bam(unit_path, ncpu, 2000000) if world == 1 else None
+        cpu = None
+        if world == 1 and os.path.exists(REF_EXT) and os.path.exists(FAKE_HOST):
+            have_bai = ensure_bai(unit_path)
+            thr = min(16, ncpu)
+            par = (ext or {}).get("reference_unit", {}).get(f"threads_{thr}") or ref_read_bam(unit_path, thr, 1, 0)
+            cpu = {"value": par["value"], "unit": "Mrecords/s", "cores": ncpu, "kind": "reference",
+                   "sample": f"the whole {par['rows']}-record unit BAM ({'with' if have_bai else 'WITHOUT'} its .bai => contig-parallel mode), unchanged reference extension under "
+                             f"harness/fake_duckdb, {par['threads']} scan threads x 2 htslib threads, zlib"}
         rec_c = comp_bytes / rows
-        config.update({"records_per_gpu": int(rows), "compressed_gb_per_gpu": comp_bytes / 1e9, "inflated_gb_per_gpu": ib_out / 1e9,
-                       "bgzf_blocks_per_gpu": int(nblocks), "tiles": reps, "compressed_bytes_per_record": rec_c,
-                       "l2": "inputs (>= 10 GB per GPU) far exceed the 126 MB L2; no flush needed"})
+        run = {"records_per_gpu": int(rows), "compressed_gb_per_gpu": comp_bytes / 1e9, "inflated_gb_per_gpu": ib_out / 1e9,
+               "bgzf_blocks_per_gpu": int(nblocks), "tiles": reps, "compressed_bytes_per_record": rec_c, "layout": "compact wire layout (DH_BAM_COMPACT_OUTPUT)",
+               "l2": "inputs (>= 10 GB per GPU) far exceed the 126 MB L2; no flush needed"}
         line = {"metric": "read_bam_Mrecords_per_s", "value": value, "unit": "Mrecords/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "u8", "data": "synthetic", "config": config,
+                "dtype": "u8", "data": "synthetic", "config": config, "run": run, "parity": parity,
                 "kernel_ms_per_step": {"bgzf_inflate": kms[0] / args.steps, "bam_walk": kms[1] / args.steps, "bam_decode": kms[2] / args.steps},
+                "value_duckdb_layout": {"value": total_rows / 1e6 / (ms_duck / 1e3), "unit": "Mrecords/s", "ms_per_step": ms_duck,
+                                        "bam_decode_ms": kms_duck[2] / args.steps},
                 "inflate": {"metric": "bgzf_inflate_decompressed_GBps", "value": inflate_gbs, "unit": "GB/s",
                             "ms_per_step": ims / args.steps, "compressed_gb": ib_comp / 1e9, "inflated_gb": ib_out / 1e9,
                             "phase_ms": {"bgzf_decode3_kernel": ph1, "bgzf_resolve3_kernel": ph2, "fallback_filter": ph3},
@@ -505,12 +671,15 @@ def main():
                              "algorithmic_bytes_per_launch": alg_bytes,
                              "peak_source": peak_src, "kernel_ms": kernel_ms},
                 "e2e": {"value": e2e_val, "unit": "Mrecords/s", "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
-                        "ms_per_step": e2e_step, "pcie_h2d_gbs": h2d_gbs, "pcie_d2h_gbs": d2h_gbs,
+                        "ms_per_step": e2e_step, "d2h_bytes_per_record": d2h_bytes / max(rows, 1), "pcie_h2d_gbs": h2d_gbs, "pcie_d2h_gbs": d2h_gbs,
                         "pcie_ingest_roofline_Mrec_s": h2d_gbs * 1e3 / rec_c,
                         "pcie_ingest_roofline_frac": e2e_val / (h2d_gbs * 1e3 / rec_c),
                         "pcie_return_roofline_frac": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / d2h_gbs,
                         "pcie_bidir_h2d_gbs": bi_h2d, "pcie_bidir_d2h_gbs": bi_d2h,
-                        "pcie_return_roofline_frac_bidir": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / bi_d2h},
+                        "pcie_return_roofline_frac_bidir": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / bi_d2h,
+                        "duckdb_layout": {"value": total_rows / 1e6 / (e2e_duck_step / 1e3), "unit": "Mrecords/s", "ms_per_step": e2e_duck_step,
+                                          "d2h_bytes_per_step": int(d2h_duck), "d2h_bytes_per_record": d2h_duck / max(rows, 1)}},
+                "ext_e2e": ext, "bgunzip_e2e": bgunzip, "strong_scaling": strong,
                 "read_bcf": bcf_res, "contig_sharded": shard_res,
                 "cpu_baseline": cpu, "clocks": clk.summary(), "gpu_launches": int(launches), "host_cores": ncpu}
         print(json.dumps(line), flush=True)

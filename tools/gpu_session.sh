@@ -1,0 +1,19 @@
+#!/bin/bash
+# One GPU session.  usage: tools/gpu_session.sh [stage ...]   stages: box tests newtests bench ref ncu scale2
+#   box       machine facts                      tests     the whole -m gpu suite
+#   newtests  only this round's new GPU tests    bench     bench.py (both arms)
+#   ncu       launch list + --set full capture of the inflate kernels (after the plain runs)
+mkdir -p gpurun_out
+T=${TAG:-r2}
+for stage in "$@"; do
+  case $stage in
+    box) (nproc; free -g; lscpu | grep -E "Model name|Socket|NUMA|Thread|Core"; nvidia-smi -L) > gpurun_out/${T}_box.txt 2>&1 ;;
+    smoke) timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; echo "smoke exit $?"; tail -3 gpurun_out/${T}_smoke.log ;;
+    newtests) timeout 1500 python -m pytest tests/test_wire_gpu.py tests/test_ext_gpu.py -m gpu -x -q > gpurun_out/${T}_pytest_new.log 2>&1; echo "pytest(new) exit $?" | tee -a gpurun_out/${T}_pytest_new.log; tail -25 gpurun_out/${T}_pytest_new.log ;;
+    tests) timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/${T}_pytest_gpu.log; tail -25 gpurun_out/${T}_pytest_gpu.log ;;
+    bench) timeout 1500 python bench.py --steps 3 --warmup 3 > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"; cat gpurun_out/${T}_bench.json; tail -5 gpurun_out/${T}_bench.err ;;
+    ref) timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_reference_bench.json 2> gpurun_out/${T}_reference_bench.err; cat gpurun_out/${T}_reference_bench.json; tail -3 gpurun_out/${T}_reference_bench.err ;;
+    ncu) bash tools/gpu_ncu1.sh ;;
+    *) echo "unknown stage $stage" ;;
+  esac
+done
