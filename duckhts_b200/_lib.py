@@ -80,6 +80,7 @@ SIGNATURES = {
     "dh_bgzf_dev_check": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "dh_bgzf_dev_read": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
     "dh_bam_open": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "dh_bam_open_file": (C.c_void_p, [C.c_void_p, C.c_char_p]),
     "dh_bam_close": (None, [C.c_void_p]),
     "dh_bam_n_ref": (C.c_int32, [C.c_void_p]),
     "dh_bam_ref_name": (C.c_char_p, [C.c_void_p, C.c_int32]),

@@ -87,6 +87,16 @@ class BamFile:
             raise DuckhtsError("dh_bam_open failed: " + lib().dh_last_error().decode())
         self.tags = []
 
+    @classmethod
+    def open_file(cls, ctx, path):
+        """dh_bam_open_file: the file is streamed through pinned staging buffers instead of being held as one image."""
+        o = cls.__new__(cls)
+        o.a, o.ctx, o.tags = None, ctx, []
+        o.h = lib().dh_bam_open_file(ctx.h, path.encode() if isinstance(path, str) else path)
+        if not o.h:
+            raise DuckhtsError("dh_bam_open_file failed: " + lib().dh_last_error().decode())
+        return o
+
     def close(self):
         if self.h:
             lib().dh_bam_close(self.h)
@@ -281,7 +291,9 @@ def _compact_batch_to_columns(bf, b):
             slot_cols.append((c, k, "b" if ty[0] == "B" else "s"))
     if on(11):
         slot_cols.append((11, "rg", "s"))
-    lens = {c: (arr(c, np.uint32) if kind != "b" else arr(c, np.uint64).reshape(n, 2)) for c, _, kind in slot_cols}
+    lens = {c: (arr(c, np.uint32) if kind != "b" else
+                (np.frombuffer(C.string_at(b.data[c], 16 * n), dtype=np.uint64).reshape(n, 2) if n else np.zeros((0, 2), np.uint64)))
+            for c, _, kind in slot_cols}
     valids = {c: validity_to_bool(b.validity[c], n) for c, _, _ in slot_cols}
     vals = {c: [None] * n for c, _, _ in slot_cols}
     for r in range(n):
@@ -387,7 +399,7 @@ def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, 
              regions=None, contigs=None, aux_map=None, compact=False, filt=None):
     """Whole scan -> one dict of columns in row order (test/inspection helper; the product API is batch-wise).
     index = index file bytes; with it, regions = list of region strings, or contigs = (tid_lo, tid_hi) / True."""
-    with BamFile(ctx, data) as bf:
+    with (BamFile.open_file(ctx, data) if isinstance(data, str) else BamFile(ctx, data)) as bf:
         bf.set_projection(col_mask, tags)
         if aux_map is not None:          # aux_map = iterable of excluded tags (may be empty)
             bf.set_aux_map(True, aux_map)

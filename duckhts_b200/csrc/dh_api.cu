@@ -32,8 +32,10 @@ int cuda_fail(cudaError_t e, const char *what) {
 
 int DevBuf::reserve(size_t n) {
     if (n <= cap) return DH_OK;
+    // growing means cudaFree + cudaMalloc (a device-wide synchronisation): leave room, sizes of successive batches creep up
+    const bool regrow = cap != 0;
     release();
-    size_t want = std::max(n, (size_t)1 << 20);
+    size_t want = std::max(regrow ? n + n / 4 : n, (size_t)1 << 20);
     cudaError_t e = cudaMalloc(&p, want);
     if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMalloc"); }
     cap = want;
@@ -46,8 +48,9 @@ void DevBuf::release() {
 }
 int PinBuf::reserve(size_t n) {
     if (n <= cap) return DH_OK;
+    const bool regrow = cap != 0;
     release();
-    size_t want = std::max(n, (size_t)1 << 16);
+    size_t want = std::max(regrow ? n + n / 4 : n, (size_t)1 << 16);
     cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocPortable);
     if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaHostAlloc"); }
     cap = want;

@@ -7,9 +7,13 @@
 // decoded and two being uploaded/inflated ahead) and up to five batches are in flight, so the D2H copy engine --
 // the binding resource when every column returns to the host -- never waits for a kernel.  Everything the host
 // does per segment is O(#BGZF blocks) bookkeeping; no record or byte of payload is touched on the CPU.
+#include <errno.h>
+#include <fcntl.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <deque>
@@ -269,6 +273,111 @@ int free_slots(const dh_bam *b) {
     return n;
 }
 
+// pread of one big range by a few threads (one thread moves page-cache bytes at a fraction of the PCIe rate)
+bool read_range(int fd, uint8_t *buf, uint64_t n, uint64_t off) {
+    if (n == 0) return true;
+    const int nt = (int)std::min<uint64_t>(8, (n + (32ull << 20) - 1) / (32ull << 20));
+    std::vector<int> ok((size_t)nt, 1);
+    auto work = [&](int t) {
+        uint64_t lo = n * (uint64_t)t / (uint64_t)nt, hi = n * (uint64_t)(t + 1) / (uint64_t)nt;
+        while (lo < hi) {
+            const ssize_t k = pread(fd, buf + lo, (size_t)std::min<uint64_t>(hi - lo, 64ull << 20), (off_t)(off + lo));
+            if (k < 0 && errno == EINTR) continue;
+            if (k <= 0) { ok[(size_t)t] = 0; return; }
+            lo += (uint64_t)k;
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    for (int v : ok) if (!v) return false;
+    return true;
+}
+
+// File mode: read and frame the next segment (rows A1 / A3 as bytes arrive: htslib's framing-only reader thread, bgzf.c:1485-1539,
+// does the same ahead of its inflate workers).  Appends the segment's blocks to the table and the segment to b->segs; sets
+// b->frame_done when nothing is left for this scan.  The compressed bytes stay in a pinned staging buffer until issue_inflate copies
+// them to the device; two buffers alternate, so reading segment k + 1 overlaps the copy of segment k.
+int frame_segment(dh_bam *b) {
+    if (b->frame_done) return DH_OK;
+    BlockTable &bt = b->bt;
+    const int k = (int)b->segs.size(), st = k & 1;
+    if (b->frame_pos >= b->fsize) { b->frame_done = true; return DH_OK; }
+    if (!b->ev_stage[st]) DH_CUDA(cudaEventCreate(&b->ev_stage[st]));
+    if (b->stage_used[st]) DH_CUDA(cudaEventSynchronize(b->ev_stage[st]));   // segment k - 2 has left this buffer
+    const uint64_t cbase = b->frame_pos & ~15ull;
+    const uint64_t want = std::min<uint64_t>(b->seg_comp + (b->frame_pos - cbase), b->fsize - cbase);
+    int rc = b->stage[st].reserve(b->seg_comp + 64);
+    if (rc != DH_OK) return rc;
+    uint8_t *buf = (uint8_t *)b->stage[st].p;
+    if (!read_range(b->fd, buf, want, cbase)) { set_error("read: %s", strerror(errno)); return DH_EIO; }
+    b->stage_used[st] = true;
+    const size_t b0 = bt.blocks.size();
+    uint64_t off = b->frame_pos - cbase, u = bt.uoff.back();
+    const uint64_t u0 = u;
+    bool broken = false;
+    while (off < want) {
+        if (want - off < 18) break;
+        const uint8_t *h = buf + off;
+        const bool ok = h[0] == 31 && h[1] == 139 && h[2] == 8 && (h[3] & 4) && (h[10] | (h[11] << 8)) == 6 && h[12] == 'B' && h[13] == 'C' && (h[14] | (h[15] << 8)) == 2;
+        if (!ok) { broken = true; break; }
+        const uint32_t bsize = (uint32_t)(h[16] | (h[17] << 8)) + 1;
+        if (bsize < 18 + 8) { broken = true; break; }
+        if (want - off < bsize) break;                       // continues in the next segment (or is cut by the end of the file)
+        dh_bgzf_block B;
+        B.coffset = cbase + off;
+        B.csize = bsize;
+        const uint8_t *f = h + bsize - 8;
+        B.crc = (uint32_t)f[0] | ((uint32_t)f[1] << 8) | ((uint32_t)f[2] << 16) | ((uint32_t)f[3] << 24);
+        B.isize = (uint32_t)f[4] | ((uint32_t)f[5] << 8) | ((uint32_t)f[6] << 16) | ((uint32_t)f[7] << 24);
+        B.reserved = 0;
+        if (B.isize > BGZF_MAX_OUT) { broken = true; break; }
+        if (bt.blocks.size() - b0 >= (1u << 17) || u + B.isize - u0 > (3ull << 30)) break;
+        // range scans stop framing once the look-ahead behind the range end is in the table
+        if (b->limit_blk != SIZE_MAX && bt.blocks.size() >= b->end_blk && u - bt.uoff[b->limit_blk] >= b->carry_cap) { b->frame_done = true; break; }
+        bt.blocks.push_back(B);
+        u += B.isize;
+        bt.uoff.push_back(u);
+        bt.eof_marker = (bsize == 28 && B.isize == 0);
+        if (b->limit_coff != UINT64_MAX && b->limit_blk == SIZE_MAX && B.coffset >= b->limit_coff) {
+            // the block the range ends in (bgzf_tell's "end of block k" = start of block k + 1; empty blocks are skipped the same way)
+            size_t lb = bt.blocks.size() - 1;
+            uint32_t lo = B.coffset == b->limit_coff ? b->limit_uoff : 0;
+            if (lo >= B.isize) { lb += 1; lo = 0; }           // resolved when that block is framed: limit_off 0 of the next block
+            b->limit_blk = lb;
+            b->limit_off = lo;
+            b->end_blk = lb + (lo ? 1 : 0) + 2;
+        }
+        off += bsize;
+    }
+    const size_t b1 = bt.blocks.size();
+    bt.end_off = cbase + off;
+    if (b1 == b0) {
+        // nothing whole: a broken header, or a block cut by the end of the file (htslib reads what lies in front of it, then fails)
+        if (!b->frame_done && (broken || cbase + want >= b->fsize)) b->truncated = true;
+        else if (!b->frame_done) { set_error("internal: no BGZF block fits a segment"); return DH_EINVAL; }
+        b->frame_done = true;
+        return DH_OK;
+    }
+    Seg sg{b0, b1, st};
+    b->segs.push_back(sg);
+    b->frame_pos = cbase + off;
+    if (broken) { b->truncated = true; b->frame_done = true; }
+    if (b->frame_pos >= b->fsize) b->frame_done = true;
+    return DH_OK;
+}
+
+// does segment k exist?  (memory image: all segments are planned by begin_range; file mode: they are framed as the scan gets there)
+int ensure_seg(dh_bam *b, int k, bool &exists) {
+    while (b->fd >= 0 && (size_t)k >= b->segs.size() && !b->frame_done) {
+        const int rc = frame_segment(b);
+        if (rc != DH_OK) return rc;
+    }
+    exists = (size_t)k < b->segs.size();
+    return DH_OK;
+}
+
 // H2D + inflate of segment k into slot k % NSEG (asynchronous)
 int issue_inflate(dh_bam *b, int k) {
     SegSlot &s = b->ss[k % NSEG];
@@ -296,8 +405,11 @@ int issue_inflate(dh_bam *b, int k) {
     cudaStream_t sc = s_copy(b), si = s_inf(b);
     DH_CUDA(cudaStreamWaitEvent(sc, s.ev_inf1, 0));  // previous inflate from this comp buffer is done (no-op if never recorded)
     if (!staged) {
-        DH_CUDA(cudaMemcpyAsync(s.comp.p, b->data + s.cbase, cbytes, cudaMemcpyHostToDevice, sc));
+        // memory image: straight from the caller's (pinned) buffer; file mode: from the staging buffer frame_segment() filled
+        const uint8_t *src = b->fd >= 0 ? (const uint8_t *)b->stage[sg.stage].p : b->data + s.cbase;
+        DH_CUDA(cudaMemcpyAsync(s.comp.p, src, cbytes, cudaMemcpyHostToDevice, sc));
         DH_CUDA(cudaMemsetAsync((uint8_t *)s.comp.p + cbytes, 0, DH_COMP_PAD, sc));
+        if (b->fd >= 0) DH_CUDA(cudaEventRecord(b->ev_stage[sg.stage], sc));   // the staging buffer may be refilled once this copy is done
     }
     DH_CUDA(cudaMemcpyAsync(s.desc.p, s.h_desc.p, nblk * sizeof(BlockDesc), cudaMemcpyHostToDevice, sc));
     DH_CUDA(cudaEventRecord(s.ev_h2d, sc));
@@ -354,7 +466,9 @@ int walk_segment(dh_bam *b, int k) {
     he[0] = -b->carry;                       // the carried record starts exactly there
     if (first_seg) { he[0] = b->first_entry; he[1] = b->first_entry; }   // scan start is a known record boundary
     else if (b->carry == 0) he[1] = 0;       // previous segment ended exactly on a record boundary
-    const bool is_final = b->to_eof && s.b1 == bt.blocks.size();
+    bool has_next = false;
+    if ((rc = ensure_seg(b, k + 1, has_next)) != DH_OK) return rc;
+    const bool is_final = b->to_eof && !has_next && (b->fd >= 0 || s.b1 == bt.blocks.size());
     int64_t limit_end = INT64_MAX;
     if (!b->to_eof && b->limit_blk < s.b1) {
         limit_end = b->limit_blk >= s.b0 ? (int64_t)(bt.uoff[b->limit_blk] - bt.uoff[s.b0]) + b->limit_off : 0;
@@ -483,7 +597,7 @@ int walk_segment(dh_bam *b, int k) {
                       (unsigned long long)b->carry_cap);
             return DH_ENOMEM;
         }
-        if ((size_t)k + 1 >= b->segs.size()) {
+        if (!has_next) {
             // range scan whose last record runs past the inflated look-ahead (carry_cap bytes behind the range end)
             set_error("the record at the end of the scan range is longer than the %llu-byte look-ahead: raise the carry buffer (dh_bam_configure)",
                       (unsigned long long)b->carry_cap);
@@ -491,7 +605,7 @@ int walk_segment(dh_bam *b, int k) {
         }
     } else {
         b->st.end_voffset = voff_of(lw.exit_off);
-        if ((size_t)k + 1 >= b->segs.size()) {
+        if (!has_next) {
             b->chain_done = true;
             // behind the last good block of a truncated image htslib's next read fails (bam_read1: bgzf_read != 4 and != 0 -> -2)
             if (b->truncated && is_final && b->final_status == 0) b->final_status = -2;
@@ -617,8 +731,11 @@ int have_work(dh_bam *b) {
         if (b->cur_seg >= 0 && b->next_batch_i < b->batches.size()) return 1;
         if (b->chain_done) return 0;
         int k = b->cur_seg + 1;
-        if ((size_t)k >= b->segs.size()) { b->chain_done = true; return 0; }
-        int rc = issue_inflate(b, k);  // no-op when prefetched
+        bool exists = false;
+        int rc = ensure_seg(b, k, exists);
+        if (rc != DH_OK) return rc;
+        if (!exists) { b->chain_done = true; return 0; }
+        rc = issue_inflate(b, k);  // no-op when prefetched
         if (rc != DH_OK) return rc;
         b->cur_seg = k;
         if ((rc = walk_segment(b, k)) != DH_OK) return rc;
@@ -626,8 +743,11 @@ int have_work(dh_bam *b) {
         // the decode stream.  Its slot is the one segment k+2 will be inflated into.
         if (k >= 1) DH_CUDA(cudaEventRecord(b->ss[(k - 1) % NSEG].ev_free, s_comp(b)));
         // prefetch: H2D + inflate of the next two segments overlap this segment's decode batches and their D2H copies
-        for (int a = 1; a < NSEG && !b->chain_done; ++a)
-            if ((size_t)(k + a) < b->segs.size() && (rc = issue_inflate(b, k + a)) != DH_OK) return rc;
+        // (file mode reads ahead through two staging buffers: one segment beyond the one being decoded)
+        for (int a = 1; a < (b->fd >= 0 ? 2 : NSEG) && !b->chain_done; ++a) {
+            if ((rc = ensure_seg(b, k + a, exists)) != DH_OK) return rc;
+            if (exists && (rc = issue_inflate(b, k + a)) != DH_OK) return rc;
+        }
     }
 }
 
@@ -662,10 +782,68 @@ dh_bam *dh_bam_open(dh_ctx *ctx, const uint8_t *data, uint64_t size) {
     return b;
 }
 
+dh_bam *dh_bam_open_file(dh_ctx *ctx, const char *path) {
+    if (!ctx || !path) { set_error("dh_bam_open_file: bad arguments"); return nullptr; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return nullptr; }
+    const int fd = open(path, O_RDONLY);
+    struct stat sb;
+    if (fd < 0 || fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode)) {
+        set_error("cannot open %s: %s", path, strerror(errno));
+        if (fd >= 0) close(fd);
+        return nullptr;
+    }
+    dh_bam *b = new dh_bam();
+    b->ctx = ctx;
+    b->fd = fd;
+    b->fsize = (uint64_t)sb.st_size;
+    b->size = b->fsize;
+    b->seg_comp = 512ull << 20;      // two pinned staging buffers of this size; the file itself is never pinned
+    memset(&b->st, 0, sizeof b->st);
+    // the header: the leading bytes of the file, more of them until the header blocks are all there (a 20,000-contig header is ~1 MB)
+    uint64_t take = std::min<uint64_t>(b->fsize, 4ull << 20);
+    for (;;) {
+        b->head.resize((size_t)take);
+        if (!read_range(fd, b->head.data(), take, 0)) { set_error("read: %s", strerror(errno)); dh_bam_close(b); return nullptr; }
+        b->bt = BlockTable();
+        uint64_t bad = 0;
+        const int wrc = walk_blocks(b->head.data(), take, 0, b->bt, &bad);
+        if (wrc != DH_OK) b->bt.end_off = bad;              // a block cut by the end of what was read (or a broken one): the blocks in front count
+        if (b->bt.blocks.empty()) {
+            set_error(b->fsize ? "invalid BGZF header at offset 0" : "empty file");
+            dh_bam_close(b);
+            return nullptr;
+        }
+        b->data = b->head.data();
+        {   // not a BAM at all?  say so now instead of reading more and more of a file that will never parse
+            const dh_bgzf_block &B0 = b->bt.blocks[0];
+            std::vector<uint8_t> u0((size_t)B0.isize + 8);
+            uint64_t n0 = 0;
+            if (dh_bgzf_inflate_host(ctx, b->head.data(), B0.csize, u0.data(), u0.size(), &n0, nullptr) != DH_OK || (n0 >= 4 && memcmp(u0.data(), "BAM\1", 4) != 0)) {
+                set_error("invalid BAM binary header");
+                b->data = nullptr;
+                dh_bam_close(b);
+                return nullptr;
+            }
+        }
+        const int prc = parse_header(b);
+        b->data = nullptr;
+        if (prc == DH_OK && b->first_blk < b->bt.blocks.size()) break;
+        if (prc == DH_OK && take >= b->fsize) break;        // header only, no alignment block behind it
+        if (take >= b->fsize) { if (prc == DH_OK) break; dh_bam_close(b); return nullptr; }
+        take = std::min<uint64_t>(b->fsize, take * 4);      // the header (or the block of the first record) continues behind what was read
+    }
+    b->first_voff = b->first_blk < b->bt.blocks.size() ? ((b->bt.blocks[b->first_blk].coffset << 16) | b->first_off) : (b->bt.end_off << 16);
+    build_dictionaries(b);
+    if (ensure_events(b) != DH_OK || upload_tables(b) != DH_OK) { dh_bam_close(b); return nullptr; }
+    return b;
+}
+
 void dh_bam_close(dh_bam *b) {
     if (!b) return;
     cudaSetDevice(b->ctx->device);
     cudaDeviceSynchronize();
+    if (b->fd >= 0) close(b->fd);
+    for (int i = 0; i < 2; ++i) { b->stage[i].release(); if (b->ev_stage[i]) cudaEventDestroy(b->ev_stage[i]); }
     for (auto &s : b->ss) {
         s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release(); s.rec.release();
         s.h_desc.release(); s.h_status.release(); s.h_blk_start.release(); s.h_entry.release(); s.h_todo.release();
@@ -698,6 +876,7 @@ const char *dh_bam_header_text(const dh_bam *b, uint32_t *len) {
 }
 uint64_t dh_bam_first_voffset(const dh_bam *b) {
     if (!b) return 0;
+    if (b->fd >= 0) return b->first_voff;
     if (b->first_blk >= b->bt.blocks.size()) return b->bt.end_off << 16;
     return (b->bt.blocks[b->first_blk].coffset << 16) | b->first_off;
 }
@@ -755,6 +934,7 @@ int dh_bam_configure(dh_bam *b, uint64_t seg_comp_bytes, uint32_t batch_rows, ui
 int dh_bam_set_mode(dh_bam *b, uint32_t flags) {
     if (!b) return DH_EINVAL;
     DH_CUDA(cudaSetDevice(b->ctx->device));
+    if ((flags & DH_BAM_DEVICE_INPUT) && b->fd >= 0) { set_error("DH_BAM_DEVICE_INPUT needs a memory image (dh_bam_open), not a file handle"); return DH_EINVAL; }
     if ((flags & DH_BAM_DEVICE_INPUT) && !b->d_image.p) {
         int rc = b->d_image.reserve(b->bt.end_off + DH_COMP_PAD + 16);
         if (rc != DH_OK) return rc;
@@ -798,6 +978,12 @@ dh_bam *dh_bam_clone(const dh_bam *src, dh_ctx *ctx) {
     b->ctx = ctx;
     b->data = src->data;
     b->size = src->size;
+    if (src->fd >= 0) {      // file mode: an own descriptor (own file position is not needed: pread), the header as parsed
+        b->fd = dup(src->fd);
+        if (b->fd < 0) { set_error("dup: %s", strerror(errno)); delete b; return nullptr; }
+        b->fsize = src->fsize;
+        b->first_voff = src->first_voff;
+    }
     b->bt = src->bt;
     b->text = src->text;
     b->ref_names = src->ref_names;
@@ -837,6 +1023,46 @@ static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fre
     // drop whatever an abandoned scan left in flight (this context's streams only: other contexts may share the device)
     DH_CUDA(cudaStreamSynchronize(b->ctx->stream));
     for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(b->ctx->copy_streams[i]));
+    if (b->fd >= 0) {
+        // file mode: the block table restarts at the block the range begins in and grows as segments are read (frame_segment)
+        const uint64_t vb = voff_beg ? voff_beg : b->first_voff;
+        BlockTable &t = b->bt;
+        t.blocks.clear();
+        t.uoff.assign(1, 0);
+        t.end_off = vb >> 16;
+        t.eof_marker = false;
+        b->frame_pos = vb >> 16;
+        b->frame_done = b->frame_pos >= b->fsize;
+        b->truncated = false;
+        b->to_eof = voff_end == UINT64_MAX || (voff_end >> 16) >= b->fsize;
+        b->limit_coff = b->to_eof ? UINT64_MAX : (voff_end >> 16);
+        b->limit_uoff = (uint32_t)(voff_end & 0xffff);
+        b->limit_blk = SIZE_MAX;
+        b->limit_off = 0;
+        b->end_blk = SIZE_MAX;
+        b->segs.clear();
+        for (auto &s : b->ss) s.issued_for = -1;
+        b->first_entry = (int64_t)(vb & 0xffff);     // "end of block k" chains into block k + 1 by itself (the walk starts nothing in k)
+        b->cur_seg = -1;
+        b->batches.clear();
+        b->next_batch_i = 0;
+        b->inflight.clear();
+        b->issued = b->returned = 0;
+        b->carry = 0;
+        b->chain_done = b->frame_done;
+        if (fresh) {
+            for (auto &o : b->bs) o.state = SLOT_FREE;
+            b->auto_slot = -1;
+            b->rows_total = 0;
+            b->final_status = 0;
+            memset(&b->st, 0, sizeof b->st);
+            b->st.end_voffset = vb;
+            if (!b->ev_scan0) DH_CUDA(cudaEventCreate(&b->ev_scan0));
+            DH_CUDA(cudaEventRecord(b->ev_scan0, s_comp(b)));
+        }
+        b->scanning = true;
+        return DH_OK;
+    }
     const BlockTable &bt = b->bt;
     const size_t nb = bt.blocks.size();
     size_t b_first = b->first_blk;
@@ -1054,9 +1280,12 @@ int dh_bam_prefetch(dh_bam *b) {
     // uploads + inflate of the first segments are enqueued (asynchronous); the boundary walk, which needs their result on the
     // host, is left to the first acquire
     if (b->cur_seg != -1 || b->chain_done) return DH_OK;
-    for (int k = 0; k < NSEG && (size_t)k < b->segs.size(); ++k) {
-        const int rc = issue_inflate(b, k);
+    for (int k = 0; k < (b->fd >= 0 ? 2 : NSEG); ++k) {
+        bool exists = false;
+        int rc = ensure_seg(b, k, exists);
+        if (rc == DH_OK && exists) rc = issue_inflate(b, k);
         if (rc != DH_OK) { b->scanning = false; return rc; }
+        if (!exists) break;
     }
     return DH_OK;
 }
@@ -1219,17 +1448,33 @@ int dh_bam_scan_stats_get(const dh_bam *b, dh_bam_scan_stats *out) {
     return DH_OK;
 }
 
-// Does a record start at offset 0 of block `blk`?  htslib starts a block at a record boundary whenever the next record does not fit
-// the current one (bgzf_flush_try, htslib/sam.c:883), but the blocks behind a record longer than a block start in the middle of it,
-// and foreign writers cut anywhere (htslib/test/bgzf_boundaries).  The block is inflated (GPU) and its records are chained on the
-// host: every header must be plausible and the chain must end exactly at the block end or run past it with its last record.
-static bool block_starts_a_record(const dh_bam *b, size_t blk) {
-    const BlockTable &bt = b->bt;
-    const dh_bgzf_block &B = bt.blocks[blk];
-    if (B.isize < 36) return false;
-    std::vector<uint8_t> u((size_t)B.isize + 8);
+// compressed bytes [off, off + n) of the image, wherever it lives
+static bool fetch_bytes(const dh_bam *b, uint64_t off, uint64_t n, std::vector<uint8_t> &out) {
+    if (off > b->size || n > b->size - off) return false;
+    out.resize((size_t)n);
+    if (b->fd < 0) { memcpy(out.data(), b->data + off, (size_t)n); return true; }
+    return read_range(b->fd, out.data(), n, off);
+}
+static inline bool hdr_ok(const uint8_t *h) {
+    return h[0] == 31 && h[1] == 139 && h[2] == 8 && (h[3] & 4) && (h[10] | (h[11] << 8)) == 6 && h[12] == 'B' && h[13] == 'C' && (h[14] | (h[15] << 8)) == 2;
+}
+
+// Does a record start at offset 0 of the BGZF block at file offset `coff`?  htslib starts a block at a record boundary whenever the
+// next record does not fit the current one (bgzf_flush_try, htslib/sam.c:883), but the blocks behind a record longer than a block
+// start in the middle of it, and foreign writers cut anywhere (htslib/test/bgzf_boundaries).  The block is inflated (GPU) and its
+// records are chained on the host: every header must be plausible and the chain must end exactly at the block end or run past it
+// with its last record.  *csize_out = the block's size.
+static bool block_starts_a_record(const dh_bam *b, uint64_t coff, uint32_t *csize_out) {
+    std::vector<uint8_t> c;
+    if (!fetch_bytes(b, coff, std::min<uint64_t>(65536, b->size - coff), c) || c.size() < 26 || !hdr_ok(c.data())) return false;
+    const uint32_t csize = (uint32_t)(c[16] | (c[17] << 8)) + 1;
+    if (csize < 26 || csize > c.size()) return false;
+    if (csize_out) *csize_out = csize;
+    const uint32_t isize = (uint32_t)c[csize - 4] | ((uint32_t)c[csize - 3] << 8) | ((uint32_t)c[csize - 2] << 16) | ((uint32_t)c[csize - 1] << 24);
+    if (isize < 36 || isize > BGZF_MAX_OUT) return false;
+    std::vector<uint8_t> u((size_t)isize + 8);
     uint64_t n = 0;
-    if (dh_bgzf_inflate_host(b->ctx, b->data + B.coffset, B.csize, u.data(), u.size(), &n, nullptr) != DH_OK || n != B.isize) return false;
+    if (dh_bgzf_inflate_host(b->ctx, c.data(), csize, u.data(), u.size(), &n, nullptr) != DH_OK || n != isize) return false;
     const int32_t n_ref = (int32_t)b->ref_names.size();
     auto le32 = [&](uint64_t p) { return (uint32_t)u[p] | ((uint32_t)u[p + 1] << 8) | ((uint32_t)u[p + 2] << 16) | ((uint32_t)u[p + 3] << 24); };
     uint64_t off = 0;
@@ -1250,31 +1495,65 @@ static bool block_starts_a_record(const dh_bam *b, size_t blk) {
     return seen > 0 && off >= n;      // off < n: fewer than 36 bytes left that are no record header
 }
 
+// file offset of the first BGZF block at or behind `target` (north-star item (a): the BSIZE chain cannot be entered in the middle,
+// so a candidate is every offset that carries the 16 fixed header bytes and whose chain of BSIZE fields meets two more such headers
+// or the end of the file); UINT64_MAX if there is none in the next 256 KB
+static uint64_t find_block_at_or_after(const dh_bam *b, uint64_t target) {
+    if (b->fd < 0) {
+        const size_t blk = block_of(b, target);
+        return blk < b->bt.blocks.size() ? b->bt.blocks[blk].coffset : UINT64_MAX;
+    }
+    std::vector<uint8_t> w;
+    const uint64_t n = std::min<uint64_t>(256u << 10, b->size - std::min(target, b->size));
+    if (n < 28 || !fetch_bytes(b, target, n, w)) return UINT64_MAX;
+    for (uint64_t o = 0; o + 28 <= n; ++o) {
+        if (!hdr_ok(w.data() + o)) continue;
+        uint64_t q = o;
+        int ok = 0;
+        for (int hop = 0; hop < 3; ++hop) {
+            const uint64_t bs = (uint64_t)(w[q + 16] | (w[q + 17] << 8)) + 1;
+            if (bs < 26) break;
+            q += bs;
+            if (target + q == b->size) { ok = 3; break; }              // the chain ends exactly at the end of the file
+            if (q + 18 > n) { ok = hop + 1 >= 2 ? 3 : ok; break; }      // ran out of window after at least two good hops
+            if (!hdr_ok(w.data() + q)) break;
+            ok = hop + 1;
+        }
+        if (ok >= 2) return target + o;
+    }
+    return UINT64_MAX;
+}
+
 int dh_bam_split(const dh_bam *b, int n_parts, uint64_t *voffs) {
     if (!b || n_parts < 1 || !voffs) { set_error("dh_bam_split: bad arguments"); return DH_EINVAL; }
     std::lock_guard<std::mutex> lk(b->mu);
     if (cudaSetDevice(b->ctx->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return DH_ECUDA; }
-    const BlockTable &bt = b->bt;
-    const size_t nb = bt.blocks.size();
     voffs[0] = dh_bam_first_voffset(b);
+    const uint64_t end = b->fd >= 0 ? b->fsize : b->bt.end_off;
     // the block holding the first record stays whole in part 0; cut the rest by compressed bytes
-    size_t lo = std::min(nb, b->first_blk + (b->first_off ? 1 : 0));
-    const uint64_t c0 = lo < nb ? bt.blocks[lo].coffset : bt.end_off, c1 = bt.end_off;
-    size_t prev = lo;
+    uint64_t c0 = std::min(end, voffs[0] >> 16);
+    if (voffs[0] & 0xffff) {      // first record in the middle of a block: cuts start behind that block
+        uint32_t cs = 0;
+        std::vector<uint8_t> h;
+        if (fetch_bytes(b, c0, std::min<uint64_t>(18, end - c0), h) && h.size() == 18 && hdr_ok(h.data())) cs = (uint32_t)(h[16] | (h[17] << 8)) + 1;
+        c0 = std::min(end, c0 + cs);
+    }
+    uint64_t prev = c0;
     bool collapsed = false;
     for (int p = 1; p < n_parts; ++p) {
-        uint64_t target = c0 + (c1 - c0) * (uint64_t)p / (uint64_t)n_parts;
-        size_t blk = std::max(block_of(b, target), prev);
+        const uint64_t target = std::max(prev, c0 + (end - c0) * (uint64_t)p / (uint64_t)n_parts);
         // a cut must be a record boundary: move on to the next block that verifiably starts one (a few tries: the blocks behind a long
         // read); a file whose blocks do not start records at all (foreign writer) is not cut: part 0 gets everything
-        int tries = 0;
-        while (!collapsed && blk < nb && bt.blocks[blk].isize > 0 && !block_starts_a_record(b, blk)) {
-            ++blk;
-            if (++tries >= 64) collapsed = true;
+        uint64_t coff = collapsed ? UINT64_MAX : find_block_at_or_after(b, target);
+        for (int tries = 0; coff != UINT64_MAX && coff < end; ++tries) {
+            uint32_t cs = 0;
+            if (block_starts_a_record(b, coff, &cs)) break;
+            if (cs == 0 || tries >= 64) { collapsed = true; coff = UINT64_MAX; break; }
+            coff += cs;                                                // the next block of the chain
+            if (coff + 28 > end) coff = UINT64_MAX;                    // only the EOF marker (or nothing) is left
         }
-        while (!collapsed && blk < nb && bt.blocks[blk].isize == 0) ++blk;    // empty blocks (EOF marker) hold no record
-        voffs[p] = (collapsed || blk >= nb) ? UINT64_MAX : (bt.blocks[blk].coffset << 16);
-        prev = std::min(blk, nb);
+        voffs[p] = (collapsed || coff == UINT64_MAX || coff >= end) ? UINT64_MAX : (coff << 16);
+        if (voffs[p] != UINT64_MAX) prev = coff;
     }
     voffs[n_parts] = UINT64_MAX;
     return DH_OK;

@@ -47,7 +47,7 @@ struct BatchSlot {
     int state = SLOT_FREE;
 };
 
-struct Seg { size_t b0, b1; };
+struct Seg { size_t b0, b1; int stage = -1; };   // stage: file mode, which pinned staging buffer holds the segment's compressed bytes
 
 }  // namespace dh
 
@@ -60,6 +60,20 @@ struct dh_bam {
     dh_ctx *ctx = nullptr;
     const uint8_t *data = nullptr;
     uint64_t size = 0;
+    // file mode (dh_bam_open_file): the image is never held whole; segments are read into two pinned staging buffers by parallel
+    // pread and framed (A1) as they arrive, so the block table grows with the scan.  The table is one contiguous run of blocks
+    // starting at bt.blocks[0].coffset (the header blocks, or the first block of the range being scanned).
+    int fd = -1;
+    uint64_t fsize = 0;
+    uint64_t frame_pos = 0;        // file offset of the first block not framed yet
+    bool frame_done = false;       // nothing more to frame for this scan (end of file, broken block, or past the range end)
+    uint64_t limit_coff = UINT64_MAX;   // file mode: block address and in-block offset of the range end (UINT64_MAX: to EOF)
+    uint32_t limit_uoff = 0;
+    uint64_t first_voff = 0;       // virtual offset of the first alignment record
+    std::vector<uint8_t> head;     // file mode: the leading bytes that hold the header blocks
+    PinBuf stage[2];
+    cudaEvent_t ev_stage[2] = {nullptr, nullptr};   // the last host-to-device copy out of each staging buffer
+    bool stage_used[2] = {false, false};
     BlockTable bt;
     bool truncated = false;        // the image ends in a broken / cut block: the scan returns what lies in front of it, then status -2
     // header

@@ -30,6 +30,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/stat.h>
+#include <time.h>
 #include <unistd.h>
 
 #include "duckdb_ext_abi.h"
@@ -265,10 +266,17 @@ typedef struct {
     int n_rg;
     int next_worker;         /* atomic */
     int cancel_from;         /* atomic: sources >= this are not read (an earlier one ended in an error / invalid record) */
+    char *deferred_err;      /* a scan that could not start: reported by local init, where the reference finds it (bam_reader.c:601-671) */
+    /* DUCKHTS_PROFILE=1: where the scan threads spend their time (nanoseconds, summed over threads; printed when the scan is freed) */
+    int profile;
+    uint64_t ns_lock, ns_acquire, ns_fill, n_chunks, n_acquire, n_busy;
+    double t_init;
     char type_of[DH_BAM_MAX_COLS];               /* per batch column: tag type letter, 0 for core columns */
 } bam_global_t;
 
 typedef struct { int worker; } bam_local_t;
+
+static bam_global_t *g_last_bam_global;   /* the scan whose local inits follow (the stable API gives local init no handle on the global state) */
 
 static void bam_bind_free(void *p) {
     bam_bind_t *b = (bam_bind_t *)p;
@@ -285,9 +293,18 @@ static void bam_release_ref(bam_source_t *s, bam_batch_ref *br) {
     dh_bam_release_batch(s->bam, br->b.slot);
     free(br);
 }
+static double now_sec(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + ts.tv_nsec * 1e-9; }
+static inline uint64_t now_ns(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec; }
 static void bam_global_free(void *p) {
     bam_global_t *g = (bam_global_t *)p;
     if (!g) return;
+    bam_global_t *expect = g;
+    __atomic_compare_exchange_n(&g_last_bam_global, &expect, NULL, 0, __ATOMIC_ACQ_REL, __ATOMIC_ACQUIRE);
+    if (g->profile)
+        fprintf(stderr, "[duckhts profile] read_bam: %d source(s), %s layout, %llu chunks, %llu batches (%llu busy waits); thread-seconds: lock wait %.3f, acquire %.3f, fill %.3f; "
+                "wall since init %.3f s\n", g->n_src, g->compact ? "compact" : "duckdb", (unsigned long long)g->n_chunks, (unsigned long long)g->n_acquire,
+                (unsigned long long)g->n_busy, g->ns_lock * 1e-9, g->ns_acquire * 1e-9, g->ns_fill * 1e-9, now_sec() - g->t_init);
+    free(g->deferred_err);
     for (int i = 0; i < g->n_src; ++i) {
         bam_source_t *s = &g->src[i];
         if (s->cur) { free(s->cur); s->cur = NULL; }     /* the handle forgets its held slots at the next scan / close */
@@ -318,9 +335,11 @@ static void read_bam_bind(duckdb_bind_info info) {
     b->ctx = dh_ctx_create(devs[0]);
     if (!b->ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
     else {
-        b->image = slurp_pinned(path, &b->size);
-        if (!b->image) snprintf(err, sizeof err, "Failed to open SAM/BAM/CRAM file: %s", path);
-        else if (!(b->bam = dh_bam_open(b->ctx, b->image, b->size))) snprintf(err, sizeof err, "Failed to read SAM/BAM/CRAM header");
+        /* streamed: only the header blocks are read here; the scan reads the file segment by segment (dh_bam_open_file) */
+        struct stat stt;
+        if (stat(path, &stt) != 0 || !S_ISREG(stt.st_mode) || access(path, R_OK) != 0) snprintf(err, sizeof err, "Failed to open SAM/BAM/CRAM file: %s", path);
+        else if (!(b->bam = dh_bam_open_file(b->ctx, path))) snprintf(err, sizeof err, "Failed to read SAM/BAM/CRAM header");
+        else b->size = (uint64_t)stt.st_size;
     }
     if (err[0]) {
         api.duckdb_bind_set_error(info, err);
@@ -386,6 +405,8 @@ static void read_bam_init(duckdb_init_info info) {
     memset(g, 0, sizeof *g);
     g->bind = b;
     g->cancel_from = MAX_SOURCES + 1;
+    g->profile = getenv("DUCKHTS_PROFILE") != NULL;
+    g->t_init = now_sec();
     g->n_proj = api.duckdb_init_get_column_count(info);
     g->col_ids = (idx_t *)calloc(g->n_proj ? g->n_proj : 1, sizeof(idx_t));
     g->abi_col = (int *)calloc(g->n_proj ? g->n_proj : 1, sizeof(int));
@@ -434,7 +455,7 @@ static void read_bam_init(duckdb_init_info info) {
         if (contig_mode && n_src > b->n_contigs) n_src = b->n_contigs;
     }
     const int n_slots = (int)env_u64("DUCKHTS_SLOTS", 8);
-    const uint32_t batch_rows = (uint32_t)env_u64("DUCKHTS_BATCH_ROWS", 256u << 10);
+    const uint32_t batch_rows = (uint32_t)env_u64("DUCKHTS_BATCH_ROWS", 128u << 10);
     int32_t tid_bounds[MAX_SOURCES + 1];
     uint64_t voffs[MAX_SOURCES + 1];
     if (n_src > 1) {
@@ -486,9 +507,9 @@ static void read_bam_init(duckdb_init_info info) {
     for (int i = 0; i < g->n_src && !err[0]; ++i)
         if (!g->src[i].done && dh_bam_prefetch(g->src[i].bam) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
     if (err[0]) {
-        api.duckdb_init_set_error(info, err);
-        bam_global_free(g);
-        return;
+        /* the reference meets these in local init, after DuckDB has the schema: keep the scan state, hand the message to the workers */
+        g->deferred_err = strdup(err);
+        for (int i = 0; i < g->n_src; ++i) g->src[i].done = 1;
     }
     /* compact layout: what the fillers need besides the batch */
     if (g->compact) {
@@ -518,11 +539,15 @@ static void read_bam_init(duckdb_init_info info) {
     }
     api.duckdb_init_set_max_threads(info, 64);
     api.duckdb_init_set_init_data(info, g, bam_global_free);
+    __atomic_store_n(&g_last_bam_global, g, __ATOMIC_RELEASE);
 }
 
 static void read_bam_local_init(duckdb_init_info info) {
+    bam_bind_t *b = (bam_bind_t *)api.duckdb_init_get_bind_data(info);
+    bam_global_t *g = __atomic_load_n(&g_last_bam_global, __ATOMIC_ACQUIRE);
+    if (g && g->bind == b && g->deferred_err) { api.duckdb_init_set_error(info, g->deferred_err); return; }
     bam_local_t *l = (bam_local_t *)api.duckdb_malloc(sizeof *l);
-    l->worker = -1;     /* numbered at the first scan call (the global state is not reachable from here in the stable API) */
+    l->worker = -1;     /* numbered at the first scan call */
     api.duckdb_init_set_init_data(info, l, api.duckdb_free);
 }
 
@@ -730,7 +755,9 @@ static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
         const int si = pick_source(g, l->worker);
         if (si < 0) { api.duckdb_data_chunk_set_size(output, 0); return; }
         bam_source_t *s = &g->src[si];
+        const uint64_t t_lock = g->profile ? now_ns() : 0;
         pthread_mutex_lock(&s->mu);
+        if (g->profile) __atomic_fetch_add(&g->ns_lock, now_ns() - t_lock, __ATOMIC_RELAXED);
         if (s->done) { pthread_mutex_unlock(&s->mu); continue; }
         if (!s->cur || s->cursor >= s->cur->b.n_rows) {
             if (s->cur) {   /* every row of it is claimed: it goes back when the last claim is filled */
@@ -739,7 +766,9 @@ static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
                 s->cur = NULL;
             }
             bam_batch_ref *br = (bam_batch_ref *)calloc(1, sizeof *br);
+            const uint64_t t_acq = g->profile ? now_ns() : 0;
             const int rc = dh_bam_acquire_batch(s->bam, &br->b);
+            if (g->profile) { __atomic_fetch_add(&g->ns_acquire, now_ns() - t_acq, __ATOMIC_RELAXED); __atomic_fetch_add(rc == DH_EBUSY ? &g->n_busy : &g->n_acquire, 1, __ATOMIC_RELAXED); }
             if (rc == 1) { s->cur = br; s->cursor = 0; }
             else {
                 free(br);
@@ -771,8 +800,10 @@ static void read_bam_scan(duckdb_function_info info, duckdb_data_chunk output) {
         br->refs++;
         pthread_mutex_unlock(&s->mu);
 
+        const uint64_t t_fill = g->profile ? now_ns() : 0;
         if (br->b.layout == DH_BAM_COMPACT_OUTPUT) fill_compact_layout(g, &br->b, r0, n, output);
         else fill_duckdb_layout(g, &br->b, r0, n, output);
+        if (g->profile) { __atomic_fetch_add(&g->ns_fill, now_ns() - t_fill, __ATOMIC_RELAXED); __atomic_fetch_add(&g->n_chunks, 1, __ATOMIC_RELAXED); }
 
         pthread_mutex_lock(&s->mu);
         if (--br->refs == 0 && br->closed) bam_release_ref(s, br);

@@ -124,6 +124,13 @@ typedef struct dh_bam dh_bam;
 /* Frames the image (A1), inflates the header blocks on the GPU and parses the BAM header on the host.
  * `data` must stay valid (and should be pinned, dh_host_alloc) until dh_bam_close.  NULL on error. */
 dh_bam *dh_bam_open(dh_ctx *ctx, const uint8_t *data, uint64_t size);
+/* The same on a FILE, streamed (north-star item (a); htslib never holds more than a block or two either, bgzf.c:1004-1239):
+ * only the header blocks are read here.  Scans read the file segment by segment with parallel pread into two pinned staging
+ * buffers (dh_bam_configure's seg_comp_bytes each, default 512 MiB), frame the BGZF blocks as the bytes arrive, and copy to the
+ * device from there; the first batch leaves before the file has been read, and pinned memory does not grow with the file.
+ * Everything else (projection, ranges, index scans, split, clone, batches) works as on a memory image; DH_BAM_DEVICE_INPUT
+ * does not apply. */
+dh_bam *dh_bam_open_file(dh_ctx *ctx, const char *path);
 void dh_bam_close(dh_bam *b);
 int32_t dh_bam_n_ref(const dh_bam *b);                       /* sam_hdr_nref */
 const char *dh_bam_ref_name(const dh_bam *b, int32_t tid);   /* sam_hdr_tid2name */

@@ -363,3 +363,64 @@ def test_long_record_at_a_range_end_is_finished_from_the_look_ahead(ctx):
         assert lo["status"] == 0 and hi["status"] == 0
         assert lo["n"] + hi["n"] == exp["n"], cut_blk
         assert lo["qname"] + hi["qname"] == orc.strcol_list(exp["qname"])
+
+
+# ---- streamed files (dh_bam_open_file): same rows as the memory image, whatever the segment size ---------------------------------
+def test_streamed_file_scans_match_the_memory_image(ctx, tmp_path):
+    path = util.synth_path("bam", n_records=120000, seed=21, paired=True, index=True)
+    img = np.fromfile(path, dtype=np.uint8)
+    exp = oracle_of(img, TAGS)
+    for kw in ({}, {"seg_comp": 1 << 16, "batch_rows": 777}, {"seg_comp": 1 << 20, "batch_rows": 50000, "compact": True}, {"seg_comp": 3 << 20}):
+        got = dh.bam_scan(ctx, path, tags=TAGS, **kw)
+        util.assert_bam_equal(got, exp)
+        assert got["ref_names"] == exp["ref_names"] and got["text"] == exp["text"]
+    # ranges of dh_bam_split on the file handle (block boundaries found by header search + record check), merged in order
+    with dh.BamFile.open_file(ctx, path) as bf, dh.BamFile(ctx, img) as mem:
+        assert bf.first_voffset == mem.first_voffset
+        for parts in (2, 5):
+            voffs = bf.split(parts)
+            assert voffs[0] == mem.first_voffset and voffs[-1] == dh.VOFF_MAX
+            assert all(a <= b for a, b in zip(voffs, voffs[1:]))
+            qn, total = [], 0
+            for p in range(parts):
+                if voffs[p] == dh.VOFF_MAX:
+                    continue
+                got = dh.bam_scan(ctx, path, tags=TAGS, voff=(voffs[p], voffs[p + 1]), seg_comp=1 << 18, compact=bool(p & 1))
+                assert got["status"] == 0
+                if voffs[p + 1] != dh.VOFF_MAX:
+                    assert got["stats"].end_voffset == voffs[p + 1]
+                qn += got["qname"]
+                total += got["n"]
+            assert total == exp["n"] and qn == orc.strcol_list(exp["qname"])
+    # index-driven scans on the file handle: regions and the contig mode
+    bai = np.fromfile(path + ".bai", dtype=np.uint8)
+    for regions in (["chr3:10,000,000-20,000,000"], ["chr2:1-5000000", "chr7:49000000-"]):
+        a = dh.bam_scan(ctx, path, tags=TAGS, index=bai, regions=regions, seg_comp=1 << 18)
+        m = dh.bam_scan(ctx, img, tags=TAGS, index=bai, regions=regions)
+        assert a["n"] == m["n"] > 0 and a["qname"] == m["qname"] and np.array_equal(a["pos"], m["pos"])
+    a = dh.bam_scan(ctx, path, tags=TAGS, index=bai, contigs=True, seg_comp=1 << 19)
+    m = dh.bam_scan(ctx, img, tags=TAGS, index=bai, contigs=True)
+    assert a["n"] == m["n"] == exp["n"] and a["qname"] == m["qname"]
+    # edge records, a header of several blocks, tiny files, records straddling blocks: written to disk, streamed back
+    stream = bam_header(REFS, TEXT) + b"".join(edge_records())
+    refs = [(b"contig_%05d" % i, 1000 + i) for i in range(20000)]
+    big_header = bam_header(refs, b"@CO\t" + b"x" * 200000 + b"\n") + bam_record(b"r", 0, 19999, 1, 1, [(1, "M")], seq="A", qual=[1])
+    for i, data in enumerate((util.make_bgzf(stream, block=4096), util.make_bgzf(stream, block=333), util.make_bgzf(big_header), util.make_bgzf(bam_header(REFS, TEXT)),
+                              util.make_bgzf(bam_header([], b"")))):
+        p = str(tmp_path / f"f{i}.bam")
+        open(p, "wb").write(data)
+        e = oracle_of(np.frombuffer(data, dtype=np.uint8), EDGE_TAGS)
+        util.assert_bam_equal(dh.bam_scan(ctx, p, tags=EDGE_TAGS, seg_comp=1 << 16, batch_rows=5), e)
+    # truncated on disk
+    blocks, _ = dh.bgzf_walk(img)
+    cut = blocks[len(blocks) // 2]
+    p = str(tmp_path / "cut.bam")
+    open(p, "wb").write(img[:cut[0] + cut[1] // 2].tobytes())
+    e = oracle_of(img[:cut[0]], TAGS)
+    got = dh.bam_scan(ctx, p, tags=TAGS, seg_comp=1 << 20)
+    assert got["n"] == e["n"] and got["status"] < 0 and got["qname"] == orc.strcol_list(e["qname"])
+    with pytest.raises(dh.DuckhtsError):
+        open(str(tmp_path / "x.bam"), "wb").write(b"not a BGZF file, not at all")
+        dh.bam_scan(ctx, str(tmp_path / "x.bam"))
+    with pytest.raises(dh.DuckhtsError):
+        dh.bam_scan(ctx, str(tmp_path / "missing.bam"))
