@@ -14,6 +14,16 @@ for stage in "$@"; do
     bench) timeout 1500 python bench.py --steps 3 --warmup 3 > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"; cat gpurun_out/${T}_bench.json; tail -5 gpurun_out/${T}_bench.err ;;
     ref) timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_reference_bench.json 2> gpurun_out/${T}_reference_bench.err; cat gpurun_out/${T}_reference_bench.json; tail -3 gpurun_out/${T}_reference_bench.err ;;
     ncu) bash tools/gpu_ncu1.sh ;;
+    extprof) # where the scan threads of the extension spend their time (DUCKHTS_PROFILE), on the bench unit, 1 / 4 / 16 threads, both layouts
+      U=$(python -c "import bench,os; print(bench.gen_unit('bam', 4000000, 0x9E3779B97F4A7C15, True, os.cpu_count()))")
+      for t in 1 4 16; do for lay in compact duckdb; do
+        DUCKHTS_LAYOUT=$lay DUCKHTS_PROFILE=1 harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam $U standard_tags=true --cols 0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14 --threads $t --time 2>&1 | sed "s/^/[$lay t=$t] /"
+      done; done > gpurun_out/${T}_extprof.log 2>&1; cat gpurun_out/${T}_extprof.log ;;
+    ab_resolve) # inflate phase 2: shared-memory kernel (default) against the global-memory one of round 1
+      for v in 4 3; do
+        if [ $v = 3 ]; then export DH_RESOLVE3=1; else unset DH_RESOLVE3; fi
+        timeout 600 python bench.py --steps 3 --warmup 2 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve$v', json.dumps({'value': d['value'], 'inflate': d['inflate'], 'e2e': d['e2e']['value']}))"
+      done > gpurun_out/${T}_ab_resolve.log 2>&1; unset DH_RESOLVE3; cat gpurun_out/${T}_ab_resolve.log ;;
     *) echo "unknown stage $stage" ;;
   esac
 done
