@@ -62,6 +62,7 @@ SIGNATURES = {
     "dh_version": (C.c_char_p, []),
     "dh_last_error": (C.c_char_p, []),
     "dh_device_count": (C.c_int, []),
+    "dh_trim": (None, []),
     "dh_ctx_create": (C.c_void_p, [C.c_int]),
     "dh_ctx_destroy": (None, [C.c_void_p]),
     "dh_ctx_sm_count": (C.c_int, [C.c_void_p]),

@@ -354,11 +354,13 @@ constexpr int BCF_MAX_FMT_COLS = 256;   // FORMAT columns a header may declare (
 constexpr int BCF_MAX_INFO_COLS = 1024;
 
 __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__ BcfDecodeParams p, const BcfTables t) {
-    __shared__ BRec r;
-    __shared__ FmtDesc fd[BCF_MAX_FMT];
-    __shared__ int16_t col2desc[BCF_MAX_FMT_COLS];
+    // Two copies of the per-record state: thread 0 parses record k + 1 and writes its site-level cells while warps 1..7 write the
+    // FORMAT cells of record k (r1: thread 0 did this with 255 threads waiting at the barrier).
+    __shared__ BRec r_s[2];
+    __shared__ FmtDesc fd_s[2][BCF_MAX_FMT];
+    __shared__ int16_t col2desc_s[2][BCF_MAX_FMT_COLS];
     __shared__ uint32_t seen[BCF_MAX_INFO_COLS / 32];
-    __shared__ uint64_t rec_base_s;
+    __shared__ uint64_t rec_base_s[2];
     const uint32_t bi = p.b_lo + blockIdx.x;
     if (bi >= p.b_hi) return;
     const uint32_t count = p.walk[bi].count;
@@ -369,12 +371,16 @@ __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__
     const uint32_t ns = t.n_samples, tid = threadIdx.x, lane = tid & 31u;
     uint64_t hp = p.heap_base[bi];   // thread 0 only
 
-    for (uint32_t k = 0; k < count; ++k) {
+    // site-level part of record k (thread 0): parse, core and INFO columns, FORMAT descriptors for the other warps
+    auto site_level = [&](const uint32_t k, const int q) {
+        BRec &r = r_s[q];
+        FmtDesc *fd = fd_s[q];
+        int16_t *col2desc = col2desc_s[q];
         const uint64_t R = (uint64_t)p.row_base[bi] + k;
-        if (tid == 0) {
+        {
             bcf_parse(u, bstart + rec[k], INT64_MAX / 2, true, t, r, fd);   // validated by the walk: cannot fail
             const uint64_t base = hp;
-            rec_base_s = base;
+            rec_base_s[q] = base;
             hp += r.need;
             for (int c = 0; c < t.n_fmt; ++c) col2desc[c] = -1;
             for (uint32_t i = 0; i < r.n_fmt; ++i) {
@@ -509,10 +515,23 @@ __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__
                 set_bit(val, R);
             }
         }
-        __syncthreads();
-        // ---------------- FORMAT columns: all threads over the samples (bcf_reader.c:1738-1998) ----------------
-        if (t.any_fmt && r.n_fmt) {
-            const uint64_t base = rec_base_s;
+    };
+
+    constexpr uint32_t WORKERS = 256u - 32u;       // warps 1..7
+    if (tid == 0) site_level(0, 0);
+    __syncthreads();
+    for (uint32_t k = 0; k < count; ++k) {
+        const uint64_t R = (uint64_t)p.row_base[bi] + k;
+        const int q = (int)(k & 1u);
+        const BRec &r = r_s[q];
+        const FmtDesc *fd = fd_s[q];
+        const int16_t *col2desc = col2desc_s[q];
+        if (tid < 32u) {
+            if (tid == 0 && k + 1 < count) site_level(k + 1, q ^ 1);
+        } else if (t.any_fmt && r.n_fmt) {
+            // ---------------- FORMAT columns: warps 1..7 over the samples (bcf_reader.c:1738-1998) ----------------
+            const uint32_t wtid = tid - 32u;
+            const uint64_t base = rec_base_s[q];
             for (int c = 0; c < t.n_fmt; ++c) {
                 if (!t.fmt_want[c]) continue;
                 const int di = col2desc[c];
@@ -522,8 +541,8 @@ __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__
                 const bool is_list = (meta & META_LIST) != 0, is_gt = (meta & META_GT) != 0;
                 uint8_t *col = p.fmt[c];
                 unsigned long long *val = p.fmt_valid[c];
-                for (uint32_t s0 = 0; s0 < ns; s0 += blockDim.x) {
-                    const uint32_t s = s0 + tid;
+                for (uint32_t s0 = 0; s0 < ns; s0 += WORKERS) {
+                    const uint32_t s = s0 + wtid;
                     const uint64_t row = R * ns + s;
                     bool valid = false;
                     if (s < ns) {
@@ -595,7 +614,7 @@ __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__
                         }
                     }
                     const uint32_t mask = __ballot_sync(0xffffffffu, valid);
-                    if (lane == 0) set_bits32(val, R * ns + (s0 + (tid & ~31u)), mask);
+                    if (lane == 0) set_bits32(val, R * ns + (s0 + (wtid & ~31u)), mask);
                 }
             }
         }

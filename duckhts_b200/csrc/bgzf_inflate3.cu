@@ -1147,8 +1147,10 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (between_phases && (e = cudaEventRecord(between_phases, stream)) != cudaSuccess) return e;
-    // phase 2: the shared-memory kernel; DH_RESOLVE3=1 keeps the global-memory one (warp per block) for A/B measurements
-    static const bool use_v3 = getenv("DH_RESOLVE3") != nullptr;
+    // phase 2: warp per block in global memory (bgzf_resolve3_kernel).  DH_RESOLVE4=1 selects the shared-memory kernel, measured r2b:
+    // 295.5 ms against 104.0 ms on the 100 M-record bench (468,651 blocks) -- three 72 KB CTAs per SM put 3 blocks in flight where
+    // the warp-per-block kernel has 32, and the window's dependency rounds (two barriers each) do not make one block 10x faster.
+    static const bool use_v3 = getenv("DH_RESOLVE4") == nullptr;
     if (use_v3) bgzf_resolve3_kernel<<<(nblocks + 7u) / 8u, 256, 0, stream>>>(blocks, nblocks, out, status, ncmd, areas);
     else bgzf_resolve4_kernel<<<nblocks, R4_THREADS, sizeof(R4Smem), stream>>>(blocks, nblocks, out, status, ncmd, areas);
     return cudaGetLastError();

@@ -9,6 +9,8 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -30,34 +32,97 @@ int cuda_fail(cudaError_t e, const char *what) {
     return DH_ECUDA;
 }
 
+// ---- allocation cache -------------------------------------------------------------------------------------------------
+// cudaMalloc / cudaHostAlloc of the pipeline's buffers (GBs of segment buffers, ~100 MB pinned batch arenas) cost more than a scan of a
+// small file, and a session runs many scans: released buffers are kept (per device / pinned) and handed to the next reserve that
+// fits.  DH_ALLOC_CACHE=0 turns it off; dh_trim() gives everything back.
+namespace {
+struct AllocCache {
+    std::mutex mu;
+    std::multimap<size_t, void *> dev[64];
+    std::multimap<size_t, void *> pin;
+    size_t dev_bytes[64] = {}, pin_bytes = 0;
+    const size_t dev_cap = 48ull << 30, pin_cap = 8ull << 30;
+    const bool on = !(getenv("DH_ALLOC_CACHE") && atoi(getenv("DH_ALLOC_CACHE")) == 0);
+};
+AllocCache &cache() { static AllocCache c; return c; }
+void *cache_take(std::multimap<size_t, void *> &m, size_t &total, size_t n, size_t *got) {
+    auto it = m.lower_bound(n);
+    if (it == m.end() || it->first > n + n / 2 + (64u << 20)) return nullptr;     // do not burn a 3 GiB buffer on a 1 MiB request
+    void *p = it->second;
+    *got = it->first;
+    total -= it->first;
+    m.erase(it);
+    return p;
+}
+}  // namespace
+
 int DevBuf::reserve(size_t n) {
     if (n <= cap) return DH_OK;
     // growing means cudaFree + cudaMalloc (a device-wide synchronisation): leave room, sizes of successive batches creep up
     const bool regrow = cap != 0;
+    if (regrow) cudaDeviceSynchronize();      // what cudaFree would have waited for: work in flight may still use the old buffer
     release();
     size_t want = std::max(regrow ? n + n / 4 : n, (size_t)1 << 20);
+    int d = 0;
+    cudaGetDevice(&d);
+    dev = d;
+    AllocCache &c = cache();
+    if (c.on && d >= 0 && d < 64) {
+        std::lock_guard<std::mutex> lk(c.mu);
+        size_t got = 0;
+        if (void *q = cache_take(c.dev[d], c.dev_bytes[d], want, &got)) { p = q; cap = got; return DH_OK; }
+    }
     cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess && c.on) {           // out of memory with buffers parked in the cache: give them back and try once more
+        cudaGetLastError();
+        dh_trim();
+        e = cudaMalloc(&p, want);
+    }
     if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMalloc"); }
     cap = want;
     return DH_OK;
 }
 void DevBuf::release() {
-    if (p) cudaFree(p);
+    if (p) {
+        AllocCache &c = cache();
+        bool kept = false;
+        if (c.on && dev >= 0 && dev < 64) {
+            std::lock_guard<std::mutex> lk(c.mu);
+            if (c.dev_bytes[dev] + cap <= c.dev_cap) { c.dev[dev].emplace(cap, p); c.dev_bytes[dev] += cap; kept = true; }
+        }
+        if (!kept) cudaFree(p);
+    }
     p = nullptr;
     cap = 0;
 }
 int PinBuf::reserve(size_t n) {
     if (n <= cap) return DH_OK;
     const bool regrow = cap != 0;
+    if (regrow) cudaDeviceSynchronize();
     release();
     size_t want = std::max(regrow ? n + n / 4 : n, (size_t)1 << 16);
+    AllocCache &c = cache();
+    if (c.on) {
+        std::lock_guard<std::mutex> lk(c.mu);
+        size_t got = 0;
+        if (void *q = cache_take(c.pin, c.pin_bytes, want, &got)) { p = q; cap = got; return DH_OK; }
+    }
     cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocPortable);
     if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaHostAlloc"); }
     cap = want;
     return DH_OK;
 }
 void PinBuf::release() {
-    if (p) cudaFreeHost(p);
+    if (p) {
+        AllocCache &c = cache();
+        bool kept = false;
+        if (c.on) {
+            std::lock_guard<std::mutex> lk(c.mu);
+            if (c.pin_bytes + cap <= c.pin_cap) { c.pin.emplace(cap, p); c.pin_bytes += cap; kept = true; }
+        }
+        if (!kept) cudaFreeHost(p);
+    }
     p = nullptr;
     cap = 0;
 }
@@ -146,6 +211,24 @@ extern "C" {
 
 const char *dh_version(void) { return "duckhts_b200 0.1 (sm_100a)"; }
 const char *dh_last_error(void) { return g_err; }
+
+void dh_trim(void) {
+    AllocCache &c = cache();
+    std::lock_guard<std::mutex> lk(c.mu);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (int d = 0; d < 64; ++d) {
+        if (c.dev[d].empty()) continue;
+        cudaSetDevice(d);
+        for (auto &e : c.dev[d]) cudaFree(e.second);
+        c.dev[d].clear();
+        c.dev_bytes[d] = 0;
+    }
+    cudaSetDevice(cur);
+    for (auto &e : c.pin) cudaFreeHost(e.second);
+    c.pin.clear();
+    c.pin_bytes = 0;
+}
 
 int dh_device_count(void) {
     int n = 0;

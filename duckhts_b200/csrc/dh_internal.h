@@ -24,6 +24,7 @@ int cuda_fail(cudaError_t e, const char *what);  // records the message, returns
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
+    int dev = 0;     // device the buffer lives on
     int reserve(size_t n);
     void release();
 };

@@ -57,6 +57,35 @@ static int device_list(int *devs) {
     if (n == 0) devs[n++] = 0;
     return n;
 }
+/* Contexts (streams, events, staging) outlive the query that made them: a session's next query on the same device takes one from the
+ * pool instead of creating CUDA streams and re-allocating.  One context serves one query at a time. */
+static pthread_mutex_t g_pool_mu = PTHREAD_MUTEX_INITIALIZER;
+static struct { dh_ctx *ctx; int device, busy; } g_pool[64];
+static dh_ctx *ctx_acquire(int device) {
+    pthread_mutex_lock(&g_pool_mu);
+    int free_slot = -1;
+    for (int i = 0; i < 64; ++i) {
+        if (g_pool[i].ctx && !g_pool[i].busy && g_pool[i].device == device) { g_pool[i].busy = 1; dh_ctx *c = g_pool[i].ctx; pthread_mutex_unlock(&g_pool_mu); return c; }
+        if (!g_pool[i].ctx && free_slot < 0) free_slot = i;
+    }
+    pthread_mutex_unlock(&g_pool_mu);
+    dh_ctx *c = dh_ctx_create(device);
+    if (!c) return NULL;
+    pthread_mutex_lock(&g_pool_mu);
+    for (int i = 0; i < 64 && free_slot >= 0; ++i)
+        if (!g_pool[i].ctx) { g_pool[i].ctx = c; g_pool[i].device = device; g_pool[i].busy = 1; free_slot = -2; break; }
+    pthread_mutex_unlock(&g_pool_mu);
+    return c;       /* pool full: the context is simply destroyed when released */
+}
+static void ctx_release(dh_ctx *c) {
+    if (!c) return;
+    pthread_mutex_lock(&g_pool_mu);
+    for (int i = 0; i < 64; ++i)
+        if (g_pool[i].ctx == c) { g_pool[i].busy = 0; pthread_mutex_unlock(&g_pool_mu); return; }
+    pthread_mutex_unlock(&g_pool_mu);
+    dh_ctx_destroy(c);
+}
+
 static uint64_t env_u64(const char *name, uint64_t dflt) {
     const char *e = getenv(name);
     return (e && *e) ? strtoull(e, NULL, 0) : dflt;
@@ -283,7 +312,7 @@ static void bam_bind_free(void *p) {
     if (!b) return;
     if (b->bam) dh_bam_close(b->bam);
     if (b->index) dh_index_free(b->index);
-    if (b->ctx) dh_ctx_destroy(b->ctx);
+    if (b->ctx) ctx_release(b->ctx);
     if (b->image) dh_host_free(b->image);
     free(b->path);
     free(b->region);
@@ -308,7 +337,7 @@ static void bam_global_free(void *p) {
     for (int i = 0; i < g->n_src; ++i) {
         bam_source_t *s = &g->src[i];
         if (s->cur) { free(s->cur); s->cur = NULL; }     /* the handle forgets its held slots at the next scan / close */
-        if (s->owns) { if (s->bam) dh_bam_close(s->bam); if (s->ctx) dh_ctx_destroy(s->ctx); }
+        if (s->owns) { if (s->bam) dh_bam_close(s->bam); if (s->ctx) ctx_release(s->ctx); }
         pthread_mutex_destroy(&s->mu);
     }
     free(g->col_ids); free(g->abi_col); free(g->out_of_abi); free(g->ref_cells); free(g->sample_cells);
@@ -332,7 +361,7 @@ static void read_bam_bind(duckdb_bind_info info) {
     memset(b, 0, sizeof *b);
     int devs[MAX_SOURCES];
     device_list(devs);
-    b->ctx = dh_ctx_create(devs[0]);
+    b->ctx = ctx_acquire(devs[0]);
     if (!b->ctx) snprintf(err, sizeof err, "read_bam: no usable CUDA device (%s)", dh_last_error());
     else {
         /* streamed: only the header blocks are read here; the scan reads the file segment by segment (dh_bam_open_file) */
@@ -469,7 +498,7 @@ static void read_bam_init(duckdb_init_info info) {
         if (i == 0) { s->bam = b->bam; s->ctx = NULL; s->owns = 0; }
         else {
             s->owns = 1;
-            s->ctx = dh_ctx_create(devs[i]);
+            s->ctx = ctx_acquire(devs[i]);
             s->bam = s->ctx ? dh_bam_clone(b->bam, s->ctx) : NULL;
             if (!s->bam) { snprintf(err, sizeof err, "read_bam: cannot start a pipeline on device %d: %s", devs[i], dh_last_error()); break; }
         }
@@ -875,7 +904,9 @@ typedef struct {
     uint64_t cursor;        /* next row of the batch: records (wide) or records x samples (tidy) */
     int done;
     int next_region;        /* region cursor of a chained region scan (bcf_reader.c:172, 1318-1333) */
+    char *deferred_err;     /* a scan that could not start: reported by local init, where the reference finds it */
 } bcf_global_t;
+static bcf_global_t *g_last_bcf_global;
 
 /* start the scan of the next region that yields an iterator: 1 started, 0 none left, < 0 error */
 static int bcf_next_region(bcf_bind_t *b, bcf_global_t *l) {
@@ -892,7 +923,7 @@ static void bcf_bind_free(void *p) {
     if (!b) return;
     if (b->bcf) dh_bcf_close(b->bcf);
     if (b->index) dh_index_free(b->index);
-    if (b->ctx) dh_ctx_destroy(b->ctx);
+    if (b->ctx) ctx_release(b->ctx);
     if (b->image) dh_host_free(b->image);
     free(b->region);
     for (int i = 0; i < b->n_regions; ++i) free(b->regions[i]);
@@ -905,8 +936,11 @@ static void bcf_bind_free(void *p) {
 static void bcf_global_free(void *p) {
     bcf_global_t *l = (bcf_global_t *)p;
     if (!l) return;
+    bcf_global_t *expect = l;
+    __atomic_compare_exchange_n(&g_last_bcf_global, &expect, NULL, 0, __ATOMIC_ACQ_REL, __ATOMIC_ACQUIRE);
     free(l->cur);
     free(l->col_ids);
+    free(l->deferred_err);
     pthread_mutex_destroy(&l->mu);
     api.duckdb_free(l);
 }
@@ -936,7 +970,7 @@ static void read_bcf_bind(duckdb_bind_info info) {
     memset(b, 0, sizeof *b);
     int devs[MAX_SOURCES];
     device_list(devs);
-    dh_ctx *ctx = b->ctx = dh_ctx_create(devs[0]);
+    dh_ctx *ctx = b->ctx = ctx_acquire(devs[0]);
     if (!ctx) snprintf(err, sizeof err, "read_bcf: no usable CUDA device (%s)", dh_last_error());
     else {
         if (region && region[0]) {
@@ -1050,31 +1084,28 @@ static void read_bcf_init(duckdb_init_info info) {
     free(iw);
     free(fw);
     if (rc == DH_OK) rc = dh_bcf_set_slots(b->bcf, (int)env_u64("DUCKHTS_SLOTS", 8));
+    char err[600];
+    err[0] = 0;
     if (rc == DH_OK && b->n_regions > 0) {
-        if (!b->index) {
-            char err[600];
-            snprintf(err, sizeof err, "Region query requires an index file (.tbi or .csi). Region: %s", b->region);
-            api.duckdb_init_set_error(info, err);
-            bcf_global_free(l);
-            return;
+        if (!b->index) snprintf(err, sizeof err, "Region query requires an index file (.tbi or .csi). Region: %s", b->region);
+        else {
+            const int started = bcf_next_region(b, l);
+            if (started < 0) snprintf(err, sizeof err, "%s", dh_last_error());
+            else if (!started) l->done = 1;     /* no region named a contig: an empty result, not an error (bcf_reader.c:952-956) */
         }
-        const int started = bcf_next_region(b, l);
-        if (started < 0) {
-            api.duckdb_init_set_error(info, dh_last_error());
-            bcf_global_free(l);
-            return;
-        }
-        if (!started) l->done = 1;              /* no region named a contig: an empty result, not an error (bcf_reader.c:952-956) */
-    } else if (rc != DH_OK || dh_bcf_scan_begin(b->bcf) != DH_OK) {
-        api.duckdb_init_set_error(info, dh_last_error());
-        bcf_global_free(l);
-        return;
-    }
+    } else if (rc != DH_OK || dh_bcf_scan_begin(b->bcf) != DH_OK) snprintf(err, sizeof err, "%s", dh_last_error());
+    if (err[0]) { l->deferred_err = strdup(err); l->done = 1; }   /* the reference meets these in local init (after the schema is known) */
     api.duckdb_init_set_max_threads(info, 64);
     api.duckdb_init_set_init_data(info, l, bcf_global_free);
+    __atomic_store_n(&g_last_bcf_global, l, __ATOMIC_RELEASE);
 }
 
-static void read_bcf_local_init(duckdb_init_info info) { api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free); }
+static void read_bcf_local_init(duckdb_init_info info) {
+    bcf_bind_t *b = (bcf_bind_t *)api.duckdb_init_get_bind_data(info);
+    bcf_global_t *l = __atomic_load_n(&g_last_bcf_global, __ATOMIC_ACQUIRE);
+    if (l && l->bind == b && l->deferred_err) { api.duckdb_init_set_error(info, l->deferred_err); return; }
+    api.duckdb_init_set_init_data(info, api.duckdb_malloc(8), api.duckdb_free);
+}
 
 /* ---- column fillers: one batch column -> one output vector, rows [0, n) of the chunk -------------------------------------
  * Cell k of the chunk comes from batch cell idx(k) = (i0 + k) / div * mul + add: site-level columns of tidy rows repeat
@@ -1286,7 +1317,7 @@ static void bgunzip_bind(duckdb_bind_info info) {
         device_list(devs);
         struct stat stt;
         if ((in_fd = open(in, O_RDONLY)) < 0 || fstat(in_fd, &stt) != 0 || !S_ISREG(stt.st_mode)) snprintf(err, sizeof err, "bgunzip: cannot open input %s", in);
-        else if (!(ctx = dh_ctx_create(devs[0]))) snprintf(err, sizeof err, "bgunzip: no usable CUDA device (%s)", dh_last_error());
+        else if (!(ctx = ctx_acquire(devs[0]))) snprintf(err, sizeof err, "bgunzip: no usable CUDA device (%s)", dh_last_error());
         else if ((out_fd = open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0666)) < 0) snprintf(err, sizeof err, "bgunzip: cannot open output %s: %s", out_path, strerror(errno));
         else {
             dh_inflate_stats st;
@@ -1301,7 +1332,7 @@ static void bgunzip_bind(duckdb_bind_info info) {
     }
     if (in_fd >= 0) close(in_fd);
     if (out_fd >= 0) close(out_fd);
-    if (ctx) dh_ctx_destroy(ctx);
+    if (ctx) ctx_release(ctx);
     if (err[0]) api.duckdb_bind_set_error(info, err);
     else {
         if (!keep) unlink(in);

@@ -43,6 +43,10 @@ dh_ctx *dh_ctx_create(int device);
 void dh_ctx_destroy(dh_ctx *ctx);
 int dh_ctx_sm_count(const dh_ctx *ctx);
 
+/* The library keeps the device and pinned buffers of finished scans (a session runs many; allocating them costs more than a small
+ * scan) up to 48 GiB per device and 8 GiB pinned; dh_trim() gives them back.  DH_ALLOC_CACHE=0 in the environment disables it. */
+void dh_trim(void);
+
 /* Pinned host memory: buffers handed to the *_host entry points copy at full PCIe rate only when they
  * come from here (pageable memory works, through the driver's bounce buffers). */
 void *dh_host_alloc(size_t bytes);

@@ -18,7 +18,14 @@ for stage in "$@"; do
       U=$(python -c "import bench,os; print(bench.gen_unit('bam', 4000000, 0x9E3779B97F4A7C15, True, os.cpu_count()))")
       for t in 1 4 16; do for lay in compact duckdb; do
         DUCKHTS_LAYOUT=$lay DUCKHTS_PROFILE=1 harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam $U standard_tags=true --cols 0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14 --threads $t --time 2>&1 | sed "s/^/[$lay t=$t] /"
-      done; done > gpurun_out/${T}_extprof.log 2>&1; cat gpurun_out/${T}_extprof.log ;;
+      done; done > gpurun_out/${T}_extprof.log 2>&1
+      python tools/make_tiled.py /tmp/duckhts_b200_cache/tiled100m.bam 100e6 >> gpurun_out/${T}_extprof.log 2>&1
+      for t in 1 16; do
+        DUCKHTS_PROFILE=1 harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam /tmp/duckhts_b200_cache/tiled100m.bam standard_tags=true --cols 0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14 --threads $t --time --repeat 3 2>&1 | sed "s/^/[100M t=$t] /"
+      done >> gpurun_out/${T}_extprof.log 2>&1
+      DH_TRACE=1 DUCKHTS_PROFILE=1 harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam /tmp/duckhts_b200_cache/tiled100m.bam standard_tags=true --cols 0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14 --threads 16 --time > gpurun_out/${T}_exttrace.log 2>&1
+      rm -f /tmp/duckhts_b200_cache/tiled100m.bam
+      cat gpurun_out/${T}_extprof.log; tail -5 gpurun_out/${T}_exttrace.log ;;
     ab_resolve) # inflate phase 2: shared-memory kernel (default) against the global-memory one of round 1
       for v in 4 3; do
         if [ $v = 3 ]; then export DH_RESOLVE3=1; else unset DH_RESOLVE3; fi
