@@ -259,7 +259,7 @@ def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
         n = bf.drain()
         return n, bf.stats()
 
-    bf.set_mode(device_input=True, device_output=True)
+    bf.set_mode(device_input=True, device_output=True, compact=True)
     for _ in range(min(args.warmup, 2)):
         n, st = once()
     assert st.status == 0 and n == n_sites, (st.status, n, n_sites)
@@ -274,18 +274,23 @@ def bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum):
     out.update({"value": sites / (ms / 1e3), "unit": "sites/s", "rows_per_s": sites * ns / (ms / 1e3), "ms_per_step": ms,
                 "inflated_mb": st.inflated_bytes / 1e6,
                 "kernel_ms_per_step": {"bgzf_inflate": k[0] / args.steps, "bcf_walk": k[1] / args.steps, "bcf_decode": k[2] / args.steps}})
-    bf.set_mode(device_input=False, device_output=False)
-    walls = []
-    for it in range(1 + min(args.steps, 2)):
-        barrier()
-        t0 = time.perf_counter()
-        n, st = once()
-        if it:
-            walls.append(rmax((time.perf_counter() - t0) * 1e3))
-    w = float(np.mean(walls))
-    out["e2e"] = {"value": sites / (w / 1e3), "unit": "sites/s", "rows_per_s": sites * ns / (w / 1e3), "ms_per_step": w,
-                  "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes),
-                  "d2h_gbs": st.d2h_bytes / 1e9 / (w / 1e3)}
+    def e2e(compact, steps):
+        bf.set_mode(device_input=False, device_output=False, compact=compact)
+        walls = []
+        for it in range(1 + steps):
+            barrier()
+            t0 = time.perf_counter()
+            n, s = once()
+            if it:
+                walls.append(rmax((time.perf_counter() - t0) * 1e3))
+        w = float(np.mean(walls))
+        return {"value": sites / (w / 1e3), "unit": "sites/s", "rows_per_s": sites * ns / (w / 1e3), "ms_per_step": w,
+                "h2d_bytes_per_step": int(s.h2d_bytes), "d2h_bytes_per_step": int(s.d2h_bytes), "d2h_bytes_per_site": s.d2h_bytes / max(n, 1),
+                "d2h_gbs": s.d2h_bytes / 1e9 / (w / 1e3)}
+
+    out["e2e"] = e2e(True, min(args.steps, 2))
+    out["e2e"]["layout"] = "compact FORMAT cells (GT 4 bytes, numeric lists as 2-byte counts + children)"
+    out["e2e"]["duckdb_layout"] = e2e(False, 1)
     bf.close()
     del pin
     if rank == 0 and os.path.exists(FAKE_HOST):

@@ -52,7 +52,8 @@ class BcfBatch(C.Structure):
                 ("core", C.c_void_p * 7), ("core_validity", C.c_void_p * 7),
                 ("info", C.POINTER(C.c_void_p)), ("info_validity", C.POINTER(C.c_void_p)),
                 ("format", C.POINTER(C.c_void_p)), ("format_validity", C.POINTER(C.c_void_p)),
-                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64), ("slot", C.c_int32), ("pad2", C.c_int32)]
+                ("heap", C.c_void_p), ("heap_bytes", C.c_uint64), ("bytes", C.c_uint64), ("slot", C.c_int32), ("layout", C.c_uint32),
+                ("format_rec", C.POINTER(C.c_void_p))]
 
 
 _lib = None

@@ -64,8 +64,8 @@ class BcfFile:
     def configure(self, seg_comp=0, batch_records=0, string_bytes=0):
         check(lib().dh_bcf_configure(self.h, seg_comp, batch_records, string_bytes), "dh_bcf_configure")
 
-    def set_mode(self, device_input=False, device_output=False):
-        check(lib().dh_bcf_set_mode(self.h, (1 if device_input else 0) | (2 if device_output else 0)), "dh_bcf_set_mode")
+    def set_mode(self, device_input=False, device_output=False, compact=False):
+        check(lib().dh_bcf_set_mode(self.h, (1 if device_input else 0) | (2 if device_output else 0) | (4 if compact else 0)), "dh_bcf_set_mode")
 
     def scan_begin(self):
         check(lib().dh_bcf_scan_begin(self.h), "dh_bcf_scan_begin")
@@ -159,6 +159,43 @@ def _column_text(ptr, vptr, n, typ, is_list, heap):
     return vals
 
 
+def _compact_format_text(ptr, vptr, n, f, heap, rec_ptr, n_rec, ns):
+    """n FORMAT cells of the compact wire layout -> text (include/duckhts_cuda.h, dh_bcf_set_mode): GT cells are packed in 4 bytes,
+    numeric LIST cells are an element count with the children at a per-record base; anything else has the DuckDB layout."""
+    name, typ, is_list = f
+    valid = validity_to_bool(vptr, n) if vptr else None
+    if typ == 3 and not is_list and name == "GT":
+        cells = np.frombuffer(C.string_at(ptr, 4 * n), dtype=np.uint32)
+        out = []
+        for i in range(n):
+            if valid is not None and not valid[i]:
+                out.append("\\N")
+                continue
+            v = int(cells[i])
+            if not v >> 31:
+                out.append(_esc(bytes([v & 0xff, (v >> 8) & 0xff, (v >> 16) & 0xff])[:(v >> 24) & 3]))
+            else:
+                off = v & 0x7fffffff
+                ln = int(np.frombuffer(C.string_at(heap + off, 4), dtype=np.uint32)[0])
+                out.append(_esc(C.string_at(heap + off + 4, ln)))
+        return out
+    if is_list and typ in (1, 2):
+        cnt = np.frombuffer(C.string_at(ptr, 2 * n), dtype=np.uint16)
+        rec = np.frombuffer(C.string_at(rec_ptr, 8 * n_rec), dtype=np.uint32).reshape(n_rec, 2)
+        out = []
+        for i in range(n):
+            if valid is not None and not valid[i]:
+                out.append("\\N")
+                continue
+            r, smp = divmod(i, ns)
+            first = int(rec[r, 0]) + smp * int(rec[r, 1])
+            raw = C.string_at(heap + 4 * first, 4 * int(cnt[i]))
+            kids = [str(int(v)) for v in np.frombuffer(raw, dtype=np.int32)] if typ == 1 else ["%.9g" % float(v) for v in np.frombuffer(raw, dtype=np.float32)]
+            out.append("[" + ",".join(kids) + "]")
+        return out
+    return _column_text(ptr, vptr, n, typ, is_list, heap)
+
+
 def schema_names(bf, tidy):
     names = list(CORE_NAMES) + ["INFO_" + f[0] for f in bf.info]
     if bf.samples:
@@ -169,12 +206,14 @@ def schema_names(bf, tidy):
     return names
 
 
-def rows_text(ctx, data, tidy=True, batch_records=0, seg_comp=0, index=None, regions=None):
+def rows_text(ctx, data, tidy=True, batch_records=0, seg_comp=0, index=None, regions=None, compact=False):
     """Whole scan as text lines (header line first), like `fake_duckdb EXT read_bcf FILE [tidy_format=true] --dump`.
     index = CSI bytes + regions = list of region strings: the reference's chained single-region scans (bcf_reader.c:917-951)."""
     from .bam import Index
     with BcfFile(ctx, data) as bf, (Index(ctx, index) if index is not None else _NoIndex()) as ix:
         bf.configure(seg_comp, batch_records, 0)
+        if compact:
+            bf.set_mode(compact=True)
         lines = ["\t".join(schema_names(bf, tidy))]
         ns = len(bf.samples)
         status = 0
@@ -198,7 +237,11 @@ def rows_text(ctx, data, tidy=True, batch_records=0, seg_comp=0, index=None, reg
             core_types = (3, "i64", 3, 3, 3, "f64", 3)
             site = [_column_text(b.core[c], b.core_validity[c], n, core_types[c], c in (4, 6), heap) for c in range(7)]
             site += [_column_text(b.info[i], b.info_validity[i], n, f[1], f[2], heap) for i, f in enumerate(bf.info)]
-            fmt = [_column_text(b.format[i], b.format_validity[i], n * ns, f[1], f[2], heap) for i, f in enumerate(bf.format)]
+            if b.layout == 4:
+                fmt = [_compact_format_text(b.format[i], b.format_validity[i], n * ns, f, heap, b.format_rec[i], n, ns) if b.format[i] else
+                       _column_text(b.format[i], b.format_validity[i], n * ns, f[1], f[2], heap) for i, f in enumerate(bf.format)]
+            else:
+                fmt = [_column_text(b.format[i], b.format_validity[i], n * ns, f[1], f[2], heap) for i, f in enumerate(bf.format)]
             for r in range(n):
                 srow = [col[r] for col in site]
                 if not ns:

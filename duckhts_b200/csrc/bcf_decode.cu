@@ -563,7 +563,33 @@ __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__
                                     const int32_t v = (int32_t)w;
                                     len += (a > 0 ? 1u : 0u) + ((v >> 1) ? dec_len((v >> 1) - 1) : 1u);
                                 }
-                                if (len > 0) {
+                                if (len > 0 && p.compact) {
+                                    // compact GT cell: <= 3 characters ("0|1") ride in the cell, [25:24] = length, [23:0] = the bytes; longer
+                                    // strings (alleles >= 10, polyploid calls) go to the bump region as {uint32 length, bytes}, cell = 1 << 31 | heap offset
+                                    uint8_t tmp[12];
+                                    uint8_t *dst = tmp;
+                                    uint64_t o = 0;
+                                    if (len > 3u) { o = bump_alloc(p, 4ull + len); dst = o == UINT64_MAX ? nullptr : p.heap + p.fixed_bytes + o + 4; }
+                                    uint32_t cell = 0u;
+                                    if (dst) {
+                                        uint32_t q = 0;
+                                        for (int32_t a = 0; a < d.n; ++a) {
+                                            const uint32_t w = word_at(u, vp, a, d.type);
+                                            if (w == I32_VEND) break;
+                                            const int32_t v = (int32_t)w;
+                                            if (a > 0) dst[q++] = (v & 1) ? '|' : '/';
+                                            if (!(v >> 1)) dst[q++] = '.';
+                                            else { const uint32_t n = dec_len((v >> 1) - 1); dec_put(dst + q, (v >> 1) - 1, n); q += n; }
+                                        }
+                                        if (len <= 3u) cell = (len << 24) | (uint32_t)tmp[0] | (len > 1u ? (uint32_t)tmp[1] << 8 : 0u) | (len > 2u ? (uint32_t)tmp[2] << 16 : 0u);
+                                        else {
+                                            *reinterpret_cast<uint32_t *>(dst - 4) = len;
+                                            cell = 0x80000000u | (uint32_t)(p.fixed_bytes + o);
+                                        }
+                                    }
+                                    reinterpret_cast<uint32_t *>(col)[row] = cell;
+                                    valid = true;
+                                } else if (len > 0) {
                                     uint8_t tmp[12];
                                     uint8_t *dst = tmp;
                                     uint64_t o = 0;
@@ -604,10 +630,15 @@ __global__ void __launch_bounds__(256) bcf_decode_kernel(const __grid_constant__
                                         if (word_is_vend(w, d.type)) break;     // the rest of the vector is vector_end (vcf.c:6233-6236)
                                         if (w != miss && w != vend) child[n_out++] = w;
                                     }
-                                    ListEntry e;
-                                    e.offset = (base + d.slot) / 4 + (uint64_t)s * (uint32_t)d.n;
-                                    e.length = n_out;
-                                    reinterpret_cast<ListEntry *>(col)[row] = e;
+                                    if (p.compact) {
+                                        reinterpret_cast<uint16_t *>(col)[row] = (uint16_t)(n_out < 65535u ? n_out : 65535u);
+                                        if (s == 0u) reinterpret_cast<uint2 *>(p.fmt_rec[c])[R] = make_uint2((uint32_t)((base + d.slot) / 4), (uint32_t)d.n);
+                                    } else {
+                                        ListEntry e;
+                                        e.offset = (base + d.slot) / 4 + (uint64_t)s * (uint32_t)d.n;
+                                        e.length = n_out;
+                                        reinterpret_cast<ListEntry *>(col)[row] = e;
+                                    }
                                     valid = true;
                                 }
                             }

@@ -57,6 +57,10 @@ struct BcfDecodeParams {
     uint64_t fixed_bytes;           // size of the fixed region (list children at structural capacity)
     uint64_t bump_cap;              // size of the bump region (strings > 12 bytes, string-list cells)
     unsigned long long *bump_used;  // bytes requested from the bump region (may exceed bump_cap: the host then retries)
+    // compact wire layout (dh_bcf_set_mode(DH_BAM_COMPACT_OUTPUT), include/duckhts_cuda.h): the GT column is 4 bytes per cell, numeric
+    // LIST FORMAT columns are a 2-byte element count per cell + {first child, values per sample} per RECORD
+    uint32_t compact, pad;
+    uint8_t *const *fmt_rec;        // n_fmt device pointers: per record {uint32 first child (4-byte units from `heap`), uint32 values per sample}
 };
 
 cudaError_t launch_bcf_walk(const WalkParams &p, const BcfTables &t, cudaStream_t stream);

@@ -56,6 +56,7 @@ struct dh_bcf_state {
     PinBuf h_ptrs[MAX_SLOTS];
     std::vector<const void *> out_info[MAX_SLOTS], out_fmt[MAX_SLOTS];
     std::vector<const uint64_t *> out_info_v[MAX_SLOTS], out_fmt_v[MAX_SLOTS];
+    std::vector<const void *> out_fmt_rec[MAX_SLOTS];   // compact layout: per-record {first child, values per sample} of the numeric LIST FORMAT columns
     dh_bcf_batch desc[MAX_SLOTS];
     uint64_t bump_off[MAX_SLOTS] = {};    // where the bump counter sits in the arena
 };
@@ -295,6 +296,10 @@ int upload_tables(dh_bam *b) {
 
 uint32_t info_width(const Field &f) { return f.is_list ? 16u : f.type == HT_FLAG ? 1u : f.type == HT_STR ? 16u : 4u; }
 uint32_t fmt_width(const Field &f) { return (f.is_list || f.type == HT_STR) ? 16u : 4u; }
+bool fmt_is_gt(const Field &f) { return f.name == "GT" && f.type == HT_STR; }
+bool fmt_is_numlist(const Field &f) { return f.is_list && (f.type == HT_INT || f.type == HT_REAL); }
+// compact wire layout: GT 4 bytes, numeric lists a 2-byte count, the rest as in the DuckDB layout
+uint32_t fmt_width_compact(const Field &f) { return fmt_is_gt(f) ? 4u : fmt_is_numlist(f) ? 2u : fmt_width(f); }
 const uint32_t CORE_WIDTH[BCF_CORE_COLS] = {16, 8, 16, 16, 16, 8, 16};
 
 int issue_bcf_batch(dh_bam *b) {
@@ -324,21 +329,25 @@ int issue_bcf_batch(dh_bam *b) {
         if (st->info[c].type != HT_FLAG) { info_voff[c] = off; off = al(off + ((n_rec + 63) / 64) * 8); }
     }
     const uint64_t site_end = off;
+    const bool compact = (b->mode & DH_BAM_COMPACT_OUTPUT) != 0;
+    std::vector<uint64_t> fmt_roff(nf, UINT64_MAX);
     for (size_t c = 0; c < nf; ++c) {
         if (!st->fmt_want[c]) continue;
         fmt_off[c] = off;
-        off = al(off + fmt_width(st->fmt[c]) * rows);
+        off = al(off + (compact ? fmt_width_compact(st->fmt[c]) : fmt_width(st->fmt[c])) * rows);
         fmt_voff[c] = off;
         off = al(off + ((rows + 63) / 64) * 8 + 8);
+        if (compact && fmt_is_numlist(st->fmt[c])) { fmt_roff[c] = off; off = al(off + 8 * n_rec); }
     }
     const uint64_t heap_off = off, fixed = (bb.heap + A256) & ~A256, main_bytes = heap_off + fixed, total = main_bytes + st->bump_cap;
     int rc;
     if ((rc = o.arena.reserve(total + 256)) != DH_OK || (rc = o.h_arena.reserve(total + 256)) != DH_OK) return rc;
-    const size_t tbl = 2 * (ni + nf) * sizeof(void *) + 64;
+    const size_t tbl = (2 * (ni + nf) + nf) * sizeof(void *) + 64;
     if ((rc = st->h_ptrs[slot].reserve(tbl)) != DH_OK) return rc;
     uint8_t *dev = (uint8_t *)o.arena.p, *host = (uint8_t *)o.h_arena.p;
     void **tp = (void **)st->h_ptrs[slot].p;
-    void **d_info = tp, **d_info_v = tp + ni, **d_fmt = tp + 2 * ni, **d_fmt_v = tp + 2 * ni + nf;
+    void **d_info = tp, **d_info_v = tp + ni, **d_fmt = tp + 2 * ni, **d_fmt_v = tp + 2 * ni + nf, **d_fmt_rec = tp + 2 * ni + 2 * nf;
+    st->out_fmt_rec[slot].assign(nf, nullptr);
     st->out_info[slot].assign(ni, nullptr);
     st->out_info_v[slot].assign(ni, nullptr);
     st->out_fmt[slot].assign(nf, nullptr);
@@ -363,8 +372,9 @@ int issue_bcf_batch(dh_bam *b) {
         if (info_voff[c] != UINT64_MAX) { d_info_v[c] = dev + info_voff[c]; st->out_info_v[slot][c] = (const uint64_t *)(host + info_voff[c]); }
     }
     for (size_t c = 0; c < nf; ++c) {
-        d_fmt[c] = d_fmt_v[c] = nullptr;
+        d_fmt[c] = d_fmt_v[c] = d_fmt_rec[c] = nullptr;
         if (fmt_off[c] == UINT64_MAX) continue;
+        if (fmt_roff[c] != UINT64_MAX) { d_fmt_rec[c] = dev + fmt_roff[c]; st->out_fmt_rec[slot][c] = host + fmt_roff[c]; }
         d_fmt[c] = dev + fmt_off[c];
         d_fmt_v[c] = dev + fmt_voff[c];
         st->out_fmt[slot][c] = host + fmt_off[c];
@@ -384,6 +394,8 @@ int issue_bcf_batch(dh_bam *b) {
     dp.info_valid = (unsigned long long *const *)d_info_v;
     dp.fmt = (uint8_t *const *)d_fmt;
     dp.fmt_valid = (unsigned long long *const *)d_fmt_v;
+    dp.fmt_rec = (uint8_t *const *)d_fmt_rec;
+    dp.compact = compact ? 1u : 0u;
     dp.heap = dev + heap_off;
     dp.heap_host = (uint64_t)(uintptr_t)(host + heap_off);
     dp.fixed_bytes = fixed;
@@ -407,6 +419,8 @@ int issue_bcf_batch(dh_bam *b) {
     d.info_validity = st->out_info_v[slot].data();
     d.format = st->out_fmt[slot].data();
     d.format_validity = st->out_fmt_v[slot].data();
+    d.format_rec = st->out_fmt_rec[slot].data();
+    d.layout = compact ? DH_BAM_COMPACT_OUTPUT : 0u;
     d.heap = host + heap_off;
     d.heap_bytes = fixed;
     d.bytes = keep ? 0 : main_bytes;

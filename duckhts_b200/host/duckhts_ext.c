@@ -1084,6 +1084,10 @@ static void read_bcf_init(duckdb_init_info info) {
     free(iw);
     free(fw);
     if (rc == DH_OK) rc = dh_bcf_set_slots(b->bcf, (int)env_u64("DUCKHTS_SLOTS", 8));
+    {   /* FORMAT cells cross PCIe packed unless DUCKHTS_LAYOUT=duckdb asks for ready-made vectors */
+        const char *lay = getenv("DUCKHTS_LAYOUT");
+        if (rc == DH_OK) rc = dh_bcf_set_mode(b->bcf, (lay && !strcmp(lay, "duckdb")) ? 0u : DH_BAM_COMPACT_OUTPUT);
+    }
     char err[600];
     err[0] = 0;
     if (rc == DH_OK && b->n_regions > 0) {
@@ -1195,6 +1199,59 @@ static void fill_bcf_column(duckdb_vector vec, idx_t n, int type, int is_list, c
     }
 }
 
+/* compact wire layout (dh_bcf_set_mode(DH_BAM_COMPACT_OUTPUT)): the two FORMAT cell kinds the GPU leaves packed */
+static void fill_bcf_gt_compact(duckdb_vector vec, idx_t n, const uint32_t *cells, const uint64_t *validity, const cell_map *m, const uint8_t *heap) {
+    duckdb_string_t *out = (duckdb_string_t *)api.duckdb_vector_get_data(vec);
+    uint64_t *val = NULL;
+    for (idx_t k = 0; k < n; ++k) {
+        const uint64_t i = map_idx(m, k);
+        if (!bit_valid(validity, i)) {
+            if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
+            api.duckdb_validity_set_row_invalid(val, k);
+            continue;
+        }
+        const uint32_t v = cells[i];
+        if (!(v >> 31)) {                         /* <= 3 characters in the cell */
+            duckdb_string_t c;
+            memset(&c, 0, sizeof c);
+            c.value.inlined.length = (v >> 24) & 3u;
+            c.value.inlined.inlined[0] = (char)(v & 0xff); c.value.inlined.inlined[1] = (char)((v >> 8) & 0xff); c.value.inlined.inlined[2] = (char)((v >> 16) & 0xff);
+            out[k] = c;
+        } else {                                  /* {length, bytes} in the heap */
+            const uint8_t *p = heap + (v & 0x7fffffffu);
+            uint32_t len;
+            memcpy(&len, p, 4);
+            put_string(vec, out, k, (const char *)p + 4, len);
+        }
+    }
+}
+static void fill_bcf_numlist_compact(duckdb_vector vec, idx_t n, const uint16_t *cnt, const uint64_t *validity, const cell_map *m, const uint8_t *heap,
+                                     const uint32_t *rec, uint64_t ns) {
+    duckdb_list_entry *out = (duckdb_list_entry *)api.duckdb_vector_get_data(vec);
+    idx_t total = api.duckdb_list_vector_get_size(vec), need = total;
+    for (idx_t k = 0; k < n; ++k) { const uint64_t i = map_idx(m, k); if (bit_valid(validity, i)) need += cnt[i]; }
+    api.duckdb_list_vector_reserve(vec, need);
+    api.duckdb_list_vector_set_size(vec, need);
+    uint32_t *child = (uint32_t *)api.duckdb_vector_get_data(api.duckdb_list_vector_get_child(vec));
+    uint64_t *val = NULL;
+    for (idx_t k = 0; k < n; ++k) {
+        const uint64_t i = map_idx(m, k);
+        out[k].offset = total;
+        out[k].length = 0;
+        if (!bit_valid(validity, i)) {
+            if (!val) { api.duckdb_vector_ensure_validity_writable(vec); val = api.duckdb_vector_get_validity(vec); }
+            api.duckdb_validity_set_row_invalid(val, k);
+            continue;
+        }
+        const uint64_t r = i / ns, smp = i % ns;
+        const uint32_t *src = (const uint32_t *)heap + rec[2 * r] + smp * rec[2 * r + 1];
+        const uint32_t c = cnt[i];
+        for (uint32_t e = 0; e < c; ++e) child[total + e] = src[e];
+        out[k].length = c;
+        total += c;
+    }
+}
+
 static void read_bcf_scan(duckdb_function_info info, duckdb_data_chunk output) {
     bcf_global_t *l = (bcf_global_t *)api.duckdb_function_get_init_data(info);
     if (!l) { api.duckdb_data_chunk_set_size(output, 0); return; }
@@ -1255,9 +1312,14 @@ static void read_bcf_scan(duckdb_function_info info, duckdb_data_chunk output) {
             for (idx_t k = 0; k < n; ++k) put_cell(vec, out, k, &b->sample_cells[(r0 + k) % ns]);
         } else {
             const uint64_t k = c - (idx_t)b->fmt_start, f = k % (uint64_t)b->n_fmt;
-            if (b->default_gt) fill_bcf_column(vec, n, 3, 0, NULL, NULL, &site, bt->heap);
-            else if (b->tidy) { const cell_map m = {r0, 1, 1, 0}; fill_bcf_column(vec, n, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], &m, bt->heap); }
-            else { const cell_map m = {r0, 1, ns, k / (uint64_t)b->n_fmt}; fill_bcf_column(vec, n, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], &m, bt->heap); }
+            if (b->default_gt) { fill_bcf_column(vec, n, 3, 0, NULL, NULL, &site, bt->heap); continue; }
+            const cell_map m = b->tidy ? (cell_map){r0, 1, 1, 0} : (cell_map){r0, 1, ns, k / (uint64_t)b->n_fmt};
+            const int is_gt = b->fmt[f].type == 3 && !b->fmt[f].is_list && !strcmp(b->fmt[f].name, "GT");
+            const int numlist = b->fmt[f].is_list && (b->fmt[f].type == 1 || b->fmt[f].type == 2);
+            if (bt->layout == DH_BAM_COMPACT_OUTPUT && bt->format[f] && is_gt) fill_bcf_gt_compact(vec, n, (const uint32_t *)bt->format[f], bt->format_validity[f], &m, bt->heap);
+            else if (bt->layout == DH_BAM_COMPACT_OUTPUT && bt->format[f] && numlist)
+                fill_bcf_numlist_compact(vec, n, (const uint16_t *)bt->format[f], bt->format_validity[f], &m, bt->heap, (const uint32_t *)bt->format_rec[f], ns);
+            else fill_bcf_column(vec, n, b->fmt[f].type, b->fmt[f].is_list, bt->format[f], bt->format_validity[f], &m, bt->heap);
         }
     }
     pthread_mutex_lock(&l->mu);

@@ -354,7 +354,14 @@ int dh_bcf_set_projection(dh_bcf *b, uint32_t core_mask, const uint8_t *info_wan
 /* Pipeline knobs (0 = keep): compressed bytes per inflate segment, records per batch, bytes of the per-batch region
  * for strings longer than 12 bytes and string-list cells. */
 int dh_bcf_configure(dh_bcf *b, uint64_t seg_comp_bytes, uint32_t batch_records, uint64_t string_bytes);
-int dh_bcf_set_mode(dh_bcf *b, uint32_t flags);      /* DH_BAM_DEVICE_INPUT / DH_BAM_DEVICE_OUTPUT, as for dh_bam */
+/* DH_BAM_DEVICE_INPUT / DH_BAM_DEVICE_OUTPUT as for dh_bam.  DH_BAM_COMPACT_OUTPUT: the FORMAT columns -- 2,504 cells per record
+ * and column, where the bytes of a batch are -- leave the GPU compact (site-level columns keep the DuckDB layout):
+ *   GT            uint32 per cell: bit 31 clear: [25:24] = length (<= 3), [23:0] = the characters ("0|1"); bit 31 set: [30:0] = offset
+ *                 in `heap` of {uint32 length, bytes} (alleles >= 10, polyploid calls)
+ *   INTEGER[] / FLOAT[]   uint16 per cell = number of elements kept (missing and vector_end dropped); the cell of sample s of record r
+ *                 has its children at ((uint32 *)heap)[first + s * per], {first, per} = ((uint32 *)format_rec[f])[2 r .. 2 r + 1]
+ *   everything else as in the DuckDB layout.  48 -> 21 bytes per (record, sample) for GT, DP, GQ, AD. */
+int dh_bcf_set_mode(dh_bcf *b, uint32_t flags);
 int dh_bcf_scan_begin(dh_bcf *b);
 /* Region query through the CSI index (bcf_itr_querys + bcf_itr_next, htslib/vcf.h:1321-1330; used by
  * src/bcf_reader.c:917-951): the records with rid == contig, pos < end and pos + rlen > beg, in file order.  One
@@ -378,7 +385,8 @@ typedef struct {
     uint64_t heap_bytes;
     uint64_t bytes;        /* bytes copied device -> host for this batch */
     int32_t slot;          /* pipeline slot: the argument of dh_bcf_release_batch */
-    int32_t pad2;
+    uint32_t layout;       /* 0 = DuckDB vector layout, DH_BAM_COMPACT_OUTPUT = compact FORMAT cells (dh_bcf_set_mode) */
+    const void *const *format_rec;   /* compact layout, numeric LIST FORMAT columns: per record {uint32 first child, uint32 values per sample}; else NULL */
 } dh_bcf_batch;
 /* Returns 1 and fills *out (buffers stay valid until the next call on this handle), 0 at end of scan, < 0 on error. */
 int dh_bcf_next_batch(dh_bcf *b, dh_bcf_batch *out);

@@ -41,6 +41,8 @@ def test_read_bcf_matches_reference_golden(ctx, name, tidy):
     got, status, _ = bcf.rows_text(ctx, img, tidy=tidy)
     assert status == 0
     assert got == exp, first_diff(got, exp)
+    got, status, _ = bcf.rows_text(ctx, img, tidy=tidy, compact=True, batch_records=3)      # compact FORMAT cells (GT 4 bytes, numeric lists as counts)
+    assert status == 0 and got == exp, first_diff(got, exp)
 
 
 def ref_dump(path, *args):
@@ -74,6 +76,9 @@ def test_read_bcf_matches_live_reference_on_synthetic(ctx, n_sites, n_samples, s
     assert status == 0
     assert len(got) == len(exp) == 1 + n_sites * max(n_samples, 1)
     assert got == exp, first_diff(got, exp)
+    if n_samples <= 300:
+        got, status, _ = bcf.rows_text(ctx, img, tidy=True, compact=True, **kw)
+        assert status == 0 and got == exp, first_diff(got, exp)
 
 
 # ---- against the oracle (oracle/bcf_oracle.py), incl. inputs the reference stops on ---------------------------------

@@ -361,8 +361,9 @@ def test_read_bcf_worker_threads_and_wide_mode(threads):
     edge = os.path.join(GOLD, "edge_small.bcf")
     for args in ((), ("tidy_format=true",)):
         rc_r, out_r, _ = run(REF_EXT, "read_bcf", edge, *args, "--hash")
-        rc_o, out_o, err_o = run(OUR_EXT, "read_bcf", edge, *args, "--hash", "--threads", str(threads))
-        assert rc_r == 0 and rc_o == 0 and multiset(out_o) == multiset(out_r), err_o
+        for env in ({}, {"DUCKHTS_LAYOUT": "duckdb"}):      # compact FORMAT cells (default) and ready-made DuckDB vectors
+            rc_o, out_o, err_o = run(OUR_EXT, "read_bcf", edge, *args, "--hash", "--threads", str(threads), env=env)
+            assert rc_r == 0 and rc_o == 0 and multiset(out_o) == multiset(out_r), err_o
 
 
 def test_bgunzip_streams_in_segments(tmp_path):
