@@ -1218,29 +1218,32 @@ int dh_bam_split_contigs(const dh_bam *b, const dh_index *idx, int n_parts, int3
 // batch in flight and hand its slot over as HELD.
 static int acquire_locked(dh_bam *b, dh_bam_batch *out) {
     DH_CUDA(cudaSetDevice(b->ctx->device));
-    auto top_up = [&]() -> int {
+    // refill the free slots; `exhausted` = the current range has nothing left to issue (else the slots ran out first)
+    auto top_up = [&](bool &exhausted) -> int {
+        exhausted = false;
         while (free_slots(b) > 0) {
             int w = have_work(b);
             if (w < 0) return w;
-            if (w == 0) break;
+            if (w == 0) { exhausted = true; break; }
             int rc = issue_batch(b);
             if (rc != DH_OK) return rc;
         }
         return DH_OK;
     };
-    int rc = top_up();
+    bool exhausted = false;
+    int rc = top_up(exhausted);
     if (rc != DH_OK) { b->scanning = false; return rc; }
-    while (b->inflight.empty() && !b->pending.empty() && b->final_status == 0) {
+    while (b->inflight.empty() && exhausted && !b->pending.empty() && b->final_status == 0) {
         // this range is exhausted: go on with the next one of the query (rows keep counting)
         const IdxChunk c = b->pending.front();
         b->pending.pop_front();
-        if ((rc = begin_range(b, c.u, c.v, false)) != DH_OK || (rc = top_up()) != DH_OK) { b->scanning = false; return rc; }
+        if ((rc = begin_range(b, c.u, c.v, false)) != DH_OK || (rc = top_up(exhausted)) != DH_OK) { b->scanning = false; return rc; }
     }
     if (b->inflight.empty()) {
         b->st.rows = b->rows_total;
         b->st.status = b->final_status;
-        if (free_slots(b) == 0 && !b->chain_done) {
-            set_error("every batch slot is held by the caller: release one (dh_bam_release_batch) or raise dh_bam_set_slots");
+        if (!exhausted) {      // every slot is held by the caller and batches remain: not the end of the scan
+            set_error("every batch slot is held by the caller: release one or raise the number of slots");
             return DH_EBUSY;
         }
         return 0;
@@ -1262,7 +1265,7 @@ static int acquire_locked(dh_bam *b, dh_bam_batch *out) {
         fprintf(stderr, "[dh_trace] batch %llu rows %llu decode %.1f-%.1f d2h %.1f-%.1f (%.1f GB/s)\n", (unsigned long long)b->returned,
                 (unsigned long long)o.desc.n_rows, t0, t1, t2, t3, o.desc.bytes / 1e6 / (t3 - t2 > 0 ? t3 - t2 : 1));
     }
-    rc = top_up();  // keep the pipeline full while the caller consumes this one
+    rc = top_up(exhausted);  // keep the pipeline full while the caller consumes this one
     if (rc != DH_OK) { b->scanning = false; return rc; }
     *out = o.desc;
     if (b->inflight.empty() && b->chain_done) out->status = b->final_status;

@@ -575,29 +575,32 @@ int dh_bcf_scan_region(dh_bcf *h, const dh_index *idx, const char *region) {
 static int bcf_acquire_locked(dh_bam *b, dh_bcf_batch *out) {
     dh_bcf_state *st = b->bcf;
     DH_CUDA(cudaSetDevice(b->ctx->device));
-    auto top_up = [&]() -> int {
+    // refill the free slots; `exhausted` = the current range has nothing left to issue (else the slots ran out first)
+    auto top_up = [&](bool &exhausted) -> int {
+        exhausted = false;
         while (scan_free_slots(b) > 0) {
             int w = scan_have_work(b);
             if (w < 0) return w;
-            if (w == 0) break;
+            if (w == 0) { exhausted = true; break; }
             int rc = issue_bcf_batch(b);
             if (rc != DH_OK) return rc;
         }
         return DH_OK;
     };
-    int rc = top_up();
+    bool exhausted = false;
+    int rc = top_up(exhausted);
     if (rc != DH_OK) { b->scanning = false; return rc; }
-    while (b->inflight.empty() && !b->pending.empty() && b->final_status == 0) {
-        // this virtual-offset range of the region query is exhausted: go on with the next one
+    while (b->inflight.empty() && exhausted && !b->pending.empty() && b->final_status == 0) {
+        // this range is exhausted: go on with the next one of the query (rows keep counting)
         const IdxChunk c = b->pending.front();
         b->pending.pop_front();
-        if ((rc = scan_begin_range(b, c.u, c.v, false)) != DH_OK || (rc = top_up()) != DH_OK) { b->scanning = false; return rc; }
+        if ((rc = scan_begin_range(b, c.u, c.v, false)) != DH_OK || (rc = top_up(exhausted)) != DH_OK) { b->scanning = false; return rc; }
     }
     if (b->inflight.empty()) {
         b->st.rows = b->rows_total;
         b->st.status = b->final_status;
-        if (scan_free_slots(b) == 0 && !b->chain_done) {
-            set_error("every batch slot is held by the caller: release one (dh_bcf_release_batch) or raise dh_bcf_set_slots");
+        if (!exhausted) {      // every slot is held by the caller and batches remain: not the end of the scan
+            set_error("every batch slot is held by the caller: release one or raise the number of slots");
             return DH_EBUSY;
         }
         return 0;
@@ -625,7 +628,7 @@ static int bcf_acquire_locked(dh_bam *b, dh_bcf_batch *out) {
         st->desc[slot].bytes += used;
     }
     st->desc[slot].heap_bytes += used;
-    rc = top_up();
+    rc = top_up(exhausted);
     if (rc != DH_OK) { b->scanning = false; return rc; }
     *out = st->desc[slot];
     if (b->inflight.empty() && b->chain_done) out->status = b->final_status;
