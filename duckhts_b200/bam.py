@@ -51,8 +51,9 @@ class Index:
     """A BAI or CSI index image (dh_index; reference hts_idx_load3).  CSI is BGZF: the GPU inflates it."""
 
     def __init__(self, ctx, data):
+        """ctx may be None for a BAI (plain bytes, parsed on the host); a CSI needs a context to be inflated."""
         self.a = _as_u8(data)
-        self.h = lib().dh_index_load(ctx.h, self.a.ctypes.data, self.a.size)
+        self.h = lib().dh_index_load(ctx.h if ctx is not None else None, self.a.ctypes.data, self.a.size)
         if not self.h:
             raise DuckhtsError("dh_index_load failed: " + lib().dh_last_error().decode())
 
@@ -63,6 +64,12 @@ class Index:
     @property
     def is_csi(self):
         return bool(lib().dh_index_is_csi(self.h))
+
+    def split_contigs(self, n_parts):
+        """dh_index_split_contigs: n_parts + 1 contig bounds of about equal compressed size (host code, no GPU)."""
+        v = (C.c_int32 * (n_parts + 1))()
+        check(lib().dh_index_split_contigs(self.h, n_parts, v), "dh_index_split_contigs")
+        return list(v)
 
     def close(self):
         if self.h:

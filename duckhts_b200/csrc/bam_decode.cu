@@ -89,7 +89,9 @@ __device__ __forceinline__ int64_t skip_aux_scalar(const uint8_t *u, int64_t s, 
     return s + size;
 }
 
-// scalar bam_aux_get (sam.c:4832-4855) over aux bytes [a0, end): returns offset of the type byte or -1
+// scalar bam_aux_get (sam.c:4832-4855) over aux bytes [a0, end): offset of the type byte, NONE (no such tag: errno ENOENT) or
+// CORRUPT (errno EINVAL: a broken entry in front of the tag, or the tag's own value incomplete; bam_aux_next :4823, bam_aux_get :4841-4842)
+constexpr int64_t CORRUPT = INT64_MIN + 1;
 __device__ __forceinline__ int64_t aux_get_scalar(const uint8_t *u, int64_t a0, int64_t end, uint32_t t0, uint32_t t1) {
     if (end - a0 <= 2) return NONE;
     int64_t s = a0 + 2;
@@ -97,12 +99,13 @@ __device__ __forceinline__ int64_t aux_get_scalar(const uint8_t *u, int64_t a0, 
         bool complete;
         int64_t nx = skip_aux_scalar(u, s, end, &complete);
         if (ld8(u, s - 2) == t0 && ld8(u, s - 1) == t1) {
-            if (nx == NONE) return NONE;
+            if (nx == NONE) return CORRUPT;
             uint32_t ty = ld8(u, s);
-            if ((ty == 'Z' || ty == 'H') && !complete) return NONE;
+            if ((ty == 'Z' || ty == 'H') && !complete) return CORRUPT;
             return s;
         }
-        if (nx == NONE || end - nx <= 2) return NONE;
+        if (nx == NONE) return CORRUPT;
+        if (end - nx <= 2) return NONE;
         s = nx + 2;
     }
 }
@@ -155,6 +158,7 @@ __device__ __forceinline__ int parse_record(const uint8_t *u, int64_t off, int64
     // bam_tag2cigar (sam.c:675-730): fast-path test first
     if (r.n_cigar && ld32u(u, r.cigar) == (4u | ((uint32_t)r.l_qseq << 4)) && r.tid >= 0 && r.pos >= 0) {
         int64_t CG = aux_get_scalar(u, r.aux, r.end, 'C', 'G');
+        if (CG == CORRUPT) return -4;       // bam_tag2cigar: bad aux data (errno != ENOENT, sam.c:690-694) -> bam_read1 returns -4 (:837-838)
         if (CG != NONE && ld8(u, CG) == 'B' && (ld8(u, CG + 1) == 'I' || ld8(u, CG + 1) == 'i')) {
             uint32_t CG_len = ld32u(u, CG + 2);
             if (CG_len >= r.n_cigar && CG_len < (1u << 29)) {

@@ -397,3 +397,24 @@ def test_files_whose_blocks_do_not_start_records_are_not_cut(tmp_path):
         rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, "--hash", env=env)
         assert rc_r == 0 and rc_o == 0, err_o
         assert out_o == out_r, path
+
+
+def test_corrupt_aux_behind_a_placeholder_cigar_ends_the_scan_like_htslib(tmp_path):
+    """bam_tag2cigar's fast path (first CIGAR op = l_seq S) looks for a CG tag; aux data that is broken in front of it (or a
+    CG value cut short) is "bad aux data": bam_tag2cigar returns -1 (sam.c:690-694), bam_read1 -4, the reference scan ends there."""
+    import struct
+    from tests.util import aux_tag, bam_header, bam_record
+    good = [bam_record(b"g%d" % i, 0, 0, i, 1, [(4, "M")], seq="ACGT", qual=[1] * 4) for i in range(40)]
+    cases = {"unknown_type_in_front": aux_tag("NM", "C", 1) + b"ZZ?" + aux_tag("AS", "C", 9),
+             "cg_value_cut_short": aux_tag("NM", "C", 1) + b"CGBI" + struct.pack("<I", 5) + struct.pack("<II", 1, 2),
+             "no_cg_at_all": aux_tag("NM", "C", 1) + aux_tag("AS", "C", 9),
+             "corrupt_behind_cg": b"CGBI" + struct.pack("<I", 2) + struct.pack("<II", (3 << 4) | 0, (2 << 4) | 1) + b"ZZ?x"}
+    for name, aux in cases.items():
+        placeholder = bam_record(b"ph", 0, 0, 7, 1, [(5, "S"), (9, "N")], seq="ACGTA", qual=[2] * 5, aux=aux)
+        path = str(tmp_path / f"{name}.bam")
+        open(path, "wb").write(util.make_bgzf(bam_header([(b"c1", 100000)]) + b"".join(good[:25]) + placeholder + b"".join(good[25:])))
+        (rc_r, out_r, _), (rc_o, out_o, err_o) = both("read_bam", path)
+        assert rc_r == 0 and rc_o == 0, err_o
+        assert out_o == out_r, name
+        n = len(out_r.splitlines()) - 1
+        assert n == (41 if name in ("no_cg_at_all", "corrupt_behind_cg") else 25), (name, n)

@@ -1,6 +1,8 @@
 """Multi-process host logic of the sharded scans, world_size 2 over gloo on CPU: every rank takes its
-share of the file (a contig group from the BAI index — BASELINE configs[3] — or a virtual-offset range), scans it (here:
-the oracle stands in for the GPU), and rank 0 merges in rank order.  The merged rows must be the unsharded scan.
+share of the file (a contig group from the BAI index — BASELINE configs[3] — computed by the PRODUCT's partition function
+dh_index_split_contigs, which is host code), scans it (here: the oracle stands in for the GPU; the -m gpu version of this test,
+tests/test_wire_gpu.py::test_cloned_handles_scan_ranges_that_merge_to_the_sequential_scan, merges real dh_bam_next_batch output),
+and rank 0 merges in rank order.  The merged rows must be the unsharded scan.
 No collective on the data path: torch.distributed only carries the barrier, the max-over-ranks time and the test's gather."""
 import os
 import sys
@@ -15,17 +17,12 @@ from tests import util
 REF_DUMP = os.path.join(util.ROOT, "harness", "_bin", "ref_dump")
 
 
-def contig_bounds(weights, n_parts):
-    """The balanced contiguous partition dh_bam_split_contigs computes (duckhts_b200/csrc/dh_bam.cu), restated."""
-    pre = np.concatenate([[0], np.cumsum(weights)])
-    out = [0]
-    for p in range(1, n_parts):
-        target = int(pre[-1]) // n_parts * p
-        t = int(np.searchsorted(pre, target, side="left"))
-        if t > 0 and target - pre[t - 1] < pre[min(t, len(weights))] - target:
-            t -= 1
-        out.append(min(max(t, out[-1]), len(weights)))
-    return out + [len(weights)]
+def product_bounds(bai, n_parts):
+    """The partition the product computes: dh_index_split_contigs (duckhts_b200/csrc/dh_bam.cu) on the BAI image -- host code of
+    libduckhts_cuda.so, no GPU involved (a BAI is parsed on the host)."""
+    import duckhts_b200 as dh
+    with dh.Index(None, bai) as ix:
+        return ix.split_contigs(n_parts)
 
 
 def worker(rank, world, port, path, q):
@@ -37,9 +34,7 @@ def worker(rank, world, port, path, q):
     bai = np.fromfile(path + ".bai", dtype=np.uint8)
     rc, infl, _ = orc.bgzf_inflate(img)
     dec = orc.bam_decode(infl, [])
-    n_ref = len(dec["ref_names"])
-    weights = [int(np.sum(dec["tid"] == t)) for t in range(n_ref)]      # stands in for the index's compressed spans
-    bounds = contig_bounds(weights, world)
+    bounds = product_bounds(bai, world)          # every rank computes the same partition from the index, no communication
     dist.barrier()
     rows = orc.contig_scan_rows(img, bai, dec, bounds[rank], bounds[rank + 1])
     gathered = [None] * world
@@ -72,8 +67,13 @@ def test_contig_group_shards_merge_in_rank_order_world2():
     assert mx >= n / 2
 
 
-def test_contig_bounds_partition_is_contiguous_and_balanced():
-    w = [10, 10, 10, 10, 40, 10, 10]
-    b = contig_bounds(w, 4)
-    assert b[0] == 0 and b[-1] == 7 and all(x <= y for x, y in zip(b, b[1:]))
-    assert contig_bounds([5] * 22, 8)[-1] == 22 and len(contig_bounds([5] * 22, 8)) == 9
+@pytest.mark.skipif(not util.have_gen(), reason="generator binary absent")
+def test_product_partition_is_contiguous_balanced_and_covers_every_contig():
+    path = util.synth_path("bam", n_records=6000, seed=41, paired=True, extra=("--unplaced", "10"), index=True)
+    bai = np.fromfile(path + ".bai", dtype=np.uint8)
+    for parts in (1, 2, 3, 8, 22, 40):
+        b = product_bounds(bai, parts)
+        assert len(b) == parts + 1 and b[0] == 0 and b[-1] == 22 and all(x <= y for x, y in zip(b, b[1:]))
+    b8 = product_bounds(bai, 8)
+    sizes = [y - x for x, y in zip(b8, b8[1:])]
+    assert max(sizes) <= 5 and min(sizes) >= 1          # 22 equal contigs over 8 parts: 2 or 3 (4 at a rounding edge) each
