@@ -264,7 +264,8 @@ def test_worker_threads_return_the_reference_rows(threads):
 def test_one_query_over_several_pipelines_keeps_file_order():
     """One source per listed device (here: the same GPU three times), ranges from dh_bam_split / contig groups from
     dh_bam_split_contigs; one scan thread walks the sources in order = the reference's row order, cell for cell."""
-    env = {"DUCKHTS_DEVICES": "0,0,0", "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "4096"}
+    # DUCKHTS_TEST_DEVICES=0,1,... runs this on real GPUs (a multi-GPU box); the default uses GPU 0 three times
+    env = {"DUCKHTS_DEVICES": os.environ.get("DUCKHTS_TEST_DEVICES", "0,0,0"), "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "4096"}
     seq = util.synth_path("bam", n_records=60000, seed=31, paired=True)
     idx = util.synth_path("bam", n_records=30000, seed=31, paired=True, extra=("--unplaced", "25"), index=True)
     for path in (seq, idx, os.path.join(GOLD, "range.bam")):
@@ -291,7 +292,7 @@ def test_invalid_record_in_an_early_range_ends_the_whole_scan(tmp_path):
     blocks = [util.bgzf_block(bam_header([(b"c1", 100000)]))] + [util.bgzf_block(b"".join(recs[i:i + 50])) for i in range(0, len(recs), 50)]
     path = str(tmp_path / "bad.bam")
     open(path, "wb").write(b"".join(blocks) + util.BGZF_EOF)
-    env = {"DUCKHTS_DEVICES": "0,0,0,0", "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "256"}
+    env = {"DUCKHTS_DEVICES": os.environ.get("DUCKHTS_TEST_DEVICES", "0,0,0,0"), "DUCKHTS_MIN_SHARD_BYTES": "1", "DUCKHTS_BATCH_ROWS": "256"}
     rc_r, out_r, _ = run(REF_EXT, "read_bam", path)
     rc_o, out_o, err_o = run(OUR_EXT, "read_bam", path, env=env)
     assert rc_r == 0 and rc_o == 0, err_o

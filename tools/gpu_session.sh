@@ -14,6 +14,18 @@ for stage in "$@"; do
     bench) timeout 1500 python bench.py --steps 3 --warmup 3 > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"; cat gpurun_out/${T}_bench.json; tail -5 gpurun_out/${T}_bench.err ;;
     ref) timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_reference_bench.json 2> gpurun_out/${T}_reference_bench.err; cat gpurun_out/${T}_reference_bench.json; tail -3 gpurun_out/${T}_reference_bench.err ;;
     ncu) bash tools/gpu_ncu1.sh ;;
+    multi) # N GPUs (gpurun --gpus N; NG=N): bench.py under torchrun (weak + strong scaling lines), then ONE query over N GPUs through the extension
+      NG=${NG:-2}
+      timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $NG --steps 2 --warmup 2 --bcf-tiles 10 \
+        > gpurun_out/${T}_bench_n${NG}.json 2> gpurun_out/${T}_bench_n${NG}.err; echo "bench n=$NG exit $?"; cat gpurun_out/${T}_bench_n${NG}.json; tail -3 gpurun_out/${T}_bench_n${NG}.err
+      python tools/make_tiled.py /tmp/duckhts_b200_cache/tiled100m.bam 100e6 > gpurun_out/${T}_multi_ext.log 2>&1
+      DEVS=$(python -c "print(','.join(str(i) for i in range($NG)))")
+      for devs in 0 $DEVS; do
+        DUCKHTS_DEVICES=$devs DUCKHTS_PROFILE=1 harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam /tmp/duckhts_b200_cache/tiled100m.bam standard_tags=true --cols 0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14 --threads 16 --time --repeat 3 2>&1 | sed "s/^/[devices $devs] /"
+        DUCKHTS_DEVICES=$devs harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam /tmp/duckhts_b200_cache/tiled100m.bam standard_tags=true --cols 0,1,3,9,47 --threads 1 --hash 2>&1 | sed "s/^/[devices $devs, ordered hash] /"
+      done >> gpurun_out/${T}_multi_ext.log 2>&1
+      rm -f /tmp/duckhts_b200_cache/tiled100m.bam; cat gpurun_out/${T}_multi_ext.log
+      DUCKHTS_TEST_DEVICES=$DEVS timeout 900 python -m pytest tests/test_ext_gpu.py -m gpu -q -k "several_pipelines or early_range or worker_threads" > gpurun_out/${T}_pytest_multi.log 2>&1; tail -3 gpurun_out/${T}_pytest_multi.log ;;
     extprof) # where the scan threads of the extension spend their time (DUCKHTS_PROFILE), on the bench unit, 1 / 4 / 16 threads, both layouts
       U=$(python -c "import bench,os; print(bench.gen_unit('bam', 4000000, 0x9E3779B97F4A7C15, True, os.cpu_count()))")
       for t in 1 4 16; do for lay in compact duckdb; do
