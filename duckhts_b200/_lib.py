@@ -106,6 +106,8 @@ SIGNATURES = {
     "dh_bam_rg_sample": (C.c_char_p, [C.c_void_p, C.c_int32]),
     "dh_bam_clone": (C.c_void_p, [C.c_void_p, C.c_void_p]),
     "dh_bam_set_filter": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "dh_bam_index_build": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
+    "dh_free": (None, [C.c_void_p]),
     "dh_index_split_contigs": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32)]),
     "dh_bgzf_inflate_fd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(InflateStats)]),
     "dh_bcf_set_slots": (C.c_int, [C.c_void_p, C.c_int]),

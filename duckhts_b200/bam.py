@@ -188,6 +188,15 @@ class BamFile:
             out.append((C.string_at(p, n.value), lib().dh_bam_rg_sample(self.h, i)))
         return out
 
+    def index_build(self):
+        """dh_bam_index_build: the BAI image of this (coordinate-sorted) file, built from one GPU scan -> bytes."""
+        p, n = C.c_void_p(), C.c_uint64(0)
+        check(lib().dh_bam_index_build(self.h, C.byref(p), C.byref(n)), "dh_bam_index_build")
+        try:
+            return C.string_at(p.value, n.value)
+        finally:
+            lib().dh_free(p)
+
     def acquire(self):
         """dh_bam_acquire_batch: the batch stays valid until release(batch.slot)."""
         b = BamBatch()

@@ -1358,6 +1358,92 @@ __global__ void __launch_bounds__(128) bam_auxmap_kernel(const __grid_constant__
     }
 }
 
+// =======================================================================================================
+// N2: runs of equal (tid, bin) + linear index for bam_index (htslib/hts.c hts_idx_push :2553-2642; sam_index, sam.c:989-1027)
+// =======================================================================================================
+__device__ __forceinline__ uint32_t reg2bin_bai(int64_t beg, int64_t end) {   // hts_reg2bin(beg, end, 14, 5), htslib/hts.h
+    --end;
+    if (beg >> 14 == end >> 14) return (uint32_t)(4681 + (beg >> 14));
+    if (beg >> 17 == end >> 17) return (uint32_t)(585 + (beg >> 17));
+    if (beg >> 20 == end >> 20) return (uint32_t)(73 + (beg >> 20));
+    if (beg >> 23 == end >> 23) return (uint32_t)(9 + (beg >> 23));
+    if (beg >> 26 == end >> 26) return (uint32_t)(1 + (beg >> 26));
+    return 0u;
+}
+__global__ void __launch_bounds__(128) bam_index_kernel(const IndexParams p, const ScanTables t) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n) return;
+    const uint32_t count = p.walk[i].count;
+    const int64_t bstart = p.blk_start[i];
+    const uint16_t *rec = p.rec + ((bstart - p.rec_bias) / 36 + (int64_t)i);
+    IdxBlock ob;
+    ob.base = ob.n_runs = 0;
+    ob.first_tid = ob.last_tid = -2;
+    ob.first_beg = ob.last_beg = 0;
+    ob.err = 0;
+    ob.count = count;
+    // pass 0 counts the runs, pass 1 writes them (one atomicAdd per block keeps a block's runs together and in order)
+    for (int pass = 0; pass < 2 && count; ++pass) {
+        uint32_t nruns = 0, cur_bin = 0xffffffffu, nm = 0, nu = 0;
+        int32_t cur_tid = -2;
+        int64_t last_beg = 0;
+        IdxRun *out = p.runs + ob.base;
+        for (uint32_t j = 0; j < count; ++j) {
+            Rec r;
+            const int64_t off = bstart + rec[j];
+            parse_record(p.u, off, INT64_MAX / 2, false, t.n_ref, r);
+            int64_t beg = r.pos, rl = (r.flag & 4u) ? 0 : r.rlen;          // bam_endpos (sam.c:519-524)
+            if (rl == 0) rl = 1;
+            int64_t end = beg + rl;
+            if (r.tid < 0) { beg = -1; end = 0; }
+            if (pass == 0) {
+                if (j == 0) { ob.first_tid = r.tid; ob.first_beg = beg; }
+                else if (r.tid == cur_tid && r.tid >= 0 && last_beg > beg) ob.err = ob.err ? ob.err : 1;   // unsorted positions
+                if (r.tid >= 0 && (beg > (1ll << 29) || end > (1ll << 29))) ob.err = ob.err ? ob.err : 2;
+                ob.last_tid = r.tid;
+            }
+            if (r.tid >= 0) {                                                  // shoehorn [-1, 0) into the leftmost window (hts.c:2625-2627)
+                if (beg < 0) beg = 0;
+                if (end <= 0) end = 1;
+            }
+            last_beg = beg;                                                    // z.last_coor is the clamped start (hts.c:2641)
+            if (pass == 0) ob.last_beg = beg;
+            const uint32_t bin = reg2bin_bai(beg, end);
+            if (r.tid != cur_tid || bin != cur_bin) {
+                if (pass == 1 && nruns) { IdxRun &q = out[nruns - 1]; q.n_mapped = nm; q.n_unmapped = nu; }
+                if (pass == 1) { IdxRun &q = out[nruns]; q.start_u = (uint64_t)(p.u_base + off); q.tid = r.tid; q.bin = bin; q.n_mapped = q.n_unmapped = 0; }
+                ++nruns;
+                cur_tid = r.tid;
+                cur_bin = bin;
+                nm = nu = 0;
+            }
+            if (r.flag & 4u) ++nu; else ++nm;
+            if (pass == 1 && r.tid >= 0) {
+                // linear index (insert_to_l, hts.c:2338-2362): the first record that touches a window, in file order
+                const int64_t w0 = beg >> 14, w1 = (end - 1) >> 14;
+                const uint64_t me = (uint64_t)(p.u_base + off);
+                for (int64_t w = w0; w <= w1; ++w) {
+                    if ((uint64_t)w >= p.lin_n[r.tid]) { p.blocks[i].err = 3; break; }
+                    atomicMin(&p.lin[p.lin_base[r.tid] + w], (unsigned long long)me);
+                }
+            }
+        }
+        if (pass == 0) {
+            ob.n_runs = nruns;
+            ob.base = atomicAdd(p.counter, nruns);
+            if (ob.base + nruns > p.run_cap) { ob.err = 4; ob.n_runs = 0; p.blocks[i] = ob; return; }
+            p.blocks[i] = ob;
+        } else if (nruns) { IdxRun &q = out[nruns - 1]; q.n_mapped = nm; q.n_unmapped = nu; }
+    }
+    if (!count) p.blocks[i] = ob;
+}
+
+cudaError_t launch_bam_index(const IndexParams &p, const ScanTables &t, cudaStream_t stream) {
+    if (p.n == 0) return cudaSuccess;
+    bam_index_kernel<<<(p.n + 127u) / 128u, 128, 0, stream>>>(p, t);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream) {
     if (p.n == 0) return cudaSuccess;
     bam_walk_kernel<<<(p.n + 127u) / 128u, 128, 0, stream>>>(p, t);

@@ -122,6 +122,40 @@ struct AuxMapParams {
     uint64_t heap_host;
 };
 
+// ---- N2: index build (bam_index) -----------------------------------------------------------------------------------------
+// hts_idx_push (htslib/hts.c:2553-2642) closes a chunk whenever the bin changes: the file is a sequence of RUNS of records with the
+// same (tid, bin).  One thread per BGZF block emits the runs of its records (the host merges runs that continue across blocks) and
+// feeds the linear index (first record start per 16 kb window = atomicMin over inflated offsets, which order like virtual offsets).
+struct IdxRun {
+    uint64_t start_u;             // inflated offset (relative to the scan's block table) of the run's first record
+    int32_t tid;
+    uint32_t bin;                 // hts_reg2bin(beg, end, 14, 5); 4680 for reads without a contig
+    uint32_t n_mapped, n_unmapped;
+};
+struct IdxBlock {                 // per walk block
+    uint32_t base, n_runs;        // its runs: runs[base .. base + n_runs)
+    int32_t first_tid, last_tid;  // sortedness across blocks (hts_idx_push :2597-2616)
+    int64_t first_beg, last_beg;
+    int32_t err;                  // 0; 1 unsorted positions; 2 coordinate beyond 2^29 (hts_idx_check_range); 3 linear index too short
+    uint32_t count;
+};
+struct IndexParams {
+    const uint8_t *u;
+    const BlockWalk *walk;
+    const int64_t *blk_start;
+    const uint16_t *rec;
+    int64_t rec_bias;
+    uint32_t n;                   // walk blocks (incl. the carry pseudo-block 0)
+    int64_t u_base;               // table-relative inflated offset of segment offset 0
+    IdxRun *runs;
+    uint32_t run_cap;
+    unsigned int *counter;        // runs claimed so far
+    IdxBlock *blocks;
+    unsigned long long *lin;      // linear index: per contig lin_n[tid] windows at lin_base[tid], initialised to ~0
+    const uint32_t *lin_base, *lin_n;
+    int32_t n_ref;
+};
+cudaError_t launch_bam_index(const IndexParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_auxmap(const AuxMapParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream);
 cudaError_t launch_bam_decode(const DecodeParams &p, const ScanTables &t, cudaStream_t stream);

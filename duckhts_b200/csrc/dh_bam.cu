@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <deque>
+#include <map>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1418,6 +1419,237 @@ int dh_bam_batch_checksum(dh_bam *b, const dh_bam_batch *batch, uint64_t *sums) 
         bam_checksum_host(cp, nthr);
         for (int c = 0; c < ncols; ++c) sums[c] += local[c];
     }
+    return DH_OK;
+}
+
+// ---- N2: bam_index -----------------------------------------------------------------------------------------------------------
+void dh_free(void *p) { free(p); }
+
+int dh_bam_index_build(dh_bam *b, uint8_t **bai, uint64_t *bai_size) {
+    if (!b || !bai || !bai_size || b->kind != 0) { set_error("dh_bam_index_build: bad arguments"); return DH_EINVAL; }
+    std::lock_guard<std::mutex> lk(b->mu);
+    *bai = nullptr;
+    *bai_size = 0;
+    // the scan: every record, no column (nothing is decoded, only the boundary walk runs)
+    const uint64_t keep_mask = b->col_mask;
+    const bool keep_aux = b->aux_map;
+    const uint32_t fr = b->flag_require, fe = b->flag_exclude, mq = b->min_mapq;
+    b->col_mask = 0;
+    b->aux_map = false;
+    b->flag_require = b->flag_exclude = b->min_mapq = 0;
+    b->filt_mode = 0;
+    b->filt.clear();
+    b->pending.clear();
+    int rc = upload_tables(b);
+    auto restore = [&]() { b->col_mask = keep_mask; b->aux_map = keep_aux; b->flag_require = fr; b->flag_exclude = fe; b->min_mapq = mq; upload_tables(b); b->scanning = false; };
+    if (rc == DH_OK) rc = begin_range(b, 0, UINT64_MAX, true);
+    if (rc != DH_OK) { restore(); return rc; }
+    const int32_t n_ref = (int32_t)b->ref_names.size();
+    // linear index on the device: per contig the windows its length needs, plus slack for reads that run over the end
+    std::vector<uint32_t> lin_base((size_t)n_ref + 1, 0), lin_n((size_t)std::max(n_ref, 1), 0);
+    for (int32_t t = 0; t < n_ref; ++t) {
+        lin_n[(size_t)t] = (uint32_t)std::min<uint64_t>(32769, ((uint64_t)b->ref_lens[(size_t)t] >> 14) + 64);
+        lin_base[(size_t)t + 1] = lin_base[(size_t)t] + lin_n[(size_t)t];
+    }
+    const size_t lin_total = lin_base[(size_t)n_ref];
+    DevBuf d_lin, d_lin_base, d_lin_n, d_runs, d_blocks, d_counter;
+    PinBuf h_runs, h_blocks;
+    std::vector<IdxRun> runs;                 // the file as runs of equal (tid, bin), merged across blocks
+    int64_t prev_tid = -2, prev_beg = 0;
+    int err = 0;
+    auto cleanup = [&]() { d_lin.release(); d_lin_base.release(); d_lin_n.release(); d_runs.release(); d_blocks.release(); d_counter.release(); h_runs.release(); h_blocks.release(); };
+    if ((rc = d_lin.reserve(std::max<size_t>(1, lin_total) * 8)) != DH_OK || (rc = d_lin_base.reserve(((size_t)n_ref + 1) * 4)) != DH_OK ||
+        (rc = d_lin_n.reserve(std::max<size_t>(1, (size_t)n_ref) * 4)) != DH_OK || (rc = d_counter.reserve(64)) != DH_OK) { cleanup(); restore(); return rc; }
+    cudaStream_t sk = s_comp(b);
+    cudaMemsetAsync(d_lin.p, 0xff, std::max<size_t>(1, lin_total) * 8, sk);
+    cudaMemcpyAsync(d_lin_base.p, lin_base.data(), ((size_t)n_ref + 1) * 4, cudaMemcpyHostToDevice, sk);
+    if (n_ref) cudaMemcpyAsync(d_lin_n.p, lin_n.data(), (size_t)n_ref * 4, cudaMemcpyHostToDevice, sk);
+    for (;;) {
+        const int w = have_work(b);            // inflates and walks the next segment (and starts the ones behind it)
+        if (w < 0) { rc = w; break; }
+        if (w == 0) break;
+        SegSlot &s = b->ss[b->cur_seg % NSEG];
+        const uint32_t n = (uint32_t)(s.b1 - s.b0) + 1;
+        uint64_t n_rec = 0;
+        const BlockWalk *hw = (const BlockWalk *)s.h_walk.p;
+        for (uint32_t i = 0; i < n; ++i) n_rec += hw[i].count;
+        if ((rc = d_runs.reserve(std::max<uint64_t>(1, n_rec) * sizeof(IdxRun))) != DH_OK || (rc = d_blocks.reserve((size_t)n * sizeof(IdxBlock))) != DH_OK ||
+            (rc = h_runs.reserve(std::max<uint64_t>(1, n_rec) * sizeof(IdxRun))) != DH_OK || (rc = h_blocks.reserve((size_t)n * sizeof(IdxBlock))) != DH_OK) break;
+        IndexParams ip;
+        memset(&ip, 0, sizeof ip);
+        ip.u = (const uint8_t *)s.out.p + b->carry_cap;
+        ip.walk = hw;
+        ip.blk_start = (const int64_t *)s.h_blk_start.p;
+        ip.rec = (const uint16_t *)s.rec.p;
+        ip.rec_bias = s.rec_bias;
+        ip.n = n;
+        ip.u_base = (int64_t)b->bt.uoff[s.b0];
+        ip.runs = (IdxRun *)d_runs.p;
+        ip.run_cap = (uint32_t)std::min<uint64_t>(n_rec, 0xffffffffu);
+        ip.counter = (unsigned int *)d_counter.p;
+        ip.blocks = (IdxBlock *)d_blocks.p;
+        ip.lin = (unsigned long long *)d_lin.p;
+        ip.lin_base = (const uint32_t *)d_lin_base.p;
+        ip.lin_n = (const uint32_t *)d_lin_n.p;
+        ip.n_ref = n_ref;
+        // only the blocks the walk accepted count: a stop (invalid record) ends the index like it ends sam_index
+        cudaMemsetAsync(d_counter.p, 0, 4, sk);
+        cudaMemsetAsync(d_blocks.p, 0, (size_t)n * sizeof(IdxBlock), sk);
+        cudaError_t ce = launch_bam_index(ip, b->tabs, sk);
+        b->ctx->launches++;
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_blocks.p, d_blocks.p, (size_t)n * sizeof(IdxBlock), cudaMemcpyDeviceToHost, sk);
+        if (ce == cudaSuccess && n_rec) ce = cudaMemcpyAsync(h_runs.p, d_runs.p, n_rec * sizeof(IdxRun), cudaMemcpyDeviceToHost, sk);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(sk);
+        if (ce != cudaSuccess) { rc = cuda_fail(ce, "bam_index_kernel"); break; }
+        // blocks in order, up to the batches the walk planned (rows behind an invalid record are not part of the file for htslib)
+        uint32_t last_blk = 0;
+        for (auto &bb : b->batches) last_blk = std::max(last_blk, bb.b_hi);
+        const IdxBlock *hb = (const IdxBlock *)h_blocks.p;
+        const IdxRun *hr = (const IdxRun *)h_runs.p;
+        for (uint32_t i = 0; i < last_blk && !err; ++i) {
+            const IdxBlock &ib = hb[i];
+            if (!ib.count) continue;
+            if (ib.err) { err = ib.err; break; }
+            // sortedness across blocks (hts_idx_push :2597-2616)
+            if (prev_tid != -2 && ib.first_tid == prev_tid && ib.first_tid >= 0 && prev_beg > ib.first_beg) { err = 1; break; }
+            prev_tid = ib.last_tid;
+            prev_beg = ib.last_beg;
+            for (uint32_t q = 0; q < ib.n_runs; ++q) {
+                const IdxRun &r = hr[ib.base + q];
+                if (!runs.empty() && runs.back().tid == r.tid && runs.back().bin == r.bin) { runs.back().n_mapped += r.n_mapped; runs.back().n_unmapped += r.n_unmapped; }
+                else runs.push_back(r);
+            }
+        }
+        b->next_batch_i = b->batches.size();   // nothing to decode: on to the next segment
+        if (err) break;
+    }
+    // the linear index comes back once
+    std::vector<uint64_t> lin(std::max<size_t>(1, lin_total));
+    if (rc == DH_OK && !err && lin_total) {
+        cudaError_t ce = cudaMemcpy(lin.data(), d_lin.p, lin_total * 8, cudaMemcpyDeviceToHost);
+        if (ce != cudaSuccess) rc = cuda_fail(ce, "linear index copy");
+    }
+    const int final_status = b->final_status;
+    const uint64_t file_end = b->fd >= 0 ? b->fsize : b->bt.end_off;
+    cleanup();
+    restore();
+    if (rc != DH_OK) return rc;
+    if (err) {
+        set_error(err == 1 ? "unsorted positions: bam_index needs a coordinate-sorted file" : err == 2 ? "a coordinate beyond 2^29 cannot be stored in a BAI index (use CSI)"
+                  : err == 3 ? "a read lies far beyond the end of its reference sequence" : "internal: run buffer overflow");
+        return DH_EFORMAT;
+    }
+    if (final_status < -1 || b->truncated) { set_error("corrupted or truncated BAM file (record status %d)", final_status); return DH_EFORMAT; }   // sam_index: ret < -1 -> error
+    // ---- hts_idx_push / hts_idx_finish on the run sequence ----
+    const BlockTable &bt = b->bt;
+    // bgzf_tell with the stream read up to inflated offset u.  A read that ends exactly at a block end leaves the stream at (address of
+    // the block that follows, 0) (bgzf_read, htslib/bgzf.c: block_address = bgzf_htell() once block_offset == block_length), so the
+    // header's last block never appears when the header fills it, and the offset after the last record is the EOF marker's address.
+    auto tell = [&](uint64_t u) -> uint64_t {
+        const size_t nb = bt.blocks.size();
+        if (nb == 0) return file_end << 16;
+        if (u == 0) return bt.blocks[0].coffset << 16;
+        const size_t blk = (size_t)(std::upper_bound(bt.uoff.begin(), bt.uoff.end(), u - 1) - bt.uoff.begin()) - 1;   // holds byte u - 1
+        if (blk >= nb) return file_end << 16;
+        if (u < bt.uoff[blk + 1]) return (bt.blocks[blk].coffset << 16) | (u - bt.uoff[blk]);
+        return (blk + 1 < nb ? bt.blocks[blk + 1].coffset : file_end) << 16;
+    };
+    // contigs must form one group each; placed reads may not follow reads without a contig (:2599-2610)
+    {
+        std::vector<uint8_t> seen((size_t)std::max(n_ref, 1), 0);
+        int32_t cur = -2;
+        bool no_coor = false;
+        for (auto &r : runs) {
+            if (r.tid == cur) continue;
+            if (r.tid >= 0 && (no_coor || seen[(size_t)r.tid])) { set_error(no_coor ? "reads without a contig are not in a single block at the end" : "chromosome blocks not continuous"); return DH_EFORMAT; }
+            if (r.tid >= 0) seen[(size_t)r.tid] = 1; else no_coor = true;
+            cur = r.tid;
+        }
+    }
+    const uint64_t final_offset = tell(bt.uoff.back());     // bgzf_tell after the read that met the end of the file (hts_idx_finish)
+    struct Chunk { uint64_t u, v; };
+    std::vector<std::map<uint32_t, std::vector<Chunk>>> bins((size_t)std::max(n_ref, 1));
+    struct Meta { uint64_t off_beg = 0, off_end = 0, n_mapped = 0, n_unmapped = 0; bool any = false; };
+    std::vector<Meta> meta((size_t)std::max(n_ref, 1));
+    uint64_t n_no_coor = 0;
+    for (size_t i = 0; i < runs.size(); ++i) {
+        const IdxRun &r = runs[i];
+        const uint64_t beg = tell(r.start_u), end = i + 1 < runs.size() ? tell(runs[i + 1].start_u) : final_offset;
+        if (r.tid < 0) { n_no_coor += (uint64_t)r.n_mapped + r.n_unmapped; continue; }
+        bins[(size_t)r.tid][r.bin].push_back(Chunk{beg, end});
+        Meta &m = meta[(size_t)r.tid];
+        if (!m.any) { m.any = true; m.off_beg = beg; }
+        m.off_end = end;
+        m.n_mapped += r.n_mapped;
+        m.n_unmapped += r.n_unmapped;
+    }
+    // hts_idx_finish: update_loff's backward fill of the linear index (:2433-2436), compress_binning (:2457-2508)
+    std::vector<std::vector<uint64_t>> lidx((size_t)std::max(n_ref, 1));
+    for (int32_t t = 0; t < n_ref; ++t) {
+        const uint64_t *src = lin.data() + lin_base[(size_t)t];
+        int64_t nwin = 0;
+        for (int64_t wv = (int64_t)lin_n[(size_t)t] - 1; wv >= 0; --wv) if (src[wv] != UINT64_MAX) { nwin = wv + 1; break; }
+        auto &L = lidx[(size_t)t];
+        L.resize((size_t)nwin);
+        for (int64_t wv = 0; wv < nwin; ++wv) L[(size_t)wv] = src[wv] == UINT64_MAX ? UINT64_MAX : tell(src[wv]);
+        for (int64_t wv = nwin - 2; wv >= 0; --wv) if (L[(size_t)wv] == UINT64_MAX) L[(size_t)wv] = L[(size_t)wv + 1];
+        auto &B = bins[(size_t)t];
+        static const uint32_t LEVEL_FIRST[6] = {0, 1, 9, 73, 585, 4681};
+        for (int l = 5; l > 0; --l) {
+            const uint32_t start = LEVEL_FIRST[l];
+            std::vector<uint32_t> keys;
+            for (auto &kv : B) if (kv.first >= start && kv.first < 37449) keys.push_back(kv.first);
+            for (uint32_t k : keys) {
+                auto it = B.find(k);
+                if (it == B.end()) continue;
+                auto &pl = it->second;
+                if (l < 5 && pl.size() > 1) std::sort(pl.begin(), pl.end(), [](const Chunk &a, const Chunk &c) { return a.u < c.u; });
+                if ((pl.back().v >> 16) - (pl.front().u >> 16) < 0x10000ull) {      // HTS_MIN_MARKER_DIST
+                    const uint32_t parent = (k - 1) >> 3;
+                    auto pit = B.find(parent);
+                    if (pit == B.end()) continue;
+                    pit->second.insert(pit->second.end(), pl.begin(), pl.end());
+                    B.erase(it);
+                }
+            }
+        }
+        auto z = B.find(0);
+        if (z != B.end()) std::sort(z->second.begin(), z->second.end(), [](const Chunk &a, const Chunk &c) { return a.u < c.u; });
+        for (auto &kv : B) {       // merge adjacent chunks that start from the same BGZF block
+            auto &pl = kv.second;
+            size_t m = 0;
+            for (size_t q = 1; q < pl.size(); ++q) {
+                if ((pl[m].v >> 16) >= (pl[q].u >> 16)) { if (pl[m].v < pl[q].v) pl[m].v = pl[q].v; }
+                else pl[++m] = pl[q];
+            }
+            pl.resize(m + 1);
+        }
+    }
+    // ---- hts_idx_save: "BAI\1", n_ref, per contig {n_bin, {bin, n_chunk, chunks}, n_intv, ioffsets}, n_no_coor ----
+    std::vector<uint8_t> out;
+    auto put32 = [&](uint32_t v) { for (int q = 0; q < 4; ++q) out.push_back((uint8_t)(v >> (8 * q))); };
+    auto put64 = [&](uint64_t v) { for (int q = 0; q < 8; ++q) out.push_back((uint8_t)(v >> (8 * q))); };
+    out.insert(out.end(), {'B', 'A', 'I', 1});
+    put32((uint32_t)n_ref);
+    for (int32_t t = 0; t < n_ref; ++t) {
+        auto &B = bins[(size_t)t];
+        const Meta &m = meta[(size_t)t];
+        put32((uint32_t)(B.size() + (m.any ? 1 : 0)));
+        for (auto &kv : B) {
+            put32(kv.first);
+            put32((uint32_t)kv.second.size());
+            for (auto &c : kv.second) { put64(c.u); put64(c.v); }
+        }
+        if (m.any) { put32(37450u); put32(2u); put64(m.off_beg); put64(m.off_end); put64(m.n_mapped); put64(m.n_unmapped); }
+        put32((uint32_t)lidx[(size_t)t].size());
+        for (uint64_t v : lidx[(size_t)t]) put64(v);
+    }
+    put64(n_no_coor);
+    uint8_t *res = (uint8_t *)malloc(out.size());
+    if (!res) { set_error("out of memory"); return DH_ENOMEM; }
+    memcpy(res, out.data(), out.size());
+    *bai = res;
+    *bai_size = out.size();
     return DH_OK;
 }
 

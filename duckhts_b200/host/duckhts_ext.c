@@ -1441,6 +1441,85 @@ static void register_bgunzip(duckdb_connection con) {
     api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_int); api.duckdb_destroy_logical_type(&t_bool);
 }
 
+/* ================================================================================================================
+ * bam_index — like the reference (src/hts_index_builder.c:110-160, 326-345): the index is built in bind (sam_index_build3 there,
+ * one GPU scan here: dh_bam_index_build) and the scan returns one row (success, index_path, index_format).  BAI only (min_shift 0).
+ * ================================================================================================================ */
+typedef struct { char *index_path; int emitted; } ix_bind_t;
+static void ix_bind_free(void *p) { ix_bind_t *g = (ix_bind_t *)p; if (g) { free(g->index_path); api.duckdb_free(g); } }
+static void bam_index_bind(duckdb_bind_info info) {
+    duckdb_value pv = api.duckdb_bind_get_parameter(info, 0);
+    char *path = api.duckdb_get_varchar(pv);
+    api.duckdb_destroy_value(&pv);
+    if (!path || !path[0]) { api.duckdb_bind_set_error(info, "bam_index requires a file path"); if (path) api.duckdb_free(path); return; }
+    char *index_path = named_varchar(info, "index_path");
+    const int64_t min_shift = named_int(info, "min_shift", 0);
+    char err[1200], out_path[4200];
+    err[0] = 0;
+    if (index_path) snprintf(out_path, sizeof out_path, "%s", index_path);
+    else snprintf(out_path, sizeof out_path, "%s.bai", path);
+    int devs[MAX_SOURCES];
+    device_list(devs);
+    dh_ctx *ctx = NULL;
+    dh_bam *bam = NULL;
+    uint8_t *bai = NULL;
+    uint64_t n = 0;
+    /* every failure reads like the reference's: "bam_index: failed to build index for PATH (error N)" with sam_index_build3's codes
+     * (-2 cannot open, -1 could not index, -4 could not save) */
+    int code = 0;
+    if (min_shift > 0) snprintf(err, sizeof err, "bam_index: CSI output (min_shift > 0) is not available in this build");
+    else if (!(ctx = ctx_acquire(devs[0]))) snprintf(err, sizeof err, "bam_index: no usable CUDA device (%s)", dh_last_error());
+    else if (!(bam = dh_bam_open_file(ctx, path))) code = -2;
+    else if (dh_bam_index_build(bam, &bai, &n) != DH_OK) code = -1;
+    else {
+        FILE *f = fopen(out_path, "wb");
+        if (!f || fwrite(bai, 1, n, f) != n) code = -4;
+        if (f && fclose(f) != 0) code = -4;
+    }
+    if (code) snprintf(err, sizeof err, "bam_index: failed to build index for %s (error %d)", path, code);
+    if (bai) dh_free(bai);
+    if (bam) dh_bam_close(bam);
+    if (ctx) ctx_release(ctx);
+    if (err[0]) api.duckdb_bind_set_error(info, err);
+    else {
+        duckdb_logical_type t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN), t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR);
+        api.duckdb_bind_add_result_column(info, "success", t_bool);
+        api.duckdb_bind_add_result_column(info, "index_path", t_varchar);
+        api.duckdb_bind_add_result_column(info, "index_format", t_varchar);
+        api.duckdb_destroy_logical_type(&t_bool); api.duckdb_destroy_logical_type(&t_varchar);
+        ix_bind_t *g = (ix_bind_t *)api.duckdb_malloc(sizeof *g);
+        g->index_path = strdup(out_path); g->emitted = 0;
+        api.duckdb_bind_set_bind_data(info, g, ix_bind_free);
+    }
+    api.duckdb_free(path);
+    if (index_path) api.duckdb_free(index_path);
+}
+static void bam_index_init(duckdb_init_info info) { ((ix_bind_t *)api.duckdb_init_get_bind_data(info))->emitted = 0; }
+static void bam_index_scan(duckdb_function_info info, duckdb_data_chunk output) {
+    ix_bind_t *g = (ix_bind_t *)api.duckdb_function_get_bind_data(info);
+    if (g->emitted) { api.duckdb_data_chunk_set_size(output, 0); return; }
+    ((bool *)api.duckdb_vector_get_data(api.duckdb_data_chunk_get_vector(output, 0)))[0] = true;
+    api.duckdb_vector_assign_string_element(api.duckdb_data_chunk_get_vector(output, 1), 0, g->index_path ? g->index_path : "");
+    api.duckdb_vector_assign_string_element(api.duckdb_data_chunk_get_vector(output, 2), 0, "BAI");
+    g->emitted = 1;
+    api.duckdb_data_chunk_set_size(output, 1);
+}
+static void register_bam_index(duckdb_connection con) {
+    duckdb_table_function tf = api.duckdb_create_table_function();
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER);
+    api.duckdb_table_function_set_name(tf, "bam_index");
+    api.duckdb_table_function_add_parameter(tf, t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "index_path", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "min_shift", t_int);
+    api.duckdb_table_function_add_named_parameter(tf, "threads", t_int);      /* accepted for compatibility */
+    api.duckdb_table_function_set_bind(tf, bam_index_bind);
+    api.duckdb_table_function_set_init(tf, bam_index_init);
+    api.duckdb_table_function_set_function(tf, bam_index_scan);
+    api.duckdb_register_table_function(con, tf);
+    api.duckdb_destroy_table_function(&tf);
+    api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_int);
+}
+
 /* ---- entry point (reference duckdb_capi/duckdb_extension.h:1179-1195) ------------------------------------------------ */
 __attribute__((visibility("default"))) bool duckhts_init_c_api(duckdb_extension_info info, struct duckdb_extension_access *access) {
     const duckdb_ext_api_v1 *host = (const duckdb_ext_api_v1 *)access->get_api(info, DUCKDB_EXT_ABI_VERSION);
@@ -1452,6 +1531,7 @@ __attribute__((visibility("default"))) bool duckhts_init_c_api(duckdb_extension_
     register_read_bam(con);
     register_read_bcf(con);
     register_bgunzip(con);
+    register_bam_index(con);
     api.duckdb_disconnect(&con);
     return true;
 }

@@ -305,6 +305,18 @@ int dh_index_split_contigs(const dh_index *idx, int n_parts, int32_t *tid_bounds
  * GPUs of a box: one handle per GPU, each scanning the range / contig group dh_bam_split(_contigs) gives it. */
 dh_bam *dh_bam_clone(const dh_bam *src, dh_ctx *ctx);
 
+/* ---- N2: index build ---------------------------------------------------------------------------------------------------
+ * Replaces bam_index(path) = sam_index_build3 -> sam_index (htslib/sam.c:989-1027: sam_read1 + hts_idx_push per record) ->
+ * hts_idx_finish -> hts_idx_save (htslib/hts.c:2400-2642, 2754-2860), src/hts_index_builder.c:110-160, for BAI (min_shift 0).
+ * The file is scanned once on the GPU (inflate + boundary walk; no column is decoded): a kernel emits the runs of records with
+ * equal (contig, bin) and the linear index, the host closes the chunks, applies hts_idx_finish's rules (bins whose chunks span
+ * less than 64 KB of file move to their parent, adjacent chunks of one BGZF block merge) and serialises the BAI.  The result has
+ * the bins, chunks, linear index, per-contig mapped / unmapped counts and n_no_coor htslib writes (bins in ascending order; htslib
+ * writes them in its hash table's order).  *bai is malloc'ed: free it with dh_free.  DH_EFORMAT: the file is not coordinate-sorted
+ * or a coordinate does not fit a BAI (2^29). */
+int dh_bam_index_build(dh_bam *b, uint8_t **bai, uint64_t *bai_size);
+void dh_free(void *p);
+
 /* ---- N3: predicate pushdown ------------------------------------------------------------------------------------------
  * Record filter evaluated in the boundary kernel next to the region test, so rejected records cost no row, no heap byte
  * and no PCIe byte.  A record passes iff (FLAG & flag_require) == flag_require, (FLAG & flag_exclude) == 0 and
