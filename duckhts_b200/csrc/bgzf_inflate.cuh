@@ -49,7 +49,7 @@ cudaError_t launch_bgzf_inflate(const uint8_t *comp, const BlockDesc *blocks, ui
 // launch_bgzf_inflate(..., only_flagged = true).
 cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
                                    uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream,
-                                   cudaEvent_t between_phases = nullptr);
+                                   cudaEvent_t between_phases = nullptr, cudaStream_t stream2 = nullptr, cudaEvent_t mid = nullptr);
 
 // {index of the first block whose status is not 0, or -1; its status} -> out[0..1]; `out` may be pinned host memory
 cudaError_t launch_status_first_bad(const int *status, uint32_t nblocks, int *out, cudaStream_t stream);

@@ -61,10 +61,14 @@ constexpr unsigned FULL = 0xffffffffu;
 // The main CTAs run P1<DH_P1_WARPS>; a lane whose tables do not fit queues its stream (as it stood at that deflate block header),
 // and the retry CTAs of the same grid resume it as P1<4> (decode_pass<P1Retry, true> below).  What does not fit there either
 // is flagged INF_NEEDS_V1 and redone by the lane-group kernel (bgzf_inflate.cu), as before.
-template <int W>
+// BYTES = the CTA's shared-memory budget.  232448 (227 KB) + the 1 KB the system reserves per CTA is ALL of an SM's 228 KB: while
+// such a CTA is resident no other CTA fits on its SM, whatever its size (every CTA costs the reserved 1 KB) -- the column kernels
+// and phase 2 of the previous segment wait.  The "small" variant (DH_P1_SMALL_BYTES, default 222 KB: 576 entries, the p99 of the
+// BAM blocks is 578) leaves room for five CTAs without shared memory of their own next to it (DH_P1_SMALL=1, see launch below).
+template <int W, int BYTES = 232448>
 struct P1 {
     static constexpr int WARPS = W, THREADS = W * 32;
-    static constexpr int TAB_N = (232448 / THREADS - 32) / 2;
+    static constexpr int TAB_N = (BYTES / THREADS - 32) / 2;
     static constexpr int SCR_N = 96;                 // build scratch at the end of the pool (free again before the distance table is built)
     static constexpr int SCR_LENS = TAB_N - SCR_N;   // litlen + distance code lengths, FOUR per entry (<= 316 lengths = 79 entries)
     static constexpr int SCR_NC = TAB_N - 16;        // next_code[16]
@@ -72,7 +76,7 @@ struct P1 {
     static constexpr int LIT_CAP = TAB_N - SCR_N < (1 << LROOT) + 512 ? TAB_N - SCR_N : (1 << LROOT) + 512;
     // per warp: tables [TAB_N][32] u16, then the input ring [2 chunks][32 lanes][16 bytes]
     static constexpr int WARP_SMEM = TAB_N * 64 + 2 * 512;
-    static_assert(WARP_SMEM * WARPS <= 232448, "phase 1 is sized to fill the 227 KB of one SM");
+    static_assert(WARP_SMEM * WARPS <= BYTES && BYTES <= 232448, "phase 1 is sized to fill (most of) the 227 KB of one SM");
 };
 #ifndef DH_TAIL_TAKE
 #define DH_TAIL_TAKE 1
@@ -83,10 +87,15 @@ struct P1 {
 #ifndef DH_RETRY_CTAS
 #define DH_RETRY_CTAS 4
 #endif
+#ifndef DH_P1_SMALL_BYTES
+#define DH_P1_SMALL_BYTES (222 * 1024)
+#endif
 using P1Main = P1<DH_P1_WARPS>;
 using P1Retry = P1<4>;
-constexpr int P1_SMEM = P1Main::WARP_SMEM * P1Main::WARPS > P1Retry::WARP_SMEM * P1Retry::WARPS ? P1Main::WARP_SMEM * P1Main::WARPS
-                                                                                                 : P1Retry::WARP_SMEM * P1Retry::WARPS;
+using P1MainS = P1<DH_P1_WARPS, DH_P1_SMALL_BYTES>;
+using P1RetryS = P1<4, DH_P1_SMALL_BYTES>;
+template <class M, class R>
+constexpr int p1_smem() { return M::WARP_SMEM * M::WARPS > R::WARP_SMEM * R::WARPS ? M::WARP_SMEM * M::WARPS : R::WARP_SMEM * R::WARPS; }
 
 // ---- table entries (u16) ---------------------------------------------------------------------------------
 // litlen:  bit15 = 1: length code   [14:12] extra bits  [11:4] base-3  [3:0] code length
@@ -735,6 +744,7 @@ __device__ __forceinline__ void decode_pass(const uint8_t *__restrict__ comp, co
 }
 
 // n_main_warps = 0: no retry CTAs in this grid (every lane keeps its INF_NEEDS_V1 verdict)
+template <class P1Main, class P1Retry>
 __global__ void __launch_bounds__(P1Main::THREADS, 1)
 bgzf_decode3_kernel(const uint8_t *__restrict__ comp, const BlockDesc *__restrict__ blocks, uint32_t nblocks,
                     int *__restrict__ status, uint32_t *__restrict__ ncmd_out, uint8_t *__restrict__ work,
@@ -769,12 +779,18 @@ __device__ uint32_t g_crc3[CRC3_WORDS];
 #endif
 constexpr uint32_t LONG_COPY = DH_LONG_COPY;   // copies of at least this many bytes are done by the whole warp
 
+// SMEM_TABS = false: the CRC tables are read through the read-only path (L1) instead of a shared-memory copy, so that the CTA needs no
+// shared memory of its own and fits next to a (small-variant) phase-1 CTA of the next segment.
+template <bool SMEM_TABS>
 __global__ void __launch_bounds__(256, 4)
 bgzf_resolve3_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uint8_t *__restrict__ outbuf,
                      int *__restrict__ status, const uint32_t *__restrict__ ncmd_in, const uint8_t *__restrict__ work) {
-    __shared__ uint32_t tabs[CRC3_WORDS];
-    for (int i = threadIdx.x; i < CRC3_WORDS; i += 256) tabs[i] = g_crc3[i];
-    __syncthreads();
+    __shared__ uint32_t tabs_s[SMEM_TABS ? CRC3_WORDS : 1];
+    if (SMEM_TABS) {
+        for (int i = threadIdx.x; i < CRC3_WORDS; i += 256) tabs_s[i] = g_crc3[i];
+        __syncthreads();
+    }
+    auto tab = [&](uint32_t i) -> uint32_t { return SMEM_TABS ? tabs_s[i] : __ldg(g_crc3 + i); };
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t b = blockIdx.x * 8u + (threadIdx.x >> 5);
     if (b >= nblocks) return;
@@ -856,13 +872,12 @@ bgzf_resolve3_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
     }
 
     // ---- CRC-32 (htslib/bgzf.c:793) of the finished block ----
-    const uint32_t *T0 = tabs + 4 * 256;
     const uint8_t *p = o, *end = o + d.isize;
     const uint8_t *a0 = reinterpret_cast<const uint8_t *>(((uintptr_t)o + 127u) & ~(uintptr_t)127);
     if (a0 > end) a0 = end;
     uint32_t r = 0xffffffffu;
     if (lane == 0)
-        for (; p < a0; ++p) r = T0[(r ^ *p) & 0xffu] ^ (r >> 8);
+        for (; p < a0; ++p) r = tab(4 * 256 + ((r ^ *p) & 0xffu)) ^ (r >> 8);
     r = __shfl_sync(FULL, r, 0);
     const uint32_t rows = (uint32_t)(end - a0) >> 7;
     if (rows) {
@@ -871,15 +886,15 @@ bgzf_resolve3_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
         for (uint32_t row = 0; row < rows; ++row) {
             uint32_t w = wp[(size_t)row * 32u];
             if (row == 0 && lane == 0) w ^= r;
-            H = tabs[H & 0xffu] ^ tabs[256 + ((H >> 8) & 0xffu)] ^ tabs[512 + ((H >> 16) & 0xffu)] ^ tabs[768 + (H >> 24)] ^ w;
+            H = tab(H & 0xffu) ^ tab(256 + ((H >> 8) & 0xffu)) ^ tab(512 + ((H >> 16) & 0xffu)) ^ tab(768 + (H >> 24)) ^ w;
         }
-        uint32_t v = crc_mulmod(tabs[5 * 256 + lane], H);
+        uint32_t v = crc_mulmod(tab(5 * 256 + lane), H);
 #pragma unroll
         for (int sft = 16; sft; sft >>= 1) v ^= __shfl_xor_sync(FULL, v, sft);
         r = v;
     }
     if (lane == 0) {
-        for (p = a0 + ((size_t)rows << 7); p < end; ++p) r = T0[(r ^ *p) & 0xffu] ^ (r >> 8);
+        for (p = a0 + ((size_t)rows << 7); p < end; ++p) r = tab(4 * 256 + ((r ^ *p) & 0xffu)) ^ (r >> 8);
         if ((r ^ 0xffffffffu) != d.crc) status[b] = INF_ERR_CRC;
         else if (pos != d.isize) status[b] = INF_ERR_ISIZE;
     }
@@ -1100,8 +1115,21 @@ static void build_crc3_tables(uint32_t *t) {
     for (int l = 0; l < 32; ++l) t[5 * 256 + l] = crc_shift(x2n, 0x80000000u, 128u - 4u * (uint32_t)l);
 }
 
+// How the two phases are placed (measured A/B in profiles/r2i_*):
+//   DH_P1_SMALL=1     phase 1 runs with the 222 KB pools, so other CTAs can share its SMs,
+//   DH_RESOLVE_LDG=1  phase 2 keeps no shared-memory copy of the CRC tables (needed to fit next to phase 1),
+//   stream2 != null   phase 2 (and whatever the caller enqueues behind it) runs on stream2 behind `mid`, so that phase 1 of the
+//                     caller's NEXT launch on `stream` overlaps it.
+struct V3Config { bool p1_small, resolve_ldg, resolve4; };
+static const V3Config &v3_config() {
+    static const V3Config c = {getenv("DH_P1_SMALL") && atoi(getenv("DH_P1_SMALL")) != 0, getenv("DH_RESOLVE_LDG") && atoi(getenv("DH_RESOLVE_LDG")) != 0,
+                               getenv("DH_RESOLVE4") != nullptr};
+    return c;
+}
+
 cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
-                                   uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream, cudaEvent_t between_phases) {
+                                   uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream, cudaEvent_t between_phases,
+                                   cudaStream_t stream2, cudaEvent_t mid) {
     static std::mutex mu;
     static bool ready[64] = {};
     int dev = 0;
@@ -1115,7 +1143,9 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
             build_crc3_tables(host_tabs);
             e = cudaMemcpyToSymbol(g_crc3, host_tabs, sizeof host_tabs);
             if (e != cudaSuccess) return e;
-            e = cudaFuncSetAttribute(bgzf_decode3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P1_SMEM);
+            e = cudaFuncSetAttribute(bgzf_decode3_kernel<P1Main, P1Retry>, cudaFuncAttributeMaxDynamicSharedMemorySize, p1_smem<P1Main, P1Retry>());
+            if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(bgzf_decode3_kernel<P1MainS, P1RetryS>, cudaFuncAttributeMaxDynamicSharedMemorySize, p1_smem<P1MainS, P1RetryS>());
             if (e != cudaSuccess) return e;
             uint32_t x2n[32];
             crc_x2n_init(x2n);
@@ -1128,9 +1158,13 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
             ready[dev] = true;
         }
     }
+    const V3Config &cfg = v3_config();
     e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    if (nblocks == 0) return cudaSuccess;
+    if (nblocks == 0) {
+        if (stream2 && mid) { if ((e = cudaEventRecord(mid, stream)) != cudaSuccess) return e; return cudaStreamWaitEvent(stream2, mid, 0); }
+        return cudaSuccess;
+    }
     uint32_t *ncmd = reinterpret_cast<uint32_t *>(work);
     unsigned int *retry = reinterpret_cast<unsigned int *>(work + inflate_work_retry(nblocks));   // queue header + 8 words per block
     uint8_t *areas = work + inflate_work_header(nblocks);
@@ -1142,17 +1176,27 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     uint32_t retry_ctas = P1Main::TAB_N < P1Retry::TAB_N ? (sm_count >= 64 ? (uint32_t)DH_RETRY_CTAS : sm_count >= 8 ? 1u : 0u) : 0u;
     uint32_t ctas = (nblocks + P1Main::THREADS - 1) / P1Main::THREADS;
     if (ctas > (uint32_t)sm_count - retry_ctas) ctas = (uint32_t)sm_count - retry_ctas;
-    bgzf_decode3_kernel<<<ctas + retry_ctas, P1Main::THREADS, P1_SMEM, stream>>>(comp, blocks, nblocks, status, ncmd, areas, counter,
-                                                                                 retry, retry_ctas);
+    if (cfg.p1_small)
+        bgzf_decode3_kernel<P1MainS, P1RetryS><<<ctas + retry_ctas, P1MainS::THREADS, p1_smem<P1MainS, P1RetryS>(), stream>>>(
+            comp, blocks, nblocks, status, ncmd, areas, counter, retry, retry_ctas);
+    else
+        bgzf_decode3_kernel<P1Main, P1Retry><<<ctas + retry_ctas, P1Main::THREADS, p1_smem<P1Main, P1Retry>(), stream>>>(
+            comp, blocks, nblocks, status, ncmd, areas, counter, retry, retry_ctas);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (between_phases && (e = cudaEventRecord(between_phases, stream)) != cudaSuccess) return e;
+    cudaStream_t s2 = stream;
+    if (stream2 && mid) {
+        if ((e = cudaEventRecord(mid, stream)) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(stream2, mid, 0)) != cudaSuccess) return e;
+        s2 = stream2;
+    }
     // phase 2: warp per block in global memory (bgzf_resolve3_kernel).  DH_RESOLVE4=1 selects the shared-memory kernel, measured r2b:
     // 295.5 ms against 104.0 ms on the 100 M-record bench (468,651 blocks) -- three 72 KB CTAs per SM put 3 blocks in flight where
     // the warp-per-block kernel has 32, and the window's dependency rounds (two barriers each) do not make one block 10x faster.
-    static const bool use_v3 = getenv("DH_RESOLVE4") == nullptr;
-    if (use_v3) bgzf_resolve3_kernel<<<(nblocks + 7u) / 8u, 256, 0, stream>>>(blocks, nblocks, out, status, ncmd, areas);
-    else bgzf_resolve4_kernel<<<nblocks, R4_THREADS, sizeof(R4Smem), stream>>>(blocks, nblocks, out, status, ncmd, areas);
+    if (cfg.resolve4) bgzf_resolve4_kernel<<<nblocks, R4_THREADS, sizeof(R4Smem), s2>>>(blocks, nblocks, out, status, ncmd, areas);
+    else if (cfg.resolve_ldg) bgzf_resolve3_kernel<false><<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
+    else bgzf_resolve3_kernel<true><<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
     return cudaGetLastError();
 }
 

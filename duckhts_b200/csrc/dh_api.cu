@@ -183,7 +183,7 @@ uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_ba
 }
 
 int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
-                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream, int sm_limit) {
+                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream, int sm_limit, cudaStream_t stream2, cudaEvent_t mid) {
     const int sms = sm_limit > 0 && sm_limit < c->sm_count ? sm_limit : c->sm_count;
     static const bool force_v1 = getenv("DH_INFLATE_V1") != nullptr;
     if (force_v1) {
@@ -195,10 +195,11 @@ int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint3
     if (rc != DH_OK) return rc;
     const bool tp = c->time_phases;
     if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[0], stream));
-    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, sms, stream, tp ? c->ev_ph[1] : nullptr));
-    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[2], stream));
-    DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, stream, true));
-    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[3], stream));
+    DH_CUDA(launch_bgzf_inflate_v3(comp, descs, n, out, status, (uint8_t *)work.p, counter, sms, stream, tp ? c->ev_ph[1] : nullptr, stream2, mid));
+    cudaStream_t tail = stream2 && mid ? stream2 : stream;     // where phase 2 went
+    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[2], tail));
+    DH_CUDA(launch_bgzf_inflate(comp, descs, n, out, status, counter + 1, c->sm_count, tail, true));
+    if (tp) DH_CUDA(cudaEventRecord(c->ev_ph[3], tail));
     c->launches += 3;   // phase 1 (main + retry CTAs in one grid), phase 2, the lane-group filter
     return DH_OK;
 }
@@ -253,7 +254,8 @@ dh_ctx *dh_ctx_create(int device) {
         return nullptr;
     }
     c->sm_count = prop.multiProcessorCount;
-    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&c->inf2_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; i < 3 && ok; ++i) {
         ok = cudaStreamCreateWithFlags(&c->copy_streams[i], cudaStreamNonBlocking) == cudaSuccess &&
              cudaEventCreate(&c->slots[i].ev_k0) == cudaSuccess && cudaEventCreate(&c->slots[i].ev_k1) == cudaSuccess &&
@@ -288,6 +290,7 @@ void dh_ctx_destroy(dh_ctx *c) {
     if (c->ev_timer[0]) cudaEventDestroy(c->ev_timer[0]);
     if (c->ev_timer[1]) cudaEventDestroy(c->ev_timer[1]);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->inf2_stream) cudaStreamDestroy(c->inf2_stream);
     delete c;
 }
 
@@ -611,10 +614,15 @@ int dh_bgzf_inflate_fd(dh_ctx *c, int in_fd, int out_fd, dh_inflate_stats *st) {
 struct dh_bgzf_dev {
     dh_ctx *ctx;
     BlockTable bt;
-    DevBuf comp, out, desc, status, work;
+    DevBuf comp, out, desc, status, work, work2;
     struct Seg { size_t b0, b1; uint64_t cbase, cmd_words; };
     std::vector<Seg> segs;
+    cudaEvent_t ev_mid[2] = {}, ev_tail[2] = {};      // two-stream mode (DH_PHASE_STREAMS=2): phase 2 of launch i overlaps phase 1 of launch i + 1
 };
+static bool phase_streams_two() {
+    static const bool two = getenv("DH_PHASE_STREAMS") && atoi(getenv("DH_PHASE_STREAMS")) == 2;
+    return two;
+}
 
 dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size) {
     if (!c || !comp) { set_error("dh_bgzf_dev_load: bad arguments"); return nullptr; }
@@ -639,7 +647,8 @@ dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size
         size_t e = b;
         uint64_t cbase = d->bt.blocks[b].coffset & ~15ull;
         // a launch covers at most 2 GiB of compressed bytes (32-bit in_off) and 2^17 blocks (bounded work buffer)
-        while (e < nb && e - b < (1u << 17) && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
+        const size_t max_blocks = phase_streams_two() ? (1u << 15) : (1u << 17);   // two streams: shorter launches interleave better
+        while (e < nb && e - b < max_blocks && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
         const size_t quantum = (size_t)c->sm_count * 128u;   // streams phase 1 decodes at a time: launch whole rounds
         if (e < nb && e - b > quantum) e = b + (e - b) / quantum * quantum;
         const uint64_t cw = fill_descs(d->bt, b, e, cbase, 0, 0, descs.data() + b);
@@ -661,7 +670,8 @@ void dh_bgzf_dev_free(dh_bgzf_dev *d) {
     if (!d) return;
     cudaSetDevice(d->ctx->device);
     cudaStreamSynchronize(d->ctx->stream);
-    d->comp.release(); d->out.release(); d->desc.release(); d->status.release(); d->work.release();
+    d->comp.release(); d->out.release(); d->desc.release(); d->status.release(); d->work.release(); d->work2.release();
+    for (int i = 0; i < 2; ++i) { if (d->ev_mid[i]) cudaEventDestroy(d->ev_mid[i]); if (d->ev_tail[i]) cudaEventDestroy(d->ev_tail[i]); }
     delete d;
 }
 uint64_t dh_bgzf_dev_nblocks(const dh_bgzf_dev *d) { return d ? d->bt.blocks.size() : 0; }
@@ -672,6 +682,25 @@ int dh_bgzf_dev_inflate(dh_bgzf_dev *d) {
     if (!d) { set_error("dh_bgzf_dev_inflate: null handle"); return DH_EINVAL; }
     dh_ctx *c = d->ctx;
     DH_CUDA(cudaSetDevice(c->device));
+    if (phase_streams_two() && d->segs.size() > 1) {
+        // phase 1 of every launch on the context's stream, phase 2 (+ filter) on the second stream; two work areas in turn
+        for (int i = 0; i < 2; ++i) {
+            if (!d->ev_mid[i]) DH_CUDA(cudaEventCreateWithFlags(&d->ev_mid[i], cudaEventDisableTiming));
+            if (!d->ev_tail[i]) DH_CUDA(cudaEventCreateWithFlags(&d->ev_tail[i], cudaEventDisableTiming));
+        }
+        for (size_t i = 0; i < d->segs.size(); ++i) {
+            auto &s = d->segs[i];
+            const int q = (int)(i & 1);
+            if (i >= 2) DH_CUDA(cudaStreamWaitEvent(c->stream, d->ev_tail[q], 0));      // launch i - 2 has left this work area
+            int rc = inflate_blocks(c, (const uint8_t *)d->comp.p + s.cbase, (const BlockDesc *)d->desc.p + s.b0, (uint32_t)(s.b1 - s.b0),
+                                    s.cmd_words, (uint8_t *)d->out.p, (int *)d->status.p + s.b0, q ? d->work2 : d->work,
+                                    (unsigned int *)c->counter.p + 4 * q, c->stream, 0, c->inf2_stream, d->ev_mid[q]);
+            if (rc != DH_OK) return rc;
+            DH_CUDA(cudaEventRecord(d->ev_tail[q], c->inf2_stream));
+        }
+        DH_CUDA(cudaStreamWaitEvent(c->stream, d->ev_tail[(d->segs.size() - 1) & 1], 0));   // the context's stream ends behind the last phase 2
+        return DH_OK;
+    }
     for (auto &s : d->segs) {
         int rc = inflate_blocks(c, (const uint8_t *)d->comp.p + s.cbase, (const BlockDesc *)d->desc.p + s.b0, (uint32_t)(s.b1 - s.b0),
                                 s.cmd_words, (uint8_t *)d->out.p, (int *)d->status.p + s.b0, d->work, (unsigned int *)c->counter.p,
@@ -739,6 +768,7 @@ int dh_ctx_sync(dh_ctx *c) {
     DH_CUDA(cudaSetDevice(c->device));
     DH_CUDA(cudaStreamSynchronize(c->stream));
     for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(c->copy_streams[i]));
+    DH_CUDA(cudaStreamSynchronize(c->inf2_stream));
     return DH_OK;
 }
 int dh_timer_start(dh_ctx *c) {

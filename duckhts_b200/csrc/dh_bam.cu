@@ -245,6 +245,7 @@ int ensure_events(dh_bam *b) {
             DH_CUDA(cudaEventCreate(&s.ev_inf0));
             DH_CUDA(cudaEventCreate(&s.ev_inf1));
             DH_CUDA(cudaEventCreate(&s.ev_inf_done));
+            DH_CUDA(cudaEventCreateWithFlags(&s.ev_mid, cudaEventDisableTiming));
             DH_CUDA(cudaEventCreate(&s.ev_free));
             DH_CUDA(cudaEventCreate(&s.ev_walk0));
             DH_CUDA(cudaEventCreate(&s.ev_walk1));
@@ -404,6 +405,8 @@ int issue_inflate(dh_bam *b, int k) {
     if ((rc = s.h_status.reserve(64)) != DH_OK) return rc;
     const uint64_t cw = fill_descs(bt, sg.b0, sg.b1, s.cbase, sg.b0, b->carry_cap, (BlockDesc *)s.h_desc.p);
     cudaStream_t sc = s_copy(b), si = s_inf(b);
+    // DH_PHASE_STREAMS=2: phase 2 of segment k runs on a second stream, so phase 1 of segment k + 1 (next on `si`) overlaps it
+    static const bool two = getenv("DH_PHASE_STREAMS") && atoi(getenv("DH_PHASE_STREAMS")) == 2;
     DH_CUDA(cudaStreamWaitEvent(sc, s.ev_inf1, 0));  // previous inflate from this comp buffer is done (no-op if never recorded)
     if (!staged) {
         // memory image: straight from the caller's (pinned) buffer; file mode: from the staging buffer frame_segment() filled
@@ -419,12 +422,14 @@ int issue_inflate(dh_bam *b, int k) {
     DH_CUDA(cudaEventRecord(s.ev_inf0, si));
     const uint8_t *comp_ptr = staged ? (const uint8_t *)b->d_image.p + s.cbase : (const uint8_t *)s.comp.p;
     if ((rc = inflate_blocks(b->ctx, comp_ptr, (const BlockDesc *)s.desc.p, (uint32_t)nblk, cw, (uint8_t *)s.out.p, (int *)s.status.p,
-                             s.work, (unsigned int *)b->ctx->counter.p + 16 + 2 * (k % NSEG), si, inflate_sms(b))) != DH_OK)
+                             s.work, (unsigned int *)b->ctx->counter.p + 16 + 2 * (k % NSEG), si, inflate_sms(b), two ? b->ctx->inf2_stream : nullptr,
+                             two ? s.ev_mid : nullptr)) != DH_OK)
         return rc;
-    DH_CUDA(cudaEventRecord(s.ev_inf1, si));
-    DH_CUDA(launch_status_first_bad((const int *)s.status.p, (uint32_t)nblk, (int *)s.h_status.p, si));
+    cudaStream_t st = two ? b->ctx->inf2_stream : si;      // the stream phase 2 ended on
+    DH_CUDA(cudaEventRecord(s.ev_inf1, st));
+    DH_CUDA(launch_status_first_bad((const int *)s.status.p, (uint32_t)nblk, (int *)s.h_status.p, st));
     b->ctx->launches++;
-    DH_CUDA(cudaEventRecord(s.ev_inf_done, si));
+    DH_CUDA(cudaEventRecord(s.ev_inf_done, st));
     s.issued_for = k;
     b->st.h2d_bytes += (staged ? 0 : cbytes) + nblk * sizeof(BlockDesc);
     b->st.inflated_bytes += s.obytes;
@@ -849,7 +854,7 @@ void dh_bam_close(dh_bam *b) {
         s.comp.release(); s.out.release(); s.desc.release(); s.status.release(); s.work.release(); s.rec.release();
         s.h_desc.release(); s.h_status.release(); s.h_blk_start.release(); s.h_entry.release(); s.h_todo.release();
         s.h_walk.release(); s.h_row_base.release(); s.h_heap_base.release(); s.h_map_base.release();
-        for (cudaEvent_t e : {s.ev_h2d, s.ev_inf0, s.ev_inf1, s.ev_inf_done, s.ev_free, s.ev_walk0, s.ev_walk1, s.ev_walk2}) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : {s.ev_mid, s.ev_h2d, s.ev_inf0, s.ev_inf1, s.ev_inf_done, s.ev_free, s.ev_walk0, s.ev_walk1, s.ev_walk2}) if (e) cudaEventDestroy(e);
     }
     for (auto &s : b->bs) {
         s.arena.release(); s.h_arena.release();
@@ -1024,6 +1029,7 @@ static int begin_range(dh_bam *b, uint64_t voff_beg, uint64_t voff_end, bool fre
     // drop whatever an abandoned scan left in flight (this context's streams only: other contexts may share the device)
     DH_CUDA(cudaStreamSynchronize(b->ctx->stream));
     for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(b->ctx->copy_streams[i]));
+    DH_CUDA(cudaStreamSynchronize(b->ctx->inf2_stream));
     if (b->fd >= 0) {
         // file mode: the block table restarts at the block the range begins in and grows as segments are read (frame_segment)
         const uint64_t vb = voff_beg ? voff_beg : b->first_voff;
@@ -1329,6 +1335,7 @@ int dh_bam_set_slots(dh_bam *b, int n_slots) {
     // whatever scan was under way is abandoned: its batches are forgotten once the streams are idle
     DH_CUDA(cudaStreamSynchronize(b->ctx->stream));
     for (int i = 0; i < 3; ++i) DH_CUDA(cudaStreamSynchronize(b->ctx->copy_streams[i]));
+    DH_CUDA(cudaStreamSynchronize(b->ctx->inf2_stream));
     for (auto &o : b->bs) o.state = SLOT_FREE;
     b->inflight.clear();
     b->auto_slot = -1;

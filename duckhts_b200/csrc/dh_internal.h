@@ -53,7 +53,8 @@ uint64_t fill_descs(const BlockTable &bt, size_t b0, size_t b1, uint64_t comp_ba
 // Inflate `n` described blocks on `stream`: lockstep kernels (phase 1 + 2), then the lane-group kernel in filter mode
 // for blocks the compact tables could not hold.  `work` is grown as needed.  counter: >= 2 device words.
 int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint32_t n, uint64_t cmd_words, uint8_t *out,
-                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream, int sm_limit = 0);
+                   int *status, DevBuf &work, unsigned int *counter, cudaStream_t stream, int sm_limit = 0,
+                   cudaStream_t stream2 = nullptr, cudaEvent_t mid = nullptr);   // stream2 + mid: phase 2 and the filter run on stream2
 
 }  // namespace dh
 
@@ -61,6 +62,7 @@ struct dh_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;        // the stream every kernel is launched on
+    cudaStream_t inf2_stream = nullptr;   // phase 2 of the inflate when the scan pipeline splits the phases over two streams (DH_PHASE_STREAMS=2)
     cudaStream_t copy_streams[3] = {};    // pipeline slots for the *_host entry points
     cudaEvent_t ev_timer[2] = {};
     dh::DevBuf l2_scratch;

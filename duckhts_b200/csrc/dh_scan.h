@@ -26,7 +26,7 @@ struct SegSlot {
     DevBuf comp, out, desc, status, work, rec;
     int64_t rec_bias = 0;
     PinBuf h_desc, h_status, h_blk_start, h_entry, h_todo, h_walk, h_row_base, h_heap_base, h_map_base;
-    cudaEvent_t ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_inf_done = nullptr, ev_free = nullptr, ev_walk0 = nullptr,
+    cudaEvent_t ev_mid = nullptr, ev_h2d = nullptr, ev_inf0 = nullptr, ev_inf1 = nullptr, ev_inf_done = nullptr, ev_free = nullptr, ev_walk0 = nullptr,
                 ev_walk1 = nullptr, ev_walk2 = nullptr;
     size_t b0 = 0, b1 = 0;  // file block range
     uint64_t cbase = 0, obytes = 0;

@@ -563,7 +563,7 @@ int main(int argc, char **argv) {
     for (int i = 0; i < g_nfuncs; ++i) if (!strcmp(g_funcs[i]->name, fname)) tf = g_funcs[i];
     if (!tf) { fprintf(stderr, "table function %s not registered (have:", fname); for (int i = 0; i < g_nfuncs; ++i) fprintf(stderr, " %s", g_funcs[i]->name); fprintf(stderr, ")\n"); return 2; }
 
-    int repeat = 1;
+    int repeat = 1, want_time = 0;
     for (int i = 4; i < argc; ++i) if (!strcmp(argv[i], "--repeat") && i + 1 < argc) repeat = atoi(argv[i + 1]);
     if (repeat < 1) repeat = 1;
     int rc = 0;
@@ -578,7 +578,7 @@ int main(int argc, char **argv) {
     for (int i = 4; i < argc; ++i) {
         if (!strcmp(argv[i], "--dump")) mode = MODE_DUMP;
         else if (!strcmp(argv[i], "--hash")) mode = MODE_HASH;
-        else if (!strcmp(argv[i], "--time")) mode = MODE_TIME;
+        else if (!strcmp(argv[i], "--time")) { want_time = 1; if (mode != MODE_HASH) mode = MODE_TIME; }
         else if (!strcmp(argv[i], "--cols") && i + 1 < argc) cols = argv[++i];
         else if (!strcmp(argv[i], "--threads") && i + 1 < argc) threads = atoi(argv[++i]);
         else if (!strcmp(argv[i], "--repeat") && i + 1 < argc) ++i;
@@ -646,7 +646,7 @@ int main(int argc, char **argv) {
             else printf("%s\t-\t%016" PRIx64 "\n", bind.col_names[col_ids[c]], msum);
         }
     }
-    if (mode == MODE_TIME) {
+    if (mode == MODE_TIME || want_time) {
         if (run == 0) { first_s = best_s = dt; first_bind = best_bind = t_bind; }
         else if (dt < best_s) { best_s = dt; best_bind = t_bind; }
         if (run + 1 == repeat)

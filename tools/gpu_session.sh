@@ -38,11 +38,22 @@ for stage in "$@"; do
       DH_TRACE=1 DUCKHTS_PROFILE=1 harness/_bin/fake_duckdb duckhts_b200/lib/duckhts.duckdb_extension.so read_bam /tmp/duckhts_b200_cache/tiled100m.bam standard_tags=true --cols 0,1,2,3,4,5,6,7,8,9,10,11,12,47,40,14 --threads 16 --time > gpurun_out/${T}_exttrace.log 2>&1
       rm -f /tmp/duckhts_b200_cache/tiled100m.bam
       cat gpurun_out/${T}_extprof.log; tail -5 gpurun_out/${T}_exttrace.log ;;
-    ab_resolve) # inflate phase 2: shared-memory kernel (default) against the global-memory one of round 1
-      for v in 4 3; do
-        if [ $v = 3 ]; then export DH_RESOLVE3=1; else unset DH_RESOLVE3; fi
-        timeout 600 python bench.py --steps 3 --warmup 2 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve$v', json.dumps({'value': d['value'], 'inflate': d['inflate'], 'e2e': d['e2e']['value']}))"
-      done > gpurun_out/${T}_ab_resolve.log 2>&1; unset DH_RESOLVE3; cat gpurun_out/${T}_ab_resolve.log ;;
+    ab_resolve) # inflate phase 2: the shared-memory kernel (DH_RESOLVE4=1) against the warp-per-block kernel in global memory (default)
+      for v in 3 4; do
+        if [ $v = 4 ]; then export DH_RESOLVE4=1; else unset DH_RESOLVE4; fi
+        timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve$v', json.dumps({'value': d['value'], 'inflate': d['inflate'], 'e2e': d['e2e']['value']}))"
+      done > gpurun_out/${T}_ab_resolve.log 2>&1; unset DH_RESOLVE4; cat gpurun_out/${T}_ab_resolve.log ;;
+    ab_overlap) # who shares an SM with phase 1: pools of 227 KB (nobody) or 222 KB; phase 2 with / without its shared-memory tables; one or two inflate streams
+      for cfg in "0 0 1" "1 0 1" "1 1 1" "1 1 2" "0 1 2" "0 0 2"; do
+        set -- $cfg
+        export DH_P1_SMALL=$1 DH_RESOLVE_LDG=$2 DH_PHASE_STREAMS=$3
+        timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('p1_small=$1 resolve_ldg=$2 phase_streams=$3', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'inflate': d['inflate'], 'e2e': d['e2e']['value'], 'parity': d.get('parity', {}).get('ok')}))"
+      done > gpurun_out/${T}_ab_overlap.log 2>&1; unset DH_P1_SMALL DH_RESOLVE_LDG DH_PHASE_STREAMS; cat gpurun_out/${T}_ab_overlap.log ;;
+    cfg4) # BASELINE configs[3] at size: a sorted 100 M-record file, index built on the GPU and by htslib, every cell hashed against the reference
+      df -h /tmp | tail -1
+      timeout 2400 python tools/cfg4_100m.py --records ${CFG4_RECORDS:-100e6} --devices 0 --out gpurun_out/${T}_cfg4.json > gpurun_out/${T}_cfg4.log 2>&1; echo "cfg4 exit $?" | tee -a gpurun_out/${T}_cfg4.log
+      timeout 1200 python tools/cfg4_100m.py --records ${CFG4_RECORDS:-100e6} --devices 0,0 --ordered --skip-index --out gpurun_out/${T}_cfg4_two_sources.json > gpurun_out/${T}_cfg4_two_sources.log 2>&1; echo "cfg4 (two sources, ordered) exit $?" | tee -a gpurun_out/${T}_cfg4_two_sources.log
+      grep -h "cfg4\]" gpurun_out/${T}_cfg4.log gpurun_out/${T}_cfg4_two_sources.log; tail -3 gpurun_out/${T}_cfg4.log ;;
     *) echo "unknown stage $stage" ;;
   esac
 done
