@@ -21,6 +21,11 @@ class InflateStats(C.Structure):
                 ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
 
 
+class DeflateStats(C.Structure):
+    _fields_ = [("in_bytes", C.c_uint64), ("out_bytes", C.c_uint64), ("n_blocks", C.c_uint64), ("h2d_bytes", C.c_uint64),
+                ("d2h_bytes", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
+
+
 DH_BAM_CORE_COLS = 13
 DH_BAM_MAX_COLS = 13 + 63
 
@@ -110,6 +115,10 @@ SIGNATURES = {
     "dh_free": (None, [C.c_void_p]),
     "dh_index_split_contigs": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32)]),
     "dh_bgzf_inflate_fd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(InflateStats)]),
+    "dh_bgzf_deflate_bound": (C.c_uint64, [C.c_uint64]),
+    "dh_bgzf_deflate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64),
+                                       C.POINTER(DeflateStats)]),
+    "dh_bgzf_deflate_fd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(DeflateStats)]),
     "dh_bcf_set_slots": (C.c_int, [C.c_void_p, C.c_int]),
     "dh_bcf_acquire_batch": (C.c_int, [C.c_void_p, C.POINTER(BcfBatch)]),
     "dh_bcf_release_batch": (C.c_int, [C.c_void_p, C.c_int32]),

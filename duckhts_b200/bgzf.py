@@ -3,7 +3,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import BgzfBlock, DuckhtsError, InflateStats, check, lib
+from ._lib import BgzfBlock, DeflateStats, DuckhtsError, InflateStats, check, lib
 
 
 class PinnedBuffer:
@@ -119,6 +119,27 @@ def bgzf_inflate(ctx, data, out=None, want_output=True):
         err.rc, err.stats = rc, st
         raise err
     return (o[: n.value] if o is not None else None), st
+
+
+def bgzf_deflate(ctx, data, level=-1, out=None):
+    """N1: compress bytes into a BGZF stream host->host (bgzip(), src/bgzip.c:209-273).  Returns (uint8 array, stats)."""
+    a = _as_u8(data)
+    cap = lib().dh_bgzf_deflate_bound(a.size)
+    o = _as_u8(out) if out is not None else np.empty(cap, dtype=np.uint8)
+    st = DeflateStats()
+    n = C.c_uint64(0)
+    rc = lib().dh_bgzf_deflate_host(ctx.h, a.ctypes.data if a.size else None, a.size, int(level), o.ctypes.data, o.size, C.byref(n), C.byref(st))
+    if rc < 0:
+        raise DuckhtsError(f"dh_bgzf_deflate_host rc={rc}: {lib().dh_last_error().decode()}")
+    return o[: n.value], st
+
+
+def bgzf_deflate_fd(ctx, fd_in, fd_out, level=-1):
+    st = DeflateStats()
+    rc = lib().dh_bgzf_deflate_fd(ctx.h, int(fd_in), int(fd_out), int(level), C.byref(st))
+    if rc < 0:
+        raise DuckhtsError(f"dh_bgzf_deflate_fd rc={rc}: {lib().dh_last_error().decode()}")
+    return st
 
 
 class BgzfDevice:

@@ -19,6 +19,10 @@
 // Integer/byte work only: HBM-bound, no tensor cores.  Layout: records of one block are consecutive rows, so a
 // warp's column stores are contiguous per column; the long strings of a record (QNAME, SEQ, QUAL, ...) are
 // consecutive 4-byte-aligned slots of ONE heap, so a warp writes ~320 contiguous bytes per record.
+#include <stdlib.h>
+
+#include <mutex>
+
 #include "bam_decode.cuh"
 
 namespace dh {
@@ -1444,7 +1448,23 @@ cudaError_t launch_bam_index(const IndexParams &p, const ScanTables &t, cudaStre
     return cudaGetLastError();
 }
 
+// DH_CARVEOUT_MAX=1 (A/B, profiles/r2i): ask for the largest shared-memory carve-out although these kernels use none, so that an SM
+// configured for the inflate's 222 KB phase-1 CTA does not have to drain before one of their CTAs may join it.
+static void column_kernels_carveout() {
+    static std::once_flag once[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+    std::call_once(once[dev], [] {
+        const char *e = getenv("DH_CARVEOUT_MAX");
+        if (!e || !atoi(e)) return;
+        cudaFuncSetAttribute(bam_walk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(bam_decode_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(bam_decode_compact_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    });
+}
+
 cudaError_t launch_bam_walk(const WalkParams &p, const ScanTables &t, cudaStream_t stream) {
+    column_kernels_carveout();
     if (p.n == 0) return cudaSuccess;
     bam_walk_kernel<<<(p.n + 127u) / 128u, 128, 0, stream>>>(p, t);
     return cudaGetLastError();

@@ -1155,6 +1155,10 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
             if (e != cudaSuccess) return e;
             e = cudaFuncSetAttribute(bgzf_resolve4_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
             if (e != cudaSuccess) return e;
+            if (getenv("DH_CARVEOUT_MAX") && atoi(getenv("DH_CARVEOUT_MAX"))) {       // see bam_decode.cu
+                cudaFuncSetAttribute(bgzf_resolve3_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+                cudaFuncSetAttribute(bgzf_resolve3_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+            }
             ready[dev] = true;
         }
     }

@@ -449,7 +449,7 @@ int dh_bgzf_inflate_host(dh_ctx *c, const uint8_t *comp, uint64_t comp_size, uin
 
 // ---- A2/A3 file -> file, streaming (bgunzip) ---------------------------------------------------------------
 // pread / pwrite of one big range by a few threads: one thread moves page-cache bytes at a fraction of what the GPU takes
-static bool parallel_io(int fd, uint8_t *buf, uint64_t n, uint64_t off, bool write) {
+bool dh_parallel_io(int fd, uint8_t *buf, uint64_t n, uint64_t off, bool write) {
     if (n == 0) return true;
     int nt = (int)std::min<uint64_t>(8, (n + (32ull << 20) - 1) / (32ull << 20));
     std::vector<int> ok((size_t)nt, 1);
@@ -512,7 +512,7 @@ int dh_bgzf_inflate_fd(dh_ctx *c, int in_fd, int out_fd, dh_inflate_stats *st) {
                 break;
             }
         if (st->bad_block >= 0 && (uint64_t)st->bad_block < p.blk0) return DH_OK;   // an earlier segment already failed
-        if (!parallel_io(out_fd, (uint8_t *)s.h_out.p, good, p.out_off, true)) { set_error("write: %s", strerror(errno)); return DH_EIO; }
+        if (!dh_parallel_io(out_fd, (uint8_t *)s.h_out.p, good, p.out_off, true)) { set_error("write: %s", strerror(errno)); return DH_EIO; }
         return DH_OK;
     };
 
@@ -526,7 +526,7 @@ int dh_bgzf_inflate_fd(dh_ctx *c, int in_fd, int out_fd, dh_inflate_stats *st) {
         if ((rc = retire(slot)) != DH_OK || st->bad_block >= 0) break;
         const uint64_t want = std::min<uint64_t>(F_COMP, fsize - foff);
         if ((rc = s.h_comp.reserve(F_COMP + 64)) != DH_OK || (rc = s.h_out.reserve(F_OUT + BGZF_MAX_OUT)) != DH_OK) break;
-        if (!parallel_io(in_fd, (uint8_t *)s.h_comp.p, want, foff, false)) { set_error("read: %s", strerror(errno)); rc = DH_EIO; break; }
+        if (!dh_parallel_io(in_fd, (uint8_t *)s.h_comp.p, want, foff, false)) { set_error("read: %s", strerror(errno)); rc = DH_EIO; break; }
         // frame the blocks that lie whole in the buffer (A1); the partial block at its end starts the next segment
         BlockTable bt;
         const uint8_t *buf = (const uint8_t *)s.h_comp.p;
@@ -647,9 +647,9 @@ dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size
         size_t e = b;
         uint64_t cbase = d->bt.blocks[b].coffset & ~15ull;
         // a launch covers at most 2 GiB of compressed bytes (32-bit in_off) and 2^17 blocks (bounded work buffer)
-        const size_t max_blocks = phase_streams_two() ? (1u << 15) : (1u << 17);   // two streams: shorter launches interleave better
+        const size_t quantum = (size_t)c->sm_count * 192u;   // streams phase 1 decodes at a time (6 warps per SM): launch whole rounds
+        const size_t max_blocks = phase_streams_two() ? 2u * quantum : (1u << 17);   // two streams: shorter launches interleave better
         while (e < nb && e - b < max_blocks && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
-        const size_t quantum = (size_t)c->sm_count * 128u;   // streams phase 1 decodes at a time: launch whole rounds
         if (e < nb && e - b > quantum) e = b + (e - b) / quantum * quantum;
         const uint64_t cw = fill_descs(d->bt, b, e, cbase, 0, 0, descs.data() + b);
         d->segs.push_back({b, e, cbase, cw});

@@ -58,6 +58,9 @@ int inflate_blocks(dh_ctx *c, const uint8_t *comp, const BlockDesc *descs, uint3
 
 }  // namespace dh
 
+// pread / pwrite of [off, off + n) by several threads (dh_api.cu)
+extern "C" bool dh_parallel_io(int fd, uint8_t *buf, uint64_t n, uint64_t off, bool write);
+
 struct dh_ctx {
     int device = 0;
     int sm_count = 0;

@@ -1442,6 +1442,84 @@ static void register_bgunzip(duckdb_connection con) {
 }
 
 /* ================================================================================================================
+ * bgzip (N1) — the reference compresses in bind with bgzf_write (src/bgzip.c:209-273); here dh_bgzf_deflate_fd streams the file through
+ * the GPU compressor.  Same parameters, same one-row result, same error texts; `threads` is accepted and unused, `level` 0 writes
+ * stored blocks and every other level runs the one GPU compressor.
+ * ================================================================================================================ */
+static void bgzip_bind(duckdb_bind_info info) {
+    duckdb_value pv = api.duckdb_bind_get_parameter(info, 0);
+    char *in = api.duckdb_get_varchar(pv);
+    api.duckdb_destroy_value(&pv);
+    if (!in || !in[0]) { api.duckdb_bind_set_error(info, "bgzip requires a file path"); if (in) api.duckdb_free(in); return; }
+    char *outp = named_varchar(info, "output_path");
+    const int keep = named_bool(info, "keep", 1), overwrite = named_bool(info, "overwrite", 0);
+    int level = (int)named_int(info, "level", -1);
+    if (level < 0 || level > 9) level = -1;                  /* src/bgzip.c:222-223: anything else opens with mode "w" */
+    char out_path[4096], err[4608];
+    err[0] = 0;
+    if (outp) snprintf(out_path, sizeof out_path, "%s", outp);
+    else snprintf(out_path, sizeof out_path, "%s.gz", in);
+    uint64_t bytes_in = 0, bytes_out = 0;
+    dh_ctx *ctx = NULL;
+    int in_fd = -1, out_fd = -1;
+    if (!overwrite && file_exists(out_path)) snprintf(err, sizeof err, "bgzip: output '%s' already exists (use overwrite := TRUE to replace)", out_path);
+    else {
+        int devs[MAX_SOURCES];
+        device_list(devs);
+        if ((in_fd = open(in, O_RDONLY)) < 0) snprintf(err, sizeof err, "bgzip: cannot open input %s: %s", in, strerror(errno));
+        else if (!(ctx = ctx_acquire(devs[0]))) snprintf(err, sizeof err, "bgzip: no usable CUDA device (%s)", dh_last_error());
+        else if ((out_fd = open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0666)) < 0) snprintf(err, sizeof err, "bgzip: cannot open output %s", out_path);
+        else {
+            dh_deflate_stats st;
+            const int rc = dh_bgzf_deflate_fd(ctx, in_fd, out_fd, level, &st);
+            if (rc == DH_EIO && strstr(dh_last_error(), "read")) snprintf(err, sizeof err, "bgzip: read error");
+            else if (rc != DH_OK) snprintf(err, sizeof err, "bgzip: write error");
+            bytes_in = st.in_bytes;
+            bytes_out = st.out_bytes;
+            if (close(out_fd) != 0 && !err[0]) snprintf(err, sizeof err, "bgzip: close error");
+            out_fd = -1;
+        }
+    }
+    if (in_fd >= 0) close(in_fd);
+    if (out_fd >= 0) close(out_fd);
+    if (ctx) ctx_release(ctx);
+    if (err[0]) api.duckdb_bind_set_error(info, err);
+    else {
+        if (!keep) unlink(in);
+        duckdb_logical_type t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN), t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR),
+                            t_bigint = api.duckdb_create_logical_type(DUCKDB_TYPE_BIGINT);
+        api.duckdb_bind_add_result_column(info, "success", t_bool);
+        api.duckdb_bind_add_result_column(info, "output_path", t_varchar);
+        api.duckdb_bind_add_result_column(info, "bytes_in", t_bigint);
+        api.duckdb_bind_add_result_column(info, "bytes_out", t_bigint);
+        api.duckdb_destroy_logical_type(&t_bool); api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_bigint);
+        gz_bind_t *g = (gz_bind_t *)api.duckdb_malloc(sizeof *g);
+        g->out_path = strdup(out_path); g->bytes_in = (int64_t)bytes_in; g->bytes_out = (int64_t)bytes_out; g->emitted = 0;
+        api.duckdb_bind_set_bind_data(info, g, gz_bind_free);
+    }
+    api.duckdb_free(in);
+    if (outp) api.duckdb_free(outp);
+}
+static void register_bgzip(duckdb_connection con) {
+    duckdb_table_function tf = api.duckdb_create_table_function();
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_int = api.duckdb_create_logical_type(DUCKDB_TYPE_INTEGER),
+                        t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN);
+    api.duckdb_table_function_set_name(tf, "bgzip");
+    api.duckdb_table_function_add_parameter(tf, t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "output_path", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "threads", t_int);
+    api.duckdb_table_function_add_named_parameter(tf, "level", t_int);
+    api.duckdb_table_function_add_named_parameter(tf, "keep", t_bool);
+    api.duckdb_table_function_add_named_parameter(tf, "overwrite", t_bool);
+    api.duckdb_table_function_set_bind(tf, bgzip_bind);
+    api.duckdb_table_function_set_init(tf, bgunzip_init);
+    api.duckdb_table_function_set_function(tf, bgunzip_scan);
+    api.duckdb_register_table_function(con, tf);
+    api.duckdb_destroy_table_function(&tf);
+    api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_int); api.duckdb_destroy_logical_type(&t_bool);
+}
+
+/* ================================================================================================================
  * bam_index — like the reference (src/hts_index_builder.c:110-160, 326-345): the index is built in bind (sam_index_build3 there,
  * one GPU scan here: dh_bam_index_build) and the scan returns one row (success, index_path, index_format).  BAI only (min_shift 0).
  * ================================================================================================================ */
@@ -1531,6 +1609,7 @@ __attribute__((visibility("default"))) bool duckhts_init_c_api(duckdb_extension_
     register_read_bam(con);
     register_read_bcf(con);
     register_bgunzip(con);
+    register_bgzip(con);
     register_bam_index(con);
     api.duckdb_disconnect(&con);
     return true;

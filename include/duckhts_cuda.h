@@ -97,6 +97,24 @@ int dh_bgzf_inflate_host(dh_ctx *ctx, const uint8_t *comp, uint64_t comp_size, u
  * DH_EFORMAT / DH_EDATA (read errors; stats->bad_block), DH_EIO (errno of the failing read / write in the message). */
 int dh_bgzf_inflate_fd(dh_ctx *ctx, int in_fd, int out_fd, dh_inflate_stats *stats);
 
+/* ---- N1: BGZF compression (the reference's bgzip(): src/bgzip.c:209-273; bgzf_write / bgzf_close, htslib/bgzf.c:624-683,
+ * 1805-1850, 2138-2150).  The input is cut into 0xff00-byte blocks like bgzf_write cuts it; each becomes one BGZF block (LZ77 +
+ * dynamic Huffman on the GPU, a stored block where that would not shrink); the 28-byte EOF marker ends the stream.  The
+ * DEFLATE bits are this library's own; inflated bytes, block boundaries in inflated space, CRC-32 and ISIZE are what htslib
+ * writes.  level: 0 = stored blocks, 1..9 and -1 (default) = the one GPU compressor (bgzip's level is a CPU time knob). */
+typedef struct dh_deflate_stats {
+    uint64_t in_bytes, out_bytes;   /* out_bytes includes the EOF marker */
+    uint64_t n_blocks;              /* data blocks written (without the EOF marker) */
+    uint64_t h2d_bytes, d2h_bytes;
+    float kernel_ms;                /* sum over launches: compress + pack kernels (CUDA events) */
+    float total_ms;
+} dh_deflate_stats;
+uint64_t dh_bgzf_deflate_bound(uint64_t in_size);      /* an output capacity that always suffices */
+int dh_bgzf_deflate_host(dh_ctx *ctx, const uint8_t *in, uint64_t in_size, int level, uint8_t *out, uint64_t out_cap,
+                         uint64_t *out_size, dh_deflate_stats *stats);
+/* file descriptor to file descriptor, streamed through three staging slots (in_fd seekable); what bgzip() runs */
+int dh_bgzf_deflate_fd(dh_ctx *ctx, int in_fd, int out_fd, int level, dh_deflate_stats *stats);
+
 /* Device-resident variant used for kernel-level measurement and by the BAM scan: upload once, inflate
  * any number of times.  dh_bgzf_dev_load frames `comp` on the host, uploads it and the block table;
  * dh_bgzf_dev_inflate enqueues the kernel(s) on the context's stream WITHOUT synchronising;

@@ -43,12 +43,14 @@ for stage in "$@"; do
         if [ $v = 4 ]; then export DH_RESOLVE4=1; else unset DH_RESOLVE4; fi
         timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve$v', json.dumps({'value': d['value'], 'inflate': d['inflate'], 'e2e': d['e2e']['value']}))"
       done > gpurun_out/${T}_ab_resolve.log 2>&1; unset DH_RESOLVE4; cat gpurun_out/${T}_ab_resolve.log ;;
-    ab_overlap) # who shares an SM with phase 1: pools of 227 KB (nobody) or 222 KB; phase 2 with / without its shared-memory tables; one or two inflate streams
-      for cfg in "0 0 1" "1 0 1" "1 1 1" "1 1 2" "0 1 2" "0 0 2"; do
-        set -- $cfg
-        export DH_P1_SMALL=$1 DH_RESOLVE_LDG=$2 DH_PHASE_STREAMS=$3
-        timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('p1_small=$1 resolve_ldg=$2 phase_streams=$3', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'inflate': d['inflate'], 'e2e': d['e2e']['value'], 'parity': d.get('parity', {}).get('ok')}))"
-      done > gpurun_out/${T}_ab_overlap.log 2>&1; unset DH_P1_SMALL DH_RESOLVE_LDG DH_PHASE_STREAMS; cat gpurun_out/${T}_ab_overlap.log ;;
+    ab_overlap) # who shares an SM with phase 1: pools of 227 KB (nobody) or 222 KB; phase 2 with / without its shared-memory tables; one or two inflate
+      # streams; the other kernels asking for the same (maximal) shared-memory carve-out as phase 1 or not
+      for cfg in ${AB_CFGS:-"0,0,1,0" "1,0,1,0" "1,0,1,1" "1,1,1,1" "1,1,2,1" "1,0,2,1"}; do
+        IFS=, read a b c d <<< "$cfg"
+        export DH_P1_SMALL=$a DH_RESOLVE_LDG=$b DH_PHASE_STREAMS=$c DH_CARVEOUT_MAX=$d
+        timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('p1_small=$a resolve_ldg=$b phase_streams=$c carveout_max=$d', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'inflate': d['inflate'], 'e2e': d['e2e']['value'], 'parity': d.get('parity')}))"
+      done > gpurun_out/${T}_ab_overlap.log 2>&1; unset DH_P1_SMALL DH_RESOLVE_LDG DH_PHASE_STREAMS DH_CARVEOUT_MAX; cat gpurun_out/${T}_ab_overlap.log ;;
+    deflate) timeout 1200 python -m pytest tests/test_deflate_gpu.py -m gpu -x -q -s > gpurun_out/${T}_pytest_deflate.log 2>&1; echo "pytest(deflate) exit $?" | tee -a gpurun_out/${T}_pytest_deflate.log; tail -40 gpurun_out/${T}_pytest_deflate.log ;;
     cfg4) # BASELINE configs[3] at size: a sorted 100 M-record file, index built on the GPU and by htslib, every cell hashed against the reference
       df -h /tmp | tail -1
       timeout 2400 python tools/cfg4_100m.py --records ${CFG4_RECORDS:-100e6} --devices 0 --out gpurun_out/${T}_cfg4.json > gpurun_out/${T}_cfg4.log 2>&1; echo "cfg4 exit $?" | tee -a gpurun_out/${T}_cfg4.log
