@@ -216,6 +216,52 @@ def common_config(args):
             "records_per_gpu_target": int(args.records), "sharding": "contiguous virtual-offset range per GPU, no collective"}
 
 
+def bench_bgzip(dh, ctx, unit_path, tiles, ncpu):
+    """N1: bgzip of the inflated unit BAM stream tiled `tiles` times (a file in the page cache -> /dev/null), dh_bgzf_deflate_fd
+    against the reference's bgzip() (htslib bgzf_write + bgzf_mt with all cores) on the same file."""
+    import ctypes as C
+    from duckhts_b200._lib import InflateStats, lib as L
+    raw_path = os.path.join(CACHE, "bench_bgzip_in.bin")
+    out = {"what": "bgzip of the inflated record stream of the unit BAM (file in the page cache -> compressed stream to /dev/null): pread, H2D, "
+                   "bgzf_deflate_kernel + pack, D2H, write(2)"}
+    try:
+        fd_in, fd_out = os.open(unit_path, os.O_RDONLY), os.open(raw_path + ".unit", os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
+        sti = InflateStats()
+        rc = L().dh_bgzf_inflate_fd(ctx.h, fd_in, fd_out, C.byref(sti))
+        os.close(fd_in)
+        os.close(fd_out)
+        assert rc == 0, rc
+        with open(raw_path, "wb") as f:
+            unit = open(raw_path + ".unit", "rb").read()
+            for _ in range(tiles):
+                f.write(unit)
+        os.unlink(raw_path + ".unit")
+        best, st = None, None
+        for _ in range(3):
+            fi, fo = os.open(raw_path, os.O_RDONLY), os.open("/dev/null", os.O_WRONLY)
+            t0 = time.perf_counter()
+            st = dh.bgzf_deflate_fd(ctx, fi, fo)
+            dt = time.perf_counter() - t0
+            os.close(fi)
+            os.close(fo)
+            best = dt if best is None else min(best, dt)
+        out.update({"metric": "bgzip_input_GBps_host_to_host", "value": st.in_bytes / 1e9 / best, "unit": "GB/s", "seconds": best, "input_gb": st.in_bytes / 1e9,
+                    "output_gb": st.out_bytes / 1e9, "ratio": st.out_bytes / st.in_bytes, "blocks": int(st.n_blocks), "kernel_ms": st.kernel_ms,
+                    "kernel_input_GBps": st.in_bytes / 1e9 / (st.kernel_ms / 1e3)})
+        if os.path.exists(REF_EXT) and os.path.exists(FAKE_HOST):
+            ref_out = raw_path + ".ref.gz"
+            r = host_run(REF_EXT, "bgzip", raw_path, "output_path=" + ref_out, f"threads={ncpu}", "overwrite=true", threads=1)
+            out["reference"] = {"value": st.in_bytes / 1e9 / r["seconds"], "unit": "GB/s", "seconds": r["seconds"], "htslib_threads": ncpu,
+                                "output_gb": os.path.getsize(ref_out) / 1e9, "ratio": os.path.getsize(ref_out) / st.in_bytes,
+                                "what": "the unchanged reference extension's bgzip() (bgzf_write, zlib default level, bgzf_mt) on the same file, output to a file in /tmp"}
+            os.unlink(ref_out)
+    except Exception as e:  # noqa: BLE001
+        out["error"] = str(e)[:300]
+    if os.path.exists(raw_path):
+        os.unlink(raw_path)
+    return out
+
+
 def gen_bcf(n_sites, n_samples, seed):
     os.makedirs(CACHE, exist_ok=True)
     path = os.path.join(CACHE, f"bench_bcf_{n_sites}_{n_samples}_{seed}.bcf")
@@ -651,6 +697,7 @@ def main():
             ext["error"] = str(e)[:300]
     if os.path.exists(big_path):
         os.unlink(big_path)
+    bgzip = bench_bgzip(dh, ctx, unit_path, 4, ncpu) if rank == 0 and world == 1 and not args.no_ext else None
 
     bcf_res = bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum) if args.bcf_sites > 0 and os.path.exists(os.path.join(HARNESS, "gen_bcf")) else None
     shard_res = bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rsum)
@@ -691,7 +738,7 @@ def main():
                         "pcie_return_roofline_frac_bidir": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / bi_d2h,
                         "duckdb_layout": {"value": total_rows / 1e6 / (e2e_duck_step / 1e3), "unit": "Mrecords/s", "ms_per_step": e2e_duck_step,
                                           "d2h_bytes_per_step": int(d2h_duck), "d2h_bytes_per_record": d2h_duck / max(rows, 1)}},
-                "ext_e2e": ext, "bgunzip_e2e": bgunzip, "strong_scaling": strong,
+                "ext_e2e": ext, "bgunzip_e2e": bgunzip, "bgzip_e2e": bgzip, "strong_scaling": strong,
                 "read_bcf": bcf_res, "contig_sharded": shard_res,
                 "cpu_baseline": cpu, "clocks": clk.summary(), "gpu_launches": int(launches), "host_cores": ncpu}
         print(json.dumps(line), flush=True)
