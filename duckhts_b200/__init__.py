@@ -9,3 +9,4 @@ from ._lib import DuckhtsError, lib, lib_path  # noqa: F401
 from .bgzf import BgzfDevice, Context, bgzf_deflate, bgzf_deflate_fd, bgzf_inflate, bgzf_walk  # noqa: F401
 from .bam import BamFile, Index, bam_scan, batch_to_columns, STD_TAGS, VOFF_MAX  # noqa: F401,E402
 from .bcf import BcfFile  # noqa: F401,E402
+from .text import TextFile  # noqa: F401,E402

@@ -1520,6 +1520,378 @@ static void register_bgzip(duckdb_connection con) {
 }
 
 /* ================================================================================================================
+ * read_tabix (N4) — the generic tab-separated reader of the reference (src/tabix_reader.c:500-778 bind, 852-1030 scan), sequential
+ * scan of a bgzip'ed file.  Bind sniffs the first lines like the reference (the index's meta character and line_skip, the header
+ * line, the number of fields of the first data line, auto_detect over 100 lines); the scan takes batches of lines from dh_text
+ * (every line and field located on the GPU) and applies the reference's per-cell rules: absent, empty and "." are NULL, BIGINT /
+ * DOUBLE columns go through strtoll / strtod and are NULL unless the whole field parses.  Not served by this build: region queries
+ * (bind error), read_gtf / read_gff.
+ * ================================================================================================================ */
+#define TBX_MAX_COLS 256
+typedef struct {
+    char *path;
+    dh_ctx *ctx;
+    dh_text *text;
+    int n_cols, meta_char, line_skip, skip_header_line;
+    int types[TBX_MAX_COLS];            /* DUCKDB_TYPE_VARCHAR / BIGINT / INTEGER / DOUBLE */
+} tbx_bind_t;
+typedef struct {
+    tbx_bind_t *bind;
+    idx_t n_proj;
+    idx_t *col_ids;                     /* cell slot of output vector i, or -1 */
+    int *col_types;                     /* its type */
+    dh_text_batch b;
+    int have;                           /* a batch is open */
+    uint64_t next;                      /* next line of it */
+    int skip_remaining, skipped_header, finished;
+} tbx_global_t;
+
+static void tbx_bind_free(void *p) {
+    tbx_bind_t *b = (tbx_bind_t *)p;
+    if (!b) return;
+    if (b->text) dh_text_close(b->text);
+    if (b->ctx) ctx_release(b->ctx);
+    free(b->path);
+    api.duckdb_free(b);
+}
+static void tbx_global_free(void *p) { tbx_global_t *g = (tbx_global_t *)p; if (g) { free(g->col_ids); free(g->col_types); api.duckdb_free(g); } }
+
+static int tbx_type_of_name(const char *s) {           /* src/tabix_reader.c:218-232 */
+    if (!s) return DUCKDB_TYPE_VARCHAR;
+    if (!strcasecmp(s, "INT") || !strcasecmp(s, "INTEGER")) return DUCKDB_TYPE_INTEGER;
+    if (!strcasecmp(s, "BIGINT") || !strcasecmp(s, "LONG")) return DUCKDB_TYPE_BIGINT;
+    if (!strcasecmp(s, "DOUBLE") || !strcasecmp(s, "FLOAT") || !strcasecmp(s, "REAL")) return DUCKDB_TYPE_DOUBLE;
+    return DUCKDB_TYPE_VARCHAR;
+}
+static int tbx_count_fields(const char *s, size_t n) { int c = 1; for (size_t i = 0; i < n; ++i) c += s[i] == '\t'; return c; }
+/* the idx-th field of line s[0, n): NULL if the line has fewer */
+static const char *tbx_field(const char *s, size_t n, int idx, int *len) {
+    int cur = 0;
+    size_t start = 0;
+    for (size_t i = 0; i <= n; ++i)
+        if (i == n || s[i] == '\t') {
+            if (cur == idx) { *len = (int)(i - start); return s + start; }
+            ++cur;
+            start = i + 1;
+        }
+    *len = 0;
+    return NULL;
+}
+static int tbx_parse_i64(const char *s, int len, int64_t *out) {      /* parse_int64_span, src/tabix_reader.c:58-68 */
+    if (len <= 0 || len >= 128) return 0;
+    char buf[128], *end = NULL;
+    memcpy(buf, s, (size_t)len);
+    buf[len] = 0;
+    const long long v = strtoll(buf, &end, 10);
+    if (!end || *end) return 0;
+    *out = (int64_t)v;
+    return 1;
+}
+static int tbx_parse_f64(const char *s, int len, double *out) {
+    if (len <= 0 || len >= 128) return 0;
+    char buf[128], *end = NULL;
+    memcpy(buf, s, (size_t)len);
+    buf[len] = 0;
+    const double v = strtod(buf, &end);
+    if (!end || *end) return 0;
+    *out = v;
+    return 1;
+}
+static int tbx_is_integer(const char *s, int len) {
+    int i = 0;
+    if (len == 0) return 0;
+    if (s[i] == '-' || s[i] == '+') ++i;
+    if (i >= len) return 0;
+    for (; i < len; ++i) if (s[i] < '0' || s[i] > '9') return 0;
+    return 1;
+}
+static int tbx_is_float(const char *s, int len) {      /* is_float_field: strtod takes the whole field (no length cap there) */
+    if (len == 0) return 0;
+    char *tmp = (char *)malloc((size_t)len + 1), *end = NULL;
+    if (!tmp) return 0;
+    memcpy(tmp, s, (size_t)len);
+    tmp[len] = 0;
+    strtod(tmp, &end);
+    const int ok = end && !*end;
+    free(tmp);
+    return ok;
+}
+/* meta character and line_skip of the tabix index next to the file (tbx_index_load2 -> tbx->conf, htslib/tbx.c:443-470): a .csi's
+ * aux block or a .tbi's header hold {format, col_seq, col_beg, col_end, meta, skip, l_nm}.  Returns 1 if an index was read. */
+static int tbx_conf_from_index(dh_ctx *ctx, const char *path, const char *index_path, int *meta, int *skip) {
+    char cand[2][1100];
+    int nc = 0;
+    if (index_path) snprintf(cand[nc++], sizeof cand[0], "%s", index_path);
+    else { snprintf(cand[nc++], sizeof cand[0], "%s.csi", path); snprintf(cand[nc++], sizeof cand[0], "%s.tbi", path); }
+    for (int i = 0; i < nc; ++i) {
+        if (!file_exists(cand[i])) continue;
+        uint64_t isz = 0, n = 0;
+        uint8_t *ibuf = slurp_pinned(cand[i], &isz);
+        if (!ibuf) return 0;
+        uint8_t head[4096];
+        /* the index is BGZF-compressed: its first block holds the header */
+        uint32_t bsize = isz >= 18 ? (uint32_t)(ibuf[16] | (ibuf[17] << 8)) + 1u : 0u;
+        int ok = bsize >= 26 && bsize <= isz;
+        uint8_t *tmp = ok ? (uint8_t *)malloc(65536) : NULL;
+        if (tmp && dh_bgzf_inflate_host(ctx, ibuf, bsize, tmp, 65536, &n, NULL) == DH_OK && n >= 36) memcpy(head, tmp, n < sizeof head ? n : sizeof head);
+        else ok = 0;
+        free(tmp);
+        dh_host_free(ibuf);
+        if (!ok) return 0;
+        const int32_t *w = NULL;
+        if (!memcmp(head, "TBI\1", 4)) w = (const int32_t *)(head + 8);                          /* magic, n_ref, then the conf */
+        else if (!memcmp(head, "CSI\1", 4) && *(const int32_t *)(head + 12) >= 28) w = (const int32_t *)(head + 16);   /* magic, min_shift, depth, l_aux, aux */
+        if (!w) return 0;
+        *meta = w[4];
+        *skip = w[5];
+        return 1;
+    }
+    return 0;
+}
+
+static void read_tabix_bind(duckdb_bind_info info) {
+    duckdb_value pv = api.duckdb_bind_get_parameter(info, 0);
+    char *path = api.duckdb_get_varchar(pv);
+    api.duckdb_destroy_value(&pv);
+    if (!path || !path[0]) { api.duckdb_bind_set_error(info, "read_tabix requires a file path"); if (path) api.duckdb_free(path); return; }
+    char *region = named_varchar(info, "region"), *index_path = named_varchar(info, "index_path");
+    const int header = named_bool(info, "header", 0), auto_detect = named_bool(info, "auto_detect", 0);
+    char err[1400];
+    err[0] = 0;
+    tbx_bind_t *b = (tbx_bind_t *)api.duckdb_malloc(sizeof *b);
+    memset(b, 0, sizeof *b);
+    b->meta_char = '#';
+    char **names = NULL;
+    int n_names = 0, types_given = 0, n_types = 0;
+    duckdb_value v = api.duckdb_bind_get_named_parameter(info, "header_names");
+    if (v && !api.duckdb_is_null_value(v)) {
+        const idx_t n = api.duckdb_get_list_size(v);
+        if (n > 0) {
+            names = (char **)calloc((size_t)n, sizeof(char *));
+            n_names = (int)n;
+            for (idx_t i = 0; i < n; ++i) { duckdb_value e = api.duckdb_get_list_child(v, i); char *s = api.duckdb_get_varchar(e); names[i] = strdup(s ? s : ""); if (s) api.duckdb_free(s); api.duckdb_destroy_value(&e); }
+        }
+    }
+    if (v) api.duckdb_destroy_value(&v);
+    v = api.duckdb_bind_get_named_parameter(info, "column_types");
+    if (v && !api.duckdb_is_null_value(v)) {
+        const idx_t n = api.duckdb_get_list_size(v);
+        if (n > 0) {
+            types_given = 1;
+            n_types = (int)(n > TBX_MAX_COLS ? TBX_MAX_COLS : n);
+            for (int i = 0; i < n_types; ++i) { duckdb_value e = api.duckdb_get_list_child(v, (idx_t)i); char *s = api.duckdb_get_varchar(e); b->types[i] = tbx_type_of_name(s); if (s) api.duckdb_free(s); api.duckdb_destroy_value(&e); }
+            b->n_cols = (int)n;
+        }
+    }
+    if (v) api.duckdb_destroy_value(&v);
+
+    uint8_t *head = NULL;
+    uint64_t head_n = 0;
+    int devs[MAX_SOURCES];
+    device_list(devs);
+    if (region && region[0]) snprintf(err, sizeof err, "read_tabix: region queries are not served by this build (sequential scans only)");
+    else if (!file_exists(path)) snprintf(err, sizeof err, "Cannot open file");
+    else if (!(b->ctx = ctx_acquire(devs[0]))) snprintf(err, sizeof err, "read_tabix: no usable CUDA device (%s)", dh_last_error());
+    else if (!(b->text = dh_text_open_file(b->ctx, path))) snprintf(err, sizeof err, "read_tabix: %s", dh_last_error());
+    else if (!(head = (uint8_t *)malloc(4u << 20)) || dh_text_head(b->text, head, 4u << 20, &head_n) != DH_OK) snprintf(err, sizeof err, "read_tabix: %s", head ? dh_last_error() : "out of memory");
+    if (!err[0]) {
+        int skip_lines = 0, from_index_meta = '#';
+        if (tbx_conf_from_index(b->ctx, path, index_path, &from_index_meta, &skip_lines)) b->meta_char = from_index_meta ? from_index_meta : '#';
+        b->line_skip = skip_lines;
+        /* the first lines, as the reference reads them (src/tabix_reader.c:657-680) */
+        int n_cols = 0, header_from_skip = 0;
+        char *header_candidate = NULL;
+        size_t hc_len = 0;
+        uint64_t pos = 0;
+        while (pos < head_n) {
+            uint64_t e = pos;
+            while (e < head_n && head[e] != '\n') ++e;
+            if (e == head_n && head_n == (4u << 20)) break;          /* a line cut by the end of what was sniffed */
+            size_t len = (size_t)(e - pos);
+            const char *line = (const char *)head + pos;
+            pos = e + 1;
+            if (len && line[len - 1] == '\r') --len;
+            if (len == 0) continue;
+            if (skip_lines > 0) {
+                if (header && !names) { free(header_candidate); header_candidate = strndup(line, len); hc_len = len; header_from_skip = 1; }
+                --skip_lines;
+                continue;
+            }
+            if (b->meta_char && line[0] == b->meta_char) continue;
+            if (header && !names && !header_candidate) { header_candidate = strndup(line, len); hc_len = len; }
+            else { n_cols = tbx_count_fields(line, len); break; }
+        }
+        if (names && n_names > 0) { n_cols = n_names; b->skip_header_line = header ? 1 : 0; }
+        else if (header && header_candidate) {
+            n_names = tbx_count_fields(header_candidate, hc_len);
+            names = (char **)calloc((size_t)n_names, sizeof(char *));
+            for (int i = 0; i < n_names; ++i) {
+                int flen = 0;
+                const char *f = tbx_field(header_candidate, hc_len, i, &flen);
+                while (f && flen > 0 && (*f == ' ' || *f == '\t')) { ++f; --flen; }
+                while (f && flen > 0 && (f[flen - 1] == ' ' || f[flen - 1] == '\t')) --flen;
+                names[i] = f ? strndup(f, (size_t)flen) : strdup("");
+            }
+            n_cols = n_names;
+            b->skip_header_line = header_from_skip ? 0 : 1;
+        }
+        free(header_candidate);
+        if (n_cols == 0) n_cols = 1;
+        if (n_cols > TBX_MAX_COLS) n_cols = TBX_MAX_COLS;
+        if (b->n_cols == 0) b->n_cols = n_cols;
+        if (types_given && b->n_cols != n_cols) snprintf(err, sizeof err, "column_types length does not match detected column count");
+        if (!err[0]) {
+            if (!types_given) for (int i = 0; i < b->n_cols; ++i) b->types[i] = DUCKDB_TYPE_VARCHAR;
+            if (auto_detect && !types_given) {
+                /* src/tabix_reader.c:706-757: up to 100 data lines; integers stay BIGINT, anything strtod takes makes DOUBLE, the rest VARCHAR */
+                int state[TBX_MAX_COLS];
+                for (int i = 0; i < b->n_cols; ++i) state[i] = DUCKDB_TYPE_INTEGER;
+                int skip2 = b->line_skip, skip_header = b->skip_header_line, seen = 0;
+                pos = 0;
+                while (seen < 100 && pos < head_n) {
+                    uint64_t e = pos;
+                    while (e < head_n && head[e] != '\n') ++e;
+                    size_t len = (size_t)(e - pos);
+                    const char *line = (const char *)head + pos;
+                    pos = e + 1;
+                    if (len && line[len - 1] == '\r') --len;
+                    if (len == 0) continue;
+                    if (skip2 > 0) { --skip2; continue; }
+                    if (b->meta_char && line[0] == b->meta_char) continue;
+                    if (skip_header) { skip_header = 0; continue; }
+                    for (int i = 0; i < b->n_cols; ++i) {
+                        int flen = 0;
+                        const char *f = tbx_field(line, len, i, &flen);
+                        if (!f || flen == 0 || (flen == 1 && f[0] == '.')) continue;
+                        if (tbx_is_integer(f, flen)) continue;
+                        if (tbx_is_float(f, flen)) { if (state[i] != DUCKDB_TYPE_VARCHAR) state[i] = DUCKDB_TYPE_DOUBLE; }
+                        else state[i] = DUCKDB_TYPE_VARCHAR;
+                    }
+                    ++seen;
+                }
+                for (int i = 0; i < b->n_cols; ++i) b->types[i] = state[i] == DUCKDB_TYPE_INTEGER ? DUCKDB_TYPE_BIGINT : state[i];
+            }
+            for (int i = 0; i < b->n_cols; ++i) {
+                char col_name[32];
+                const char *name = (names && i < n_names && names[i] && names[i][0]) ? names[i] : (snprintf(col_name, sizeof col_name, "column%d", i), col_name);
+                duckdb_logical_type t = api.duckdb_create_logical_type((duckdb_type)b->types[i]);
+                api.duckdb_bind_add_result_column(info, name, t);
+                api.duckdb_destroy_logical_type(&t);
+            }
+        }
+    }
+    free(head);
+    for (int i = 0; i < n_names; ++i) free(names[i]);
+    free(names);
+    if (err[0]) { api.duckdb_bind_set_error(info, err); tbx_bind_free(b); }
+    else { b->path = strdup(path); api.duckdb_bind_set_bind_data(info, b, tbx_bind_free); }
+    api.duckdb_free(path);
+    if (region) api.duckdb_free(region);
+    if (index_path) api.duckdb_free(index_path);
+}
+
+static void read_tabix_init(duckdb_init_info info) {
+    tbx_bind_t *b = (tbx_bind_t *)api.duckdb_init_get_bind_data(info);
+    tbx_global_t *g = (tbx_global_t *)api.duckdb_malloc(sizeof *g);
+    memset(g, 0, sizeof *g);
+    g->bind = b;
+    g->n_proj = api.duckdb_init_get_column_count(info);
+    g->col_ids = (idx_t *)calloc(g->n_proj ? g->n_proj : 1, sizeof(idx_t));
+    g->col_types = (int *)calloc(g->n_proj ? g->n_proj : 1, sizeof(int));
+    uint32_t proj[TBX_MAX_COLS];
+    uint32_t np = 0;
+    /* one cell slot per projected schema column; a column asked for twice shares its slot */
+    int slot_of[TBX_MAX_COLS];
+    for (int i = 0; i < TBX_MAX_COLS; ++i) slot_of[i] = -1;
+    for (idx_t i = 0; i < g->n_proj; ++i) {
+        const idx_t c = api.duckdb_init_get_column_index(info, i);
+        if (c < (idx_t)b->n_cols && slot_of[c] < 0) { slot_of[c] = (int)np; proj[np++] = (uint32_t)c; }
+        g->col_ids[i] = c < (idx_t)b->n_cols ? (idx_t)slot_of[c] : (idx_t)-1;
+        g->col_types[i] = c < (idx_t)b->n_cols ? b->types[c] : DUCKDB_TYPE_VARCHAR;
+    }
+    g->skip_remaining = b->line_skip;
+    api.duckdb_init_set_init_data(info, g, tbx_global_free);
+    api.duckdb_init_set_max_threads(info, 1);
+    if (dh_text_configure(b->text, (uint32_t)b->n_cols, proj, np, b->meta_char) != DH_OK || dh_text_scan_begin(b->text) != DH_OK)
+        api.duckdb_init_set_error(info, dh_last_error());
+}
+
+static void read_tabix_scan(duckdb_function_info info, duckdb_data_chunk output) {
+    tbx_global_t *g = (tbx_global_t *)api.duckdb_function_get_init_data(info);
+    tbx_bind_t *b = g->bind;
+    const idx_t ncol = api.duckdb_data_chunk_get_column_count(output);
+    duckdb_vector vecs[TBX_MAX_COLS];
+    void *data[TBX_MAX_COLS];
+    for (idx_t c = 0; c < ncol && c < TBX_MAX_COLS; ++c) { vecs[c] = api.duckdb_data_chunk_get_vector(output, c); data[c] = api.duckdb_vector_get_data(vecs[c]); }
+    idx_t rows = 0;
+    while (rows < 2048 && !g->finished) {
+        if (!g->have || g->next >= g->b.n_lines) {
+            const int rc = dh_text_next_batch(b->text, &g->b);
+            if (rc < 0) { api.duckdb_function_set_error(info, dh_last_error()); g->finished = 1; break; }
+            if (rc == 0) { g->finished = 1; break; }
+            g->have = 1;
+            g->next = 0;
+        }
+        const dh_text_batch *tb = &g->b;
+        for (; g->next < tb->n_lines && rows < 2048; ++g->next) {
+            const uint8_t fl = tb->flags[g->next];
+            /* src/tabix_reader.c:893-902, in that order: empty; the first line_skip lines; meta; the header line */
+            if (fl & 1) continue;
+            if (g->skip_remaining > 0) { --g->skip_remaining; continue; }
+            if (fl & 2) continue;
+            if (b->skip_header_line && !g->skipped_header) { g->skipped_header = 1; continue; }
+            const uint32_t *cells = tb->cells + g->next * tb->n_proj * 2u;
+            for (idx_t c = 0; c < ncol; ++c) {
+                const idx_t slot = g->col_ids[c];
+                if (slot == (idx_t)-1) continue;
+                const uint32_t beg = cells[2 * slot], end = cells[2 * slot + 1];
+                const char *f = (const char *)tb->text + beg;
+                const int flen = beg == 0xffffffffu ? 0 : (int)(end - beg);
+                int null = beg == 0xffffffffu || flen == 0 || (flen == 1 && f[0] == '.');
+                const int ty = g->col_types[c];
+                if (!null && (ty == DUCKDB_TYPE_BIGINT || ty == DUCKDB_TYPE_INTEGER)) {
+                    int64_t val = 0;
+                    if (tbx_parse_i64(f, flen, &val)) { if (ty == DUCKDB_TYPE_BIGINT) ((int64_t *)data[c])[rows] = val; else ((int32_t *)data[c])[rows] = (int32_t)val; }
+                    else null = 1;
+                } else if (!null && ty == DUCKDB_TYPE_DOUBLE) {
+                    double val = 0;
+                    if (tbx_parse_f64(f, flen, &val)) ((double *)data[c])[rows] = val; else null = 1;
+                } else if (!null) put_string(vecs[c], (duckdb_string_t *)data[c], rows, f, (uint32_t)flen);
+                if (null) {
+                    api.duckdb_vector_ensure_validity_writable(vecs[c]);
+                    uint64_t *val = api.duckdb_vector_get_validity(vecs[c]);
+                    val[rows >> 6] &= ~(1ull << (rows & 63));
+                }
+            }
+            ++rows;
+        }
+    }
+    api.duckdb_data_chunk_set_size(output, rows);
+}
+
+static void register_read_tabix(duckdb_connection con) {
+    duckdb_table_function tf = api.duckdb_create_table_function();
+    duckdb_logical_type t_varchar = api.duckdb_create_logical_type(DUCKDB_TYPE_VARCHAR), t_bool = api.duckdb_create_logical_type(DUCKDB_TYPE_BOOLEAN);
+    duckdb_logical_type t_list = api.duckdb_create_list_type(t_varchar);
+    api.duckdb_table_function_set_name(tf, "read_tabix");
+    api.duckdb_table_function_add_parameter(tf, t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "region", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "index_path", t_varchar);
+    api.duckdb_table_function_add_named_parameter(tf, "attributes_map", t_bool);     /* accepted like the reference's shared registration; read_gtf / read_gff only */
+    api.duckdb_table_function_add_named_parameter(tf, "header", t_bool);
+    api.duckdb_table_function_add_named_parameter(tf, "header_names", t_list);
+    api.duckdb_table_function_add_named_parameter(tf, "auto_detect", t_bool);
+    api.duckdb_table_function_add_named_parameter(tf, "column_types", t_list);
+    api.duckdb_table_function_set_bind(tf, read_tabix_bind);
+    api.duckdb_table_function_set_init(tf, read_tabix_init);
+    api.duckdb_table_function_set_function(tf, read_tabix_scan);
+    api.duckdb_table_function_supports_projection_pushdown(tf, true);
+    api.duckdb_register_table_function(con, tf);
+    api.duckdb_destroy_table_function(&tf);
+    api.duckdb_destroy_logical_type(&t_list); api.duckdb_destroy_logical_type(&t_varchar); api.duckdb_destroy_logical_type(&t_bool);
+}
+
+/* ================================================================================================================
  * bam_index — like the reference (src/hts_index_builder.c:110-160, 326-345): the index is built in bind (sam_index_build3 there,
  * one GPU scan here: dh_bam_index_build) and the scan returns one row (success, index_path, index_format).  BAI only (min_shift 0).
  * ================================================================================================================ */
@@ -1610,6 +1982,7 @@ __attribute__((visibility("default"))) bool duckhts_init_c_api(duckdb_extension_
     register_read_bcf(con);
     register_bgunzip(con);
     register_bgzip(con);
+    register_read_tabix(con);
     register_bam_index(con);
     api.duckdb_disconnect(&con);
     return true;

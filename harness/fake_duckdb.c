@@ -60,6 +60,8 @@ typedef struct Val {
     int is_null;
     char *s;
     int64_t i;
+    struct Val **items;           /* LIST: name=a,b,c on the command line */
+    idx_t n_items;
 } Val;
 
 typedef struct { char *name; LType *type; } NamedParam;
@@ -255,8 +257,15 @@ static idx_t api_chunk_get_column_count(duckdb_data_chunk c) { return ((Chunk *)
 
 /* ---- values ------------------------------------------------------------------------------------------------------ */
 static Val *val_null(void) { Val *v = xmalloc(sizeof *v); v->is_null = 1; v->id = DUCKDB_TYPE_INVALID; return v; }
-static Val *val_copy(const Val *s) { Val *v = xmalloc(sizeof *v); *v = *s; if (s->s) v->s = xstrdup(s->s); return v; }
-static void api_destroy_value(duckdb_value *v) { if (v && *v) { Val *x = (Val *)*v; free(x->s); free(x); *v = NULL; } }
+static Val *val_copy(const Val *s) {
+    Val *v = xmalloc(sizeof *v);
+    *v = *s;
+    if (s->s) v->s = xstrdup(s->s);
+    if (s->n_items) { v->items = xmalloc(sizeof(Val *) * s->n_items); for (idx_t i = 0; i < s->n_items; ++i) v->items[i] = val_copy(s->items[i]); }
+    return v;
+}
+static void val_free(Val *x) { if (!x) return; for (idx_t i = 0; i < x->n_items; ++i) val_free(x->items[i]); free(x->items); free(x->s); free(x); }
+static void api_destroy_value(duckdb_value *v) { if (v && *v) { val_free((Val *)*v); *v = NULL; } }
 static bool api_is_null_value(duckdb_value v) { return !v || ((Val *)v)->is_null; }
 static char *api_get_varchar(duckdb_value vv) {      /* caller frees with duckdb_free */
     Val *v = (Val *)vv;
@@ -276,8 +285,11 @@ static bool api_get_bool(duckdb_value vv) {
 }
 static int64_t api_get_int64(duckdb_value vv) { Val *v = (Val *)vv; if (!v || v->is_null) return 0; return v->s ? strtoll(v->s, NULL, 10) : v->i; }
 static duckdb_logical_type api_get_value_type(duckdb_value vv) { return api_create_logical_type(vv ? ((Val *)vv)->id : DUCKDB_TYPE_INVALID); }
-static idx_t api_get_list_size(duckdb_value v) { (void)v; return 0; }
-static duckdb_value api_get_list_child(duckdb_value v, idx_t i) { (void)v; (void)i; return (duckdb_value)val_null(); }
+static idx_t api_get_list_size(duckdb_value v) { return v ? ((Val *)v)->n_items : 0; }
+static duckdb_value api_get_list_child(duckdb_value v, idx_t i) {
+    Val *x = (Val *)v;
+    return (duckdb_value)(x && i < x->n_items ? val_copy(x->items[i]) : val_null());
+}
 
 /* ---- table functions ---------------------------------------------------------------------------------------------- */
 static duckdb_table_function api_create_table_function(void) { return (duckdb_table_function)xmalloc(sizeof(TFunc)); }
@@ -534,6 +546,15 @@ static Val *parse_value(const char *text, const LType *t) {
     Val *v = xmalloc(sizeof *v);
     v->id = t ? t->id : DUCKDB_TYPE_VARCHAR;
     if (!strcmp(text, "NULL")) { v->is_null = 1; return v; }
+    if (v->id == DUCKDB_TYPE_LIST) {
+        char *dup = xstrdup(text), *save = NULL;
+        idx_t cap = 1;
+        for (const char *q = text; *q; ++q) cap += *q == ',';
+        v->items = xmalloc(sizeof(Val *) * cap);
+        for (char *tok = strtok_r(dup, ",", &save); tok; tok = strtok_r(NULL, ",", &save)) v->items[v->n_items++] = parse_value(tok, t->child);
+        free(dup);
+        return v;
+    }
     if (v->id == DUCKDB_TYPE_BOOLEAN) v->i = !strcasecmp(text, "true") || !strcmp(text, "1");
     else if (v->id == DUCKDB_TYPE_VARCHAR) v->s = xstrdup(text);
     else v->i = strtoll(text, NULL, 10);
@@ -563,7 +584,7 @@ int main(int argc, char **argv) {
     for (int i = 0; i < g_nfuncs; ++i) if (!strcmp(g_funcs[i]->name, fname)) tf = g_funcs[i];
     if (!tf) { fprintf(stderr, "table function %s not registered (have:", fname); for (int i = 0; i < g_nfuncs; ++i) fprintf(stderr, " %s", g_funcs[i]->name); fprintf(stderr, ")\n"); return 2; }
 
-    int repeat = 1, want_time = 0;
+    int repeat = 1, want_time = 0, want_types = 0;
     for (int i = 4; i < argc; ++i) if (!strcmp(argv[i], "--repeat") && i + 1 < argc) repeat = atoi(argv[i + 1]);
     if (repeat < 1) repeat = 1;
     int rc = 0;
@@ -583,6 +604,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--threads") && i + 1 < argc) threads = atoi(argv[++i]);
         else if (!strcmp(argv[i], "--repeat") && i + 1 < argc) ++i;
         else if (!strcmp(argv[i], "--entry") && i + 1 < argc) ++i;
+        else if (!strcmp(argv[i], "--types")) want_types = 1;
         else {
             char *eq = strchr(argv[i], '=');
             if (!eq) { fprintf(stderr, "bad argument %s\n", argv[i]); return 2; }
@@ -616,6 +638,13 @@ int main(int argc, char **argv) {
     if ((idx_t)threads > global.max_threads) threads = (int)global.max_threads;
     if (mode == MODE_DUMP) {
         for (idx_t c = 0; c < n_col_ids; ++c) printf("%s%s", bind.col_names[col_ids[c]], c + 1 < n_col_ids ? "\t" : "\n");
+        /* --types: the duckdb_type id of every column (of a LIST's element behind a slash) */
+        if (want_types) for (idx_t c = 0; c < n_col_ids; ++c) {
+            const LType *t = bind.col_types[col_ids[c]];
+            printf("#%d", (int)t->id);
+            if (t->child) printf("/%d", (int)t->child->id);
+            printf("%s", c + 1 < n_col_ids ? "\t" : "\n");
+        }
     }
     pthread_mutex_t lock = PTHREAD_MUTEX_INITIALIZER;
     Worker *ws = xmalloc(sizeof(Worker) * threads);

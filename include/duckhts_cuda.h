@@ -115,6 +115,28 @@ int dh_bgzf_deflate_host(dh_ctx *ctx, const uint8_t *in, uint64_t in_size, int l
 /* file descriptor to file descriptor, streamed through three staging slots (in_fd seekable); what bgzip() runs */
 int dh_bgzf_deflate_fd(dh_ctx *ctx, int in_fd, int out_fd, int level, dh_deflate_stats *stats);
 
+/* ---- N4: the text path (read_tabix's sequential scan, src/tabix_reader.c:852-1030: hts_getline per line, get_field per cell).
+ * A bgzip'ed tab-separated text file comes back as batches of whole lines: the inflated text and, for every line and every
+ * projected column, the [begin, end) offsets of the field (a '\r' in front of the '\n' is not part of the line, like
+ * bgzf_getline).  flags[i] marks the lines the reference skips wherever they stand: 1 = an empty line, 2 = one that starts with the
+ * meta character.  What depends on the line NUMBER (line_skip, the header line) and the typed conversions stay with the caller. */
+typedef struct dh_text dh_text;
+typedef struct dh_text_batch {
+    uint64_t n_lines, line0;        /* lines in this batch; number of the first one in the file */
+    const uint8_t *text;            /* pinned host memory, valid until the next call on the handle */
+    uint64_t text_bytes;
+    const uint32_t *cells;          /* [n_lines][n_proj][2]: begin, end; begin = 0xffffffff: the line has fewer fields */
+    const uint8_t *flags;           /* [n_lines] */
+    uint32_t n_proj;
+    int32_t status;                 /* with return value 0: 0 = end of file, -2 = a cut or corrupt block ended the scan */
+} dh_text_batch;
+dh_text *dh_text_open_file(dh_ctx *ctx, const char *path);          /* NULL: unreadable, or not BGZF (dh_last_error) */
+void dh_text_close(dh_text *t);
+int dh_text_head(dh_text *t, uint8_t *buf, uint64_t cap, uint64_t *n);      /* the first inflated bytes (whole blocks, <= cap) */
+int dh_text_configure(dh_text *t, uint32_t n_cols, const uint32_t *proj, uint32_t n_proj, int meta_char);
+int dh_text_scan_begin(dh_text *t);
+int dh_text_next_batch(dh_text *t, dh_text_batch *out);             /* 1 = a batch, 0 = done (out->status), < 0 = error */
+
 /* Device-resident variant used for kernel-level measurement and by the BAM scan: upload once, inflate
  * any number of times.  dh_bgzf_dev_load frames `comp` on the host, uploads it and the block table;
  * dh_bgzf_dev_inflate enqueues the kernel(s) on the context's stream WITHOUT synchronising;

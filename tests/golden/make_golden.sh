@@ -57,3 +57,19 @@ for f in vcf_file edge_small plain_small; do
   $H $RX read_bcf $f.bcf tidy_format=true --dump > $f.bcf.tidy.txt 2>/dev/null
   $H $RX read_bcf $f.bcf --dump > $f.bcf.wide.txt 2>/dev/null
 done
+# ---- N4: the reference's text fixtures and what its read_tabix returns for them (the unchanged extension under harness/fake_duckdb)
+H=../../harness/_bin/fake_duckdb
+R=../../oracle/_ref/libduckhts_ref.so
+for f in meta_tabix.tsv.gz header_tabix.tsv.gz gff_file.gff.gz formatcols.vcf.gz no_contig.vcf.gz; do
+  cp $REF/test/data/$f $f; chmod u+w $f
+  for x in tbi csi; do if [ -f $REF/test/data/$f.$x ]; then cp $REF/test/data/$f.$x $f.$x; chmod u+w $f.$x; fi; done
+done
+$H $R read_tabix meta_tabix.tsv.gz --dump --types > tabix.meta.tsv
+$H $R read_tabix meta_tabix.tsv.gz header_names=chrom,pos,value --dump --types > tabix.meta_names.tsv
+$H $R read_tabix meta_tabix.tsv.gz auto_detect=true --dump --types > tabix.meta_auto.tsv
+$H $R read_tabix header_tabix.tsv.gz header=true --dump --types > tabix.header.tsv
+$H $R read_tabix header_tabix.tsv.gz header=true column_types=VARCHAR,BIGINT,VARCHAR --dump --types > tabix.header_types.tsv
+$H $R read_tabix gff_file.gff.gz --dump --types > tabix.gff.tsv
+$H $R read_tabix gff_file.gff.gz --cols 0,2 --dump --types > tabix.gff_proj.tsv
+$H $R read_tabix formatcols.vcf.gz --dump --types > tabix.vcf.tsv
+$H $R read_tabix no_contig.vcf.gz auto_detect=true --dump --types > tabix.no_contig_auto.tsv

@@ -50,6 +50,7 @@ for stage in "$@"; do
         export DH_P1_SMALL=$a DH_RESOLVE_LDG=$b DH_PHASE_STREAMS=$c DH_CARVEOUT_MAX=$d
         timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('p1_small=$a resolve_ldg=$b phase_streams=$c carveout_max=$d', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'inflate': d['inflate'], 'e2e': d['e2e']['value'], 'parity': d.get('parity')}))"
       done > gpurun_out/${T}_ab_overlap.log 2>&1; unset DH_P1_SMALL DH_RESOLVE_LDG DH_PHASE_STREAMS DH_CARVEOUT_MAX; cat gpurun_out/${T}_ab_overlap.log ;;
+    text) timeout 1200 python -m pytest tests/test_text_gpu.py -m gpu -x -q > gpurun_out/${T}_pytest_text.log 2>&1; echo "pytest(text) exit $?" | tee -a gpurun_out/${T}_pytest_text.log; tail -40 gpurun_out/${T}_pytest_text.log ;;
     deflate) timeout 1200 python -m pytest tests/test_deflate_gpu.py -m gpu -x -q -s > gpurun_out/${T}_pytest_deflate.log 2>&1; echo "pytest(deflate) exit $?" | tee -a gpurun_out/${T}_pytest_deflate.log; tail -40 gpurun_out/${T}_pytest_deflate.log ;;
     cfg4) # BASELINE configs[3] at size: a sorted 100 M-record file, index built on the GPU and by htslib, every cell hashed against the reference
       df -h /tmp | tail -1
