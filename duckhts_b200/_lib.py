@@ -26,6 +26,11 @@ class DeflateStats(C.Structure):
                 ("d2h_bytes", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
 
 
+class TextBatch(C.Structure):
+    _fields_ = [("n_lines", C.c_uint64), ("line0", C.c_uint64), ("text", C.c_void_p), ("text_bytes", C.c_uint64),
+                ("cells", C.c_void_p), ("flags", C.c_void_p), ("n_proj", C.c_uint32), ("status", C.c_int32)]
+
+
 DH_BAM_CORE_COLS = 13
 DH_BAM_MAX_COLS = 13 + 63
 
@@ -116,6 +121,12 @@ SIGNATURES = {
     "dh_index_split_contigs": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32)]),
     "dh_bgzf_inflate_fd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(InflateStats)]),
     "dh_bgzf_deflate_bound": (C.c_uint64, [C.c_uint64]),
+    "dh_text_open_file": (C.c_void_p, [C.c_void_p, C.c_char_p]),
+    "dh_text_close": (None, [C.c_void_p]),
+    "dh_text_head": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dh_text_configure": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32), C.c_uint32, C.c_int]),
+    "dh_text_scan_begin": (C.c_int, [C.c_void_p]),
+    "dh_text_next_batch": (C.c_int, [C.c_void_p, C.POINTER(TextBatch)]),
     "dh_bgzf_deflate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64),
                                        C.POINTER(DeflateStats)]),
     "dh_bgzf_deflate_fd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(DeflateStats)]),

@@ -4,34 +4,11 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import DuckhtsError, check, lib
-
-
-class TextBatch(C.Structure):
-    _fields_ = [("n_lines", C.c_uint64), ("line0", C.c_uint64), ("text", C.c_void_p), ("text_bytes", C.c_uint64),
-                ("cells", C.c_void_p), ("flags", C.c_void_p), ("n_proj", C.c_uint32), ("status", C.c_int32)]
-
-
-_SIGS = {
-    "dh_text_open_file": (C.c_void_p, [C.c_void_p, C.c_char_p]),
-    "dh_text_close": (None, [C.c_void_p]),
-    "dh_text_head": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
-    "dh_text_configure": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32), C.c_uint32, C.c_int]),
-    "dh_text_scan_begin": (C.c_int, [C.c_void_p]),
-    "dh_text_next_batch": (C.c_int, [C.c_void_p, C.POINTER(TextBatch)]),
-}
-_bound = False
+from ._lib import DuckhtsError, TextBatch, check, lib
 
 
 def _lib():
-    global _bound
-    L = lib()
-    if not _bound:
-        for name, (res, args) in _SIGS.items():
-            f = getattr(L, name)
-            f.restype, f.argtypes = res, args
-        _bound = True
-    return L
+    return lib()
 
 
 class TextFile:

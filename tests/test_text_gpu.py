@@ -73,7 +73,7 @@ def test_lines_and_fields_against_the_restatement(ctx, tmp_path, monkeypatch, bl
         with dh.TextFile(ctx, path) as tf:
             got, status = tf.scan(n_cols, proj)
             if seg_kb:
-                assert tf.batches > 3
+                assert tf.batches > 2
         exp = oracle_lines(data, n_cols, list(range(n_cols)) if proj is None else proj)
         assert status == 0 and len(got) == len(exp)
         assert got == exp
