@@ -262,6 +262,34 @@ def bench_bgzip(dh, ctx, unit_path, tiles, ncpu):
     return out
 
 
+def bench_tabix(dh, ctx):
+    """N4: read_tabix over a bgzip'ed 5-column table, every column, through both extensions under the fake host."""
+    out = {"what": "read_tabix(path), all 5 VARCHAR columns, 10,000,000 lines (a seeded 200,000-line unit tiled x50, compressed by dh_bgzf_deflate); "
+                   "file -> filled DuckDB vectors under harness/fake_duckdb, one scan thread (the reference's read_tabix is single-threaded)"}
+    path = os.path.join(CACHE, "bench_tabix.tsv.gz")
+    try:
+        rng = np.random.default_rng(0x7ab1)
+        pos = np.cumsum(rng.integers(1, 400, 200000))
+        unit = "".join("chr%d\t%d\t%d\tfeature_%d\t%.3f\n" % (1 + i * 22 // 200000, p, p + 150, i, s) for i, (p, s) in enumerate(zip(pos.tolist(), rng.random(200000).tolist()))).encode()
+        text = np.frombuffer(unit * 50, dtype=np.uint8)
+        comp, st = dh.bgzf_deflate(ctx, text)
+        comp.tofile(path)
+        n_lines = 200000 * 50
+        r = host_run(OUR_EXT, "read_tabix", path, threads=1, repeat=3)
+        assert r["rows"] == n_lines, r
+        out.update({"metric": "read_tabix_Mlines_per_s", "value": n_lines / 1e6 / r["best_seconds"], "unit": "Mlines/s", "seconds": r["best_seconds"],
+                    "cold_seconds": r["seconds"], "lines": n_lines, "text_gb": text.size / 1e9, "compressed_gb": comp.size / 1e9,
+                    "text_GBps": text.size / 1e9 / r["best_seconds"]})
+        if os.path.exists(REF_EXT):
+            q = host_run(REF_EXT, "read_tabix", path, threads=1)
+            out["reference"] = {"value": q["rows"] / 1e6 / q["seconds"], "unit": "Mlines/s", "seconds": q["seconds"], "rows": q["rows"]}
+    except Exception as e:  # noqa: BLE001
+        out["error"] = str(e)[:300]
+    if os.path.exists(path):
+        os.unlink(path)
+    return out
+
+
 def gen_bcf(n_sites, n_samples, seed):
     os.makedirs(CACHE, exist_ok=True)
     path = os.path.join(CACHE, f"bench_bcf_{n_sites}_{n_samples}_{seed}.bcf")
@@ -698,6 +726,7 @@ def main():
     if os.path.exists(big_path):
         os.unlink(big_path)
     bgzip = bench_bgzip(dh, ctx, unit_path, 4, ncpu) if rank == 0 and world == 1 and not args.no_ext else None
+    tabix = bench_tabix(dh, ctx) if rank == 0 and world == 1 and not args.no_ext and os.path.exists(FAKE_HOST) else None
 
     bcf_res = bench_bcf(dh, ctx, args, rank, barrier, rmax, rsum) if args.bcf_sites > 0 and os.path.exists(os.path.join(HARNESS, "gen_bcf")) else None
     shard_res = bench_contig_shards(dh, ctx, args, unit_path, rank, world, barrier, rmax, rsum)
@@ -738,7 +767,7 @@ def main():
                         "pcie_return_roofline_frac_bidir": (d2h_bytes / 1e9 / (e2e_step / 1e3)) / bi_d2h,
                         "duckdb_layout": {"value": total_rows / 1e6 / (e2e_duck_step / 1e3), "unit": "Mrecords/s", "ms_per_step": e2e_duck_step,
                                           "d2h_bytes_per_step": int(d2h_duck), "d2h_bytes_per_record": d2h_duck / max(rows, 1)}},
-                "ext_e2e": ext, "bgunzip_e2e": bgunzip, "bgzip_e2e": bgzip, "strong_scaling": strong,
+                "ext_e2e": ext, "bgunzip_e2e": bgunzip, "bgzip_e2e": bgzip, "read_tabix_e2e": tabix, "strong_scaling": strong,
                 "read_bcf": bcf_res, "contig_sharded": shard_res,
                 "cpu_baseline": cpu, "clocks": clk.summary(), "gpu_launches": int(launches), "host_cores": ncpu}
         print(json.dumps(line), flush=True)

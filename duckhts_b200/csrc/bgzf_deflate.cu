@@ -33,8 +33,15 @@ namespace dh {
 namespace dfl {
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int WARPS = 8;                      // per CTA
-constexpr int HASH_BITS = 12;
+#ifndef DH_DFL_HASH_BITS
+#define DH_DFL_HASH_BITS 11
+#endif
+#ifndef DH_DFL_CTAS
+#define DH_DFL_CTAS 4
+#endif
+constexpr int WARPS = 8;                      // per CTA; DH_DFL_CTAS CTAs per SM: the kernel waits on L1/L2 loads (ncu r2o: 4.0 of 10.75 cycles
+                                              // per instruction on the long scoreboard at 16 warps per SM), so shared memory is kept under 7 KB per warp
+constexpr int HASH_BITS = DH_DFL_HASH_BITS;
 constexpr uint32_t MIN_MATCH = 4, MAX_MATCH = 258;
 constexpr int NLL = 288, ND = 32, NCL = 19;
 constexpr int CRCW = 5 * 256 + 32;            // the same tables as the inflate's phase 2 (bgzf_inflate3.cu)
@@ -49,14 +56,17 @@ struct WarpSmem {
             uint16_t s[NLL];                  // symbol of sorted leaf i
             uint16_t parent[2 * NLL];
             uint8_t depth[2 * NLL];
-            uint16_t rle[NLL + ND + 4];       // code-length symbols: sym | extra << 5
+            uint16_t rle[NLL + ND + 4];       // code-length symbols: sym | extra << 5 (alive until the header is written)
         } hb;
+        uint32_t win[128];                    // sweep 2: output window (ring of 32-bit words); lies over hb.f, which is dead by then
     };
-    uint32_t hist_ll[NLL], hist_d[ND], hist_cl[NCL + 1];
-    uint32_t code_ll[NLL], code_d[ND], code_cl[NCL + 1];   // reversed code | length << 16
+    // the histograms turn into the code tables once the lengths are known and the block's size has been summed up
+    union { uint32_t hist_ll[NLL]; uint32_t code_ll[NLL]; };      // code tables: reversed code | length << 16
+    union { uint32_t hist_d[ND]; uint32_t code_d[ND]; };
+    union { uint32_t hist_cl[NCL + 1]; uint32_t code_cl[NCL + 1]; };
     uint8_t len_ll[NLL], len_d[ND], len_cl[NCL + 1];
-    uint32_t win[128];                        // sweep 2: output window (ring of 32-bit words)
 };
+static_assert(sizeof(WarpSmem) * WARPS * DH_DFL_CTAS <= 227 * 1024, "shared memory of the resident CTAs");
 
 __device__ __forceinline__ uint32_t load32u(const uint8_t *p) {     // unaligned 32-bit load (may touch up to 7 bytes behind p)
     const uint32_t *a = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
@@ -227,7 +237,7 @@ constexpr uint32_t SCRATCH_STRIDE = ROLE_BYTES + (0xff00u / MIN_MATCH + 64u) * 4
 // =====================================================================================================================
 // the kernel: warp w of the grid compresses block w of the launch
 // =====================================================================================================================
-__global__ void __launch_bounds__(WARPS * 32, 2)
+__global__ void __launch_bounds__(WARPS * 32, DH_DFL_CTAS)
 bgzf_deflate_kernel(const uint8_t *__restrict__ in, uint64_t in_bytes, uint32_t nblocks, uint8_t *__restrict__ slots,
                     uint8_t *__restrict__ scratch, uint32_t *__restrict__ csize, int level) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -341,15 +351,16 @@ bgzf_deflate_kernel(const uint8_t *__restrict__ in, uint64_t in_bytes, uint32_t 
         __syncwarp();
         // the run-length symbols survive the next build: it uses hb.f / s / parent / depth only
         build_lengths(sm, sm.hist_cl, sm.len_cl, NCL, 7, lane);
-        assign_codes(sm.len_ll, sm.code_ll, 286, lane);
-        assign_codes(sm.len_d, sm.code_d, 30, lane);
-        assign_codes(sm.len_cl, sm.code_cl, NCL, lane);
         uint64_t bits = 0;
         for (uint32_t i = lane; i < 286u; i += 32u) bits += (uint64_t)sm.hist_ll[i] * sm.len_ll[i];
         if (lane < 30u) bits += (uint64_t)sm.hist_d[lane] * sm.len_d[lane];
         if (lane < (uint32_t)NCL) bits += (uint64_t)sm.hist_cl[lane] * (sm.len_cl[lane] + (lane == 16u ? 2u : lane == 17u ? 3u : lane == 18u ? 7u : 0u));
 #pragma unroll
         for (int sft = 16; sft; sft >>= 1) bits += __shfl_xor_sync(FULL, bits, sft);
+        __syncwarp();
+        assign_codes(sm.len_ll, sm.code_ll, 286, lane);      // the histograms are gone from here on
+        assign_codes(sm.len_d, sm.code_d, 30, lane);
+        assign_codes(sm.len_cl, sm.code_cl, NCL, lane);
         if (lane == 0) {
             const uint8_t order[NCL] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
             ncl = NCL; while (ncl > 4u && sm.len_cl[order[ncl - 1u]] == 0) --ncl;
