@@ -170,6 +170,8 @@ SIGNATURES = {
     "dh_bgzf_dev_inflate_timed": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "dh_measure_pcie_bidir": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "dh_ctx_launch_count": (C.c_uint64, [C.c_void_p]),
+    "dh_bgzf_inflate_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.POINTER(BgzfBlock), C.c_uint32, C.c_void_p, C.c_uint64,
+                                          C.POINTER(C.c_uint64), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_void_p]),
 }
 
 

@@ -155,6 +155,26 @@ int dh_bgzf_dev_inflate_timed(dh_bgzf_dev *d, float *ms);
 int dh_bgzf_dev_check(dh_bgzf_dev *d, int64_t *bad_block, int32_t *bad_code);
 int dh_bgzf_dev_read(dh_bgzf_dev *d, uint64_t offset, uint8_t *dst, uint64_t n);
 
+/* ---- No-allocation inflate.  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The lane-group inflate
+ * kernel (inflate + CRC-32 + ISIZE per block, as dh_bgzf_inflate_host runs it) with its scratch — block descriptors, per-block
+ * verdicts, work ticket — in a fixed file-scope __device__ array of DH_NOALLOC_SCRATCH_BYTES that every GPU loading the library
+ * holds until exit; the call makes no cudaMalloc / cudaFree / cudaMallocHost and needs no dh_ctx.
+ *   d_comp   DEVICE buffer holding the BGZF image from file offset 0: block i starts at d_comp + blocks[i].coffset.  16-byte
+ *            aligned, and comp_cap (its size) must leave DH_NOALLOC_COMP_PAD readable bytes after every block (the kernel's bulk
+ *            copies run ahead of the payload).
+ *   blocks   HOST array from dh_bgzf_walk, n_blocks <= DH_NOALLOC_MAX_BLOCKS (more: DH_EINVAL, split the call).
+ *   d_out    DEVICE buffer; block i's bytes go to d_out + (sum of ISIZE of the blocks before it); *out_size = the total.
+ *   stream   a cudaStream_t (NULL = the default stream); the call returns after the stream has drained.
+ * Returns DH_OK, DH_EINVAL (limit or argument), DH_ECUDA, or DH_EDATA with *bad_block / *bad_code = the first failing block.
+ * Every call on a device shares the one array: calls of one process are serialised inside the library; do not rely on its
+ * contents between calls, and calls from different processes use their own copies. */
+#define DH_NOALLOC_MAX_BLOCKS 16384u
+#define DH_NOALLOC_SCRATCH_BYTES 590080u
+#define DH_NOALLOC_COMP_PAD 8192u
+int dh_bgzf_inflate_noalloc(int device, const uint8_t *d_comp, uint64_t comp_cap, const dh_bgzf_block *blocks, uint32_t n_blocks,
+                            uint8_t *d_out, uint64_t out_cap, uint64_t *out_size, int64_t *bad_block, int32_t *bad_code, void *stream);
+
 /* ---- A4-A15: read_bam scan -----------------------------------------------------------------------------
  * Replaces, for one BAM image in host memory, what bam_read_bind/local_init/bam_read_function get from htslib
  * (src/bam_reader.c:410-1038): sam_open + sam_hdr_read (bam_hdr_read, htslib/sam.c:229-342), then per record
