@@ -342,7 +342,7 @@ def _compact_batch_to_columns(bf, b):
             continue
         valid = validity_to_bool(b.validity[c], n)
         d = {"valid": valid if valid is not None else np.zeros(0, bool)}
-        if ty == "i":
+        if ty in ("i", "c"):        # "c": a CIGAR metric as a derived BIGINT column (dh_bam_set_projection, N3)
             d["i"] = arr(c, np.int64)
         elif ty == "f":
             d["f"] = arr(c, np.float64)
@@ -380,7 +380,7 @@ def batch_to_columns(bf, b):
             continue
         valid = validity_to_bool(b.validity[c], n)
         d = {"valid": valid if valid is not None else np.zeros(0, bool)}
-        if ty == "i":
+        if ty in ("i", "c"):        # "c": a CIGAR metric as a derived BIGINT column (dh_bam_set_projection, N3)
             d["i"] = np.frombuffer(C.string_at(b.data[c], n * 8), dtype=np.int64).copy() if n else np.zeros(0, np.int64)
         elif ty == "f":
             d["f"] = np.frombuffer(C.string_at(b.data[c], n * 8), dtype=np.float64).copy() if n else np.zeros(0, np.float64)
@@ -461,11 +461,11 @@ def bam_scan(ctx, data, tags=(), col_mask=None, voff=(0, VOFF_MAX), seg_comp=0, 
             for key in ("i", "f"):
                 if parts and key in parts[0]["tags"][k]:
                     d[key] = np.concatenate([p["tags"][k][key] for p in parts])
-                elif not parts and ty == key:
+                elif not parts and (ty == key or (ty == "c" and key == "i")):
                     d[key] = np.zeros(0, np.int64 if key == "i" else np.float64)
             if ty[0] == "B":
                 d["b"] = [x for p in parts for x in p["tags"][k]["b"]]
-            elif ty not in ("i", "f"):
+            elif ty not in ("i", "f", "c"):
                 d["s"] = [x for p in parts for x in p["tags"][k]["s"]]
             res["tags"].append(d)
         return res

@@ -384,6 +384,52 @@ __global__ void __launch_bounds__(128) bam_walk_kernel(const WalkParams p, const
     p.out[i] = w;
 }
 
+// ---- N3: CIGAR metrics as derived columns (tag request type 'c') ---------------------------------------------------------
+// What the reference's scalar UDFs compute from read_bam's CIGAR text (src/kmer_udf.c:197-269 parse_cigar_metrics, :271-293
+// cigar_has_operator_text, registered at :1231-1238), here from the binary CIGAR next to the decode that holds it in registers:
+//   t0 = 'S' cigar_has_soft_clip  'H' cigar_has_hard_clip (0 / 1)   'l' cigar_left_soft_clip   'r' cigar_right_soft_clip
+//        'q' cigar_query_length   'a' cigar_aligned_query_length    'R' cigar_reference_length  'o' cigar_has_op(CIGAR, t1) (0 / 1)
+// NULL (false returned) where the UDF returns NULL: "*" (no CIGAR), an operation of length 0 ("0M": op_len <= 0), an operation the
+// text parser does not know ('B', '?'); cigar_has_op answers false for "*" and stops at its operator before it sees later flaws.
+__device__ __forceinline__ bool cigar_metric(const uint8_t *u, const Rec &r, uint32_t metric, uint32_t opch, long long &out) {
+    out = 0;
+    if (r.cig_n == 0u) return metric == 'o';
+    long long ql = 0, al = 0, rl = 0, first_len = 0, last_len = 0;
+    uint32_t first_op = 15u, last_op = 15u;
+    bool soft = false, hard = false;
+    for (uint32_t k = 0; k < r.cig_n; ++k) {
+        const uint32_t c = ld32u(u, r.cigar + 4ll * k), ln = c >> 4, op = c & 15u;
+        if (ln == 0u) return false;
+        if (metric == 'o') {
+            if ((uint32_t)"MIDNSHP=XB??????"[op] == opch) { out = 1; return true; }
+            continue;
+        }
+        switch (op) {
+        case 0: case 7: case 8: ql += ln; al += ln; rl += ln; break;   // M = X
+        case 1: ql += ln; break;                                        // I
+        case 4: ql += ln; soft = true; break;                           // S
+        case 5: hard = true; break;                                     // H
+        case 2: case 3: rl += ln; break;                                // D N
+        case 6: break;                                                  // P
+        default: return false;
+        }
+        if (k == 0u) { first_op = op; first_len = ln; }
+        last_op = op;
+        last_len = ln;
+    }
+    switch (metric) {
+    case 'S': out = soft; break;
+    case 'H': out = hard; break;
+    case 'l': out = first_op == 4u ? first_len : 0; break;
+    case 'r': out = last_op == 4u ? last_len : 0; break;
+    case 'q': out = ql; break;
+    case 'a': out = al; break;
+    case 'R': out = rl; break;
+    default: break;   // 'o': operator not found
+    }
+    return true;
+}
+
 // =======================================================================================================
 // columnar decode: one warp per BGZF block, 32 records per step
 // =======================================================================================================
@@ -692,7 +738,11 @@ __global__ void __launch_bounds__(128) bam_decode_kernel(const __grid_constant__
                 if (!t.tags[k].want) continue;
                 const uint32_t ty_req = t.tags[k].type;
                 bool valid = false;
-                if (act) {
+                if (act && ty_req == 'c') {
+                    long long mv;
+                    valid = cigar_metric(u, r, t.tags[k].t0, t.tags[k].t1, mv);
+                    reinterpret_cast<int64_t *>(p.col[c])[row] = mv;
+                } else if (act) {
                     const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
                     if (ty_req == 'B') {
                         // bam_assign_list_int / _double (bam_reader.c:106-138): the writer follows the value's RUNTIME subtype
@@ -1010,7 +1060,11 @@ __global__ void __launch_bounds__(128) bam_decode_compact_kernel(const __grid_co
                 if (!t.tags[k].want) continue;
                 const uint32_t ty_req = t.tags[k].type;
                 bool valid = false;
-                if (act) {
+                if (act && ty_req == 'c') {
+                    long long mv;
+                    valid = cigar_metric(u, r, t.tags[k].t0, t.tags[k].t1, mv);
+                    reinterpret_cast<int64_t *>(p.col[c])[row] = mv;
+                } else if (act) {
                     const int64_t a = aux_find(u, r, t.tags[k].t0 | (t.tags[k].t1 << 8));
                     if (ty_req == 'B') {
                         uint64_t off8 = 0, len = 0;

@@ -1104,6 +1104,258 @@ bgzf_resolve4_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
     }
 }
 
+// =========================================================================================================
+// phase 2, fifth generation: one warp per block, BYTE-parallel, a window of recent output in shared memory, 16-byte stores
+// =========================================================================================================
+// What the two earlier forms showed: the warp-per-block kernel spends 2.4 warp instructions per output byte on
+// command-parallel byte loops (one lane per command: ragged lengths, dependency rounds, every long copy a serial whole-warp
+// episode) and moves every back-reference byte through L2/DRAM as 1-byte LDG/STG (3.8x DRAM read amplification); the
+// CTA-per-block kernel with the whole 64 KB window in shared memory fixes the traffic but keeps 3 blocks per SM in flight and
+// loses 3x.  This form keeps the warp per block (32 blocks per SM in flight) and turns the work around: lanes own OUTPUT BYTES.
+//   * 32 commands per step as before (one per lane; warp scans give each its destination); every command is two segments
+//     (its literals, its match);
+//   * the step's output span is done in chunks of <= 512 bytes: the segments that touch the chunk set a bit at their first byte
+//     in a 512-bit start mask and write a descriptor {start, source position, source ADDRESS} at their ordinal (two ballots);
+//   * rows of 32 bytes, one byte per lane: ordinal = population count of the start mask up to the byte, one 16-byte descriptor
+//     load, source address = descriptor base + offset -- ONE generic load whatever the source is: the literal stream, the
+//     warp's window of its last 1.5-3.5 KB of output in shared memory (linear, slid down when full), or the output buffer in global
+//     memory for anything older; a byte whose source lies in the same row takes it from the owning lane's register by shuffle
+//     (every earlier row is complete, so no other dependency exists); overlapping matches (distance < length) are folded to
+//     their first period by a multiply-shift modulo;
+//   * finished 16-byte units leave the window with st.global.v4 (north-star item (b)), aligned to the output buffer; only the
+//     first and last partial unit of a block use byte stores;
+//   * the CRC-32 (same lane-interleaved Horner form as resolve3) reads its 128-byte rows from the window as they complete: the
+//     output is never read back from global memory.
+// DRAM traffic = command + literal streams in, inflated bytes out, far sources.
+constexpr uint32_t R5_CH = 512, R5_BUF = 3456, R5_KEEP = 1536, R5_LST = 512;
+constexpr uint32_t R5_WARP_SMEM = R5_BUF + 64 * 16 + 64 * 4 + 64 + R5_LST;
+constexpr uint32_t R5_PER = 1u << 31;
+#ifndef DH_R5_ROWS
+#define DH_R5_ROWS 4
+#endif
+constexpr int R5_ROWS = DH_R5_ROWS;    // rows (of 32 bytes) per round of the row loop
+
+__global__ void __launch_bounds__(256, 4)
+bgzf_resolve5_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uint8_t *__restrict__ outbuf,
+                     int *__restrict__ status, const uint32_t *__restrict__ ncmd_in, const uint8_t *__restrict__ work) {
+    __shared__ uint32_t tabs_s[CRC3_WORDS];
+    __shared__ __align__(16) uint8_t warp_s[8][R5_WARP_SMEM];
+    for (int i = threadIdx.x; i < CRC3_WORDS; i += 256) tabs_s[i] = g_crc3[i];
+    __syncthreads();
+    auto tab = [&](uint32_t i) -> uint32_t { return tabs_s[i]; };
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t b = blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (b >= nblocks) return;
+    if (status[b] != INF_OK) return;
+    uint8_t *buf = warp_s[threadIdx.x >> 5];
+    uint4 *desc = reinterpret_cast<uint4 *>(buf + R5_BUF);
+    uint32_t *per = reinterpret_cast<uint32_t *>(buf + R5_BUF + 64 * 16);
+    uint32_t *mask = per + 64;
+    uint8_t *lstage = reinterpret_cast<uint8_t *>(mask + 16);     // the step's literals, staged by one coalesced 16-byte load per lane
+    const BlockDesc d = blocks[b];
+    uint8_t *o = outbuf + d.out_off;
+    const uint8_t *lit = work + d.cmd_off;
+    const uint32_t area = inflate_work_cap(d.isize);
+    const uint32_t *cmd_top = reinterpret_cast<const uint32_t *>(work + d.cmd_off + area) - 1;
+    const uint32_t n = ncmd_in[b];
+    // q = p + A: position in the 128-byte aligned frame of the output buffer; the window holds q in [wlo, wlo + R5_BUF), wlo a
+    // multiple of 128, so its 16-byte units and 128-byte rows are the buffer's
+    const uint32_t A = (uint32_t)((uintptr_t)o & 127u);
+    uint8_t *ob = o - A;
+    const uint32_t endq = A + d.isize;
+    const uint32_t fu0 = (A + 15u) >> 4;          // first unit that lies wholly inside the block
+    uint32_t fu = fu0;                            // next unit to store
+    bool head_pending = (A & 15u) != 0u;          // bytes in front of unit fu0 leave by byte stores
+    const uint32_t head_end = (fu0 << 4) < endq ? (fu0 << 4) : endq;
+    uint32_t a0q = (A + 127u) & ~127u;            // CRC: bytes [A, a0q) by lane 0, rows [a0q, rows_end), bytes [rows_end, endq) by lane 0
+    if (a0q > endq) a0q = endq;
+    const uint32_t rows_end = a0q + ((endq - a0q) & ~127u);
+    uint32_t cq = A, r = 0xffffffffu, H = 0;
+    bool first_row = true;
+    uint32_t pos = 0, lpos = 0, wlo = 0;
+    uint32_t le_mask;
+    asm volatile("mov.u32 %0, %%lanemask_le;" : "=r"(le_mask));      // (volatile: the compiler recomputed it in every row)
+    const uint32_t lt_mask = le_mask >> 1;
+    uint32_t c_next = lane < n ? cmd_top[-(int)lane] : 0x80000000u;
+
+    for (uint32_t k0 = 0; k0 < n; k0 += 32u) {
+        const uint32_t c = c_next;
+        {   // the next step's commands and this step's literals are on their way while the scans run
+            const uint32_t kn = k0 + 32u + lane;
+            c_next = kn < n ? cmd_top[-(int)kn] : 0x80000000u;
+        }
+        const uint32_t lmis = (uint32_t)((uintptr_t)(lit + lpos) & 15u);
+        const uint32_t lso = lpos - lmis + 16u * lane;              // offset in the block's work area of this lane's 16 staged bytes
+        uint4 lst = make_uint4(0u, 0u, 0u, 0u);
+        if (lso + 16u <= area) lst = *reinterpret_cast<const uint4 *>(lit + lso);
+        const bool isrun = (c >> 31) != 0u;
+        const uint32_t lr = isrun ? (c & 0x7fffffffu) : (c >> 23);
+        const uint32_t len = isrun ? 0u : ((c >> 15) & 255u) + 3u;
+        const uint32_t dist = (c & 0x7fffu) + 1u;
+        uint32_t ae = lr + len, le = lr;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const uint32_t va = __shfl_up_sync(FULL, ae, sft), vl = __shfl_up_sync(FULL, le, sft);
+            if (lane >= (uint32_t)sft) { ae += va; le += vl; }
+        }
+        const uint32_t dl = pos + ae - lr - len;     // where this command's literals go
+        const uint32_t dm = dl + lr;                 // where its match goes
+        const uint32_t me = dm + len;
+        const uint32_t src0 = dm - dist;             // first source byte of the match
+        const uint8_t *lsrc = lit + (lpos + le - lr);   // its literals in the literal stream
+        const uint32_t gend = pos + __shfl_sync(FULL, ae, 31);
+        if (gend > d.isize) break;                   // cannot happen after a clean phase 1; the ISIZE check below reports it
+        uint32_t permagic = 0u;
+        if (dist < len) permagic = dist | ((131072u / dist + 1u) << 9);
+        reinterpret_cast<uint4 *>(lstage)[lane] = lst;                // (the previous step's rows are behind a __syncwarp)
+        const uint32_t lrel = lpos + le - lr - (lpos - lmis);       // this command's literals inside the staged bytes
+        const bool lstaged = lrel + lr <= R5_LST;
+
+        for (uint32_t cb = pos; cb < gend; cb += R5_CH) {
+            const uint32_t ce = cb + R5_CH < gend ? cb + R5_CH : gend;
+            // ---- room in the window: slide the last R5_KEEP bytes (and whatever is not stored / summed yet) down ----
+            if (cb + A + R5_CH > wlo + R5_BUF) {
+                const uint32_t nlo = (cb + A - R5_KEEP) & ~127u;        // cb + A > R5_BUF - R5_CH here, so no underflow
+                const uint32_t delta = nlo - wlo, units = (cb + A - nlo + 15u) >> 4;
+                for (uint32_t u0 = 0; u0 < units; u0 += 32u) {
+                    uint4 x = make_uint4(0u, 0u, 0u, 0u);
+                    if (u0 + lane < units) x = *reinterpret_cast<const uint4 *>(buf + delta + ((u0 + lane) << 4));
+                    __syncwarp();
+                    if (u0 + lane < units) *reinterpret_cast<uint4 *>(buf + ((u0 + lane) << 4)) = x;
+                    __syncwarp();
+                }
+                wlo = nlo;
+            }
+            // ---- the segments of this chunk: start bits, descriptors at their ordinal ----
+            if (lane < 16u) mask[lane] = 0u;
+            __syncwarp();
+            const bool hasL = lr != 0u && dl < ce && dm > cb, hasM = len != 0u && dm < ce && me > cb;
+            const uint32_t bl = __ballot_sync(FULL, hasL), bm = __ballot_sync(FULL, hasM);   // (also orders the mask clear)
+            const uint32_t ord = __popc(bl & lt_mask) + __popc(bm & lt_mask);
+            if (hasL) {
+                const uint32_t st = (dl > cb ? dl : cb) - cb;
+                atomicOr(&mask[st >> 5], 1u << (st & 31u));
+                const uint64_t ga = (uint64_t)(uintptr_t)(lstaged ? lstage + lrel : lsrc);
+                desc[ord] = make_uint4(dl, 0x80000000u, (uint32_t)ga, (uint32_t)(ga >> 32));
+            }
+            if (hasM) {
+                const uint32_t st = (dm > cb ? dm : cb) - cb;
+                atomicOr(&mask[st >> 5], 1u << (st & 31u));
+                // sources inside the window come from there, older ones from the output buffer (all of those are stored: they lie
+                // at least R5_KEEP - 128 bytes behind the chunk)
+                const uint8_t *sp = src0 + A >= wlo ? buf + (src0 + A - wlo) : o + src0;
+                const uint64_t ga = (uint64_t)(uintptr_t)sp;
+                const uint32_t oi = ord + (hasL ? 1u : 0u);
+                desc[oi] = make_uint4(dm | (permagic ? R5_PER : 0u), src0, (uint32_t)ga, (uint32_t)(ga >> 32));
+                if (permagic) per[oi] = permagic;
+            }
+            __syncwarp();
+            // ---- rows of 32 bytes ----
+            const uint32_t nrow = (ce - cb + 31u) >> 5;
+            uint32_t acc = 0xffffffffu;                                     // (segments started in earlier rows) - 1
+            uint8_t *wp = buf + (cb + A - wlo) + lane;
+            // R5_ROWS rows per round: their loads are in flight together; a byte whose source lies inside the round's bytes takes it
+            // from the owning lane's register -- rows in order: first from the rows in front (final by then), then from its own row
+            for (uint32_t row = 0; row < nrow; row += R5_ROWS, wp += 32 * R5_ROWS) {
+                const uint32_t rs = cb + (row << 5);
+                uint32_t v[R5_ROWS], dd[R5_ROWS];
+                bool pend[R5_ROWS], valid[R5_ROWS];
+#pragma unroll
+                for (int j = 0; j < R5_ROWS; ++j) {
+                    const uint32_t p = rs + 32u * j + lane;
+                    const uint32_t m = mask[row + j];
+                    const uint32_t ai = acc + __popc(m & le_mask);
+                    acc += __popc(m);
+                    const uint4 D = desc[ai];
+                    uint32_t off = p - D.x;
+                    if ((int)off < 0) {                            // R5_PER: an overlapping match, fold into its first period
+                        const uint32_t pm_ = per[ai];
+                        off &= 0x7fffffffu;
+                        off -= ((off * (pm_ >> 9)) >> 17) * (pm_ & 511u);
+                    }
+                    const uint32_t sp = D.y + off;                 // source position (literals: negative)
+                    valid[j] = p < ce;
+                    pend[j] = valid[j] && (int)sp >= (int)rs;
+                    dd[j] = sp - rs;                               // relative to the round: 0 .. 32 j + lane - 1 = inside it
+                    v[j] = 0u;
+                    if (valid[j] && !pend[j]) v[j] = *reinterpret_cast<const uint8_t *>((uintptr_t)((((uint64_t)D.w << 32) | D.z) + off));
+                }
+#pragma unroll
+                for (int j = 0; j < R5_ROWS; ++j) {
+                    uint32_t pm = __ballot_sync(FULL, pend[j]);
+                    if (pm) {
+#pragma unroll
+                        for (int i = 0; i < j; ++i) {
+                            const uint32_t vv = __shfl_sync(FULL, v[i], (int)(dd[j] & 31u));
+                            if (pend[j] && (dd[j] >> 5) == (uint32_t)i) { v[j] = vv; pend[j] = false; }
+                        }
+                        pm = __ballot_sync(FULL, pend[j]);
+                        for (int it = 0; pm && it < 32; ++it) {   // (every pass settles the lowest pending lane at least)
+                            const uint32_t vv = __shfl_sync(FULL, v[j], (int)(dd[j] & 31u));
+                            if (pend[j] && !((pm >> (dd[j] & 31u)) & 1u)) { v[j] = vv; pend[j] = false; }
+                            pm = __ballot_sync(FULL, pend[j]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < R5_ROWS; ++j)
+                    if (valid[j]) wp[32 * j] = (uint8_t)v[j];
+                __syncwarp();
+            }
+            // ---- finished 16-byte units leave ----
+            const uint32_t avail = ce + A;
+            const uint32_t fend = avail >> 4;
+            for (uint32_t u = fu + lane; u < fend; u += 32u)
+                *reinterpret_cast<uint4 *>(ob + ((size_t)u << 4)) = *reinterpret_cast<const uint4 *>(buf + ((u << 4) - wlo));
+            if (fend > fu) fu = fend;
+            if (head_pending && avail >= head_end) {
+                const uint32_t q = (A & ~15u) + lane;
+                if (lane < 16u && q >= A && q < head_end) ob[q] = buf[q - wlo];
+                head_pending = false;
+            }
+            // ---- CRC-32 catches up from the window ----
+            if (cq < a0q) {
+                const uint32_t lim = a0q < avail ? a0q : avail;
+                if (lane == 0)
+                    for (uint32_t q = cq; q < lim; ++q) r = tab(4 * 256 + ((r ^ buf[q - wlo]) & 0xffu)) ^ (r >> 8);
+                cq = lim;
+            }
+            while (cq >= a0q && cq + 128u <= rows_end && cq + 128u <= avail) {
+                uint32_t w = *reinterpret_cast<const uint32_t *>(buf + (cq - wlo) + 4u * lane);
+                if (first_row && lane == 0) w ^= r;
+                first_row = false;
+                H = tab(H & 0xffu) ^ tab(256 + ((H >> 8) & 0xffu)) ^ tab(512 + ((H >> 16) & 0xffu)) ^ tab(768 + (H >> 24)) ^ w;
+                cq += 128u;
+            }
+            __syncwarp();
+        }
+        pos = gend;
+        lpos += __shfl_sync(FULL, le, 31);
+    }
+
+    // ---- the last partial unit, the end of the CRC, the footer checks ----
+    if (pos == d.isize) {
+        if (head_pending) {                            // a block that ends inside its first partial unit
+            const uint32_t q = (A & ~15u) + lane;
+            if (lane < 16u && q >= A && q < head_end) ob[q] = buf[q - wlo];
+        }
+        const uint32_t q = (fu << 4) + lane;
+        if (lane < 16u && q >= head_end && q < endq) ob[q] = buf[q - wlo];
+        if (rows_end > a0q) {
+            uint32_t v = crc_mulmod(tab(5 * 256 + lane), H);
+#pragma unroll
+            for (int sft = 16; sft; sft >>= 1) v ^= __shfl_xor_sync(FULL, v, sft);
+            r = v;
+        }
+        if (lane == 0)
+            for (uint32_t q2 = rows_end; q2 < endq; ++q2) r = tab(4 * 256 + ((r ^ buf[q2 - wlo]) & 0xffu)) ^ (r >> 8);
+    }
+    if (lane == 0) {
+        if (pos != d.isize) status[b] = INF_ERR_ISIZE;
+        else if ((r ^ 0xffffffffu) != d.crc) status[b] = INF_ERR_CRC;
+    }
+}
+
 // ---- host side ---------------------------------------------------------------------------------------------------
 static void build_crc3_tables(uint32_t *t) {
     uint32_t slice[8 * 256], x2n[32];
@@ -1120,10 +1372,10 @@ static void build_crc3_tables(uint32_t *t) {
 //   DH_RESOLVE_LDG=1  phase 2 keeps no shared-memory copy of the CRC tables (needed to fit next to phase 1),
 //   stream2 != null   phase 2 (and whatever the caller enqueues behind it) runs on stream2 behind `mid`, so that phase 1 of the
 //                     caller's NEXT launch on `stream` overlaps it.
-struct V3Config { bool p1_small, resolve_ldg, resolve4; };
+struct V3Config { bool p1_small, resolve_ldg, resolve4, resolve5; };
 static const V3Config &v3_config() {
     static const V3Config c = {getenv("DH_P1_SMALL") && atoi(getenv("DH_P1_SMALL")) != 0, getenv("DH_RESOLVE_LDG") && atoi(getenv("DH_RESOLVE_LDG")) != 0,
-                               getenv("DH_RESOLVE4") != nullptr};
+                               getenv("DH_RESOLVE4") != nullptr, !getenv("DH_RESOLVE5") || atoi(getenv("DH_RESOLVE5")) != 0};
     return c;
 }
 
@@ -1195,10 +1447,12 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
         if ((e = cudaStreamWaitEvent(stream2, mid, 0)) != cudaSuccess) return e;
         s2 = stream2;
     }
-    // phase 2: warp per block in global memory (bgzf_resolve3_kernel).  DH_RESOLVE4=1 selects the shared-memory kernel, measured r2b:
-    // 295.5 ms against 104.0 ms on the 100 M-record bench (468,651 blocks) -- three 72 KB CTAs per SM put 3 blocks in flight where
-    // the warp-per-block kernel has 32, and the window's dependency rounds (two barriers each) do not make one block 10x faster.
+    // phase 2: bgzf_resolve5_kernel (warp per block, byte-parallel rows, shared-memory window, 16-byte stores) is the default since
+    // r2v: 94.9 ms against 104.7 ms of bgzf_resolve3_kernel (DH_RESOLVE5=0: warp per block, command-parallel, in global memory) on the
+    // 100 M-record bench (468,651 blocks), and half its DRAM reads.  DH_RESOLVE4=1 selects the CTA-per-block shared-memory kernel,
+    // measured r2b: 295.5 ms -- three 72 KB CTAs per SM put 3 blocks in flight where the warp-per-block kernels have 32.
     if (cfg.resolve4) bgzf_resolve4_kernel<<<nblocks, R4_THREADS, sizeof(R4Smem), s2>>>(blocks, nblocks, out, status, ncmd, areas);
+    else if (cfg.resolve5) bgzf_resolve5_kernel<<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
     else if (cfg.resolve_ldg) bgzf_resolve3_kernel<false><<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
     else bgzf_resolve3_kernel<true><<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
     return cudaGetLastError();

@@ -22,6 +22,8 @@
 #include <thread>
 #include <vector>
 
+#include <ctype.h>
+
 #include "dh_scan.h"
 #include "inflate_core.cuh"
 
@@ -38,7 +40,7 @@ uint32_t col_width(const dh_bam *b, int c) {
     }
     if (c < BAM_CORE_COLS) return 16;
     char t = (char)b->tags[c - BAM_CORE_COLS].type;
-    return (t == 'i' || t == 'f') ? 8 : 16;
+    return (t == 'i' || t == 'f' || t == 'c') ? 8 : 16;
 }
 bool col_nullable(int c) { return c == COL_RG || c == COL_SAMPLE || c >= BAM_CORE_COLS; }
 // compact wire layout (DH_BAM_COMPACT_OUTPUT, include/duckhts_cuda.h)
@@ -50,7 +52,7 @@ uint32_t col_width_compact(const dh_bam *b, int c) {
     }
     if (c < BAM_CORE_COLS) return 4;   // POS, PNEXT, TLEN int32; RNAME, RNEXT, SAMPLE_ID codes; string lengths
     const char t = (char)b->tags[c - BAM_CORE_COLS].type;
-    return (t == 'i' || t == 'f') ? 8 : t == 'B' ? 16 : t == 'A' ? 1 : 4;
+    return (t == 'i' || t == 'f' || t == 'c') ? 8 : t == 'B' ? 16 : t == 'A' ? 1 : 4;
 }
 bool is_compact(const dh_bam *b) { return (b->mode & DH_BAM_COMPACT_OUTPUT) != 0; }
 
@@ -898,6 +900,13 @@ int dh_bam_set_projection(dh_bam *b, uint64_t col_mask, const dh_tag_req *tags, 
         r.t0 = (uint8_t)tags[i].tag[0];
         r.t1 = (uint8_t)tags[i].tag[1];
         char ty = tags[i].type == 'H' ? 'Z' : tags[i].type;
+        if (ty == 'c') {   // N3: a CIGAR metric as a derived BIGINT column (tag[0] = metric, tag[1] = the operator of cigar_has_op)
+            if (!strchr("SHlrqaRo", (char)r.t0) || !r.t0) { set_error("unknown CIGAR metric '%c'", tags[i].tag[0]); return DH_EINVAL; }
+            if (r.t0 == 'o') {
+                r.t1 = (uint8_t)toupper(r.t1);
+                if (!r.t1 || !strchr("MIDNSHP=X", (char)r.t1)) { set_error("cigar_has_op: '%c' is not a CIGAR operator", tags[i].tag[1]); return DH_EINVAL; }
+            }
+        } else
         if (ty != 'i' && ty != 'f' && ty != 'Z' && ty != 'A' && ty != 'B') { set_error("unsupported tag column type '%c'", tags[i].type); return DH_EINVAL; }
         r.type = (uint8_t)ty;
         r.want = 1;
@@ -1392,7 +1401,7 @@ int dh_bam_batch_checksum(dh_bam *b, const dh_bam_batch *batch, uint64_t *sums) 
         if (c < BAM_CORE_COLS) cp.kind[c] = CORE_KIND[c];
         else {
             const char t = (char)b->tags[(size_t)(c - BAM_CORE_COLS)].type;
-            cp.kind[c] = t == 'i' ? CK_TAG_I : t == 'f' ? CK_TAG_F : t == 'A' ? CK_TAG_A : t == 'B' ? CK_TAG_B : CK_STR;
+            cp.kind[c] = (t == 'i' || t == 'c') ? CK_TAG_I : t == 'f' ? CK_TAG_F : t == 'A' ? CK_TAG_A : t == 'B' ? CK_TAG_B : CK_STR;
         }
     }
     if (o.on_device) {

@@ -207,7 +207,7 @@ uint64_t dh_bam_n_blocks(const dh_bam *b);
  * 7 PNEXT 8 TLEN 9 SEQ 10 QUAL 11 READ_GROUP_ID 12 SAMPLE_ID, then one column per requested typed tag
  * (standard_tags, bam_reader.c:54-70).  col_mask bit c = column c is projected (projection pushdown,
  * bam_reader.c:676-679); tag k is column 13+k (tag columns past bit 63, i.e. k >= 51, are always projected).  Tag types: 'i' BIGINT, 'f' DOUBLE, 'Z' VARCHAR (SAM Z or H),
- * 'A' VARCHAR, 'B' LIST of 8-byte children (BIGINT or DOUBLE by the column's declared sub-type; the cell writer
+ * 'A' VARCHAR, 'c' BIGINT CIGAR metric (N3 below), 'B' LIST of 8-byte children (BIGINT or DOUBLE by the column's declared sub-type; the cell writer
  * follows the value's RUNTIME sub-type as bam_assign_list_int/_double do, bam_reader.c:106-138, 954-962). */
 #define DH_BAM_CORE_COLS 13
 #define DH_BAM_MAX_TAGS 63
@@ -383,6 +383,13 @@ void dh_free(void *p);
  * MAPQ >= min_mapq: the conjunctions of the reference's flag predicates (is_paired, is_unmapped, is_reverse, ...,
  * src/kmer_udf.c:1082-1183) and a mapping-quality floor.  All zero = no filter.  Set before the scan begins. */
 int dh_bam_set_filter(dh_bam *b, uint32_t flag_require, uint32_t flag_exclude, uint32_t min_mapq);
+/* CIGAR metrics as derived columns: the reference's scalar UDFs over read_bam's CIGAR text (src/kmer_udf.c:197-293, registered
+ * at :1231-1238) computed by the decode kernel from the binary CIGAR.  Request them through dh_bam_set_projection as tag columns of
+ * type 'c' (a BIGINT column, 8 bytes per row in both layouts, NULL where the UDF returns NULL: "*", an operation of length 0, an
+ * operation the text parser rejects):  tag[0] = 'S' cigar_has_soft_clip, 'H' cigar_has_hard_clip (0 / 1), 'l' cigar_left_soft_clip,
+ * 'r' cigar_right_soft_clip, 'q' cigar_query_length, 'a' cigar_aligned_query_length, 'R' cigar_reference_length,
+ * 'o' cigar_has_op(CIGAR, tag[1]) (0 / 1; tag[1] one of MIDNSHP=X, lower case accepted).  The SAM-flag predicates
+ * (is_paired ... is_supplementary, sam_flag_has) are single AND tests of the FLAG column; as row filters they are dh_bam_set_filter. */
 
 /* ---- B1-B10: read_bcf scan --------------------------------------------------------------------------------------
  * Replaces, for one BCF image in host memory, what bcf_read_bind / bcf_read_local_init / bcf_read_function get from

@@ -341,3 +341,48 @@ def test_reference_golden_vectors(ctx, name):
     assert len(lines) == len(exp)
     for i, (a, b) in enumerate(zip(lines, exp)):
         assert a == b, f"{name} line {i}"
+
+
+def test_cigar_metric_columns(ctx):
+    """N3: the reference's CIGAR UDFs (src/kmer_udf.c:197-293, :1231-1238) as derived columns of the decode kernel (tag requests of
+    type 'c'), against the restatement of those UDFs applied to the CIGAR column -- both layouts, clipped / padded / placeholder /
+    zero-length / 'B' operations, CIGARs of thousands of operations, mixed with real tag columns."""
+    from oracle import cigar_udf as cu
+
+    metrics = [(b"S", "c"), (b"H", "c"), (b"l", "c"), (b"r", "c"), (b"q", "c"), (b"a", "c"), (b"R", "c"), (b"oS", "c"), (b"oi", "c"), (b"oN", "c")]
+    tags = [(b"NM", "i")] + metrics + [(b"MD", "Z")]
+
+    def check(img, **kw):
+        rc, infl, _ = orc.bgzf_inflate(img)
+        assert rc == 0
+        exp = orc.bam_decode(infl, [(b"NM", "i"), (b"MD", "Z")])
+        cig = orc.strcol_list(exp["cigar"])
+        for compact in (False, True):
+            got = dh.bam_scan(ctx, img, tags=tags, compact=compact, **kw)
+            assert got["n"] == exp["n"] and got["cigar"] == cig
+            assert np.array_equal(got["tags"][0]["i"][exp["tags"][0]["valid"]], exp["tags"][0]["i"][exp["tags"][0]["valid"]])
+            assert got["tags"][-1]["s"] == orc.strcol_list(exp["tags"][1]["s"])
+            for k, (tg, _) in enumerate(metrics):
+                col = got["tags"][1 + k]
+                want = [cu.cigar_has_op(c, chr(tg[1])) if tg[:1] == b"o" else cu.cigar_metric(c, tg.decode()) for c in cig]
+                assert [bool(v) for v in col["valid"]] == [w is not None for w in want], (tg, compact)
+                assert [int(x) for x, w in zip(col["i"], want) if w is not None] == [w for w in want if w is not None], (tg, compact)
+        return exp
+
+    check(util.synth_bam_bytes(n_records=20000, seed=31, paired=True), batch_rows=3000)
+    for name in util.golden_names():
+        check(np.fromfile(os.path.join(util.GOLDEN, name + ".bam"), dtype=np.uint8))
+    ops = [[(5, "S"), (90, "M"), (5, "S")], [(5, "H"), (95, "M")], [(10, "M"), (2, "I"), (3, "D"), (7, "N"), (4, "P"), (8, "="), (9, "X")],
+           [(3, "S")], [(0, "M"), (5, "M")], [(5, "M"), (0, "I"), (3, "S")], [(4, "M"), (3, "B"), (2, "M")], [],
+           [(1, "M"), (1, "I")] * 1500, [(268435455, "N"), (1, "M")], [(2, "H"), (3, "S"), (10, "M"), (4, "S"), (1, "H")]]
+    recs = []
+    for k, cg in enumerate(ops):
+        qlen = sum(l for l, o in cg if o in "MIS=X")
+        recs.append(bam_record(qname=b"q%d" % k, cigar=cg, seq="A" * min(qlen, 4000) if cg else "ACGT", pos=100 + k))
+    img = util.make_bgzf(bam_header([(b"chr1", 1 << 29)]) + b"".join(recs))
+    exp = check(img)
+    assert exp["n"] >= 8        # (records whose CIGAR and SEQ lengths disagree end the scan like bam_read1: kept out of the list above)
+    with pytest.raises(dh.DuckhtsError):
+        dh.bam_scan(ctx, img, tags=[(b"oQ", "c")])
+    with pytest.raises(dh.DuckhtsError):
+        dh.bam_scan(ctx, img, tags=[(b"z", "c")])

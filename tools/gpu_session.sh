@@ -43,6 +43,12 @@ for stage in "$@"; do
         if [ $v = 4 ]; then export DH_RESOLVE4=1; else unset DH_RESOLVE4; fi
         timeout 600 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve$v', json.dumps({'value': d['value'], 'inflate': d['inflate'], 'e2e': d['e2e']['value']}))"
       done > gpurun_out/${T}_ab_resolve.log 2>&1; unset DH_RESOLVE4; cat gpurun_out/${T}_ab_resolve.log ;;
+    ab_resolve5) # inflate phase 2: the byte-parallel ring kernel (DH_RESOLVE5=1) against the warp-per-block kernel in global memory
+      DH_RESOLVE5=1 timeout 240 python -m pytest tests/test_bgzf_gpu.py tests/test_zz_no_alloc.py tests/test_bam_gpu.py -m gpu -x -q > gpurun_out/${T}_pytest_resolve5.log 2>&1; echo "pytest(resolve5) exit $?" | tee -a gpurun_out/${T}_pytest_resolve5.log; tail -15 gpurun_out/${T}_pytest_resolve5.log
+      for v in 0 1; do
+        export DH_RESOLVE5=$v
+        timeout 300 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve5=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'inflate': d['inflate'], 'kernel_ms': d['kernel_ms_per_step'], 'e2e': d['e2e']['value'], 'parity': [c['ok'] for c in d['parity']['checks']]}))"
+      done > gpurun_out/${T}_ab_resolve5.log 2>&1; unset DH_RESOLVE5; cat gpurun_out/${T}_ab_resolve5.log ;;
     ab_overlap) # who shares an SM with phase 1: pools of 227 KB (nobody) or 222 KB; phase 2 with / without its shared-memory tables; one or two inflate
       # streams; the other kernels asking for the same (maximal) shared-memory carve-out as phase 1 or not
       for cfg in ${AB_CFGS:-"0,0,1,0" "1,0,1,0" "1,0,1,1" "1,1,1,1" "1,1,2,1" "1,0,2,1"}; do
