@@ -1131,13 +1131,13 @@ constexpr uint32_t R5_CH = 512, R5_BUF = 3456, R5_KEEP = 1536, R5_LST = 512;
 constexpr uint32_t R5_WARP_SMEM = R5_BUF + 64 * 16 + 64 * 4 + 64 + R5_LST;
 constexpr uint32_t R5_PER = 1u << 31;
 #ifndef DH_R5_ROWS
-#define DH_R5_ROWS 4
+#define DH_R5_ROWS 2     // r2u/r2v: 2 rows 95.2 ms, 4 rows 94.9 ms (and spills): the loads of two rows in flight are enough
 #endif
 constexpr int R5_ROWS = DH_R5_ROWS;    // rows (of 32 bytes) per round of the row loop
 
 __global__ void __launch_bounds__(256, 4)
 bgzf_resolve5_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uint8_t *__restrict__ outbuf,
-                     int *__restrict__ status, const uint32_t *__restrict__ ncmd_in, const uint8_t *__restrict__ work) {
+                     int *__restrict__ status, const uint32_t *__restrict__ ncmd_in, const uint8_t *__restrict__ work, const int pf_mode) {
     __shared__ uint32_t tabs_s[CRC3_WORDS];
     __shared__ __align__(16) uint8_t warp_s[8][R5_WARP_SMEM];
     for (int i = threadIdx.x; i < CRC3_WORDS; i += 256) tabs_s[i] = g_crc3[i];
@@ -1177,27 +1177,34 @@ bgzf_resolve5_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
     asm volatile("mov.u32 %0, %%lanemask_le;" : "=r"(le_mask));      // (volatile: the compiler recomputed it in every row)
     const uint32_t lt_mask = le_mask >> 1;
     uint32_t c_next = lane < n ? cmd_top[-(int)lane] : 0x80000000u;
+    // the literals of a step are staged by one 16-byte load per lane, issued a whole step ahead (as soon as the scan has said where the
+    // next step's literals begin) and stored to shared memory when that step starts
+    auto stage_load = [&](uint32_t lp) -> uint4 {
+        const uint32_t lso = (lp & ~15u) + 16u * lane;             // offset in the block's work area (16-byte aligned like the area)
+        uint4 x = make_uint4(0u, 0u, 0u, 0u);
+        if (lso + 16u <= area) x = *reinterpret_cast<const uint4 *>(lit + lso);
+        return x;
+    };
+    uint4 lst = stage_load(0u);
 
     for (uint32_t k0 = 0; k0 < n; k0 += 32u) {
         const uint32_t c = c_next;
-        {   // the next step's commands and this step's literals are on their way while the scans run
+        {   // the next step's commands are on their way while the scan runs
             const uint32_t kn = k0 + 32u + lane;
             c_next = kn < n ? cmd_top[-(int)kn] : 0x80000000u;
         }
-        const uint32_t lmis = (uint32_t)((uintptr_t)(lit + lpos) & 15u);
-        const uint32_t lso = lpos - lmis + 16u * lane;              // offset in the block's work area of this lane's 16 staged bytes
-        uint4 lst = make_uint4(0u, 0u, 0u, 0u);
-        if (lso + 16u <= area) lst = *reinterpret_cast<const uint4 *>(lit + lso);
+        const uint32_t lmis = lpos & 15u;
         const bool isrun = (c >> 31) != 0u;
         const uint32_t lr = isrun ? (c & 0x7fffffffu) : (c >> 23);
         const uint32_t len = isrun ? 0u : ((c >> 15) & 255u) + 3u;
         const uint32_t dist = (c & 0x7fffu) + 1u;
-        uint32_t ae = lr + len, le = lr;
+        uint32_t sc = (lr + len) | (lr << 16);       // one scan for both sums: <= 32 * 513 output bytes, <= 32 * 255 literals per step
 #pragma unroll
         for (int sft = 1; sft < 32; sft <<= 1) {
-            const uint32_t va = __shfl_up_sync(FULL, ae, sft), vl = __shfl_up_sync(FULL, le, sft);
-            if (lane >= (uint32_t)sft) { ae += va; le += vl; }
+            const uint32_t vs = __shfl_up_sync(FULL, sc, sft);
+            if (lane >= (uint32_t)sft) sc += vs;
         }
+        const uint32_t ae = sc & 0xffffu, le = sc >> 16;
         const uint32_t dl = pos + ae - lr - len;     // where this command's literals go
         const uint32_t dm = dl + lr;                 // where its match goes
         const uint32_t me = dm + len;
@@ -1208,6 +1215,7 @@ bgzf_resolve5_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
         uint32_t permagic = 0u;
         if (dist < len) permagic = dist | ((131072u / dist + 1u) << 9);
         reinterpret_cast<uint4 *>(lstage)[lane] = lst;                // (the previous step's rows are behind a __syncwarp)
+        lst = stage_load(lpos + __shfl_sync(FULL, le, 31));           // the next step's literals
         const uint32_t lrel = lpos + le - lr - (lpos - lmis);       // this command's literals inside the staged bytes
         const bool lstaged = lrel + lr <= R5_LST;
 
@@ -1243,7 +1251,12 @@ bgzf_resolve5_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
                 atomicOr(&mask[st >> 5], 1u << (st & 31u));
                 // sources inside the window come from there, older ones from the output buffer (all of those are stored: they lie
                 // at least R5_KEEP - 128 bytes behind the chunk)
-                const uint8_t *sp = src0 + A >= wlo ? buf + (src0 + A - wlo) : o + src0;
+                const bool far = src0 + A < wlo;
+                const uint8_t *sp = far ? o + src0 : buf + (src0 + A - wlo);
+                if (far && pf_mode) {          // an old source: ask for its line(s) now, the rows that read it come a few hundred cycles later
+                    if (pf_mode == 1) { asm volatile("prefetch.global.L2 [%0];" ::"l"(sp)); asm volatile("prefetch.global.L2 [%0];" ::"l"(sp + (len - 1u))); }
+                    else { asm volatile("prefetch.global.L1 [%0];" ::"l"(sp)); asm volatile("prefetch.global.L1 [%0];" ::"l"(sp + (len - 1u))); }
+                }
                 const uint64_t ga = (uint64_t)(uintptr_t)sp;
                 const uint32_t oi = ord + (hasL ? 1u : 0u);
                 desc[oi] = make_uint4(dm | (permagic ? R5_PER : 0u), src0, (uint32_t)ga, (uint32_t)(ga >> 32));
@@ -1258,27 +1271,36 @@ bgzf_resolve5_kernel(const BlockDesc *__restrict__ blocks, uint32_t nblocks, uin
             // from the owning lane's register -- rows in order: first from the rows in front (final by then), then from its own row
             for (uint32_t row = 0; row < nrow; row += R5_ROWS, wp += 32 * R5_ROWS) {
                 const uint32_t rs = cb + (row << 5);
-                uint32_t v[R5_ROWS], dd[R5_ROWS];
+                uint32_t v[R5_ROWS], dd[R5_ROWS], off[R5_ROWS], ai[R5_ROWS];
+                uint4 D[R5_ROWS];
                 bool pend[R5_ROWS], valid[R5_ROWS];
+                uint32_t anyper = 0u;
 #pragma unroll
                 for (int j = 0; j < R5_ROWS; ++j) {
-                    const uint32_t p = rs + 32u * j + lane;
                     const uint32_t m = mask[row + j];
-                    const uint32_t ai = acc + __popc(m & le_mask);
+                    ai[j] = acc + __popc(m & le_mask);
                     acc += __popc(m);
-                    const uint4 D = desc[ai];
-                    uint32_t off = p - D.x;
-                    if ((int)off < 0) {                            // R5_PER: an overlapping match, fold into its first period
-                        const uint32_t pm_ = per[ai];
-                        off &= 0x7fffffffu;
-                        off -= ((off * (pm_ >> 9)) >> 17) * (pm_ & 511u);
-                    }
-                    const uint32_t sp = D.y + off;                 // source position (literals: negative)
-                    valid[j] = p < ce;
+                    D[j] = desc[ai[j]];
+                    off[j] = rs + 32u * j + lane - D[j].x;
+                    anyper |= off[j];
+                }
+                if (__any_sync(FULL, (int)anyper < 0)) {           // R5_PER: overlapping matches in this round, fold them into their first period
+#pragma unroll
+                    for (int j = 0; j < R5_ROWS; ++j)
+                        if ((int)off[j] < 0) {
+                            const uint32_t pm_ = per[ai[j]];
+                            off[j] &= 0x7fffffffu;
+                            off[j] -= ((off[j] * (pm_ >> 9)) >> 17) * (pm_ & 511u);
+                        }
+                }
+#pragma unroll
+                for (int j = 0; j < R5_ROWS; ++j) {
+                    const uint32_t sp = D[j].y + off[j];           // source position (literals: negative)
+                    valid[j] = rs + 32u * j + lane < ce;
                     pend[j] = valid[j] && (int)sp >= (int)rs;
                     dd[j] = sp - rs;                               // relative to the round: 0 .. 32 j + lane - 1 = inside it
                     v[j] = 0u;
-                    if (valid[j] && !pend[j]) v[j] = *reinterpret_cast<const uint8_t *>((uintptr_t)((((uint64_t)D.w << 32) | D.z) + off));
+                    if (valid[j] && !pend[j]) v[j] = *reinterpret_cast<const uint8_t *>((uintptr_t)((((uint64_t)D[j].w << 32) | D[j].z) + off[j]));
                 }
 #pragma unroll
                 for (int j = 0; j < R5_ROWS; ++j) {
@@ -1372,10 +1394,11 @@ static void build_crc3_tables(uint32_t *t) {
 //   DH_RESOLVE_LDG=1  phase 2 keeps no shared-memory copy of the CRC tables (needed to fit next to phase 1),
 //   stream2 != null   phase 2 (and whatever the caller enqueues behind it) runs on stream2 behind `mid`, so that phase 1 of the
 //                     caller's NEXT launch on `stream` overlaps it.
-struct V3Config { bool p1_small, resolve_ldg, resolve4, resolve5; };
+struct V3Config { bool p1_small, resolve_ldg, resolve4, resolve5; int r5_pf; };
 static const V3Config &v3_config() {
     static const V3Config c = {getenv("DH_P1_SMALL") && atoi(getenv("DH_P1_SMALL")) != 0, getenv("DH_RESOLVE_LDG") && atoi(getenv("DH_RESOLVE_LDG")) != 0,
-                               getenv("DH_RESOLVE4") != nullptr, !getenv("DH_RESOLVE5") || atoi(getenv("DH_RESOLVE5")) != 0};
+                               getenv("DH_RESOLVE4") != nullptr, !getenv("DH_RESOLVE5") || atoi(getenv("DH_RESOLVE5")) != 0,
+                               getenv("DH_R5_PF") ? atoi(getenv("DH_R5_PF")) : 1};
     return c;
 }
 
@@ -1452,7 +1475,7 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     // 100 M-record bench (468,651 blocks), and half its DRAM reads.  DH_RESOLVE4=1 selects the CTA-per-block shared-memory kernel,
     // measured r2b: 295.5 ms -- three 72 KB CTAs per SM put 3 blocks in flight where the warp-per-block kernels have 32.
     if (cfg.resolve4) bgzf_resolve4_kernel<<<nblocks, R4_THREADS, sizeof(R4Smem), s2>>>(blocks, nblocks, out, status, ncmd, areas);
-    else if (cfg.resolve5) bgzf_resolve5_kernel<<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
+    else if (cfg.resolve5) bgzf_resolve5_kernel<<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas, cfg.r5_pf);
     else if (cfg.resolve_ldg) bgzf_resolve3_kernel<false><<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
     else bgzf_resolve3_kernel<true><<<(nblocks + 7u) / 8u, 256, 0, s2>>>(blocks, nblocks, out, status, ncmd, areas);
     return cudaGetLastError();

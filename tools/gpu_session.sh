@@ -49,6 +49,15 @@ for stage in "$@"; do
         export DH_RESOLVE5=$v
         timeout 300 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('resolve5=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'inflate': d['inflate'], 'kernel_ms': d['kernel_ms_per_step'], 'e2e': d['e2e']['value'], 'parity': [c['ok'] for c in d['parity']['checks']]}))"
       done > gpurun_out/${T}_ab_resolve5.log 2>&1; unset DH_RESOLVE5; cat gpurun_out/${T}_ab_resolve5.log ;;
+    r5_pf) # phase 2: prefetch of old (global-memory) match sources when their descriptor is built: 0 none, 1 into L2, 2 into L1
+      for v in ${PFS:-0 1 2}; do
+        DH_R5_PF=$v timeout 300 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('r5_pf=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'phase_ms': d['inflate']['phase_ms'], 'kernel_ms': d['kernel_ms_per_step'], 'parity': [c['ok'] for c in d['parity']['checks']]}))"
+      done > gpurun_out/${T}_r5_pf.log 2>&1; cat gpurun_out/${T}_r5_pf.log ;;
+    sm_reserve) # SMs the inflate leaves to the column kernels in device-output mode (default 32, r1k sweep); again with the new phase 2
+      for v in ${RESERVES:-24 40}; do
+        DH_INFLATE_SM_RESERVE=$v timeout 300 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('reserve=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'kernel_ms': d['kernel_ms_per_step'], 'e2e': d['e2e']['value']}))"
+      done > gpurun_out/${T}_sm_reserve.log 2>&1; cat gpurun_out/${T}_sm_reserve.log ;;
+    ncu2) bash tools/gpu_ncu2.sh ;;
     ab_overlap) # who shares an SM with phase 1: pools of 227 KB (nobody) or 222 KB; phase 2 with / without its shared-memory tables; one or two inflate
       # streams; the other kernels asking for the same (maximal) shared-memory carve-out as phase 1 or not
       for cfg in ${AB_CFGS:-"0,0,1,0" "1,0,1,0" "1,0,1,1" "1,1,1,1" "1,1,2,1" "1,0,2,1"}; do
