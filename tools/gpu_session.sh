@@ -51,7 +51,7 @@ for stage in "$@"; do
       done > gpurun_out/${T}_ab_resolve5.log 2>&1; unset DH_RESOLVE5; cat gpurun_out/${T}_ab_resolve5.log ;;
     r5_pf) # phase 2: prefetch of old (global-memory) match sources when their descriptor is built: 0 none, 1 into L2, 2 into L1
       for v in ${PFS:-0 1 2}; do
-        DH_R5_PF=$v timeout 300 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('r5_pf=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'phase_ms': d['inflate']['phase_ms'], 'kernel_ms': d['kernel_ms_per_step'], 'parity': [c['ok'] for c in d['parity']['checks']]}))"
+        DH_R5_PF=$v timeout 170 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('r5_pf=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'phase_ms': d['inflate']['phase_ms'], 'kernel_ms': d['kernel_ms_per_step'], 'parity': [c['ok'] for c in d['parity']['checks']]}))"
       done > gpurun_out/${T}_r5_pf.log 2>&1; cat gpurun_out/${T}_r5_pf.log ;;
     sm_reserve) # SMs the inflate leaves to the column kernels in device-output mode (default 32, r1k sweep); again with the new phase 2
       for v in ${RESERVES:-24 40}; do
