@@ -51,6 +51,9 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
                                    uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream,
                                    cudaEvent_t between_phases = nullptr, cudaStream_t stream2 = nullptr, cudaEvent_t mid = nullptr);
 
+// blocks per launch that keep every SM busy to the end of phase 1: launch multiples of this (see bgzf_inflate3.cu)
+uint32_t bgzf_inflate_v3_round(int sm_count);
+
 // {index of the first block whose status is not 0, or -1; its status} -> out[0..1]; `out` may be pinned host memory
 cudaError_t launch_status_first_bad(const int *status, uint32_t nblocks, int *out, cudaStream_t stream);
 

@@ -1402,6 +1402,18 @@ static const V3Config &v3_config() {
     return c;
 }
 
+static uint32_t v3_retry_ctas(int sm_count) {
+    return P1Main::TAB_N < P1Retry::TAB_N ? (sm_count >= 64 ? (uint32_t)DH_RETRY_CTAS : sm_count >= 8 ? 1u : 0u) : 0u;
+}
+// Streams that phase 1 decodes at a time on `sm_count` SMs: every main CTA holds THREADS streams, one per lane, and a warp takes its
+// next 32 only when all of its lanes are done.  A launch of k * round blocks ends all its warps together; anything else leaves the
+// SMs to idle through the last generation (100 M-record bench, 468,651 blocks: launches of 2.06 rounds ran phase 1 in 153 ms, launches
+// of 3 rounds in 120 ms).
+uint32_t bgzf_inflate_v3_round(int sm_count) {
+    const uint32_t r = v3_retry_ctas(sm_count);
+    return ((uint32_t)sm_count > r ? (uint32_t)sm_count - r : 1u) * (uint32_t)P1Main::THREADS;
+}
+
 cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks, uint32_t nblocks, uint8_t *out, int *status,
                                    uint8_t *work, unsigned int *counter, int sm_count, cudaStream_t stream, cudaEvent_t between_phases,
                                    cudaStream_t stream2, cudaEvent_t mid) {
@@ -1452,7 +1464,7 @@ cudaError_t launch_bgzf_inflate_v3(const uint8_t *comp, const BlockDesc *blocks,
     e = cudaMemsetAsync(retry, 0, RETRY_HDR * sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     // main CTAs: one per SM at most, 6 warps x 32 streams each; retry CTAs (same pool as the main pass => none needed)
-    uint32_t retry_ctas = P1Main::TAB_N < P1Retry::TAB_N ? (sm_count >= 64 ? (uint32_t)DH_RETRY_CTAS : sm_count >= 8 ? 1u : 0u) : 0u;
+    const uint32_t retry_ctas = v3_retry_ctas(sm_count);
     uint32_t ctas = (nblocks + P1Main::THREADS - 1) / P1Main::THREADS;
     if (ctas > (uint32_t)sm_count - retry_ctas) ctas = (uint32_t)sm_count - retry_ctas;
     if (cfg.p1_small)

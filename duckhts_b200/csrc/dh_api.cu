@@ -647,7 +647,7 @@ dh_bgzf_dev *dh_bgzf_dev_load(dh_ctx *c, const uint8_t *comp, uint64_t comp_size
         size_t e = b;
         uint64_t cbase = d->bt.blocks[b].coffset & ~15ull;
         // a launch covers at most 2 GiB of compressed bytes (32-bit in_off) and 2^17 blocks (bounded work buffer)
-        const size_t quantum = (size_t)c->sm_count * 192u;   // streams phase 1 decodes at a time (6 warps per SM): launch whole rounds
+        const size_t quantum = bgzf_inflate_v3_round(c->sm_count);   // streams phase 1 decodes at a time: launch whole rounds
         const size_t max_blocks = phase_streams_two() ? 2u * quantum : (1u << 17);   // two streams: shorter launches interleave better
         while (e < nb && e - b < max_blocks && d->bt.blocks[e].coffset + d->bt.blocks[e].csize - cbase <= (2ull << 30)) ++e;
         if (e < nb && e - b > quantum) e = b + (e - b) / quantum * quantum;
