@@ -22,11 +22,12 @@
 //       decodes a literal uses the step's second lookup (the distance lookup of the match lanes) on the NEXT literal/length
 //       code and takes it too if it is a literal: two symbols per step on literal-heavy streams (r1h: -6 % BAM, -14 % BCF);
 //     * output = a LITERAL STREAM (bytes, 4 per store) + a COMMAND STREAM (one word per match), not final bytes.
-//   phase 2  bgzf_resolve3_kernel — ONE WARP PER BLOCK: 32 commands per step, warp scans give every lane its
-//     destination, literals are copied from the literal stream, matches are copied in dependency rounds (a lane
-//     waits only for earlier lanes of the same step whose destination it reads), then the warp computes the CRC-32
-//     of the finished block with coalesced loads (lane-interleaved Horner form: H = H*x^1024 + w through four
-//     256-entry tables) and compares CRC and ISIZE with the BGZF footer.
+//   phase 2  ONE WARP PER BLOCK places the literals, replays the matches and checks CRC-32 / ISIZE against the BGZF footer (CRC in a
+//     lane-interleaved Horner form: H = H*x^1024 + w through four 256-entry tables).  bgzf_resolve5_kernel (round 2, the default):
+//     lanes own output BYTES -- rows of 32 bytes over a shared-memory window of the block's recent output, one descriptor lookup and
+//     one generic load per byte, 16-byte stores; see its own header below.  bgzf_resolve3_kernel (round 1, DH_RESOLVE5=0): lanes own
+//     COMMANDS -- warp scans give every lane its destination, ragged byte loops in global memory, matches copied in dependency
+//     rounds.  bgzf_resolve4_kernel (DH_RESOLVE4=1): one CTA per block with the whole window in shared memory; measured slowest.
 // Streams whose tables do not fit the 892-entry pool either (litlen > 640 or litlen + distance > 892 entries; never
 // seen from zlib/libdeflate) stay flagged INF_NEEDS_V1 and are redone by the lane-group kernel (bgzf_inflate.cu).
 #include <stdlib.h>
