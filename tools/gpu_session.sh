@@ -1,8 +1,11 @@
 #!/bin/bash
-# One GPU session.  usage: tools/gpu_session.sh [stage ...]   stages: box tests newtests bench ref ncu scale2
+# One GPU session.  usage: TAG=r3x tools/gpu_session.sh [stage ...]   (every stage writes gpurun_out/${TAG}_*; plain runs before any ncu)
 #   box       machine facts                      tests     the whole -m gpu suite
-#   newtests  only this round's new GPU tests    bench     bench.py (both arms)
-#   ncu       launch list + --set full capture of the inflate kernels (after the plain runs)
+#   newtests  only this round's new GPU tests    bench / ref   bench.py, our arm / the reference arm
+#   ncu, ncu2 launch list + --set full capture of the inflate kernels (ncu2: COLS=1 adds the column kernels, OLD=1 resolve3)
+#   multi     NG GPUs: torchrun bench + one extension query over NG GPUs        extprof   where the extension's scan threads spend their time
+#   A/B stages (same process, same bytes, one switch): ab_resolve (resolve4), ab_resolve5, r5_pf, sm_reserve, ab_overlap
+#   text, deflate, cfg4: the GPU tests / the at-size run of those paths
 mkdir -p gpurun_out
 T=${TAG:-r2}
 for stage in "$@"; do
