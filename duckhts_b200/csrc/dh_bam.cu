@@ -226,13 +226,14 @@ cudaStream_t s_copy(dh_bam *b) { return b->ctx->copy_streams[0]; }
 cudaStream_t s_d2h(dh_bam *b) { return b->ctx->copy_streams[1]; }
 cudaStream_t s_inf(dh_bam *b) { return b->ctx->copy_streams[2]; }
 #ifndef DH_SM_RESERVE_DEVICE
-#define DH_SM_RESERVE_DEVICE 32
+#define DH_SM_RESERVE_DEVICE 36
 #endif
 // Phase 1 of the inflate is a persistent kernel that takes whole SMs (227 KB of shared memory each).  When batches go
 // back to the host, a few SMs stay free so that the decode kernels feeding the D2H copy engine are never locked out.
 // With column batches left on the device the walk/decode kernels of the previous segment are the second half of the work:
 // measured on the 100 M-record scan (r1k, DH_INFLATE_SM_RESERVE = 0 / 8 / 16 / 24 / 32 / 48): 226 / 251 / 270 / 284 / 301 / 285
-// Mrecords/s, so 32 SMs are left to them.
+// Mrecords/s, so 32 SMs were left to them; with the round-2 phase 2 and whole-round segments (r2x, r3g: 24 / 28 / 32 / 36 / 40 = 301 / 316 /
+// 321 / 325 / 296) it is 36.
 int inflate_sms(const dh_bam *b) {
     static const int reserve_dev = getenv("DH_INFLATE_SM_RESERVE") ? atoi(getenv("DH_INFLATE_SM_RESERVE")) : DH_SM_RESERVE_DEVICE;
     // BCF: the FORMAT decode of a segment is short next to its inflate (15 vs 16 ms per 177 MB): no reserve (2.8 vs 2.2 M sites/s)

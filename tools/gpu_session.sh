@@ -58,7 +58,7 @@ for stage in "$@"; do
       done > gpurun_out/${T}_r5_pf.log 2>&1; cat gpurun_out/${T}_r5_pf.log ;;
     sm_reserve) # SMs the inflate leaves to the column kernels in device-output mode (default 32, r1k sweep); again with the new phase 2
       for v in ${RESERVES:-24 40}; do
-        DH_INFLATE_SM_RESERVE=$v timeout 300 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('reserve=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'kernel_ms': d['kernel_ms_per_step'], 'e2e': d['e2e']['value']}))"
+        DH_INFLATE_SM_RESERVE=$v timeout 120 python bench.py --steps 3 --warmup 3 --no-ext --bcf-sites 0 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('reserve=$v', json.dumps({'value': d['value'], 'ms_per_step': d['ms_per_step'], 'kernel_ms': d['kernel_ms_per_step'], 'e2e': d['e2e']['value']}))"
       done > gpurun_out/${T}_sm_reserve.log 2>&1; cat gpurun_out/${T}_sm_reserve.log ;;
     ncu2) bash tools/gpu_ncu2.sh ;;
     ab_overlap) # who shares an SM with phase 1: pools of 227 KB (nobody) or 222 KB; phase 2 with / without its shared-memory tables; one or two inflate
