@@ -117,3 +117,30 @@ def test_the_simt_emulation_reports_divergence(r5):
     r5.dh_host_simt_selftest.restype = C.c_int
     msg = C.create_string_buffer(256)
     assert r5.dh_host_simt_selftest(msg, 256) == 7, msg.value
+
+
+def test_seeded_mixtures(r5):
+    """60 seeded mixtures of runs, repeats at random distances (1 .. 32 KiB), alphabet noise and text, random sizes and alignments."""
+    rng = np.random.default_rng(2026)
+    for case in range(60):
+        parts, total = [], 0
+        target = int(rng.integers(1, 65281))
+        while total < target:
+            kind = int(rng.integers(0, 5))
+            n = int(rng.integers(1, 3000))
+            if kind == 0:
+                p = bytes([int(rng.integers(0, 256))]) * n
+            elif kind == 1 and total > 0:
+                whole = b"".join(parts)
+                dist = int(rng.integers(1, min(total, 32768) + 1))
+                p = (whole[total - dist:] * (n // dist + 1))[:n]       # a copy from `dist` bytes back, overlapping when n > dist
+            elif kind == 2:
+                p = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+            elif kind == 3:
+                p = bytes(rng.choice(np.frombuffer(b"ACGTN\t\n0123", dtype=np.uint8), n))
+            else:
+                p = (b"chr%d\t%d\t.\tA\tG\t%d\tPASS\n" % (case % 22, total, n)) * (n // 20 + 1)
+            parts.append(p[:n])
+            total += len(parts[-1])
+        data = b"".join(parts)[:target]
+        check(r5, data, align=int(rng.integers(0, 128)), level=int(rng.choice([1, 6, 9])))
